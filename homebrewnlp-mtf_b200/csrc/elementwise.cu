@@ -1,0 +1,617 @@
+// Bandwidth-bound kernels of the mixer block: group norm (+gelu) forward/backward, activations,
+// residual arithmetic, embedding gather/scatter, softmax cross-entropy, parameter shadow casts.
+// All are coalesced, 16-byte vectorised where the layout allows, with warp-shuffle reductions.
+#include "obst_common.cuh"
+
+namespace obst {
+
+static constexpr float GN_EPS = 1e-5f;  // src/model/normalization.py:28
+
+// ================================================================================================
+// group norm forward: one warp per (token, head) row of `width` contiguous elements
+// ================================================================================================
+template <typename T, int MAXC>
+__global__ void __launch_bounds__(256) gn_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma,
+                                                      const T* __restrict__ beta, T* __restrict__ y, int64_t rows,
+                                                      int heads, int width, int act) {
+  constexpr int N = Vec16<T>::N;
+  const int lane = threadIdx.x & 31;
+  const int warps_per_block = blockDim.x >> 5;
+  const int chunks = width / N;
+  const float inv_w = 1.0f / (float)width;
+  for (int64_t row = (int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * warps_per_block) {
+    const T* xr = x + row * width;
+    const int h = (int)(row % heads);
+    Vec16<T> v[MAXC];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+        v[i].load(xr + c * N);
+#pragma unroll
+        for (int j = 0; j < N; ++j) s += v[i].v[j];
+      }
+    }
+    const float mean = warp_sum(s) * inv_w;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          v[i].v[j] -= mean;
+          q += v[i].v[j] * v[i].v[j];
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(q) * inv_w + GN_EPS);
+    T* yr = y + row * width;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+        Vec16<T> g, b;
+        if (gamma) g.load(gamma + (int64_t)h * width + c * N);
+        if (beta) b.load(beta + (int64_t)h * width + c * N);
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          float o = v[i].v[j] * rstd;
+          if (gamma) o *= g.v[j];
+          if (beta) o += b.v[j];
+          if (act == 1) o = gelu_obst(o);
+          v[i].v[j] = o;
+        }
+        v[i].store(yr + c * N);
+      }
+    }
+  }
+}
+
+// ================================================================================================
+// group norm backward.  grid = (token chunks, heads); a warp walks tokens of ONE head so the
+// dgamma/dbeta partials stay in registers; block-level reduce in shared memory, then fp32 atomics.
+// ================================================================================================
+template <typename T, int MAXC>
+__global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                      const T* __restrict__ gamma, const T* __restrict__ beta,
+                                                      T* __restrict__ dx, float* __restrict__ dgamma,
+                                                      float* __restrict__ dbeta, int64_t tokens, int heads, int width,
+                                                      int tokens_per_block, int act, int relu_mask, int dx_acc) {
+  constexpr int N = Vec16<T>::N;
+  extern __shared__ float s_red[];  // [2][width]
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int warps_per_block = blockDim.x >> 5;
+  const int chunks = width / N;
+  const int h = blockIdx.y;
+  const float inv_w = 1.0f / (float)width;
+  for (int i = threadIdx.x; i < 2 * width; i += blockDim.x) s_red[i] = 0.f;
+  __syncthreads();
+
+  float pg[MAXC][N], pb[MAXC][N];
+  Vec16<T> gam[MAXC], bet[MAXC];
+#pragma unroll
+  for (int i = 0; i < MAXC; ++i) {
+    const int c = lane + 32 * i;
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      pg[i][j] = 0.f;
+      pb[i][j] = 0.f;
+      gam[i].v[j] = 1.f;
+      bet[i].v[j] = 0.f;
+    }
+    if (c < chunks) {
+      if (gamma) gam[i].load(gamma + (int64_t)h * width + c * N);
+      if (beta) bet[i].load(beta + (int64_t)h * width + c * N);
+    }
+  }
+
+  const int64_t t0 = (int64_t)blockIdx.x * tokens_per_block;
+  const int64_t t1 = (t0 + tokens_per_block < tokens) ? t0 + tokens_per_block : tokens;
+  for (int64_t t = t0 + warp; t < t1; t += warps_per_block) {
+    const int64_t off = (t * heads + h) * width;
+    Vec16<T> xv[MAXC], gv[MAXC];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+        xv[i].load(x + off + c * N);
+        gv[i].load(dy + off + c * N);
+#pragma unroll
+        for (int j = 0; j < N; ++j) s += xv[i].v[j];
+      }
+    }
+    const float mean = warp_sum(s) * inv_w;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const float d = xv[i].v[j] - mean;
+          q += d * d;
+        }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(q) * inv_w + GN_EPS);
+    // g = dyv * gamma ; accumulate dgamma/dbeta ; row sums of g and g*z
+    float sg = 0.f, sgz = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const float z = (xv[i].v[j] - mean) * rstd;
+          float d = gv[i].v[j];
+          if (act == 1) d *= gelu_obst_grad(z * gam[i].v[j] + bet[i].v[j]);
+          pb[i][j] += d;
+          pg[i][j] += d * z;
+          const float g = d * gam[i].v[j];
+          gv[i].v[j] = g;
+          sg += g;
+          sgz += g * z;
+        }
+      }
+    }
+    const float mg = warp_sum(sg) * inv_w;
+    const float mgz = warp_sum(sgz) * inv_w;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+        Vec16<T> o;
+        if (dx_acc) o.load(dx + off + c * N);
+#pragma unroll
+        for (int j = 0; j < N; ++j) {
+          const float xraw = xv[i].v[j];
+          const float z = (xraw - mean) * rstd;
+          float d = rstd * (gv[i].v[j] - mg - z * mgz);
+          if (relu_mask && !(xraw > 0.f)) d = 0.f;
+          o.v[j] = dx_acc ? (o.v[j] + d) : d;
+        }
+        o.store(dx + off + c * N);
+      }
+    }
+  }
+  // block reduce of the affine gradients
+#pragma unroll
+  for (int i = 0; i < MAXC; ++i) {
+    const int c = lane + 32 * i;
+    if (c < chunks) {
+#pragma unroll
+      for (int j = 0; j < N; ++j) {
+        if (dgamma) atomicAdd(&s_red[c * N + j], pg[i][j]);
+        if (dbeta) atomicAdd(&s_red[width + c * N + j], pb[i][j]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < width; i += blockDim.x) {
+    if (dgamma) atomicAdd(&dgamma[(int64_t)h * width + i], s_red[i]);
+    if (dbeta) atomicAdd(&dbeta[(int64_t)h * width + i], s_red[width + i]);
+  }
+}
+
+template <typename T>
+static int gn_fwd_launch(const void* x, const void* gamma, const void* beta, void* y, int64_t rows, int heads,
+                         int width, int act, cudaStream_t st) {
+  constexpr int N = Vec16<T>::N;
+  OBST_REQUIRE(width % N == 0, "obst_gn_fwd: width %d must be a multiple of %d", width, N);
+  const int per_lane = (width / N + 31) / 32;
+  OBST_REQUIRE(per_lane <= 8, "obst_gn_fwd: width %d too large (max %d)", width, 256 * N);
+  const int wpb = 8;
+  int64_t blocks = (rows + wpb - 1) / wpb;
+  const int64_t cap = (int64_t)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+#define OBST_GN_FWD(MC)                                                                                       \
+  gn_fwd_kernel<T, MC><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma, (const T*)beta, \
+                                                                (T*)y, rows, heads, width, act)
+  if (per_lane <= 1) OBST_GN_FWD(1);
+  else if (per_lane <= 2) OBST_GN_FWD(2);
+  else if (per_lane <= 4) OBST_GN_FWD(4);
+  else OBST_GN_FWD(8);
+#undef OBST_GN_FWD
+  count_launch();
+  return check_launch("obst_gn_fwd");
+}
+
+template <typename T>
+static int gn_bwd_launch(const void* dy, const void* x, const void* gamma, const void* beta, void* dx, float* dgamma,
+                         float* dbeta, int64_t rows, int heads, int width, int act, int relu_mask, int dx_acc,
+                         cudaStream_t st) {
+  constexpr int N = Vec16<T>::N;
+  OBST_REQUIRE(width % N == 0, "obst_gn_bwd: width %d must be a multiple of %d", width, N);
+  OBST_REQUIRE(rows % heads == 0, "obst_gn_bwd: rows %lld not a multiple of heads %d", (long long)rows, heads);
+  const int per_lane = (width / N + 31) / 32;
+  OBST_REQUIRE(per_lane <= 8, "obst_gn_bwd: width %d too large (max %d)", width, 256 * N);
+  const int64_t tokens = rows / heads;
+  int tpb = 256;
+  // keep at least ~4 blocks per SM in flight when the problem is small
+  while (tpb > 8 && ((tokens + tpb - 1) / tpb) * heads < (int64_t)num_sms() * 4) tpb >>= 1;
+  dim3 grid((unsigned)((tokens + tpb - 1) / tpb), (unsigned)heads);
+  const size_t smem = 2 * (size_t)width * sizeof(float);
+#define OBST_GN_BWD(MC)                                                                                   \
+  gn_bwd_kernel<T, MC><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma, (const T*)beta, \
+                                                 (T*)dx, dgamma, dbeta, tokens, heads, width, tpb, act,    \
+                                                 relu_mask, dx_acc)
+  if (per_lane <= 1) OBST_GN_BWD(1);
+  else if (per_lane <= 2) OBST_GN_BWD(2);
+  else if (per_lane <= 4) OBST_GN_BWD(4);
+  else OBST_GN_BWD(8);
+#undef OBST_GN_BWD
+  count_launch();
+  return check_launch("obst_gn_bwd");
+}
+
+// ================================================================================================
+// activations and residual arithmetic: grid-stride, 16-byte vectors + scalar tail
+// ================================================================================================
+template <typename T, int KIND, bool BWD>
+__global__ void __launch_bounds__(256) act_kernel(const T* __restrict__ x, const T* __restrict__ dy,
+                                                   T* __restrict__ out, int64_t n) {
+  constexpr int N = Vec16<T>::N;
+  const int64_t nv = n / N;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
+    Vec16<T> a, g;
+    a.load(x + i * N);
+    if (BWD) g.load(dy + i * N);
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+      const float v = a.v[j];
+      float o;
+      if (KIND == 0) o = BWD ? (v > 0.f ? g.v[j] : 0.f) : fmaxf(v, 0.f);
+      else o = BWD ? g.v[j] * gelu_obst_grad(v) : gelu_obst(v);
+      a.v[j] = o;
+    }
+    a.store(out + i * N);
+  }
+  for (int64_t i = nv * N + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float v = to_f32(x[i]);
+    const float g = BWD ? to_f32(dy[i]) : 0.f;
+    float o;
+    if (KIND == 0) o = BWD ? (v > 0.f ? g : 0.f) : fmaxf(v, 0.f);
+    else o = BWD ? g * gelu_obst_grad(v) : gelu_obst(v);
+    out[i] = from_f32<T>(o);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) axpby_kernel(const T* a, const T* b, float sign, T* out, int64_t n) {
+  constexpr int N = Vec16<T>::N;
+  const int64_t nv = n / N;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
+    Vec16<T> va, vb;
+    va.load(a + i * N);
+    vb.load(b + i * N);
+#pragma unroll
+    for (int j = 0; j < N; ++j) va.v[j] = va.v[j] + sign * vb.v[j];
+    va.store(out + i * N);
+  }
+  for (int64_t i = nv * N + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    out[i] = from_f32<T>(to_f32(a[i]) + sign * to_f32(b[i]));
+}
+
+static inline unsigned ew_blocks(int64_t work_items) {
+  int64_t b = (work_items + 255) / 256;
+  const int64_t cap = (int64_t)num_sms() * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (unsigned)b;
+}
+
+// ================================================================================================
+// embedding gather / scatter-add
+// ================================================================================================
+template <typename T>
+__global__ void __launch_bounds__(256) gather_kernel(const int32_t* __restrict__ idx, const T* __restrict__ table,
+                                                      T* __restrict__ out, int64_t tokens, int vocab, int width) {
+  const int64_t total = tokens * width;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t t = i / width;
+    const int c = (int)(i - t * width);
+    int v = idx[t];
+    v = v < 0 ? 0 : (v >= vocab ? vocab - 1 : v);
+    out[i] = table[(int64_t)v * width + c];
+  }
+}
+
+// each block owns a token range, accumulates into a shared-memory copy of the table, then flushes
+template <typename T>
+__global__ void __launch_bounds__(256) scatter_kernel(const int32_t* __restrict__ idx, const T* __restrict__ dout,
+                                                       float* __restrict__ dtable, int64_t tokens, int vocab,
+                                                       int width, int tokens_per_block, int use_smem) {
+  extern __shared__ float s_tab[];
+  const int64_t t0 = (int64_t)blockIdx.x * tokens_per_block;
+  const int64_t t1 = (t0 + tokens_per_block < tokens) ? t0 + tokens_per_block : tokens;
+  const int tsz = vocab * width;
+  if (use_smem) {
+    for (int i = threadIdx.x; i < tsz; i += blockDim.x) s_tab[i] = 0.f;
+    __syncthreads();
+  }
+  const int64_t total = (t1 - t0) * width;
+  for (int64_t i = threadIdx.x; i < total; i += blockDim.x) {
+    const int64_t t = t0 + i / width;
+    const int c = (int)(i % width);
+    int v = idx[t];
+    v = v < 0 ? 0 : (v >= vocab ? vocab - 1 : v);
+    const float g = to_f32(dout[t * width + c]);
+    if (use_smem) atomicAdd(&s_tab[v * width + c], g);
+    else atomicAdd(&dtable[(int64_t)v * width + c], g);
+  }
+  if (use_smem) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < tsz; i += blockDim.x) {
+      const float v = s_tab[i];
+      if (v != 0.f) atomicAdd(&dtable[i], v);
+    }
+  }
+}
+
+// ================================================================================================
+// softmax cross-entropy (+z-loss, accuracy), forward and backward: one warp per token
+// ================================================================================================
+template <typename T, int MAXI>
+__global__ void __launch_bounds__(256) xent_kernel(const T* __restrict__ logits, const int32_t* __restrict__ targets,
+                                                    T* __restrict__ dlogits, double* __restrict__ sums, int64_t tokens,
+                                                    int vocab, float inv_n, float z_loss) {
+  __shared__ double s_acc[3];
+  if (threadIdx.x < 3) s_acc[threadIdx.x] = 0.0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int wpb = blockDim.x >> 5;
+  double a_nll = 0.0, a_z = 0.0, a_hit = 0.0;
+  for (int64_t t = (int64_t)blockIdx.x * wpb + (threadIdx.x >> 5); t < tokens; t += (int64_t)gridDim.x * wpb) {
+    const T* lr = logits + t * vocab;
+    float v[MAXI];
+    float mx = -INFINITY;
+    int arg = 0x7fffffff;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+      const int c = lane + 32 * i;
+      v[i] = (c < vocab) ? to_f32(lr[c]) : -INFINITY;
+      if (v[i] > mx) {  // strict: keeps the first index on ties (tf.argmax)
+        mx = v[i];
+        arg = c;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (om > mx || (om == mx && oa < arg)) {
+        mx = om;
+        arg = oa;
+      }
+    }
+    float se = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+      const int c = lane + 32 * i;
+      if (c < vocab) {
+        v[i] = expf(v[i] - mx);
+        se += v[i];
+      }
+    }
+    se = warp_sum(se);
+    const float logz = logf(se) + mx;
+    int tgt = targets[t];
+    tgt = tgt < 0 ? 0 : (tgt >= vocab ? vocab - 1 : tgt);
+    const float inv_se = 1.0f / se;
+    const float zc = 2.0f * z_loss * inv_n * logz;
+    T* dr = dlogits + t * vocab;
+#pragma unroll
+    for (int i = 0; i < MAXI; ++i) {
+      const int c = lane + 32 * i;
+      if (c < vocab) {
+        const float p = v[i] * inv_se;
+        const float d = (p - (c == tgt ? 1.f : 0.f)) * inv_n + zc * p;
+        dr[c] = from_f32<T>(d);
+      }
+    }
+    if (lane == 0) {
+      const float lt = to_f32(lr[tgt]);
+      a_nll += (double)(logz - lt);
+      a_z += (double)logz * (double)logz;
+      a_hit += (arg == tgt) ? 1.0 : 0.0;
+    }
+  }
+  if (lane == 0) {
+    atomicAdd(&s_acc[0], a_nll);
+    atomicAdd(&s_acc[1], a_z);
+    atomicAdd(&s_acc[2], a_hit);
+  }
+  __syncthreads();
+  if (threadIdx.x < 3 && s_acc[threadIdx.x] != 0.0) atomicAdd(&sums[threadIdx.x], s_acc[threadIdx.x]);
+}
+
+// ================================================================================================
+// parameter shadow cast (fp32 slice -> activation dtype, optional causal mask)
+// ================================================================================================
+template <typename T>
+__global__ void __launch_bounds__(256) cast_param_kernel(const float* __restrict__ src, T* __restrict__ dst, int64_t n,
+                                                          int tril_s) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    float v = src[i];
+    if (tril_s > 0) {
+      const int col = (int)(i % tril_s);
+      const int row = (int)((i / tril_s) % tril_s);
+      if (col > row) v = 0.f;
+    }
+    dst[i] = from_f32<T>(v);
+  }
+}
+
+}  // namespace obst
+
+using namespace obst;
+
+extern "C" {
+
+int obst_gn_fwd(int dtype, const void* x, const void* gamma, const void* beta, void* y, int64_t rows, int32_t heads,
+                int32_t width, int32_t act, void* stream) {
+  OBST_REQUIRE(rows >= 0 && heads > 0 && width > 0, "obst_gn_fwd: bad shape");
+  if (rows == 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == OBST_BF16) return gn_fwd_launch<bf16>(x, gamma, beta, y, rows, heads, width, act, st);
+  if (dtype == OBST_F32) return gn_fwd_launch<float>(x, gamma, beta, y, rows, heads, width, act, st);
+  OBST_REQUIRE(false, "obst_gn_fwd: bad dtype %d", dtype);
+}
+
+int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, const void* beta, void* dx,
+                float* dgamma, float* dbeta, int64_t rows, int32_t heads, int32_t width, int32_t act,
+                int32_t relu_mask, int32_t dx_accumulate, void* stream) {
+  OBST_REQUIRE(rows >= 0 && heads > 0 && width > 0, "obst_gn_bwd: bad shape");
+  if (rows == 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == OBST_BF16)
+    return gn_bwd_launch<bf16>(dy, x, gamma, beta, dx, dgamma, dbeta, rows, heads, width, act, relu_mask,
+                               dx_accumulate, st);
+  if (dtype == OBST_F32)
+    return gn_bwd_launch<float>(dy, x, gamma, beta, dx, dgamma, dbeta, rows, heads, width, act, relu_mask,
+                                dx_accumulate, st);
+  OBST_REQUIRE(false, "obst_gn_bwd: bad dtype %d", dtype);
+}
+
+int obst_act_fwd(int dtype, int32_t kind, const void* x, void* y, int64_t n, void* stream) {
+  OBST_REQUIRE(kind == 0 || kind == 1, "obst_act_fwd: bad kind %d", kind);
+  if (n <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == OBST_BF16) {
+    const unsigned b = ew_blocks(n / 8 + 1);
+    if (kind == 0) act_kernel<bf16, 0, false><<<b, 256, 0, st>>>((const bf16*)x, nullptr, (bf16*)y, n);
+    else act_kernel<bf16, 1, false><<<b, 256, 0, st>>>((const bf16*)x, nullptr, (bf16*)y, n);
+  } else if (dtype == OBST_F32) {
+    const unsigned b = ew_blocks(n / 4 + 1);
+    if (kind == 0) act_kernel<float, 0, false><<<b, 256, 0, st>>>((const float*)x, nullptr, (float*)y, n);
+    else act_kernel<float, 1, false><<<b, 256, 0, st>>>((const float*)x, nullptr, (float*)y, n);
+  } else {
+    OBST_REQUIRE(false, "obst_act_fwd: bad dtype %d", dtype);
+  }
+  count_launch();
+  return check_launch("obst_act_fwd");
+}
+
+int obst_act_bwd(int dtype, int32_t kind, const void* x, const void* dy, void* dx, int64_t n, void* stream) {
+  OBST_REQUIRE(kind == 0 || kind == 1, "obst_act_bwd: bad kind %d", kind);
+  if (n <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == OBST_BF16) {
+    const unsigned b = ew_blocks(n / 8 + 1);
+    if (kind == 0) act_kernel<bf16, 0, true><<<b, 256, 0, st>>>((const bf16*)x, (const bf16*)dy, (bf16*)dx, n);
+    else act_kernel<bf16, 1, true><<<b, 256, 0, st>>>((const bf16*)x, (const bf16*)dy, (bf16*)dx, n);
+  } else if (dtype == OBST_F32) {
+    const unsigned b = ew_blocks(n / 4 + 1);
+    if (kind == 0) act_kernel<float, 0, true><<<b, 256, 0, st>>>((const float*)x, (const float*)dy, (float*)dx, n);
+    else act_kernel<float, 1, true><<<b, 256, 0, st>>>((const float*)x, (const float*)dy, (float*)dx, n);
+  } else {
+    OBST_REQUIRE(false, "obst_act_bwd: bad dtype %d", dtype);
+  }
+  count_launch();
+  return check_launch("obst_act_bwd");
+}
+
+int obst_axpby(int dtype, const void* a, const void* b, float sign, void* out, int64_t n, void* stream) {
+  if (n <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == OBST_BF16)
+    axpby_kernel<bf16><<<ew_blocks(n / 8 + 1), 256, 0, st>>>((const bf16*)a, (const bf16*)b, sign, (bf16*)out, n);
+  else if (dtype == OBST_F32)
+    axpby_kernel<float><<<ew_blocks(n / 4 + 1), 256, 0, st>>>((const float*)a, (const float*)b, sign, (float*)out, n);
+  else
+    OBST_REQUIRE(false, "obst_axpby: bad dtype %d", dtype);
+  count_launch();
+  return check_launch("obst_axpby");
+}
+
+int obst_embed_gather(int dtype, const int32_t* idx, const void* table, void* out, int64_t tokens, int32_t vocab,
+                      int32_t width, void* stream) {
+  OBST_REQUIRE(vocab > 0 && width > 0, "obst_embed_gather: bad shape");
+  if (tokens <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned b = ew_blocks(tokens * width);
+  if (dtype == OBST_BF16)
+    gather_kernel<bf16><<<b, 256, 0, st>>>(idx, (const bf16*)table, (bf16*)out, tokens, vocab, width);
+  else if (dtype == OBST_F32)
+    gather_kernel<float><<<b, 256, 0, st>>>(idx, (const float*)table, (float*)out, tokens, vocab, width);
+  else
+    OBST_REQUIRE(false, "obst_embed_gather: bad dtype %d", dtype);
+  count_launch();
+  return check_launch("obst_embed_gather");
+}
+
+int obst_embed_scatter_add(int dtype, const int32_t* idx, const void* dout, float* dtable, int64_t tokens,
+                           int32_t vocab, int32_t width, void* stream) {
+  OBST_REQUIRE(vocab > 0 && width > 0, "obst_embed_scatter_add: bad shape");
+  if (tokens <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = (size_t)vocab * width * sizeof(float);
+  const int use_smem = smem <= 160 * 1024 ? 1 : 0;
+  int tpb = 1024;
+  while (tpb > 32 && (tokens + tpb - 1) / tpb < num_sms()) tpb >>= 1;
+  const unsigned blocks = (unsigned)((tokens + tpb - 1) / tpb);
+  if (dtype == OBST_BF16) {
+    if (use_smem && smem > 48 * 1024)
+      cudaFuncSetAttribute(scatter_kernel<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    scatter_kernel<bf16><<<blocks, 256, use_smem ? smem : 0, st>>>(idx, (const bf16*)dout, dtable, tokens, vocab,
+                                                                    width, tpb, use_smem);
+  } else if (dtype == OBST_F32) {
+    if (use_smem && smem > 48 * 1024)
+      cudaFuncSetAttribute(scatter_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    scatter_kernel<float><<<blocks, 256, use_smem ? smem : 0, st>>>(idx, (const float*)dout, dtable, tokens, vocab,
+                                                                     width, tpb, use_smem);
+  } else {
+    OBST_REQUIRE(false, "obst_embed_scatter_add: bad dtype %d", dtype);
+  }
+  count_launch();
+  return check_launch("obst_embed_scatter_add");
+}
+
+int obst_xent_fwd_bwd(int dtype, const void* logits, const int32_t* targets, void* dlogits, double* sums,
+                      int64_t tokens, int32_t vocab, float inv_n, float z_loss, void* stream) {
+  OBST_REQUIRE(vocab > 0 && vocab <= 1024, "obst_xent_fwd_bwd: vocab %d unsupported (1..1024)", vocab);
+  if (tokens <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t blocks = (tokens + 7) / 8;
+  const int64_t cap = (int64_t)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  const int per_lane = (vocab + 31) / 32;
+#define OBST_XENT(T, MI)                                                                                        \
+  xent_kernel<T, MI><<<(unsigned)blocks, 256, 0, st>>>((const T*)logits, targets, (T*)dlogits, sums, tokens, \
+                                                        vocab, inv_n, z_loss)
+  if (dtype == OBST_BF16) {
+    if (per_lane <= 8) OBST_XENT(bf16, 8);
+    else OBST_XENT(bf16, 32);
+  } else if (dtype == OBST_F32) {
+    if (per_lane <= 8) OBST_XENT(float, 8);
+    else OBST_XENT(float, 32);
+  } else {
+    OBST_REQUIRE(false, "obst_xent_fwd_bwd: bad dtype %d", dtype);
+  }
+#undef OBST_XENT
+  count_launch();
+  return check_launch("obst_xent_fwd_bwd");
+}
+
+int obst_cast_param(int dtype_dst, const float* src, void* dst, int64_t n, int32_t tril_s, void* stream) {
+  if (n <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned b = ew_blocks(n);
+  if (dtype_dst == OBST_BF16) cast_param_kernel<bf16><<<b, 256, 0, st>>>(src, (bf16*)dst, n, tril_s);
+  else if (dtype_dst == OBST_F32) cast_param_kernel<float><<<b, 256, 0, st>>>(src, (float*)dst, n, tril_s);
+  else OBST_REQUIRE(false, "obst_cast_param: bad dtype %d", dtype_dst);
+  count_launch();
+  return check_launch("obst_cast_param");
+}
+
+}  // extern "C"

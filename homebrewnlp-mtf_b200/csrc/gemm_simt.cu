@@ -1,0 +1,121 @@
+// SIMT (CUDA-core FMA) implementation of the obst_gemm descriptor: any strides, fp32 or bf16 inputs,
+// fp32 accumulation.  It serves (1) float32 configs, where the <=1e-5 parity bar rules out tensor-core
+// input rounding, (2) geometries the TMA path cannot address, (3) an on-device cross-check of the
+// tcgen05 kernel.  64x64 output tile per 256-thread block, 4x4 micro-tile per thread.
+#include "gemm_params.cuh"
+
+namespace obst {
+
+template <typename TI>
+__device__ __forceinline__ float ld_elem(const void* base, int64_t off) {
+  return to_f32(reinterpret_cast<const TI*>(base)[off]);
+}
+
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256) gemm_simt_kernel(const GemmParams p) {
+  __shared__ float As[16][64 + 4];
+  __shared__ float Bs[16][64 + 4];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;
+  const int g = blockIdx.z;
+  const int glo = g % p.GLO, ghi = g / p.GLO;
+  const int m0 = blockIdx.x * 64, n0 = blockIdx.y * 64;
+  if (p.tri == 3 && n0 > m0 + 63) return;
+  const int64_t a_base = (int64_t)glo * p.a_glo + (int64_t)ghi * p.a_ghi;
+  const int64_t b_base = (int64_t)glo * p.b_glo + (int64_t)ghi * p.b_ghi;
+
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  int k_begin = 0, k_end = p.KI;
+  if (p.tri == 1) k_end = min(p.KI, m0 + 64);
+  if (p.tri == 2) k_begin = (m0 / 16) * 16;
+
+  for (int ko = 0; ko < p.KO; ++ko) {
+    for (int k0 = k_begin; k0 < k_end; k0 += 16) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int e = tid + 256 * i;
+        int kk, mm;
+        if (p.a_k == 1) { kk = e & 15; mm = e >> 4; } else { mm = e & 63; kk = e >> 6; }
+        const int m = m0 + mm, k = k0 + kk;
+        float v = 0.f;
+        if (m < p.M && k < p.KI) {
+          v = ld_elem<TI>(p.A, a_base + (int64_t)m * p.a_mn + (int64_t)k * p.a_k + (int64_t)ko * p.a_ko);
+          if (p.tri == 1 && k > m) v = 0.f;
+          if (p.tri == 2 && k < m) v = 0.f;
+        }
+        As[kk][mm] = v;
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int e = tid + 256 * i;
+        int kk, nn;
+        if (p.b_k == 1) { kk = e & 15; nn = e >> 4; } else { nn = e & 63; kk = e >> 6; }
+        const int n = n0 + nn, k = k0 + kk;
+        float v = 0.f;
+        if (n < p.N && k < p.KI)
+          v = ld_elem<TI>(p.B, b_base + (int64_t)n * p.b_mn + (int64_t)k * p.b_k + (int64_t)ko * p.b_ko);
+        Bs[kk][nn] = v;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int kk = 0; kk < 16; ++kk) {
+        float a[4], b[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) a[i] = As[kk][ty * 4 + i];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = Bs[kk][tx * 4 + j];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      }
+      __syncthreads();
+    }
+  }
+
+  const int64_t d_base = (int64_t)glo * p.d_glo + (int64_t)ghi * p.d_ghi;
+  TO* D = reinterpret_cast<TO*>(p.D);
+  const TO* R = reinterpret_cast<const TO*>(p.R);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= p.M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= p.N) continue;
+      if (p.tri == 3 && n > m) continue;
+      const int64_t off = d_base + (int64_t)m * p.d_ld + n;
+      float v = acc[i][j];
+      switch (p.epi) {
+        case 1: v = fmaxf(v, 0.f); break;
+        case 2: v = to_f32(R[off]) + v; break;
+        case 3: v = to_f32(R[off]) - v; break;
+        case 4: v = (to_f32(R[off]) > 0.f) ? v : 0.f; break;
+        default: break;
+      }
+      if (p.accumulate) atomicAdd(reinterpret_cast<float*>(p.D) + off, v);
+      else D[off] = from_f32<TO>(v);
+    }
+  }
+}
+
+int gemm_simt_launch(const GemmParams& p, cudaStream_t st) {
+  dim3 grid((unsigned)((p.M + 63) / 64), (unsigned)((p.N + 63) / 64), (unsigned)(p.GLO * p.GHI));
+  OBST_REQUIRE(grid.y <= 65535 && grid.z <= 65535, "obst_gemm(simt): grid too large (N tiles %u, groups %u)", grid.y,
+               grid.z);
+  if (p.dtype_in == OBST_BF16 && p.dtype_out == OBST_BF16) gemm_simt_kernel<bf16, bf16><<<grid, 256, 0, st>>>(p);
+  else if (p.dtype_in == OBST_BF16 && p.dtype_out == OBST_F32) gemm_simt_kernel<bf16, float><<<grid, 256, 0, st>>>(p);
+  else if (p.dtype_in == OBST_F32 && p.dtype_out == OBST_F32) gemm_simt_kernel<float, float><<<grid, 256, 0, st>>>(p);
+  else if (p.dtype_in == OBST_F32 && p.dtype_out == OBST_BF16) gemm_simt_kernel<float, bf16><<<grid, 256, 0, st>>>(p);
+  else OBST_REQUIRE(false, "obst_gemm(simt): bad dtypes %d/%d", p.dtype_in, p.dtype_out);
+  count_launch();
+  return check_launch("obst_gemm(simt)");
+}
+
+}  // namespace obst

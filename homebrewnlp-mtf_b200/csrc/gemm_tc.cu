@@ -1,0 +1,654 @@
+// tcgen05 / TMEM / TMA implementation of the obst_gemm descriptor for bf16 operands (sm_100a).
+//
+// One persistent, warp-specialised kernel serves every contraction of the mixer step:
+//   warp 0      : TMA producer   (cp.async.bulk.tensor, 5-D maps, 128B swizzle, 4-stage mbarrier ring)
+//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (128 x BN x 16, fp32 accumulate in TMEM)
+//   warps 2..5  : epilogue       (tcgen05.ld 32x32b -> registers -> fused op -> 16-byte global stores / fp32 red)
+// Two 256-column TMEM accumulators let the epilogue of tile i overlap the MMAs of tile i+1.
+// Operands may be K-major or MN-major in global memory (the smem/instruction descriptors carry the
+// majorness), so forward, dgrad and wgrad all read the tensors where they lie: no transposes.
+// Triangular modes skip whole k-blocks / output tiles of the causal token-mixing matrices.
+#include <cuda.h>
+
+#include <mutex>
+#include <string>
+#include <unordered_map>
+
+#include "gemm_params.cuh"
+
+namespace obst {
+
+static constexpr int BM = 128;
+static constexpr int BK = 64;
+static constexpr int STAGES = 4;
+static constexpr int A_STAGE_BYTES = BM * BK * 2;        // 16 KB
+static constexpr int B_STAGE_BYTES = 256 * BK * 2;       // 32 KB (BN <= 256)
+static constexpr int TMEM_COLS = 512;
+static constexpr int ACC_STRIDE = 256;                   // columns per accumulator buffer
+static constexpr int TC_THREADS = 192;
+static constexpr int SMEM_BAR_OFF = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
+static constexpr int SMEM_BYTES = SMEM_BAR_OFF + 256 + 1024;  // barriers + alignment slack
+
+struct TcParams {
+  void* D;
+  const void* R;
+  int64_t d_ld, d_glo, d_ghi;
+  int32_t M, N;
+  int32_t nkb_inner, nkb;  // k-blocks per ko, total k-blocks
+  int32_t GLO, G;
+  int32_t BN, tiles_m, tiles_n, total_tiles;
+  int32_t splits, tri, epi, accumulate, out_f32;
+  int32_t a_mn, b_mn;                  // 1 = MN-major operand
+  int32_t a_uglo, a_ughi, a_uko;       // does the operand depend on g_lo / g_hi / ko
+  int32_t b_uglo, b_ughi, b_uko;
+};
+
+// ------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must trap, never hang the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int which) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if ((++spins & 0x3ff) == 0 && clock64() - t0 > 4000000000ll) {
+      printf("obst gemm_tc: mbarrier timeout (role %d, block %d, thread %d)\n", which, (int)blockIdx.x,
+             (int)threadIdx.x);
+      __trap();
+    }
+  }
+}
+
+__device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2,
+                                            int c3, int c4) {
+  asm volatile(
+      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], "
+      "[%2];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+               "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+// D[tmem] (+)= A[smem] * B[smem], bf16 inputs, fp32 accumulate
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrive once all previously issued tcgen05 ops of this thread have completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
+// shared-memory matrix descriptor (SWIZZLE_128B, descriptor version 1)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fff);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+  d |= (uint64_t)1 << 46;  // version
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+
+struct Tile {
+  int m0, n0, glo, ghi, kb0, kb1;
+};
+
+__device__ __forceinline__ bool get_tile(const TcParams& p, int tile, Tile& t) {
+  const int nt = tile % p.tiles_n;
+  int r = tile / p.tiles_n;
+  const int mt = r % p.tiles_m;
+  r /= p.tiles_m;
+  const int g = r % p.G;
+  const int sp = r / p.G;
+  t.m0 = mt * BM;
+  t.n0 = nt * p.BN;
+  t.glo = g % p.GLO;
+  t.ghi = g / p.GLO;
+  if (p.tri == 3 && t.n0 > t.m0 + BM - 1) return false;
+  int kb0 = 0, kb1 = p.nkb;
+  if (p.tri == 1) kb1 = min(p.nkb, (t.m0 + BM + BK - 1) / BK);
+  if (p.tri == 2) kb0 = t.m0 / BK;
+  if (p.splits > 1) {
+    const int len = kb1 - kb0;
+    const int per = (len + p.splits - 1) / p.splits;
+    kb0 += sp * per;
+    kb1 = min(kb1, kb0 + per);
+  }
+  t.kb0 = kb0;
+  t.kb1 = kb1;
+  return kb1 > kb0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// epilogue helpers: 8 consecutive output columns of one row
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void epi_apply(float (&v)[8], const float (&r)[8], int epi) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    switch (epi) {
+      case 1: v[j] = fmaxf(v[j], 0.f); break;
+      case 2: v[j] = r[j] + v[j]; break;
+      case 3: v[j] = r[j] - v[j]; break;
+      case 4: v[j] = r[j] > 0.f ? v[j] : 0.f; break;
+      default: break;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + STAGES * A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM_BAR_OFF);
+  uint64_t* full_bar = bars;                 // [STAGES]
+  uint64_t* empty_bar = bars + STAGES;       // [STAGES]
+  uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
+  uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tfull_bar[s], 1);
+      mbar_init(&tempty_bar[s], 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_ptr, TMEM_COLS);
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + p.BN * BK * 2);
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      Tile t;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        if (!get_tile(p, tile, t)) continue;
+        const int a2 = p.a_uglo ? t.glo : 0, a3 = p.a_ughi ? t.ghi : 0;
+        const int b2 = p.b_uglo ? t.glo : 0, b3 = p.b_ughi ? t.ghi : 0;
+        for (int kb = t.kb0; kb < t.kb1; ++kb) {
+          const int ki = kb % p.nkb_inner, ko = kb / p.nkb_inner;
+          const int k0 = ki * BK;
+          mbar_wait(&empty_bar[stage], phase ^ 1, 0);
+          mbar_expect_tx(&full_bar[stage], stage_bytes);
+          uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
+          uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
+          const int a4 = p.a_uko ? ko : 0, b4 = p.b_uko ? ko : 0;
+          if (!p.a_mn) {
+            tma_load_5d(sa, &tmA, &full_bar[stage], k0, t.m0, a2, a3, a4);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_5d(sa + j * (64 * BK * 2), &tmA, &full_bar[stage], t.m0 + 64 * j, k0, a2, a3, a4);
+          }
+          if (!p.b_mn) {
+            tma_load_5d(sb, &tmB, &full_bar[stage], k0, t.n0, b2, b3, b4);
+          } else {
+            for (int j = 0; j < p.BN / 64; ++j)
+              tma_load_5d(sb + j * (64 * BK * 2), &tmB, &full_bar[stage], t.n0 + 64 * j, k0, b2, b3, b4);
+          }
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
+                             ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      // K-major: 8-row groups 1024 B apart (SBO), 32 B per UMMA_K step.
+      // MN-major: 64-element MN groups 8192 B apart (LBO), 8-row k groups 1024 B apart (SBO), 2048 B per UMMA_K.
+      const uint32_t a_lbo = p.a_mn ? 64 * BK * 2 : 16, b_lbo = p.b_mn ? 64 * BK * 2 : 16;
+      const uint32_t a_kadv = p.a_mn ? 2048 : 32, b_kadv = p.b_mn ? 2048 : 32;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      Tile t;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        if (!get_tile(p, tile, t)) continue;
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1, 1);
+        tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * ACC_STRIDE);
+        for (int kb = t.kb0; kb < t.kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase, 2);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
+          const uint32_t sb = smem_u32(smem_b + stage * B_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t adesc = make_smem_desc(sa + k * a_kadv, a_lbo, 1024);
+            const uint64_t bdesc = make_smem_desc(sb + k * b_kadv, b_lbo, 1024);
+            umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > t.kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tfull_bar[acc]);  // accumulator ready for the epilogue
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are the ones this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    Tile t;
+    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+      if (!get_tile(p, tile, t)) continue;
+      mbar_wait(&tfull_bar[acc], acc_phase, 3);
+      tcgen05_fence_after();
+      const int m = t.m0 + quarter * 32 + lane;
+      const bool row_ok = m < p.M;
+      const int64_t row_off = (int64_t)t.glo * p.d_glo + (int64_t)t.ghi * p.d_ghi + (int64_t)m * p.d_ld;
+      const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
+      for (int c = 0; c < p.BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(taddr0 + (uint32_t)(c * 32), r);
+        tmem_ld_wait();
+        if (row_ok) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int n = t.n0 + c * 32 + q * 8;
+            if (n >= p.N) continue;
+            float v[8], rr[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              v[j] = __uint_as_float(r[q * 8 + j]);
+              rr[j] = 0.f;
+            }
+            if (p.out_f32) {
+              float* dp = reinterpret_cast<float*>(p.D) + row_off + n;
+              if (p.epi >= 2) {
+                const float4 r0 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.R) + row_off + n);
+                const float4 r1 =
+                    *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.R) + row_off + n + 4);
+                rr[0] = r0.x; rr[1] = r0.y; rr[2] = r0.z; rr[3] = r0.w;
+                rr[4] = r1.x; rr[5] = r1.y; rr[6] = r1.z; rr[7] = r1.w;
+              }
+              epi_apply(v, rr, p.epi);
+              if (p.accumulate) {
+                if (p.tri == 3 && n + 7 > m) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j)
+                    if (n + j <= m) atomicAdd(dp + j, v[j]);
+                } else {
+                  red_add_v4(dp, v[0], v[1], v[2], v[3]);
+                  red_add_v4(dp + 4, v[4], v[5], v[6], v[7]);
+                }
+              } else {
+                if (p.tri == 3) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j)
+                    if (n + j > m) v[j] = 0.f;
+                }
+                *reinterpret_cast<float4*>(dp) = make_float4(v[0], v[1], v[2], v[3]);
+                *reinterpret_cast<float4*>(dp + 4) = make_float4(v[4], v[5], v[6], v[7]);
+              }
+            } else {
+              bf16* dp = reinterpret_cast<bf16*>(p.D) + row_off + n;
+              if (p.epi >= 2) {
+                const uint4 ru = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.R) + row_off + n);
+                const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z),
+                             f3 = unpack_bf16x2(ru.w);
+                rr[0] = f0.x; rr[1] = f0.y; rr[2] = f1.x; rr[3] = f1.y;
+                rr[4] = f2.x; rr[5] = f2.y; rr[6] = f3.x; rr[7] = f3.y;
+              }
+              epi_apply(v, rr, p.epi);
+              if (p.tri == 3) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                  if (n + j > m) v[j] = 0.f;
+              }
+              uint4 o;
+              o.x = pack_bf16x2(v[0], v[1]);
+              o.y = pack_bf16x2(v[2], v[3]);
+              o.z = pack_bf16x2(v[4], v[5]);
+              o.w = pack_bf16x2(v[6], v[7]);
+              *reinterpret_cast<uint4*>(dp) = o;
+            }
+          }
+        }
+      }
+      tcgen05_fence_before();
+      mbar_arrive(&tempty_bar[acc]);  // 128 arrivals release the accumulator back to the MMA warp
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side: tensor-map construction (cached) and launch
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                        CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                        CUtensorMapFloatOOBfill);
+
+static PFN_tmapEncodeTiled get_encode_fn() {
+  static PFN_tmapEncodeTiled fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_tmapEncodeTiled>(ptr);
+  }
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  uint64_t dims[5];
+  uint64_t strides[4];
+  uint32_t box[2];
+};
+
+static std::mutex g_map_mu;
+static std::unordered_map<std::string, CUtensorMap> g_map_cache;
+
+// operand view: 5-D (inner, outer, g_lo, g_hi, ko); rows = M (A) or N (B); box_rows = rows per TMA box
+static int make_operand_map(const void* ptr, int64_t s_mn, int64_t s_k, int64_t s_ko, int64_t s_glo, int64_t s_ghi,
+                            int rows, int KI, int KO, int GLO, int GHI, bool mn_major, int box_rows, CUtensorMap* out,
+                            bool strict) {
+  MapKey key;
+  memset(&key, 0, sizeof(key));
+  key.ptr = ptr;
+  const uint64_t es = 2;
+  if (mn_major) {
+    key.dims[0] = (uint64_t)rows;
+    key.dims[1] = (uint64_t)KI;
+    key.strides[0] = (uint64_t)s_k * es;
+    key.box[0] = 64;
+    key.box[1] = 64;
+  } else {
+    key.dims[0] = (uint64_t)KI;
+    key.dims[1] = (uint64_t)rows;
+    key.strides[0] = (uint64_t)s_mn * es;
+    key.box[0] = 64;
+    key.box[1] = (uint32_t)box_rows;
+  }
+  key.dims[2] = s_glo ? (uint64_t)GLO : 1;
+  key.dims[3] = s_ghi ? (uint64_t)GHI : 1;
+  key.dims[4] = (s_ko && KO > 1) ? (uint64_t)KO : 1;
+  // strides of size-1 dims are never used for addressing; give them a legal (multiple of 16 B) value
+  key.strides[1] = key.dims[2] > 1 ? (uint64_t)s_glo * es : 16;
+  key.strides[2] = key.dims[3] > 1 ? (uint64_t)s_ghi * es : 16;
+  key.strides[3] = key.dims[4] > 1 ? (uint64_t)s_ko * es : 16;
+  if (key.dims[1] == 1 && (key.strides[0] % 16) != 0) key.strides[0] = 16;
+  for (int i = 0; i < 4; ++i) {
+    if (key.strides[i] % 16 != 0 || key.strides[i] == 0) {
+      if (strict) set_error("obst_gemm(tc): operand stride %llu B not a multiple of 16", (unsigned long long)key.strides[i]);
+      return OBST_ENOTSUP;
+    }
+  }
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) {
+    if (strict) set_error("obst_gemm(tc): operand pointer not 16-byte aligned");
+    return OBST_ENOTSUP;
+  }
+  std::string skey(reinterpret_cast<const char*>(&key), sizeof(key));
+  {
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    auto it = g_map_cache.find(skey);
+    if (it != g_map_cache.end()) {
+      *out = it->second;
+      return OBST_OK;
+    }
+  }
+  PFN_tmapEncodeTiled enc = get_encode_fn();
+  if (!enc) {
+    set_error("obst_gemm(tc): cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return OBST_ECUDA;
+  }
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t box[5] = {key.box[0], key.box[1], 1, 1, 1}, estr[5] = {1, 1, 1, 1, 1};
+  for (int i = 0; i < 5; ++i) gdim[i] = key.dims[i];
+  for (int i = 0; i < 4; ++i) gstr[i] = key.strides[i];
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("obst_gemm(tc): cuTensorMapEncodeTiled failed (%d) dims=[%llu,%llu,%llu,%llu,%llu] strides=[%llu,%llu,%llu,%llu]",
+              (int)r, (unsigned long long)gdim[0], (unsigned long long)gdim[1], (unsigned long long)gdim[2],
+              (unsigned long long)gdim[3], (unsigned long long)gdim[4], (unsigned long long)gstr[0],
+              (unsigned long long)gstr[1], (unsigned long long)gstr[2], (unsigned long long)gstr[3]);
+    return OBST_ECUDA;
+  }
+  {
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    if (g_map_cache.size() > 65536) g_map_cache.clear();
+    g_map_cache.emplace(skey, m);
+  }
+  *out = m;
+  return OBST_OK;
+}
+
+int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
+#define TC_NOTSUP(...)                  \
+  do {                                  \
+    if (strict) set_error(__VA_ARGS__); \
+    return OBST_ENOTSUP;                \
+  } while (0)
+  if (g.dtype_in != OBST_BF16) TC_NOTSUP("obst_gemm(tc): inputs must be bf16");
+  const bool a_mn = g.a_mn == 1 && g.a_k != 1;
+  const bool b_mn = g.b_mn == 1 && g.b_k != 1;
+  if (!a_mn && g.a_k != 1) TC_NOTSUP("obst_gemm(tc): operand A has no unit stride");
+  if (!b_mn && g.b_k != 1) TC_NOTSUP("obst_gemm(tc): operand B has no unit stride");
+  if ((g.tri == 1 || g.tri == 2) && g.KO != 1) TC_NOTSUP("obst_gemm(tc): triangular modes need KO == 1");
+  const bool out_f32 = g.dtype_out == OBST_F32;
+  const int oal = out_f32 ? 4 : 8;
+  if (g.N % 8 != 0 || g.d_ld % oal != 0 || g.d_glo % oal != 0 || g.d_ghi % oal != 0 ||
+      (reinterpret_cast<uintptr_t>(g.D) & 15) != 0 || (g.R && (reinterpret_cast<uintptr_t>(g.R) & 15) != 0))
+    TC_NOTSUP("obst_gemm(tc): output not 16-byte addressable (N=%d ld=%lld)", g.N, (long long)g.d_ld);
+  if (g.accumulate && !out_f32) TC_NOTSUP("obst_gemm(tc): accumulate needs fp32 output");
+  if (g.epi >= 2 && !g.R) TC_NOTSUP("obst_gemm(tc): epilogue %d needs R", g.epi);
+#undef TC_NOTSUP
+
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.D = g.D;
+  p.R = g.R;
+  p.d_ld = g.d_ld;
+  p.d_glo = g.d_glo;
+  p.d_ghi = g.d_ghi;
+  p.M = g.M;
+  p.N = g.N;
+  p.nkb_inner = (g.KI + BK - 1) / BK;
+  p.nkb = p.nkb_inner * g.KO;
+  p.GLO = g.GLO;
+  p.G = g.GLO * g.GHI;
+  p.BN = g.N > 128 ? 256 : (g.N > 64 ? 128 : 64);
+  p.tiles_m = (g.M + BM - 1) / BM;
+  p.tiles_n = (g.N + p.BN - 1) / p.BN;
+  p.tri = g.tri;
+  p.epi = g.epi;
+  p.accumulate = g.accumulate;
+  p.out_f32 = out_f32 ? 1 : 0;
+  p.a_mn = a_mn;
+  p.b_mn = b_mn;
+  p.a_uglo = g.a_glo != 0;
+  p.a_ughi = g.a_ghi != 0;
+  p.a_uko = (g.a_ko != 0 && g.KO > 1);
+  p.b_uglo = g.b_glo != 0;
+  p.b_ughi = g.b_ghi != 0;
+  p.b_uko = (g.b_ko != 0 && g.KO > 1);
+  const int64_t base_tiles = (int64_t)p.tiles_m * p.tiles_n * p.G;
+  int splits = 1;
+  if (g.accumulate) {
+    splits = g.splits;
+    if (splits <= 0) {
+      // enough work items to fill the machine ~2x, but keep >= 8 k-blocks per split
+      const int sms = num_sms();
+      splits = (int)((2 * sms + base_tiles - 1) / base_tiles);
+      const int max_by_k = p.nkb / 8 > 0 ? p.nkb / 8 : 1;
+      if (splits > max_by_k) splits = max_by_k;
+      if (splits < 1) splits = 1;
+    }
+    if (splits > p.nkb) splits = p.nkb;
+  }
+  p.splits = splits;
+  const int64_t total = base_tiles * splits;
+  OBST_REQUIRE(total < (1ll << 31), "obst_gemm(tc): too many tiles");
+  p.total_tiles = (int)total;
+
+  CUtensorMap tmA, tmB;
+  int rc = make_operand_map(g.A, g.a_mn, g.a_k, g.a_ko, g.a_glo, g.a_ghi, g.M, g.KI, g.KO, g.GLO, g.GHI, a_mn, BM, &tmA,
+                            strict);
+  if (rc != OBST_OK) return rc;
+  rc = make_operand_map(g.B, g.b_mn, g.b_k, g.b_ko, g.b_glo, g.b_ghi, g.N, g.KI, g.KO, g.GLO, g.GHI, b_mn, p.BN, &tmB,
+                        strict);
+  if (rc != OBST_OK) return rc;
+
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) {
+      set_error("obst_gemm(tc): cannot opt in to %d B of shared memory: %s", SMEM_BYTES, cudaGetErrorString(e));
+      return OBST_ECUDA;
+    }
+    attr_set = true;
+  }
+  int grid = num_sms();
+  if (grid > p.total_tiles) grid = p.total_tiles;
+  gemm_tc_kernel<<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmA, tmB, p);
+  count_launch();
+  return check_launch("obst_gemm(tc)");
+}
+
+}  // namespace obst
+
+using namespace obst;
+
+extern "C" int obst_gemm(const obst_gemm_desc* d, int backend, void* stream) {
+  OBST_REQUIRE(d != nullptr, "obst_gemm: null descriptor");
+  OBST_REQUIRE(d->M > 0 && d->N > 0 && d->KI > 0 && d->KO > 0 && d->GLO > 0 && d->GHI > 0,
+               "obst_gemm: bad sizes M=%d N=%d KI=%d KO=%d GLO=%d GHI=%d", d->M, d->N, d->KI, d->KO, d->GLO, d->GHI);
+  OBST_REQUIRE(d->A.ptr && d->B.ptr && d->D, "obst_gemm: null operand");
+  OBST_REQUIRE(d->tri >= 0 && d->tri <= 3 && d->epi >= 0 && d->epi <= 4, "obst_gemm: bad tri/epi %d/%d", d->tri, d->epi);
+  OBST_REQUIRE(!(d->epi >= 2 && d->R == nullptr), "obst_gemm: epilogue %d needs R", d->epi);
+  OBST_REQUIRE(!(d->accumulate && d->dtype_out != OBST_F32), "obst_gemm: accumulate needs fp32 output");
+  OBST_REQUIRE(!(d->accumulate && d->epi >= 2), "obst_gemm: accumulate cannot be combined with an R epilogue");
+  OBST_REQUIRE(!((d->tri == 1 || d->tri == 2) && d->KO != 1), "obst_gemm: tri 1/2 need KO == 1");
+  OBST_REQUIRE(!(d->tri == 3 && !d->accumulate), "obst_gemm: tri 3 needs accumulate");
+  GemmParams p;
+  p.A = d->A.ptr; p.B = d->B.ptr; p.D = d->D; p.R = d->R;
+  p.a_mn = d->A.s_mn; p.a_k = d->A.s_k; p.a_ko = d->A.s_ko; p.a_glo = d->A.s_glo; p.a_ghi = d->A.s_ghi;
+  p.b_mn = d->B.s_mn; p.b_k = d->B.s_k; p.b_ko = d->B.s_ko; p.b_glo = d->B.s_glo; p.b_ghi = d->B.s_ghi;
+  p.d_ld = d->d_ld; p.d_glo = d->d_glo; p.d_ghi = d->d_ghi;
+  p.M = d->M; p.N = d->N; p.KI = d->KI; p.KO = d->KO; p.GLO = d->GLO; p.GHI = d->GHI;
+  p.dtype_in = d->dtype_in; p.dtype_out = d->dtype_out;
+  p.tri = d->tri; p.epi = d->epi; p.accumulate = d->accumulate; p.splits = d->splits;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (backend == 1) return gemm_simt_launch(p, st);
+  if (backend == 2) return gemm_tc_launch(p, st, true);
+  OBST_REQUIRE(backend == 0, "obst_gemm: bad backend %d", backend);
+  if (p.dtype_in == OBST_BF16) {
+    const int rc = gemm_tc_launch(p, st, false);
+    if (rc != OBST_ENOTSUP) return rc;
+  }
+  return gemm_simt_launch(p, st);
+}

@@ -1,0 +1,345 @@
+// Fused multi-tensor optimizer update for
+//   adaptive_clip:<c> - sm3 - momentum:<beta>:1:<nesterov> - learning_rate  (+ weight decay, assign_sub)
+// src/optimizer/__init__.py:31-66, src/optimizer/optimizers.py:13-14,60-84,114-128.
+//
+// HBM-bound: one pass computes the two L2 norms per tensor, one pass does everything else.  A tensor
+// is viewed as [rows, cols] (cols = last dim).  A warp owns whole rows, lanes own fixed columns, so
+//   - the SM3 "max over the other dims" of the last dim lives in registers across rows,
+//   - the max for every other dim is one warp reduction per row + one atomicMax,
+// and the new accumulators are staged in fp32 (acc_new) because an SM3 accumulator may DEcrease.
+#include "obst_common.cuh"
+
+namespace obst {
+
+__device__ __forceinline__ void atomic_max_nonneg(float* addr, float v) {
+  // v >= 0 and *addr >= 0: IEEE order == signed-int order
+  atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
+}
+
+template <typename TS>
+__device__ __forceinline__ float ld_state(const void* p, int64_t i) {
+  return to_f32(reinterpret_cast<const TS*>(p)[i]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass 1: per-tensor sum g^2 and sum cast_AT(p)^2
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* __restrict__ table,
+                                                         const int32_t* __restrict__ item_tensor,
+                                                         const int32_t* __restrict__ item_row0,
+                                                         const int32_t* __restrict__ item_rows, int act_bf16,
+                                                         int grad_bf16, double* __restrict__ norms) {
+  __shared__ double s_part[2][8];
+  const int item = blockIdx.x;
+  const int ti = item_tensor[item];
+  const obst_opt_tensor T = table[ti];
+  const int64_t cols = T.dims[T.ndim - 1];
+  const int64_t e0 = (int64_t)item_row0[item] * cols;
+  const int64_t n = (int64_t)item_rows[item] * cols;
+  const float* __restrict__ g = T.g + e0;
+  const float* __restrict__ p = T.p + e0;
+  float sg = 0.f, sw = 0.f;
+  const bool vec_ok = ((e0 & 3) == 0);
+  const int64_t nv = vec_ok ? n / 4 : 0;
+  for (int64_t i = threadIdx.x; i < nv; i += blockDim.x) {
+    const float4 gv = reinterpret_cast<const float4*>(g)[i];
+    const float4 pv = reinterpret_cast<const float4*>(p)[i];
+    float ga[4] = {gv.x, gv.y, gv.z, gv.w}, pa[4] = {pv.x, pv.y, pv.z, pv.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float gg = grad_bf16 ? round_to<bf16>(ga[j]) : ga[j];
+      const float ww = act_bf16 ? round_to<bf16>(pa[j]) : pa[j];
+      sg += gg * gg;
+      sw += ww * ww;
+    }
+  }
+  for (int64_t i = nv * 4 + threadIdx.x; i < n; i += blockDim.x) {
+    const float gg = grad_bf16 ? round_to<bf16>(g[i]) : g[i];
+    const float ww = act_bf16 ? round_to<bf16>(p[i]) : p[i];
+    sg += gg * gg;
+    sw += ww * ww;
+  }
+  double dg = warp_sum_d((double)sg), dw = warp_sum_d((double)sw);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+    s_part[0][warp] = dg;
+    s_part[1][warp] = dw;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0.0, b = 0.0;
+    for (int w = 0; w < 8; ++w) {
+      a += s_part[0][w];
+      b += s_part[1][w];
+    }
+    atomicAdd(&norms[2 * ti], a);
+    atomicAdd(&norms[2 * ti + 1], b);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass 2: the update
+// ------------------------------------------------------------------------------------------------
+struct OptHyper {
+  float clip, beta, lr, weight_decay;
+  int nesterov, act_bf16, grad_bf16;
+};
+
+// NI > 0: lanes keep their column maxima in registers (cols <= 32*VEC*NI).  NI == 0: any cols, slower.
+template <typename TS, int VEC, int NI>
+__global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* __restrict__ table,
+                                                          const int32_t* __restrict__ item_tensor,
+                                                          const int32_t* __restrict__ item_row0,
+                                                          const int32_t* __restrict__ item_rows,
+                                                          const double* __restrict__ norms, const OptHyper hp) {
+  extern __shared__ float s_col[];  // [cols] block-level column maxima
+  const int item = blockIdx.x;
+  const int ti = item_tensor[item];
+  const obst_opt_tensor T = table[ti];
+  const int nd = T.ndim;
+  const int cols = T.dims[nd - 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < cols; i += blockDim.x) s_col[i] = 0.f;
+  __syncthreads();
+
+  float scale = 1.f;
+  if (hp.clip > 0.f) {
+    const float sg = (float)norms[2 * ti], sw = (float)norms[2 * ti + 1];
+    const float gn = fminf(rsqrtf(sg), 1e6f);  // rsqrt(0) = inf -> 1e6
+    const float wn = fmaxf(sqrtf(sw), 1e-3f);
+    scale = fminf(wn * gn * hp.clip, 1.f);
+  }
+  const void* acc_last = T.acc[nd - 1];
+  constexpr int NIR = NI > 0 ? NI : 1;
+  float al[NIR * VEC], cm[NIR * VEC];
+  if (NI > 0) {
+#pragma unroll
+    for (int i = 0; i < NIR; ++i) {
+      const int c = (lane + 32 * i) * VEC;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        cm[i * VEC + j] = 0.f;
+        al[i * VEC + j] = (c + j < cols) ? ld_state<TS>(acc_last, c + j) : 0.f;
+      }
+    }
+  }
+  const int row_end = item_row0[item] + item_rows[item];
+  const int iters = NI > 0 ? NI : (cols + 32 * VEC - 1) / (32 * VEC);
+  for (int r = item_row0[item] + warp; r < row_end; r += 8) {
+    int idx[3] = {0, 0, 0};
+    float rowmin = INFINITY;
+    {
+      int rem = r;
+      for (int i = nd - 2; i >= 0; --i) {
+        idx[i] = rem % T.dims[i];
+        rem /= T.dims[i];
+        rowmin = fminf(rowmin, ld_state<TS>(T.acc[i], idx[i]));
+      }
+    }
+    const int64_t rbase = (int64_t)r * cols;
+    float rowmax = 0.f;
+#pragma unroll
+    for (int i = 0; i < (NI > 0 ? NI : 64); ++i) {
+      if (i >= iters) break;
+      const int c = (lane + 32 * i) * VEC;
+      if (c >= cols) continue;
+      float pv[VEC], gv[VEC], mv[VEC];
+      if (VEC == 4) {
+        const float4 p4 = *reinterpret_cast<const float4*>(T.p + rbase + c);
+        const float4 g4 = *reinterpret_cast<const float4*>(T.g + rbase + c);
+        pv[0] = p4.x; pv[1] = p4.y; pv[2] = p4.z; pv[3] = p4.w;
+        gv[0] = g4.x; gv[1] = g4.y; gv[2] = g4.z; gv[3] = g4.w;
+        if (sizeof(TS) == 2) {
+          const uint2 m2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(T.m) + rbase + c);
+          const float2 a = unpack_bf16x2(m2.x), b = unpack_bf16x2(m2.y);
+          mv[0] = a.x; mv[1] = a.y; mv[2] = b.x; mv[3] = b.y;
+        } else {
+          const float4 m4 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(T.m) + rbase + c);
+          mv[0] = m4.x; mv[1] = m4.y; mv[2] = m4.z; mv[3] = m4.w;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+          pv[j] = T.p[rbase + c + j];
+          gv[j] = T.g[rbase + c + j];
+          mv[j] = ld_state<TS>(T.m, rbase + c + j);
+        }
+      }
+      float pn[VEC], mn[VEC];
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        float g = hp.grad_bf16 ? round_to<bf16>(gv[j]) : gv[j];
+        g = g * scale;
+        const float a_last = NI > 0 ? al[i * VEC + j] : ld_state<TS>(acc_last, c + j);
+        const float nu = fminf(rowmin, a_last) + g * g;
+        if (NI > 0) cm[i * VEC + j] = fmaxf(cm[i * VEC + j], nu);
+        else atomic_max_nonneg(&s_col[c + j], nu);
+        rowmax = fmaxf(rowmax, nu);
+        float u = g * (1.0f / fmaxf(sqrtf(nu), 1e-5f));
+        const float m_new = hp.beta * mv[j] + u;
+        u = hp.nesterov ? (u + hp.beta * m_new) : m_new;
+        u = u * hp.lr;
+        if (T.decay && hp.weight_decay > 0.f) {
+          const float w = hp.act_bf16 ? round_to<bf16>(pv[j]) : pv[j];
+          u += w * hp.lr * hp.weight_decay;
+        }
+        pn[j] = pv[j] - u;
+        mn[j] = m_new;
+      }
+      // shadow value (what the next forward pass reads), causal mask folded in
+      float sh[VEC];
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        sh[j] = pn[j];
+        if (T.tril_s > 0) {
+          const int64_t e = rbase + c + j;
+          const int col = (int)(e % T.tril_s);
+          const int row = (int)((e / T.tril_s) % T.tril_s);
+          if (col > row) sh[j] = 0.f;
+        }
+      }
+      if (VEC == 4) {
+        *reinterpret_cast<float4*>(T.p + rbase + c) = make_float4(pn[0], pn[1], pn[2], pn[3]);
+        if (sizeof(TS) == 2) {
+          uint2 m2;
+          m2.x = pack_bf16x2(mn[0], mn[1]);
+          m2.y = pack_bf16x2(mn[2], mn[3]);
+          *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(T.m) + rbase + c) = m2;
+        } else {
+          *reinterpret_cast<float4*>(reinterpret_cast<float*>(T.m) + rbase + c) =
+              make_float4(mn[0], mn[1], mn[2], mn[3]);
+        }
+        if (T.shadow) {
+          if (hp.act_bf16) {
+            uint2 s2;
+            s2.x = pack_bf16x2(sh[0], sh[1]);
+            s2.y = pack_bf16x2(sh[2], sh[3]);
+            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(T.shadow) + rbase + c) = s2;
+          } else {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(T.shadow) + rbase + c) =
+                make_float4(sh[0], sh[1], sh[2], sh[3]);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+          T.p[rbase + c + j] = pn[j];
+          reinterpret_cast<TS*>(T.m)[rbase + c + j] = from_f32<TS>(mn[j]);
+          if (T.shadow) {
+            if (hp.act_bf16) reinterpret_cast<bf16*>(T.shadow)[rbase + c + j] = __float2bfloat16_rn(sh[j]);
+            else reinterpret_cast<float*>(T.shadow)[rbase + c + j] = sh[j];
+          }
+        }
+      }
+    }
+    rowmax = warp_max(rowmax);
+    if (lane == 0) {
+      for (int i = 0; i < nd - 1; ++i) atomic_max_nonneg(T.acc_new[i] + idx[i], rowmax);
+    }
+  }
+  if (NI > 0) {
+#pragma unroll
+    for (int i = 0; i < NIR; ++i) {
+      const int c = (lane + 32 * i) * VEC;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j)
+        if (c + j < cols && cm[i * VEC + j] > 0.f) atomic_max_nonneg(&s_col[c + j], cm[i * VEC + j]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < cols; i += blockDim.x) {
+    const float v = s_col[i];
+    if (v > 0.f) atomic_max_nonneg(T.acc_new[nd - 1] + i, v);
+  }
+}
+
+template <typename TS>
+__global__ void __launch_bounds__(256) opt_finalize_kernel(const obst_opt_tensor* __restrict__ table) {
+  const obst_opt_tensor T = table[blockIdx.x];
+  for (int i = 0; i < T.ndim; ++i) {
+    TS* acc = reinterpret_cast<TS*>(T.acc[i]);
+    float* an = T.acc_new[i];
+    for (int k = threadIdx.x; k < T.dims[i]; k += blockDim.x) {
+      acc[k] = from_f32<TS>(an[k]);
+      an[k] = 0.f;
+    }
+  }
+}
+
+}  // namespace obst
+
+using namespace obst;
+
+extern "C" {
+
+int obst_opt_norms(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
+                   const int32_t* item_row0, const int32_t* item_rows, int32_t nitems, int32_t dtype_act,
+                   int32_t grad_bf16, double* norms, void* stream) {
+  OBST_REQUIRE(table && norms && ntensors > 0, "obst_opt_norms: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(norms, 0, sizeof(double) * 2 * (size_t)ntensors, st);
+  if (e != cudaSuccess) {
+    set_error("obst_opt_norms: memset failed: %s", cudaGetErrorString(e));
+    return OBST_ECUDA;
+  }
+  if (nitems <= 0) return OBST_OK;
+  opt_norms_kernel<<<(unsigned)nitems, 256, 0, st>>>(table, item_tensor, item_row0, item_rows,
+                                                     dtype_act == OBST_BF16, grad_bf16, norms);
+  count_launch();
+  return check_launch("obst_opt_norms");
+}
+
+// All tensors in one launch share the (VEC, NI) instantiation: max_cols = largest last dim in the
+// table; vec4 != 0 promises every last dim is a multiple of 4 (so every row start is 16-byte aligned).
+int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
+                    const int32_t* item_row0, const int32_t* item_rows, int32_t nitems, int32_t max_cols,
+                    int32_t vec4, int32_t dtype_act, int32_t dtype_state, int32_t grad_bf16, const double* norms,
+                    float clip, float beta, int32_t nesterov, float lr, float weight_decay, void* stream) {
+  OBST_REQUIRE(table && ntensors > 0 && max_cols > 0, "obst_opt_update: bad arguments");
+  OBST_REQUIRE(clip <= 0.f || norms != nullptr, "obst_opt_update: clip > 0 needs norms");
+  OBST_REQUIRE(max_cols <= 12288, "obst_opt_update: last dim %d too large (max 12288)", max_cols);
+  if (nitems <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  OptHyper hp;
+  hp.clip = clip; hp.beta = beta; hp.lr = lr; hp.weight_decay = weight_decay;
+  hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
+  const size_t smem = (size_t)max_cols * sizeof(float);
+  const int vec = vec4 ? 4 : 1;
+  const int ni = (max_cols + 32 * vec - 1) / (32 * vec);
+#define OBST_OPT(TS, V, N) \
+  opt_update_kernel<TS, V, N><<<(unsigned)nitems, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, norms, hp)
+#define OBST_OPT_NI(TS, V)                 \
+  do {                                     \
+    if (ni <= 1) OBST_OPT(TS, V, 1);       \
+    else if (ni <= 2) OBST_OPT(TS, V, 2);  \
+    else if (ni <= 4) OBST_OPT(TS, V, 4);  \
+    else if (ni <= 8) OBST_OPT(TS, V, 8);  \
+    else if (ni <= 16) OBST_OPT(TS, V, 16); \
+    else OBST_OPT(TS, V, 0);               \
+  } while (0)
+  if (dtype_state == OBST_BF16) {
+    if (vec4) OBST_OPT_NI(bf16, 4);
+    else OBST_OPT_NI(bf16, 1);
+  } else if (dtype_state == OBST_F32) {
+    if (vec4) OBST_OPT_NI(float, 4);
+    else OBST_OPT_NI(float, 1);
+  } else {
+    OBST_REQUIRE(false, "obst_opt_update: bad state dtype %d", dtype_state);
+  }
+#undef OBST_OPT_NI
+#undef OBST_OPT
+  count_launch();
+  return check_launch("obst_opt_update");
+}
+
+int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dtype_state, void* stream) {
+  OBST_REQUIRE(table && ntensors > 0, "obst_opt_finalize: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype_state == OBST_BF16) opt_finalize_kernel<bf16><<<(unsigned)ntensors, 256, 0, st>>>(table);
+  else if (dtype_state == OBST_F32) opt_finalize_kernel<float><<<(unsigned)ntensors, 256, 0, st>>>(table);
+  else OBST_REQUIRE(false, "obst_opt_finalize: bad state dtype %d", dtype_state);
+  count_launch();
+  return check_launch("obst_opt_finalize");
+}
+
+}  // extern "C"

@@ -1,0 +1,214 @@
+"""ctypes binding of libobst_b200.so (the C-ABI declared in include/obst_b200.h).
+
+PyTorch is only the plumbing here: it owns device memory and the CUDA stream; every kernel on the
+hot path is one of the entry points below.  There is no CPU fallback: if the shared library is
+missing or a call fails, this module raises.
+"""
+import ctypes
+import os
+import typing
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libobst_b200.so")
+
+F32, BF16 = 0, 1
+
+c_void_p = ctypes.c_void_p
+c_int = ctypes.c_int
+c_i32 = ctypes.c_int32
+c_i64 = ctypes.c_int64
+c_float = ctypes.c_float
+
+
+class Operand(ctypes.Structure):
+    _fields_ = [("ptr", c_void_p), ("s_mn", c_i64), ("s_k", c_i64), ("s_ko", c_i64), ("s_glo", c_i64),
+                ("s_ghi", c_i64)]
+
+
+class GemmDesc(ctypes.Structure):
+    _fields_ = [("dtype_in", c_i32), ("dtype_out", c_i32), ("M", c_i32), ("N", c_i32), ("KI", c_i32), ("KO", c_i32),
+                ("GLO", c_i32), ("GHI", c_i32), ("A", Operand), ("B", Operand), ("D", c_void_p), ("R", c_void_p),
+                ("d_ld", c_i64), ("d_glo", c_i64), ("d_ghi", c_i64), ("tri", c_i32), ("epi", c_i32),
+                ("accumulate", c_i32), ("splits", c_i32)]
+
+
+class OptTensor(ctypes.Structure):
+    _fields_ = [("p", c_void_p), ("shadow", c_void_p), ("g", c_void_p), ("m", c_void_p), ("acc", c_void_p * 4),
+                ("acc_new", c_void_p * 4), ("numel", c_i64), ("dims", c_i32 * 4), ("ndim", c_i32), ("decay", c_i32),
+                ("tril_s", c_i32), ("pad_", c_i32)]
+
+
+# name -> (restype, argtypes); must list every symbol include/obst_b200.h declares (tests check this)
+SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] = {
+    "obst_version": (c_int, []),
+    "obst_last_error": (ctypes.c_char_p, []),
+    "obst_launch_count": (c_i64, []),
+    "obst_launch_count_reset": (None, []),
+    "obst_gemm": (c_int, [ctypes.POINTER(GemmDesc), c_int, c_void_p]),
+    "obst_gn_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_i32, c_void_p]),
+    "obst_gn_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64,
+                            c_i32, c_i32, c_i32, c_i32, c_i32, c_void_p]),
+    "obst_act_fwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_i64, c_void_p]),
+    "obst_act_bwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
+    "obst_axpby": (c_int, [c_int, c_void_p, c_void_p, c_float, c_void_p, c_i64, c_void_p]),
+    "obst_embed_gather": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
+    "obst_embed_scatter_add": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
+    "obst_xent_fwd_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_float, c_float,
+                                  c_void_p]),
+    "obst_cast_param": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_void_p]),
+    "obst_opt_norms": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_void_p,
+                               c_void_p]),
+    "obst_opt_update": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32, c_i32,
+                                c_i32, c_void_p, c_float, c_float, c_i32, c_float, c_float, c_void_p]),
+    "obst_opt_finalize": (c_int, [c_void_p, c_i32, c_i32, c_void_p]),
+}
+
+_lib = None
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def load() -> ctypes.CDLL:
+    """Load the shared library (once).  Raises if it has not been built: there is no fallback path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise NativeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          f"(or `make -C homebrewnlp-mtf_b200/csrc`) first; there is no CPU fallback")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str = ""):
+    if rc != 0:
+        msg = load().obst_last_error().decode("utf-8", "replace")
+        raise NativeError(f"{what} failed with code {rc}: {msg}")
+
+
+def dtype_code(dtype: torch.dtype) -> int:
+    if dtype == torch.float32:
+        return F32
+    if dtype == torch.bfloat16:
+        return BF16
+    raise NativeError(f"unsupported dtype {dtype}")
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: typing.Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise NativeError("obst kernels need CUDA tensors (no CPU fallback)")
+
+
+# ---- thin wrappers -----------------------------------------------------------------------------------------
+
+def launch_count() -> int:
+    return int(load().obst_launch_count())
+
+
+def launch_count_reset():
+    load().obst_launch_count_reset()
+
+
+def operand(t: torch.Tensor, s_mn: int, s_k: int, s_ko: int = 0, s_glo: int = 0, s_ghi: int = 0,
+            offset: int = 0) -> Operand:
+    return Operand(t.data_ptr() + offset * t.element_size(), s_mn, s_k, s_ko, s_glo, s_ghi)
+
+
+def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO: int = 1, GLO: int = 1, GHI: int = 1,
+         d_ld: int, d_glo: int = 0, d_ghi: int = 0, d_offset: int = 0, R: typing.Optional[torch.Tensor] = None,
+         r_offset: typing.Optional[int] = None, tri: int = 0, epi: int = 0, accumulate: bool = False, splits: int = 0,
+         dtype_in: torch.dtype = torch.bfloat16, backend: int = 0):
+    """D[g,m,n] = epi(sum_k A[g,m,k] B[g,n,k]) -- see include/obst_b200.h for the full semantics."""
+    _cuda(D, R)
+    desc = GemmDesc()
+    desc.dtype_in = dtype_code(dtype_in)
+    desc.dtype_out = dtype_code(D.dtype)
+    desc.M, desc.N, desc.KI, desc.KO, desc.GLO, desc.GHI = M, N, KI, KO, GLO, GHI
+    desc.A, desc.B = A, B
+    desc.D = D.data_ptr() + d_offset * D.element_size()
+    if R is not None:
+        ro = d_offset if r_offset is None else r_offset
+        desc.R = R.data_ptr() + ro * R.element_size()
+    else:
+        desc.R = None
+    desc.d_ld, desc.d_glo, desc.d_ghi = d_ld, d_glo, d_ghi
+    desc.tri, desc.epi, desc.accumulate, desc.splits = tri, epi, int(accumulate), splits
+    check(load().obst_gemm(ctypes.byref(desc), backend, stream_ptr()), "obst_gemm")
+
+
+def gn_fwd(x, gamma, beta, y, heads: int, width: int, act: int = 0):
+    _cuda(x, y)
+    rows = x.numel() // width
+    check(load().obst_gn_fwd(dtype_code(x.dtype), _p(x), _p(gamma), _p(beta), _p(y), rows, heads, width, act,
+                             stream_ptr()), "obst_gn_fwd")
+
+
+def gn_bwd(dy, x, gamma, beta, dx, dgamma, dbeta, heads: int, width: int, act: int = 0, relu_mask: bool = False,
+           dx_accumulate: bool = False):
+    _cuda(dy, x, dx)
+    rows = x.numel() // width
+    check(load().obst_gn_bwd(dtype_code(x.dtype), _p(dy), _p(x), _p(gamma), _p(beta), _p(dx), _p(dgamma), _p(dbeta),
+                             rows, heads, width, act, int(relu_mask), int(dx_accumulate), stream_ptr()),
+          "obst_gn_bwd")
+
+
+def act_fwd(kind: int, x, y):
+    _cuda(x, y)
+    check(load().obst_act_fwd(dtype_code(x.dtype), kind, _p(x), _p(y), x.numel(), stream_ptr()), "obst_act_fwd")
+
+
+def act_bwd(kind: int, x, dy, dx):
+    _cuda(x, dy, dx)
+    check(load().obst_act_bwd(dtype_code(x.dtype), kind, _p(x), _p(dy), _p(dx), x.numel(), stream_ptr()),
+          "obst_act_bwd")
+
+
+def axpby(a, b, sign: float, out):
+    _cuda(a, b, out)
+    check(load().obst_axpby(dtype_code(a.dtype), _p(a), _p(b), sign, _p(out), a.numel(), stream_ptr()), "obst_axpby")
+
+
+def embed_gather(idx, table, out):
+    _cuda(idx, table, out)
+    vocab, width = table.shape
+    check(load().obst_embed_gather(dtype_code(table.dtype), _p(idx), _p(table), _p(out), idx.numel(), vocab, width,
+                                   stream_ptr()), "obst_embed_gather")
+
+
+def embed_scatter_add(idx, dout, dtable):
+    _cuda(idx, dout, dtable)
+    vocab, width = dtable.shape
+    check(load().obst_embed_scatter_add(dtype_code(dout.dtype), _p(idx), _p(dout), _p(dtable), idx.numel(), vocab,
+                                        width, stream_ptr()), "obst_embed_scatter_add")
+
+
+def xent_fwd_bwd(logits, targets, dlogits, sums, inv_n: float, z_loss: float):
+    _cuda(logits, targets, dlogits, sums)
+    vocab = logits.shape[-1]
+    tokens = logits.numel() // vocab
+    check(load().obst_xent_fwd_bwd(dtype_code(logits.dtype), _p(logits), _p(targets), _p(dlogits), _p(sums), tokens,
+                                   vocab, inv_n, z_loss, stream_ptr()), "obst_xent_fwd_bwd")
+
+
+def cast_param(src, dst, tril_s: int = 0):
+    _cuda(src, dst)
+    check(load().obst_cast_param(dtype_code(dst.dtype), _p(src), _p(dst), src.numel(), tril_s, stream_ptr()),
+          "obst_cast_param")

@@ -1,0 +1,198 @@
+/*
+ * obst_b200.h -- C-ABI of the B200-native OBST mixer training-step hot path.
+ *
+ * The reference (HomebrewNLP/HomebrewNLP-MTF) has no FFI: its "operator API" is the Python
+ * registries LAYER_FUNCTIONS (src/model/frontend.py:58-75) and OPTIMIZERS
+ * (src/optimizer/optimizers.py:131-151); every FLOP is a TF/XLA kernel picked by Mesh-TensorFlow.
+ * This header is what a binding for that path would bind instead: one entry point per fused device
+ * op, each citing the reference lines whose arithmetic it replaces.
+ *
+ * Conventions (all entry points):
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless named host_*;
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued, never synchronised;
+ *   - nothing is allocated or freed (the caller owns every buffer), except a host-side cache of
+ *     TMA tensor maps inside obst_gemm (host memory, keyed by operand geometry);
+ *   - return 0 on success, a negative OBST_E* code otherwise; obst_last_error() gives the text;
+ *   - dtype codes: OBST_F32 = 0, OBST_BF16 = 1.  "AT" below = the activation dtype
+ *     (calculation_dtype, src/dataclass.py:253-255).
+ */
+#ifndef OBST_B200_H
+#define OBST_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OBST_F32 0
+#define OBST_BF16 1
+
+#define OBST_OK 0
+#define OBST_EINVAL (-1)   /* bad argument / unsupported shape */
+#define OBST_ECUDA (-2)    /* CUDA runtime or driver error at launch */
+#define OBST_ENOTSUP (-3)  /* requested backend cannot run this problem */
+
+/* ---- library plumbing (no reference counterpart) ------------------------------------------ */
+int obst_version(void);
+const char* obst_last_error(void);
+/* number of kernels this library has launched since load / since the last reset (bench.py's
+ * gpu_launches). */
+int64_t obst_launch_count(void);
+void obst_launch_count_reset(void);
+
+/* ---- GEMM family -------------------------------------------------------------------------------
+ * One descriptor covers every contraction on the path:
+ *   dense  W_in / W_mid (+ReLU)            src/model/basic.py:33-34,47-57; src/model/backend.py:108-110
+ *   grouped W_out (per head)               src/model/basic.py:122-126
+ *   causal token mixing (lower-triangular) src/model/spatial.py:19-23,73,81; src/utils_mtf.py:411-415
+ *   input linear / LM head                 src/model/__init__.py:82,144-145
+ *   all dgrad / wgrad einsums              mtf.einsum gradients driven by src/optimizer/__init__.py:151-174
+ *                                          and src/model/revnet.py:91-120
+ *
+ * Semantics, for g in [0, GLO*GHI) with g_lo = g % GLO, g_hi = g / GLO:
+ *   acc[m,n] = sum_{ko<KO} sum_{k<KI} A(g,m,ko,k) * B(g,n,ko,k)       (fp32 accumulate)
+ *   X(g,r,ko,k) = X.ptr[g_lo*s_glo + g_hi*s_ghi + r*s_mn + ko*s_ko + k*s_k]
+ *   tri: 0 none
+ *        1 promise: A(g,m,k) == 0 for k > m, the kernel may skip those products (KO must be 1)
+ *        2 promise: A(g,m,k) == 0 for k < m, likewise
+ *        3 only outputs with n <= m are accumulated (requires accumulate != 0)
+ *   epi: 0 D=acc | 1 D=relu(acc) | 2 D=R+acc | 3 D=R-acc | 4 D=acc*[R>0]
+ *   accumulate!=0: D (fp32 only) += value with atomics (split-K allowed; tri==3 masks the store)
+ *   D/R address: ptr[g_lo*d_glo + g_hi*d_ghi + m*d_ld + n]; R may alias D.
+ * backend: 0 auto (tcgen05 when dtype_in is bf16 and the geometry is TMA-legal, else SIMT),
+ *          1 SIMT fp32-FMA kernel (any strides, fp32 or bf16 inputs), 2 tcgen05/TMEM/TMA kernel.
+ */
+typedef struct obst_operand {
+  const void* ptr;
+  int64_t s_mn;  /* element stride along M (operand A) or N (operand B) */
+  int64_t s_k;   /* element stride along the inner reduction index k    */
+  int64_t s_ko;  /* element stride along the outer reduction index ko   */
+  int64_t s_glo; /* element stride along g_lo (0 = broadcast)           */
+  int64_t s_ghi; /* element stride along g_hi (0 = broadcast)           */
+} obst_operand;
+
+typedef struct obst_gemm_desc {
+  int32_t dtype_in;  /* OBST_F32 | OBST_BF16 (A and B)          */
+  int32_t dtype_out; /* OBST_F32 | OBST_BF16 (D and R)          */
+  int32_t M, N, KI, KO;
+  int32_t GLO, GHI;
+  obst_operand A, B;
+  void* D;
+  const void* R;
+  int64_t d_ld, d_glo, d_ghi;
+  int32_t tri;
+  int32_t epi;
+  int32_t accumulate;
+  int32_t splits; /* split-K factor for accumulate mode; 0 = choose */
+} obst_gemm_desc;
+
+int obst_gemm(const obst_gemm_desc* desc, int backend, void* stream);
+
+/* ---- group norm (per token, per head), src/model/normalization.py:22-34 ------------------------
+ * x, y: [rows, heads, width] contiguous AT; gamma/beta: [heads, width] AT (may be NULL = no
+ * scale / no shift).  y = (x-mean)*rsqrt(mean((x-mean)^2)+1e-5)*gamma + beta.
+ * act: 0 none | 1 OBST gelu applied to y (src/model/activation.py:158-161; fuses the
+ * "norm -> activation-gelu" layer pair of block_config[1], configs/32big_mixer.json:13-19). */
+int obst_gn_fwd(int dtype, const void* x, const void* gamma, const void* beta, void* y,
+                int64_t rows, int32_t heads, int32_t width, int32_t act, void* stream);
+
+/* Backward of the above (full LayerNorm gradient).  dy: grad of the output
+ * (after the activation when act=1); dx written (dx_accumulate=0) or added to (1);
+ * dgamma/dbeta: fp32 [heads,width], accumulated with atomics.
+ * relu_mask: 1 = x is the output of a ReLU (W_mid path, src/model/basic.py:50,55-56): the
+ * gradient is additionally multiplied by [x > 0] so the caller gets d(pre-ReLU). */
+int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, const void* beta,
+                void* dx, float* dgamma, float* dbeta, int64_t rows, int32_t heads, int32_t width,
+                int32_t act, int32_t relu_mask, int32_t dx_accumulate, void* stream);
+
+/* ---- activations, src/model/activation.py:158-169,201-211 ---------------------------------------
+ * kind: 0 relu | 1 OBST gelu 0.5x(1+tanh(0.044715x^3+sqrt(2/pi)x)). */
+int obst_act_fwd(int dtype, int32_t kind, const void* x, void* y, int64_t n, void* stream);
+int obst_act_bwd(int dtype, int32_t kind, const void* x, const void* dy, void* dx, int64_t n,
+                 void* stream);
+
+/* ---- residual stream arithmetic, src/model/revnet.py:23,89,120; src/model/__init__.py:129 ------
+ * out = a + sign*b (sign = +1 or -1), all AT, n elements; out may alias a or b. */
+int obst_axpby(int dtype, const void* a, const void* b, float sign, void* out, int64_t n,
+               void* stream);
+
+/* ---- embedding gather / scatter-add, src/model/embedding.py:39-125 ------------------------------
+ * gather: out[t,:] = table[idx[t],:]  (table AT [vocab,width]);
+ * scatter: dtable[idx[t],:] += dout[t,:]  (dtable fp32 [vocab,width], atomics). */
+int obst_embed_gather(int dtype, const int32_t* idx, const void* table, void* out, int64_t tokens,
+                      int32_t vocab, int32_t width, void* stream);
+int obst_embed_scatter_add(int dtype, const int32_t* idx, const void* dout, float* dtable,
+                           int64_t tokens, int32_t vocab, int32_t width, void* stream);
+
+/* ---- softmax cross-entropy + z-loss + accuracy, forward and backward in one pass ---------------
+ * src/mtf_wrapper.py:64-71, src/model/__init__.py:185-187.
+ * logits AT [tokens,vocab]; targets int32 [tokens]; inv_n = 1/(global target count).
+ * dlogits (AT, may alias logits) = (softmax-onehot)*inv_n + 2*z_loss*inv_n*logZ*softmax.
+ * sums (double[3], accumulated with atomics): {sum(logZ-logit[tgt]), sum(logZ^2), #argmax==tgt}. */
+int obst_xent_fwd_bwd(int dtype, const void* logits, const int32_t* targets, void* dlogits,
+                      double* sums, int64_t tokens, int32_t vocab, float inv_n, float z_loss,
+                      void* stream);
+
+/* ---- parameter shadow copies --------------------------------------------------------------------
+ * The graph reads every variable through a cast to the activation dtype
+ * (mtf.Variable.value).  dst(AT) = cast(src fp32); tril_s > 0 additionally
+ * zeroes entries with col > row of each trailing [tril_s, tril_s] matrix (the causal mask of
+ * src/model/spatial.py:19-23 folded into the weight the kernels see). */
+int obst_cast_param(int dtype_dst, const float* src, void* dst, int64_t n, int32_t tril_s,
+                    void* stream);
+
+/* ---- fused optimizer update ---------------------------------------------------------------------
+ * adaptive_clip:<clip> - sm3 - momentum:<beta>:1:<nesterov> - learning_rate, plus the
+ * weight-decay rule and assign_sub:  src/optimizer/__init__.py:31-66,
+ * src/optimizer/optimizers.py:13-14,60-84,114-128, src/optimizer/backend.py:23-25.
+ *
+ * One obst_opt_tensor per variable (table lives in DEVICE memory, built by the caller once):
+ *   p      fp32 master slice (updated in place)
+ *   shadow AT copy refreshed with the new value (may be NULL); tril_s as in obst_cast_param
+ *   g      fp32 gradient (post-allreduce); grad_bf16!=0 rounds it to bf16 first, which is the
+ *          dtype the reference hands to the optimizer when calculation_dtype is bfloat16
+ *   m      momentum state, state dtype (optimizer_slice_dtype)
+ *   acc[i] SM3 accumulator of dim i (state dtype), length dims[i]; ndim in 1..4
+ *   acc_new[i] fp32 staging for the new accumulator (scratch, length dims[i])
+ * Three launches: norms -> update (+ new-accumulator max) -> finalize accumulators.
+ */
+typedef struct obst_opt_tensor {
+  float* p;
+  void* shadow;
+  float* g;
+  void* m;
+  void* acc[4];
+  float* acc_new[4];
+  int64_t numel;
+  int32_t dims[4];
+  int32_t ndim;
+  int32_t decay;   /* 1 = "large tensor" per src/optimizer/__init__.py:49-61 */
+  int32_t tril_s;
+  int32_t pad_;
+} obst_opt_tensor;
+
+/* Work list (DEVICE arrays, built by the caller once): item i covers rows
+ * [item_row0[i], item_row0[i]+item_rows[i]) of tensor item_tensor[i] viewed as [numel/cols, cols]
+ * with cols = dims[ndim-1].
+ * norms: double[2*ntensors] scratch, zeroed by obst_opt_norms: {sum g^2, sum cast_AT(p)^2}. */
+int obst_opt_norms(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
+                   const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
+                   int32_t dtype_act, int32_t grad_bf16, double* norms, void* stream);
+/* reads norms, old accumulators and m; writes p, shadow, m and max-reduces the new SM3
+ * accumulators into acc_new (which must be zero on entry; obst_opt_finalize leaves it zero).
+ * max_cols = largest last dim over the table (<= 12288); vec4 != 0 promises that every last dim is
+ * a multiple of 4.  clip <= 0 skips adaptive_clip (norms may then be NULL). */
+int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
+                    const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
+                    int32_t max_cols, int32_t vec4, int32_t dtype_act, int32_t dtype_state, int32_t grad_bf16, const double* norms,
+                    float clip, float beta, int32_t nesterov, float lr, float weight_decay,
+                    void* stream);
+/* acc[i] = cast_state(acc_new[i]); acc_new[i] = 0. */
+int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dtype_state,
+                      void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OBST_B200_H */

@@ -1,0 +1,284 @@
+"""Kernel-level GPU tests: every C-ABI entry point against a plain torch fp32 statement of the same op.
+
+These are floating-point kernels, so the checker here is torch fp32 on the same device (the model-level
+parity tests against oracle/ are in test_parity_gpu.py).  Tolerances are written at each comparison:
+fp32 paths 1e-5 relative (north_star), bf16 paths 2e-2 relative to the tensor's scale.
+"""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def nat():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from obst import native
+    native.load()
+    return native
+
+
+def rel_err(a, b):
+    a = a.double()
+    b = b.double()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def max_rel(a, b):
+    a = a.double()
+    b = b.double()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-30))
+
+
+DEV = "cuda"
+
+
+def randn(*shape, dtype=torch.bfloat16, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(dtype).to(DEV)
+
+
+# ---------------------------------------------------------------------------------------------------
+# GEMM: both back ends, every operand layout the training step uses
+# ---------------------------------------------------------------------------------------------------
+BACKENDS = [1, 2]
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("M,N,K", [(256, 512, 512), (200, 64, 96), (128, 256, 32), (384, 8192, 512)])
+def test_gemm_kmajor_kmajor(nat, backend, M, N, K):
+    a = randn(M, K, seed=1)
+    b = randn(N, K, seed=2)
+    d = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    nat.gemm(nat.operand(a, K, 1), nat.operand(b, K, 1), d, M, N, K, d_ld=N, backend=backend)
+    ref = a.float() @ b.float().t()
+    assert max_rel(d, ref) < 1e-2  # bf16 output rounding (2^-8) dominates
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("epi", [0, 1, 2, 3, 4])
+def test_gemm_b_mnmajor_epilogues(nat, backend, epi):
+    M, N, K = 256, 512, 256
+    a = randn(M, K, seed=3)
+    b = randn(K, N, seed=4)  # [K, N]: N contiguous = MN-major B (a weight read in place by the forward pass)
+    r = randn(M, N, seed=5, scale=4.0)
+    d = r.clone()
+    nat.gemm(nat.operand(a, K, 1), nat.operand(b, 1, N), d, M, N, K, d_ld=N, R=d if epi >= 2 else None, epi=epi,
+             backend=backend)
+    acc = a.float() @ b.float()
+    ref = {0: acc, 1: acc.relu(), 2: r.float() + acc, 3: r.float() - acc, 4: acc * (r.float() > 0)}[epi]
+    assert max_rel(d, ref) < 1e-2
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("M,N,K,splits", [(512, 512, 4096, 0), (64, 4096, 2048, 3), (4096, 512, 1024, 1)])
+def test_gemm_wgrad_mnmajor_accumulate(nat, backend, M, N, K, splits):
+    a = randn(K, M, seed=6)  # activations [T, f]: reduction index is the row
+    b = randn(K, N, seed=7)
+    d0 = randn(M, N, dtype=torch.float32, seed=8)
+    d = d0.clone()
+    nat.gemm(nat.operand(a, 1, M), nat.operand(b, 1, N), d, M, N, K, d_ld=N, accumulate=True, splits=splits,
+             backend=backend)
+    ref = d0 + a.float().t() @ b.float()
+    assert max_rel(d, ref) < 1e-4  # fp32 accumulate of exact bf16 products; only summation order differs
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_gemm_grouped_heads(nat, backend):
+    T, H, J, K = 512, 8, 256, 128
+    n = randn(T, H, J, seed=9)
+    w = randn(H, J, K, seed=10, scale=0.1)
+    x1 = randn(T, H, K, seed=11)
+    y = x1.clone()
+    # y[t,h,:] = x1[t,h,:] + n[t,h,:] @ w[h]   (W_out, residual add fused, in place)
+    nat.gemm(nat.operand(n, H * J, 1, s_glo=J), nat.operand(w, 1, K, s_glo=J * K), y, T, K, J, GLO=H, d_ld=H * K,
+             d_glo=K, R=y, epi=2, backend=backend)
+    ref = x1.float() + torch.einsum("thj,hjk->thk", n.float(), w.float())
+    assert max_rel(y, ref) < 1e-2
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+@pytest.mark.parametrize("S,K", [(256, 64), (512, 128)])
+def test_gemm_token_mix_forward_and_dx(nat, backend, S, K):
+    Bn, H = 3, 4
+    F = H * K
+    mix = torch.tril(randn(H, S, S, seed=12, scale=0.05).float()).to(torch.bfloat16)
+    x = randn(Bn, S, H, K, seed=13)
+    out = torch.empty_like(x)
+    # out[b,s,h,k] = sum_{t<=s} mix[h,s,t] x[b,t,h,k]
+    nat.gemm(nat.operand(mix, S, 1, s_glo=S * S), nat.operand(x, 1, F, s_glo=K, s_ghi=S * F), out, S, K, S, GLO=H,
+             GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, tri=1, backend=backend)
+    ref = torch.einsum("hst,bthk->bshk", mix.float(), x.float())
+    assert max_rel(out, ref) < 1e-2
+    # dx[b,t,h,k] = sum_{s>=t} mix[h,s,t] dout[b,s,h,k]   (A = mix^T, read MN-major)
+    dx = torch.empty_like(x)
+    nat.gemm(nat.operand(mix, 1, S, s_glo=S * S), nat.operand(x, 1, F, s_glo=K, s_ghi=S * F), dx, S, K, S, GLO=H,
+             GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, tri=2, backend=backend)
+    ref = torch.einsum("hst,bshk->bthk", mix.float(), x.float())
+    assert max_rel(dx, ref) < 1e-2
+
+
+@pytest.mark.parametrize("backend", BACKENDS)
+def test_gemm_token_mix_weight_grad(nat, backend):
+    Bn, H, S, K = 5, 4, 256, 64
+    F = H * K
+    do = randn(Bn, S, H, K, seed=14)
+    x = randn(Bn, S, H, K, seed=15)
+    dm = torch.zeros(H, S, S, dtype=torch.float32, device=DEV)
+    # dM[h,s,t] = [t<=s] sum_{b,k} do[b,s,h,k] x[b,t,h,k]  (outer reduction index = b)
+    nat.gemm(nat.operand(do, F, 1, s_ko=S * F, s_glo=K), nat.operand(x, F, 1, s_ko=S * F, s_glo=K), dm, S, S, K,
+             KO=Bn, GLO=H, d_ld=S, d_glo=S * S, tri=3, accumulate=True, backend=backend)
+    ref = torch.tril(torch.einsum("bshk,bthk->hst", do.float(), x.float()))
+    assert max_rel(dm, ref) < 1e-4
+    assert float(torch.triu(dm, diagonal=1).abs().max()) == 0.0  # masked entries never receive gradient
+
+
+def test_gemm_fp32_simt(nat):
+    M, N, K = 96, 72, 50
+    a = randn(M, K, dtype=torch.float32, seed=16)
+    b = randn(K, N, dtype=torch.float32, seed=17)
+    d = torch.empty(M, N, dtype=torch.float32, device=DEV)
+    nat.gemm(nat.operand(a, K, 1), nat.operand(b, 1, N), d, M, N, K, d_ld=N, dtype_in=torch.float32)
+    ref = (a.double() @ b.double())
+    assert max_rel(d, ref) < 1e-5
+
+
+def test_gemm_tc_matches_simt_bitwise_shape_sweep(nat):
+    """auto backend must pick tcgen05 for bf16 and agree with the SIMT kernel on identical inputs."""
+    for (M, N, K) in [(128, 128, 64), (1024, 1024, 1024), (640, 320, 448)]:
+        a = randn(M, K, seed=M)
+        b = randn(N, K, seed=N + 1)
+        d1 = torch.empty(M, N, dtype=torch.float32, device=DEV)
+        d2 = torch.empty(M, N, dtype=torch.float32, device=DEV)
+        nat.gemm(nat.operand(a, K, 1), nat.operand(b, K, 1), d1, M, N, K, d_ld=N, backend=1)
+        nat.gemm(nat.operand(a, K, 1), nat.operand(b, K, 1), d2, M, N, K, d_ld=N, backend=0)
+        assert max_rel(d2, d1) < 1e-5
+
+
+# ---------------------------------------------------------------------------------------------------
+# group norm / activations / residual / embedding / cross-entropy / casts
+# ---------------------------------------------------------------------------------------------------
+def gelu_ref(x):
+    return 0.5 * x * (1 + torch.tanh(0.044715 * x ** 3 + math.sqrt(2 / math.pi) * x))
+
+
+def gn_ref(x, gamma, beta, act):
+    xh = x - x.mean(-1, keepdim=True)
+    y = xh * torch.rsqrt((xh * xh).mean(-1, keepdim=True) + 1e-5) * gamma + beta
+    return gelu_ref(y) if act else y
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("width", [32, 64, 512, 1024])
+@pytest.mark.parametrize("act", [0, 1])
+def test_gn_fwd_bwd(nat, dtype, tol, width, act):
+    T, H = 300, 8
+    x = randn(T, H, width, dtype=dtype, seed=20, scale=2.0)
+    gamma = (1 + 0.02 * torch.randn(H, width)).to(dtype).to(DEV)
+    beta = (0.02 * torch.randn(H, width)).to(dtype).to(DEV)
+    dy = randn(T, H, width, dtype=dtype, seed=21)
+    y = torch.empty_like(x)
+    nat.gn_fwd(x, gamma, beta, y, H, width, act)
+    xr = x.double().requires_grad_(True)
+    gr = gamma.double().requires_grad_(True)
+    br = beta.double().requires_grad_(True)
+    yr = gn_ref(xr, gr, br, act)
+    assert rel_err(y, yr.detach()) < tol
+    yr.backward(dy.double())
+    dx0 = randn(T, H, width, dtype=dtype, seed=22)
+    dx = dx0.clone()
+    dg = torch.zeros(H, width, device=DEV)
+    db = torch.zeros(H, width, device=DEV)
+    nat.gn_bwd(dy, x, gamma, beta, dx, dg, db, H, width, act=act, dx_accumulate=True)
+    assert rel_err(dx, dx0.double() + xr.grad) < tol
+    assert rel_err(dg, gr.grad) < tol
+    assert rel_err(db, br.grad) < tol
+
+
+def test_gn_bwd_relu_mask(nat):
+    T, H, W = 64, 8, 64
+    x = randn(T, H, W, dtype=torch.float32, seed=23).relu()
+    dy = randn(T, H, W, dtype=torch.float32, seed=24)
+    dx = torch.empty_like(x)
+    nat.gn_bwd(dy, x, None, None, dx, None, None, H, W, relu_mask=True)
+    xr = x.double().requires_grad_(True)
+    gn_ref(xr, 1.0, 0.0, 0).backward(dy.double())
+    assert rel_err(dx, xr.grad * (x > 0)) < 1e-5
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("kind", [0, 1])
+def test_activations(nat, dtype, tol, kind):
+    n = 8 * 1000 + 3
+    x = randn(n, dtype=dtype, seed=25, scale=2.0)
+    dy = randn(n, dtype=dtype, seed=26)
+    y = torch.empty_like(x)
+    dx = torch.empty_like(x)
+    nat.act_fwd(kind, x, y)
+    nat.act_bwd(kind, x, dy, dx)
+    xr = x.double().requires_grad_(True)
+    yr = xr.relu() if kind == 0 else gelu_ref(xr)
+    yr.backward(dy.double())
+    assert rel_err(y, yr.detach()) < tol
+    assert rel_err(dx, xr.grad) < tol
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_axpby(nat, dtype):
+    a = randn(4099, dtype=dtype, seed=27)
+    b = randn(4099, dtype=dtype, seed=28)
+    out = torch.empty_like(a)
+    nat.axpby(a, b, -1.0, out)
+    assert torch.equal(out, (a.float() - b.float()).to(dtype))
+    nat.axpby(a, b, 1.0, a)
+    assert torch.equal(a, (out.float() + 2 * b.float()).to(dtype)) or rel_err(a, out.float() + 2 * b.float()) < 1e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_embedding_gather_scatter(nat, dtype):
+    V, W, T = 256, 64, 5000
+    table = randn(V, W, dtype=dtype, seed=29)
+    idx = torch.randint(0, V, (T,), dtype=torch.int32, device=DEV)
+    out = torch.empty(T, W, dtype=dtype, device=DEV)
+    nat.embed_gather(idx, table, out)
+    assert torch.equal(out, table[idx.long()])
+    dout = randn(T, W, dtype=dtype, seed=30)
+    dt = torch.zeros(V, W, device=DEV)
+    nat.embed_scatter_add(idx, dout, dt)
+    ref = torch.zeros(V, W, device=DEV, dtype=torch.float64).index_add_(0, idx.long(), dout.double())
+    assert rel_err(dt, ref) < 1e-5
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
+def test_xent(nat, dtype, tol):
+    T, V = 3000, 256
+    logits = randn(T, V, dtype=dtype, seed=31, scale=3.0)
+    tgt = torch.randint(0, V, (T,), dtype=torch.int32, device=DEV)
+    dl = torch.empty_like(logits)
+    sums = torch.zeros(3, dtype=torch.float64, device=DEV)
+    n_global = 2 * T  # the normaliser is the GLOBAL token count, not this shard's
+    nat.xent_fwd_bwd(logits, tgt, dl, sums, 1.0 / n_global, 1e-4)
+    lr = logits.double().requires_grad_(True)
+    logz = torch.logsumexp(lr, -1)
+    nll = (logz - lr.gather(1, tgt.long()[:, None])[:, 0]).sum()
+    z2 = (logz ** 2).sum()
+    loss = nll / n_global + 1e-4 * z2 / n_global
+    loss.backward()
+    assert abs(float(sums[0]) - float(nll)) / float(nll) < 1e-5
+    assert abs(float(sums[1]) - float(z2)) / float(z2) < 1e-5
+    assert float(sums[2]) == float((logits.float().argmax(-1) == tgt).sum())
+    assert rel_err(dl, lr.grad) < tol
+
+
+def test_cast_param_tril(nat):
+    H, S = 3, 64
+    src = randn(H, S, S, dtype=torch.float32, seed=32)
+    dst = torch.empty(H, S, S, dtype=torch.bfloat16, device=DEV)
+    nat.cast_param(src, dst, tril_s=S)
+    assert torch.equal(dst, torch.tril(src).to(torch.bfloat16))
+    dst2 = torch.empty(H, S, S, dtype=torch.float32, device=DEV)
+    nat.cast_param(src, dst2)
+    assert torch.equal(dst2, src)
