@@ -1,0 +1,69 @@
+"""Layer-string grammar and registry (src/model/frontend.py:21-75): a block is a list of strings
+"name-extra1-extra2..."; each is dispatched through LAYER_FUNCTIONS with a BlockArgs carrying the extras."""
+from ..dataclass import BlockArgs, BlockConfig, ModelParameter
+from ..utils_core import scoped
+from ..utils_mtf import Tensor
+from .activation import activate
+from .basic import (bottleneck_group_linear, dropout, feed_forward, feed_forward_product_key_memory, group_linear,
+                    product_key_memory, reduced_half_linear, rezero, sum_heads, transpose_sequence_features)
+from .normalization import norm
+from .spatial import attention, cummean, cumsum
+
+
+def _get_block_part(block_part_config: BlockConfig, params: ModelParameter, block_input: Tensor) -> Tensor:
+    out = block_input
+    layers = list(block_part_config.layer)
+    skip_next = False
+    for idx, layer in enumerate(layers, 1):
+        if skip_next:
+            skip_next = False
+            continue
+        name, *extras = layer.split('-')
+        args = BlockArgs(params, out, extras, idx == len(layers))
+        # a residual buffer handed down by the reversible driver may only be consumed by the LAST layer
+        pending = params.residual
+        if idx != len(layers):
+            params.residual = None
+        if name == 'norm' and idx < len(layers) and layers[idx].split('-') == ['activation', 'gelu']:
+            # peephole: "norm-..." directly followed by "activation-gelu" runs as one fused kernel
+            out = scoped(name + '_', norm, args, None, True)
+            skip_next = True
+        else:
+            out = scoped(name + '_', LAYER_FUNCTIONS[name], args)
+        if idx != len(layers):
+            params.residual = pending
+    if block_part_config.skip and block_part_config.memory_reduction_strategy in ("none", "checkpoint"):
+        raise NotImplementedError("skip connections of the 'none'/'checkpoint' strategies are not on the hot path")
+    return out
+
+
+def block_part_fn(params: ModelParameter, block_part_config: BlockConfig, block_input: Tensor,
+                  name_prefix: str = 'block') -> Tensor:
+    return scoped(f"{name_prefix}_", _get_block_part, block_part_config, params, block_input)
+
+
+def _unsupported(name):
+    def fn(args: BlockArgs) -> Tensor:
+        raise NotImplementedError(f"layer '{name}' is registered by the reference but is outside the mixer hot path")
+
+    return fn
+
+
+LAYER_FUNCTIONS = {'feed_forward': feed_forward,
+                   'attention': attention,
+                   'cummean': cummean,
+                   'cumsum': cumsum,
+                   'norm': norm,
+                   'rezero': rezero,
+                   'activation': activate,
+                   'convolution': _unsupported('convolution'),
+                   'dropout': dropout,
+                   'group_linear': group_linear,
+                   'split_path': _unsupported('split_path'),
+                   'feed_forward_product_key_memory': feed_forward_product_key_memory,
+                   'product_key_memory': product_key_memory,
+                   'reduced_half_linear': reduced_half_linear,
+                   'transpose_sequence_features': transpose_sequence_features,
+                   'bottleneck_group_linear': bottleneck_group_linear,
+                   'sum_heads': sum_heads
+                   }

@@ -1,0 +1,92 @@
+"""Reversible residual stack: the RevGradOp of src/model/revnet.py, run eagerly.
+
+forward  (src/model/revnet.py:20-24):  (x1, x2) -> (x2, x1 + f(x2)); nothing but the two streams is kept.
+backward (src/model/revnet.py:55-120): for each sub-block, last to first: x2 is known, f(x2) is RE-COMPUTED with
+the tape on, x1 = y1 - f(x2) is reconstructed (the subtraction rides on the last GEMM's epilogue), then f is
+back-propagated: dx1 = dy1, dx2 = dy2 + J^T dy1 (the add rides on the first norm's backward kernel).
+All four buffers (two streams, two gradients) are updated in place."""
+import typing
+
+import torch
+
+from .. import native
+from .. import utils_core
+from ..dataclass import BlockConfig, ModelParameter
+from ..utils_mtf import Tensor
+from .backend import TapeEntry, reset_shared_ordinals, run_tape
+from .frontend import block_part_fn
+
+
+def _apply(params: ModelParameter, config: BlockConfig, index: int, x2: Tensor, x1_buf: torch.Tensor, sign: float):
+    """x1_buf <- x1_buf + sign * f(x2), fused into f's last GEMM when that layer supports it."""
+    params.residual = (x1_buf, sign)
+    f = block_part_fn(params, config, x2, str(index))
+    if params.residual is not None:  # last layer could not fuse the residual
+        params.residual = None
+        native.axpby(x1_buf, f.data, sign, x1_buf)
+
+
+def reversible_body(params: ModelParameter, src: Tensor) -> Tensor:
+    """_body for memory_reduction_strategy == 'revnet' (src/model/__init__.py:101-106,124-129)."""
+    dims = src.dims
+    p = src.data.clone()  # x1
+    q = src.data          # x2 (src itself is not needed again: its gradient path is dp + dq)
+    outer_tape = params.tape
+    snapshots: typing.List[typing.Tuple[dict, int]] = []
+    params.tape = None  # forward keeps no activations
+    trace = getattr(params, "debug_trace", None)  # tests only: copies of the two streams after every sub-block
+    if trace is not None:
+        trace["src"] = src.data.clone()
+    for i in range(params.depth):
+        for config in params.block_config:
+            snapshots.append((utils_core.snapshot(), params.attention_idx))
+            _apply(params, config, i, Tensor(q, dims), p, 1.0)  # y1 = x1 + f(x2), in place on x1's buffer
+            p, q = q, p                                          # outputs (x2, y1)
+            if trace is not None:
+                trace[f"x1_{i}_{len(snapshots) - 1 - i * len(params.block_config)}"] = p.clone()
+                trace[f"x2_{i}_{len(snapshots) - 1 - i * len(params.block_config)}"] = q.clone()
+    out = torch.empty_like(p)
+    native.axpby(p, q, 1.0, out)  # out = x1 + x2  (src/model/__init__.py:129)
+    if trace is not None:
+        trace["out"] = out.clone()
+    params.tape = outer_tape
+
+    if outer_tape is not None:
+        n_cfg = len(params.block_config)
+
+        def bwd(dout: torch.Tensor, mask, acc):
+            nonlocal p, q
+            dp = dout
+            dq = dout.clone()
+            saved_names, saved_idx = utils_core.snapshot(), params.attention_idx
+            saved_scope = list(utils_core._SCOPE)
+            reducer = getattr(params, "grad_reducer", None)
+            utils_core._SCOPE[:] = body_scope
+            for j in range(len(snapshots) - 1, -1, -1):
+                i, c = divmod(j, n_cfg)
+                config = params.block_config[c]
+                names, att_idx = snapshots[j]
+                utils_core.restore(names)
+                params.attention_idx = att_idx
+                reset_shared_ordinals(params, str(i), f"{c}v")
+                # state after block j is (p, q) = (x2_in, x1_in + f(x2_in))
+                params.tape = []
+                _apply(params, config, i, Tensor(p, dims), q, -1.0)   # q <- x1_in = y1 - f(x2_in)
+                tape, params.tape = params.tape, None
+                run_tape(tape, dq, acc=dp)                              # dp <- dy2 + J^T dy1
+                del tape
+                p, q, dp, dq = q, p, dq, dp                             # (x1_in, x2_in), (dx1, dx2)
+                if trace is not None:
+                    trace[f"rx1_{i}_{c}"] = p.clone()
+                    trace[f"rx2_{i}_{c}"] = q.clone()
+                if c == 0 and reducer is not None:
+                    reducer.on_depth_done(i)  # both sub-blocks of depth i done: its gradients are final
+            utils_core.restore(saved_names)
+            params.attention_idx = saved_idx
+            utils_core._SCOPE[:] = saved_scope
+            native.axpby(dp, dq, 1.0, dp)  # d src = dx1 + dx2 (x1 = x2 = src at the input)
+            return dp
+
+        body_scope = list(utils_core._SCOPE)
+        outer_tape.append(TapeEntry(bwd))
+    return Tensor(out, dims)

@@ -1,0 +1,215 @@
+"""get_optimizer: reverse-mode sweep + per-variable update (src/optimizer/__init__.py of the reference).
+
+The reference differentiates the graph op by op (`:128-174`) and then emits ~25 small ops per variable
+(`update`, `:31-66`).  Here the sweep replays the tape recorded by build(); the update of ALL variables is three
+kernel launches (norms, update, finalize) over a device-side table of tensors.  Gradients are summed over
+micro-batches and data-parallel ranks in one flat fp32 buffer before the update, so every rank applies the
+identical step (adaptive-clip norms are taken after the allreduce)."""
+import ctypes
+import typing
+
+import torch
+
+from .. import native
+from ..dataclass import ModelParameter
+from ..model import backward as _backward
+from ..model.backend import Variable
+from ..utils_mtf import feature_dims_used
+from .backend import slot_name
+from .context import OptimizerCtx
+from .learning_rate import get_learning_rate
+from .optimizers import OPTIMIZERS, FusedPlan, lower_plan
+
+ITEM_ELEMS = 32768  # elements per work item of the fused kernels
+
+
+def is_large_tensor(params: ModelParameter, var: Variable) -> bool:
+    """The weight-decay predicate of src/optimizer/__init__.py:49-57, evaluated on the variable's scope name."""
+    name = var.name
+    features_used = feature_dims_used(params, var.dims)
+    large_tensor = features_used and len(var.dims) > len(params.feature_dims)
+    large_tensor |= not features_used and len(var.dims) >= 2
+    large_tensor &= var.size > 1
+    large_tensor &= "norm" not in name
+    large_tensor &= "rezero" not in name
+    large_tensor &= "embed" not in name
+    large_tensor &= "input" not in name or "lang_in" in name or "vid_in" in name
+    large_tensor &= "output" not in name or "lang_out" in name or "vid_out" in name
+    return bool(large_tensor)
+
+
+def _depth_of(var: Variable) -> int:
+    """Depth index from the scope name `.../body0v/<depth>_<cfg>v/...`; -1 for input/output variables."""
+    parts = var.name.split('/')
+    if "body0v" in parts:
+        blk = parts[parts.index("body0v") + 1]
+        return int(blk.split('_')[0])
+    return -1
+
+
+class FusedOptimizer:
+    """State + launch plumbing of the fused update.  Owns the flat gradient buffer (so DP reduction is one or a few
+    contiguous allreduces), the momentum / SM3 slots and the device-side tensor table."""
+
+    def __init__(self, params: ModelParameter, plan: FusedPlan):
+        self.params = params
+        self.plan = plan
+        dev = torch.device(params.device)
+        self.state_dtype = params.optimizer_dtype.slice_dtype
+        self.act_dtype = params.variable_dtype.activation_dtype
+        variables = [v for v in params.variable_cache.values() if v.trainable]
+        if not variables:
+            raise RuntimeError("no trainable variables: run build() once before get_optimizer()")
+        for v in variables:
+            if not 1 <= len(v.dims) <= 4:
+                raise NotImplementedError(f"sm3 on rank-{len(v.dims)} variable {v.name}: ranks 1..4 are fused "
+                                          f"(rank 0 falls back to adam in the reference, unused by the mixer)")
+        # flat layout: per-depth variables first (their gradients are final first during the last backward pass),
+        # shared mixing maps / input / output variables last
+        shared = {id(v) for v in variables if _depth_of(v) == 0 and "embed" in v.name}
+        order = sorted(range(len(variables)),
+                       key=lambda i: (1 if (_depth_of(variables[i]) < 0 or id(variables[i]) in shared) else 0,
+                                      -_depth_of(variables[i]) if _depth_of(variables[i]) >= 0 else 0, i))
+        self.variables = [variables[i] for i in order]
+        sizes = [v.size for v in self.variables]
+        pad = [(-s) % 64 for s in sizes]  # keep every tensor 256-byte aligned inside the flat buffers
+        total = sum(s + p for s, p in zip(sizes, pad))
+        self.flat_grad = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_momentum = torch.zeros(total, dtype=self.state_dtype, device=dev)
+        n_acc = sum(sum(d.size for d in v.dims) + 64 * len(v.dims) for v in self.variables)
+        self.flat_acc = torch.zeros(n_acc, dtype=self.state_dtype, device=dev)
+        self.flat_acc_new = torch.zeros(n_acc, dtype=torch.float32, device=dev)
+        self.norms = torch.zeros(2 * len(self.variables), dtype=torch.float64, device=dev)
+        self.slots: typing.Dict[str, torch.Tensor] = {}
+        self.offsets: typing.List[typing.Tuple[int, int]] = []
+        self.depth_ranges: typing.Dict[int, typing.List[int]] = {}
+
+        table = (native.OptTensor * len(self.variables))()
+        items_t, items_r0, items_rows = [], [], []
+        off = 0
+        aoff = 0
+        max_cols, vec4 = 1, True
+        for ti, (v, sz, pd) in enumerate(zip(self.variables, sizes, pad)):
+            old_grad = v.grad
+            v.grad = self.flat_grad[off:off + sz].view(v.data.shape)
+            if old_grad is not None:
+                v.grad.copy_(old_grad)
+            m = self.flat_momentum[off:off + sz].view(v.data.shape)
+            self.slots[slot_name(params, v.name, "momentum")] = m
+            self.offsets.append((off, sz))
+            d = _depth_of(v)
+            key = -1 if (d < 0 or id(v) in shared) else d
+            rng = self.depth_ranges.setdefault(key, [off, off + sz + pd])
+            rng[0] = min(rng[0], off)
+            rng[1] = max(rng[1], off + sz + pd)
+            t = table[ti]
+            t.p = v.data.data_ptr()
+            t.shadow = v.value.data_ptr() if v.value is not v.data else None
+            t.g = v.grad.data_ptr()
+            t.m = m.data_ptr()
+            dims = [dd.size for dd in v.dims]
+            for i, n in enumerate(dims):
+                a = self.flat_acc[aoff:aoff + n]
+                an = self.flat_acc_new[aoff:aoff + n]
+                self.slots[slot_name(params, v.name, f"dim{i}")] = a
+                t.acc[i] = a.data_ptr()
+                t.acc_new[i] = an.data_ptr()
+                t.dims[i] = n
+                aoff += n + ((-n) % 64)
+            t.numel = sz
+            t.ndim = len(dims)
+            t.decay = int(is_large_tensor(params, v))
+            t.tril_s = v.tril_s
+            cols = dims[-1]
+            rows = sz // cols
+            max_cols = max(max_cols, cols)
+            vec4 &= cols % 4 == 0
+            rpi = max(1, ITEM_ELEMS // cols)
+            for r0 in range(0, rows, rpi):
+                items_t.append(ti)
+                items_r0.append(r0)
+                items_rows.append(min(rpi, rows - r0))
+            off += sz + pd
+        self.max_cols, self.vec4 = max_cols, vec4
+        raw = bytes(table)
+        self.table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
+        self.n_items = len(items_t)
+        self.item_tensor = torch.tensor(items_t, dtype=torch.int32, device=dev)
+        self.item_row0 = torch.tensor(items_r0, dtype=torch.int32, device=dev)
+        self.item_rows = torch.tensor(items_rows, dtype=torch.int32, device=dev)
+        self.decay_names = [v.name for v in self.variables if is_large_tensor(params, v)]
+
+    @property
+    def n_params(self) -> int:
+        return sum(sz for _, sz in self.offsets)
+
+    def zero_grad(self):
+        self.flat_grad.zero_()
+
+    def step(self, lr: float):
+        lib = native.load()
+        st = native.stream_ptr()
+        p, plan = self.params, self.plan
+        nt = len(self.variables)
+        grad_bf16 = int(self.act_dtype == torch.bfloat16)
+        act, sdt = native.dtype_code(self.act_dtype), native.dtype_code(self.state_dtype)
+        tp, it, ir0, irs = (self.table.data_ptr(), self.item_tensor.data_ptr(), self.item_row0.data_ptr(),
+                            self.item_rows.data_ptr())
+        if plan.clip > 0:
+            native.check(lib.obst_opt_norms(tp, nt, it, ir0, irs, self.n_items, act, grad_bf16, self.norms.data_ptr(),
+                                            st), "obst_opt_norms")
+        native.check(lib.obst_opt_update(tp, nt, it, ir0, irs, self.n_items, self.max_cols, int(self.vec4), act, sdt,
+                                         grad_bf16, self.norms.data_ptr(), plan.clip, plan.beta, int(plan.nesterov),
+                                         float(lr), float(p.weight_decay), st), "obst_opt_update")
+        native.check(lib.obst_opt_finalize(tp, nt, sdt, st), "obst_opt_finalize")
+        # fp32 activations without a causal mask read the master slice directly: nothing to refresh
+
+
+def update(ctx: OptimizerCtx):
+    """src/optimizer/__init__.py:31-66 for ALL variables at once: walk the optimizer string, lower the plan, run."""
+    params = ctx.params
+    ctx.plan = []
+    for opt in params.optimizer.split('-'):
+        opt, *args = opt.split(':')
+        ctx.grad = OPTIMIZERS[opt](ctx, *args)
+    plan = lower_plan(ctx.plan)
+    opt_state: FusedOptimizer = params.optimizer_state
+    if opt_state.plan != plan:
+        raise RuntimeError("optimizer string changed after the optimizer state was created")
+    opt_state.step(ctx.learning_rate)
+    ctx.update_ops.extend(v.name for v in opt_state.variables)
+
+
+def _ensure_state(params: ModelParameter) -> FusedOptimizer:
+    state = getattr(params, "optimizer_state", None)
+    if state is None:
+        ctx = OptimizerCtx(params, [], 0.0, 0, True)
+        for opt in params.optimizer.split('-'):
+            opt, *args = opt.split(':')
+            OPTIMIZERS[opt](ctx, *args)
+        state = FusedOptimizer(params, lower_plan(ctx.plan))
+        params.optimizer_state = state
+    return state
+
+
+def get_optimizer(loss_list: typing.List[typing.Any], params: ModelParameter, manual_step: int, fn: str
+                  ) -> typing.Tuple[typing.List[str], float]:
+    """Differentiate the recorded step and, when fn == "update", apply the parameter update.
+    Same contract as the reference (src/optimizer/__init__.py:69-186): returns (update_ops, learning_rate);
+    any fn other than "update" only accumulates gradients (the reference's "add"/"accumulate" arm, used for all
+    but the last micro-batch)."""
+    state = _ensure_state(params)
+    update_ops: typing.List[str] = []
+    learning_rate_ctx = get_learning_rate(params, loss_list, update_ops)
+    learning_rate = float(learning_rate_ctx.learning_rate)
+    reducer = getattr(params, "grad_reducer", None)
+    if reducer is not None:
+        reducer.begin_backward(last=(fn == "update"))
+    _backward(params)
+    if fn != "update":
+        return update_ops, learning_rate
+    if reducer is not None:
+        reducer.finish()
+    ctx = OptimizerCtx(params, update_ops, learning_rate, int(params.global_step) + 1, True)
+    update(ctx)
+    return ctx.update_ops, learning_rate

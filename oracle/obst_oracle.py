@@ -1,0 +1,503 @@
+"""CPU oracle: a NumPy restatement of the OBST mixer training step.  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this
+module, and only as the checker / reported CPU baseline.  The product (homebrewnlp-mtf_b200/) never does.
+
+PARITY UNPINNED: the reference holds no golden vectors, known-answer tests or fixtures for this path
+(its tests assert statistics of initialisers only) and it cannot be executed here
+(tensorflow==2.7.0 + mesh-tensorflow are not installable: requirements.txt:2-3, Python 3.12, no network).
+What pins this file is (a) line-by-line citation of the reference below, (b) the reference-authored
+statistical invariants re-asserted in tests/test_oracle.py, (c) an independent torch-autograd cross-check
+of every hand-written backward formula, (d) the committed fixtures under tests/golden/ made by this file.
+
+Citations are paths under /root/reference.
+"""
+import json
+import math
+import typing
+
+import numpy as np
+
+GN_EPS = 1e-5  # src/model/normalization.py:28
+
+
+# ----------------------------------------------------------------------------------------------------------
+# configuration: the derived sizes of src/dataclass.py:184-342 for the language ("gpt") mode
+# ----------------------------------------------------------------------------------------------------------
+class Shapes:
+    """Sizes derived exactly as ModelParameter does (src/dataclass.py:221-234,283-285; src/model/__init__.py:76-78)."""
+
+    def __init__(self, config: typing.Dict[str, typing.Any]):
+        c = dict(config)
+        self.config = c
+        self.heads = int(c.get("heads", 8))
+        self.features_per_head = c.get("features_per_head")
+        features = c.get("features")
+        if features is None and self.features_per_head is None:
+            raise ValueError("Either features or features_per_head has to be specified")  # src/dataclass.py:221
+        if features is None:
+            features = self.features_per_head * self.heads
+        if self.features_per_head is None:
+            self.features_per_head = features // self.heads
+        self.features = int(features)
+        self.sequence_length = int(c.get("sequence_length", 32))
+        self.train_batch_size = int(c.get("train_batch_size", 1))
+        self.depth = int(c.get("depth", 16))
+        self.vocab_size = int(c.get("vocab_size", 256))
+        self.group_linear_factor = c.get("group_linear_factor", 2)
+        mm = c.get("intermediate_feed_forward_multiplier_multiplier")
+        m = c.get("intermediate_feed_forward_multiplier")
+        if mm is not None:  # src/dataclass.py:230-232
+            m = self.group_linear_factor * mm / self.heads
+        if m is None:
+            m = self.group_linear_factor / self.heads
+        self.intermediate = int(self.heads * self.features_per_head * m)  # src/dataclass.py:283-285
+        self.vocab_weight_factorization = c.get("vocab_weight_factorization", 0.125)
+        self.intermediate0 = int(self.intermediate * self.vocab_weight_factorization)  # src/model/__init__.py:78
+        self.group_features = int(self.features_per_head * self.group_linear_factor)  # src/utils_mtf.py:376-380
+        self.embedding_stddev = c.get("embedding_stddev", 0.04)
+        self.z_loss = c.get("z_loss", 1e-4)
+        self.learning_rate = c.get("learning_rate", 5e-5)
+        self.learning_rate_config = c.get("learning_rate_config", {})
+        self.weight_decay = c.get("weight_decay", 0.001)
+        self.optimizer = c.get("optimizer", "learning_rate")
+        self.calculation_dtype = c.get("calculation_dtype", "float32")
+        self.optimizer_slice_dtype = c.get("optimizer_slice_dtype", "float32")
+
+    # short names used in the math below
+    @property
+    def dims(self):
+        return (self.train_batch_size, self.sequence_length, self.heads, self.features_per_head, self.features,
+                self.intermediate, self.group_features, self.intermediate0, self.vocab_size, self.depth)
+
+
+def load_config(path: str) -> typing.Dict[str, typing.Any]:
+    with open(path) as f:
+        return json.load(f)
+
+
+TINY_CONFIG = {  # BASELINE.json configs[0]: "tiny mixer LM (2 layers, d_model=256, ctx=256, batch 8) fp32"
+    "embedding_stddev": 0.004, "calc_accuracy": True, "scale_by_depth": True,
+    "block_config": [
+        {"layer": ["norm-shift-scale-features-group",
+                   "bottleneck_group_linear-in:relu-mid:relu-mid:norm-mid:shift-mid:scale-mid:features"]},
+        {"layer": ["norm-shift-scale-features-group",
+                   "attention-biased_attention_map-absolute-input_as_value-shared",
+                   "norm-shift-scale-features-group", "activation-gelu",
+                   "attention-biased_attention_map-absolute-input_as_value-shared"]}],
+    "group_linear_factor": 2, "intermediate_feed_forward_multiplier_multiplier": 0.5, "depth": 2,
+    "use_initial_position_embedding": False, "sequence_length": 256, "features_per_head": 32, "heads": 8,
+    "train_batch_size": 8, "data_seed": 134567, "vocab_size": 256, "model_mode": "gpt", "use_language": True,
+    "learning_rate": 0.01, "opt_beta1": 0.9, "memory_reduction_strategy": "revnet", "opt_beta2": 0.99,
+    "optimizer": "adaptive_clip:0.003-sm3-momentum:0.9:1:1-learning_rate", "weight_decay": 0.0001,
+    "macro_batching": 1, "calculation_dtype": "float32", "storage_dtype": "float32",
+    "optimizer_slice_dtype": "float32", "slice_dtype": "float32",
+    "learning_rate_config": {"linear_warmup": {"final_step": 4096}},
+}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# initialisation (src/model/backend.py:18-40,97-105; src/model/embedding.py:175-178)
+# ----------------------------------------------------------------------------------------------------------
+def orthogonal_init(rng: np.random.Generator, sizes: typing.Sequence[int], fan_in: int) -> np.ndarray:
+    """OrthogonalInit.__call__ (src/model/backend.py:28-40): QR of a normal [max,min] matrix, sign-fixed,
+    transposed when fan_out > fan_in, reshaped to the variable's dims.  scale_by_depth is never applied on
+    this path (BlockArgs.__call__ drops is_last, src/dataclass.py:396)."""
+    total = int(np.prod(sizes))
+    fan_out = total // fan_in
+    transpose = fan_out > fan_in
+    shape = (fan_out, fan_in) if transpose else (fan_in, fan_out)
+    q, r = np.linalg.qr(rng.standard_normal(shape))
+    q = q * np.sign(np.diag(r))
+    if transpose:
+        q = q.T
+    return np.ascontiguousarray(q.reshape(sizes)).astype(np.float32)
+
+
+def param_names(sh: Shapes) -> typing.List[str]:
+    """Creation order of the trainable variables (depth-major, as the graph builds them)."""
+    names = ["embed", "w0"]
+    for i in range(sh.depth):
+        names += [f"g0_{i}", f"b0_{i}", f"win_{i}", f"wmid_{i}", f"gm_{i}", f"bm_{i}", f"wout_{i}",
+                  f"g1_{i}", f"b1_{i}"]
+        if i == 0:
+            names.append("mix_a")
+        names += [f"g2_{i}", f"b2_{i}"]
+        if i == 0:
+            names.append("mix_b")
+    names.append("wo")
+    return names
+
+
+def init_params(sh: Shapes, seed: int = 0) -> typing.Dict[str, np.ndarray]:
+    """Seeded draw following the reference's init rules.  (The reference seeds each OrthogonalInit with
+    Python's global `random`, src/model/backend.py:24, so parity runs IMPORT these weights on both sides.)"""
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    rng = np.random.default_rng(seed)
+    p: typing.Dict[str, np.ndarray] = {}
+
+    def normal(shape, mean, std):  # normal_var, src/model/backend.py:103-105
+        return (mean + std * rng.standard_normal(shape)).astype(np.float32)
+
+    p["embed"] = normal((V, I0), 0.0, sh.embedding_stddev)  # src/model/embedding.py:175-178,230
+    p["w0"] = orthogonal_init(rng, (1, I0, H, K), fan_in=I0)  # src/model/__init__.py:82
+    for i in range(L):
+        p[f"g0_{i}"] = normal((H, K), 1.0, 0.02)  # src/model/normalization.py:30-33
+        p[f"b0_{i}"] = normal((H, K), 0.0, 0.02)
+        p[f"win_{i}"] = orthogonal_init(rng, (H, K, I), fan_in=H * K)  # src/model/basic.py:33,124
+        p[f"wmid_{i}"] = orthogonal_init(rng, (I, H, K2), fan_in=I)
+        p[f"gm_{i}"] = normal((H, K2), 1.0, 0.02)
+        p[f"bm_{i}"] = normal((H, K2), 0.0, 0.02)
+        p[f"wout_{i}"] = orthogonal_init(rng, (H, K2, K), fan_in=H * K2)
+        p[f"g1_{i}"] = normal((H, K), 1.0, 0.02)
+        p[f"b1_{i}"] = normal((H, K), 0.0, 0.02)
+        if i == 0:  # "shared": one variable per call site, reused at every depth (src/model/backend.py:50-94)
+            p["mix_a"] = normal((H, S, S), 0.0, sh.embedding_stddev)  # src/model/spatial.py:19-23
+        p[f"g2_{i}"] = normal((H, K), 1.0, 0.02)
+        p[f"b2_{i}"] = normal((H, K), 0.0, 0.02)
+        if i == 0:
+            p["mix_b"] = normal((H, S, S), 0.0, sh.embedding_stddev)
+    # output_embedding = "absolute-orthogonal": orthogonal_var WITHOUT fan_in dims -> fan_in 1 -> QR of a
+    # column = one unit-norm vector (src/dataclass.py:41, src/model/backend.py:20-29)
+    p["wo"] = orthogonal_init(rng, (H, K, 1, V), fan_in=1)
+    assert list(p.keys()) == param_names(sh)
+    return p
+
+
+def is_large_tensor(name: str) -> bool:
+    """Weight-decay predicate of src/optimizer/__init__.py:49-57 evaluated on this model's variables:
+    only the three feed-forward weights pass (norm/embed/input/output scopes are excluded)."""
+    return name.startswith(("win_", "wmid_", "wout_"))
+
+
+def synthetic_tokens(sh: Shapes, seed: typing.Optional[int] = None, batch: typing.Optional[int] = None):
+    """x = w[:, :S], y = w[:, 1:S+1] (src/inputs.py:543-551, output_offset=1 src/dataclass.py:48)."""
+    seed = sh.config.get("data_seed", 456772) if seed is None else seed
+    b = sh.train_batch_size if batch is None else batch
+    rng = np.random.default_rng(seed)
+    w = rng.integers(0, sh.vocab_size, size=(b, sh.sequence_length + 1), dtype=np.int64).astype(np.int32)
+    return np.ascontiguousarray(w[:, :-1]), np.ascontiguousarray(w[:, 1:])
+
+
+# ----------------------------------------------------------------------------------------------------------
+# layer math, forward and explicit backward
+# ----------------------------------------------------------------------------------------------------------
+def gn_fwd(x, gamma, beta):
+    """norm(): src/model/normalization.py:22-34 with extras shift,scale,features,group -> per (token, head)."""
+    xh = x - x.mean(-1, keepdims=True)
+    r = 1.0 / np.sqrt((xh * xh).mean(-1, keepdims=True) + GN_EPS)
+    z = xh * r
+    return z * gamma + beta, (z, r)
+
+
+def gn_bwd(dy, cache, gamma):
+    z, r = cache
+    red = tuple(range(dy.ndim - 2))
+    dgamma = (dy * z).sum(red)
+    dbeta = dy.sum(red)
+    g = dy * gamma
+    dx = r * (g - g.mean(-1, keepdims=True) - z * (g * z).mean(-1, keepdims=True))
+    return dx, dgamma, dbeta
+
+
+_C0 = 0.044715
+_C1 = math.sqrt(2.0 / math.pi)
+
+
+def gelu_fwd(x):
+    """_gelu: src/model/activation.py:158-161 -- the cubic term is NOT scaled by sqrt(2/pi)."""
+    return 0.5 * x * (1.0 + np.tanh(_C0 * x * x * x + _C1 * x))
+
+
+def gelu_grad(x):
+    th = np.tanh(_C0 * x * x * x + _C1 * x)
+    return 0.5 * (1.0 + th) + 0.5 * x * (1.0 - th * th) * (3.0 * _C0 * x * x + _C1)
+
+
+def mix_fwd(m_tril, x):
+    """attention() with biased_attention_map + input_as_value: out[b,s,h,k] = sum_t M[h,s,t] tril[s,t] x[b,t,h,k]
+    (src/model/spatial.py:19-23,73,77,81; mask = greater_equal(range(seq), range(_seq)), src/utils_mtf.py:411-415)."""
+    # [h,s,t] @ [b,h,t,k] -> [b,h,s,k]
+    return np.matmul(m_tril[None], x.transpose(0, 2, 1, 3)).transpose(0, 2, 1, 3)
+
+
+def mix_bwd(m_tril, x, do):
+    dx = np.matmul(m_tril.transpose(0, 2, 1)[None], do.transpose(0, 2, 1, 3)).transpose(0, 2, 1, 3)
+    # dM[h,s,t] = tril * sum_{b,k} do[b,s,h,k] x[b,t,h,k]
+    dm = np.einsum("bhsk,bhtk->hst", do.transpose(0, 2, 1, 3), x.transpose(0, 2, 1, 3), optimize=True)
+    return dx, np.tril(dm)
+
+
+class Block0:
+    """block_config[0] = norm ; bottleneck_group_linear (src/model/basic.py:47-57,122-126)."""
+
+    @staticmethod
+    def fwd(p, i, x, keep=False):
+        B, S, H, K = x.shape
+        a, c0 = gn_fwd(x, p[f"g0_{i}"], p[f"b0_{i}"])
+        win = p[f"win_{i}"]
+        wmid = p[f"wmid_{i}"]
+        wout = p[f"wout_{i}"]
+        I = win.shape[-1]
+        K2 = wmid.shape[-1]
+        a2 = a.reshape(B * S, H * K)
+        h1 = np.maximum(a2 @ win.reshape(H * K, I), 0)  # in: relu
+        h2 = np.maximum(h1 @ wmid.reshape(I, H * K2), 0).reshape(B, S, H, K2)  # mid: relu
+        n, cm = gn_fwd(h2, p[f"gm_{i}"], p[f"bm_{i}"])  # mid: norm-shift-scale (group width K2)
+        f = np.einsum("bshj,hjk->bshk", n, wout, optimize=True)  # out: grouped, no activation
+        cache = (a2, c0, h1, h2, n, cm) if keep else None
+        return f, cache
+
+    @staticmethod
+    def bwd(p, i, cache, df):
+        a2, c0, h1, h2, n, cm = cache
+        B, S, H, K2 = h2.shape
+        win = p[f"win_{i}"]
+        wmid = p[f"wmid_{i}"]
+        wout = p[f"wout_{i}"]
+        I = win.shape[-1]
+        K = wout.shape[-1]
+        g = {}
+        g[f"wout_{i}"] = np.einsum("bshj,bshk->hjk", n, df, optimize=True)
+        dn = np.einsum("bshk,hjk->bshj", df, wout, optimize=True)
+        dh2, g[f"gm_{i}"], g[f"bm_{i}"] = gn_bwd(dn, cm, p[f"gm_{i}"])
+        dh2 = (dh2 * (h2 > 0)).reshape(B * S, H * K2)
+        g[f"wmid_{i}"] = (h1.T @ dh2).reshape(I, H, K2)
+        dh1 = (dh2 @ wmid.reshape(I, H * K2).T) * (h1 > 0)
+        g[f"win_{i}"] = (a2.T @ dh1).reshape(H, K, I)
+        da = (dh1 @ win.reshape(H * K, I).T).reshape(B, S, H, K)
+        dx, g[f"g0_{i}"], g[f"b0_{i}"] = gn_bwd(da, c0, p[f"g0_{i}"])
+        return dx, g
+
+
+class Block1:
+    """block_config[1] = norm ; mix_A ; norm ; gelu ; mix_B  (configs/32big_mixer.json:13-19)."""
+
+    @staticmethod
+    def fwd(p, i, x, keep=False):
+        ma = np.tril(p["mix_a"])
+        mb = np.tril(p["mix_b"])
+        a, c1 = gn_fwd(x, p[f"g1_{i}"], p[f"b1_{i}"])
+        m1 = mix_fwd(ma, a)
+        y2, c2 = gn_fwd(m1, p[f"g2_{i}"], p[f"b2_{i}"])
+        c = gelu_fwd(y2)
+        f = mix_fwd(mb, c)
+        cache = (a, c1, c2, y2, c, ma, mb) if keep else None
+        return f, cache
+
+    @staticmethod
+    def bwd(p, i, cache, df):
+        a, c1, c2, y2, c, ma, mb = cache
+        g = {}
+        dc, g["mix_b"] = mix_bwd(mb, c, df)
+        dy2 = dc * gelu_grad(y2)
+        dm1, g[f"g2_{i}"], g[f"b2_{i}"] = gn_bwd(dy2, c2, p[f"g2_{i}"])
+        da, g["mix_a"] = mix_bwd(ma, a, dm1)
+        dx, g[f"g1_{i}"], g[f"b1_{i}"] = gn_bwd(da, c1, p[f"g1_{i}"])
+        return dx, g
+
+
+BLOCKS = (Block0, Block1)
+
+
+def _cast_params(params, dtype):
+    return {k: v.astype(dtype) for k, v in params.items()}
+
+
+def forward(sh: Shapes, params, tok_x, tok_y, dtype=np.float64, n_global: typing.Optional[int] = None,
+            trace: typing.Optional[dict] = None):
+    """_input -> _body (revnet) -> _output -> _loss  (src/model/__init__.py:75-85,101-129,138-145,183-187).
+    Returns (loss, accuracy, state) where state holds what backward() needs.  `n_global` = targets.size of the
+    GLOBAL batch (src/mtf_wrapper.py:67: the loss normaliser), default = this batch."""
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    Bn = tok_x.shape[0]
+    p = _cast_params(params, dtype)
+    n = float(Bn * S if n_global is None else n_global)
+    e = p["embed"][tok_x]  # Gather, src/model/embedding.py:118-122
+    src = (e.reshape(Bn * S, I0) @ p["w0"].reshape(I0, F)).reshape(Bn, S, H, K)
+    x1 = src
+    x2 = src
+    if trace is not None:
+        trace["src"] = src.copy()
+    for i in range(L):
+        for c, blk in enumerate(BLOCKS):
+            f, _ = blk.fwd(p, i, x2)
+            x1, x2 = x2, x1 + f  # RevGradOp: y1 = x1 + f(x2); outputs (x2, y1)  src/model/revnet.py:23-24
+            if trace is not None:
+                trace[f"x1_{i}_{c}"] = x1.copy()
+                trace[f"x2_{i}_{c}"] = x2.copy()
+    out = x1 + x2  # src/model/__init__.py:129
+    logits = out.reshape(Bn * S, F) @ p["wo"].reshape(F, V)
+    mx = logits.max(-1, keepdims=True)
+    logz = np.log(np.exp(logits - mx).sum(-1)) + mx[:, 0]
+    tgt = tok_y.reshape(-1).astype(np.int64)
+    nll = (logz - logits[np.arange(Bn * S), tgt]).sum()
+    z2 = (logz * logz).sum()
+    loss = nll / n + sh.z_loss * z2 / n
+    acc = float((logits.argmax(-1) == tgt).sum()) / n
+    if trace is not None:
+        trace["out"] = out.copy()
+        trace["logits"] = logits.copy()
+        trace["logz"] = logz.copy()
+        trace["loss_nll"] = nll / n
+    state = dict(p=p, e=e, x1=x1, x2=x2, out=out, logits=logits, logz=logz, tgt=tgt, n=n, tok_x=tok_x)
+    return float(loss), acc, state
+
+
+def backward(sh: Shapes, state, trace: typing.Optional[dict] = None):
+    """Reverse sweep of src/optimizer/__init__.py:143-174 with RevGradOp.gradient (src/model/revnet.py:55-120):
+    inputs of each reversible sub-block are RECONSTRUCTED (x1 = y1 - f(x2)), f is recomputed, then backpropagated."""
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    p = state["p"]
+    logits, logz, tgt, n = state["logits"], state["logz"], state["tgt"], state["n"]
+    Bn = state["tok_x"].shape[0]
+    sm = np.exp(logits - logz[:, None])
+    dlogits = sm / n
+    dlogits[np.arange(Bn * S), tgt] -= 1.0 / n
+    dlogits += (2.0 * sh.z_loss / n) * logz[:, None] * sm
+    grads: typing.Dict[str, np.ndarray] = {}
+    out2 = state["out"].reshape(Bn * S, F)
+    grads["wo"] = (out2.T @ dlogits).reshape(H, K, 1, V)
+    dout = (dlogits @ p["wo"].reshape(F, V).T).reshape(Bn, S, H, K)
+    pp, q = state["x1"], state["x2"]  # final (x1, x2)
+    dp, dq = dout, dout.copy()
+    for i in reversed(range(L)):
+        for c in reversed(range(len(BLOCKS))):
+            blk = BLOCKS[c]
+            x2_in = pp  # src/model/revnet.py:58,90
+            f, cache = blk.fwd(p, i, x2_in, keep=True)  # recompute (cloned forward ops) :59-60
+            x1_in = q - f  # :89
+            dx2_f, g = blk.bwd(p, i, cache, dq)
+            for k, v in g.items():
+                grads[k] = grads[k] + v if k in grads else v  # shared mixers accumulate over all depths
+            dx1_in = dq  # :88
+            dx2_in = dp + dx2_f  # :120
+            pp, q, dp, dq = x1_in, x2_in, dx1_in, dx2_in
+            if trace is not None:
+                trace[f"rx1_{i}_{c}"] = pp.copy()
+                trace[f"rx2_{i}_{c}"] = q.copy()
+    dsrc = (dp + dq).reshape(Bn * S, F)
+    e2 = state["e"].reshape(Bn * S, I0)
+    grads["w0"] = (e2.T @ dsrc).reshape(1, I0, H, K)
+    de = dsrc @ p["w0"].reshape(I0, F).T
+    dE = np.zeros((V, I0), dtype=de.dtype)
+    np.add.at(dE, state["tok_x"].reshape(-1), de)  # ScatterAdd, src/model/embedding.py:39-83
+    grads["embed"] = dE
+    return grads
+
+
+# ----------------------------------------------------------------------------------------------------------
+# optimizer  (src/optimizer/__init__.py:31-66; src/optimizer/optimizers.py:13-14,60-84,114-128)
+# ----------------------------------------------------------------------------------------------------------
+def round_bf16(x: np.ndarray) -> np.ndarray:
+    """fp32 -> bfloat16 -> fp32, round-to-nearest-even (what a cast to a bfloat16 slice does)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    u = x.view(np.uint32)
+    r = ((u >> 16) & 1) + np.uint32(0x7FFF)
+    out = ((u + r) & np.uint32(0xFFFF0000)).view(np.float32)
+    return np.where(np.isnan(x), x, out)
+
+
+def learning_rate(sh: Shapes, global_step: int) -> float:
+    """get_learning_rate + MODULES (src/optimizer/learning_rate.py:27-72); global_step is read BEFORE the
+    increment, so lr == 0 on the very first step with linear_warmup."""
+    lr = np.float32(sh.learning_rate)
+    gs = np.float32(global_step)
+    for name, cfg in sh.learning_rate_config.items():
+        start = np.float32(cfg.get("start_step", 0))
+        final = np.float32(cfg.get("final_step", 0))
+        factor = np.float32(cfg.get("factor", 1.0))
+        if name == "linear_warmup":
+            warm = np.float32(gs < final)
+            lr = lr * (gs / final * warm + np.float32(1) * (np.float32(1) - warm))
+        elif name == "exponential_decay":
+            lr = lr * np.power(factor, np.maximum(gs - start, np.float32(0)))
+        elif name == "linear_decay":
+            lr = lr * np.clip(np.float32(1) - (gs - start) / (final - start), 0, 1)
+        elif name == "lower_bound":
+            lr = np.maximum(lr, factor)
+        elif name == "upper_bound":
+            lr = np.minimum(lr, factor)
+        else:
+            raise KeyError(name)
+    return float(np.float32(lr))
+
+
+def init_opt_state(params) -> typing.Dict[str, typing.Dict[str, np.ndarray]]:
+    """zeros, one buffer per dim + momentum (src/optimizer/backend.py:23-25; optimizers.py:64-68,123)."""
+    st = {}
+    for k, v in params.items():
+        st[k] = {f"dim{i}": np.zeros(d, np.float32) for i, d in enumerate(v.shape)}
+        st[k]["momentum"] = np.zeros(v.shape, np.float32)
+    return st
+
+
+def optimizer_step(sh: Shapes, params, grads, opt_state, lr: float):
+    """In-place update of params (fp32 slices) and opt_state, all arithmetic in fp32
+    (optimizer_calculation_dtype).  `grads` already carry the dtype the graph would hand over."""
+    f32 = np.float32
+    act_bf16 = sh.calculation_dtype == "bfloat16"
+    st_bf16 = sh.optimizer_slice_dtype == "bfloat16"
+    lr = f32(lr)
+    chain = [o.split(":") for o in sh.optimizer.split("-")]
+    for name, p in params.items():
+        g = grads[name].astype(f32)
+        w = round_bf16(p) if act_bf16 else p  # var.value: the slice cast to the activation dtype
+        st = opt_state[name]
+        for opt, *args in chain:
+            if opt == "adaptive_clip":  # optimizers.py:79-84
+                clip = f32(float(args[0]))
+                sg = f32(np.sum(g.astype(np.float64) ** 2))
+                sw = f32(np.sum(w.astype(np.float64) ** 2))
+                with np.errstate(divide="ignore"):
+                    gn = np.minimum(f32(1) / np.sqrt(sg), f32(1e6))
+                wn = np.maximum(np.sqrt(sw), f32(1e-3))
+                g = g * np.minimum(wn * gn * clip, f32(1))
+            elif opt == "sm3":  # optimizers.py:60-76
+                nd = p.ndim
+                acc = st["dim0"].reshape([-1] + [1] * (nd - 1))
+                for i in range(1, nd):
+                    shape = [1] * nd
+                    shape[i] = -1
+                    acc = np.minimum(acc, st[f"dim{i}"].reshape(shape))
+                nu = acc + g * g
+                for i in range(nd):
+                    red = tuple(j for j in range(nd) if j != i)
+                    new = nu.max(axis=red) if red else nu
+                    st[f"dim{i}"] = round_bf16(new) if st_bf16 else new.astype(f32)
+                g = g * (f32(1) / np.maximum(np.sqrt(nu), f32(1e-5)))  # opt_rsqrt, optimizers.py:13-14
+            elif opt == "momentum":  # optimizers.py:118-128
+                mult, gmult, nesterov = f32(float(args[0])), f32(float(args[1])), bool(int(args[2]))
+                new_state = mult * st["momentum"] + g * gmult
+                st["momentum"] = round_bf16(new_state) if st_bf16 else new_state.astype(f32)
+                g = g + mult * new_state if nesterov else new_state
+            elif opt == "learning_rate":  # optimizers.py:114-115
+                g = g * lr
+            else:
+                raise NotImplementedError(f"oracle: optimizer '{opt}'")
+        if is_large_tensor(name) and sh.weight_decay > 0:  # __init__.py:49-61
+            g = g + w * lr * f32(sh.weight_decay)
+        params[name] = (p - g).astype(f32)  # assign_sub on the fp32 slice, __init__.py:64
+
+
+def train_step(sh: Shapes, params, opt_state, tok_x, tok_y, global_step: int, dtype=np.float64):
+    """One full step: forward, backward, update.  Returns (loss, accuracy, grads, lr)."""
+    loss, acc, state = forward(sh, params, tok_x, tok_y, dtype=dtype)
+    grads = backward(sh, state)
+    if sh.calculation_dtype == "bfloat16":
+        grads = {k: round_bf16(v.astype(np.float32)) for k, v in grads.items()}
+    lr = learning_rate(sh, global_step)
+    optimizer_step(sh, params, grads, opt_state, lr)
+    return loss, acc, grads, lr
+
+
+def count_params(sh: Shapes) -> int:
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    per_depth = H * K * I + I * H * K2 + H * K2 * K + 2 * H * K2 + 6 * H * K
+    return L * per_depth + 2 * H * S * S + V * I0 + I0 * F + F * V
+
+
+def flops_per_token_fwd(sh: Shapes) -> float:
+    """causal-aware algorithmic forward FLOPs per token."""
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    return L * (2 * (F * I + I * H * K2 + H * K2 * K) + 2 * 2 * F * (S + 1) / 2) + 2 * (I0 * F + F * V)
