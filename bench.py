@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""bench.py -- train tokens/sec of the OBST mixer training step (BASELINE.json's metric).
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched under torchrun, one rank per GPU)
+    python bench.py --impl reference ...                      (the CPU restatement timed on the host cores)
+
+One "step" = one full training step (forward, reversible backward with recompute, gradient allreduce,
+fused optimizer update) of configs/32big_mixer.json's shape on synthetic tokens with random-init weights.
+The GLOBAL batch (1024 x 512 tokens) is fixed: N ranks take 1024/N rows each ("scaling": "strong").
+Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "homebrewnlp-mtf_b200"))
+
+METRIC = "train tokens/sec (32big_mixer shape)"
+UNIT = "tokens/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="32big_mixer", choices=["32big_mixer", "32ctx_mixer", "32mixer_group", "tiny"])
+    ap.add_argument("--micro-batch", type=int, default=0, help="rows per micro-batch (0 = auto)")
+    ap.add_argument("--depth", type=int, default=0, help="override depth (debug only: makes the number INVALID)")
+    ap.add_argument("--cpu-rows", type=int, default=2, help="sequences per step of the CPU baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d.get("hbm_gbs", 6650.0), "tf_burst": d.get("bf16_tflops", 1590.0),
+                "tf_sustained": d.get("bf16_tflops_sustained", d.get("bf16_tflops", 1590.0)), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "source": "fallback"}
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md's clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index = index
+        self.stop_flag = threading.Event()
+        self.samples = []
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 7:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
+        sm = [float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit()]
+        mx = [float(s[1]) for s in self.samples if s[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[3 + i].lower().startswith("active") for s in self.samples)]
+        pw = [float(s[2]) for s in self.samples if s[2].replace(".", "").isdigit()]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "reasons": reasons, "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------------------
+# CPU baseline / reference arm: the oracle (a port: the reference needs TF 2.7 + mesh-tensorflow, not installable)
+# ------------------------------------------------------------------------------------------------------------
+def cpu_step_rate(workload: str, rows: int, steps: int, warmup: int, depth: int = 0):
+    import numpy as np
+    from oracle import obst_oracle as orc
+    from obst.configs import mixer_config
+    cfg = mixer_config(workload)
+    if depth:
+        cfg["depth"] = depth
+    cfg["train_batch_size"] = rows
+    sh = orc.Shapes(cfg)
+    cores = os.cpu_count() or 1
+    params = orc.init_params_fast(sh, seed=0)
+    state = orc.init_opt_state(params)
+    tx, ty = orc.synthetic_tokens(sh)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        orc.train_step(sh, params, state, tx, ty, 2048 + i, dtype=np.float32)
+        times.append(time.perf_counter() - t0)
+    timed = times[warmup:]
+    tokens = rows * sh.sequence_length
+    value = tokens * len(timed) / sum(timed)
+    sample = (f"{len(timed)} full train steps (fwd + reversible bwd with recompute + optimizer) of the {workload} model "
+              f"(depth {sh.depth}) on {rows} sequences = {tokens} tokens each, numpy fp32 / BLAS threads")
+    return value, cores, sample, sum(timed) / len(timed)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    value, cores, sample, sec = cpu_step_rate(args.workload, args.cpu_rows, args.steps, args.warmup, args.depth)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{args.workload} (bounded sample: {args.cpu_rows} sequences per step)"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0,
+            "note": "reference needs tensorflow==2.7.0 + mesh-tensorflow (not installable: py3.12, no network); "
+                    "this arm times oracle/obst_oracle.py, the CPU restatement of the same step"}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from obst import native
+    from obst.configs import mixer_config
+    from obst.dataclass import ModelParameter
+    from obst.parallel import GradReducer, shard_rows
+    from obst.run.train import get_train_model, read_scalars
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback for the product path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    native.load()
+
+    cfg = mixer_config(args.workload)
+    if args.depth:
+        cfg["depth"] = args.depth
+    gb = cfg["train_batch_size"]
+    seq = cfg["sequence_length"]
+    r0, r1 = shard_rows(gb, rank, world)
+    rows = r1 - r0
+    mb = args.micro_batch or max(1, min(rows, 65536 // seq))
+    cfg["micro_batch_size"] = mb
+    cfg["device"] = f"cuda:{local_rank}"
+    import contextlib
+    import io
+    with contextlib.redirect_stdout(io.StringIO()) if rank else contextlib.nullcontext():
+        params = ModelParameter(cfg)
+    if world > 1:
+        params.grad_reducer = GradReducer(params)
+    params.global_step = 2048  # mid-warm-up: lr = 0.005 (step 0 would run with lr == 0)
+
+    # synthetic tokens: x = w[:, :S], y = w[:, 1:S+1]  (src/inputs.py:543-551), pinned host memory
+    g = torch.Generator().manual_seed(134567)
+    w = torch.randint(0, cfg["vocab_size"], (gb, seq + 1), generator=g, dtype=torch.int32)[r0:r1]
+    host_x = w[:, :-1].contiguous().unsqueeze(-1).pin_memory()
+    host_y = w[:, 1:].contiguous().unsqueeze(-1).pin_memory()
+    dev_x = host_x.cuda(non_blocking=True)
+    dev_y = host_y.cuda(non_blocking=True)
+
+    def step_resident():
+        return get_train_model(params, None, None, None, dev_x, dev_y, None, None, None, params.manual_global_step)
+
+    def step_e2e():
+        x = host_x.cuda(non_blocking=True)
+        y = host_y.cuda(non_blocking=True)
+        out = get_train_model(params, None, None, None, x, y, None, None, None, params.manual_global_step)
+        return read_scalars(params, out[3])
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms: float) -> float:
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(max(args.warmup, 1)):
+        out = step_resident()
+    scal = read_scalars(params, out[3])
+    barrier()
+
+    # ---- timed region 1: inputs resident in HBM, device timing -------------------------------------------
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    native.launch_count_reset()
+    native.gemm_profile(True)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        out = step_resident()
+    ev1.record()
+    barrier()
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = native.launch_count()
+    gemm_ms, gemm_flops, gemm_n = native.gemm_profile(False)
+    # ---- timed region 2: end to end through the public API with HOST buffers ----------------------------
+    barrier()
+    ev2, ev3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev2.record()
+    for _ in range(args.steps):
+        scal = step_e2e()
+    ev3.record()
+    barrier()
+    e2e_ms_total = max_over_ranks(ev2.elapsed_time(ev3))
+    sampler.stop_flag.set()
+    sampler.join(timeout=2)
+
+    tokens_per_step = gb * seq
+    ms_per_step = ms_total / args.steps
+    value = tokens_per_step / (ms_per_step * 1e-3)
+    e2e_value = tokens_per_step / (e2e_ms_total / args.steps * 1e-3)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    from oracle import obst_oracle as orc  # shape arithmetic only (FLOP formula of SURVEY.md 8(d))
+    sh = orc.Shapes(cfg)
+    flops_tok = 3.0 * orc.flops_per_token_fwd(sh)
+    pk = peaks()
+    # dominant kernel: gemm_tc_kernel (every contraction of the step).  achieved = algorithmic FLOPs (3 x forward,
+    # causal-aware, recompute NOT credited) that this rank's launches carry / summed launch durations (CUDA events
+    # around every launch on the launching stream, inside timed region 1).
+    rank_tokens = rows * seq * args.steps
+    achieved = flops_tok * rank_tokens / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "gemm_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch")
+    roofline = {"bound": "tensor", "kernel": "obst::gemm_tc_kernel", "achieved": achieved, "peak": pk["tf_sustained"],
+                "unit": "TFLOP/s", "frac": (achieved / pk["tf_sustained"]) if achieved else None, "traffic": traffic,
+                "peak_source": f"{pk['source']} (bf16_tflops_sustained: kernel timed inside a long step)",
+                "launches": gemm_n, "kernel_ms_per_step": gemm_ms / args.steps,
+                "kernel_share_of_step": gemm_ms / ms_total if ms_total else None,
+                "executed_tflops": gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None,
+                "whole_step_frac_of_peak": flops_tok * tokens_per_step / world / (ms_per_step * 1e-3) / 1e12 /
+                pk["tf_sustained"]}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "bf16" if cfg["calculation_dtype"] == "bfloat16" else "f32",
+            "data": "synthetic",
+            "config": {"workload": f"{args.workload}: depth {sh.depth}, global batch {gb} x seq {seq} "
+                                   f"({tokens_per_step} tokens/step), {orc.count_params(sh)} params, random init",
+                       "parallelism": f"dp{world}", "micro_batch_rows": mb, "rows_per_rank": rows,
+                       "l2": "inputs larger than L2 (every activation tensor is >= 512 MiB; weights 1.4 GB)",
+                       "loss": scal["loss"], "accuracy": scal["accuracy"]},
+            "clocks": sampler.summary(),
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * rows * seq * 4 * world,
+                    "d2h_bytes_per_step": 24 * world, "ms_per_step": e2e_ms_total / args.steps},
+            "gpu_launches": launches, "roofline": roofline}
+    if args.depth:
+        line["INVALID"] = "depth override"
+    if world == 1 and not args.no_cpu_baseline:
+        v, cores, sample, _ = cpu_step_rate(args.workload, args.cpu_rows, 1, 1, args.depth)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -132,6 +132,25 @@ def operand(t: torch.Tensor, s_mn: int, s_k: int, s_ko: int = 0, s_glo: int = 0,
     return Operand(t.data_ptr() + offset * t.element_size(), s_mn, s_k, s_ko, s_glo, s_ghi)
 
 
+_PROFILE = None  # list of (start_event, end_event, flops) while gemm_profile(True)
+
+
+def gemm_profile(on: bool):
+    """bench.py's live roofline measurement: CUDA events around every obst_gemm launch on the launching stream.
+    gemm_profile(True) starts collecting; gemm_profile(False) synchronises and returns
+    (summed launch duration in ms, executed useful FLOPs, number of launches)."""
+    global _PROFILE
+    if on:
+        _PROFILE = []
+        return None
+    rec, _PROFILE = _PROFILE, None
+    if not rec:
+        return 0.0, 0.0, 0
+    torch.cuda.synchronize()
+    ms = sum(s.elapsed_time(e) for s, e, _ in rec)
+    return ms, float(sum(f for _, _, f in rec)), len(rec)
+
+
 def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO: int = 1, GLO: int = 1, GHI: int = 1,
          d_ld: int, d_glo: int = 0, d_ghi: int = 0, d_offset: int = 0, R: typing.Optional[torch.Tensor] = None,
          r_offset: typing.Optional[int] = None, tri: int = 0, epi: int = 0, accumulate: bool = False, splits: int = 0,
@@ -151,6 +170,14 @@ def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO
         desc.R = None
     desc.d_ld, desc.d_glo, desc.d_ghi = d_ld, d_glo, d_ghi
     desc.tri, desc.epi, desc.accumulate, desc.splits = tri, epi, int(accumulate), splits
+    if _PROFILE is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        check(load().obst_gemm(ctypes.byref(desc), backend, stream_ptr()), "obst_gemm")
+        ev1.record()
+        useful = (M + 1) / (2.0 * M) if tri in (1, 2, 3) else 1.0  # causal half of a square [M, M] map
+        _PROFILE.append((ev0, ev1, 2.0 * M * N * KI * KO * GLO * GHI * useful))
+        return
     check(load().obst_gemm(ctypes.byref(desc), backend, stream_ptr()), "obst_gemm")
 
 

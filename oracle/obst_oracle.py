@@ -164,6 +164,38 @@ def init_params(sh: Shapes, seed: int = 0) -> typing.Dict[str, np.ndarray]:
     return p
 
 
+def init_params_fast(sh: Shapes, seed: int = 0) -> typing.Dict[str, np.ndarray]:
+    """TIMING ONLY (bench.py's CPU baseline): same tensors and scales as init_params, but the orthogonal weights
+    are drawn as N(0, 1/fan) instead of through a QR (which alone takes ~20 s for the 32big parameter set)."""
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    rng = np.random.default_rng(seed)
+    p: typing.Dict[str, np.ndarray] = {}
+
+    def normal(shape, mean, std):
+        return (mean + std * rng.standard_normal(shape, dtype=np.float32)).astype(np.float32)
+
+    p["embed"] = normal((V, I0), 0.0, sh.embedding_stddev)
+    p["w0"] = normal((1, I0, H, K), 0.0, (1.0 / max(I0, F)) ** 0.5)
+    for i in range(L):
+        p[f"g0_{i}"] = normal((H, K), 1.0, 0.02)
+        p[f"b0_{i}"] = normal((H, K), 0.0, 0.02)
+        p[f"win_{i}"] = normal((H, K, I), 0.0, (1.0 / max(F, I)) ** 0.5)
+        p[f"wmid_{i}"] = normal((I, H, K2), 0.0, (1.0 / max(I, H * K2)) ** 0.5)
+        p[f"gm_{i}"] = normal((H, K2), 1.0, 0.02)
+        p[f"bm_{i}"] = normal((H, K2), 0.0, 0.02)
+        p[f"wout_{i}"] = normal((H, K2, K), 0.0, (1.0 / max(H * K2, K)) ** 0.5)
+        p[f"g1_{i}"] = normal((H, K), 1.0, 0.02)
+        p[f"b1_{i}"] = normal((H, K), 0.0, 0.02)
+        if i == 0:
+            p["mix_a"] = normal((H, S, S), 0.0, sh.embedding_stddev)
+        p[f"g2_{i}"] = normal((H, K), 1.0, 0.02)
+        p[f"b2_{i}"] = normal((H, K), 0.0, 0.02)
+        if i == 0:
+            p["mix_b"] = normal((H, S, S), 0.0, sh.embedding_stddev)
+    p["wo"] = normal((H, K, 1, V), 0.0, (1.0 / (F * V)) ** 0.5)
+    return p
+
+
 def is_large_tensor(name: str) -> bool:
     """Weight-decay predicate of src/optimizer/__init__.py:49-57 evaluated on this model's variables:
     only the three feed-forward weights pass (norm/embed/input/output scopes are excluded)."""
@@ -228,28 +260,34 @@ def mix_bwd(m_tril, x, do):
     return dx, np.tril(dm)
 
 
+def _ident(x):
+    return x
+
+
 class Block0:
     """block_config[0] = norm ; bottleneck_group_linear (src/model/basic.py:47-57,122-126)."""
 
     @staticmethod
-    def fwd(p, i, x, keep=False):
+    def fwd(p, i, x, keep=False, rnd=_ident):
         B, S, H, K = x.shape
         a, c0 = gn_fwd(x, p[f"g0_{i}"], p[f"b0_{i}"])
+        a = rnd(a)
         win = p[f"win_{i}"]
         wmid = p[f"wmid_{i}"]
         wout = p[f"wout_{i}"]
         I = win.shape[-1]
         K2 = wmid.shape[-1]
         a2 = a.reshape(B * S, H * K)
-        h1 = np.maximum(a2 @ win.reshape(H * K, I), 0)  # in: relu
-        h2 = np.maximum(h1 @ wmid.reshape(I, H * K2), 0).reshape(B, S, H, K2)  # mid: relu
+        h1 = rnd(np.maximum(a2 @ win.reshape(H * K, I), 0))  # in: relu
+        h2 = rnd(np.maximum(h1 @ wmid.reshape(I, H * K2), 0)).reshape(B, S, H, K2)  # mid: relu
         n, cm = gn_fwd(h2, p[f"gm_{i}"], p[f"bm_{i}"])  # mid: norm-shift-scale (group width K2)
+        n = rnd(n)
         f = np.einsum("bshj,hjk->bshk", n, wout, optimize=True)  # out: grouped, no activation
         cache = (a2, c0, h1, h2, n, cm) if keep else None
         return f, cache
 
     @staticmethod
-    def bwd(p, i, cache, df):
+    def bwd(p, i, cache, df, rnd=_ident):
         a2, c0, h1, h2, n, cm = cache
         B, S, H, K2 = h2.shape
         win = p[f"win_{i}"]
@@ -259,13 +297,13 @@ class Block0:
         K = wout.shape[-1]
         g = {}
         g[f"wout_{i}"] = np.einsum("bshj,bshk->hjk", n, df, optimize=True)
-        dn = np.einsum("bshk,hjk->bshj", df, wout, optimize=True)
+        dn = rnd(np.einsum("bshk,hjk->bshj", df, wout, optimize=True))
         dh2, g[f"gm_{i}"], g[f"bm_{i}"] = gn_bwd(dn, cm, p[f"gm_{i}"])
-        dh2 = (dh2 * (h2 > 0)).reshape(B * S, H * K2)
+        dh2 = rnd(dh2 * (h2 > 0)).reshape(B * S, H * K2)
         g[f"wmid_{i}"] = (h1.T @ dh2).reshape(I, H, K2)
-        dh1 = (dh2 @ wmid.reshape(I, H * K2).T) * (h1 > 0)
+        dh1 = rnd((dh2 @ wmid.reshape(I, H * K2).T) * (h1 > 0))
         g[f"win_{i}"] = (a2.T @ dh1).reshape(H, K, I)
-        da = (dh1 @ win.reshape(H * K, I).T).reshape(B, S, H, K)
+        da = rnd(dh1 @ win.reshape(H * K, I).T).reshape(B, S, H, K)
         dx, g[f"g0_{i}"], g[f"b0_{i}"] = gn_bwd(da, c0, p[f"g0_{i}"])
         return dx, g
 
@@ -274,25 +312,28 @@ class Block1:
     """block_config[1] = norm ; mix_A ; norm ; gelu ; mix_B  (configs/32big_mixer.json:13-19)."""
 
     @staticmethod
-    def fwd(p, i, x, keep=False):
+    def fwd(p, i, x, keep=False, rnd=_ident):
         ma = np.tril(p["mix_a"])
         mb = np.tril(p["mix_b"])
         a, c1 = gn_fwd(x, p[f"g1_{i}"], p[f"b1_{i}"])
-        m1 = mix_fwd(ma, a)
+        a = rnd(a)
+        m1 = rnd(mix_fwd(ma, a))
         y2, c2 = gn_fwd(m1, p[f"g2_{i}"], p[f"b2_{i}"])
-        c = gelu_fwd(y2)
+        c = rnd(gelu_fwd(y2))
         f = mix_fwd(mb, c)
         cache = (a, c1, c2, y2, c, ma, mb) if keep else None
         return f, cache
 
     @staticmethod
-    def bwd(p, i, cache, df):
+    def bwd(p, i, cache, df, rnd=_ident):
         a, c1, c2, y2, c, ma, mb = cache
         g = {}
         dc, g["mix_b"] = mix_bwd(mb, c, df)
-        dy2 = dc * gelu_grad(y2)
+        dy2 = rnd(dc) * gelu_grad(y2)
         dm1, g[f"g2_{i}"], g[f"b2_{i}"] = gn_bwd(dy2, c2, p[f"g2_{i}"])
+        dm1 = rnd(dm1)
         da, g["mix_a"] = mix_bwd(ma, a, dm1)
+        da = rnd(da)
         dx, g[f"g1_{i}"], g[f"b1_{i}"] = gn_bwd(da, c1, p[f"g1_{i}"])
         return dx, g
 
@@ -305,29 +346,31 @@ def _cast_params(params, dtype):
 
 
 def forward(sh: Shapes, params, tok_x, tok_y, dtype=np.float64, n_global: typing.Optional[int] = None,
-            trace: typing.Optional[dict] = None):
+            trace: typing.Optional[dict] = None, rnd=_ident):
     """_input -> _body (revnet) -> _output -> _loss  (src/model/__init__.py:75-85,101-129,138-145,183-187).
     Returns (loss, accuracy, state) where state holds what backward() needs.  `n_global` = targets.size of the
-    GLOBAL batch (src/mtf_wrapper.py:67: the loss normaliser), default = this batch."""
+    GLOBAL batch (src/mtf_wrapper.py:67: the loss normaliser), default = this batch.
+    `rnd` (default identity) is applied wherever an activation tensor is materialised; passing `round_bf16` gives
+    the arithmetic twin of a calculation_dtype=bfloat16 run, used by the tests to size the error budget."""
     B, S, H, K, F, I, K2, I0, V, L = sh.dims
     Bn = tok_x.shape[0]
     p = _cast_params(params, dtype)
     n = float(Bn * S if n_global is None else n_global)
     e = p["embed"][tok_x]  # Gather, src/model/embedding.py:118-122
-    src = (e.reshape(Bn * S, I0) @ p["w0"].reshape(I0, F)).reshape(Bn, S, H, K)
+    src = rnd((e.reshape(Bn * S, I0) @ p["w0"].reshape(I0, F)).reshape(Bn, S, H, K))
     x1 = src
     x2 = src
     if trace is not None:
         trace["src"] = src.copy()
     for i in range(L):
         for c, blk in enumerate(BLOCKS):
-            f, _ = blk.fwd(p, i, x2)
-            x1, x2 = x2, x1 + f  # RevGradOp: y1 = x1 + f(x2); outputs (x2, y1)  src/model/revnet.py:23-24
+            f, _ = blk.fwd(p, i, x2, rnd=rnd)
+            x1, x2 = x2, rnd(x1 + f)  # RevGradOp: y1 = x1 + f(x2); outputs (x2, y1)  src/model/revnet.py:23-24
             if trace is not None:
                 trace[f"x1_{i}_{c}"] = x1.copy()
                 trace[f"x2_{i}_{c}"] = x2.copy()
-    out = x1 + x2  # src/model/__init__.py:129
-    logits = out.reshape(Bn * S, F) @ p["wo"].reshape(F, V)
+    out = rnd(x1 + x2)  # src/model/__init__.py:129
+    logits = rnd(out.reshape(Bn * S, F) @ p["wo"].reshape(F, V))
     mx = logits.max(-1, keepdims=True)
     logz = np.log(np.exp(logits - mx).sum(-1)) + mx[:, 0]
     tgt = tok_y.reshape(-1).astype(np.int64)
@@ -340,7 +383,7 @@ def forward(sh: Shapes, params, tok_x, tok_y, dtype=np.float64, n_global: typing
         trace["logits"] = logits.copy()
         trace["logz"] = logz.copy()
         trace["loss_nll"] = nll / n
-    state = dict(p=p, e=e, x1=x1, x2=x2, out=out, logits=logits, logz=logz, tgt=tgt, n=n, tok_x=tok_x)
+    state = dict(p=p, e=e, x1=x1, x2=x2, out=out, logits=logits, logz=logz, tgt=tgt, n=n, tok_x=tok_x, rnd=rnd)
     return float(loss), acc, state
 
 
@@ -355,31 +398,33 @@ def backward(sh: Shapes, state, trace: typing.Optional[dict] = None):
     dlogits = sm / n
     dlogits[np.arange(Bn * S), tgt] -= 1.0 / n
     dlogits += (2.0 * sh.z_loss / n) * logz[:, None] * sm
+    rnd = state.get("rnd", _ident)
+    dlogits = rnd(dlogits)
     grads: typing.Dict[str, np.ndarray] = {}
     out2 = state["out"].reshape(Bn * S, F)
     grads["wo"] = (out2.T @ dlogits).reshape(H, K, 1, V)
-    dout = (dlogits @ p["wo"].reshape(F, V).T).reshape(Bn, S, H, K)
+    dout = rnd(dlogits @ p["wo"].reshape(F, V).T).reshape(Bn, S, H, K)
     pp, q = state["x1"], state["x2"]  # final (x1, x2)
     dp, dq = dout, dout.copy()
     for i in reversed(range(L)):
         for c in reversed(range(len(BLOCKS))):
             blk = BLOCKS[c]
             x2_in = pp  # src/model/revnet.py:58,90
-            f, cache = blk.fwd(p, i, x2_in, keep=True)  # recompute (cloned forward ops) :59-60
-            x1_in = q - f  # :89
-            dx2_f, g = blk.bwd(p, i, cache, dq)
+            f, cache = blk.fwd(p, i, x2_in, keep=True, rnd=rnd)  # recompute (cloned forward ops) :59-60
+            x1_in = rnd(q - f)  # :89
+            dx2_f, g = blk.bwd(p, i, cache, dq, rnd=rnd)
             for k, v in g.items():
                 grads[k] = grads[k] + v if k in grads else v  # shared mixers accumulate over all depths
             dx1_in = dq  # :88
-            dx2_in = dp + dx2_f  # :120
+            dx2_in = rnd(dp + dx2_f)  # :120
             pp, q, dp, dq = x1_in, x2_in, dx1_in, dx2_in
             if trace is not None:
                 trace[f"rx1_{i}_{c}"] = pp.copy()
                 trace[f"rx2_{i}_{c}"] = q.copy()
-    dsrc = (dp + dq).reshape(Bn * S, F)
+    dsrc = rnd(dp + dq).reshape(Bn * S, F)
     e2 = state["e"].reshape(Bn * S, I0)
     grads["w0"] = (e2.T @ dsrc).reshape(1, I0, H, K)
-    de = dsrc @ p["w0"].reshape(I0, F).T
+    de = rnd(dsrc @ p["w0"].reshape(I0, F).T)
     dE = np.zeros((V, I0), dtype=de.dtype)
     np.add.at(dE, state["tok_x"].reshape(-1), de)  # ScatterAdd, src/model/embedding.py:39-83
     grads["embed"] = dE
