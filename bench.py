@@ -172,7 +172,7 @@ def run_b200(args):
         params = ModelParameter(cfg)
     if world > 1:
         params.grad_reducer = GradReducer(params)
-    params.global_step = 2048  # mid-warm-up: lr = 0.005 (step 0 would run with lr == 0)
+    # global_step starts at 0 exactly like a fresh reference run: linear warm-up, lr = 0.01 * step / 4096
 
     # synthetic tokens: x = w[:, :S], y = w[:, 1:S+1]  (src/inputs.py:543-551), pinned host memory
     g = torch.Generator().manual_seed(134567)
@@ -244,9 +244,8 @@ def run_b200(args):
             dist.destroy_process_group()
         return
 
-    from oracle import obst_oracle as orc  # shape arithmetic only (FLOP formula of SURVEY.md 8(d))
-    sh = orc.Shapes(cfg)
-    flops_tok = 3.0 * orc.flops_per_token_fwd(sh)
+    from obst.analysis import count_params, flops_per_token_fwd
+    flops_tok = 3.0 * flops_per_token_fwd(params)
     pk = peaks()
     # dominant kernel: gemm_tc_kernel (every contraction of the step).  achieved = algorithmic FLOPs (3 x forward,
     # causal-aware, recompute NOT credited) that this rank's launches carry / summed launch durations (CUDA events
@@ -270,8 +269,8 @@ def run_b200(args):
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16" if cfg["calculation_dtype"] == "bfloat16" else "f32",
             "data": "synthetic",
-            "config": {"workload": f"{args.workload}: depth {sh.depth}, global batch {gb} x seq {seq} "
-                                   f"({tokens_per_step} tokens/step), {orc.count_params(sh)} params, random init",
+            "config": {"workload": f"{args.workload}: depth {params.depth}, global batch {gb} x seq {seq} "
+                                   f"({tokens_per_step} tokens/step), {count_params(params)} params, random init",
                        "parallelism": f"dp{world}", "micro_batch_rows": mb, "rows_per_rank": rows,
                        "l2": "inputs larger than L2 (every activation tensor is >= 512 MiB; weights 1.4 GB)",
                        "loss": scal["loss"], "accuracy": scal["accuracy"]},

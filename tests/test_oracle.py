@@ -1,0 +1,292 @@
+"""Pins the CPU oracle (oracle/obst_oracle.py): against the only expectations the reference authors wrote
+(statistics of the initialisers, tests/variable_test.py / basic_*_test.py of the reference), against an
+independent torch-autograd statement of the same forward pass, against closed-form values, and against the
+committed fixtures in tests/golden/.  Runs on CPU in well under a minute."""
+import copy
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import obst_oracle as orc
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tiny_step.npz")
+
+
+def small_cfg(**kw):
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=2, train_batch_size=2, sequence_length=64)
+    cfg.update(kw)
+    return cfg
+
+
+# ---- shapes / work figures ------------------------------------------------------------
+@pytest.mark.parametrize("name,dims,n_params,fwd_flops", [
+    ("32big_mixer", (1024, 512, 8, 512, 4096, 512, 1024, 64, 256, 32), 342376448, 808189952),
+    ("32ctx_mixer", (256, 2048, 8, 256, 2048, 256, 512, 32, 256, 32), 152248320, 437518336),
+    ("32mixer_group", (4096, 256, 8, 256, 2048, 256, 512, 32, 256, 32), 86188032, 202637312),
+    ("tiny", (8, 256, 8, 32, 256, 32, 64, 4, 256, 2), 1203200, 560128),
+])
+def test_shapes_params_and_flops(name, dims, n_params, fwd_flops):
+    from obst.configs import mixer_config
+    sh = orc.Shapes(mixer_config(name))
+    assert sh.dims == dims
+    assert orc.count_params(sh) == n_params
+    assert orc.flops_per_token_fwd(sh) == fwd_flops
+
+
+def test_param_inventory_matches_count():
+    sh = orc.Shapes(small_cfg())
+    p = orc.init_params(sh, 0)
+    assert sum(v.size for v in p.values()) == orc.count_params(sh)
+    assert len(p) == sh.depth * 11 + 5  # per depth 3 GEMM weights + 8 norm vectors; M_A, M_B, E, W0, W_o
+    assert [n for n in p if orc.is_large_tensor(n)] == [f"{w}_{i}" for i in range(sh.depth)
+                                                        for w in ("win", "wmid", "wout")]
+
+
+# ---- reference-authored statistical invariants (the only expectations the reference's tests hold) ----------
+def test_orthogonal_var_statistics():
+    """tests/variable_test.py:79-88 of the reference: std of an orthogonal variable = 1/sqrt(max(fan_in, fan_out));
+    rows/columns orthonormal."""
+    rng = np.random.default_rng(0)
+    for sizes, fan_in in (((8, 32, 32), 256), ((32, 8, 64), 32), ((8, 64, 32), 512), ((1, 4, 8, 32), 4)):
+        w = orc.orthogonal_init(rng, sizes, fan_in)
+        total = int(np.prod(sizes))
+        fan_out = total // fan_in
+        m = w.reshape(fan_in, fan_out).astype(np.float64)
+        if fan_out > fan_in:
+            assert np.allclose(m @ m.T, np.eye(fan_in), atol=1e-5)
+        else:
+            assert np.allclose(m.T @ m, np.eye(fan_out), atol=1e-5)
+        assert np.isclose(w.std(), 1 / math.sqrt(max(fan_in, fan_out)), rtol=0.05)
+
+
+def test_output_embedding_is_one_unit_vector():
+    sh = orc.Shapes(small_cfg())
+    p = orc.init_params(sh, 0)
+    assert np.isclose(np.linalg.norm(p["wo"].astype(np.float64)), 1.0, atol=1e-5)
+
+
+def test_normal_var_statistics():
+    """tests/variable_test.py:36-77: norm shift 0 +- 0.02, norm scale 1 +- 0.02, embeddings N(0, embedding_stddev)."""
+    sh = orc.Shapes(orc.TINY_CONFIG)
+    p = orc.init_params(sh, 0)
+    g = np.concatenate([p[k].ravel() for k in p if k.startswith("g")])
+    b = np.concatenate([p[k].ravel() for k in p if k.startswith("b")])
+    assert abs(g.mean() - 1) < 2e-3 and abs(g.std() - 0.02) < 2e-3
+    assert abs(b.mean()) < 2e-3 and abs(b.std() - 0.02) < 2e-3
+    for k in ("mix_a", "mix_b", "embed"):
+        assert abs(p[k].std() - sh.embedding_stddev) < 0.1 * sh.embedding_stddev
+
+
+def test_linear_stack_keeps_unit_std_and_relu_ratio():
+    """tests/basic_linear_square_test.py:28-33 / tests/backend.py:13: an orthogonal linear keeps std ~ 1 on N(0,1)
+    input; a ReLU after it scales the std by ~ 1/1.42."""
+    rng = np.random.default_rng(1)
+    x = rng.standard_normal((4096, 256))
+    w = orc.orthogonal_init(rng, (256, 256), 256).astype(np.float64)
+    y = x @ w
+    assert np.isclose(np.mean(np.std(y, -1)), 1.0, rtol=0.02)
+    # the reference's own tolerance (rtol 0.2, tests/basic_linear_square_test.py:33); exact value sqrt(1/2 - 1/2pi)
+    assert np.isclose(np.mean(np.std(np.maximum(y, 0), -1)), 1 / 1.42, rtol=0.2)
+    assert np.isclose(np.maximum(y, 0).std(), math.sqrt(0.5 - 0.5 / math.pi), rtol=0.02)
+
+
+# ---- the math itself ---------------------------------------------------------------------------------------
+def test_initial_loss_is_ln_vocab_plus_zloss():
+    sh = orc.Shapes(small_cfg(train_batch_size=4))
+    p = orc.init_params(sh, 0)
+    tx, ty = orc.synthetic_tokens(sh)
+    loss, acc, _ = orc.forward(sh, p, tx, ty)
+    lnv = math.log(256)
+    assert abs(loss - (lnv + 1e-4 * lnv ** 2)) < 5e-3
+    assert 0 <= acc <= 0.05
+
+
+def test_gelu_is_the_reference_form_not_the_textbook_one():
+    x = np.linspace(-3, 3, 13)
+    ref = 0.5 * x * (1 + np.tanh(0.044715 * x ** 3 + math.sqrt(2 / math.pi) * x))
+    textbook = 0.5 * x * (1 + np.tanh(math.sqrt(2 / math.pi) * (x + 0.044715 * x ** 3)))
+    assert np.allclose(orc.gelu_fwd(x), ref)
+    assert not np.allclose(orc.gelu_fwd(x), textbook)
+    eps = 1e-6
+    assert np.allclose(orc.gelu_grad(x), (orc.gelu_fwd(x + eps) - orc.gelu_fwd(x - eps)) / (2 * eps), atol=1e-6)
+
+
+def _torch_forward(sh, tp, tok_x, tok_y):
+    """Independent statement of Appendix A in torch, differentiated by autograd (no reversibility)."""
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    Bn = tok_x.shape[0]
+
+    def gn(x, g, b):
+        xh = x - x.mean(-1, keepdim=True)
+        return xh * torch.rsqrt((xh * xh).mean(-1, keepdim=True) + 1e-5) * g + b
+
+    def gelu(x):
+        return 0.5 * x * (1 + torch.tanh(0.044715 * x ** 3 + math.sqrt(2 / math.pi) * x))
+
+    e = tp["embed"][torch.from_numpy(tok_x).long()]
+    src = torch.einsum("bsi,ihk->bshk", e, tp["w0"][0])
+    x1 = x2 = src
+    for i in range(L):
+        a = gn(x2, tp[f"g0_{i}"], tp[f"b0_{i}"])
+        h1 = torch.relu(torch.einsum("bshk,hki->bsi", a, tp[f"win_{i}"]))
+        h2 = torch.relu(torch.einsum("bsi,ihj->bshj", h1, tp[f"wmid_{i}"]))
+        n = gn(h2, tp[f"gm_{i}"], tp[f"bm_{i}"])
+        f = torch.einsum("bshj,hjk->bshk", n, tp[f"wout_{i}"])
+        x1, x2 = x2, x1 + f
+        a = gn(x2, tp[f"g1_{i}"], tp[f"b1_{i}"])
+        m1 = torch.einsum("hst,bthk->bshk", torch.tril(tp["mix_a"]), a)
+        c = gelu(gn(m1, tp[f"g2_{i}"], tp[f"b2_{i}"]))
+        f = torch.einsum("hst,bthk->bshk", torch.tril(tp["mix_b"]), c)
+        x1, x2 = x2, x1 + f
+    out = x1 + x2
+    logits = torch.einsum("bshk,hkv->bsv", out, tp["wo"][:, :, 0]).reshape(Bn * S, V)
+    logz = torch.logsumexp(logits, -1)
+    tgt = torch.from_numpy(tok_y.reshape(-1)).long()
+    n = Bn * S
+    return (logz - logits[torch.arange(n), tgt]).sum() / n + sh.z_loss * (logz ** 2).sum() / n
+
+
+def test_hand_written_backward_matches_autograd():
+    """Every explicit VJP of the oracle (norm, relu, gelu, dense/grouped GEMMs, causal mixing with the gradient
+    of the SHARED maps summed over depths, embedding scatter-add, reversible reconstruction) against autograd."""
+    sh = orc.Shapes(small_cfg(train_batch_size=2, sequence_length=32))
+    p = orc.init_params(sh, 3)
+    tx, ty = orc.synthetic_tokens(sh)
+    loss, _, state = orc.forward(sh, p, tx, ty, dtype=np.float64)
+    grads = orc.backward(sh, state)
+    tp = {k: torch.from_numpy(v.astype(np.float64)).requires_grad_(True) for k, v in p.items()}
+    tloss = _torch_forward(sh, tp, tx, ty)
+    tloss.backward()
+    assert abs(float(tloss) - loss) < 1e-10
+    for k, v in tp.items():
+        ref = v.grad.numpy()
+        err = np.linalg.norm(grads[k] - ref) / (np.linalg.norm(ref) + 1e-30)
+        assert err < 1e-7, (k, err)
+    assert np.abs(np.triu(grads["mix_a"], 1)).max() == 0
+
+
+def test_reversible_reconstruction_is_exact_in_float64_and_lossy_in_float32():
+    sh = orc.Shapes(orc.TINY_CONFIG)
+    p = orc.init_params(sh, 0)
+    tx, ty = orc.synthetic_tokens(sh)
+    res = {}
+    for dt in (np.float64, np.float32):
+        tr = {}
+        _, _, st = orc.forward(sh, p, tx, ty, dtype=dt, trace=tr)
+        orc.backward(sh, st, trace=tr)
+        res[dt] = np.linalg.norm(tr["rx1_0_0"].astype(np.float64) - tr["src"]) / np.linalg.norm(tr["src"])
+    assert res[np.float64] < 1e-9
+    # |x1| ~ 4e-4 is reconstructed from y1 - f with |f| ~ 0.3: fp32 loses ~3 digits here (DESIGN.md "Parity")
+    assert 1e-4 < res[np.float32] < 0.5
+
+
+def test_data_parallel_sharding_is_a_sum_with_the_global_normaliser():
+    """per-rank gradients with the GLOBAL loss normaliser add up to the full-batch gradient."""
+    sh = orc.Shapes(small_cfg(train_batch_size=4, sequence_length=32, depth=1))
+    p = orc.init_params(sh, 5)
+    tx, ty = orc.synthetic_tokens(sh)
+    loss, _, st = orc.forward(sh, p, tx, ty)
+    full = orc.backward(sh, st)
+    n = tx.size
+    parts, losses = [], []
+    for r in range(2):
+        sl = slice(2 * r, 2 * r + 2)
+        l_r, _, st_r = orc.forward(sh, p, tx[sl], ty[sl], n_global=n)
+        parts.append(orc.backward(sh, st_r))
+        losses.append(l_r)
+    assert abs(sum(losses) - loss) < 1e-12
+    for k in full:
+        assert np.allclose(parts[0][k] + parts[1][k], full[k], rtol=1e-9, atol=1e-14), k
+
+
+# ---- optimizer ---------------------------------------------------------------------------------------------
+def test_round_bf16_matches_torch():
+    x = np.random.default_rng(0).standard_normal(10000).astype(np.float32) * 1e3
+    x[:4] = [0.0, -0.0, 1.0039062, 3.3895314e38]
+    ref = torch.from_numpy(x).to(torch.bfloat16).float().numpy()
+    assert np.array_equal(orc.round_bf16(x), ref)
+
+
+def test_learning_rate_schedule():
+    sh = orc.Shapes(orc.TINY_CONFIG)
+    assert orc.learning_rate(sh, 0) == 0.0  # read BEFORE the increment: the first step runs with lr == 0
+    assert np.isclose(orc.learning_rate(sh, 2048), 0.005)
+    assert np.isclose(orc.learning_rate(sh, 4096), 0.01) and np.isclose(orc.learning_rate(sh, 10 ** 6), 0.01)
+
+
+def test_optimizer_step_closed_form_first_step():
+    """First step from zero state: nu = g'^2, u = sign(g') (|g'| > 1e-5), m = u, update = lr*(1.9*u) + decay."""
+    sh = orc.Shapes(small_cfg(depth=1))
+    p = orc.init_params(sh, 0)
+    rng = np.random.default_rng(1)
+    g = {k: rng.standard_normal(v.shape).astype(np.float32) for k, v in p.items()}
+    st = orc.init_opt_state(p)
+    p2 = {k: v.copy() for k, v in p.items()}
+    lr = 0.005
+    orc.optimizer_step(sh, p2, g, st, lr)
+    for k in p:
+        gn = np.sqrt((g[k].astype(np.float64) ** 2).sum())
+        wn = max(np.sqrt((p[k].astype(np.float64) ** 2).sum()), 1e-3)
+        gs = g[k] * min(wn / gn * 0.003, 1.0)
+        big = np.abs(gs) > 1e-4
+        upd = p[k] - p2[k]
+        exp = lr * 1.9 * np.sign(gs) + (p[k] * lr * 1e-4 if orc.is_large_tensor(k) else 0)
+        assert np.allclose(upd[big], exp[big], rtol=1e-3, atol=1e-7), k
+        assert np.allclose(st[k]["momentum"][big], np.sign(gs)[big], rtol=1e-3)
+        for i in range(p[k].ndim):
+            red = tuple(j for j in range(p[k].ndim) if j != i)
+            assert np.allclose(st[k][f"dim{i}"], (gs * gs).max(axis=red), rtol=1e-5)
+
+
+def test_lr_zero_leaves_weights_bit_identical_but_moves_state():
+    sh = orc.Shapes(small_cfg(depth=1))
+    p = orc.init_params(sh, 0)
+    tx, ty = orc.synthetic_tokens(sh)
+    st = orc.init_opt_state(p)
+    p2 = {k: v.copy() for k, v in p.items()}
+    _, _, _, lr = orc.train_step(sh, p2, st, tx, ty, global_step=0)
+    assert lr == 0.0
+    for k in p:
+        assert np.array_equal(p[k], p2[k])
+    assert np.abs(st["win_0"]["momentum"]).max() > 0
+    # masked entries of the mixing maps never receive gradient: their state stays exactly zero
+    assert np.abs(np.triu(st["mix_a"]["momentum"], 1)).max() == 0
+
+
+def test_bf16_state_is_rounded_once_per_step():
+    cfg = small_cfg(depth=1, calculation_dtype="bfloat16", optimizer_slice_dtype="bfloat16")
+    sh = orc.Shapes(cfg)
+    p = orc.init_params(sh, 0)
+    tx, ty = orc.synthetic_tokens(sh)
+    st = orc.init_opt_state(p)
+    orc.train_step(sh, p, st, tx, ty, global_step=100)
+    for k in st:
+        for slot, v in st[k].items():
+            assert np.array_equal(v, orc.round_bf16(v)), (k, slot)
+
+
+# ---- committed fixtures -------------------------------------------------------------------------------------
+def test_golden_fixture():
+    gold = np.load(GOLDEN)
+    sh = orc.Shapes(small_cfg())
+    p = orc.init_params(sh, seed=0)
+    tx, ty = orc.synthetic_tokens(sh)
+    trace = {}
+    loss, acc, state = orc.forward(sh, p, tx, ty, dtype=np.float64, trace=trace)
+    grads = orc.backward(sh, state)
+    st = orc.init_opt_state(p)
+    p2 = {k: v.copy() for k, v in p.items()}
+    orc.optimizer_step(sh, p2, {k: v.astype(np.float32) for k, v in grads.items()}, st, orc.learning_rate(sh, 2048))
+    assert np.isclose(loss, float(gold["loss"]), rtol=1e-12)
+    assert acc == float(gold["accuracy"])
+    assert np.allclose(trace["logits"][:4, :8], gold["logits_head"], rtol=1e-10)
+    assert np.allclose(trace[f"x2_{sh.depth - 1}_1"][0, :2, 0, :8], gold["x2_last_head"], rtol=1e-10)
+    for k in grads:
+        assert np.isclose(np.linalg.norm(grads[k]), float(gold[f"gnorm/{k}"]), rtol=1e-9), k
+        assert np.isclose(p2[k].astype(np.float64).sum(), float(gold[f"pnew_sum/{k}"]), rtol=1e-6, atol=1e-6), k
+        assert np.isclose(np.linalg.norm(st[k]["momentum"]), float(gold[f"mom_norm/{k}"]), rtol=1e-5), k
+        assert np.isclose(st[k]["dim0"].astype(np.float64).sum(), float(gold[f"dim0_sum/{k}"]), rtol=1e-5), k
