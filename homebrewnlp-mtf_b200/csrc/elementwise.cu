@@ -10,7 +10,9 @@ static constexpr float GN_EPS = 1e-5f;  // src/model/normalization.py:28
 // ================================================================================================
 // group norm forward: one warp per (token, head) row of `width` contiguous elements
 // ================================================================================================
-template <typename T, int MAXC>
+// ROWS rows are in flight per warp (all their loads are issued before the first reduction): with one 1 KB row per
+// warp the kernel is latency-bound at ~60 % of HBM; 4 rows give the memory system 8 x 16 B per lane to chew on.
+template <typename T, int MAXC, int ROWS>
 __global__ void __launch_bounds__(256) gn_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma,
                                                       const T* __restrict__ beta, T* __restrict__ y, int64_t rows,
                                                       int heads, int width, int act) {
@@ -19,52 +21,76 @@ __global__ void __launch_bounds__(256) gn_fwd_kernel(const T* __restrict__ x, co
   const int warps_per_block = blockDim.x >> 5;
   const int chunks = width / N;
   const float inv_w = 1.0f / (float)width;
-  for (int64_t row = (int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5); row < rows;
-       row += (int64_t)gridDim.x * warps_per_block) {
-    const T* xr = x + row * width;
-    const int h = (int)(row % heads);
-    Vec16<T> v[MAXC];
-    float s = 0.f;
+  const int64_t gstride = (int64_t)gridDim.x * warps_per_block * ROWS;
+  for (int64_t base = ((int64_t)blockIdx.x * warps_per_block + (threadIdx.x >> 5)) * ROWS; base < rows;
+       base += gstride) {
+    Vec16<T> v[ROWS][MAXC];
+    float s[ROWS];
 #pragma unroll
-    for (int i = 0; i < MAXC; ++i) {
-      const int c = lane + 32 * i;
-      if (c < chunks) {
-        v[i].load(xr + c * N);
+    for (int r = 0; r < ROWS; ++r) {
+      s[r] = 0.f;
+      const int64_t row = base + r;
+      if (row < rows) {
+        const T* xr = x + row * width;
 #pragma unroll
-        for (int j = 0; j < N; ++j) s += v[i].v[j];
-      }
-    }
-    const float mean = warp_sum(s) * inv_w;
-    float q = 0.f;
-#pragma unroll
-    for (int i = 0; i < MAXC; ++i) {
-      const int c = lane + 32 * i;
-      if (c < chunks) {
-#pragma unroll
-        for (int j = 0; j < N; ++j) {
-          v[i].v[j] -= mean;
-          q += v[i].v[j] * v[i].v[j];
+        for (int i = 0; i < MAXC; ++i) {
+          const int c = lane + 32 * i;
+          if (c < chunks) v[r][i].load(xr + c * N);
         }
       }
     }
-    const float rstd = rsqrtf(warp_sum(q) * inv_w + GN_EPS);
-    T* yr = y + row * width;
 #pragma unroll
-    for (int i = 0; i < MAXC; ++i) {
-      const int c = lane + 32 * i;
-      if (c < chunks) {
-        Vec16<T> g, b;
-        if (gamma) g.load(gamma + (int64_t)h * width + c * N);
-        if (beta) b.load(beta + (int64_t)h * width + c * N);
+    for (int r = 0; r < ROWS; ++r) {
 #pragma unroll
-        for (int j = 0; j < N; ++j) {
-          float o = v[i].v[j] * rstd;
-          if (gamma) o *= g.v[j];
-          if (beta) o += b.v[j];
-          if (act == 1) o = gelu_obst(o);
-          v[i].v[j] = o;
+      for (int i = 0; i < MAXC; ++i) {
+        const int c = lane + 32 * i;
+        if (c < chunks && base + r < rows) {
+#pragma unroll
+          for (int j = 0; j < N; ++j) s[r] += v[r][i].v[j];
         }
-        v[i].store(yr + c * N);
+      }
+      s[r] = warp_sum(s[r]) * inv_w;  // mean
+    }
+    float q[ROWS];
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      q[r] = 0.f;
+#pragma unroll
+      for (int i = 0; i < MAXC; ++i) {
+        const int c = lane + 32 * i;
+        if (c < chunks && base + r < rows) {
+#pragma unroll
+          for (int j = 0; j < N; ++j) {
+            v[r][i].v[j] -= s[r];
+            q[r] += v[r][i].v[j] * v[r][i].v[j];
+          }
+        }
+      }
+      q[r] = rsqrtf(warp_sum(q[r]) * inv_w + GN_EPS);  // rstd
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      const int64_t row = base + r;
+      if (row >= rows) continue;
+      const int h = (int)(row % heads);
+      T* yr = y + row * width;
+#pragma unroll
+      for (int i = 0; i < MAXC; ++i) {
+        const int c = lane + 32 * i;
+        if (c < chunks) {
+          Vec16<T> g, b;
+          if (gamma) g.load(gamma + (int64_t)h * width + c * N);
+          if (beta) b.load(beta + (int64_t)h * width + c * N);
+#pragma unroll
+          for (int j = 0; j < N; ++j) {
+            float o = v[r][i].v[j] * q[r];
+            if (gamma) o *= g.v[j];
+            if (beta) o += b.v[j];
+            if (act == 1) o = gelu_obst(o);
+            v[r][i].v[j] = o;
+          }
+          v[r][i].store(yr + c * N);
+        }
       }
     }
   }
@@ -111,16 +137,42 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
 
   const int64_t t0 = (int64_t)blockIdx.x * tokens_per_block;
   const int64_t t1 = (t0 + tokens_per_block < tokens) ? t0 + tokens_per_block : tokens;
+  // register double-buffering: the next token's x / dy (/ dx when accumulating) are requested before this token's
+  // reductions start (narrow rows only: the wide ones already keep 8+ loads in flight per lane)
+  constexpr bool PREF = MAXC <= 2;
+  Vec16<T> xn[MAXC], gn[MAXC], on[MAXC];
+  auto load_row = [&](int64_t t, Vec16<T>* xv, Vec16<T>* gv, Vec16<T>* ov) {
+    const int64_t o = (t * heads + h) * width;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < chunks) {
+        xv[i].load(x + o + c * N);
+        gv[i].load(dy + o + c * N);
+        if (dx_acc) ov[i].load(dx + o + c * N);
+      }
+    }
+  };
+  if (PREF && t0 + warp < t1) load_row(t0 + warp, xn, gn, on);
   for (int64_t t = t0 + warp; t < t1; t += warps_per_block) {
     const int64_t off = (t * heads + h) * width;
-    Vec16<T> xv[MAXC], gv[MAXC];
+    Vec16<T> xv[MAXC], gv[MAXC], ov[MAXC];
+    if (PREF) {
+#pragma unroll
+      for (int i = 0; i < MAXC; ++i) {
+        xv[i] = xn[i];
+        gv[i] = gn[i];
+        ov[i] = on[i];
+      }
+      if (t + warps_per_block < t1) load_row(t + warps_per_block, xn, gn, on);
+    } else {
+      load_row(t, xv, gv, ov);
+    }
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       if (c < chunks) {
-        xv[i].load(x + off + c * N);
-        gv[i].load(dy + off + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) s += xv[i].v[j];
       }
@@ -166,14 +218,13 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
       const int c = lane + 32 * i;
       if (c < chunks) {
         Vec16<T> o;
-        if (dx_acc) o.load(dx + off + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
           const float xraw = xv[i].v[j];
           const float z = (xraw - mean) * rstd;
           float d = rstd * (gv[i].v[j] - mg - z * mgz);
           if (relu_mask && !(xraw > 0.f)) d = 0.f;
-          o.v[j] = dx_acc ? (o.v[j] + d) : d;
+          o.v[j] = dx_acc ? (ov[i].v[j] + d) : d;
         }
         o.store(dx + off + c * N);
       }
@@ -206,17 +257,18 @@ static int gn_fwd_launch(const void* x, const void* gamma, const void* beta, voi
   const int per_lane = (width / N + 31) / 32;
   OBST_REQUIRE(per_lane <= 8, "obst_gn_fwd: width %d too large (max %d)", width, 256 * N);
   const int wpb = 8;
-  int64_t blocks = (rows + wpb - 1) / wpb;
+  const int rpw = per_lane <= 2 ? 4 : (per_lane <= 4 ? 2 : 1);
+  int64_t blocks = (rows + (int64_t)wpb * rpw - 1) / ((int64_t)wpb * rpw);
   const int64_t cap = (int64_t)num_sms() * 8;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-#define OBST_GN_FWD(MC)                                                                                       \
-  gn_fwd_kernel<T, MC><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma, (const T*)beta, \
-                                                                (T*)y, rows, heads, width, act)
-  if (per_lane <= 1) OBST_GN_FWD(1);
-  else if (per_lane <= 2) OBST_GN_FWD(2);
-  else if (per_lane <= 4) OBST_GN_FWD(4);
-  else OBST_GN_FWD(8);
+#define OBST_GN_FWD(MC, R)                                                                                       \
+  gn_fwd_kernel<T, MC, R><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma, (const T*)beta, \
+                                                                   (T*)y, rows, heads, width, act)
+  if (per_lane <= 1) OBST_GN_FWD(1, 4);
+  else if (per_lane <= 2) OBST_GN_FWD(2, 4);
+  else if (per_lane <= 4) OBST_GN_FWD(4, 2);
+  else OBST_GN_FWD(8, 1);
 #undef OBST_GN_FWD
   count_launch();
   return check_launch("obst_gn_fwd");

@@ -26,7 +26,11 @@ static constexpr int B_STAGE_BYTES = 256 * BK * 2;       // 32 KB (BN <= 256)
 static constexpr int TMEM_COLS = 512;
 static constexpr int ACC_STRIDE = 256;                   // columns per accumulator buffer
 static constexpr int TC_THREADS = 192;
-static constexpr int SMEM_BAR_OFF = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
+static constexpr int EPI_BOX_ROWS = 32;                  // one epilogue warp's TMEM lane quarter
+static constexpr int EPI_BOX_COLS = 64;                  // 64 bf16 = 128 B = one swizzle row
+static constexpr int EPI_BUF_BYTES = EPI_BOX_ROWS * EPI_BOX_COLS * 2;  // 4 KB
+static constexpr int SMEM_EPI_OFF = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
+static constexpr int SMEM_BAR_OFF = SMEM_EPI_OFF + 4 * 2 * EPI_BUF_BYTES;  // 4 warps x 2 staging buffers
 static constexpr int SMEM_BYTES = SMEM_BAR_OFF + 256 + 1024;  // barriers + alignment slack
 
 struct TcParams {
@@ -38,6 +42,7 @@ struct TcParams {
   int32_t GLO, G;
   int32_t BN, tiles_m, tiles_n, total_tiles;
   int32_t splits, tri, epi, accumulate, out_f32;
+  int32_t tma_store;                   // bf16 output through smem staging + TMA store (and TMA load of R)
   int32_t a_mn, b_mn;                  // 1 = MN-major operand
   int32_t a_uglo, a_ughi, a_uko;       // does the operand depend on g_lo / g_hi / ko
   int32_t b_uglo, b_ughi, b_uko;
@@ -92,6 +97,21 @@ __device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* map, u
       "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
       : "memory");
 }
+
+__device__ __forceinline__ void tma_store_5d(const CUtensorMap* map, const void* src, int c0, int c1, int c2, int c3,
+                                             int c4) {
+  asm volatile("cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(map)),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -201,7 +221,8 @@ __device__ __forceinline__ void epi_apply(float (&v)[8], const float (&r)[8], in
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcParams p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR, const TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* smem_a = smem;
@@ -211,7 +232,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* empty_bar = bars + STAGES;       // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  uint64_t* rbar = bars + 2 * STAGES + 4;        // [4 warps][2 buffers] R-tile arrival
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 12);
+  uint8_t* smem_epi = smem + SMEM_EPI_OFF;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -227,6 +250,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_init(&tfull_bar[s], 1);
       mbar_init(&tempty_bar[s], 128);
     }
+    for (int s = 0; s < 8; ++s) mbar_init(&rbar[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc(tmem_ptr, TMEM_COLS);
@@ -324,6 +348,95 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int acc = 0;
     uint32_t acc_phase = 0;
     Tile t;
+    if (p.tma_store) {
+      // bf16 output: TMEM -> registers -> fused op -> swizzled smem slab (32 rows x 128 B) -> TMA store.
+      // R (residual / ReLU mask) arrives the same way (TMA load into the slab), so global traffic is full lines.
+      uint8_t* const buf0 = smem_epi + quarter * 2 * EPI_BUF_BYTES;
+      uint64_t* const rb0 = &rbar[quarter * 2];
+      uint32_t rphase = 0;  // bit b = phase of slab b's R barrier
+      uint32_t it = 0;
+      const int nchunks = (p.BN + EPI_BOX_COLS - 1) / EPI_BOX_COLS;
+      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
+        if (!get_tile(p, tile, t)) continue;
+        mbar_wait(&tfull_bar[acc], acc_phase, 3);
+        tcgen05_fence_after();
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
+        const int row0 = t.m0 + quarter * 32;
+        for (int c = 0; c < nchunks; ++c, ++it) {
+          const int b = it & 1;
+          uint8_t* const buf = buf0 + b * EPI_BUF_BYTES;
+          uint64_t* const rb = rb0 + b;
+          const int col0 = t.n0 + c * EPI_BOX_COLS;
+          const bool live = row0 < p.M && col0 < p.N;  // warp-uniform
+          if (lane == 0) bulk_wait_read<1>();          // the store that last used this slab has read it
+          __syncwarp();
+          if (p.epi >= 2 && live) {
+            if (lane == 0) {
+              mbar_expect_tx(rb, EPI_BUF_BYTES);
+              tma_load_5d(buf, &tmR, rb, col0, row0, t.glo, t.ghi, 0);
+            }
+          }
+          uint32_t r[64];
+          {
+            uint32_t (&ra)[32] = *reinterpret_cast<uint32_t (*)[32]>(&r[0]);
+            uint32_t (&rb2)[32] = *reinterpret_cast<uint32_t (*)[32]>(&r[32]);
+            tmem_ld32(taddr0 + (uint32_t)(c * EPI_BOX_COLS), ra);
+            tmem_ld32(taddr0 + (uint32_t)(c * EPI_BOX_COLS + 32), rb2);
+            tmem_ld_wait();
+          }
+          if (c == nchunks - 1) {
+            // accumulator fully read: hand it back to the MMA warp before the store work of this chunk
+            tcgen05_fence_before();
+            mbar_arrive(&tempty_bar[acc]);
+          }
+          if (!live) {
+            if (lane == 0) bulk_commit();  // empty group: keeps "one group per chunk" for wait_group.read 1
+            continue;
+          }
+          if (p.epi >= 2) {
+            mbar_wait(rb, (rphase >> b) & 1u, 4);
+            rphase ^= 1u << b;
+          }
+          uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4));
+            float v[8], rr[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              v[e] = __uint_as_float(r[j * 8 + e]);
+              rr[e] = 0.f;
+            }
+            if (p.epi >= 2) {
+              const uint4 ru = *slot;
+              const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z),
+                           f3 = unpack_bf16x2(ru.w);
+              rr[0] = f0.x; rr[1] = f0.y; rr[2] = f1.x; rr[3] = f1.y;
+              rr[4] = f2.x; rr[5] = f2.y; rr[6] = f3.x; rr[7] = f3.y;
+            }
+            epi_apply(v, rr, p.epi);
+            uint4 o;
+            o.x = pack_bf16x2(v[0], v[1]);
+            o.y = pack_bf16x2(v[2], v[3]);
+            o.z = pack_bf16x2(v[4], v[5]);
+            o.w = pack_bf16x2(v[6], v[7]);
+            *slot = o;
+          }
+          fence_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_5d(&tmD, buf, col0, row0, t.glo, t.ghi, 0);
+            bulk_commit();
+          }
+        }
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+      if (lane == 0) bulk_wait_all();
+      __syncwarp();
+    } else {
     for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
       if (!get_tile(p, tile, t)) continue;
       mbar_wait(&tfull_bar[acc], acc_phase, 3);
@@ -367,11 +480,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   red_add_v4(dp + 4, v[4], v[5], v[6], v[7]);
                 }
               } else {
-                if (p.tri == 3) {
-#pragma unroll
-                  for (int j = 0; j < 8; ++j)
-                    if (n + j > m) v[j] = 0.f;
-                }
                 *reinterpret_cast<float4*>(dp) = make_float4(v[0], v[1], v[2], v[3]);
                 *reinterpret_cast<float4*>(dp + 4) = make_float4(v[4], v[5], v[6], v[7]);
               }
@@ -385,11 +493,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 rr[4] = f2.x; rr[5] = f2.y; rr[6] = f3.x; rr[7] = f3.y;
               }
               epi_apply(v, rr, p.epi);
-              if (p.tri == 3) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                  if (n + j > m) v[j] = 0.f;
-              }
               uint4 o;
               o.x = pack_bf16x2(v[0], v[1]);
               o.y = pack_bf16x2(v[2], v[3]);
@@ -406,6 +509,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         acc = 0;
         acc_phase ^= 1;
       }
+    }
     }
   }
 
@@ -527,6 +631,63 @@ static int make_operand_map(const void* ptr, int64_t s_mn, int64_t s_k, int64_t 
   return OBST_OK;
 }
 
+// output / residual view: 5-D (n, m, g_lo, g_hi, 1), box = 64 columns x 32 rows (one epilogue warp's slab)
+static int make_out_map(const void* ptr, int N, int M, int GLO, int GHI, int64_t d_ld, int64_t d_glo, int64_t d_ghi,
+                        CUtensorMap* out, bool strict) {
+  MapKey key;
+  memset(&key, 0, sizeof(key));
+  key.ptr = ptr;
+  const uint64_t es = 2;
+  key.dims[0] = (uint64_t)N;
+  key.dims[1] = (uint64_t)M;
+  key.dims[2] = (GLO > 1) ? (uint64_t)GLO : 1;
+  key.dims[3] = (GHI > 1) ? (uint64_t)GHI : 1;
+  key.dims[4] = 1;
+  key.strides[0] = (uint64_t)d_ld * es;
+  key.strides[1] = key.dims[2] > 1 ? (uint64_t)d_glo * es : 16;
+  key.strides[2] = key.dims[3] > 1 ? (uint64_t)d_ghi * es : 16;
+  key.strides[3] = 16;
+  key.box[0] = EPI_BOX_COLS;
+  key.box[1] = EPI_BOX_ROWS;
+  if (key.dims[1] == 1 && (key.strides[0] % 16) != 0) key.strides[0] = 16;
+  for (int i = 0; i < 4; ++i)
+    if (key.strides[i] % 16 != 0 || key.strides[i] == 0) return OBST_ENOTSUP;
+  if ((reinterpret_cast<uintptr_t>(ptr) & 15) != 0) return OBST_ENOTSUP;
+  std::string skey(reinterpret_cast<const char*>(&key), sizeof(key));
+  skey.push_back('D');
+  {
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    auto it = g_map_cache.find(skey);
+    if (it != g_map_cache.end()) {
+      *out = it->second;
+      return OBST_OK;
+    }
+  }
+  PFN_tmapEncodeTiled enc = get_encode_fn();
+  if (!enc) {
+    set_error("obst_gemm(tc): cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+    return OBST_ECUDA;
+  }
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t box[5] = {key.box[0], key.box[1], 1, 1, 1}, estr[5] = {1, 1, 1, 1, 1};
+  for (int i = 0; i < 5; ++i) gdim[i] = key.dims[i];
+  for (int i = 0; i < 4; ++i) gstr[i] = key.strides[i];
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    if (strict) set_error("obst_gemm(tc): cuTensorMapEncodeTiled(output) failed (%d)", (int)r);
+    return OBST_ENOTSUP;
+  }
+  {
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    g_map_cache.emplace(skey, m);
+  }
+  *out = m;
+  return OBST_OK;
+}
+
 int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
 #define TC_NOTSUP(...)                  \
   do {                                  \
@@ -603,6 +764,17 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
                         strict);
   if (rc != OBST_OK) return rc;
 
+  CUtensorMap tmD = tmA, tmR = tmA;  // placeholders when the direct-store epilogue is used
+  p.tma_store = 0;
+  if (!out_f32 && !g.accumulate) {
+    int rd = make_out_map(g.D, g.N, g.M, g.GLO, g.GHI, g.d_ld, g.d_glo, g.d_ghi, &tmD, strict);
+    int rr = OBST_OK;
+    if (rd == OBST_OK && g.epi >= 2)
+      rr = make_out_map(g.R, g.N, g.M, g.GLO, g.GHI, g.d_ld, g.d_glo, g.d_ghi, &tmR, strict);
+    if (rd == OBST_ECUDA || rr == OBST_ECUDA) return OBST_ECUDA;
+    p.tma_store = (rd == OBST_OK && rr == OBST_OK) ? 1 : 0;
+  }
+
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
@@ -614,7 +786,7 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   }
   int grid = num_sms();
   if (grid > p.total_tiles) grid = p.total_tiles;
-  gemm_tc_kernel<<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmA, tmB, p);
+  gemm_tc_kernel<<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmA, tmB, tmD, tmR, p);
   count_launch();
   return check_launch("obst_gemm(tc)");
 }

@@ -249,14 +249,20 @@ def gelu_grad(x):
 def mix_fwd(m_tril, x):
     """attention() with biased_attention_map + input_as_value: out[b,s,h,k] = sum_t M[h,s,t] tril[s,t] x[b,t,h,k]
     (src/model/spatial.py:19-23,73,77,81; mask = greater_equal(range(seq), range(_seq)), src/utils_mtf.py:411-415)."""
-    # [h,s,t] @ [b,h,t,k] -> [b,h,s,k]
-    return np.matmul(m_tril[None], x.transpose(0, 2, 1, 3)).transpose(0, 2, 1, 3)
+    # [h,s,t] @ [b,h,t,k] -> [b,h,s,k]   (contiguous copies so that BLAS takes the batched product)
+    xt = np.ascontiguousarray(x.transpose(0, 2, 1, 3))
+    return np.ascontiguousarray(np.matmul(m_tril[None], xt).transpose(0, 2, 1, 3))
 
 
 def mix_bwd(m_tril, x, do):
-    dx = np.matmul(m_tril.transpose(0, 2, 1)[None], do.transpose(0, 2, 1, 3)).transpose(0, 2, 1, 3)
-    # dM[h,s,t] = tril * sum_{b,k} do[b,s,h,k] x[b,t,h,k]
-    dm = np.einsum("bhsk,bhtk->hst", do.transpose(0, 2, 1, 3), x.transpose(0, 2, 1, 3), optimize=True)
+    dot = np.ascontiguousarray(do.transpose(0, 2, 1, 3))  # [b,h,s,k]
+    mt = np.ascontiguousarray(m_tril.transpose(0, 2, 1))
+    dx = np.ascontiguousarray(np.matmul(mt[None], dot).transpose(0, 2, 1, 3))
+    # dM[h,s,t] = tril * sum_{b,k} do[b,s,h,k] x[b,t,h,k]:  per head [s, b*k] @ [b*k, t]
+    B, S, H, K = x.shape
+    a = np.ascontiguousarray(do.transpose(2, 1, 0, 3)).reshape(H, S, B * K)
+    b = np.ascontiguousarray(x.transpose(2, 0, 3, 1)).reshape(H, B * K, S)
+    dm = np.matmul(a, b)
     return dx, np.tril(dm)
 
 
@@ -282,7 +288,8 @@ class Block0:
         h2 = rnd(np.maximum(h1 @ wmid.reshape(I, H * K2), 0)).reshape(B, S, H, K2)  # mid: relu
         n, cm = gn_fwd(h2, p[f"gm_{i}"], p[f"bm_{i}"])  # mid: norm-shift-scale (group width K2)
         n = rnd(n)
-        f = np.einsum("bshj,hjk->bshk", n, wout, optimize=True)  # out: grouped, no activation
+        nh = np.ascontiguousarray(n.transpose(2, 0, 1, 3)).reshape(H, B * S, K2)
+        f = np.ascontiguousarray(np.matmul(nh, wout).reshape(H, B, S, -1).transpose(1, 2, 0, 3))  # out: grouped
         cache = (a2, c0, h1, h2, n, cm) if keep else None
         return f, cache
 
@@ -296,8 +303,11 @@ class Block0:
         I = win.shape[-1]
         K = wout.shape[-1]
         g = {}
-        g[f"wout_{i}"] = np.einsum("bshj,bshk->hjk", n, df, optimize=True)
-        dn = rnd(np.einsum("bshk,hjk->bshj", df, wout, optimize=True))
+        nh = np.ascontiguousarray(n.transpose(2, 3, 0, 1)).reshape(H, K2, B * S)
+        dfh = np.ascontiguousarray(df.transpose(2, 0, 1, 3)).reshape(H, B * S, K)
+        g[f"wout_{i}"] = np.matmul(nh, dfh)
+        dn = np.matmul(dfh, np.ascontiguousarray(wout.transpose(0, 2, 1))).reshape(H, B, S, K2)
+        dn = rnd(np.ascontiguousarray(dn.transpose(1, 2, 0, 3)))
         dh2, g[f"gm_{i}"], g[f"bm_{i}"] = gn_bwd(dn, cm, p[f"gm_{i}"])
         dh2 = rnd(dh2 * (h2 > 0)).reshape(B * S, H * K2)
         g[f"wmid_{i}"] = (h1.T @ dh2).reshape(I, H, K2)
