@@ -139,7 +139,7 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
   const int64_t t1 = (t0 + tokens_per_block < tokens) ? t0 + tokens_per_block : tokens;
   // register double-buffering: the next token's x / dy (/ dx when accumulating) are requested before this token's
   // reductions start (narrow rows only: the wide ones already keep 8+ loads in flight per lane)
-  constexpr bool PREF = MAXC <= 2;
+  constexpr bool PREF = false;  // measured: the extra registers cost more occupancy than the prefetch buys
   Vec16<T> xn[MAXC], gn[MAXC], on[MAXC];
   auto load_row = [&](int64_t t, Vec16<T>* xv, Vec16<T>* gv, Vec16<T>* ov) {
     const int64_t o = (t * heads + h) * width;
@@ -257,7 +257,7 @@ static int gn_fwd_launch(const void* x, const void* gamma, const void* beta, voi
   const int per_lane = (width / N + 31) / 32;
   OBST_REQUIRE(per_lane <= 8, "obst_gn_fwd: width %d too large (max %d)", width, 256 * N);
   const int wpb = 8;
-  const int rpw = per_lane <= 2 ? 4 : (per_lane <= 4 ? 2 : 1);
+  const int rpw = 1;  // measured on B200: 1 row/warp at 64 warps/SM (4.0 TB/s) beats 4 rows/warp at 16 warps/SM (3.2)
   int64_t blocks = (rows + (int64_t)wpb * rpw - 1) / ((int64_t)wpb * rpw);
   const int64_t cap = (int64_t)num_sms() * 8;
   if (blocks > cap) blocks = cap;
@@ -265,9 +265,9 @@ static int gn_fwd_launch(const void* x, const void* gamma, const void* beta, voi
 #define OBST_GN_FWD(MC, R)                                                                                       \
   gn_fwd_kernel<T, MC, R><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma, (const T*)beta, \
                                                                    (T*)y, rows, heads, width, act)
-  if (per_lane <= 1) OBST_GN_FWD(1, 4);
-  else if (per_lane <= 2) OBST_GN_FWD(2, 4);
-  else if (per_lane <= 4) OBST_GN_FWD(4, 2);
+  if (per_lane <= 1) OBST_GN_FWD(1, 1);
+  else if (per_lane <= 2) OBST_GN_FWD(2, 1);
+  else if (per_lane <= 4) OBST_GN_FWD(4, 1);
   else OBST_GN_FWD(8, 1);
 #undef OBST_GN_FWD
   count_launch();

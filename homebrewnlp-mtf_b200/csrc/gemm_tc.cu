@@ -9,6 +9,7 @@
 // majorness), so forward, dgrad and wgrad all read the tensors where they lie: no transposes.
 // Triangular modes skip whole k-blocks / output tiles of the causal token-mixing matrices.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <mutex>
 #include <string>
@@ -20,18 +21,13 @@ namespace obst {
 
 static constexpr int BM = 128;
 static constexpr int BK = 64;
-static constexpr int STAGES = 4;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;        // 16 KB
-static constexpr int B_STAGE_BYTES = 256 * BK * 2;       // 32 KB (BN <= 256)
 static constexpr int TMEM_COLS = 512;
 static constexpr int ACC_STRIDE = 256;                   // columns per accumulator buffer
 static constexpr int TC_THREADS = 192;
 static constexpr int EPI_BOX_ROWS = 32;                  // one epilogue warp's TMEM lane quarter
 static constexpr int EPI_BOX_COLS = 64;                  // 64 bf16 = 128 B = one swizzle row
 static constexpr int EPI_BUF_BYTES = EPI_BOX_ROWS * EPI_BOX_COLS * 2;  // 4 KB
-static constexpr int SMEM_EPI_OFF = STAGES * (A_STAGE_BYTES + B_STAGE_BYTES);
-static constexpr int SMEM_BAR_OFF = SMEM_EPI_OFF + 4 * 2 * EPI_BUF_BYTES;  // 4 warps x 2 staging buffers
-static constexpr int SMEM_BYTES = SMEM_BAR_OFF + 256 + 1024;  // barriers + alignment slack
 
 struct TcParams {
   void* D;
@@ -89,13 +85,47 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, int wh
   }
 }
 
+// CG == 2: executed by both CTAs of a pair; the transaction bytes are credited to the LEADER CTA's barrier
+// (same offset, CTA-rank bit cleared), which is the one the MMA thread waits on.
+template <int CG>
 __device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2,
                                             int c3, int c4) {
-  asm volatile(
-      "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], "
-      "[%2];" ::"r"(smem_u32(dst)),
-      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
-      : "memory");
+  if (CG == 2) {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, "
+        "%5, %6, %7}], [%2];" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2), "r"(c3),
+        "r"(c4)
+        : "memory");
+  } else {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, %7}], "
+        "[%2];" ::"r"(smem_u32(dst)),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+  }
+}
+
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+// arrive on the barrier at the same offset in CTA `target` of the cluster (CG == 1: the local barrier)
+template <int CG>
+__device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t target) {
+  if (CG == 2) {
+    asm volatile(
+        "{\n"
+        ".reg .b32 remote;\n"
+        "mapa.shared::cluster.u32 remote, %0, %1;\n"
+        "mbarrier.arrive.shared::cluster.b64 _, [remote];\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(target)
+        : "memory");
+  } else {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+  }
 }
 
 __device__ __forceinline__ void tma_store_5d(const CUtensorMap* map, const void* src, int c0, int c1, int c2, int c3,
@@ -116,32 +146,66 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
+template <int CG>
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
-               "r"(ncols)
-               : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  if (CG == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+                 "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  } else {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)),
+                 "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
 }
+template <int CG>
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+  if (CG == 2)
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+  else
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
 
 // D[tmem] (+)= A[smem] * B[smem], bf16 inputs, fp32 accumulate
+template <int CG>
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                           uint32_t accumulate) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-      "}\n" ::"r"(tmem_d),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-      : "memory");
+  if (CG == 2) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
 }
 // mbarrier arrive once all previously issued tcgen05 ops of this thread have completed
+// (CG == 2: the arrive is multicast to the barrier at the same offset in BOTH CTAs of the pair)
+template <int CG>
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-               : "memory");
+  if (CG == 2) {
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+            smem_u32(bar)),
+        "h"((uint16_t)3)
+        : "memory");
+  } else {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+  }
 }
 
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
@@ -178,20 +242,23 @@ struct Tile {
   int m0, n0, glo, ghi, kb0, kb1;
 };
 
+// CG = CTAs per tile (1, or 2 = a CTA pair sharing one 256-row tile through tcgen05 cta_group::2)
+template <int CG>
 __device__ __forceinline__ bool get_tile(const TcParams& p, int tile, Tile& t) {
+  constexpr int TM = BM * CG;
   const int nt = tile % p.tiles_n;
   int r = tile / p.tiles_n;
   const int mt = r % p.tiles_m;
   r /= p.tiles_m;
   const int g = r % p.G;
   const int sp = r / p.G;
-  t.m0 = mt * BM;
+  t.m0 = mt * TM;
   t.n0 = nt * p.BN;
   t.glo = g % p.GLO;
   t.ghi = g / p.GLO;
-  if (p.tri == 3 && t.n0 > t.m0 + BM - 1) return false;
+  if (p.tri == 3 && t.n0 > t.m0 + TM - 1) return false;
   int kb0 = 0, kb1 = p.nkb;
-  if (p.tri == 1) kb1 = min(p.nkb, (t.m0 + BM + BK - 1) / BK);
+  if (p.tri == 1) kb1 = min(p.nkb, (t.m0 + TM + BK - 1) / BK);
   if (p.tri == 2) kb0 = t.m0 / BK;
   if (p.splits > 1) {
     const int len = kb1 - kb0;
@@ -220,24 +287,41 @@ __device__ __forceinline__ void epi_apply(float (&v)[8], const float (&r)[8], in
   }
 }
 
+template <int CG>
+struct Cfg {
+  static constexpr int STAGES = CG == 2 ? 6 : 4;
+  static constexpr int B_STAGE = 256 / CG * BK * 2;  // bytes of this CTA's share of the B tile
+  static constexpr int EPI_OFF = STAGES * (A_STAGE_BYTES + B_STAGE);
+  static constexpr int BAR_OFF = EPI_OFF + 4 * 2 * EPI_BUF_BYTES;
+  static constexpr int SMEM = BAR_OFF + 256 + 1024;
+};
+
+template <int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR, const TcParams p) {
+  constexpr int STAGES = Cfg<CG>::STAGES;
+  constexpr int B_STAGE = Cfg<CG>::B_STAGE;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + STAGES * A_STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM_BAR_OFF);
-  uint64_t* full_bar = bars;                 // [STAGES]
-  uint64_t* empty_bar = bars + STAGES;       // [STAGES]
-  uint64_t* tfull_bar = bars + 2 * STAGES;   // [2]
-  uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]
+  uint8_t* smem_epi = smem + Cfg<CG>::EPI_OFF;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg<CG>::BAR_OFF);
+  uint64_t* full_bar = bars;                     // [STAGES]  (CG==2: only the leader's are waited on)
+  uint64_t* empty_bar = bars + STAGES;           // [STAGES]
+  uint64_t* tfull_bar = bars + 2 * STAGES;       // [2]
+  uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]       (CG==2: only the leader's are used)
   uint64_t* rbar = bars + 2 * STAGES + 4;        // [4 warps][2 buffers] R-tile arrival
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 12);
-  uint8_t* smem_epi = smem + SMEM_EPI_OFF;
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  uint32_t rank = 0;
+  if (CG == 2) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const bool leader = rank == 0;
+  const int cluster_id = blockIdx.x / CG;
+  const int num_clusters = gridDim.x / CG;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
@@ -248,18 +332,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 128);
+      mbar_init(&tempty_bar[s], 128 * CG);
     }
     for (int s = 0; s < 8; ++s) mbar_init(&rbar[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) tmem_alloc(tmem_ptr, TMEM_COLS);
+  if (warp == 1) tmem_alloc<CG>(tmem_ptr, TMEM_COLS);
   tcgen05_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync();
+  else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
-  const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + p.BN * BK * 2);
+  const int bn_cta = p.BN / CG;  // B rows (N) this CTA stages
+  const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + bn_cta * BK * 2) * CG;  // what the (leader's) barrier sees
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -267,30 +353,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       Tile t;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        if (!get_tile(p, tile, t)) continue;
+      for (int tile = cluster_id; tile < p.total_tiles; tile += num_clusters) {
+        if (!get_tile<CG>(p, tile, t)) continue;
         const int a2 = p.a_uglo ? t.glo : 0, a3 = p.a_ughi ? t.ghi : 0;
         const int b2 = p.b_uglo ? t.glo : 0, b3 = p.b_ughi ? t.ghi : 0;
+        const int am0 = t.m0 + (int)rank * BM;
+        const int bn0 = t.n0 + (int)rank * bn_cta;
         for (int kb = t.kb0; kb < t.kb1; ++kb) {
           const int ki = kb % p.nkb_inner, ko = kb / p.nkb_inner;
           const int k0 = ki * BK;
           mbar_wait(&empty_bar[stage], phase ^ 1, 0);
-          mbar_expect_tx(&full_bar[stage], stage_bytes);
+          if (leader) mbar_expect_tx(&full_bar[stage], stage_bytes);
           uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
-          uint8_t* sb = smem_b + stage * B_STAGE_BYTES;
+          uint8_t* sb = smem_b + stage * B_STAGE;
           const int a4 = p.a_uko ? ko : 0, b4 = p.b_uko ? ko : 0;
           if (!p.a_mn) {
-            tma_load_5d(sa, &tmA, &full_bar[stage], k0, t.m0, a2, a3, a4);
+            tma_load_5d<CG>(sa, &tmA, &full_bar[stage], k0, am0, a2, a3, a4);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              tma_load_5d(sa + j * (64 * BK * 2), &tmA, &full_bar[stage], t.m0 + 64 * j, k0, a2, a3, a4);
+              tma_load_5d<CG>(sa + j * (64 * BK * 2), &tmA, &full_bar[stage], am0 + 64 * j, k0, a2, a3, a4);
           }
           if (!p.b_mn) {
-            tma_load_5d(sb, &tmB, &full_bar[stage], k0, t.n0, b2, b3, b4);
+            tma_load_5d<CG>(sb, &tmB, &full_bar[stage], k0, bn0, b2, b3, b4);
           } else {
-            for (int j = 0; j < p.BN / 64; ++j)
-              tma_load_5d(sb + j * (64 * BK * 2), &tmB, &full_bar[stage], t.n0 + 64 * j, k0, b2, b3, b4);
+            for (int j = 0; j < bn_cta / 64; ++j)
+              tma_load_5d<CG>(sb + j * (64 * BK * 2), &tmB, &full_bar[stage], bn0 + 64 * j, k0, b2, b3, b4);
           }
           if (++stage == STAGES) {
             stage = 0;
@@ -300,10 +388,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one thread) =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (one thread of the leader CTA) =====================
+    if (lane == 0 && leader) {
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
-                             ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+                             ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)((BM * CG) >> 4) << 24);
       // K-major: 8-row groups 1024 B apart (SBO), 32 B per UMMA_K step.
       // MN-major: 64-element MN groups 8192 B apart (LBO), 8-row k groups 1024 B apart (SBO), 2048 B per UMMA_K.
       const uint32_t a_lbo = p.a_mn ? 64 * BK * 2 : 16, b_lbo = p.b_mn ? 64 * BK * 2 : 16;
@@ -313,8 +401,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int acc = 0;
       uint32_t acc_phase = 0;
       Tile t;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        if (!get_tile(p, tile, t)) continue;
+      for (int tile = cluster_id; tile < p.total_tiles; tile += num_clusters) {
+        if (!get_tile<CG>(p, tile, t)) continue;
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1, 1);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)(acc * ACC_STRIDE);
@@ -322,20 +410,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           mbar_wait(&full_bar[stage], phase, 2);
           tcgen05_fence_after();
           const uint32_t sa = smem_u32(smem_a + stage * A_STAGE_BYTES);
-          const uint32_t sb = smem_u32(smem_b + stage * B_STAGE_BYTES);
+          const uint32_t sb = smem_u32(smem_b + stage * B_STAGE);
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             const uint64_t adesc = make_smem_desc(sa + k * a_kadv, a_lbo, 1024);
             const uint64_t bdesc = make_smem_desc(sb + k * b_kadv, b_lbo, 1024);
-            umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > t.kb0 || k > 0) ? 1u : 0u);
+            umma_bf16<CG>(tmem_d, adesc, bdesc, idesc, (kb > t.kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);  // frees the smem slot when these MMAs retire
+          umma_commit<CG>(&empty_bar[stage]);  // frees the smem slot (in both CTAs) when these MMAs retire
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
           }
         }
-        umma_commit(&tfull_bar[acc]);  // accumulator ready for the epilogue
+        umma_commit<CG>(&tfull_bar[acc]);  // accumulator ready for the epilogue warps (of both CTAs)
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -348,6 +436,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int acc = 0;
     uint32_t acc_phase = 0;
     Tile t;
+    const int cta_m = (int)rank * BM;
     if (p.tma_store) {
       // bf16 output: TMEM -> registers -> fused op -> swizzled smem slab (32 rows x 128 B) -> TMA store.
       // R (residual / ReLU mask) arrives the same way (TMA load into the slab), so global traffic is full lines.
@@ -356,12 +445,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t rphase = 0;  // bit b = phase of slab b's R barrier
       uint32_t it = 0;
       const int nchunks = (p.BN + EPI_BOX_COLS - 1) / EPI_BOX_COLS;
-      for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-        if (!get_tile(p, tile, t)) continue;
+      for (int tile = cluster_id; tile < p.total_tiles; tile += num_clusters) {
+        if (!get_tile<CG>(p, tile, t)) continue;
         mbar_wait(&tfull_bar[acc], acc_phase, 3);
         tcgen05_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
-        const int row0 = t.m0 + quarter * 32;
+        const int row0 = t.m0 + cta_m + quarter * 32;
         for (int c = 0; c < nchunks; ++c, ++it) {
           const int b = it & 1;
           uint8_t* const buf = buf0 + b * EPI_BUF_BYTES;
@@ -373,7 +462,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (p.epi >= 2 && live) {
             if (lane == 0) {
               mbar_expect_tx(rb, EPI_BUF_BYTES);
-              tma_load_5d(buf, &tmR, rb, col0, row0, t.glo, t.ghi, 0);
+              tma_load_5d<1>(buf, &tmR, rb, col0, row0, t.glo, t.ghi, 0);
             }
           }
           uint32_t r[64];
@@ -387,7 +476,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (c == nchunks - 1) {
             // accumulator fully read: hand it back to the MMA warp before the store work of this chunk
             tcgen05_fence_before();
-            mbar_arrive(&tempty_bar[acc]);
+            mbar_arrive_cta<CG>(&tempty_bar[acc], 0);
           }
           if (!live) {
             if (lane == 0) bulk_commit();  // empty group: keeps "one group per chunk" for wait_group.read 1
@@ -437,88 +526,91 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (lane == 0) bulk_wait_all();
       __syncwarp();
     } else {
-    for (int tile = blockIdx.x; tile < p.total_tiles; tile += gridDim.x) {
-      if (!get_tile(p, tile, t)) continue;
-      mbar_wait(&tfull_bar[acc], acc_phase, 3);
-      tcgen05_fence_after();
-      const int m = t.m0 + quarter * 32 + lane;
-      const bool row_ok = m < p.M;
-      const int64_t row_off = (int64_t)t.glo * p.d_glo + (int64_t)t.ghi * p.d_ghi + (int64_t)m * p.d_ld;
-      const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
-      for (int c = 0; c < p.BN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(taddr0 + (uint32_t)(c * 32), r);
-        tmem_ld_wait();
-        if (row_ok) {
+      // fp32 output (plain store or split-K / cross-depth accumulation with red.global.add)
+      for (int tile = cluster_id; tile < p.total_tiles; tile += num_clusters) {
+        if (!get_tile<CG>(p, tile, t)) continue;
+        mbar_wait(&tfull_bar[acc], acc_phase, 3);
+        tcgen05_fence_after();
+        const int m = t.m0 + cta_m + quarter * 32 + lane;
+        const bool row_ok = m < p.M;
+        const int64_t row_off = (int64_t)t.glo * p.d_glo + (int64_t)t.ghi * p.d_ghi + (int64_t)m * p.d_ld;
+        const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
+        for (int c = 0; c < p.BN / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld32(taddr0 + (uint32_t)(c * 32), r);
+          tmem_ld_wait();
+          if (row_ok) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int n = t.n0 + c * 32 + q * 8;
-            if (n >= p.N) continue;
-            float v[8], rr[8];
+            for (int q = 0; q < 4; ++q) {
+              const int n = t.n0 + c * 32 + q * 8;
+              if (n >= p.N) continue;
+              float v[8], rr[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              v[j] = __uint_as_float(r[q * 8 + j]);
-              rr[j] = 0.f;
-            }
-            if (p.out_f32) {
-              float* dp = reinterpret_cast<float*>(p.D) + row_off + n;
-              if (p.epi >= 2) {
-                const float4 r0 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.R) + row_off + n);
-                const float4 r1 =
-                    *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.R) + row_off + n + 4);
-                rr[0] = r0.x; rr[1] = r0.y; rr[2] = r0.z; rr[3] = r0.w;
-                rr[4] = r1.x; rr[5] = r1.y; rr[6] = r1.z; rr[7] = r1.w;
+              for (int j = 0; j < 8; ++j) {
+                v[j] = __uint_as_float(r[q * 8 + j]);
+                rr[j] = 0.f;
               }
-              epi_apply(v, rr, p.epi);
-              if (p.accumulate) {
-                if (p.tri == 3 && n + 7 > m) {
+              if (p.out_f32) {
+                float* dp = reinterpret_cast<float*>(p.D) + row_off + n;
+                if (p.epi >= 2) {
+                  const float4 r0 =
+                      *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.R) + row_off + n);
+                  const float4 r1 =
+                      *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.R) + row_off + n + 4);
+                  rr[0] = r0.x; rr[1] = r0.y; rr[2] = r0.z; rr[3] = r0.w;
+                  rr[4] = r1.x; rr[5] = r1.y; rr[6] = r1.z; rr[7] = r1.w;
+                }
+                epi_apply(v, rr, p.epi);
+                if (p.accumulate) {
+                  if (p.tri == 3 && n + 7 > m) {
 #pragma unroll
-                  for (int j = 0; j < 8; ++j)
-                    if (n + j <= m) atomicAdd(dp + j, v[j]);
+                    for (int j = 0; j < 8; ++j)
+                      if (n + j <= m) atomicAdd(dp + j, v[j]);
+                  } else {
+                    red_add_v4(dp, v[0], v[1], v[2], v[3]);
+                    red_add_v4(dp + 4, v[4], v[5], v[6], v[7]);
+                  }
                 } else {
-                  red_add_v4(dp, v[0], v[1], v[2], v[3]);
-                  red_add_v4(dp + 4, v[4], v[5], v[6], v[7]);
+                  *reinterpret_cast<float4*>(dp) = make_float4(v[0], v[1], v[2], v[3]);
+                  *reinterpret_cast<float4*>(dp + 4) = make_float4(v[4], v[5], v[6], v[7]);
                 }
               } else {
-                *reinterpret_cast<float4*>(dp) = make_float4(v[0], v[1], v[2], v[3]);
-                *reinterpret_cast<float4*>(dp + 4) = make_float4(v[4], v[5], v[6], v[7]);
+                bf16* dp = reinterpret_cast<bf16*>(p.D) + row_off + n;
+                if (p.epi >= 2) {
+                  const uint4 ru = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.R) + row_off + n);
+                  const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z),
+                               f3 = unpack_bf16x2(ru.w);
+                  rr[0] = f0.x; rr[1] = f0.y; rr[2] = f1.x; rr[3] = f1.y;
+                  rr[4] = f2.x; rr[5] = f2.y; rr[6] = f3.x; rr[7] = f3.y;
+                }
+                epi_apply(v, rr, p.epi);
+                uint4 o;
+                o.x = pack_bf16x2(v[0], v[1]);
+                o.y = pack_bf16x2(v[2], v[3]);
+                o.z = pack_bf16x2(v[4], v[5]);
+                o.w = pack_bf16x2(v[6], v[7]);
+                *reinterpret_cast<uint4*>(dp) = o;
               }
-            } else {
-              bf16* dp = reinterpret_cast<bf16*>(p.D) + row_off + n;
-              if (p.epi >= 2) {
-                const uint4 ru = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.R) + row_off + n);
-                const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z),
-                             f3 = unpack_bf16x2(ru.w);
-                rr[0] = f0.x; rr[1] = f0.y; rr[2] = f1.x; rr[3] = f1.y;
-                rr[4] = f2.x; rr[5] = f2.y; rr[6] = f3.x; rr[7] = f3.y;
-              }
-              epi_apply(v, rr, p.epi);
-              uint4 o;
-              o.x = pack_bf16x2(v[0], v[1]);
-              o.y = pack_bf16x2(v[2], v[3]);
-              o.z = pack_bf16x2(v[4], v[5]);
-              o.w = pack_bf16x2(v[6], v[7]);
-              *reinterpret_cast<uint4*>(dp) = o;
             }
           }
         }
+        tcgen05_fence_before();
+        mbar_arrive_cta<CG>(&tempty_bar[acc], 0);  // 128*CG arrivals release the accumulator to the MMA warp
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
       }
-      tcgen05_fence_before();
-      mbar_arrive(&tempty_bar[acc]);  // 128 arrivals release the accumulator back to the MMA warp
-      if (++acc == 2) {
-        acc = 0;
-        acc_phase ^= 1;
-      }
-    }
     }
   }
 
   tcgen05_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync();  // the peer's smem / barriers / TMEM must outlive every remote access
+  else __syncthreads();
   if (warp == 1) {
     __syncwarp();
     tcgen05_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    tmem_dealloc<CG>(tmem_base, TMEM_COLS);
   }
 }
 
@@ -723,7 +815,16 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   p.GLO = g.GLO;
   p.G = g.GLO * g.GHI;
   p.BN = g.N > 128 ? 256 : (g.N > 64 ? 128 : 64);
-  p.tiles_m = (g.M + BM - 1) / BM;
+  // CTA pairs (tcgen05 cta_group::2): one 256-row tile per pair, each CTA stages half of B, so every byte of B
+  // crosses L2->SM once per 256 rows instead of once per 128 (the 1-CTA kernel is L2-bandwidth-bound at
+  // 128x256 tiles).  Needs >= 64 B rows per CTA and more than one 128-row tile of M.
+  static const int force_cg = [] {
+    const char* e = getenv("OBST_GEMM_CTA_GROUP");
+    return e ? atoi(e) : 0;
+  }();
+  int cg = (p.BN >= 128 && g.M > BM) ? 2 : 1;
+  if (force_cg == 1) cg = 1;
+  p.tiles_m = (g.M + BM * cg - 1) / (BM * cg);
   p.tiles_n = (g.N + p.BN - 1) / p.BN;
   p.tri = g.tri;
   p.epi = g.epi;
@@ -760,8 +861,8 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   int rc = make_operand_map(g.A, g.a_mn, g.a_k, g.a_ko, g.a_glo, g.a_ghi, g.M, g.KI, g.KO, g.GLO, g.GHI, a_mn, BM, &tmA,
                             strict);
   if (rc != OBST_OK) return rc;
-  rc = make_operand_map(g.B, g.b_mn, g.b_k, g.b_ko, g.b_glo, g.b_ghi, g.N, g.KI, g.KO, g.GLO, g.GHI, b_mn, p.BN, &tmB,
-                        strict);
+  rc = make_operand_map(g.B, g.b_mn, g.b_k, g.b_ko, g.b_glo, g.b_ghi, g.N, g.KI, g.KO, g.GLO, g.GHI, b_mn, p.BN / cg,
+                        &tmB, strict);
   if (rc != OBST_OK) return rc;
 
   CUtensorMap tmD = tmA, tmR = tmA;  // placeholders when the direct-store epilogue is used
@@ -777,16 +878,42 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
 
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         Cfg<1>::SMEM);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM);
     if (e != cudaSuccess) {
-      set_error("obst_gemm(tc): cannot opt in to %d B of shared memory: %s", SMEM_BYTES, cudaGetErrorString(e));
+      set_error("obst_gemm(tc): cannot opt in to %d B of shared memory: %s", Cfg<2>::SMEM, cudaGetErrorString(e));
       return OBST_ECUDA;
     }
     attr_set = true;
   }
-  int grid = num_sms();
-  if (grid > p.total_tiles) grid = p.total_tiles;
-  gemm_tc_kernel<<<grid, TC_THREADS, SMEM_BYTES, st>>>(tmA, tmB, tmD, tmR, p);
+  if (cg == 2) {
+    int clusters = num_sms() / 2;
+    if (clusters > p.total_tiles) clusters = p.total_tiles;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)(2 * clusters));
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = Cfg<2>::SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2>, tmA, tmB, tmD, tmR, p);
+    if (e != cudaSuccess) {
+      set_error("obst_gemm(tc): cluster launch failed: %s", cudaGetErrorString(e));
+      return OBST_ECUDA;
+    }
+  } else {
+    int grid = num_sms();
+    if (grid > p.total_tiles) grid = p.total_tiles;
+    gemm_tc_kernel<1><<<grid, TC_THREADS, Cfg<1>::SMEM, st>>>(tmA, tmB, tmD, tmR, p);
+  }
   count_launch();
   return check_launch("obst_gemm(tc)");
 }
