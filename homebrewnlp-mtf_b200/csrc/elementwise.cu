@@ -100,81 +100,95 @@ __global__ void __launch_bounds__(256) gn_fwd_kernel(const T* __restrict__ x, co
 // group norm backward.  grid = (token chunks, heads); a warp walks tokens of ONE head so the
 // dgamma/dbeta partials stay in registers; block-level reduce in shared memory, then fp32 atomics.
 // ================================================================================================
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+               "l"(gmem_src)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+// Each warp streams its rows through a private 2-stage shared-memory ring with cp.async (no register staging): the
+// next row's x / dy (/ dx) are in flight while the current row is reduced, and the only long-lived registers are
+// the dgamma/dbeta partials -- occupancy AND memory-level parallelism stay high.
 template <typename T, int MAXC>
 __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                       const T* __restrict__ gamma, const T* __restrict__ beta,
                                                       T* __restrict__ dx, float* __restrict__ dgamma,
                                                       float* __restrict__ dbeta, int64_t tokens, int heads, int width,
                                                       int tokens_per_block, int act, int relu_mask, int dx_acc) {
-  constexpr int N = Vec16<T>::N;
-  extern __shared__ float s_red[];  // [2][width]
+  constexpr int N = Raw16<T>::N;
+  extern __shared__ __align__(16) uint8_t s_raw[];
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
   const int warps_per_block = blockDim.x >> 5;
   const int chunks = width / N;
   const int h = blockIdx.y;
   const float inv_w = 1.0f / (float)width;
+  const int rowb = width * (int)sizeof(T);
+  // layout: [2*width floats: block reduction][gamma row][beta row][per warp: 2 stages x (x, dy, dx) rows]
+  float* s_red = reinterpret_cast<float*>(s_raw);
+  T* s_gam = reinterpret_cast<T*>(s_raw + 2 * width * sizeof(float));
+  T* s_bet = s_gam + width;
+  uint8_t* s_ring = reinterpret_cast<uint8_t*>(s_bet + width) + (size_t)warp * 6 * rowb;
   for (int i = threadIdx.x; i < 2 * width; i += blockDim.x) s_red[i] = 0.f;
+  for (int i = threadIdx.x; i < width; i += blockDim.x) {
+    s_gam[i] = gamma ? gamma[(int64_t)h * width + i] : from_f32<T>(1.f);
+    s_bet[i] = beta ? beta[(int64_t)h * width + i] : from_f32<T>(0.f);
+  }
   __syncthreads();
 
   float pg[MAXC][N], pb[MAXC][N];
-  Vec16<T> gam[MAXC], bet[MAXC];
 #pragma unroll
-  for (int i = 0; i < MAXC; ++i) {
-    const int c = lane + 32 * i;
+  for (int i = 0; i < MAXC; ++i)
 #pragma unroll
     for (int j = 0; j < N; ++j) {
       pg[i][j] = 0.f;
       pb[i][j] = 0.f;
-      gam[i].v[j] = 1.f;
-      bet[i].v[j] = 0.f;
     }
-    if (c < chunks) {
-      if (gamma) gam[i].load(gamma + (int64_t)h * width + c * N);
-      if (beta) bet[i].load(beta + (int64_t)h * width + c * N);
-    }
-  }
 
   const int64_t t0 = (int64_t)blockIdx.x * tokens_per_block;
   const int64_t t1 = (t0 + tokens_per_block < tokens) ? t0 + tokens_per_block : tokens;
-  // register double-buffering: the next token's x / dy (/ dx when accumulating) are requested before this token's
-  // reductions start (narrow rows only: the wide ones already keep 8+ loads in flight per lane)
-  constexpr bool PREF = false;  // measured: the extra registers cost more occupancy than the prefetch buys
-  Vec16<T> xn[MAXC], gn[MAXC], on[MAXC];
-  auto load_row = [&](int64_t t, Vec16<T>* xv, Vec16<T>* gv, Vec16<T>* ov) {
-    const int64_t o = (t * heads + h) * width;
+  auto issue = [&](int64_t t, int stage) {
+    const int64_t off = (t * heads + h) * width;
+    uint8_t* base = s_ring + stage * 3 * rowb;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       if (c < chunks) {
-        xv[i].load(x + o + c * N);
-        gv[i].load(dy + o + c * N);
-        if (dx_acc) ov[i].load(dx + o + c * N);
+        cp_async16(base + c * 16, x + off + c * N);
+        cp_async16(base + rowb + c * 16, dy + off + c * N);
+        if (dx_acc) cp_async16(base + 2 * rowb + c * 16, dx + off + c * N);
       }
     }
+    cp_async_commit();
   };
-  if (PREF && t0 + warp < t1) load_row(t0 + warp, xn, gn, on);
-  for (int64_t t = t0 + warp; t < t1; t += warps_per_block) {
-    const int64_t off = (t * heads + h) * width;
-    Vec16<T> xv[MAXC], gv[MAXC], ov[MAXC];
-    if (PREF) {
-#pragma unroll
-      for (int i = 0; i < MAXC; ++i) {
-        xv[i] = xn[i];
-        gv[i] = gn[i];
-        ov[i] = on[i];
-      }
-      if (t + warps_per_block < t1) load_row(t + warps_per_block, xn, gn, on);
+  int stage = 0;
+  if (t0 + warp < t1) issue(t0 + warp, 0);
+  for (int64_t t = t0 + warp; t < t1; t += warps_per_block, stage ^= 1) {
+    if (t + warps_per_block < t1) {
+      issue(t + warps_per_block, stage ^ 1);
+      cp_async_wait<1>();
     } else {
-      load_row(t, xv, gv, ov);
+      cp_async_wait<0>();
     }
+    __syncwarp();
+    const int64_t off = (t * heads + h) * width;
+    const T* sx = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb);
+    const T* sdy = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb + rowb);
+    const T* sdx = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb + 2 * rowb);
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       if (c < chunks) {
+        Vec16<T> v;
+        v.load(sx + c * N);
 #pragma unroll
-        for (int j = 0; j < N; ++j) s += xv[i].v[j];
+        for (int j = 0; j < N; ++j) s += v.v[j];
       }
     }
     const float mean = warp_sum(s) * inv_w;
@@ -183,29 +197,34 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       if (c < chunks) {
+        Vec16<T> v;
+        v.load(sx + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          const float d = xv[i].v[j] - mean;
+          const float d = v.v[j] - mean;
           q += d * d;
         }
       }
     }
     const float rstd = rsqrtf(warp_sum(q) * inv_w + GN_EPS);
-    // g = dyv * gamma ; accumulate dgamma/dbeta ; row sums of g and g*z
     float sg = 0.f, sgz = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       if (c < chunks) {
+        Vec16<T> xv, dv, gv, bv;
+        xv.load(sx + c * N);
+        dv.load(sdy + c * N);
+        gv.load(s_gam + c * N);
+        bv.load(s_bet + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          const float z = (xv[i].v[j] - mean) * rstd;
-          float d = gv[i].v[j];
-          if (act == 1) d *= gelu_obst_grad(z * gam[i].v[j] + bet[i].v[j]);
+          const float z = (xv.v[j] - mean) * rstd;
+          float d = dv.v[j];
+          if (act == 1) d *= gelu_obst_grad(z * gv.v[j] + bv.v[j]);
           pb[i][j] += d;
           pg[i][j] += d * z;
-          const float g = d * gam[i].v[j];
-          gv[i].v[j] = g;
+          const float g = d * gv.v[j];
           sg += g;
           sgz += g * z;
         }
@@ -217,18 +236,25 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       if (c < chunks) {
-        Vec16<T> o;
+        Vec16<T> xv, dv, gv, bv, o;
+        xv.load(sx + c * N);
+        dv.load(sdy + c * N);
+        gv.load(s_gam + c * N);
+        bv.load(s_bet + c * N);
+        if (dx_acc) o.load(sdx + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          const float xraw = xv[i].v[j];
-          const float z = (xraw - mean) * rstd;
-          float d = rstd * (gv[i].v[j] - mg - z * mgz);
-          if (relu_mask && !(xraw > 0.f)) d = 0.f;
-          o.v[j] = dx_acc ? (ov[i].v[j] + d) : d;
+          const float z = (xv.v[j] - mean) * rstd;
+          float d = dv.v[j];
+          if (act == 1) d *= gelu_obst_grad(z * gv.v[j] + bv.v[j]);
+          float r = rstd * (d * gv.v[j] - mg - z * mgz);
+          if (relu_mask && !(xv.v[j] > 0.f)) r = 0.f;
+          o.v[j] = dx_acc ? (o.v[j] + r) : r;
         }
         o.store(dx + off + c * N);
       }
     }
+    __syncwarp();  // everyone is done with this stage before the next iteration refills it
   }
   // block reduce of the affine gradients
 #pragma unroll
@@ -288,11 +314,17 @@ static int gn_bwd_launch(const void* dy, const void* x, const void* gamma, const
   // keep at least ~4 blocks per SM in flight when the problem is small
   while (tpb > 8 && ((tokens + tpb - 1) / tpb) * heads < (int64_t)num_sms() * 4) tpb >>= 1;
   dim3 grid((unsigned)((tokens + tpb - 1) / tpb), (unsigned)heads);
-  const size_t smem = 2 * (size_t)width * sizeof(float);
-#define OBST_GN_BWD(MC)                                                                                   \
-  gn_bwd_kernel<T, MC><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma, (const T*)beta, \
-                                                 (T*)dx, dgamma, dbeta, tokens, heads, width, tpb, act,    \
-                                                 relu_mask, dx_acc)
+  const size_t rowb = (size_t)width * sizeof(T);
+  const size_t smem = 2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * 6 * rowb;
+  OBST_REQUIRE(smem <= 220 * 1024, "obst_gn_bwd: width %d needs %zu B of shared memory", width, smem);
+#define OBST_GN_BWD(MC)                                                                                       \
+  do {                                                                                                        \
+    if (smem > 48 * 1024)                                                                                     \
+      cudaFuncSetAttribute(gn_bwd_kernel<T, MC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);     \
+    gn_bwd_kernel<T, MC><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma, (const T*)beta, \
+                                                   (T*)dx, dgamma, dbeta, tokens, heads, width, tpb, act,    \
+                                                   relu_mask, dx_acc);                                        \
+  } while (0)
   if (per_lane <= 1) OBST_GN_BWD(1);
   else if (per_lane <= 2) OBST_GN_BWD(2);
   else if (per_lane <= 4) OBST_GN_BWD(4);

@@ -24,7 +24,8 @@ static constexpr int BK = 64;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;        // 16 KB
 static constexpr int TMEM_COLS = 512;
 static constexpr int ACC_STRIDE = 256;                   // columns per accumulator buffer
-static constexpr int TC_THREADS = 192;
+static constexpr int TC_THREADS = 320;                   // TMA warp, MMA warp, 8 epilogue warps
+static constexpr int EPI_WARPS = 8;
 static constexpr int EPI_BOX_ROWS = 32;                  // one epilogue warp's TMEM lane quarter
 static constexpr int EPI_BOX_COLS = 64;                  // 64 bf16 = 128 B = one swizzle row
 static constexpr int EPI_BUF_BYTES = EPI_BOX_ROWS * EPI_BOX_COLS * 2;  // 4 KB
@@ -287,13 +288,48 @@ __device__ __forceinline__ void epi_apply(float (&v)[8], const float (&r)[8], in
   }
 }
 
+// One epilogue chunk of one thread: 64 accumulator columns of its row -> fused op -> bf16 -> the row's 128-byte
+// line of the swizzled slab (16-byte slot j lives at j ^ (row & 7): conflict-free for a quarter-warp).
+template <int EPI>
+__device__ __forceinline__ void epi_chunk(uint8_t* buf, int lane, const uint32_t (&r)[64]) {
+  uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4));
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[j * 8 + e]);
+    if (EPI == 1) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+    } else if (EPI >= 2) {
+      const uint4 ru = *slot;
+      const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z),
+                   f3 = unpack_bf16x2(ru.w);
+      const float rr[8] = {f0.x, f0.y, f1.x, f1.y, f2.x, f2.y, f3.x, f3.y};
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        if (EPI == 2) v[e] = rr[e] + v[e];
+        else if (EPI == 3) v[e] = rr[e] - v[e];
+        else v[e] = rr[e] > 0.f ? v[e] : 0.f;
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]);
+    o.w = pack_bf16x2(v[6], v[7]);
+    *slot = o;
+  }
+}
+
 template <int CG>
 struct Cfg {
-  static constexpr int STAGES = CG == 2 ? 6 : 4;
+  static constexpr int STAGES = CG == 2 ? 5 : 3;
   static constexpr int B_STAGE = 256 / CG * BK * 2;  // bytes of this CTA's share of the B tile
   static constexpr int EPI_OFF = STAGES * (A_STAGE_BYTES + B_STAGE);
-  static constexpr int BAR_OFF = EPI_OFF + 4 * 2 * EPI_BUF_BYTES;
-  static constexpr int SMEM = BAR_OFF + 256 + 1024;
+  static constexpr int BAR_OFF = EPI_OFF + EPI_WARPS * 2 * EPI_BUF_BYTES;
+  static constexpr int SMEM = BAR_OFF + 512 + 1024;
 };
 
 template <int CG>
@@ -312,8 +348,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* empty_bar = bars + STAGES;           // [STAGES]
   uint64_t* tfull_bar = bars + 2 * STAGES;       // [2]
   uint64_t* tempty_bar = bars + 2 * STAGES + 2;  // [2]       (CG==2: only the leader's are used)
-  uint64_t* rbar = bars + 2 * STAGES + 4;        // [4 warps][2 buffers] R-tile arrival
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 12);
+  uint64_t* rbar = bars + 2 * STAGES + 4;        // [8 warps][2 buffers] R-tile arrival
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4 + 2 * EPI_WARPS);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -332,9 +368,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull_bar[s], 1);
-      mbar_init(&tempty_bar[s], 128 * CG);
+      mbar_init(&tempty_bar[s], EPI_WARPS * 32 * CG);
     }
-    for (int s = 0; s < 8; ++s) mbar_init(&rbar[s], 1);
+    for (int s = 0; s < 2 * EPI_WARPS; ++s) mbar_init(&rbar[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) tmem_alloc<CG>(tmem_ptr, TMEM_COLS);
@@ -431,8 +467,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
+    // ===================== epilogue (warps 2..9) =====================
+    // Two warps per TMEM lane quarter; they take alternate column chunks of the tile.
     const int quarter = warp & 3;  // TMEM lanes [32*quarter, 32*quarter+32) are the ones this warp may read
+    const int ew = warp - 2;       // 0..7
+    const int half = ew >> 2;      // which of the two warps of this quarter
     int acc = 0;
     uint32_t acc_phase = 0;
     Tile t;
@@ -440,8 +479,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (p.tma_store) {
       // bf16 output: TMEM -> registers -> fused op -> swizzled smem slab (32 rows x 128 B) -> TMA store.
       // R (residual / ReLU mask) arrives the same way (TMA load into the slab), so global traffic is full lines.
-      uint8_t* const buf0 = smem_epi + quarter * 2 * EPI_BUF_BYTES;
-      uint64_t* const rb0 = &rbar[quarter * 2];
+      uint8_t* const buf0 = smem_epi + ew * 2 * EPI_BUF_BYTES;
+      uint64_t* const rb0 = &rbar[ew * 2];
       uint32_t rphase = 0;  // bit b = phase of slab b's R barrier
       uint32_t it = 0;
       const int nchunks = (p.BN + EPI_BOX_COLS - 1) / EPI_BOX_COLS;
@@ -451,7 +490,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tcgen05_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
         const int row0 = t.m0 + cta_m + quarter * 32;
-        for (int c = 0; c < nchunks; ++c, ++it) {
+        if (half >= nchunks) {  // narrow tile: nothing for this warp, but the accumulator hand-back counts it
+          tcgen05_fence_before();
+          mbar_arrive_cta<CG>(&tempty_bar[acc], 0);
+        }
+        for (int c = half; c < nchunks; c += 2, ++it) {
           const int b = it & 1;
           uint8_t* const buf = buf0 + b * EPI_BUF_BYTES;
           uint64_t* const rb = rb0 + b;
@@ -473,8 +516,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tmem_ld32(taddr0 + (uint32_t)(c * EPI_BOX_COLS + 32), rb2);
             tmem_ld_wait();
           }
-          if (c == nchunks - 1) {
-            // accumulator fully read: hand it back to the MMA warp before the store work of this chunk
+          if (c + 2 >= nchunks) {
+            // this warp's last read of the accumulator: hand it back before the store work of this chunk
             tcgen05_fence_before();
             mbar_arrive_cta<CG>(&tempty_bar[acc], 0);
           }
@@ -486,30 +529,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_wait(rb, (rphase >> b) & 1u, 4);
             rphase ^= 1u << b;
           }
-          uint8_t* rowp = buf + lane * 128;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4));
-            float v[8], rr[8];
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              v[e] = __uint_as_float(r[j * 8 + e]);
-              rr[e] = 0.f;
-            }
-            if (p.epi >= 2) {
-              const uint4 ru = *slot;
-              const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z),
-                           f3 = unpack_bf16x2(ru.w);
-              rr[0] = f0.x; rr[1] = f0.y; rr[2] = f1.x; rr[3] = f1.y;
-              rr[4] = f2.x; rr[5] = f2.y; rr[6] = f3.x; rr[7] = f3.y;
-            }
-            epi_apply(v, rr, p.epi);
-            uint4 o;
-            o.x = pack_bf16x2(v[0], v[1]);
-            o.y = pack_bf16x2(v[2], v[3]);
-            o.z = pack_bf16x2(v[4], v[5]);
-            o.w = pack_bf16x2(v[6], v[7]);
-            *slot = o;
+          switch (p.epi) {
+            case 0: epi_chunk<0>(buf, lane, r); break;
+            case 1: epi_chunk<1>(buf, lane, r); break;
+            case 2: epi_chunk<2>(buf, lane, r); break;
+            case 3: epi_chunk<3>(buf, lane, r); break;
+            default: epi_chunk<4>(buf, lane, r); break;
           }
           fence_async_smem();
           __syncwarp();
@@ -535,7 +560,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool row_ok = m < p.M;
         const int64_t row_off = (int64_t)t.glo * p.d_glo + (int64_t)t.ghi * p.d_ghi + (int64_t)m * p.d_ld;
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
-        for (int c = 0; c < p.BN / 32; ++c) {
+        for (int c = half; c < p.BN / 32; c += 2) {
           uint32_t r[32];
           tmem_ld32(taddr0 + (uint32_t)(c * 32), r);
           tmem_ld_wait();
@@ -595,7 +620,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
         tcgen05_fence_before();
-        mbar_arrive_cta<CG>(&tempty_bar[acc], 0);  // 128*CG arrivals release the accumulator to the MMA warp
+        mbar_arrive_cta<CG>(&tempty_bar[acc], 0);  // 256*CG arrivals release the accumulator to the MMA warp
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;

@@ -80,6 +80,35 @@ struct Vec16<bf16> {
   }
 };
 
+// ---- the same 16 bytes kept PACKED in registers (4 regs) and unpacked on use: for kernels that must hold
+// several rows / operands at once and would otherwise lose occupancy to fp32 copies
+template <typename T>
+struct Raw16;
+template <>
+struct Raw16<float> {
+  static constexpr int N = 4;
+  float4 r;
+  __device__ __forceinline__ void load(const float* p) { r = *reinterpret_cast<const float4*>(p); }
+  __device__ __forceinline__ void store(float* p) const { *reinterpret_cast<float4*>(p) = r; }
+  __device__ __forceinline__ void unpack(float (&v)[4]) const { v[0] = r.x; v[1] = r.y; v[2] = r.z; v[3] = r.w; }
+  __device__ __forceinline__ void pack(const float (&v)[4]) { r = make_float4(v[0], v[1], v[2], v[3]); }
+};
+template <>
+struct Raw16<bf16> {
+  static constexpr int N = 8;
+  uint4 r;
+  __device__ __forceinline__ void load(const bf16* p) { r = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void store(bf16* p) const { *reinterpret_cast<uint4*>(p) = r; }
+  __device__ __forceinline__ void unpack(float (&v)[8]) const {
+    const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), c = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+  }
+  __device__ __forceinline__ void pack(const float (&v)[8]) {
+    r.x = pack_bf16x2(v[0], v[1]); r.y = pack_bf16x2(v[2], v[3]);
+    r.z = pack_bf16x2(v[4], v[5]); r.w = pack_bf16x2(v[6], v[7]);
+  }
+};
+
 // ---- warp reductions ---------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
