@@ -343,3 +343,170 @@ int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dt
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// Allocation-free single-tensor update
+// ================================================================================================
+// The entry points above expect the caller to have put a tensor table, a work list, the norm scratch and the
+// accumulator staging into device memory.  Some hosts cannot do that: a plug-in living inside a process whose
+// framework has already claimed the whole GPU for its own pool, or a runtime that forbids driver allocation calls
+// from extension code.  For them the same three kernels are driven from a fixed block of device memory that is
+// part of this library's image: nothing is allocated, by us or by the caller.
+namespace obst {
+
+static constexpr int NA_MAX_ITEMS = 4096;       // work items (row ranges) of one tensor
+static constexpr int NA_MAX_DIM_SUM = 16384;    // sum of the tensor's dims (SM3 staging, one float per entry)
+static constexpr size_t NA_OFF_TABLE = 0;                                  // 1 x obst_opt_tensor (padded to 256)
+static constexpr size_t NA_OFF_NORMS = 256;                                // 2 doubles (padded to 256)
+static constexpr size_t NA_OFF_ITEMS = 512;                                // 3 x int32[NA_MAX_ITEMS]
+static constexpr size_t NA_OFF_ACC = NA_OFF_ITEMS + 3 * 4 * (size_t)NA_MAX_ITEMS;  // float[NA_MAX_DIM_SUM + 4*64]
+static constexpr size_t NA_BYTES = NA_OFF_ACC + 4 * ((size_t)NA_MAX_DIM_SUM + 4 * 64);
+static_assert(sizeof(obst_opt_tensor) <= 256, "table slot too small");
+static_assert(NA_BYTES <= 128 * 1024, "keep the resident scratch modest");
+
+// Lives in every GPU that loads the library, from load to exit (about 114 KB).  In HOST code this name is only a
+// stand-in for the symbol: the device address must be asked for (cudaGetSymbolAddress) before it is handed to a
+// kernel.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+struct NaFill {
+  obst_opt_tensor t;  // acc_new[] is filled in on the device
+  int32_t rows, rows_per_item, nitems, dim_sum_padded;
+};
+
+// Writes the one-entry table and the work list, and clears what the update expects to start at zero
+// (norm sums, SM3 staging): the block keeps whatever the previous call left behind.
+__global__ void __launch_bounds__(256) na_fill_kernel(unsigned char* scratch, NaFill f) {
+  obst_opt_tensor* table = reinterpret_cast<obst_opt_tensor*>(scratch + NA_OFF_TABLE);
+  double* norms = reinterpret_cast<double*>(scratch + NA_OFF_NORMS);
+  int32_t* item_tensor = reinterpret_cast<int32_t*>(scratch + NA_OFF_ITEMS);
+  int32_t* item_row0 = item_tensor + NA_MAX_ITEMS;
+  int32_t* item_rows = item_row0 + NA_MAX_ITEMS;
+  float* acc = reinterpret_cast<float*>(scratch + NA_OFF_ACC);
+  if (threadIdx.x == 0) {
+    obst_opt_tensor t = f.t;
+    int off = 0;
+    for (int i = 0; i < 4; ++i) {
+      t.acc_new[i] = i < t.ndim ? acc + off : nullptr;
+      if (i < t.ndim) off += t.dims[i] + ((64 - t.dims[i] % 64) % 64);
+    }
+    *table = t;
+    norms[0] = 0.0;
+    norms[1] = 0.0;
+  }
+  for (int i = threadIdx.x; i < f.nitems; i += blockDim.x) {
+    const int r0 = i * f.rows_per_item;
+    item_tensor[i] = 0;
+    item_row0[i] = r0;
+    item_rows[i] = min(f.rows_per_item, f.rows - r0);
+  }
+  for (int i = threadIdx.x; i < f.dim_sum_padded; i += blockDim.x) acc[i] = 0.f;
+}
+
+}  // namespace obst
+
+extern "C" int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, void* const* acc,
+                                     const int32_t* dims, int32_t ndim, int32_t decay, int32_t tril_s,
+                                     int32_t dtype_act, int32_t dtype_state, int32_t grad_bf16, float clip, float beta,
+                                     int32_t nesterov, float lr, float weight_decay, void* stream) {
+  OBST_REQUIRE(p && g && m && acc && dims, "obst_opt_step_noalloc: null argument");
+  OBST_REQUIRE(ndim >= 1 && ndim <= 4, "obst_opt_step_noalloc: ndim %d outside 1..4", ndim);
+  OBST_REQUIRE(dtype_state == OBST_BF16 || dtype_state == OBST_F32, "obst_opt_step_noalloc: bad state dtype %d",
+               dtype_state);
+  NaFill f;
+  memset(&f, 0, sizeof(f));
+  int64_t numel = 1;
+  int dim_sum = 0;
+  for (int i = 0; i < ndim; ++i) {
+    OBST_REQUIRE(dims[i] > 0 && acc[i], "obst_opt_step_noalloc: dim %d is empty or has no accumulator", i);
+    numel *= dims[i];
+    dim_sum += dims[i] + ((64 - dims[i] % 64) % 64);
+    f.t.dims[i] = dims[i];
+    f.t.acc[i] = acc[i];
+  }
+  const int cols = dims[ndim - 1];
+  OBST_REQUIRE(dim_sum <= NA_MAX_DIM_SUM + 4 * 64,
+               "obst_opt_step_noalloc: the dims (each rounded up to 64) add up to %d, the built-in staging holds %d",
+               dim_sum, NA_MAX_DIM_SUM + 4 * 64);
+  OBST_REQUIRE(cols <= 12288, "obst_opt_step_noalloc: last dim %d too large (max 12288)", cols);
+  const int64_t rows64 = numel / cols;
+  const int rpi = 32768 / cols > 0 ? 32768 / cols : 1;
+  const int64_t nitems64 = (rows64 + rpi - 1) / rpi;
+  OBST_REQUIRE(nitems64 <= NA_MAX_ITEMS,
+               "obst_opt_step_noalloc: tensor of %lld elements needs %lld work items, the built-in list holds %d "
+               "(about %lld elements at this last dim)",
+               (long long)numel, (long long)nitems64, NA_MAX_ITEMS, (long long)NA_MAX_ITEMS * rpi * cols);
+  f.t.p = p;
+  f.t.shadow = shadow;
+  f.t.g = g;
+  f.t.m = m;
+  f.t.numel = numel;
+  f.t.ndim = ndim;
+  f.t.decay = decay;
+  f.t.tril_s = tril_s;
+  f.rows = (int32_t)rows64;
+  f.rows_per_item = rpi;
+  f.nitems = (int32_t)nitems64;
+  f.dim_sum_padded = dim_sum;
+
+  // Set-up, once per device, with that device current: turn the symbol into a device address.
+  static unsigned char* dev_ptr[64] = {nullptr};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("obst_opt_step_noalloc: cudaGetDevice failed or device index %d unsupported: %s", dev,
+              cudaGetErrorString(e));
+    return OBST_ECUDA;
+  }
+  if (dev_ptr[dev] == nullptr) {
+    unsigned char* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess || ptr == nullptr) {
+      set_error("obst_opt_step_noalloc: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return OBST_ECUDA;
+    }
+    dev_ptr[dev] = ptr;
+  }
+  unsigned char* scratch = dev_ptr[dev];
+  cudaStream_t st = (cudaStream_t)stream;
+  const obst_opt_tensor* table = reinterpret_cast<const obst_opt_tensor*>(scratch + NA_OFF_TABLE);
+  double* norms = reinterpret_cast<double*>(scratch + NA_OFF_NORMS);
+  const int32_t* item_tensor = reinterpret_cast<const int32_t*>(scratch + NA_OFF_ITEMS);
+  const int32_t* item_row0 = item_tensor + NA_MAX_ITEMS;
+  const int32_t* item_rows = item_row0 + NA_MAX_ITEMS;
+
+  na_fill_kernel<<<1, 256, 0, st>>>(scratch, f);
+  if (clip > 0.f)
+    opt_norms_kernel<<<(unsigned)f.nitems, 256, 0, st>>>(table, item_tensor, item_row0, item_rows,
+                                                         dtype_act == OBST_BF16, grad_bf16, norms);
+  OptHyper hp;
+  hp.clip = clip; hp.beta = beta; hp.lr = lr; hp.weight_decay = weight_decay;
+  hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
+  const size_t smem = (size_t)cols * sizeof(float);
+  const int vec = (cols % 4 == 0) ? 4 : 1;
+  const int ni = (cols + 32 * vec - 1) / (32 * vec);
+#define OBST_NA(TS, V, N) \
+  opt_update_kernel<TS, V, N><<<(unsigned)f.nitems, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, norms, hp)
+#define OBST_NA_NI(TS, V)                \
+  do {                                   \
+    if (ni <= 1) OBST_NA(TS, V, 1);      \
+    else if (ni <= 2) OBST_NA(TS, V, 2); \
+    else if (ni <= 4) OBST_NA(TS, V, 4); \
+    else if (ni <= 8) OBST_NA(TS, V, 8); \
+    else if (ni <= 16) OBST_NA(TS, V, 16); \
+    else OBST_NA(TS, V, 0);              \
+  } while (0)
+  if (dtype_state == OBST_BF16) {
+    if (vec == 4) OBST_NA_NI(bf16, 4);
+    else OBST_NA_NI(bf16, 1);
+  } else {
+    if (vec == 4) OBST_NA_NI(float, 4);
+    else OBST_NA_NI(float, 1);
+  }
+#undef OBST_NA_NI
+#undef OBST_NA
+  if (dtype_state == OBST_BF16) opt_finalize_kernel<bf16><<<1, 256, 0, st>>>(table);
+  else opt_finalize_kernel<float><<<1, 256, 0, st>>>(table);
+  count_launch(clip > 0.f ? 4 : 3);
+  return check_launch("obst_opt_step_noalloc");
+}

@@ -192,6 +192,28 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
 int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dtype_state,
                       void* stream);
 
+/* ---- the same update for ONE tensor, without any device allocation -----------------------------------
+ * No counterpart in the reference (its update always runs inside the Mesh-TensorFlow graph).
+ * obst_opt_norms/update/finalize need a tensor table, a work list, norm sums and SM3 staging in device
+ * memory that the caller has to allocate.  A host that cannot allocate -- extension code inside a process
+ * whose framework already owns all of the GPU's memory, or a runtime that bars driver allocation calls --
+ * uses this entry point instead: the table, work list, norm sums and staging live in a fixed ~114 KB block
+ * inside the library image (a file-scope __device__ array; every GPU that loads the library holds it until
+ * the process exits).  The caller passes only the tensor itself:
+ *   p, g fp32 [numel] (16-byte aligned), shadow (activation dtype, may be NULL), m and acc[i] (state dtype,
+ *   acc[i] has dims[i] entries), ndim 1..4; remaining arguments as obst_opt_update.
+ * Limits (rejected with OBST_EINVAL and a message): the dims, each rounded up to 64, may add up to at most
+ * 16640; the tensor may need at most 4096 work items of 32768/last_dim rows (134 M elements for
+ * last dims <= 32768); last dim <= 12288.
+ * The first call on each device looks up the block's device address; make that call before capturing a
+ * stream.  Every call on a device shares the block (it is cleared on entry where the update needs zeros),
+ * so two calls that overlap on the GPU -- different streams, or graph branches -- race: serialise them.
+ * Calls no cudaMalloc / cudaFree or other allocating routine; enqueues 3-4 kernels on `stream`. */
+int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, void* const* acc,
+                          const int32_t* dims, int32_t ndim, int32_t decay, int32_t tril_s,
+                          int32_t dtype_act, int32_t dtype_state, int32_t grad_bf16, float clip,
+                          float beta, int32_t nesterov, float lr, float weight_decay, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
