@@ -180,6 +180,9 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     const T* sx = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb);
     const T* sdy = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb + rowb);
     const T* sdx = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb + 2 * rowb);
+    // The kernel is instruction-issue bound, not latency bound: unpack each operand ONCE into fp32 registers and
+    // reuse (x -> z, dy -> g); gamma/beta come from shared memory when needed.
+    float zv[MAXC][N], gv[MAXC][N];
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
@@ -188,43 +191,47 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
         Vec16<T> v;
         v.load(sx + c * N);
 #pragma unroll
-        for (int j = 0; j < N; ++j) s += v.v[j];
+        for (int j = 0; j < N; ++j) {
+          zv[i][j] = v.v[j];
+          s += v.v[j];
+        }
       }
     }
     const float mean = warp_sum(s) * inv_w;
     float q = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
-      const int c = lane + 32 * i;
-      if (c < chunks) {
-        Vec16<T> v;
-        v.load(sx + c * N);
+      if (lane + 32 * i < chunks) {
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          const float d = v.v[j] - mean;
+          const float d = zv[i][j] - mean;
           q += d * d;
         }
       }
     }
     const float rstd = rsqrtf(warp_sum(q) * inv_w + GN_EPS);
     float sg = 0.f, sgz = 0.f;
+    unsigned long long maskbits = 0;  // bit (i*N+j) <= 63: raw x > 0 (ReLU mask), taken before x becomes z
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       if (c < chunks) {
-        Vec16<T> xv, dv, gv, bv;
-        xv.load(sx + c * N);
+        Vec16<T> dv, gam;
         dv.load(sdy + c * N);
-        gv.load(s_gam + c * N);
-        bv.load(s_bet + c * N);
+        gam.load(s_gam + c * N);
+        Vec16<T> bet;
+        if (act == 1) bet.load(s_bet + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          const float z = (xv.v[j] - mean) * rstd;
+          if (relu_mask && zv[i][j] > 0.f) maskbits |= 1ull << (i * N + j);
+          const float z = (zv[i][j] - mean) * rstd;
+          zv[i][j] = z;
           float d = dv.v[j];
-          if (act == 1) d *= gelu_obst_grad(z * gv.v[j] + bv.v[j]);
+          if (act == 1) d *= gelu_obst_grad(z * gam.v[j] + bet.v[j]);
           pb[i][j] += d;
           pg[i][j] += d * z;
-          const float g = d * gv.v[j];
+          const float g = d * gam.v[j];
+          gv[i][j] = g;
           sg += g;
           sgz += g * z;
         }
@@ -236,19 +243,12 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       if (c < chunks) {
-        Vec16<T> xv, dv, gv, bv, o;
-        xv.load(sx + c * N);
-        dv.load(sdy + c * N);
-        gv.load(s_gam + c * N);
-        bv.load(s_bet + c * N);
+        Vec16<T> o;
         if (dx_acc) o.load(sdx + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          const float z = (xv.v[j] - mean) * rstd;
-          float d = dv.v[j];
-          if (act == 1) d *= gelu_obst_grad(z * gv.v[j] + bv.v[j]);
-          float r = rstd * (d * gv.v[j] - mg - z * mgz);
-          if (relu_mask && !(xv.v[j] > 0.f)) r = 0.f;
+          float r = rstd * (gv[i][j] - mg - zv[i][j] * mgz);
+          if (relu_mask && !((maskbits >> (i * N + j)) & 1ull)) r = 0.f;
           o.v[j] = dx_acc ? (o.v[j] + r) : r;
         }
         o.store(dx + off + c * N);

@@ -479,55 +479,59 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (p.tma_store) {
       // bf16 output: TMEM -> registers -> fused op -> swizzled smem slab (32 rows x 128 B) -> TMA store.
       // R (residual / ReLU mask) arrives the same way (TMA load into the slab), so global traffic is full lines.
+      // A warp owns up to two 64-column chunks of its 32 rows (c = half and half + 2); chunk slot s uses slab s.
+      // Per tile: (1) R tiles are requested first, so they fly in while the MMAs finish; (2) BOTH chunks are read
+      // from TMEM into registers and the accumulator is handed back at once -- the conversion / store work then
+      // runs while the tensor core is already on the tile after next.
       uint8_t* const buf0 = smem_epi + ew * 2 * EPI_BUF_BYTES;
       uint64_t* const rb0 = &rbar[ew * 2];
-      uint32_t rphase = 0;  // bit b = phase of slab b's R barrier
-      uint32_t it = 0;
+      uint32_t rphase = 0;  // bit s = phase of slab s's R barrier
       const int nchunks = (p.BN + EPI_BOX_COLS - 1) / EPI_BOX_COLS;
       for (int tile = cluster_id; tile < p.total_tiles; tile += num_clusters) {
         if (!get_tile<CG>(p, tile, t)) continue;
+        const int row0 = t.m0 + cta_m + quarter * 32;
+        const int c0 = half, c1 = half + 2;
+        const int col0 = t.n0 + c0 * EPI_BOX_COLS, col1 = t.n0 + c1 * EPI_BOX_COLS;
+        const bool live0 = c0 < nchunks && row0 < p.M && col0 < p.N;  // warp-uniform
+        const bool live1 = c1 < nchunks && row0 < p.M && col1 < p.N;
+        if (lane == 0) {
+          bulk_wait_read<0>();  // last tile's stores have read both slabs (they were issued a whole tile ago)
+          if (p.epi >= 2) {
+            if (live0) {
+              mbar_expect_tx(rb0, EPI_BUF_BYTES);
+              tma_load_5d<1>(buf0, &tmR, rb0, col0, row0, t.glo, t.ghi, 0);
+            }
+            if (live1) {
+              mbar_expect_tx(rb0 + 1, EPI_BUF_BYTES);
+              tma_load_5d<1>(buf0 + EPI_BUF_BYTES, &tmR, rb0 + 1, col1, row0, t.glo, t.ghi, 0);
+            }
+          }
+        }
+        __syncwarp();
         mbar_wait(&tfull_bar[acc], acc_phase, 3);
         tcgen05_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
-        const int row0 = t.m0 + cta_m + quarter * 32;
-        if (half >= nchunks) {  // narrow tile: nothing for this warp, but the accumulator hand-back counts it
-          tcgen05_fence_before();
-          mbar_arrive_cta<CG>(&tempty_bar[acc], 0);
+        uint32_t ra[64], rc[64];
+        if (c0 < nchunks) {
+          tmem_ld32(taddr0 + (uint32_t)(c0 * EPI_BOX_COLS), *reinterpret_cast<uint32_t (*)[32]>(&ra[0]));
+          tmem_ld32(taddr0 + (uint32_t)(c0 * EPI_BOX_COLS + 32), *reinterpret_cast<uint32_t (*)[32]>(&ra[32]));
         }
-        for (int c = half; c < nchunks; c += 2, ++it) {
-          const int b = it & 1;
-          uint8_t* const buf = buf0 + b * EPI_BUF_BYTES;
-          uint64_t* const rb = rb0 + b;
-          const int col0 = t.n0 + c * EPI_BOX_COLS;
-          const bool live = row0 < p.M && col0 < p.N;  // warp-uniform
-          if (lane == 0) bulk_wait_read<1>();          // the store that last used this slab has read it
-          __syncwarp();
-          if (p.epi >= 2 && live) {
-            if (lane == 0) {
-              mbar_expect_tx(rb, EPI_BUF_BYTES);
-              tma_load_5d<1>(buf, &tmR, rb, col0, row0, t.glo, t.ghi, 0);
-            }
-          }
-          uint32_t r[64];
-          {
-            uint32_t (&ra)[32] = *reinterpret_cast<uint32_t (*)[32]>(&r[0]);
-            uint32_t (&rb2)[32] = *reinterpret_cast<uint32_t (*)[32]>(&r[32]);
-            tmem_ld32(taddr0 + (uint32_t)(c * EPI_BOX_COLS), ra);
-            tmem_ld32(taddr0 + (uint32_t)(c * EPI_BOX_COLS + 32), rb2);
-            tmem_ld_wait();
-          }
-          if (c + 2 >= nchunks) {
-            // this warp's last read of the accumulator: hand it back before the store work of this chunk
-            tcgen05_fence_before();
-            mbar_arrive_cta<CG>(&tempty_bar[acc], 0);
-          }
-          if (!live) {
-            if (lane == 0) bulk_commit();  // empty group: keeps "one group per chunk" for wait_group.read 1
-            continue;
-          }
+        if (c1 < nchunks) {
+          tmem_ld32(taddr0 + (uint32_t)(c1 * EPI_BOX_COLS), *reinterpret_cast<uint32_t (*)[32]>(&rc[0]));
+          tmem_ld32(taddr0 + (uint32_t)(c1 * EPI_BOX_COLS + 32), *reinterpret_cast<uint32_t (*)[32]>(&rc[32]));
+        }
+        tmem_ld_wait();
+        tcgen05_fence_before();
+        mbar_arrive_cta<CG>(&tempty_bar[acc], 0);  // accumulator is in registers: release it
+#pragma unroll
+        for (int sl = 0; sl < 2; ++sl) {
+          const bool live = sl == 0 ? live0 : live1;
+          if (!live) continue;
+          uint8_t* const buf = buf0 + sl * EPI_BUF_BYTES;
+          const uint32_t (&r)[64] = sl == 0 ? ra : rc;
           if (p.epi >= 2) {
-            mbar_wait(rb, (rphase >> b) & 1u, 4);
-            rphase ^= 1u << b;
+            mbar_wait(rb0 + sl, (rphase >> sl) & 1u, 4);
+            rphase ^= 1u << sl;
           }
           switch (p.epi) {
             case 0: epi_chunk<0>(buf, lane, r); break;
@@ -539,7 +543,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           fence_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_5d(&tmD, buf, col0, row0, t.glo, t.ghi, 0);
+            tma_store_5d(&tmD, buf, sl == 0 ? col0 : col1, row0, t.glo, t.ghi, 0);
             bulk_commit();
           }
         }
