@@ -111,10 +111,10 @@ __device__ __forceinline__ void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-// Each warp streams its rows through a private 2-stage shared-memory ring with cp.async (no register staging): the
+// Each warp streams its rows through a private BSTAGES-deep shared-memory ring with cp.async (no register staging): the
 // next row's x / dy (/ dx) are in flight while the current row is reduced, and the only long-lived registers are
 // the dgamma/dbeta partials -- occupancy AND memory-level parallelism stay high.
-template <typename T, int MAXC>
+template <typename T, int MAXC, int BSTAGES>
 __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                       const T* __restrict__ gamma, const T* __restrict__ beta,
                                                       T* __restrict__ dx, float* __restrict__ dgamma,
@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
   float* s_red = reinterpret_cast<float*>(s_raw);
   T* s_gam = reinterpret_cast<T*>(s_raw + 2 * width * sizeof(float));
   T* s_bet = s_gam + width;
-  uint8_t* s_ring = reinterpret_cast<uint8_t*>(s_bet + width) + (size_t)warp * 6 * rowb;
+  uint8_t* s_ring = reinterpret_cast<uint8_t*>(s_bet + width) + (size_t)warp * BSTAGES * 3 * rowb;
   for (int i = threadIdx.x; i < 2 * width; i += blockDim.x) s_red[i] = 0.f;
   for (int i = threadIdx.x; i < width; i += blockDim.x) {
     s_gam[i] = gamma ? gamma[(int64_t)h * width + i] : from_f32<T>(1.f);
@@ -167,14 +167,16 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     cp_async_commit();
   };
   int stage = 0;
-  if (t0 + warp < t1) issue(t0 + warp, 0);
-  for (int64_t t = t0 + warp; t < t1; t += warps_per_block, stage ^= 1) {
-    if (t + warps_per_block < t1) {
-      issue(t + warps_per_block, stage ^ 1);
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
+#pragma unroll
+  for (int s0 = 0; s0 < BSTAGES - 1; ++s0) {
+    if (t0 + warp + (int64_t)s0 * warps_per_block < t1) issue(t0 + warp + (int64_t)s0 * warps_per_block, s0);
+    else cp_async_commit();  // keep one group per slot so wait_group counts stay aligned
+  }
+  for (int64_t t = t0 + warp; t < t1; t += warps_per_block, stage = (stage + 1) % BSTAGES) {
+    const int64_t tn = t + (int64_t)(BSTAGES - 1) * warps_per_block;
+    if (tn < t1) issue(tn, (stage + BSTAGES - 1) % BSTAGES);
+    else cp_async_commit();
+    cp_async_wait<BSTAGES - 1>();
     __syncwarp();
     const int64_t off = (t * heads + h) * width;
     const T* sx = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb);
@@ -315,20 +317,29 @@ static int gn_bwd_launch(const void* dy, const void* x, const void* gamma, const
   while (tpb > 8 && ((tokens + tpb - 1) / tpb) * heads < (int64_t)num_sms() * 4) tpb >>= 1;
   dim3 grid((unsigned)((tokens + tpb - 1) / tpb), (unsigned)heads);
   const size_t rowb = (size_t)width * sizeof(T);
-  const size_t smem = 2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * 6 * rowb;
+  // ring depth: 4 rows per warp where two blocks still fit an SM, else 2
+  const bool deep = (2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * 4 * 3 * rowb) <= 100 * 1024;
+  const int bst = deep ? 4 : 2;
+  const size_t smem = 2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * (size_t)bst * 3 * rowb;
   OBST_REQUIRE(smem <= 220 * 1024, "obst_gn_bwd: width %d needs %zu B of shared memory", width, smem);
-#define OBST_GN_BWD(MC)                                                                                       \
-  do {                                                                                                        \
-    if (smem > 48 * 1024)                                                                                     \
-      cudaFuncSetAttribute(gn_bwd_kernel<T, MC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);     \
-    gn_bwd_kernel<T, MC><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma, (const T*)beta, \
-                                                   (T*)dx, dgamma, dbeta, tokens, heads, width, tpb, act,    \
-                                                   relu_mask, dx_acc);                                        \
+#define OBST_GN_BWD1(MC, ST)                                                                                    \
+  do {                                                                                                          \
+    if (smem > 48 * 1024)                                                                                       \
+      cudaFuncSetAttribute(gn_bwd_kernel<T, MC, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
+    gn_bwd_kernel<T, MC, ST><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma,              \
+                                                       (const T*)beta, (T*)dx, dgamma, dbeta, tokens, heads,   \
+                                                       width, tpb, act, relu_mask, dx_acc);                    \
+  } while (0)
+#define OBST_GN_BWD(MC)            \
+  do {                             \
+    if (deep) OBST_GN_BWD1(MC, 4); \
+    else OBST_GN_BWD1(MC, 2);      \
   } while (0)
   if (per_lane <= 1) OBST_GN_BWD(1);
   else if (per_lane <= 2) OBST_GN_BWD(2);
   else if (per_lane <= 4) OBST_GN_BWD(4);
   else OBST_GN_BWD(8);
+#undef OBST_GN_BWD1
 #undef OBST_GN_BWD
   count_launch();
   return check_launch("obst_gn_bwd");
