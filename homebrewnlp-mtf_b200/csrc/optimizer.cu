@@ -28,9 +28,19 @@ __global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* _
                                                          const int32_t* __restrict__ item_tensor,
                                                          const int32_t* __restrict__ item_row0,
                                                          const int32_t* __restrict__ item_rows, int act_bf16,
-                                                         int grad_bf16, double* __restrict__ norms) {
+                                                         int grad_bf16, double* __restrict__ norms, int carry,
+                                                         double* __restrict__ wnext, int carry_first,
+                                                         int carry_count) {
   __shared__ double s_part[2][8];
   const int item = blockIdx.x;
+  // carry mode: sum cast_AT(p)^2 was accumulated by the previous update (it wrote every p) -- move it into place
+  // instead of reading the weights again
+  if (carry && blockIdx.x == 0) {
+    for (int t = threadIdx.x; t < carry_count; t += blockDim.x) {
+      norms[2 * (carry_first + t) + 1] = wnext[carry_first + t];
+      wnext[carry_first + t] = 0.0;
+    }
+  }
   const int ti = item_tensor[item];
   const obst_opt_tensor T = table[ti];
   const int64_t cols = T.dims[T.ndim - 1];
@@ -43,7 +53,7 @@ __global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* _
   const int64_t nv = vec_ok ? n / 4 : 0;
   for (int64_t i = threadIdx.x; i < nv; i += blockDim.x) {
     const float4 gv = reinterpret_cast<const float4*>(g)[i];
-    const float4 pv = reinterpret_cast<const float4*>(p)[i];
+    const float4 pv = carry ? make_float4(0.f, 0.f, 0.f, 0.f) : reinterpret_cast<const float4*>(p)[i];
     float ga[4] = {gv.x, gv.y, gv.z, gv.w}, pa[4] = {pv.x, pv.y, pv.z, pv.w};
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -55,7 +65,8 @@ __global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* _
   }
   for (int64_t i = nv * 4 + threadIdx.x; i < n; i += blockDim.x) {
     const float gg = grad_bf16 ? round_to<bf16>(g[i]) : g[i];
-    const float ww = act_bf16 ? round_to<bf16>(p[i]) : p[i];
+    const float pw = carry ? 0.f : p[i];
+    const float ww = act_bf16 ? round_to<bf16>(pw) : pw;
     sg += gg * gg;
     sw += ww * ww;
   }
@@ -73,13 +84,15 @@ __global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* _
       b += s_part[1][w];
     }
     atomicAdd(&norms[2 * ti], a);
-    atomicAdd(&norms[2 * ti + 1], b);
+    if (!carry) atomicAdd(&norms[2 * ti + 1], b);
   }
 }
 
 // ------------------------------------------------------------------------------------------------
 // pass 2: the update
 // ------------------------------------------------------------------------------------------------
+static constexpr int OPT_MAX_ITEM_ROWS = 2048;  // rows one work item may cover (checked at launch)
+
 struct OptHyper {
   float clip, beta, lr, weight_decay;
   int nesterov, act_bf16, grad_bf16;
@@ -91,11 +104,18 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
                                                           const int32_t* __restrict__ item_tensor,
                                                           const int32_t* __restrict__ item_row0,
                                                           const int32_t* __restrict__ item_rows,
-                                                          const double* __restrict__ norms, const OptHyper hp) {
+                                                          const double* __restrict__ norms, const OptHyper hp,
+                                                          double* __restrict__ wnext) {
   extern __shared__ float s_col[];  // [cols] block-level column maxima
+  __shared__ obst_opt_tensor sT;    // the table entry (dynamically indexed: keep it out of local memory)
+  __shared__ double s_w2[8];
+  __shared__ float s_rowmax[OPT_MAX_ITEM_ROWS];
   const int item = blockIdx.x;
   const int ti = item_tensor[item];
-  const obst_opt_tensor T = table[ti];
+  if (item_rows[item] > OPT_MAX_ITEM_ROWS) __trap();  // contract of the work list (include/obst_b200.h)
+  if (threadIdx.x == 0) sT = table[ti];
+  __syncthreads();
+  const obst_opt_tensor& T = sT;
   const int nd = T.ndim;
   const int cols = T.dims[nd - 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -125,116 +145,160 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
   }
   const int row_end = item_row0[item] + item_rows[item];
   const int iters = NI > 0 ? NI : (cols + 32 * VEC - 1) / (32 * VEC);
-  for (int r = item_row0[item] + warp; r < row_end; r += 8) {
-    int idx[3] = {0, 0, 0};
-    float rowmin = INFINITY;
-    {
-      int rem = r;
-      for (int i = nd - 2; i >= 0; --i) {
-        idx[i] = rem % T.dims[i];
-        rem /= T.dims[i];
-        rowmin = fminf(rowmin, ld_state<TS>(T.acc[i], idx[i]));
+  const bool tril_fast = T.tril_s > 0 && T.tril_s == cols;  // [.., S, S] map: col = c + j, row = r % S
+  float w2 = 0.f;  // sum cast_AT(p_new)^2 of this thread: next step's weight norm, for free
+  // RG rows per warp per iteration: all their loads are issued before the first dependent instruction, which is
+  // what gives the memory system enough to do (one row at a time left this kernel latency-bound at < 3 TB/s)
+  constexpr int RG = 4;
+  for (int r0 = item_row0[item] + warp * RG; r0 < row_end; r0 += 8 * RG) {
+    int idx[RG][3];
+    float rowmin[RG], rowmax[RG];
+#pragma unroll
+    for (int q = 0; q < RG; ++q) {
+      rowmin[q] = INFINITY;
+      rowmax[q] = 0.f;
+      int rem = r0 + q;
+#pragma unroll
+      for (int i = 2; i >= 0; --i) {
+        idx[q][i] = 0;
+        if (i <= nd - 2 && r0 + q < row_end) {
+          idx[q][i] = rem % T.dims[i];
+          rem /= T.dims[i];
+          rowmin[q] = fminf(rowmin[q], ld_state<TS>(T.acc[i], idx[q][i]));
+        }
       }
     }
-    const int64_t rbase = (int64_t)r * cols;
-    float rowmax = 0.f;
-#pragma unroll
-    for (int i = 0; i < (NI > 0 ? NI : 64); ++i) {
-      if (i >= iters) break;
+#pragma unroll(NI > 0 ? NI : 1)
+    for (int i = 0; i < iters; ++i) {  // NI > 0: fully unrolled (iters == NI); NI == 0: a plain loop
       const int c = (lane + 32 * i) * VEC;
       if (c >= cols) continue;
-      float pv[VEC], gv[VEC], mv[VEC];
-      if (VEC == 4) {
-        const float4 p4 = *reinterpret_cast<const float4*>(T.p + rbase + c);
-        const float4 g4 = *reinterpret_cast<const float4*>(T.g + rbase + c);
-        pv[0] = p4.x; pv[1] = p4.y; pv[2] = p4.z; pv[3] = p4.w;
-        gv[0] = g4.x; gv[1] = g4.y; gv[2] = g4.z; gv[3] = g4.w;
-        if (sizeof(TS) == 2) {
-          const uint2 m2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(T.m) + rbase + c);
-          const float2 a = unpack_bf16x2(m2.x), b = unpack_bf16x2(m2.y);
-          mv[0] = a.x; mv[1] = a.y; mv[2] = b.x; mv[3] = b.y;
-        } else {
-          const float4 m4 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(T.m) + rbase + c);
-          mv[0] = m4.x; mv[1] = m4.y; mv[2] = m4.z; mv[3] = m4.w;
-        }
-      } else {
+      float pv[RG][VEC], gv[RG][VEC], mv[RG][VEC];
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-          pv[j] = T.p[rbase + c + j];
-          gv[j] = T.g[rbase + c + j];
-          mv[j] = ld_state<TS>(T.m, rbase + c + j);
-        }
-      }
-      float pn[VEC], mn[VEC];
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        float g = hp.grad_bf16 ? round_to<bf16>(gv[j]) : gv[j];
-        g = g * scale;
-        const float a_last = NI > 0 ? al[i * VEC + j] : ld_state<TS>(acc_last, c + j);
-        const float nu = fminf(rowmin, a_last) + g * g;
-        if (NI > 0) cm[i * VEC + j] = fmaxf(cm[i * VEC + j], nu);
-        else atomic_max_nonneg(&s_col[c + j], nu);
-        rowmax = fmaxf(rowmax, nu);
-        float u = g * (1.0f / fmaxf(sqrtf(nu), 1e-5f));
-        const float m_new = hp.beta * mv[j] + u;
-        u = hp.nesterov ? (u + hp.beta * m_new) : m_new;
-        u = u * hp.lr;
-        if (T.decay && hp.weight_decay > 0.f) {
-          const float w = hp.act_bf16 ? round_to<bf16>(pv[j]) : pv[j];
-          u += w * hp.lr * hp.weight_decay;
-        }
-        pn[j] = pv[j] - u;
-        mn[j] = m_new;
-      }
-      // shadow value (what the next forward pass reads), causal mask folded in
-      float sh[VEC];
-#pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        sh[j] = pn[j];
-        if (T.tril_s > 0) {
-          const int64_t e = rbase + c + j;
-          const int col = (int)(e % T.tril_s);
-          const int row = (int)((e / T.tril_s) % T.tril_s);
-          if (col > row) sh[j] = 0.f;
-        }
-      }
-      if (VEC == 4) {
-        *reinterpret_cast<float4*>(T.p + rbase + c) = make_float4(pn[0], pn[1], pn[2], pn[3]);
-        if (sizeof(TS) == 2) {
-          uint2 m2;
-          m2.x = pack_bf16x2(mn[0], mn[1]);
-          m2.y = pack_bf16x2(mn[2], mn[3]);
-          *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(T.m) + rbase + c) = m2;
-        } else {
-          *reinterpret_cast<float4*>(reinterpret_cast<float*>(T.m) + rbase + c) =
-              make_float4(mn[0], mn[1], mn[2], mn[3]);
-        }
-        if (T.shadow) {
-          if (hp.act_bf16) {
-            uint2 s2;
-            s2.x = pack_bf16x2(sh[0], sh[1]);
-            s2.y = pack_bf16x2(sh[2], sh[3]);
-            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(T.shadow) + rbase + c) = s2;
+      for (int q = 0; q < RG; ++q) {
+        if (r0 + q >= row_end) continue;
+        const int64_t rbase = (int64_t)(r0 + q) * cols;
+        if (VEC == 4) {
+          const float4 p4 = *reinterpret_cast<const float4*>(T.p + rbase + c);
+          const float4 g4 = *reinterpret_cast<const float4*>(T.g + rbase + c);
+          pv[q][0] = p4.x; pv[q][1] = p4.y; pv[q][2] = p4.z; pv[q][3] = p4.w;
+          gv[q][0] = g4.x; gv[q][1] = g4.y; gv[q][2] = g4.z; gv[q][3] = g4.w;
+          if (sizeof(TS) == 2) {
+            const uint2 m2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(T.m) + rbase + c);
+            const float2 a = unpack_bf16x2(m2.x), bb = unpack_bf16x2(m2.y);
+            mv[q][0] = a.x; mv[q][1] = a.y; mv[q][2] = bb.x; mv[q][3] = bb.y;
           } else {
-            *reinterpret_cast<float4*>(reinterpret_cast<float*>(T.shadow) + rbase + c) =
-                make_float4(sh[0], sh[1], sh[2], sh[3]);
+            const float4 m4 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(T.m) + rbase + c);
+            mv[q][0] = m4.x; mv[q][1] = m4.y; mv[q][2] = m4.z; mv[q][3] = m4.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) {
+            pv[q][j] = T.p[rbase + c + j];
+            gv[q][j] = T.g[rbase + c + j];
+            mv[q][j] = ld_state<TS>(T.m, rbase + c + j);
           }
         }
-      } else {
+      }
+#pragma unroll
+      for (int q = 0; q < RG; ++q) {
+        if (r0 + q >= row_end) continue;
+        const int r = r0 + q;
+        const int64_t rbase = (int64_t)r * cols;
+        float pn[VEC], mn[VEC], sh[VEC];
+        const int row_in = tril_fast ? (r % cols) : 0;
 #pragma unroll
         for (int j = 0; j < VEC; ++j) {
-          T.p[rbase + c + j] = pn[j];
-          reinterpret_cast<TS*>(T.m)[rbase + c + j] = from_f32<TS>(mn[j]);
+          float g = hp.grad_bf16 ? round_to<bf16>(gv[q][j]) : gv[q][j];
+          g = g * scale;
+          const float a_last = NI > 0 ? al[i * VEC + j] : ld_state<TS>(acc_last, c + j);
+          const float nu = fminf(rowmin[q], a_last) + g * g;
+          if (NI > 0) cm[i * VEC + j] = fmaxf(cm[i * VEC + j], nu);
+          else atomic_max_nonneg(&s_col[c + j], nu);
+          rowmax[q] = fmaxf(rowmax[q], nu);
+          // g / max(sqrt(nu), 1e-5)  (opt_rsqrt, src/optimizer/optimizers.py:13-14) without the IEEE sqrt + divide
+          float u = g * (nu >= 1e-10f ? rsqrtf(nu) : 1e5f);
+          const float m_new = hp.beta * mv[q][j] + u;
+          u = hp.nesterov ? (u + hp.beta * m_new) : m_new;
+          u = u * hp.lr;
+          if (T.decay && hp.weight_decay > 0.f) {
+            const float w = hp.act_bf16 ? round_to<bf16>(pv[q][j]) : pv[q][j];
+            u += w * hp.lr * hp.weight_decay;
+          }
+          pn[j] = pv[q][j] - u;
+          mn[j] = m_new;
+          sh[j] = pn[j];
+          if (tril_fast) {
+            if (c + j > row_in) sh[j] = 0.f;
+          } else if (T.tril_s > 0) {
+            const int64_t e = rbase + c + j;
+            const int col = (int)(e % T.tril_s);
+            const int row = (int)((e / T.tril_s) % T.tril_s);
+            if (col > row) sh[j] = 0.f;
+          }
+          const float wv = hp.act_bf16 ? round_to<bf16>(pn[j]) : pn[j];
+          w2 += wv * wv;
+        }
+        if (VEC == 4) {
+          *reinterpret_cast<float4*>(T.p + rbase + c) = make_float4(pn[0], pn[1], pn[2], pn[3]);
+          if (sizeof(TS) == 2) {
+            uint2 m2;
+            m2.x = pack_bf16x2(mn[0], mn[1]);
+            m2.y = pack_bf16x2(mn[2], mn[3]);
+            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(T.m) + rbase + c) = m2;
+          } else {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(T.m) + rbase + c) =
+                make_float4(mn[0], mn[1], mn[2], mn[3]);
+          }
           if (T.shadow) {
-            if (hp.act_bf16) reinterpret_cast<bf16*>(T.shadow)[rbase + c + j] = __float2bfloat16_rn(sh[j]);
-            else reinterpret_cast<float*>(T.shadow)[rbase + c + j] = sh[j];
+            if (hp.act_bf16) {
+              uint2 s2;
+              s2.x = pack_bf16x2(sh[0], sh[1]);
+              s2.y = pack_bf16x2(sh[2], sh[3]);
+              *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(T.shadow) + rbase + c) = s2;
+            } else {
+              *reinterpret_cast<float4*>(reinterpret_cast<float*>(T.shadow) + rbase + c) =
+                  make_float4(sh[0], sh[1], sh[2], sh[3]);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) {
+            T.p[rbase + c + j] = pn[j];
+            reinterpret_cast<TS*>(T.m)[rbase + c + j] = from_f32<TS>(mn[j]);
+            if (T.shadow) {
+              if (hp.act_bf16) reinterpret_cast<bf16*>(T.shadow)[rbase + c + j] = __float2bfloat16_rn(sh[j]);
+              else reinterpret_cast<float*>(T.shadow)[rbase + c + j] = sh[j];
+            }
           }
         }
       }
     }
-    rowmax = warp_max(rowmax);
-    if (lane == 0) {
-      for (int i = 0; i < nd - 1; ++i) atomic_max_nonneg(T.acc_new[i] + idx[i], rowmax);
+#pragma unroll
+    for (int q = 0; q < RG; ++q) {
+      const float rm = warp_max(rowmax[q]);
+      if (lane == 0 && r0 + q < row_end) s_rowmax[r0 + q - item_row0[item]] = rm;
+    }
+  }
+  __syncthreads();
+  // Row maxima -> accumulators of the non-last dims.  Rows are consecutive, so for each dim the rows sharing an
+  // index form runs; the first row of a run folds the run and issues ONE atomic (a [8, 512, 512] weight would
+  // otherwise send 4096 same-address atomics to each of its 8 dim-0 entries, which serialise in L2).
+  {
+    const int nrows = item_rows[item];
+    for (int rl = threadIdx.x; rl < nrows; rl += blockDim.x) {
+      const int r = item_row0[item] + rl;
+      int stride = 1;
+      for (int i = nd - 2; i >= 0; --i) {
+        const int v = (r / stride) % T.dims[i];
+        const bool first = rl == 0 || ((r - 1) / stride) % T.dims[i] != v;
+        if (first) {
+          float mx = s_rowmax[rl];
+          for (int k = rl + 1; k < nrows && ((item_row0[item] + k) / stride) % T.dims[i] == v; ++k)
+            mx = fmaxf(mx, s_rowmax[k]);
+          atomic_max_nonneg(T.acc_new[i] + v, mx);
+        }
+        stride *= T.dims[i];
+      }
     }
   }
   if (NI > 0) {
@@ -246,10 +310,19 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
         if (c + j < cols && cm[i * VEC + j] > 0.f) atomic_max_nonneg(&s_col[c + j], cm[i * VEC + j]);
     }
   }
+  if (wnext) {
+    const double dw = warp_sum_d((double)w2);
+    if (lane == 0) s_w2[warp] = dw;
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < cols; i += blockDim.x) {
     const float v = s_col[i];
     if (v > 0.f) atomic_max_nonneg(T.acc_new[nd - 1] + i, v);
+  }
+  if (wnext && threadIdx.x == 0) {
+    double a = 0.0;
+    for (int w = 0; w < 8; ++w) a += s_w2[w];
+    atomicAdd(&wnext[ti], a);
   }
 }
 
@@ -274,17 +347,25 @@ extern "C" {
 
 int obst_opt_norms(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
                    const int32_t* item_row0, const int32_t* item_rows, int32_t nitems, int32_t dtype_act,
-                   int32_t grad_bf16, double* norms, void* stream) {
+                   int32_t grad_bf16, double* norms, int32_t flags, double* wnext, int32_t first_tensor,
+                   int32_t tensor_count, void* stream) {
   OBST_REQUIRE(table && norms && ntensors > 0, "obst_opt_norms: bad arguments");
+  const int carry = (flags & 1) != 0;
+  OBST_REQUIRE(!carry || wnext, "obst_opt_norms: carry mode needs wnext");
+  OBST_REQUIRE(first_tensor >= 0 && tensor_count >= 0 && first_tensor + tensor_count <= ntensors,
+               "obst_opt_norms: tensor range [%d, %d) outside the table", first_tensor, first_tensor + tensor_count);
   cudaStream_t st = (cudaStream_t)stream;
-  cudaError_t e = cudaMemsetAsync(norms, 0, sizeof(double) * 2 * (size_t)ntensors, st);
-  if (e != cudaSuccess) {
-    set_error("obst_opt_norms: memset failed: %s", cudaGetErrorString(e));
-    return OBST_ECUDA;
+  if (!(flags & 2)) {
+    cudaError_t e = cudaMemsetAsync(norms + 2 * (size_t)first_tensor, 0, sizeof(double) * 2 * (size_t)tensor_count, st);
+    if (e != cudaSuccess) {
+      set_error("obst_opt_norms: memset failed: %s", cudaGetErrorString(e));
+      return OBST_ECUDA;
+    }
   }
   if (nitems <= 0) return OBST_OK;
   opt_norms_kernel<<<(unsigned)nitems, 256, 0, st>>>(table, item_tensor, item_row0, item_rows,
-                                                     dtype_act == OBST_BF16, grad_bf16, norms);
+                                                     dtype_act == OBST_BF16, grad_bf16, norms, carry, wnext,
+                                                     first_tensor, tensor_count);
   count_launch();
   return check_launch("obst_opt_norms");
 }
@@ -294,7 +375,8 @@ int obst_opt_norms(const obst_opt_tensor* table, int32_t ntensors, const int32_t
 int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
                     const int32_t* item_row0, const int32_t* item_rows, int32_t nitems, int32_t max_cols,
                     int32_t vec4, int32_t dtype_act, int32_t dtype_state, int32_t grad_bf16, const double* norms,
-                    float clip, float beta, int32_t nesterov, float lr, float weight_decay, void* stream) {
+                    double* wnext, float clip, float beta, int32_t nesterov, float lr, float weight_decay,
+                    void* stream) {
   OBST_REQUIRE(table && ntensors > 0 && max_cols > 0, "obst_opt_update: bad arguments");
   OBST_REQUIRE(clip <= 0.f || norms != nullptr, "obst_opt_update: clip > 0 needs norms");
   OBST_REQUIRE(max_cols <= 12288, "obst_opt_update: last dim %d too large (max 12288)", max_cols);
@@ -306,16 +388,15 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
   const size_t smem = (size_t)max_cols * sizeof(float);
   const int vec = vec4 ? 4 : 1;
   const int ni = (max_cols + 32 * vec - 1) / (32 * vec);
-#define OBST_OPT(TS, V, N) \
-  opt_update_kernel<TS, V, N><<<(unsigned)nitems, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, norms, hp)
-#define OBST_OPT_NI(TS, V)                 \
-  do {                                     \
-    if (ni <= 1) OBST_OPT(TS, V, 1);       \
-    else if (ni <= 2) OBST_OPT(TS, V, 2);  \
-    else if (ni <= 4) OBST_OPT(TS, V, 4);  \
-    else if (ni <= 8) OBST_OPT(TS, V, 8);  \
+#define OBST_OPT(TS, V, N)                                                                                     \
+  opt_update_kernel<TS, V, N><<<(unsigned)nitems, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, norms, \
+                                                                    hp, wnext)
+#define OBST_OPT_NI(TS, V)                  \
+  do {                                      \
+    if (ni <= 4) OBST_OPT(TS, V, 4);        \
+    else if (ni <= 8) OBST_OPT(TS, V, 8);   \
     else if (ni <= 16) OBST_OPT(TS, V, 16); \
-    else OBST_OPT(TS, V, 0);               \
+    else OBST_OPT(TS, V, 0);                \
   } while (0)
   if (dtype_state == OBST_BF16) {
     if (vec4) OBST_OPT_NI(bf16, 4);
@@ -430,7 +511,7 @@ extern "C" int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, 
                dim_sum, NA_MAX_DIM_SUM + 4 * 64);
   OBST_REQUIRE(cols <= 12288, "obst_opt_step_noalloc: last dim %d too large (max 12288)", cols);
   const int64_t rows64 = numel / cols;
-  const int rpi = 32768 / cols > 0 ? 32768 / cols : 1;
+  const int rpi = 32768 / cols > 0 ? (32768 / cols < OPT_MAX_ITEM_ROWS ? 32768 / cols : OPT_MAX_ITEM_ROWS) : 1;
   const int64_t nitems64 = (rows64 + rpi - 1) / rpi;
   OBST_REQUIRE(nitems64 <= NA_MAX_ITEMS,
                "obst_opt_step_noalloc: tensor of %lld elements needs %lld work items, the built-in list holds %d "
@@ -478,23 +559,22 @@ extern "C" int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, 
   na_fill_kernel<<<1, 256, 0, st>>>(scratch, f);
   if (clip > 0.f)
     opt_norms_kernel<<<(unsigned)f.nitems, 256, 0, st>>>(table, item_tensor, item_row0, item_rows,
-                                                         dtype_act == OBST_BF16, grad_bf16, norms);
+                                                         dtype_act == OBST_BF16, grad_bf16, norms, 0, nullptr, 0, 0);
   OptHyper hp;
   hp.clip = clip; hp.beta = beta; hp.lr = lr; hp.weight_decay = weight_decay;
   hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
   const size_t smem = (size_t)cols * sizeof(float);
   const int vec = (cols % 4 == 0) ? 4 : 1;
   const int ni = (cols + 32 * vec - 1) / (32 * vec);
-#define OBST_NA(TS, V, N) \
-  opt_update_kernel<TS, V, N><<<(unsigned)f.nitems, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, norms, hp)
-#define OBST_NA_NI(TS, V)                \
-  do {                                   \
-    if (ni <= 1) OBST_NA(TS, V, 1);      \
-    else if (ni <= 2) OBST_NA(TS, V, 2); \
-    else if (ni <= 4) OBST_NA(TS, V, 4); \
-    else if (ni <= 8) OBST_NA(TS, V, 8); \
+#define OBST_NA(TS, V, N)                                                                                     \
+  opt_update_kernel<TS, V, N><<<(unsigned)f.nitems, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, \
+                                                                      norms, hp, nullptr)
+#define OBST_NA_NI(TS, V)                  \
+  do {                                     \
+    if (ni <= 4) OBST_NA(TS, V, 4);        \
+    else if (ni <= 8) OBST_NA(TS, V, 8);   \
     else if (ni <= 16) OBST_NA(TS, V, 16); \
-    else OBST_NA(TS, V, 0);              \
+    else OBST_NA(TS, V, 0);                \
   } while (0)
   if (dtype_state == OBST_BF16) {
     if (vec == 4) OBST_NA_NI(bf16, 4);

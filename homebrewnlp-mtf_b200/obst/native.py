@@ -59,9 +59,9 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
                                   c_void_p]),
     "obst_cast_param": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_void_p]),
     "obst_opt_norms": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_void_p,
-                               c_void_p]),
+                               c_i32, c_void_p, c_i32, c_i32, c_void_p]),
     "obst_opt_update": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32, c_i32,
-                                c_i32, c_void_p, c_float, c_float, c_i32, c_float, c_float, c_void_p]),
+                                c_i32, c_void_p, c_void_p, c_float, c_float, c_i32, c_float, c_float, c_void_p]),
     "obst_opt_finalize": (c_int, [c_void_p, c_i32, c_i32, c_void_p]),
     "obst_opt_step_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, ctypes.POINTER(c_void_p),
                                       ctypes.POINTER(c_i32), c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_float,

@@ -85,7 +85,7 @@ class FusedOptimizer:
         self.depth_ranges: typing.Dict[int, typing.List[int]] = {}
 
         table = (native.OptTensor * len(self.variables))()
-        items_t, items_r0, items_rows = [], [], []
+        items = []  # (class, tensor, row0, rows)
         off = 0
         aoff = 0
         max_cols, vec4 = 1, True
@@ -124,12 +124,25 @@ class FusedOptimizer:
             rows = sz // cols
             max_cols = max(max_cols, cols)
             vec4 &= cols % 4 == 0
-            rpi = max(1, ITEM_ELEMS // cols)
+            # launch class = the register footprint the update kernel needs for this last dim (columns per lane):
+            # tensors of a class share one launch, so narrow tensors are not run with the widest instantiation
+            per_lane = -(-cols // (128 if cols % 4 == 0 else 32))
+            klass = 4 if per_lane <= 4 else (8 if per_lane <= 8 else (16 if per_lane <= 16 else 0))
+            rpi = min(2048, max(1, ITEM_ELEMS // cols))
             for r0 in range(0, rows, rpi):
-                items_t.append(ti)
-                items_r0.append(r0)
-                items_rows.append(min(rpi, rows - r0))
+                items.append((klass if cols % 4 == 0 else -klass - 1, ti, r0, min(rpi, rows - r0), cols))
             off += sz + pd
+        items.sort(key=lambda it: (it[0], it[1], it[2]))
+        items_t = [it[1] for it in items]
+        items_r0 = [it[2] for it in items]
+        items_rows = [it[3] for it in items]
+        self.groups: typing.List[typing.Dict[str, int]] = []
+        for pos, it in enumerate(items):
+            if not self.groups or self.groups[-1]["key"] != it[0]:
+                self.groups.append({"key": it[0], "item0": pos, "items": 0, "max_cols": 1, "vec4": int(it[0] >= 0)})
+            g = self.groups[-1]
+            g["items"] += 1
+            g["max_cols"] = max(g["max_cols"], it[4])
         self.max_cols, self.vec4 = max_cols, vec4
         raw = bytes(table)
         self.table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
@@ -138,6 +151,9 @@ class FusedOptimizer:
         self.item_row0 = torch.tensor(items_r0, dtype=torch.int32, device=dev)
         self.item_rows = torch.tensor(items_rows, dtype=torch.int32, device=dev)
         self.decay_names = [v.name for v in self.variables if is_large_tensor(params, v)]
+        # sum cast_AT(p)^2 per tensor, accumulated by the update itself for the NEXT step's adaptive-clip norm
+        self.wnext = torch.zeros(len(self.variables), dtype=torch.float64, device=dev)
+        self.wnorm_valid = False
 
     @property
     def n_params(self) -> int:
@@ -145,6 +161,11 @@ class FusedOptimizer:
 
     def zero_grad(self):
         self.flat_grad.zero_()
+
+    def invalidate_weight_norms(self):
+        """Call after writing Variable.data from outside the optimizer (weight import): the carried norms are stale."""
+        self.wnorm_valid = False
+        self.wnext.zero_()
 
     def step(self, lr: float):
         lib = native.load()
@@ -155,14 +176,19 @@ class FusedOptimizer:
         act, sdt = native.dtype_code(self.act_dtype), native.dtype_code(self.state_dtype)
         tp, it, ir0, irs = (self.table.data_ptr(), self.item_tensor.data_ptr(), self.item_row0.data_ptr(),
                             self.item_rows.data_ptr())
-        if plan.clip > 0:
-            native.check(lib.obst_opt_norms(tp, nt, it, ir0, irs, self.n_items, act, grad_bf16, self.norms.data_ptr(),
-                                            st), "obst_opt_norms")
-        native.check(lib.obst_opt_update(tp, nt, it, ir0, irs, self.n_items, self.max_cols, int(self.vec4), act, sdt,
-                                         grad_bf16, self.norms.data_ptr(), plan.clip, plan.beta, int(plan.nesterov),
-                                         float(lr), float(p.weight_decay), st), "obst_opt_update")
+        carry = 1 if self.wnorm_valid else 0
+        if plan.clip > 0:  # one pass over every gradient (and, on the first step only, every weight)
+            native.check(lib.obst_opt_norms(tp, nt, it, ir0, irs, self.n_items, act, grad_bf16,
+                                            self.norms.data_ptr(), carry, self.wnext.data_ptr(), 0, nt, st),
+                         "obst_opt_norms")
+        for g in self.groups:
+            o = 4 * g["item0"]
+            native.check(lib.obst_opt_update(tp, nt, it + o, ir0 + o, irs + o, g["items"], g["max_cols"], g["vec4"],
+                                             act, sdt, grad_bf16, self.norms.data_ptr(), self.wnext.data_ptr(),
+                                             plan.clip, plan.beta, int(plan.nesterov), float(lr),
+                                             float(p.weight_decay), st), "obst_opt_update")
         native.check(lib.obst_opt_finalize(tp, nt, sdt, st), "obst_opt_finalize")
-        # fp32 activations without a causal mask read the master slice directly: nothing to refresh
+        self.wnorm_valid = plan.clip > 0
 
 
 def update(ctx: OptimizerCtx):

@@ -174,20 +174,26 @@ typedef struct obst_opt_tensor {
 
 /* Work list (DEVICE arrays, built by the caller once): item i covers rows
  * [item_row0[i], item_row0[i]+item_rows[i]) of tensor item_tensor[i] viewed as [numel/cols, cols]
- * with cols = dims[ndim-1].
- * norms: double[2*ntensors] scratch, zeroed by obst_opt_norms: {sum g^2, sum cast_AT(p)^2}. */
+ * with cols = dims[ndim-1]; an item covers at most 2048 rows.  A call may pass any sub-range of the list (e.g. one depth at a time, so
+ * that the gradients read by obst_opt_norms are still in L2 when obst_opt_update reads them again).
+ * norms: double[2*ntensors] scratch: {sum g^2, sum cast_AT(p)^2} per tensor.  Entries
+ * [first_tensor, first_tensor+tensor_count) are cleared first unless flags&2.
+ * flags&1 ("carry"): sum cast_AT(p)^2 is NOT recomputed (4 B/param less traffic) but moved from
+ * wnext[t], where the previous obst_opt_update accumulated it while writing p; wnext[t] is reset. */
 int obst_opt_norms(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
                    const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
-                   int32_t dtype_act, int32_t grad_bf16, double* norms, void* stream);
+                   int32_t dtype_act, int32_t grad_bf16, double* norms, int32_t flags, double* wnext,
+                   int32_t first_tensor, int32_t tensor_count, void* stream);
 /* reads norms, old accumulators and m; writes p, shadow, m and max-reduces the new SM3
  * accumulators into acc_new (which must be zero on entry; obst_opt_finalize leaves it zero).
- * max_cols = largest last dim over the table (<= 12288); vec4 != 0 promises that every last dim is
- * a multiple of 4.  clip <= 0 skips adaptive_clip (norms may then be NULL). */
+ * max_cols = largest last dim over the items passed (<= 12288); vec4 != 0 promises that every last
+ * dim is a multiple of 4.  clip <= 0 skips adaptive_clip (norms may then be NULL).
+ * wnext (double[ntensors], may be NULL): += sum cast_AT(p_new)^2 per tensor, for the next step's carry. */
 int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
                     const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
-                    int32_t max_cols, int32_t vec4, int32_t dtype_act, int32_t dtype_state, int32_t grad_bf16, const double* norms,
-                    float clip, float beta, int32_t nesterov, float lr, float weight_decay,
-                    void* stream);
+                    int32_t max_cols, int32_t vec4, int32_t dtype_act, int32_t dtype_state,
+                    int32_t grad_bf16, const double* norms, double* wnext, float clip, float beta,
+                    int32_t nesterov, float lr, float weight_decay, void* stream);
 /* acc[i] = cast_state(acc_new[i]); acc_new[i] = 0. */
 int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dtype_state,
                       void* stream);

@@ -39,7 +39,7 @@ def _reference_step(nat, p, shadow, g, m, accs, dims, decay, tril_s, state_dtype
         t.dims[i] = d
     t.numel, t.ndim, t.decay, t.tril_s = p.numel(), len(dims), decay, tril_s
     table = torch.frombuffer(bytearray(bytes(t)), dtype=torch.uint8).to(dev)
-    rpi = max(1, 32768 // cols)
+    rpi = min(2048, max(1, 32768 // cols))
     r0 = list(range(0, rows, rpi))
     it = torch.zeros(len(r0), dtype=torch.int32, device=dev)
     ir0 = torch.tensor(r0, dtype=torch.int32, device=dev)
@@ -49,10 +49,10 @@ def _reference_step(nat, p, shadow, g, m, accs, dims, decay, tril_s, state_dtype
     sdt = nat.dtype_code(state_dtype)
     clip, beta, nesterov, lr, wd = hyper
     nat.check(lib.obst_opt_norms(table.data_ptr(), 1, it.data_ptr(), ir0.data_ptr(), irs.data_ptr(), len(r0),
-                                 nat.BF16, 1, norms.data_ptr(), st), "obst_opt_norms")
+                                 nat.BF16, 1, norms.data_ptr(), 0, None, 0, 1, st), "obst_opt_norms")
     nat.check(lib.obst_opt_update(table.data_ptr(), 1, it.data_ptr(), ir0.data_ptr(), irs.data_ptr(), len(r0), cols,
-                                  int(cols % 4 == 0), nat.BF16, sdt, 1, norms.data_ptr(), clip, beta, nesterov, lr,
-                                  wd, st), "obst_opt_update")
+                                  int(cols % 4 == 0), nat.BF16, sdt, 1, norms.data_ptr(), None, clip, beta, nesterov,
+                                  lr, wd, st), "obst_opt_update")
     nat.check(lib.obst_opt_finalize(table.data_ptr(), 1, sdt, st), "obst_opt_finalize")
     torch.cuda.synchronize()
 
