@@ -178,7 +178,7 @@ def run_b200(args):
     seq = cfg["sequence_length"]
     r0, r1 = shard_rows(gb, rank, world)
     rows = r1 - r0
-    mb = args.micro_batch or max(1, min(rows, 65536 // seq))
+    mb = args.micro_batch or max(1, min(rows, 131072 // seq))
     cfg["micro_batch_size"] = mb
     cfg["device"] = f"cuda:{local_rank}"
     import contextlib

@@ -114,7 +114,10 @@ __device__ __forceinline__ void cp_async_wait() {
 // Each warp streams its rows through a private BSTAGES-deep shared-memory ring with cp.async (no register staging): the
 // next row's x / dy (/ dx) are in flight while the current row is reduced, and the only long-lived registers are
 // the dgamma/dbeta partials -- occupancy AND memory-level parallelism stay high.
-template <typename T, int MAXC, int BSTAGES>
+// SPLIT = warps sharing one row (1 or 2).  A 1024-wide row on one warp needs 32 elements per lane x (z, g, dgamma,
+// dbeta) = 244 registers -> one block per SM; split over two warps it is the 512-wide case again (128 registers,
+// two blocks), at the price of three 64-thread named-barrier exchanges per row for the row statistics.
+template <typename T, int MAXC, int BSTAGES, int SPLIT>
 __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                       const T* __restrict__ gamma, const T* __restrict__ beta,
                                                       T* __restrict__ dx, float* __restrict__ dgamma,
@@ -122,14 +125,20 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
                                                       int tokens_per_block, int act, int relu_mask, int dx_acc) {
   constexpr int N = Raw16<T>::N;
   extern __shared__ __align__(16) uint8_t s_raw[];
+  __shared__ float s_x[4][6][2];  // [row slot][exchange + 3 * row parity][half]
+  __shared__ float s_y[4][2][2];  // second value of the third exchange
   const int lane = threadIdx.x & 31;
   const int warp = threadIdx.x >> 5;
-  const int warps_per_block = blockDim.x >> 5;
-  const int chunks = width / N;
+  const int slots = (blockDim.x >> 5) / SPLIT;  // rows in flight per block iteration
+  const int vw = warp / SPLIT;                  // row slot of this warp
+  const int half = warp % SPLIT;                // which part of the row it owns
+  const int wpart = width / SPLIT;              // columns per warp
+  const int chunks = wpart / N;
+  const int col0 = half * wpart;
   const int h = blockIdx.y;
   const float inv_w = 1.0f / (float)width;
-  const int rowb = width * (int)sizeof(T);
-  // layout: [2*width floats: block reduction][gamma row][beta row][per warp: 2 stages x (x, dy, dx) rows]
+  const int rowb = wpart * (int)sizeof(T);      // bytes of one warp's part of a row
+  // layout: [2*width floats: block reduction][gamma row][beta row][per warp: BSTAGES x (x, dy, dx) row parts]
   float* s_red = reinterpret_cast<float*>(s_raw);
   T* s_gam = reinterpret_cast<T*>(s_raw + 2 * width * sizeof(float));
   T* s_bet = s_gam + width;
@@ -140,6 +149,15 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     s_bet[i] = beta ? beta[(int64_t)h * width + i] : from_f32<T>(0.f);
   }
   __syncthreads();
+
+  // row-wide sum of a per-lane value: warp shuffle, then (SPLIT == 2) one exchange with the partner warp
+  auto row_sum = [&](float v, int slot) -> float {
+    v = warp_sum(v);
+    if (SPLIT == 1) return v;
+    if (lane == 0) s_x[vw][slot][half] = v;
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + vw) : "memory");
+    return s_x[vw][slot][0] + s_x[vw][slot][1];
+  };
 
   float pg[MAXC][N], pb[MAXC][N];
 #pragma unroll
@@ -153,7 +171,7 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
   const int64_t t0 = (int64_t)blockIdx.x * tokens_per_block;
   const int64_t t1 = (t0 + tokens_per_block < tokens) ? t0 + tokens_per_block : tokens;
   auto issue = [&](int64_t t, int stage) {
-    const int64_t off = (t * heads + h) * width;
+    const int64_t off = (t * heads + h) * width + col0;
     uint8_t* base = s_ring + stage * 3 * rowb;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
@@ -167,18 +185,19 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     cp_async_commit();
   };
   int stage = 0;
+  int parity = 0;
 #pragma unroll
   for (int s0 = 0; s0 < BSTAGES - 1; ++s0) {
-    if (t0 + warp + (int64_t)s0 * warps_per_block < t1) issue(t0 + warp + (int64_t)s0 * warps_per_block, s0);
+    if (t0 + vw + (int64_t)s0 * slots < t1) issue(t0 + vw + (int64_t)s0 * slots, s0);
     else cp_async_commit();  // keep one group per slot so wait_group counts stay aligned
   }
-  for (int64_t t = t0 + warp; t < t1; t += warps_per_block, stage = (stage + 1) % BSTAGES) {
-    const int64_t tn = t + (int64_t)(BSTAGES - 1) * warps_per_block;
+  for (int64_t t = t0 + vw; t < t1; t += slots, stage = (stage + 1) % BSTAGES, parity ^= 1) {
+    const int64_t tn = t + (int64_t)(BSTAGES - 1) * slots;
     if (tn < t1) issue(tn, (stage + BSTAGES - 1) % BSTAGES);
     else cp_async_commit();
     cp_async_wait<BSTAGES - 1>();
     __syncwarp();
-    const int64_t off = (t * heads + h) * width;
+    const int64_t off = (t * heads + h) * width + col0;
     const T* sx = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb);
     const T* sdy = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb + rowb);
     const T* sdx = reinterpret_cast<const T*>(s_ring + stage * 3 * rowb + 2 * rowb);
@@ -199,7 +218,7 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
         }
       }
     }
-    const float mean = warp_sum(s) * inv_w;
+    const float mean = row_sum(s, 3 * parity + 0) * inv_w;
     float q = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
@@ -211,7 +230,7 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
         }
       }
     }
-    const float rstd = rsqrtf(warp_sum(q) * inv_w + GN_EPS);
+    const float rstd = rsqrtf(row_sum(q, 3 * parity + 1) * inv_w + GN_EPS);
     float sg = 0.f, sgz = 0.f;
     unsigned long long maskbits = 0;  // bit (i*N+j) <= 63: raw x > 0 (ReLU mask), taken before x becomes z
 #pragma unroll
@@ -220,9 +239,9 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
       if (c < chunks) {
         Vec16<T> dv, gam;
         dv.load(sdy + c * N);
-        gam.load(s_gam + c * N);
+        gam.load(s_gam + col0 + c * N);
         Vec16<T> bet;
-        if (act == 1) bet.load(s_bet + c * N);
+        if (act == 1) bet.load(s_bet + col0 + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
           if (relu_mask && zv[i][j] > 0.f) maskbits |= 1ull << (i * N + j);
@@ -239,8 +258,22 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
         }
       }
     }
-    const float mg = warp_sum(sg) * inv_w;
-    const float mgz = warp_sum(sgz) * inv_w;
+    // one exchange for both sums: pack them through two slots of the same barrier round
+    float mg, mgz;
+    if (SPLIT == 1) {
+      mg = warp_sum(sg) * inv_w;
+      mgz = warp_sum(sgz) * inv_w;
+    } else {
+      sg = warp_sum(sg);
+      sgz = warp_sum(sgz);
+      if (lane == 0) {
+        s_x[vw][3 * parity + 2][half] = sg;
+        s_y[vw][parity][half] = sgz;
+      }
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + vw) : "memory");
+      mg = (s_x[vw][3 * parity + 2][0] + s_x[vw][3 * parity + 2][1]) * inv_w;
+      mgz = (s_y[vw][parity][0] + s_y[vw][parity][1]) * inv_w;
+    }
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
@@ -265,8 +298,8 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     if (c < chunks) {
 #pragma unroll
       for (int j = 0; j < N; ++j) {
-        if (dgamma) atomicAdd(&s_red[c * N + j], pg[i][j]);
-        if (dbeta) atomicAdd(&s_red[width + c * N + j], pb[i][j]);
+        if (dgamma) atomicAdd(&s_red[col0 + c * N + j], pg[i][j]);
+        if (dbeta) atomicAdd(&s_red[width + col0 + c * N + j], pb[i][j]);
       }
     }
   }
@@ -317,28 +350,36 @@ static int gn_bwd_launch(const void* dy, const void* x, const void* gamma, const
   while (tpb > 8 && ((tokens + tpb - 1) / tpb) * heads < (int64_t)num_sms() * 4) tpb >>= 1;
   dim3 grid((unsigned)((tokens + tpb - 1) / tpb), (unsigned)heads);
   const size_t rowb = (size_t)width * sizeof(T);
-  // ring depth: 4 rows per warp where two blocks still fit an SM, else 2
-  const bool deep = (2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * 4 * 3 * rowb) <= 100 * 1024;
+  // wide rows (more than 2 x 16 B chunks per lane) are split over two warps: per-lane state halves
+  const int split = (per_lane > 2 && per_lane % 2 == 0 && (width / N) % 64 == 0) ? 2 : 1;
+  const int pl = per_lane / split;
+  // ring depth: 4 row parts per warp where two blocks still fit an SM, else 2
+  const bool deep = (2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * 4 * 3 * (rowb / split)) <= 100 * 1024;
   const int bst = deep ? 4 : 2;
-  const size_t smem = 2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * (size_t)bst * 3 * rowb;
+  const size_t smem = 2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * (size_t)bst * 3 * (rowb / split);
   OBST_REQUIRE(smem <= 220 * 1024, "obst_gn_bwd: width %d needs %zu B of shared memory", width, smem);
-#define OBST_GN_BWD1(MC, ST)                                                                                    \
-  do {                                                                                                          \
-    if (smem > 48 * 1024)                                                                                       \
-      cudaFuncSetAttribute(gn_bwd_kernel<T, MC, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
-    gn_bwd_kernel<T, MC, ST><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma,              \
-                                                       (const T*)beta, (T*)dx, dgamma, dbeta, tokens, heads,   \
-                                                       width, tpb, act, relu_mask, dx_acc);                    \
+#define OBST_GN_BWD1(MC, ST, SP)                                                                                  \
+  do {                                                                                                            \
+    if (smem > 48 * 1024)                                                                                         \
+      cudaFuncSetAttribute(gn_bwd_kernel<T, MC, ST, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    gn_bwd_kernel<T, MC, ST, SP><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma,            \
+                                                           (const T*)beta, (T*)dx, dgamma, dbeta, tokens, heads, \
+                                                           width, tpb, act, relu_mask, dx_acc);                  \
   } while (0)
-#define OBST_GN_BWD(MC)            \
-  do {                             \
-    if (deep) OBST_GN_BWD1(MC, 4); \
-    else OBST_GN_BWD1(MC, 2);      \
+#define OBST_GN_BWD(MC, SP)            \
+  do {                                 \
+    if (deep) OBST_GN_BWD1(MC, 4, SP); \
+    else OBST_GN_BWD1(MC, 2, SP);      \
   } while (0)
-  if (per_lane <= 1) OBST_GN_BWD(1);
-  else if (per_lane <= 2) OBST_GN_BWD(2);
-  else if (per_lane <= 4) OBST_GN_BWD(4);
-  else OBST_GN_BWD(8);
+  if (split == 2) {
+    if (pl <= 2) OBST_GN_BWD(2, 2);
+    else OBST_GN_BWD(4, 2);
+  } else {
+    if (pl <= 1) OBST_GN_BWD(1, 1);
+    else if (pl <= 2) OBST_GN_BWD(2, 1);
+    else if (pl <= 4) OBST_GN_BWD(4, 1);
+    else OBST_GN_BWD(8, 1);
+  }
 #undef OBST_GN_BWD1
 #undef OBST_GN_BWD
   count_launch();
