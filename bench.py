@@ -303,8 +303,33 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+class _JsonOnlyStdout:
+    """The contract is ONE JSON line on stdout: everything else the libraries print (the reference-style config
+    warnings, torch chatter) is diverted to stderr."""
+
+    def __init__(self):
+        self.real = sys.stdout
+        self.json_open = False
+
+    def write(self, text):
+        if text.lstrip().startswith("{\""):
+            self.json_open = True
+            self.real.write(text)
+        elif self.json_open and text.strip() == "":
+            self.real.write(text)  # the newline that print() sends after the JSON text
+            self.json_open = False
+        else:
+            self.json_open = False
+            sys.stderr.write(text)
+
+    def flush(self):
+        self.real.flush()
+        sys.stderr.flush()
+
+
 if __name__ == "__main__":
     a = parse()
+    sys.stdout = _JsonOnlyStdout()
     if a.impl == "reference":
         run_reference(a)
     else:
