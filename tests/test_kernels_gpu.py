@@ -282,3 +282,60 @@ def test_cast_param_tril(nat):
     dst2 = torch.empty(H, S, S, dtype=torch.float32, device=DEV)
     nat.cast_param(src, dst2)
     assert torch.equal(dst2, src)
+
+
+# ---------------------------------------------------------------------------------------------------
+# edge cases: empty inputs, ragged sizes, the largest mixing map of the reference configs
+# ---------------------------------------------------------------------------------------------------
+def test_empty_inputs_are_no_ops(nat):
+    e = torch.empty(0, dtype=torch.bfloat16, device=DEV)
+    before = nat.launch_count()
+    nat.gn_fwd(e.view(0, 8, 64), None, None, e.view(0, 8, 64), 8, 64)
+    nat.gn_bwd(e.view(0, 8, 64), e.view(0, 8, 64), None, None, e.view(0, 8, 64), None, None, 8, 64)
+    nat.act_fwd(0, e, e)
+    nat.axpby(e, e, 1.0, e)
+    nat.xent_fwd_bwd(e.view(0, 256), torch.empty(0, dtype=torch.int32, device=DEV), e.view(0, 256),
+                     torch.zeros(3, dtype=torch.float64, device=DEV), 1.0, 1e-4)
+    nat.embed_gather(torch.empty(0, dtype=torch.int32, device=DEV), torch.zeros(4, 8, dtype=torch.bfloat16, device=DEV),
+                     e.view(0, 8))
+    assert nat.launch_count() == before  # nothing was launched, nothing failed
+
+
+def test_gemm_rejects_bad_descriptors(nat):
+    a = randn(128, 64)
+    d = torch.empty(128, 128, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(nat.NativeError, match="epilogue 2 needs R"):
+        nat.gemm(nat.operand(a, 64, 1), nat.operand(a, 64, 1), d, 128, 128, 64, d_ld=128, epi=2)
+    with pytest.raises(nat.NativeError, match="accumulate needs fp32"):
+        nat.gemm(nat.operand(a, 64, 1), nat.operand(a, 64, 1), d, 128, 128, 64, d_ld=128, accumulate=True)
+    with pytest.raises(nat.NativeError, match="tri 3 needs accumulate"):
+        nat.gemm(nat.operand(a, 64, 1), nat.operand(a, 64, 1), d, 128, 128, 64, d_ld=128, tri=3)
+    with pytest.raises(nat.NativeError):  # tcgen05 backend cannot address a row stride of 5 elements
+        nat.gemm(nat.operand(a, 5, 1), nat.operand(a, 64, 1), d, 16, 128, 4, d_ld=128, backend=2)
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 520, 136), (257, 72, 1000), (129, 8, 64)])
+def test_gemm_ragged_sizes_tc(nat, M, N, K):
+    a = randn(M, K, seed=40)
+    b = randn(N, K, seed=41)
+    d = torch.full((M + 3, N), 7.0, dtype=torch.bfloat16, device=DEV)  # 3 guard rows must stay untouched
+    nat.gemm(nat.operand(a, K, 1), nat.operand(b, K, 1), d, M, N, K, d_ld=N, backend=2)
+    assert max_rel(d[:M], a.float() @ b.float().t()) < 1e-2
+    assert float((d[M:].float() - 7.0).abs().max()) == 0.0
+
+
+def test_token_mix_at_the_longest_context_of_the_reference_configs(nat):
+    """configs/32ctx_mixer.json: sequence 2048, 256 features per head."""
+    Bn, H, S, K = 2, 2, 2048, 256
+    F = H * K
+    mix = torch.tril(randn(H, S, S, seed=42, scale=0.02).float()).to(torch.bfloat16)
+    x = randn(Bn, S, H, K, seed=43)
+    out = torch.empty_like(x)
+    nat.gemm(nat.operand(mix, S, 1, s_glo=S * S), nat.operand(x, 1, F, s_glo=K, s_ghi=S * F), out, S, K, S, GLO=H,
+             GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, tri=1)
+    assert max_rel(out, torch.einsum("hst,bthk->bshk", mix.float(), x.float())) < 1e-2
+    dm = torch.zeros(H, S, S, device=DEV)
+    nat.gemm(nat.operand(out, F, 1, s_ko=S * F, s_glo=K), nat.operand(x, F, 1, s_ko=S * F, s_glo=K), dm, S, S, K,
+             KO=Bn, GLO=H, d_ld=S, d_glo=S * S, tri=3, accumulate=True)
+    ref = torch.tril(torch.einsum("bshk,bthk->hst", out.float(), x.float()))
+    assert max_rel(dm, ref) < 1e-4

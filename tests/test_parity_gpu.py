@@ -259,3 +259,42 @@ def test_bf16_step_parity(cuda, backend):
     for name, var in byname.items():
         err = rel(to_np(var.grad), grads[name])
         assert err < budget(rel(gtwin[name], grads[name]), 2e-2), (name, err)
+
+
+def test_ragged_micro_batches(cuda):
+    """5 rows in micro-batches of 2 (2 + 2 + 1): same loss and gradients as one pass."""
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=5, sequence_length=64)
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=7)
+    tok_x, tok_y = orc.synthetic_tokens(sh)
+    res = []
+    for mb in (None, 2):
+        params = make_params(cfg, op, micro_batch_size=mb)
+        params.global_step = 4096
+        _, scal = run_product_step(params, tok_x, tok_y)
+        res.append((scal["loss"], {k: to_np(v.grad) for k, v in variables_by_oracle_name(params, sh).items()}))
+    loss, _, state = orc.forward(sh, op, tok_x, tok_y, dtype=np.float64)
+    assert abs(res[1][0] - loss) / loss < 1e-5
+    for k in res[0][1]:
+        assert rel(res[1][1][k], res[0][1][k]) < 1e-5, k
+
+
+def test_unsupported_layers_and_optimizers_fail_loudly(cuda):
+    from obst.run.train import get_train_model
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=64)
+    cfg["block_config"] = [{"layer": ["norm-shift-scale-features-group", "rezero"]}]
+    sh = orc.Shapes(orc.TINY_CONFIG)
+    from obst.dataclass import ModelParameter, gpt_mode
+    params = ModelParameter(gpt_mode(cfg))
+    x = torch.zeros(2, 64, 1, dtype=torch.int32, device="cuda")
+    with pytest.raises(NotImplementedError, match="rezero"):
+        get_train_model(params, None, None, None, x, x, None, None, None, 0)
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=64, optimizer="adam-learning_rate")
+    params = ModelParameter(gpt_mode(cfg))
+    with pytest.raises(NotImplementedError, match="adam"):
+        get_train_model(params, None, None, None, x, x, None, None, None, 0)
+    with pytest.raises(NotImplementedError, match="video"):
+        get_train_model(params, x, None, None, x, x, None, None, None, 0)
