@@ -37,6 +37,9 @@ def parse():
     ap.add_argument("--depth", type=int, default=0, help="override depth (debug only: makes the number INVALID)")
     ap.add_argument("--cpu-rows", type=int, default=1, help="sequences per step of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--store-activations", action="store_true",
+                    help="extension: keep activations instead of the reference's reversible recompute (reported "
+                         "separately; the default run is the reference algorithm)")
     return ap.parse_args()
 
 
@@ -178,7 +181,8 @@ def run_b200(args):
     seq = cfg["sequence_length"]
     r0, r1 = shard_rows(gb, rank, world)
     rows = r1 - r0
-    mb = args.micro_batch or max(1, min(rows, 131072 // seq))
+    mb = args.micro_batch or max(1, min(rows, (32768 if args.store_activations else 131072) // seq))
+    cfg["revnet_store_activations"] = bool(args.store_activations)
     cfg["micro_batch_size"] = mb
     cfg["device"] = f"cuda:{local_rank}"
     import contextlib
@@ -295,6 +299,8 @@ def run_b200(args):
             "gpu_launches": launches, "roofline": roofline}
     if args.depth:
         line["INVALID"] = "depth override"
+    if args.store_activations:
+        line["config"]["extension"] = "revnet_store_activations (no recompute / reconstruction in backward)"
     if world == 1 and not args.no_cpu_baseline:
         v, cores, sample, _ = cpu_step_rate(args.workload, args.cpu_rows, 1, 0, args.depth)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}

@@ -10,6 +10,9 @@ Extensions (no counterpart in the reference, all optional):
                     accumulated in fp32), None = whole local batch
   gemm_backend      0 auto | 1 SIMT | 2 tcgen05   (include/obst_b200.h)
   device            torch device string
+  revnet_store_activations  keep every sub-block's intermediates instead of recomputing / reconstructing them in
+                    backward (memory for speed; numerics differ from the reversible path only by the reference's
+                    reconstruction rounding).  Default false = the reference's algorithm.
 """
 import copy
 import random
@@ -56,7 +59,8 @@ DEFAULTS: typing.Dict[str, typing.Any] = dict(
     weight_decay=0.001, weight_standardisation=True, z_loss=0.0001,
 )
 # extensions of this implementation (see module docstring)
-EXTENSIONS: typing.Dict[str, typing.Any] = dict(micro_batch_size=None, gemm_backend=0, device="cuda", init_seed=0)
+EXTENSIONS: typing.Dict[str, typing.Any] = dict(micro_batch_size=None, gemm_backend=0, device="cuda", init_seed=0,
+                                                revnet_store_activations=False)
 
 
 class BlockConfig:

@@ -242,12 +242,11 @@ def linear(args: BlockArgs, old: DIM_LIST, new: DIM_LIST, relu: bool = False) ->
     xin = x.data
     if residual is not None:
         params.residual = None
-        buf, sign = residual
+        buf, sign, out = residual  # out = buf +/- x@W; out is buf itself for the in-place (reversible) case
         if relu or tuple(buf.shape) != tuple(d.size for d in out_dims):
             raise NotImplementedError("linear: residual fusion needs a plain final linear of matching shape")
-        out = buf
         native.gemm(native.operand(xin, G * Kc, 1, s_glo=Kc), native.operand(w, 1, Np, s_glo=Kc * Np), out, M, Np, Kc,
-                    GLO=G, d_ld=G * Np, d_glo=Np, R=out, epi=2 if sign > 0 else 3, dtype_in=dt, backend=be)
+                    GLO=G, d_ld=G * Np, d_glo=Np, R=buf, epi=2 if sign > 0 else 3, dtype_in=dt, backend=be)
     else:
         out = torch.empty([d.size for d in out_dims], dtype=dt, device=xin.device)
         native.gemm(native.operand(xin, G * Kc, 1, s_glo=Kc), native.operand(w, 1, Np, s_glo=Kc * Np), out, M, Np, Kc,

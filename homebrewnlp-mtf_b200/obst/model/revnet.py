@@ -17,17 +17,61 @@ from .backend import TapeEntry, reset_shared_ordinals, run_tape
 from .frontend import block_part_fn
 
 
-def _apply(params: ModelParameter, config: BlockConfig, index: int, x2: Tensor, x1_buf: torch.Tensor, sign: float):
-    """x1_buf <- x1_buf + sign * f(x2), fused into f's last GEMM when that layer supports it."""
-    params.residual = (x1_buf, sign)
+def _apply(params: ModelParameter, config: BlockConfig, index: int, x2: Tensor, x1_buf: torch.Tensor, sign: float,
+           out: typing.Optional[torch.Tensor] = None):
+    """out <- x1_buf + sign * f(x2) (out defaults to x1_buf: in place), fused into f's last GEMM when that layer
+    supports it."""
+    out = x1_buf if out is None else out
+    params.residual = (x1_buf, sign, out)
     f = block_part_fn(params, config, x2, str(index))
     if params.residual is not None:  # last layer could not fuse the residual
         params.residual = None
-        native.axpby(x1_buf, f.data, sign, x1_buf)
+        native.axpby(x1_buf, f.data, sign, out)
+
+
+def stored_body(params: ModelParameter, src: Tensor) -> Tensor:
+    """EXTENSION (`revnet_store_activations: true`, not a reference mode): the same reversible wiring
+    (x1, x2) -> (x2, x1 + f(x2)), but every sub-block's intermediates are KEPT (180 GB of HBM hold ~40 k tokens x
+    32 depths), so backward neither recomputes f nor reconstructs x1.  Gradients differ from the reversible path
+    only by the reconstruction rounding the reference incurs (they are closer to the exact ones)."""
+    dims = src.dims
+    p, q = src.data, src.data
+    outer_tape = params.tape
+    tapes: typing.List[list] = []
+    for i in range(params.depth):
+        for config in params.block_config:
+            sub: list = [] if outer_tape is not None else None
+            params.tape = sub
+            y = torch.empty_like(p)
+            _apply(params, config, i, Tensor(q, dims), p, 1.0, out=y)
+            tapes.append(sub)
+            p, q = q, y
+    out = torch.empty_like(p)
+    native.axpby(p, q, 1.0, out)
+    params.tape = outer_tape
+    if outer_tape is not None:
+        n_cfg = len(params.block_config)
+
+        def bwd(dout: torch.Tensor, mask, acc):
+            dp, dq = dout, dout.clone()
+            reducer = getattr(params, "grad_reducer", None)
+            for j in range(len(tapes) - 1, -1, -1):
+                run_tape(tapes[j], dq, acc=dp)  # dp <- dy2 + J^T dy1
+                tapes[j] = None                 # frees this sub-block's activations
+                dp, dq = dq, dp
+                if j % n_cfg == 0 and reducer is not None:
+                    reducer.on_depth_done(j // n_cfg)
+            native.axpby(dp, dq, 1.0, dp)
+            return dp
+
+        outer_tape.append(TapeEntry(bwd))
+    return Tensor(out, dims)
 
 
 def reversible_body(params: ModelParameter, src: Tensor) -> Tensor:
     """_body for memory_reduction_strategy == 'revnet' (src/model/__init__.py:101-106,124-129)."""
+    if getattr(params, "revnet_store_activations", False):
+        return stored_body(params, src)
     dims = src.dims
     p = src.data.clone()  # x1
     q = src.data          # x2 (src itself is not needed again: its gradient path is dp + dq)

@@ -43,8 +43,8 @@ def attention(args: BlockArgs) -> Tensor:
     a_op = native.operand(w, S, 1, s_glo=S * S)
     if residual is not None:
         params.residual = None
-        out, sign = residual
-        native.gemm(a_op, b_op, out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, R=out,
+        buf, sign, out = residual
+        native.gemm(a_op, b_op, out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, R=buf,
                     epi=2 if sign > 0 else 3, tri=1 if masked else 0, dtype_in=dt, backend=be)
     else:
         out = torch.empty_like(xin)

@@ -298,3 +298,20 @@ def test_unsupported_layers_and_optimizers_fail_loudly(cuda):
         get_train_model(params, None, None, None, x, x, None, None, None, 0)
     with pytest.raises(NotImplementedError, match="video"):
         get_train_model(params, x, None, None, x, x, None, None, None, 0)
+
+
+def test_store_activations_extension_matches_the_float64_oracle(cuda):
+    """revnet_store_activations keeps the forward intermediates instead of recomputing/reconstructing: its fp32
+    gradients must sit at the plain 1e-5 bar for EVERY tensor (no reconstruction error to budget for)."""
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=0)
+    tok_x, tok_y = orc.synthetic_tokens(sh)
+    params = make_params(cfg, op, revnet_store_activations=True, micro_batch_size=4)
+    params.global_step = 2048
+    _, scal = run_product_step(params, tok_x, tok_y)
+    loss, acc, state = orc.forward(sh, op, tok_x, tok_y, dtype=np.float64)
+    grads = orc.backward(sh, state)
+    assert abs(scal["loss"] - loss) / loss < 1e-5
+    for name, var in variables_by_oracle_name(params, sh).items():
+        assert rel(to_np(var.grad), grads[name]) < 1e-5, name
