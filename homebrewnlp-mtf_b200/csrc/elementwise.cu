@@ -12,10 +12,10 @@ static constexpr float GN_EPS = 1e-5f;  // src/model/normalization.py:28
 // ================================================================================================
 // ROWS rows are in flight per warp (all their loads are issued before the first reduction): with one 1 KB row per
 // warp the kernel is latency-bound at ~60 % of HBM; 4 rows give the memory system 8 x 16 B per lane to chew on.
-template <typename T, int MAXC, int ROWS>
+template <typename T, int MAXC, int ROWS, int ACT>
 __global__ void __launch_bounds__(256) gn_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma,
                                                       const T* __restrict__ beta, T* __restrict__ y, int64_t rows,
-                                                      int heads, int width, int act) {
+                                                      int heads, int width) {
   constexpr int N = Vec16<T>::N;
   const int lane = threadIdx.x & 31;
   const int warps_per_block = blockDim.x >> 5;
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(256) gn_fwd_kernel(const T* __restrict__ x, co
             float o = v[r][i].v[j] * q[r];
             if (gamma) o *= g.v[j];
             if (beta) o += b.v[j];
-            if (act == 1) o = gelu_obst(o);
+            if (ACT == 1) o = gelu_obst(o);
             v[r][i].v[j] = o;
           }
           v[r][i].store(yr + c * N);
@@ -117,12 +117,12 @@ __device__ __forceinline__ void cp_async_wait() {
 // SPLIT = warps sharing one row (1 or 2).  A 1024-wide row on one warp needs 32 elements per lane x (z, g, dgamma,
 // dbeta) = 244 registers -> one block per SM; split over two warps it is the 512-wide case again (128 registers,
 // two blocks), at the price of three 64-thread named-barrier exchanges per row for the row statistics.
-template <typename T, int MAXC, int BSTAGES, int SPLIT>
+template <typename T, int MAXC, int BSTAGES, int SPLIT, int ACT>
 __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                       const T* __restrict__ gamma, const T* __restrict__ beta,
                                                       T* __restrict__ dx, float* __restrict__ dgamma,
                                                       float* __restrict__ dbeta, int64_t tokens, int heads, int width,
-                                                      int tokens_per_block, int act, int relu_mask, int dx_acc) {
+                                                      int tokens_per_block, int relu_mask, int dx_acc) {
   constexpr int N = Raw16<T>::N;
   extern __shared__ __align__(16) uint8_t s_raw[];
   __shared__ float s_x[4][6][2];  // [row slot][exchange + 3 * row parity][half]
@@ -241,14 +241,14 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
         dv.load(sdy + c * N);
         gam.load(s_gam + col0 + c * N);
         Vec16<T> bet;
-        if (act == 1) bet.load(s_bet + col0 + c * N);
+        if (ACT == 1) bet.load(s_bet + col0 + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
           if (relu_mask && zv[i][j] > 0.f) maskbits |= 1ull << (i * N + j);
           const float z = (zv[i][j] - mean) * rstd;
           zv[i][j] = z;
           float d = dv.v[j];
-          if (act == 1) d *= gelu_obst_grad(z * gam.v[j] + bet.v[j]);
+          if (ACT == 1) d *= gelu_obst_grad(z * gam.v[j] + bet.v[j]);
           pb[i][j] += d;
           pg[i][j] += d * z;
           const float g = d * gam.v[j];
@@ -323,9 +323,17 @@ static int gn_fwd_launch(const void* x, const void* gamma, const void* beta, voi
   const int64_t cap = (int64_t)num_sms() * 8;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-#define OBST_GN_FWD(MC, R)                                                                                       \
-  gn_fwd_kernel<T, MC, R><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma, (const T*)beta, \
-                                                                   (T*)y, rows, heads, width, act)
+#define OBST_GN_FWD(MC, R)                                                                                      \
+  do {                                                                                                          \
+    if (act == 1)                                                                                               \
+      gn_fwd_kernel<T, MC, R, 1><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma,          \
+                                                                          (const T*)beta, (T*)y, rows, heads,   \
+                                                                          width);                               \
+    else                                                                                                        \
+      gn_fwd_kernel<T, MC, R, 0><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma,          \
+                                                                          (const T*)beta, (T*)y, rows, heads,   \
+                                                                          width);                               \
+  } while (0)
   if (per_lane <= 1) OBST_GN_FWD(1, 1);
   else if (per_lane <= 2) OBST_GN_FWD(2, 1);
   else if (per_lane <= 4) OBST_GN_FWD(4, 1);
@@ -358,13 +366,18 @@ static int gn_bwd_launch(const void* dy, const void* x, const void* gamma, const
   const int bst = deep ? 4 : 2;
   const size_t smem = 2 * (size_t)width * sizeof(float) + 2 * rowb + 8 * (size_t)bst * 3 * (rowb / split);
   OBST_REQUIRE(smem <= 220 * 1024, "obst_gn_bwd: width %d needs %zu B of shared memory", width, smem);
-#define OBST_GN_BWD1(MC, ST, SP)                                                                                  \
-  do {                                                                                                            \
-    if (smem > 48 * 1024)                                                                                         \
-      cudaFuncSetAttribute(gn_bwd_kernel<T, MC, ST, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
-    gn_bwd_kernel<T, MC, ST, SP><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma,            \
-                                                           (const T*)beta, (T*)dx, dgamma, dbeta, tokens, heads, \
-                                                           width, tpb, act, relu_mask, dx_acc);                  \
+#define OBST_GN_BWD2(MC, ST, SP, AC)                                                                                  \
+  do {                                                                                                                \
+    if (smem > 48 * 1024)                                                                                             \
+      cudaFuncSetAttribute(gn_bwd_kernel<T, MC, ST, SP, AC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    gn_bwd_kernel<T, MC, ST, SP, AC><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma,            \
+                                                               (const T*)beta, (T*)dx, dgamma, dbeta, tokens, heads, \
+                                                               width, tpb, relu_mask, dx_acc);                       \
+  } while (0)
+#define OBST_GN_BWD1(MC, ST, SP)               \
+  do {                                         \
+    if (act == 1) OBST_GN_BWD2(MC, ST, SP, 1); \
+    else OBST_GN_BWD2(MC, ST, SP, 0);          \
   } while (0)
 #define OBST_GN_BWD(MC, SP)            \
   do {                                 \
@@ -380,6 +393,7 @@ static int gn_bwd_launch(const void* dy, const void* x, const void* gamma, const
     else if (pl <= 4) OBST_GN_BWD(4, 1);
     else OBST_GN_BWD(8, 1);
   }
+#undef OBST_GN_BWD2
 #undef OBST_GN_BWD1
 #undef OBST_GN_BWD
   count_launch();
