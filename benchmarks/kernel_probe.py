@@ -59,6 +59,16 @@ def main():
         rep(f"W_mid fwd [{tag}] T x8192 x512", ms, 2 * T * I * H * K2)
         ms = timeit(lambda: nat.gemm(nat.operand(h2, H * K2, 1, s_glo=K2), nat.operand(wout, 1, K, s_glo=K2 * K), y, T, K, K2, GLO=H, d_ld=F, d_glo=K, R=y, epi=2, backend=be))
         rep(f"W_out fwd grouped [{tag}]", ms, 2 * T * H * K2 * K)
+        # the same forward GEMMs with the weight stored transposed (B K-major instead of MN-major)
+        win_t = win.t().contiguous()
+        ms = timeit(lambda: nat.gemm(nat.operand(x, F, 1), nat.operand(win_t, F, 1), h1, T, I, F, d_ld=I, epi=1, backend=be))
+        rep(f"W_in fwd, W^T stored [{tag}]", ms, 2 * T * I * F)
+        wmid_t = wmid.t().contiguous()
+        ms = timeit(lambda: nat.gemm(nat.operand(h1, I, 1), nat.operand(wmid_t, I, 1), h2, T, H * K2, I, d_ld=H * K2, epi=1, backend=be))
+        rep(f"W_mid fwd, W^T stored [{tag}]", ms, 2 * T * I * H * K2)
+        wout_t = wout.transpose(1, 2).contiguous()
+        ms = timeit(lambda: nat.gemm(nat.operand(h2, H * K2, 1, s_glo=K2), nat.operand(wout_t, K2, 1, s_glo=K2 * K), y, T, K, K2, GLO=H, d_ld=F, d_glo=K, R=y, epi=2, backend=be))
+        rep(f"W_out fwd grouped, W^T stored [{tag}]", ms, 2 * T * H * K2 * K)
         # dgrads
         dh2 = torch.empty(T, H * K2, device=DEV, dtype=bf)
         ms = timeit(lambda: nat.gemm(nat.operand(y, F, 1, s_glo=K), nat.operand(wout, K, 1, s_glo=K2 * K), dh2, T, K2, K, GLO=H, d_ld=H * K2, d_glo=K2, backend=be))
@@ -95,6 +105,10 @@ def main():
     rep("torch.matmul 8192^3 (cuBLAS)", ms, 2 * 8192 ** 3)
     ms = timeit(lambda: torch.matmul(x, win))
     rep("torch.matmul W_in shape (cuBLAS)", ms, 2 * T * I * F)
+    ms = timeit(lambda: torch.matmul(h1, wmid, out=h2))
+    rep("torch.matmul W_mid fwd shape (cuBLAS)", ms, 2 * T * I * H * K2)
+    ms = timeit(lambda: torch.matmul(h2, wmid.t(), out=h1))
+    rep("torch.matmul W_mid dgrad shape (cuBLAS)", ms, 2 * T * I * H * K2)
     # bandwidth kernels
     gam = torch.ones(H, K, device=DEV, dtype=bf)
     bet = torch.zeros(H, K, device=DEV, dtype=bf)
@@ -104,6 +118,22 @@ def main():
     db = torch.zeros(H, K, device=DEV)
     ms = timeit(lambda: nat.gn_bwd(y, x, gam, bet, out, dg, db, H, K))
     rep("gn_bwd [T,8,512]", ms, bytes_=3 * T * F * 2)
+    ms = timeit(lambda: nat.gn_fwd(x, gam, bet, y, H, K, 1))
+    rep("gn_fwd + gelu [T,8,512]", ms, bytes_=2 * T * F * 2)
+    ms = timeit(lambda: nat.gn_bwd(y, x, gam, bet, out, dg, db, H, K, 1))
+    rep("gn_bwd + gelu [T,8,512]", ms, bytes_=3 * T * F * 2)
+    ms = timeit(lambda: nat.gn_bwd(y, x, gam, bet, out, dg, db, H, K, 0, False, True))
+    rep("gn_bwd dx+= [T,8,512]", ms, bytes_=4 * T * F * 2)
+    gam2 = torch.ones(H, K2, device=DEV, dtype=bf)
+    bet2 = torch.zeros(H, K2, device=DEV, dtype=bf)
+    n2 = torch.empty_like(h2)
+    h2.normal_()
+    ms = timeit(lambda: nat.gn_fwd(h2, gam2, bet2, n2, H, K2, 0))
+    rep("gn_fwd [T,8,1024]", ms, bytes_=2 * T * H * K2 * 2)
+    dg2 = torch.zeros(H, K2, device=DEV)
+    db2 = torch.zeros(H, K2, device=DEV)
+    ms = timeit(lambda: nat.gn_bwd(dh2, h2, gam2, bet2, n2, dg2, db2, H, K2, 0, True))
+    rep("gn_bwd relu-mask [T,8,1024]", ms, bytes_=3 * T * H * K2 * 2)
     ms = timeit(lambda: nat.axpby(x, y, 1.0, out))
     rep("axpby [T,4096]", ms, bytes_=3 * T * F * 2)
     c = torch.empty_like(x)

@@ -127,14 +127,43 @@ __device__ __forceinline__ double warp_sum_d(double v) {
 }
 
 // ---- the reference's activation (src/model/activation.py:158-161): NOT the textbook tanh-GELU --
-__device__ __forceinline__ float gelu_obst(float x) {
-  const float u = 0.044715f * x * x * x + 0.7978845608028654f * x;
-  return 0.5f * x * (1.0f + tanhf(u));
+// 0.5 x (1 + tanh(u)), u = 0.044715 x^3 + sqrt(2/pi) x, is x * sigmoid(2u) exactly; written that way it costs one
+// MUFU.EX2 and one MUFU.RCP instead of libdevice's tanhf (the GN kernels with the fused activation ran at half the
+// bandwidth of the plain ones with tanhf).  ex2.approx / rcp.approx are ~1e-7 relative: inside the fp32 parity bar.
+__device__ __forceinline__ float gelu_obst_sigmoid(float x) {
+  // exp(-2u) = 2^(x * (a x^2 + b)),  a = -2 * 0.044715 * log2(e),  b = -2 * sqrt(2/pi) * log2(e)
+  const float t = x * fmaf(x * x, -0.12902022f, -2.3022082f);
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+  return __fdividef(1.0f, 1.0f + e);
 }
+// FAST (16-bit activations): tanh.approx.f32 is one MUFU op with ~2^-11 relative error, a quarter of a bf16 ulp --
+// the GN kernels with the fused activation are MUFU/issue bound, not HBM bound, so the second MUFU op matters.
+__device__ __forceinline__ float tanh_approx(float u) {
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  return t;
+}
+template <bool FAST>
+__device__ __forceinline__ float gelu_obst(float x) {
+  if (FAST) {
+    const float hx = 0.5f * x;
+    return fmaf(hx, tanh_approx(x * fmaf(x * x, 0.044715f, 0.7978845608028654f)), hx);
+  }
+  return x * gelu_obst_sigmoid(x);
+}
+template <bool FAST>
 __device__ __forceinline__ float gelu_obst_grad(float x) {
-  const float u = 0.044715f * x * x * x + 0.7978845608028654f * x;
-  const float th = tanhf(u);
-  return 0.5f * (1.0f + th) + 0.5f * x * (1.0f - th * th) * (3.0f * 0.044715f * x * x + 0.7978845608028654f);
+  if (FAST) {
+    const float x2 = x * x;
+    const float th = tanh_approx(x * fmaf(x2, 0.044715f, 0.7978845608028654f));
+    // 0.5 (1 + th) + 0.5 x (1 - th^2) u',  u' = 3 * 0.044715 x^2 + sqrt(2/pi)
+    const float a = fmaf(0.5f, th, 0.5f);
+    return fmaf(x * fmaf(-th, th, 1.0f), fmaf(x2, 0.0670725f, 0.3989422804014327f), a);
+  }
+  const float s = gelu_obst_sigmoid(x);
+  // d/dx [x s(2u)] = s + x s (1 - s) 2u',  2u' = 6 * 0.044715 x^2 + 2 sqrt(2/pi)
+  return s * fmaf(x * (1.0f - s), fmaf(x * x, 0.26829f, 1.5957691216057308f), 1.0f);
 }
 
 static inline int num_sms() {

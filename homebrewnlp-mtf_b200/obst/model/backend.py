@@ -31,6 +31,8 @@ class Variable:
         self.data = torch.from_numpy(np.ascontiguousarray(init, dtype=np.float32)).to(dev)  # slice_dtype fp32
         self.tril_s = 0          # >0: causal mask folded into the shadow (token-mixing maps)
         self.value: typing.Optional[torch.Tensor] = None
+        self.value_t: typing.Optional[torch.Tensor] = None  # transposed shadow, see transposed()
+        self._t_view: typing.Optional[typing.Tuple[int, int, int]] = None
         self.grad: typing.Optional[torch.Tensor] = None  # bound by the optimizer to a view of its flat buffer
         self._act_dtype = params.variable_dtype.activation_dtype
 
@@ -38,10 +40,30 @@ class Variable:
         """(Re)build the shadow: cast of the fp32 slice to the activation dtype (mtf.Variable.value)."""
         if self._act_dtype == torch.float32 and self.tril_s == 0:
             self.value = self.data
-            return
-        if self.value is None or self.value is self.data:
-            self.value = torch.empty_like(self.data, dtype=self._act_dtype)
-        native.cast_param(self.data, self.value, self.tril_s)
+        else:
+            if self.value is None or self.value is self.data:
+                self.value = torch.empty_like(self.data, dtype=self._act_dtype)
+            native.cast_param(self.data, self.value, self.tril_s)
+        self.refresh_t()
+
+    def refresh_t(self):
+        """Rewrite the transposed shadow (if one was asked for) from the shadow; the optimizer calls this after
+        every update, since its kernels rewrite `value` in place."""
+        if self.value_t is not None:
+            native.transpose_param(self.value.view(self._t_view), self.value_t)
+
+    def transposed(self, batch: int, rows: int, cols: int) -> torch.Tensor:
+        """The shadow, seen as [batch, rows, cols], stored as [batch, cols, rows].  Forward GEMMs read the weight
+        as their B operand with the contraction dim second-to-last (MN-major); the tcgen05 kernel is 12-17 %
+        faster on a K-major B, and a weight is tiny next to an activation, so a second copy is kept instead."""
+        view = (batch, rows, cols)
+        if self.value_t is None or self._t_view != view:
+            if batch * rows * cols != self.value.numel():
+                raise ValueError(f"transposed{view} does not match {self.name} {tuple(self.value.shape)}")
+            self._t_view = view
+            self.value_t = torch.empty((batch, cols, rows), dtype=self.value.dtype, device=self.value.device)
+            self.refresh_t()
+        return self.value_t
 
     def set_masked(self, s: int):
         if self.tril_s != s:
@@ -238,6 +260,7 @@ def linear(args: BlockArgs, old: DIM_LIST, new: DIM_LIST, relu: bool = False) ->
     be = params.gemm_backend
     dt = x.data.dtype
     w = var.value
+    wt = var.transposed(G, Kc, Np)  # [G, Np, Kc]: the forward B operand, K-major
     residual = params.residual
     xin = x.data
     if residual is not None:
@@ -245,11 +268,11 @@ def linear(args: BlockArgs, old: DIM_LIST, new: DIM_LIST, relu: bool = False) ->
         buf, sign, out = residual  # out = buf +/- x@W; out is buf itself for the in-place (reversible) case
         if relu or tuple(buf.shape) != tuple(d.size for d in out_dims):
             raise NotImplementedError("linear: residual fusion needs a plain final linear of matching shape")
-        native.gemm(native.operand(xin, G * Kc, 1, s_glo=Kc), native.operand(w, 1, Np, s_glo=Kc * Np), out, M, Np, Kc,
+        native.gemm(native.operand(xin, G * Kc, 1, s_glo=Kc), native.operand(wt, Kc, 1, s_glo=Kc * Np), out, M, Np, Kc,
                     GLO=G, d_ld=G * Np, d_glo=Np, R=buf, epi=2 if sign > 0 else 3, dtype_in=dt, backend=be)
     else:
         out = torch.empty([d.size for d in out_dims], dtype=dt, device=xin.device)
-        native.gemm(native.operand(xin, G * Kc, 1, s_glo=Kc), native.operand(w, 1, Np, s_glo=Kc * Np), out, M, Np, Kc,
+        native.gemm(native.operand(xin, G * Kc, 1, s_glo=Kc), native.operand(wt, Kc, 1, s_glo=Kc * Np), out, M, Np, Kc,
                     GLO=G, d_ld=G * Np, d_glo=Np, epi=1 if relu else 0, dtype_in=dt, backend=be)
 
     if params.tape is not None:

@@ -38,6 +38,7 @@ def attention(args: BlockArgs) -> Tensor:
     dt = x.data.dtype
     xin = x.data
     w = var.value
+    wt = var.transposed(H, S, S)  # M^T, so the dx GEMM reads its A operand K-major too
     residual = params.residual
     b_op = native.operand(xin, 1, F, s_glo=K, s_ghi=S * F)
     a_op = native.operand(w, S, 1, s_glo=S * S)
@@ -59,7 +60,7 @@ def attention(args: BlockArgs) -> Tensor:
                         accumulate=True, dtype_in=dt, backend=be)
             # dx[b,t,h,k] = sum_{s>=t} M[h,s,t] dy[b,s,h,k]
             dx = torch.empty_like(xin)
-            native.gemm(native.operand(w, 1, S, s_glo=S * S), native.operand(dy, 1, F, s_glo=K, s_ghi=S * F), dx, S, K,
+            native.gemm(native.operand(wt, S, 1, s_glo=S * S), native.operand(dy, 1, F, s_glo=K, s_ghi=S * F), dx, S, K,
                         S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, tri=2 if masked else 0, dtype_in=dt,
                         backend=be)
             return dx

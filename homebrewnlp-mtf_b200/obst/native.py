@@ -58,6 +58,7 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_xent_fwd_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_float, c_float,
                                   c_void_p]),
     "obst_cast_param": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_void_p]),
+    "obst_transpose_param": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
     "obst_opt_norms": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_void_p,
                                c_i32, c_void_p, c_i32, c_i32, c_void_p]),
     "obst_opt_update": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32, c_i32,
@@ -242,3 +243,12 @@ def cast_param(src, dst, tril_s: int = 0):
     _cuda(src, dst)
     check(load().obst_cast_param(dtype_code(dst.dtype), _p(src), _p(dst), src.numel(), tril_s, stream_ptr()),
           "obst_cast_param")
+
+
+def transpose_param(src, dst):
+    """dst[..., c, r] = src[..., r, c] (contiguous tensors, leading dims are the batch)."""
+    _cuda(src, dst)
+    rows, cols = src.shape[-2], src.shape[-1]
+    batch = src.numel() // max(1, rows * cols)
+    check(load().obst_transpose_param(dtype_code(src.dtype), _p(src), _p(dst), batch, rows, cols, stream_ptr()),
+          "obst_transpose_param")

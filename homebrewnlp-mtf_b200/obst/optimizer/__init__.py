@@ -188,6 +188,8 @@ class FusedOptimizer:
                                              plan.clip, plan.beta, int(plan.nesterov), float(lr),
                                              float(p.weight_decay), st), "obst_opt_update")
         native.check(lib.obst_opt_finalize(tp, nt, sdt, st), "obst_opt_finalize")
+        for v in self.variables:  # the update rewrote the shadows in place: transposed copies follow
+            v.refresh_t()
         self.wnorm_valid = plan.clip > 0
 
 

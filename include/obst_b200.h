@@ -142,6 +142,13 @@ int obst_xent_fwd_bwd(int dtype, const void* logits, const int32_t* targets, voi
 int obst_cast_param(int dtype_dst, const float* src, void* dst, int64_t n, int32_t tril_s,
                     void* stream);
 
+/* dst[b, c, r] = src[b, r, c] for `batch` row-major [rows, cols] matrices of dtype AT (src != dst).
+ * The reference's einsums read one weight in whatever orientation the contraction needs
+ * (src/model/backend.py:108-110); the tcgen05 GEMM prefers its B operand K-major, so the host keeps a
+ * transposed shadow of each weight that is a forward B operand and refreshes it after the update. */
+int obst_transpose_param(int dtype, const void* src, void* dst, int64_t batch, int32_t rows,
+                         int32_t cols, void* stream);
+
 /* ---- fused optimizer update ---------------------------------------------------------------------
  * adaptive_clip:<clip> - sm3 - momentum:<beta>:1:<nesterov> - learning_rate, plus the
  * weight-decay rule and assign_sub:  src/optimizer/__init__.py:31-66,

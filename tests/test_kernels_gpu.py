@@ -284,6 +284,17 @@ def test_cast_param_tril(nat):
     assert torch.equal(dst2, src)
 
 
+@pytest.mark.parametrize("shape,dtype", [((3, 64, 96), torch.bfloat16), ((1, 33, 7), torch.float32),
+                                         ((8, 512, 512), torch.bfloat16), ((2, 1, 65), torch.bfloat16)])
+def test_transpose_param(nat, shape, dtype):
+    src = randn(*shape, dtype=dtype, seed=33)
+    dst = torch.full((shape[0], shape[2], shape[1]), 7.0, dtype=dtype, device=DEV)
+    nat.transpose_param(src, dst)
+    assert torch.equal(dst, src.transpose(1, 2).contiguous())  # a copy: bit-exact
+    with pytest.raises(nat.NativeError):
+        nat.transpose_param(src, src)
+
+
 # ---------------------------------------------------------------------------------------------------
 # edge cases: empty inputs, ragged sizes, the largest mixing map of the reference configs
 # ---------------------------------------------------------------------------------------------------

@@ -315,3 +315,28 @@ def test_store_activations_extension_matches_the_float64_oracle(cuda):
     assert abs(scal["loss"] - loss) / loss < 1e-5
     for name, var in variables_by_oracle_name(params, sh).items():
         assert rel(to_np(var.grad), grads[name]) < 1e-5, name
+
+
+def test_transposed_shadows_follow_the_optimizer(cuda):
+    """Forward GEMMs read weight^T from a second shadow (Variable.transposed); after updates that move the weights
+    it must still be the exact transpose of the shadow the optimizer kernel rewrote."""
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=0)
+    tok_x, tok_y = orc.synthetic_tokens(sh)
+    params = make_params(cfg, op)
+    params.global_step = 2048
+    before = None
+    for _ in range(2):
+        run_product_step(params, tok_x, tok_y)
+        if before is None:
+            before = {n: v.value_t.clone() for n, v in params.variable_cache.items() if v.value_t is not None}
+    torch.cuda.synchronize()
+    assert len(before) >= 4
+    moved = 0
+    for n, v in params.variable_cache.items():
+        if v.value_t is None:
+            continue
+        assert torch.equal(v.value_t, v.value.view(v._t_view).transpose(1, 2).contiguous()), n
+        moved += int(not torch.equal(v.value_t, before[n]))
+    assert moved >= 4
