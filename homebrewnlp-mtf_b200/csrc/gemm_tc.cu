@@ -107,6 +107,46 @@ __device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* map, u
   }
 }
 
+// Warp-uniform producer: the WHOLE warp runs the loop (so tile / k coordinates are uniform values the compiler
+// keeps in uniform registers) and one elected lane issues.  With `if (lane == 0)` around the loop instead, every
+// UTMALDG was preceded by an ELECT / R2UR.BROADCAST loop and the k-block coordinates by two integer divisions:
+// the producer could not refill a stage in the 512 cycles the tensor core takes to drain one.
+__device__ __forceinline__ void mbar_expect_tx_elect(uint64_t* bar, uint32_t bytes) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "@P mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(bytes)
+      : "memory");
+}
+template <int CG>
+__device__ __forceinline__ void tma_load_5d_elect(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
+                                                  int c2, int c3, int c4) {
+  if (CG == 2) {
+    asm volatile(
+        "{\n"
+        ".reg .pred P;\n"
+        "elect.sync _|P, 0xffffffff;\n"
+        "@P cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, "
+        "%4, %5, %6, %7}], [%2];\n"
+        "}\n" ::"r"(dst),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        ".reg .pred P;\n"
+        "elect.sync _|P, 0xffffffff;\n"
+        "@P cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, "
+        "%7}], [%2];\n"
+        "}\n" ::"r"(dst),
+        "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+  }
+}
+
 __device__ __forceinline__ void cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -169,43 +209,55 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
 
-// D[tmem] (+)= A[smem] * B[smem], bf16 inputs, fp32 accumulate
+// D[tmem] (+)= A[smem] * B[smem], bf16 inputs, fp32 accumulate.  Called by the whole (converged) MMA warp; one
+// elected lane issues (see the producer note: a `lane == 0` region costs an ELECT/R2UR loop per instruction).
 template <int CG>
 __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                           uint32_t accumulate) {
   if (CG == 2) {
     asm volatile(
         "{\n"
-        ".reg .pred p;\n"
+        ".reg .pred p, e;\n"
         "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d),
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
   } else {
     asm volatile(
         "{\n"
-        ".reg .pred p;\n"
+        ".reg .pred p, e;\n"
         "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d),
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
   }
 }
-// mbarrier arrive once all previously issued tcgen05 ops of this thread have completed
-// (CG == 2: the arrive is multicast to the barrier at the same offset in BOTH CTAs of the pair)
+// mbarrier arrive once all previously issued tcgen05 ops of the issuing thread have completed
+// (CG == 2: the arrive is multicast to the barrier at the same offset in BOTH CTAs of the pair).
+// elect.sync picks the same lane every time for a full mask, so the commit tracks the MMAs above.
 template <int CG>
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   if (CG == 2) {
     asm volatile(
-        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
-            smem_u32(bar)),
+        "{\n"
+        ".reg .pred e;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+        "}\n" ::"r"(smem_u32(bar)),
         "h"((uint16_t)3)
         : "memory");
   } else {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
+    asm volatile(
+        "{\n"
+        ".reg .pred e;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+        "}\n" ::"r"(smem_u32(bar))
+        : "memory");
   }
 }
 
@@ -384,48 +436,49 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + bn_cta * BK * 2) * CG;  // what the (leader's) barrier sees
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (whole warp, one elected lane issues) =====================
+    {
       int stage = 0;
       uint32_t phase = 0;
       Tile t;
+      const uint32_t sa0 = smem_u32(smem_a), sb0 = smem_u32(smem_b), fb0 = smem_u32(full_bar);
+      const int a_boxes = p.a_mn ? BM / 64 : 1, b_boxes = p.b_mn ? bn_cta / 64 : 1;
       for (int tile = cluster_id; tile < p.total_tiles; tile += num_clusters) {
         if (!get_tile<CG>(p, tile, t)) continue;
         const int a2 = p.a_uglo ? t.glo : 0, a3 = p.a_ughi ? t.ghi : 0;
         const int b2 = p.b_uglo ? t.glo : 0, b3 = p.b_ughi ? t.ghi : 0;
         const int am0 = t.m0 + (int)rank * BM;
         const int bn0 = t.n0 + (int)rank * bn_cta;
+        int ki = t.kb0 % p.nkb_inner, ko = t.kb0 / p.nkb_inner;  // once per tile; advanced incrementally below
         for (int kb = t.kb0; kb < t.kb1; ++kb) {
-          const int ki = kb % p.nkb_inner, ko = kb / p.nkb_inner;
           const int k0 = ki * BK;
-          mbar_wait(&empty_bar[stage], phase ^ 1, 0);
-          if (leader) mbar_expect_tx(&full_bar[stage], stage_bytes);
-          uint8_t* sa = smem_a + stage * A_STAGE_BYTES;
-          uint8_t* sb = smem_b + stage * B_STAGE;
           const int a4 = p.a_uko ? ko : 0, b4 = p.b_uko ? ko : 0;
-          if (!p.a_mn) {
-            tma_load_5d<CG>(sa, &tmA, &full_bar[stage], k0, am0, a2, a3, a4);
-          } else {
-#pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              tma_load_5d<CG>(sa + j * (64 * BK * 2), &tmA, &full_bar[stage], am0 + 64 * j, k0, a2, a3, a4);
-          }
-          if (!p.b_mn) {
-            tma_load_5d<CG>(sb, &tmB, &full_bar[stage], k0, bn0, b2, b3, b4);
-          } else {
-            for (int j = 0; j < bn_cta / 64; ++j)
-              tma_load_5d<CG>(sb + j * (64 * BK * 2), &tmB, &full_bar[stage], bn0 + 64 * j, k0, b2, b3, b4);
-          }
+          const uint32_t fb = fb0 + (uint32_t)stage * 8u;
+          const uint32_t sa = sa0 + (uint32_t)stage * A_STAGE_BYTES;
+          const uint32_t sb = sb0 + (uint32_t)stage * B_STAGE;
+          mbar_wait(&empty_bar[stage], phase ^ 1, 0);
+          if (leader) mbar_expect_tx_elect(&full_bar[stage], stage_bytes);
+          // K-major: one box (64 k x rows).  MN-major: one box per 64 MN elements (64 mn x 64 k each).
+          for (int j = 0; j < a_boxes; ++j)
+            tma_load_5d_elect<CG>(sa + j * (64 * BK * 2), &tmA, fb, p.a_mn ? am0 + 64 * j : k0, p.a_mn ? k0 : am0, a2,
+                                  a3, a4);
+          for (int j = 0; j < b_boxes; ++j)
+            tma_load_5d_elect<CG>(sb + j * (64 * BK * 2), &tmB, fb, p.b_mn ? bn0 + 64 * j : k0, p.b_mn ? k0 : bn0, b2,
+                                  b3, b4);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
+          }
+          if (++ki == p.nkb_inner) {
+            ki = 0;
+            ++ko;
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer (one thread of the leader CTA) =====================
-    if (lane == 0 && leader) {
+    // ===================== MMA issuer (warp 1 of the leader CTA; one elected lane issues) =====================
+    if (leader) {
       const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
                              ((uint32_t)(p.BN >> 3) << 17) | ((uint32_t)((BM * CG) >> 4) << 24);
       // K-major: 8-row groups 1024 B apart (SBO), 32 B per UMMA_K step.
