@@ -24,7 +24,7 @@ static constexpr int BK = 64;
 static constexpr int A_STAGE_BYTES = BM * BK * 2;        // 16 KB
 static constexpr int TMEM_COLS = 512;
 static constexpr int ACC_STRIDE = 256;                   // columns per accumulator buffer
-static constexpr int TC_THREADS = 320;                   // TMA warp, MMA warp, 8 epilogue warps
+static constexpr int TC_THREADS = 352;                   // TMA warp (A), MMA warp, 8 epilogue warps, TMA warp (B)
 static constexpr int EPI_WARPS = 8;
 static constexpr int EPI_BOX_ROWS = 32;                  // one epilogue warp's TMEM lane quarter
 static constexpr int EPI_BOX_COLS = 64;                  // 64 bf16 = 128 B = one swizzle row
@@ -435,36 +435,36 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int bn_cta = p.BN / CG;  // B rows (N) this CTA stages
   const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + bn_cta * BK * 2) * CG;  // what the (leader's) barrier sees
 
-  if (warp == 0) {
-    // ===================== TMA producer (whole warp, one elected lane issues) =====================
+  if (warp == 0 || warp == 2 + EPI_WARPS) {
+    // ===================== TMA producers (whole warp, one elected lane issues) =====================
+    // warp 0 requests the A boxes of every stage (and posts the stage's byte count), warp 10 the B boxes: an
+    // MN-major operand needs a box per 64 elements, and one warp issuing up to four boxes per stage was the limit.
     {
+      const bool is_a = warp == 0;
       int stage = 0;
       uint32_t phase = 0;
       Tile t;
-      const uint32_t sa0 = smem_u32(smem_a), sb0 = smem_u32(smem_b), fb0 = smem_u32(full_bar);
-      const int a_boxes = p.a_mn ? BM / 64 : 1, b_boxes = p.b_mn ? bn_cta / 64 : 1;
+      const uint32_t s0 = is_a ? smem_u32(smem_a) : smem_u32(smem_b), fb0 = smem_u32(full_bar);
+      const uint32_t s_stride = is_a ? (uint32_t)A_STAGE_BYTES : (uint32_t)B_STAGE;
+      const CUtensorMap* tm = is_a ? &tmA : &tmB;
+      const int mn = is_a ? p.a_mn : p.b_mn;
+      const int boxes = mn ? (is_a ? BM : bn_cta) / 64 : 1;
+      const int uglo = is_a ? p.a_uglo : p.b_uglo, ughi = is_a ? p.a_ughi : p.b_ughi, uko = is_a ? p.a_uko : p.b_uko;
       for (int tile = cluster_id; tile < p.total_tiles; tile += num_clusters) {
         if (!get_tile<CG>(p, tile, t)) continue;
-        const int a2 = p.a_uglo ? t.glo : 0, a3 = p.a_ughi ? t.ghi : 0;
-        const int b2 = p.b_uglo ? t.glo : 0, b3 = p.b_ughi ? t.ghi : 0;
-        const int am0 = t.m0 + (int)rank * BM;
-        const int bn0 = t.n0 + (int)rank * bn_cta;
+        const int c2 = uglo ? t.glo : 0, c3 = ughi ? t.ghi : 0;
+        const int mn0 = is_a ? t.m0 + (int)rank * BM : t.n0 + (int)rank * bn_cta;
         int ki = t.kb0 % p.nkb_inner, ko = t.kb0 / p.nkb_inner;  // once per tile; advanced incrementally below
         for (int kb = t.kb0; kb < t.kb1; ++kb) {
           const int k0 = ki * BK;
-          const int a4 = p.a_uko ? ko : 0, b4 = p.b_uko ? ko : 0;
+          const int c4 = uko ? ko : 0;
           const uint32_t fb = fb0 + (uint32_t)stage * 8u;
-          const uint32_t sa = sa0 + (uint32_t)stage * A_STAGE_BYTES;
-          const uint32_t sb = sb0 + (uint32_t)stage * B_STAGE;
+          const uint32_t dst = s0 + (uint32_t)stage * s_stride;
           mbar_wait(&empty_bar[stage], phase ^ 1, 0);
-          if (leader) mbar_expect_tx_elect(&full_bar[stage], stage_bytes);
+          if (is_a && leader) mbar_expect_tx_elect(&full_bar[stage], stage_bytes);
           // K-major: one box (64 k x rows).  MN-major: one box per 64 MN elements (64 mn x 64 k each).
-          for (int j = 0; j < a_boxes; ++j)
-            tma_load_5d_elect<CG>(sa + j * (64 * BK * 2), &tmA, fb, p.a_mn ? am0 + 64 * j : k0, p.a_mn ? k0 : am0, a2,
-                                  a3, a4);
-          for (int j = 0; j < b_boxes; ++j)
-            tma_load_5d_elect<CG>(sb + j * (64 * BK * 2), &tmB, fb, p.b_mn ? bn0 + 64 * j : k0, p.b_mn ? k0 : bn0, b2,
-                                  b3, b4);
+          for (int j = 0; j < boxes; ++j)
+            tma_load_5d_elect<CG>(dst + j * (64 * BK * 2), tm, fb, mn ? mn0 + 64 * j : k0, mn ? k0 : mn0, c2, c3, c4);
           if (++stage == STAGES) {
             stage = 0;
             phase ^= 1;
