@@ -118,6 +118,16 @@ def main():
     db = torch.zeros(H, K, device=DEV)
     ms = timeit(lambda: nat.gn_bwd(y, x, gam, bet, out, dg, db, H, K))
     rep("gn_bwd [T,8,512]", ms, bytes_=3 * T * F * 2)
+    st = torch.empty(T * H, 2, device=DEV)
+    nat.gn_fwd(x, gam, bet, c_tmp := torch.empty_like(x), H, K, 0, stats=st)
+    ms = timeit(lambda: nat.gn_fwd(x, gam, bet, c_tmp, H, K, 0, stats=st))
+    rep("gn_fwd +stats [T,8,512]", ms, bytes_=2 * T * F * 2)
+    ms = timeit(lambda: nat.gn_bwd(y, x, gam, bet, out, dg, db, H, K, stats=st))
+    rep("gn_bwd saved stats [T,8,512]", ms, bytes_=3 * T * F * 2)
+    ms = timeit(lambda: nat.gn_bwd(y, x, gam, bet, out, dg, db, H, K, 1, stats=st))
+    rep("gn_bwd + gelu saved stats", ms, bytes_=3 * T * F * 2)
+    ms = timeit(lambda: nat.gn_bwd(y, x, gam, bet, out, dg, db, H, K, 0, False, True, stats=st))
+    rep("gn_bwd dx+= saved stats", ms, bytes_=4 * T * F * 2)
     ms = timeit(lambda: nat.gn_fwd(x, gam, bet, y, H, K, 1))
     rep("gn_fwd + gelu [T,8,512]", ms, bytes_=2 * T * F * 2)
     ms = timeit(lambda: nat.gn_bwd(y, x, gam, bet, out, dg, db, H, K, 1))
@@ -134,6 +144,10 @@ def main():
     db2 = torch.zeros(H, K2, device=DEV)
     ms = timeit(lambda: nat.gn_bwd(dh2, h2, gam2, bet2, n2, dg2, db2, H, K2, 0, True))
     rep("gn_bwd relu-mask [T,8,1024]", ms, bytes_=3 * T * H * K2 * 2)
+    st2 = torch.empty(T * H, 2, device=DEV)
+    nat.gn_fwd(h2, gam2, bet2, n2, H, K2, 0, stats=st2)
+    ms = timeit(lambda: nat.gn_bwd(dh2, h2, gam2, bet2, n2, dg2, db2, H, K2, 0, True, stats=st2))
+    rep("gn_bwd relu-mask saved stats [T,8,1024]", ms, bytes_=3 * T * H * K2 * 2)
     ms = timeit(lambda: nat.axpby(x, y, 1.0, out))
     rep("axpby [T,4096]", ms, bytes_=3 * T * F * 2)
     c = torch.empty_like(x)

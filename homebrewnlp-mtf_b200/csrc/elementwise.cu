@@ -12,10 +12,10 @@ static constexpr float GN_EPS = 1e-5f;  // src/model/normalization.py:28
 // ================================================================================================
 // ROWS rows are in flight per warp (all their loads are issued before the first reduction): with one 1 KB row per
 // warp the kernel is latency-bound at ~60 % of HBM; 4 rows give the memory system 8 x 16 B per lane to chew on.
-template <typename T, int MAXC, int ROWS, int ACT>
+template <typename T, int MAXC, int ROWS, int ACT, bool STATS>
 __global__ void __launch_bounds__(256) gn_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma,
-                                                      const T* __restrict__ beta, T* __restrict__ y, int64_t rows,
-                                                      int heads, int width) {
+                                                      const T* __restrict__ beta, T* __restrict__ y,
+                                                      float2* __restrict__ stats, int64_t rows, int heads, int width) {
   constexpr int N = Vec16<T>::N;
   const int lane = threadIdx.x & 31;
   const int warps_per_block = blockDim.x >> 5;
@@ -67,6 +67,7 @@ __global__ void __launch_bounds__(256) gn_fwd_kernel(const T* __restrict__ x, co
         }
       }
       q[r] = rsqrtf(warp_sum(q[r]) * inv_w + GN_EPS);  // rstd
+      if (STATS && lane == 0 && base + r < rows) stats[base + r] = make_float2(s[r], q[r]);
     }
 #pragma unroll
     for (int r = 0; r < ROWS; ++r) {
@@ -121,8 +122,9 @@ template <typename T, int MAXC, int BSTAGES, int SPLIT, int ACT>
 __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
                                                       const T* __restrict__ gamma, const T* __restrict__ beta,
                                                       T* __restrict__ dx, float* __restrict__ dgamma,
-                                                      float* __restrict__ dbeta, int64_t tokens, int heads, int width,
-                                                      int tokens_per_block, int relu_mask, int dx_acc) {
+                                                      float* __restrict__ dbeta, const float2* __restrict__ stats,
+                                                      int64_t tokens, int heads, int width, int tokens_per_block,
+                                                      int relu_mask, int dx_acc) {
   constexpr int N = Raw16<T>::N;
   extern __shared__ __align__(16) uint8_t s_raw[];
   __shared__ float s_x[4][6][2];  // [row slot][exchange + 3 * row parity][half]
@@ -186,6 +188,10 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
   };
   int stage = 0;
   int parity = 0;
+  // (mean, rstd) of the row saved by the forward kernel, fetched one row ahead: with them the two statistics passes
+  // (and, for split rows, two of the three exchanges) disappear -- the kernel is instruction-issue bound
+  float2 st_next = make_float2(0.f, 0.f);
+  if (stats && t0 + vw < t1) st_next = stats[(t0 + vw) * heads + h];
 #pragma unroll
   for (int s0 = 0; s0 < BSTAGES - 1; ++s0) {
     if (t0 + vw + (int64_t)s0 * slots < t1) issue(t0 + vw + (int64_t)s0 * slots, s0);
@@ -195,6 +201,8 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
     const int64_t tn = t + (int64_t)(BSTAGES - 1) * slots;
     if (tn < t1) issue(tn, (stage + BSTAGES - 1) % BSTAGES);
     else cp_async_commit();
+    const float2 st_cur = st_next;
+    if (stats && t + slots < t1) st_next = stats[(t + slots) * heads + h];
     cp_async_wait<BSTAGES - 1>();
     __syncwarp();
     const int64_t off = (t * heads + h) * width + col0;
@@ -212,25 +220,38 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
         Vec16<T> v;
         v.load(sx + c * N);
 #pragma unroll
-        for (int j = 0; j < N; ++j) {
-          zv[i][j] = v.v[j];
-          s += v.v[j];
+        for (int j = 0; j < N; ++j) zv[i][j] = v.v[j];
+      }
+    }
+    if (!stats) {
+#pragma unroll
+      for (int i = 0; i < MAXC; ++i) {
+        if (lane + 32 * i < chunks) {
+#pragma unroll
+          for (int j = 0; j < N; ++j) s += zv[i][j];
         }
       }
     }
-    const float mean = row_sum(s, 3 * parity + 0) * inv_w;
-    float q = 0.f;
+    float mean, rstd;
+    if (stats) {
+      mean = st_cur.x;
+      rstd = st_cur.y;
+    } else {
+      mean = row_sum(s, 3 * parity + 0) * inv_w;
+      float q = 0.f;
 #pragma unroll
-    for (int i = 0; i < MAXC; ++i) {
-      if (lane + 32 * i < chunks) {
+      for (int i = 0; i < MAXC; ++i) {
+        if (lane + 32 * i < chunks) {
 #pragma unroll
-        for (int j = 0; j < N; ++j) {
-          const float d = zv[i][j] - mean;
-          q += d * d;
+          for (int j = 0; j < N; ++j) {
+            const float d = zv[i][j] - mean;
+            q += d * d;
+          }
         }
       }
+      rstd = rsqrtf(row_sum(q, 3 * parity + 1) * inv_w + GN_EPS);
     }
-    const float rstd = rsqrtf(row_sum(q, 3 * parity + 1) * inv_w + GN_EPS);
+    const float nmr = -mean * rstd;
     float sg = 0.f, sgz = 0.f;
     unsigned long long maskbits = 0;  // bit (i*N+j) <= 63: raw x > 0 (ReLU mask), taken before x becomes z
 #pragma unroll
@@ -245,7 +266,7 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
 #pragma unroll
         for (int j = 0; j < N; ++j) {
           if (relu_mask && zv[i][j] > 0.f) maskbits |= 1ull << (i * N + j);
-          const float z = (zv[i][j] - mean) * rstd;
+          const float z = fmaf(zv[i][j], rstd, nmr);
           zv[i][j] = z;
           float d = dv.v[j];
           if (ACT == 1) d *= gelu_obst_grad<sizeof(T) == 2>(z * gam.v[j] + bet.v[j]);
@@ -274,6 +295,7 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
       mg = (s_x[vw][3 * parity + 2][0] + s_x[vw][3 * parity + 2][1]) * inv_w;
       mgz = (s_y[vw][parity][0] + s_y[vw][parity][1]) * inv_w;
     }
+    const float c0 = -mg * rstd, c1 = -mgz * rstd;
 #pragma unroll
     for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
@@ -282,7 +304,7 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
         if (dx_acc) o.load(sdx + c * N);
 #pragma unroll
         for (int j = 0; j < N; ++j) {
-          float r = rstd * (gv[i][j] - mg - zv[i][j] * mgz);
+          float r = fmaf(zv[i][j], c1, fmaf(gv[i][j], rstd, c0));  // rstd * (g - mean(g) - z * mean(g z))
           if (relu_mask && !((maskbits >> (i * N + j)) & 1ull)) r = 0.f;
           o.v[j] = dx_acc ? (o.v[j] + r) : r;
         }
@@ -311,8 +333,8 @@ __global__ void __launch_bounds__(256) gn_bwd_kernel(const T* __restrict__ dy, c
 }
 
 template <typename T>
-static int gn_fwd_launch(const void* x, const void* gamma, const void* beta, void* y, int64_t rows, int heads,
-                         int width, int act, cudaStream_t st) {
+static int gn_fwd_launch(const void* x, const void* gamma, const void* beta, void* y, float2* stats, int64_t rows,
+                         int heads, int width, int act, cudaStream_t st) {
   constexpr int N = Vec16<T>::N;
   OBST_REQUIRE(width % N == 0, "obst_gn_fwd: width %d must be a multiple of %d", width, N);
   const int per_lane = (width / N + 31) / 32;
@@ -323,30 +345,33 @@ static int gn_fwd_launch(const void* x, const void* gamma, const void* beta, voi
   const int64_t cap = (int64_t)num_sms() * 8;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-#define OBST_GN_FWD(MC, R)                                                                                      \
-  do {                                                                                                          \
-    if (act == 1)                                                                                               \
-      gn_fwd_kernel<T, MC, R, 1><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma,          \
-                                                                          (const T*)beta, (T*)y, rows, heads,   \
-                                                                          width);                               \
-    else                                                                                                        \
-      gn_fwd_kernel<T, MC, R, 0><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma,          \
-                                                                          (const T*)beta, (T*)y, rows, heads,   \
-                                                                          width);                               \
+#define OBST_GN_FWD2(MC, R, A, S)                                                                              \
+  gn_fwd_kernel<T, MC, R, A, S><<<(unsigned)blocks, wpb * 32, 0, st>>>((const T*)x, (const T*)gamma, (const T*)beta, \
+                                                                        (T*)y, stats, rows, heads, width)
+#define OBST_GN_FWD(MC, R)                        \
+  do {                                            \
+    if (act == 1) {                               \
+      if (stats) OBST_GN_FWD2(MC, R, 1, true);    \
+      else OBST_GN_FWD2(MC, R, 1, false);         \
+    } else {                                      \
+      if (stats) OBST_GN_FWD2(MC, R, 0, true);    \
+      else OBST_GN_FWD2(MC, R, 0, false);         \
+    }                                             \
   } while (0)
   if (per_lane <= 1) OBST_GN_FWD(1, 1);
   else if (per_lane <= 2) OBST_GN_FWD(2, 1);
   else if (per_lane <= 4) OBST_GN_FWD(4, 1);
   else OBST_GN_FWD(8, 1);
 #undef OBST_GN_FWD
+#undef OBST_GN_FWD2
   count_launch();
   return check_launch("obst_gn_fwd");
 }
 
 template <typename T>
 static int gn_bwd_launch(const void* dy, const void* x, const void* gamma, const void* beta, void* dx, float* dgamma,
-                         float* dbeta, int64_t rows, int heads, int width, int act, int relu_mask, int dx_acc,
-                         cudaStream_t st) {
+                         float* dbeta, const float2* stats, int64_t rows, int heads, int width, int act, int relu_mask,
+                         int dx_acc, cudaStream_t st) {
   constexpr int N = Vec16<T>::N;
   OBST_REQUIRE(width % N == 0, "obst_gn_bwd: width %d must be a multiple of %d", width, N);
   OBST_REQUIRE(rows % heads == 0, "obst_gn_bwd: rows %lld not a multiple of heads %d", (long long)rows, heads);
@@ -371,8 +396,8 @@ static int gn_bwd_launch(const void* dy, const void* x, const void* gamma, const
     if (smem > 48 * 1024)                                                                                             \
       cudaFuncSetAttribute(gn_bwd_kernel<T, MC, ST, SP, AC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
     gn_bwd_kernel<T, MC, ST, SP, AC><<<grid, 256, smem, st>>>((const T*)dy, (const T*)x, (const T*)gamma,            \
-                                                               (const T*)beta, (T*)dx, dgamma, dbeta, tokens, heads, \
-                                                               width, tpb, relu_mask, dx_acc);                       \
+                                                               (const T*)beta, (T*)dx, dgamma, dbeta, stats, tokens, \
+                                                               heads, width, tpb, relu_mask, dx_acc);                \
   } while (0)
 #define OBST_GN_BWD1(MC, ST, SP)               \
   do {                                         \
@@ -633,27 +658,29 @@ using namespace obst;
 
 extern "C" {
 
-int obst_gn_fwd(int dtype, const void* x, const void* gamma, const void* beta, void* y, int64_t rows, int32_t heads,
-                int32_t width, int32_t act, void* stream) {
+int obst_gn_fwd(int dtype, const void* x, const void* gamma, const void* beta, void* y, float* stats, int64_t rows,
+                int32_t heads, int32_t width, int32_t act, void* stream) {
   OBST_REQUIRE(rows >= 0 && heads > 0 && width > 0, "obst_gn_fwd: bad shape");
   if (rows == 0) return OBST_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  if (dtype == OBST_BF16) return gn_fwd_launch<bf16>(x, gamma, beta, y, rows, heads, width, act, st);
-  if (dtype == OBST_F32) return gn_fwd_launch<float>(x, gamma, beta, y, rows, heads, width, act, st);
+  float2* s2 = reinterpret_cast<float2*>(stats);
+  if (dtype == OBST_BF16) return gn_fwd_launch<bf16>(x, gamma, beta, y, s2, rows, heads, width, act, st);
+  if (dtype == OBST_F32) return gn_fwd_launch<float>(x, gamma, beta, y, s2, rows, heads, width, act, st);
   OBST_REQUIRE(false, "obst_gn_fwd: bad dtype %d", dtype);
 }
 
 int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, const void* beta, void* dx,
-                float* dgamma, float* dbeta, int64_t rows, int32_t heads, int32_t width, int32_t act,
-                int32_t relu_mask, int32_t dx_accumulate, void* stream) {
+                float* dgamma, float* dbeta, const float* stats, int64_t rows, int32_t heads, int32_t width,
+                int32_t act, int32_t relu_mask, int32_t dx_accumulate, void* stream) {
   OBST_REQUIRE(rows >= 0 && heads > 0 && width > 0, "obst_gn_bwd: bad shape");
   if (rows == 0) return OBST_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  const float2* s2 = reinterpret_cast<const float2*>(stats);
   if (dtype == OBST_BF16)
-    return gn_bwd_launch<bf16>(dy, x, gamma, beta, dx, dgamma, dbeta, rows, heads, width, act, relu_mask,
+    return gn_bwd_launch<bf16>(dy, x, gamma, beta, dx, dgamma, dbeta, s2, rows, heads, width, act, relu_mask,
                                dx_accumulate, st);
   if (dtype == OBST_F32)
-    return gn_bwd_launch<float>(dy, x, gamma, beta, dx, dgamma, dbeta, rows, heads, width, act, relu_mask,
+    return gn_bwd_launch<float>(dy, x, gamma, beta, dx, dgamma, dbeta, s2, rows, heads, width, act, relu_mask,
                                 dx_accumulate, st);
   OBST_REQUIRE(false, "obst_gn_bwd: bad dtype %d", dtype);
 }

@@ -30,15 +30,19 @@ def norm(args: BlockArgs, feature_shape: typing.Optional[DIM_LIST] = None, fuse_
     act = 1 if fuse_gelu else 0
     xin = x.data
     y = torch.empty_like(xin)
+    # (mean, rstd) per normalised row, kept for the backward kernel when one will run (8 B per `width` elements)
+    stats = None
+    if params.tape is not None:
+        stats = torch.empty(xin.numel() // width, 2, dtype=torch.float32, device=xin.device)
     native.gn_fwd(xin, None if gamma is None else gamma.value, None if beta is None else beta.value, y, heads, width,
-                  act)
+                  act, stats=stats)
     if params.tape is not None:
         def bwd(dy: torch.Tensor, mask, acc):
             dx = acc if acc is not None else torch.empty_like(xin)
             native.gn_bwd(dy, xin, None if gamma is None else gamma.value, None if beta is None else beta.value, dx,
                           None if gamma is None else gamma.ensure_grad(),
                           None if beta is None else beta.ensure_grad(), heads, width, act=act,
-                          relu_mask=mask is not None, dx_accumulate=acc is not None)
+                          relu_mask=mask is not None, dx_accumulate=acc is not None, stats=stats)
             return dx
 
         # a ReLU mask can only be folded when the masking tensor IS this layer's input (norm right after relu)

@@ -47,9 +47,10 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_launch_count": (c_i64, []),
     "obst_launch_count_reset": (None, []),
     "obst_gemm": (c_int, [ctypes.POINTER(GemmDesc), c_int, c_void_p]),
-    "obst_gn_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_i32, c_void_p]),
-    "obst_gn_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64,
-                            c_i32, c_i32, c_i32, c_i32, c_i32, c_void_p]),
+    "obst_gn_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_i32,
+                            c_void_p]),
+    "obst_gn_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                            c_i64, c_i32, c_i32, c_i32, c_i32, c_i32, c_void_p]),
     "obst_act_fwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_act_bwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_axpby": (c_int, [c_int, c_void_p, c_void_p, c_float, c_void_p, c_i64, c_void_p]),
@@ -185,19 +186,24 @@ def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO
     check(load().obst_gemm(ctypes.byref(desc), backend, stream_ptr()), "obst_gemm")
 
 
-def gn_fwd(x, gamma, beta, y, heads: int, width: int, act: int = 0):
+def gn_fwd(x, gamma, beta, y, heads: int, width: int, act: int = 0, stats=None):
+    """stats: optional fp32 [rows, 2] tensor that receives (mean, rstd) per normalised row for gn_bwd."""
     _cuda(x, y)
     rows = x.numel() // width
-    check(load().obst_gn_fwd(dtype_code(x.dtype), _p(x), _p(gamma), _p(beta), _p(y), rows, heads, width, act,
-                             stream_ptr()), "obst_gn_fwd")
+    if stats is not None and (stats.dtype != torch.float32 or stats.numel() != 2 * rows or not stats.is_cuda):
+        raise NativeError("gn_fwd: stats must be a CUDA fp32 tensor of 2 * rows elements")
+    check(load().obst_gn_fwd(dtype_code(x.dtype), _p(x), _p(gamma), _p(beta), _p(y), _p(stats), rows, heads, width,
+                             act, stream_ptr()), "obst_gn_fwd")
 
 
 def gn_bwd(dy, x, gamma, beta, dx, dgamma, dbeta, heads: int, width: int, act: int = 0, relu_mask: bool = False,
-           dx_accumulate: bool = False):
+           dx_accumulate: bool = False, stats=None):
     _cuda(dy, x, dx)
     rows = x.numel() // width
+    if stats is not None and (stats.dtype != torch.float32 or stats.numel() != 2 * rows or not stats.is_cuda):
+        raise NativeError("gn_bwd: stats must be a CUDA fp32 tensor of 2 * rows elements")
     check(load().obst_gn_bwd(dtype_code(x.dtype), _p(dy), _p(x), _p(gamma), _p(beta), _p(dx), _p(dgamma), _p(dbeta),
-                             rows, heads, width, act, int(relu_mask), int(dx_accumulate), stream_ptr()),
+                             _p(stats), rows, heads, width, act, int(relu_mask), int(dx_accumulate), stream_ptr()),
           "obst_gn_bwd")
 
 

@@ -90,21 +90,26 @@ typedef struct obst_gemm_desc {
 int obst_gemm(const obst_gemm_desc* desc, int backend, void* stream);
 
 /* ---- group norm (per token, per head), src/model/normalization.py:22-34 ------------------------
- * x, y: [rows, heads, width] contiguous AT; gamma/beta: [heads, width] AT (may be NULL = no
+ * x, y: [rows, width] contiguous AT, rows = tokens * heads (row r belongs to head r % heads);
+ * gamma/beta: [heads, width] AT (may be NULL = no
  * scale / no shift).  y = (x-mean)*rsqrt(mean((x-mean)^2)+1e-5)*gamma + beta.
  * act: 0 none | 1 OBST gelu applied to y (src/model/activation.py:158-161; fuses the
- * "norm -> activation-gelu" layer pair of block_config[1], configs/32big_mixer.json:13-19). */
+ * "norm -> activation-gelu" layer pair of block_config[1], configs/32big_mixer.json:13-19).
+ * stats: NULL, or fp32 [rows, 2] receiving (mean, rstd) of every normalised row for the
+ * backward pass (8 bytes per row of `width` elements). */
 int obst_gn_fwd(int dtype, const void* x, const void* gamma, const void* beta, void* y,
-                int64_t rows, int32_t heads, int32_t width, int32_t act, void* stream);
+                float* stats, int64_t rows, int32_t heads, int32_t width, int32_t act, void* stream);
 
 /* Backward of the above (full LayerNorm gradient).  dy: grad of the output
  * (after the activation when act=1); dx written (dx_accumulate=0) or added to (1);
  * dgamma/dbeta: fp32 [heads,width], accumulated with atomics.
  * relu_mask: 1 = x is the output of a ReLU (W_mid path, src/model/basic.py:50,55-56): the
- * gradient is additionally multiplied by [x > 0] so the caller gets d(pre-ReLU). */
+ * gradient is additionally multiplied by [x > 0] so the caller gets d(pre-ReLU).
+ * stats: what obst_gn_fwd wrote for the same x, or NULL (the statistics are then recomputed). */
 int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, const void* beta,
-                void* dx, float* dgamma, float* dbeta, int64_t rows, int32_t heads, int32_t width,
-                int32_t act, int32_t relu_mask, int32_t dx_accumulate, void* stream);
+                void* dx, float* dgamma, float* dbeta, const float* stats, int64_t rows,
+                int32_t heads, int32_t width, int32_t act, int32_t relu_mask, int32_t dx_accumulate,
+                void* stream);
 
 /* ---- activations, src/model/activation.py:158-169,201-211 ---------------------------------------
  * kind: 0 relu | 1 OBST gelu 0.5x(1+tanh(0.044715x^3+sqrt(2/pi)x)). */

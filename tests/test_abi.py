@@ -55,7 +55,7 @@ def test_argument_validation_needs_no_gpu(lib):
     assert lib.obst_xent_fwd_bwd(0, None, None, None, None, 4, 4096, 1.0, 0.0, None) == -1
     assert b"vocab" in lib.obst_last_error()
     assert lib.obst_act_fwd(0, 7, None, None, 8, None) == -1
-    assert lib.obst_gn_fwd(1, None, None, None, None, 8, 8, 100, 0, None) == -1  # width not a multiple of 8
+    assert lib.obst_gn_fwd(1, None, None, None, None, None, 8, 8, 100, 0, None) == -1  # width not a multiple of 8
 
 
 def test_struct_layout_matches_the_c_compiler(tmp_path):

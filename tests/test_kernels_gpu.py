@@ -174,14 +174,20 @@ def gn_ref(x, gamma, beta, act):
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
 @pytest.mark.parametrize("width", [32, 64, 512, 1024])
 @pytest.mark.parametrize("act", [0, 1])
-def test_gn_fwd_bwd(nat, dtype, tol, width, act):
+@pytest.mark.parametrize("saved_stats", [False, True])
+def test_gn_fwd_bwd(nat, dtype, tol, width, act, saved_stats):
     T, H = 300, 8
     x = randn(T, H, width, dtype=dtype, seed=20, scale=2.0)
     gamma = (1 + 0.02 * torch.randn(H, width)).to(dtype).to(DEV)
     beta = (0.02 * torch.randn(H, width)).to(dtype).to(DEV)
     dy = randn(T, H, width, dtype=dtype, seed=21)
     y = torch.empty_like(x)
-    nat.gn_fwd(x, gamma, beta, y, H, width, act)
+    stats = torch.full((T * H, 2), float("nan"), device=DEV) if saved_stats else None
+    nat.gn_fwd(x, gamma, beta, y, H, width, act, stats=stats)
+    if saved_stats:  # (mean, rstd) per row, for the backward kernel
+        xd = x.double().view(T * H, width)
+        assert rel_err(stats[:, 0], xd.mean(-1)) < 1e-5 + 1e-6
+        assert rel_err(stats[:, 1], (xd.var(-1, unbiased=False) + 1e-5).rsqrt()) < 1e-5
     xr = x.double().requires_grad_(True)
     gr = gamma.double().requires_grad_(True)
     br = beta.double().requires_grad_(True)
@@ -192,7 +198,7 @@ def test_gn_fwd_bwd(nat, dtype, tol, width, act):
     dx = dx0.clone()
     dg = torch.zeros(H, width, device=DEV)
     db = torch.zeros(H, width, device=DEV)
-    nat.gn_bwd(dy, x, gamma, beta, dx, dg, db, H, width, act=act, dx_accumulate=True)
+    nat.gn_bwd(dy, x, gamma, beta, dx, dg, db, H, width, act=act, dx_accumulate=True, stats=stats)
     assert rel_err(dx, dx0.double() + xr.grad) < tol
     assert rel_err(dg, gr.grad) < tol
     assert rel_err(db, br.grad) < tol
