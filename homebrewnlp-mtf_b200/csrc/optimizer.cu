@@ -119,8 +119,39 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
   const int nd = T.ndim;
   const int cols = T.dims[nd - 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // Column chunking: blockIdx.y selects a chunk of 32 * VEC * NI columns, so a lane never owns more than NI vectors
+  // of a row whatever the last dim is (a [.., 1024] weight used to need the NI = 8 instantiation: 248 registers,
+  // one block per SM, 2.5 TB/s against 5.5 TB/s for the 512-wide tensors).
+  const int cbase = NI > 0 ? (int)blockIdx.y * (32 * VEC * NI) : 0;
+  if (cbase >= cols) return;  // whole block: this tensor is narrower than the widest one of the launch
   for (int i = threadIdx.x; i < cols; i += blockDim.x) s_col[i] = 0.f;
+  // min over the non-last dims' accumulators, one ROW PER THREAD: the index arithmetic (a divide and a modulo per
+  // dim) used to be done by every warp for its rows, i.e. 32 lanes computing the same thing.  The slot holds the
+  // row's minimum until the row is processed and its maximum afterwards.
+  const int row_begin = item_row0[item];
+  for (int rl = threadIdx.x; rl < item_rows[item]; rl += blockDim.x) {
+    int rem = row_begin + rl;
+    float mn = INFINITY;
+#pragma unroll
+    for (int i = 2; i >= 0; --i) {
+      if (i <= nd - 2) {
+        const int d = T.dims[i];
+        const int q = rem / d;
+        mn = fminf(mn, ld_state<TS>(T.acc[i], rem - q * d));
+        rem = q;
+      }
+    }
+    s_rowmax[rl] = mn;
+  }
   __syncthreads();
+  // the table entry's hot fields in registers (sT is shared memory: every use would be a reload)
+  float* const Tp = T.p;
+  const float* const Tg = T.g;
+  void* const Tm = T.m;
+  void* const Tshadow = T.shadow;
+  const int tril_s = T.tril_s;
+  const float wd = (T.decay && hp.weight_decay > 0.f) ? hp.lr * hp.weight_decay : 0.f;
+  const float nes_u = hp.nesterov ? 1.f : 0.f, nes_m = hp.nesterov ? hp.beta : 1.f;
 
   float scale = 1.f;
   if (hp.clip > 0.f) {
@@ -135,7 +166,7 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
   if (NI > 0) {
 #pragma unroll
     for (int i = 0; i < NIR; ++i) {
-      const int c = (lane + 32 * i) * VEC;
+      const int c = cbase + (lane + 32 * i) * VEC;
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
         cm[i * VEC + j] = 0.f;
@@ -143,34 +174,23 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
       }
     }
   }
-  const int row_end = item_row0[item] + item_rows[item];
+  const int row_end = row_begin + item_rows[item];
   const int iters = NI > 0 ? NI : (cols + 32 * VEC - 1) / (32 * VEC);
-  const bool tril_fast = T.tril_s > 0 && T.tril_s == cols;  // [.., S, S] map: col = c + j, row = r % S
+  const bool tril_fast = tril_s > 0 && tril_s == cols;  // [.., S, S] map: col = c + j, row = r % S
   float w2 = 0.f;  // sum cast_AT(p_new)^2 of this thread: next step's weight norm, for free
   // RG rows per warp per iteration: all their loads are issued before the first dependent instruction, which is
   // what gives the memory system enough to do (one row at a time left this kernel latency-bound at < 3 TB/s)
   constexpr int RG = 4;
-  for (int r0 = item_row0[item] + warp * RG; r0 < row_end; r0 += 8 * RG) {
-    int idx[RG][3];
+  for (int r0 = row_begin + warp * RG; r0 < row_end; r0 += 8 * RG) {
     float rowmin[RG], rowmax[RG];
 #pragma unroll
     for (int q = 0; q < RG; ++q) {
-      rowmin[q] = INFINITY;
+      rowmin[q] = r0 + q < row_end ? s_rowmax[r0 + q - row_begin] : INFINITY;
       rowmax[q] = 0.f;
-      int rem = r0 + q;
-#pragma unroll
-      for (int i = 2; i >= 0; --i) {
-        idx[q][i] = 0;
-        if (i <= nd - 2 && r0 + q < row_end) {
-          idx[q][i] = rem % T.dims[i];
-          rem /= T.dims[i];
-          rowmin[q] = fminf(rowmin[q], ld_state<TS>(T.acc[i], idx[q][i]));
-        }
-      }
     }
 #pragma unroll(NI > 0 ? NI : 1)
     for (int i = 0; i < iters; ++i) {  // NI > 0: fully unrolled (iters == NI); NI == 0: a plain loop
-      const int c = (lane + 32 * i) * VEC;
+      const int c = cbase + (lane + 32 * i) * VEC;
       if (c >= cols) continue;
       float pv[RG][VEC], gv[RG][VEC], mv[RG][VEC];
 #pragma unroll
@@ -178,24 +198,24 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
         if (r0 + q >= row_end) continue;
         const int64_t rbase = (int64_t)(r0 + q) * cols;
         if (VEC == 4) {
-          const float4 p4 = *reinterpret_cast<const float4*>(T.p + rbase + c);
-          const float4 g4 = *reinterpret_cast<const float4*>(T.g + rbase + c);
+          const float4 p4 = *reinterpret_cast<const float4*>(Tp + rbase + c);
+          const float4 g4 = *reinterpret_cast<const float4*>(Tg + rbase + c);
           pv[q][0] = p4.x; pv[q][1] = p4.y; pv[q][2] = p4.z; pv[q][3] = p4.w;
           gv[q][0] = g4.x; gv[q][1] = g4.y; gv[q][2] = g4.z; gv[q][3] = g4.w;
           if (sizeof(TS) == 2) {
-            const uint2 m2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(T.m) + rbase + c);
+            const uint2 m2 = *reinterpret_cast<const uint2*>(reinterpret_cast<const bf16*>(Tm) + rbase + c);
             const float2 a = unpack_bf16x2(m2.x), bb = unpack_bf16x2(m2.y);
             mv[q][0] = a.x; mv[q][1] = a.y; mv[q][2] = bb.x; mv[q][3] = bb.y;
           } else {
-            const float4 m4 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(T.m) + rbase + c);
+            const float4 m4 = *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(Tm) + rbase + c);
             mv[q][0] = m4.x; mv[q][1] = m4.y; mv[q][2] = m4.z; mv[q][3] = m4.w;
           }
         } else {
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
-            pv[q][j] = T.p[rbase + c + j];
-            gv[q][j] = T.g[rbase + c + j];
-            mv[q][j] = ld_state<TS>(T.m, rbase + c + j);
+            pv[q][j] = Tp[rbase + c + j];
+            gv[q][j] = Tg[rbase + c + j];
+            mv[q][j] = ld_state<TS>(Tm, rbase + c + j);
           }
         }
       }
@@ -217,57 +237,56 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
           rowmax[q] = fmaxf(rowmax[q], nu);
           // g / max(sqrt(nu), 1e-5)  (opt_rsqrt, src/optimizer/optimizers.py:13-14) without the IEEE sqrt + divide
           float u = g * (nu >= 1e-10f ? rsqrtf(nu) : 1e5f);
-          const float m_new = hp.beta * mv[q][j] + u;
-          u = hp.nesterov ? (u + hp.beta * m_new) : m_new;
-          u = u * hp.lr;
-          if (T.decay && hp.weight_decay > 0.f) {
+          const float m_new = fmaf(hp.beta, mv[q][j], u);
+          u = fmaf(nes_m, m_new, nes_u * u) * hp.lr;  // nesterov: u + beta m_new; plain: m_new
+          if (wd != 0.f) {
             const float w = hp.act_bf16 ? round_to<bf16>(pv[q][j]) : pv[q][j];
-            u += w * hp.lr * hp.weight_decay;
+            u = fmaf(w, wd, u);
           }
           pn[j] = pv[q][j] - u;
           mn[j] = m_new;
           sh[j] = pn[j];
           if (tril_fast) {
             if (c + j > row_in) sh[j] = 0.f;
-          } else if (T.tril_s > 0) {
+          } else if (tril_s > 0) {
             const int64_t e = rbase + c + j;
-            const int col = (int)(e % T.tril_s);
-            const int row = (int)((e / T.tril_s) % T.tril_s);
+            const int col = (int)(e % tril_s);
+            const int row = (int)((e / tril_s) % tril_s);
             if (col > row) sh[j] = 0.f;
           }
           const float wv = hp.act_bf16 ? round_to<bf16>(pn[j]) : pn[j];
           w2 += wv * wv;
         }
         if (VEC == 4) {
-          *reinterpret_cast<float4*>(T.p + rbase + c) = make_float4(pn[0], pn[1], pn[2], pn[3]);
+          *reinterpret_cast<float4*>(Tp + rbase + c) = make_float4(pn[0], pn[1], pn[2], pn[3]);
           if (sizeof(TS) == 2) {
             uint2 m2;
             m2.x = pack_bf16x2(mn[0], mn[1]);
             m2.y = pack_bf16x2(mn[2], mn[3]);
-            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(T.m) + rbase + c) = m2;
+            *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(Tm) + rbase + c) = m2;
           } else {
-            *reinterpret_cast<float4*>(reinterpret_cast<float*>(T.m) + rbase + c) =
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(Tm) + rbase + c) =
                 make_float4(mn[0], mn[1], mn[2], mn[3]);
           }
-          if (T.shadow) {
+          if (Tshadow) {
             if (hp.act_bf16) {
               uint2 s2;
               s2.x = pack_bf16x2(sh[0], sh[1]);
               s2.y = pack_bf16x2(sh[2], sh[3]);
-              *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(T.shadow) + rbase + c) = s2;
+              *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(Tshadow) + rbase + c) = s2;
             } else {
-              *reinterpret_cast<float4*>(reinterpret_cast<float*>(T.shadow) + rbase + c) =
+              *reinterpret_cast<float4*>(reinterpret_cast<float*>(Tshadow) + rbase + c) =
                   make_float4(sh[0], sh[1], sh[2], sh[3]);
             }
           }
         } else {
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
-            T.p[rbase + c + j] = pn[j];
-            reinterpret_cast<TS*>(T.m)[rbase + c + j] = from_f32<TS>(mn[j]);
-            if (T.shadow) {
-              if (hp.act_bf16) reinterpret_cast<bf16*>(T.shadow)[rbase + c + j] = __float2bfloat16_rn(sh[j]);
-              else reinterpret_cast<float*>(T.shadow)[rbase + c + j] = sh[j];
+            Tp[rbase + c + j] = pn[j];
+            reinterpret_cast<TS*>(Tm)[rbase + c + j] = from_f32<TS>(mn[j]);
+            if (Tshadow) {
+              if (hp.act_bf16) reinterpret_cast<bf16*>(Tshadow)[rbase + c + j] = __float2bfloat16_rn(sh[j]);
+              else reinterpret_cast<float*>(Tshadow)[rbase + c + j] = sh[j];
             }
           }
         }
@@ -276,7 +295,7 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
 #pragma unroll
     for (int q = 0; q < RG; ++q) {
       const float rm = warp_max(rowmax[q]);
-      if (lane == 0 && r0 + q < row_end) s_rowmax[r0 + q - item_row0[item]] = rm;
+      if (lane == 0 && r0 + q < row_end) s_rowmax[r0 + q - row_begin] = rm;
     }
   }
   __syncthreads();
@@ -304,7 +323,7 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
   if (NI > 0) {
 #pragma unroll
     for (int i = 0; i < NIR; ++i) {
-      const int c = (lane + 32 * i) * VEC;
+      const int c = cbase + (lane + 32 * i) * VEC;
 #pragma unroll
       for (int j = 0; j < VEC; ++j)
         if (c + j < cols && cm[i * VEC + j] > 0.f) atomic_max_nonneg(&s_col[c + j], cm[i * VEC + j]);
@@ -387,17 +406,9 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
   hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
   const size_t smem = (size_t)max_cols * sizeof(float);
   const int vec = vec4 ? 4 : 1;
-  const int ni = (max_cols + 32 * vec - 1) / (32 * vec);
-#define OBST_OPT(TS, V, N)                                                                                     \
-  opt_update_kernel<TS, V, N><<<(unsigned)nitems, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, norms, \
-                                                                    hp, wnext)
-#define OBST_OPT_NI(TS, V)                  \
-  do {                                      \
-    if (ni <= 4) OBST_OPT(TS, V, 4);        \
-    else if (ni <= 8) OBST_OPT(TS, V, 8);   \
-    else if (ni <= 16) OBST_OPT(TS, V, 16); \
-    else OBST_OPT(TS, V, 0);                \
-  } while (0)
+  const dim3 grid((unsigned)nitems, (unsigned)((max_cols + 32 * vec * 4 - 1) / (32 * vec * 4)));  // y: column chunks
+#define OBST_OPT_NI(TS, V) \
+  opt_update_kernel<TS, V, 4><<<grid, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, norms, hp, wnext)
   if (dtype_state == OBST_BF16) {
     if (vec4) OBST_OPT_NI(bf16, 4);
     else OBST_OPT_NI(bf16, 1);
@@ -408,7 +419,6 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
     OBST_REQUIRE(false, "obst_opt_update: bad state dtype %d", dtype_state);
   }
 #undef OBST_OPT_NI
-#undef OBST_OPT
   count_launch();
   return check_launch("obst_opt_update");
 }
@@ -565,17 +575,9 @@ extern "C" int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, 
   hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
   const size_t smem = (size_t)cols * sizeof(float);
   const int vec = (cols % 4 == 0) ? 4 : 1;
-  const int ni = (cols + 32 * vec - 1) / (32 * vec);
-#define OBST_NA(TS, V, N)                                                                                     \
-  opt_update_kernel<TS, V, N><<<(unsigned)f.nitems, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, \
-                                                                      norms, hp, nullptr)
-#define OBST_NA_NI(TS, V)                  \
-  do {                                     \
-    if (ni <= 4) OBST_NA(TS, V, 4);        \
-    else if (ni <= 8) OBST_NA(TS, V, 8);   \
-    else if (ni <= 16) OBST_NA(TS, V, 16); \
-    else OBST_NA(TS, V, 0);                \
-  } while (0)
+  const dim3 grid((unsigned)f.nitems, (unsigned)((cols + 32 * vec * 4 - 1) / (32 * vec * 4)));
+#define OBST_NA_NI(TS, V) \
+  opt_update_kernel<TS, V, 4><<<grid, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, norms, hp, nullptr)
   if (dtype_state == OBST_BF16) {
     if (vec == 4) OBST_NA_NI(bf16, 4);
     else OBST_NA_NI(bf16, 1);
@@ -584,7 +586,6 @@ extern "C" int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, 
     else OBST_NA_NI(float, 1);
   }
 #undef OBST_NA_NI
-#undef OBST_NA
   if (dtype_state == OBST_BF16) opt_finalize_kernel<bf16><<<1, 256, 0, st>>>(table);
   else opt_finalize_kernel<float><<<1, 256, 0, st>>>(table);
   count_launch(clip > 0.f ? 4 : 3);

@@ -128,7 +128,8 @@ class FusedOptimizer:
             # tensors of a class share one launch, so narrow tensors are not run with the widest instantiation
             per_lane = -(-cols // (128 if cols % 4 == 0 else 32))
             klass = 4 if per_lane <= 4 else (8 if per_lane <= 8 else (16 if per_lane <= 16 else 0))
-            rpi = min(2048, max(1, ITEM_ELEMS // cols))
+            # the update kernel splits wide rows into 512-column chunks (one block each): size items per chunk
+            rpi = min(2048, max(1, ITEM_ELEMS // min(cols, 512)))
             for r0 in range(0, rows, rpi):
                 items.append((klass if cols % 4 == 0 else -klass - 1, ti, r0, min(rpi, rows - r0), cols))
             off += sz + pd
@@ -167,7 +168,7 @@ class FusedOptimizer:
         self.wnorm_valid = False
         self.wnext.zero_()
 
-    def step(self, lr: float):
+    def step(self, lr: float, refresh_transposed: bool = True):
         lib = native.load()
         st = native.stream_ptr()
         p, plan = self.params, self.plan
@@ -188,8 +189,9 @@ class FusedOptimizer:
                                              plan.clip, plan.beta, int(plan.nesterov), float(lr),
                                              float(p.weight_decay), st), "obst_opt_update")
         native.check(lib.obst_opt_finalize(tp, nt, sdt, st), "obst_opt_finalize")
-        for v in self.variables:  # the update rewrote the shadows in place: transposed copies follow
-            v.refresh_t()
+        if refresh_transposed:  # the update rewrote the shadows in place: transposed copies follow
+            for v in self.variables:
+                v.refresh_t()
         self.wnorm_valid = plan.clip > 0
 
 
