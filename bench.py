@@ -310,26 +310,29 @@ def run_b200(args):
 
 
 class _JsonOnlyStdout:
-    """The contract is ONE JSON line on stdout: everything else the libraries print (the reference-style config
-    warnings, torch chatter) is diverted to stderr."""
+    """The contract is ONE JSON line on stdout.  Everything else -- the reference-style config warnings, torch
+    chatter, and lines native libraries write straight to file descriptor 1 (NCCL prints its version there on some
+    boxes) -- goes to stderr: fd 1 is pointed at stderr for the whole run and the JSON line is written to a
+    duplicate of the original descriptor."""
 
     def __init__(self):
-        self.real = sys.stdout
+        sys.stdout.flush()
+        self.fd = os.dup(1)
+        os.dup2(2, 1)
         self.json_open = False
 
     def write(self, text):
         if text.lstrip().startswith("{\""):
             self.json_open = True
-            self.real.write(text)
+            os.write(self.fd, text.encode())
         elif self.json_open and text.strip() == "":
-            self.real.write(text)  # the newline that print() sends after the JSON text
+            os.write(self.fd, text.encode())  # the newline that print() sends after the JSON text
             self.json_open = False
         else:
             self.json_open = False
             sys.stderr.write(text)
 
     def flush(self):
-        self.real.flush()
         sys.stderr.flush()
 
 
