@@ -137,7 +137,7 @@ def run_reference(args):
     if rank != 0:
         return
     value, cores, sample, sec = cpu_step_rate(args.workload, args.cpu_rows, args.steps, args.warmup, args.depth)
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+    line = {"impl": "reference", "metric": METRIC.replace("32big_mixer", args.workload), "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.workload} (bounded sample per step: fwd+bwd of {args.cpu_rows} sequence(s) at "
@@ -284,7 +284,8 @@ def run_b200(args):
                 "executed_tflops": gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None,
                 "whole_step_frac_of_peak": flops_tok * tokens_per_step / world / (ms_per_step * 1e-3) / 1e12 /
                 pk["tf_sustained"]}
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+    line = {"metric": METRIC.replace("32big_mixer", args.workload), "value": value, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16" if cfg["calculation_dtype"] == "bfloat16" else "f32",
             "data": "synthetic",

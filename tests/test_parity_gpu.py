@@ -171,22 +171,37 @@ def test_sub_block_forward_backward_parity(cuda, backend, c, dtype, tol):
     """One reversible sub-block f_c (block_config[c]) on O(1) inputs: f(x), J^T dy and every parameter gradient
     against the float64 oracle -- the per-layer bar of north_star (fp32 1e-5, bf16 2e-2), free of the
     reconstruction ill-conditioning the full-depth tests have to budget for."""
+    if dtype == "float32" and backend == 0:
+        pytest.skip("float32 always runs the SIMT GEMM")
+    _sub_block_parity(backend, c, dtype, tol, batch=3, seq=256, fph=64)
+
+
+@pytest.mark.parametrize("c", [0, 1])
+@pytest.mark.parametrize("name,seq,fph", [("32big_mixer", 512, 512), ("32ctx_mixer", 2048, 256),
+                                          ("32mixer_group", 256, 256)])
+def test_sub_block_parity_at_the_shapes_of_the_reference_configs(cuda, c, name, seq, fph):
+    """The same per-layer check at the FULL per-layer shapes of BASELINE.json's three model configs (8 heads,
+    sequence / features_per_head of configs/<name>.json, hence their W_in / W_mid / W_out / mixing-map sizes), bf16,
+    tcgen05 GEMMs; only the batch is reduced (2 sequences) so that the float64 oracle finishes in seconds
+    ("per-layer parity vs fp32 oracle at reduced B, <= 2e-2")."""
+    _sub_block_parity(0, c, "bfloat16", 2e-2, batch=2, seq=seq, fph=fph)
+
+
+def _sub_block_parity(backend, c, dtype, tol, batch, seq, fph):
     from obst import utils_core
     from obst.model.backend import run_tape
     from obst.model.frontend import block_part_fn
     from obst.utils_core import scoped
     from obst.utils_mtf import Tensor
-    if dtype == "float32" and backend == 0:
-        pytest.skip("float32 always runs the SIMT GEMM")
     cfg = copy.deepcopy(orc.TINY_CONFIG)
-    cfg.update(depth=1, train_batch_size=3, sequence_length=256, features_per_head=64, calculation_dtype=dtype)
+    cfg.update(depth=1, train_batch_size=batch, sequence_length=seq, features_per_head=fph, calculation_dtype=dtype)
     sh = orc.Shapes(cfg)
     op = orc.init_params(sh, seed=5)
     names = _block_vars(sh, op, c)
     seen = {k: (orc.round_bf16(v) if dtype == "bfloat16" else v) for k, v in op.items()}
     params = make_params(cfg, op, gemm_backend=backend)
     params.import_variables = [op[n] for n in names]
-    B, S, H, K = 3, sh.sequence_length, sh.heads, sh.features_per_head
+    B, S, H, K = batch, sh.sequence_length, sh.heads, sh.features_per_head
     rng = np.random.default_rng(6)
     tdt = torch.float32 if dtype == "float32" else torch.bfloat16
     x = torch.from_numpy(rng.standard_normal((B, S, H, K)).astype(np.float32)).to(tdt).cuda()
