@@ -403,10 +403,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* rbar = bars + 2 * STAGES + 4;        // [8 warps][2 buffers] R-tile arrival
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4 + 2 * EPI_WARPS);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle and CTA rank from blockIdx (clusters are (CG,1,1) on a 1-D grid): both are then
+  // warp-uniform values for the compiler, and everything derived from them can live in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  uint32_t rank = 0;
-  if (CG == 2) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const uint32_t rank = CG == 2 ? (blockIdx.x & 1u) : 0u;
   const bool leader = rank == 0;
   const int cluster_id = blockIdx.x / CG;
   const int num_clusters = gridDim.x / CG;
