@@ -31,6 +31,8 @@ def timeit(fn, iters=10, warm=3):
 
 
 def main():
+    if os.environ.get("PROBE_LIB"):  # A/B of two builds on the same box
+        nat.LIB_PATH = os.environ["PROBE_LIB"]
     nat.load()
     T = int(os.environ.get("PROBE_T", 65536))
     F, I, H, K, K2, S = 4096, 512, 8, 512, 1024, 512

@@ -147,6 +147,54 @@ __device__ __forceinline__ void tma_load_5d_elect(uint32_t dst, const CUtensorMa
   }
 }
 
+// Epilogue-side elected-lane helpers (called by a whole converged epilogue warp).  elect.sync names the same
+// leader for the same mask every time, so the bulk-group bookkeeping (commit / wait_group are per thread) stays
+// with one lane.
+__device__ __forceinline__ void tma_store_commit_elect(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2,
+                                                       int c3, int c4) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "@P cp.async.bulk.tensor.5d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];\n"
+      "@P cp.async.bulk.commit_group;\n"
+      "}\n" ::"l"(reinterpret_cast<uint64_t>(map)),
+      "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_wait_read0_elect() {
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "@P cp.async.bulk.wait_group.read 0;\n"
+      "}\n" ::
+          : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all_elect() {
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "@P cp.async.bulk.wait_group 0;\n"
+      "}\n" ::
+          : "memory");
+}
+// expect `bytes` on `bar` and request one R box into `dst` (CTA-local barrier, never the pair variant)
+__device__ __forceinline__ void tma_load_r_elect(uint32_t dst, const CUtensorMap* map, uint32_t bar, uint32_t bytes,
+                                                 int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "@P mbarrier.arrive.expect_tx.shared::cta.b64 _, [%2], %3;\n"
+      "@P cp.async.bulk.tensor.5d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%4, %5, %6, %7, "
+      "%8}], [%2];\n"
+      "}\n" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(bytes), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(0)
+      : "memory");
+}
+
 __device__ __forceinline__ void cluster_sync() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
   asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
@@ -548,20 +596,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int col0 = t.n0 + c0 * EPI_BOX_COLS, col1 = t.n0 + c1 * EPI_BOX_COLS;
         const bool live0 = c0 < nchunks && row0 < p.M && col0 < p.N;  // warp-uniform
         const bool live1 = c1 < nchunks && row0 < p.M && col1 < p.N;
-        if (lane == 0) {
-          bulk_wait_read<0>();  // last tile's stores have read both slabs (they were issued a whole tile ago)
-          if (p.epi >= 2) {
-            if (live0) {
-              mbar_expect_tx(rb0, EPI_BUF_BYTES);
-              tma_load_5d<1>(buf0, &tmR, rb0, col0, row0, t.glo, t.ghi, 0);
-            }
-            if (live1) {
-              mbar_expect_tx(rb0 + 1, EPI_BUF_BYTES);
-              tma_load_5d<1>(buf0 + EPI_BUF_BYTES, &tmR, rb0 + 1, col1, row0, t.glo, t.ghi, 0);
-            }
-          }
-        }
+        bulk_wait_read0_elect();  // last tile's stores have read both slabs (they were issued a whole tile ago)
         __syncwarp();
+        if (p.epi >= 2) {
+          if (live0) tma_load_r_elect(smem_u32(buf0), &tmR, smem_u32(rb0), EPI_BUF_BYTES, col0, row0, t.glo, t.ghi);
+          if (live1)
+            tma_load_r_elect(smem_u32(buf0 + EPI_BUF_BYTES), &tmR, smem_u32(rb0 + 1), EPI_BUF_BYTES, col1, row0, t.glo,
+                             t.ghi);
+        }
         mbar_wait(&tfull_bar[acc], acc_phase, 3);
         tcgen05_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
@@ -596,17 +638,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           fence_async_smem();
           __syncwarp();
-          if (lane == 0) {
-            tma_store_5d(&tmD, buf, sl == 0 ? col0 : col1, row0, t.glo, t.ghi, 0);
-            bulk_commit();
-          }
+          tma_store_commit_elect(&tmD, smem_u32(buf), sl == 0 ? col0 : col1, row0, t.glo, t.ghi, 0);
         }
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
         }
       }
-      if (lane == 0) bulk_wait_all();
+      bulk_wait_all_elect();
       __syncwarp();
     } else {
       // fp32 output (plain store or split-K / cross-depth accumulation with red.global.add)
