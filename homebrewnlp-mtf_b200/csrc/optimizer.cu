@@ -96,6 +96,7 @@ static constexpr int OPT_MAX_ITEM_ROWS = 2048;  // rows one work item may cover 
 struct OptHyper {
   float clip, beta, lr, weight_decay;
   int nesterov, act_bf16, grad_bf16;
+  int sm3_only;  // generic optimizer chains (obst_opt_stage): write g * opt_rsqrt(nu) back to g, touch nothing else
 };
 
 // NI > 0: lanes keep their column maxima in registers (cols <= 32*VEC*NI).  NI == 0: any cols, slower.
@@ -237,6 +238,10 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
           rowmax[q] = fmaxf(rowmax[q], nu);
           // g / max(sqrt(nu), 1e-5)  (opt_rsqrt, src/optimizer/optimizers.py:13-14) without the IEEE sqrt + divide
           float u = g * (nu >= 1e-10f ? rsqrtf(nu) : 1e5f);
+          if (hp.sm3_only) {
+            pn[j] = u;
+            continue;
+          }
           const float m_new = fmaf(hp.beta, mv[q][j], u);
           u = fmaf(nes_m, m_new, nes_u * u) * hp.lr;  // nesterov: u + beta m_new; plain: m_new
           if (wd != 0.f) {
@@ -256,6 +261,16 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
           }
           const float wv = hp.act_bf16 ? round_to<bf16>(pn[j]) : pn[j];
           w2 += wv * wv;
+        }
+        if (hp.sm3_only) {
+          float* gw = const_cast<float*>(Tg) + rbase + c;
+          if (VEC == 4) {
+            *reinterpret_cast<float4*>(gw) = make_float4(pn[0], pn[1], pn[2], pn[3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) gw[j] = pn[j];
+          }
+          continue;
         }
         if (VEC == 4) {
           *reinterpret_cast<float4*>(Tp + rbase + c) = make_float4(pn[0], pn[1], pn[2], pn[3]);
@@ -404,6 +419,7 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
   OptHyper hp;
   hp.clip = clip; hp.beta = beta; hp.lr = lr; hp.weight_decay = weight_decay;
   hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
+  hp.sm3_only = 0;
   const size_t smem = (size_t)max_cols * sizeof(float);
   const int vec = vec4 ? 4 : 1;
   const dim3 grid((unsigned)nitems, (unsigned)((max_cols + 32 * vec * 4 - 1) / (32 * vec * 4)));  // y: column chunks
@@ -421,6 +437,37 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
 #undef OBST_OPT_NI
   count_launch();
   return check_launch("obst_opt_update");
+}
+
+/* SM3 as a stand-alone stage of a generic chain: g <- g * opt_rsqrt(nu), accumulators max-reduced into acc_new
+ * (obst_opt_finalize commits them).  Same kernel as obst_opt_update with everything after SM3 switched off. */
+int obst_opt_sm3_stage(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
+                       const int32_t* item_row0, const int32_t* item_rows, int32_t nitems, int32_t max_cols,
+                       int32_t vec4, int32_t dtype_state, void* stream) {
+  OBST_REQUIRE(table && item_tensor && item_row0 && item_rows, "obst_opt_sm3_stage: null argument");
+  OBST_REQUIRE(max_cols > 0 && max_cols <= 12288, "obst_opt_sm3_stage: last dim %d unsupported", max_cols);
+  if (nitems <= 0) return OBST_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  OptHyper hp;
+  hp.clip = 0.f; hp.beta = 0.f; hp.lr = 1.f; hp.weight_decay = 0.f;
+  hp.nesterov = 0; hp.act_bf16 = 0; hp.grad_bf16 = 0; hp.sm3_only = 1;
+  const size_t smem = (size_t)max_cols * sizeof(float);
+  const int vec = vec4 ? 4 : 1;
+  const dim3 grid((unsigned)nitems, (unsigned)((max_cols + 32 * vec * 4 - 1) / (32 * vec * 4)));
+#define OBST_SM3(TS, V) \
+  opt_update_kernel<TS, V, 4><<<grid, 256, smem, st>>>(table, item_tensor, item_row0, item_rows, nullptr, hp, nullptr)
+  if (dtype_state == OBST_BF16) {
+    if (vec4) OBST_SM3(bf16, 4);
+    else OBST_SM3(bf16, 1);
+  } else if (dtype_state == OBST_F32) {
+    if (vec4) OBST_SM3(float, 4);
+    else OBST_SM3(float, 1);
+  } else {
+    OBST_REQUIRE(false, "obst_opt_sm3_stage: bad state dtype %d", dtype_state);
+  }
+#undef OBST_SM3
+  count_launch();
+  return check_launch("obst_opt_sm3_stage");
 }
 
 int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dtype_state, void* stream) {
@@ -573,6 +620,7 @@ extern "C" int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, 
   OptHyper hp;
   hp.clip = clip; hp.beta = beta; hp.lr = lr; hp.weight_decay = weight_decay;
   hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
+  hp.sm3_only = 0;
   const size_t smem = (size_t)cols * sizeof(float);
   const int vec = (cols % 4 == 0) ? 4 : 1;
   const dim3 grid((unsigned)f.nitems, (unsigned)((cols + 32 * vec * 4 - 1) / (32 * vec * 4)));

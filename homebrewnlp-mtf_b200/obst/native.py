@@ -40,6 +40,18 @@ class OptTensor(ctypes.Structure):
                 ("tril_s", c_i32), ("pad_", c_i32)]
 
 
+class OptStageArgs(ctypes.Structure):  # obst_opt_stage_args
+    _fields_ = [("stage", c_i32), ("dtype_act", c_i32), ("dtype_state", c_i32), ("flags", c_i32),
+                ("f", c_float * 4), ("grad_base", c_void_p), ("work", c_void_p), ("work2", c_void_p),
+                ("state_a", c_void_p), ("state_b", c_void_p), ("scalars_in", c_void_p), ("scalars_out", c_void_p),
+                ("sums", c_void_p), ("sums2", c_void_p)]
+
+
+# the OBST_STAGE_* enum of include/obst_b200.h
+(STAGE_REDUCE, STAGE_ROUND_BF16, STAGE_COPY, STAGE_ADAPTIVE_CLIP, STAGE_L2NORM_CLIP, STAGE_GLOBAL_L2NORM_CLIP,
+ STAGE_VALUE_CLIP, STAGE_GRAD_CENTRALISE, STAGE_WEIGHT_CENTRALISE, STAGE_LEARNING_RATE, STAGE_MOMENTUM, STAGE_ADAM,
+ STAGE_NOVOGRAD, STAGE_GRAFT_COMBINE, STAGE_APPLY) = range(15)
+
 # name -> (restype, argtypes); must list every symbol include/obst_b200.h declares (tests check this)
 SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] = {
     "obst_version": (c_int, []),
@@ -65,6 +77,10 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_opt_update": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32, c_i32,
                                 c_i32, c_void_p, c_void_p, c_float, c_float, c_i32, c_float, c_float, c_void_p]),
     "obst_opt_finalize": (c_int, [c_void_p, c_i32, c_i32, c_void_p]),
+    "obst_opt_stage": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, ctypes.POINTER(OptStageArgs),
+                               c_void_p]),
+    "obst_opt_sm3_stage": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32,
+                                   c_void_p]),
     "obst_opt_step_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, ctypes.POINTER(c_void_p),
                                       ctypes.POINTER(c_i32), c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_float,
                                       c_float, c_i32, c_float, c_float, c_void_p]),

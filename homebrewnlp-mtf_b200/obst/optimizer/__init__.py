@@ -18,7 +18,7 @@ from ..utils_mtf import feature_dims_used
 from .backend import slot_name
 from .context import OptimizerCtx
 from .learning_rate import get_learning_rate
-from .optimizers import OPTIMIZERS, FusedPlan, lower_plan
+from .optimizers import OPTIMIZERS, FusedPlan, GenericPlan, lower_plan
 
 ITEM_ELEMS = 32768  # elements per work item of the fused kernels
 
@@ -168,7 +168,158 @@ class FusedOptimizer:
         self.wnorm_valid = False
         self.wnext.zero_()
 
-    def step(self, lr: float, refresh_transposed: bool = True):
+    # ------------------------------------------------------------------------------------------------------
+    # generic chains: one launch per stage (obst_opt_stage), slots in flat buffers laid out like flat_grad
+    # ------------------------------------------------------------------------------------------------------
+    def _flat_state(self, slot: str) -> torch.Tensor:
+        """Flat state buffer of one slot name for ALL variables (zeros on first use, src/optimizer/backend.py:23-25);
+        per-variable views are published in self.slots under the reference's names."""
+        if slot == "momentum":
+            return self.flat_momentum
+        bufs = self.__dict__.setdefault("_state_bufs", {})
+        if slot not in bufs:
+            buf = torch.zeros_like(self.flat_momentum)
+            bufs[slot] = buf
+            for v, (off, sz) in zip(self.variables, self.offsets):
+                self.slots[slot_name(self.params, v.name, slot)] = buf[off:off + sz].view(v.data.shape)
+        return bufs[slot]
+
+    def _scratch(self, name: str, numel: int, dtype) -> torch.Tensor:
+        bufs = self.__dict__.setdefault("_scratch_bufs", {})
+        if name not in bufs:
+            bufs[name] = torch.zeros(numel, dtype=dtype, device=self.flat_grad.device)
+        return bufs[name]
+
+    def _stage(self, stage: int, work: torch.Tensor, f=(), flags: int = 0, work2=None, state_a=None, state_b=None,
+               scalars=None, sums=None, sums2=None):
+        a = native.OptStageArgs()
+        a.stage, a.flags = stage, flags
+        a.dtype_act, a.dtype_state = native.dtype_code(self.act_dtype), native.dtype_code(self.state_dtype)
+        for i, v in enumerate(f):
+            a.f[i] = float(v)
+        a.grad_base, a.work = self.flat_grad.data_ptr(), work.data_ptr()
+        a.work2 = None if work2 is None else work2.data_ptr()
+        a.state_a = None if state_a is None else state_a.data_ptr()
+        a.state_b = None if state_b is None else state_b.data_ptr()
+        if scalars is not None:
+            a.scalars_in, a.scalars_out = scalars[0].data_ptr(), scalars[1].data_ptr()
+        a.sums = None if sums is None else sums.data_ptr()
+        a.sums2 = None if sums2 is None else sums2.data_ptr()
+        native.check(native.load().obst_opt_stage(self.table.data_ptr(), len(self.variables),
+                                                  self.item_tensor.data_ptr(), self.item_row0.data_ptr(),
+                                                  self.item_rows.data_ptr(), self.n_items, ctypes.byref(a),
+                                                  native.stream_ptr()), "obst_opt_stage")
+
+    def _run_stage(self, name: str, args: typing.Tuple[str, ...], work: torch.Tensor, lr: float, step_count: int):
+        """One registered stage (src/optimizer/optimizers.py:32-151) on the working gradient buffer `work`."""
+        import numpy as np
+        N = native
+        nt = len(self.variables)
+        f32 = np.float32
+        b1, b2 = f32(self.params.opt_beta1), f32(self.params.opt_beta2)
+        sums = self._scratch("sums", 4 * nt, torch.float64)
+
+        def reduce_into(dst, src=work):
+            self._stage(N.STAGE_REDUCE, src, flags=2, sums=dst)
+
+        def debias(beta):  # debias_momentum, optimizers.py:17-18, in fp32 like the graph
+            return f32(1) / (f32(1) - np.power(beta, f32(step_count)))
+
+        if name == "adaptive_clip":
+            reduce_into(sums)
+            self._stage(N.STAGE_ADAPTIVE_CLIP, work, f=[args[0]], sums=sums)
+        elif name == "l2norm_clip":
+            reduce_into(sums)
+            self._stage(N.STAGE_L2NORM_CLIP, work, f=[args[0]], sums=sums)
+        elif name == "global_l2norm_clip":  # norm of the RAW gradients of all variables, taken once per step
+            self._stage(N.STAGE_GLOBAL_L2NORM_CLIP, work, f=[args[0]], sums=self._scratch("sums_raw", 4 * nt,
+                                                                                          torch.float64))
+        elif name == "value_clip":
+            self._stage(N.STAGE_VALUE_CLIP, work, f=[args[0]])
+        elif name == "gradient_centralisation":
+            reduce_into(sums)
+            self._stage(N.STAGE_GRAD_CENTRALISE, work, sums=sums)
+        elif name == "weight_centralisation":
+            reduce_into(sums)
+            self._stage(N.STAGE_WEIGHT_CENTRALISE, work, sums=sums)
+        elif name == "learning_rate":
+            self._stage(N.STAGE_LEARNING_RATE, work, f=[lr])
+        elif name == "momentum":
+            self._stage(N.STAGE_MOMENTUM, work, f=[args[0], args[1]], flags=int(bool(int(args[2]))),
+                        state_a=self._flat_state("momentum"))
+        elif name == "adam":
+            self._stage(N.STAGE_ADAM, work, f=[b1, b2, debias(b1), debias(b2)],
+                        state_a=self._flat_state("exp_avg_p1"), state_b=self._flat_state("exp_avg_p2"))
+        elif name == "novograd":
+            reduce_into(sums)
+            pair = self.__dict__.setdefault("_novograd_p2", [torch.zeros(nt, dtype=self.state_dtype,
+                                                                         device=work.device) for _ in range(2)])
+            self._stage(N.STAGE_NOVOGRAD, work, f=[b1, b2, 0.0, debias(b2)], state_a=self._flat_state("exp_avg_p1"),
+                        scalars=pair, sums=sums)
+            pair.reverse()  # [0] is always the current exp_avg_p2
+            for i, v in enumerate(self.variables):
+                self.slots[slot_name(self.params, v.name, "exp_avg_p2")] = pair[0][i]
+        elif name == "sm3":
+            table = self.table if work is self.flat_grad else self._shifted_table(work)
+            lib, st, sdt = native.load(), native.stream_ptr(), native.dtype_code(self.state_dtype)
+            for g in self.groups:
+                o = 4 * g["item0"]
+                native.check(lib.obst_opt_sm3_stage(table.data_ptr(), nt, self.item_tensor.data_ptr() + o,
+                                                    self.item_row0.data_ptr() + o, self.item_rows.data_ptr() + o,
+                                                    g["items"], g["max_cols"], g["vec4"], sdt, st),
+                             "obst_opt_sm3_stage")
+            native.check(lib.obst_opt_finalize(table.data_ptr(), nt, sdt, st), "obst_opt_finalize")
+        elif name == "graft":  # direction of g, magnitude of the inner optimizer's step (optimizers.py:147-151)
+            sums_g = self._scratch("sums_graft", 4 * nt, torch.float64)
+            tmp = self._scratch("graft_work", self.flat_grad.numel(), torch.float32)
+            reduce_into(sums_g)
+            self._stage(N.STAGE_COPY, work, work2=tmp)
+            self._run_stage(args[0], tuple(args[1:]), tmp, lr, step_count)
+            sums_inner = self._scratch("sums_inner", 4 * nt, torch.float64)
+            reduce_into(sums_inner, tmp)
+            self._stage(N.STAGE_GRAFT_COMBINE, work, sums=sums_g, sums2=sums_inner)
+        else:
+            raise KeyError(name)
+
+    def _shifted_table(self, work: torch.Tensor) -> torch.Tensor:
+        """The tensor table with every g pointer moved into `work` (same layout as flat_grad): for the SM3 stage
+        when it runs on a copy of the gradient (graft:sm3)."""
+        cache = self.__dict__.setdefault("_shifted_tables", {})
+        key = work.data_ptr()
+        if key not in cache:
+            n = len(self.variables)
+            raw = bytearray(self.table.cpu().numpy().tobytes())
+            table = (native.OptTensor * n).from_buffer(raw)
+            delta = work.data_ptr() - self.flat_grad.data_ptr()
+            for t in table:
+                t.g = t.g + delta
+            cache[key] = torch.frombuffer(bytearray(bytes(table)), dtype=torch.uint8).to(work.device)
+        return cache[key]
+
+    def _step_generic(self, lr: float, step_count: int, refresh_transposed: bool):
+        N = native
+        plan: GenericPlan = self.plan
+        work = self.flat_grad
+        if self.act_dtype == torch.bfloat16:  # the graph hands over activation-dtype gradients
+            self._stage(N.STAGE_ROUND_BF16, work)
+
+        def uses(stage_name, stages):
+            return any(n == stage_name or (n == "graft" and a and a[0] == stage_name) for n, a in stages)
+
+        if uses("global_l2norm_clip", plan.stages):
+            self._stage(N.STAGE_REDUCE, work, flags=2, sums=self._scratch("sums_raw", 4 * len(self.variables),
+                                                                          torch.float64))
+        for name, args in plan.stages:
+            self._run_stage(name, args, work, lr, step_count)
+        self._stage(N.STAGE_APPLY, work, f=[float(lr) * float(self.params.weight_decay)])
+        self.wnorm_valid = False
+        if refresh_transposed:
+            for v in self.variables:
+                v.refresh_t()
+
+    def step(self, lr: float, refresh_transposed: bool = True, step_count: int = 1):
+        if isinstance(self.plan, GenericPlan):
+            return self._step_generic(lr, step_count, refresh_transposed)
         lib = native.load()
         st = native.stream_ptr()
         p, plan = self.params, self.plan
@@ -206,7 +357,7 @@ def update(ctx: OptimizerCtx):
     opt_state: FusedOptimizer = params.optimizer_state
     if opt_state.plan != plan:
         raise RuntimeError("optimizer string changed after the optimizer state was created")
-    opt_state.step(ctx.learning_rate)
+    opt_state.step(ctx.learning_rate, step_count=ctx.step_count)
     ctx.update_ops.extend(v.name for v in opt_state.variables)
 
 

@@ -1,18 +1,35 @@
 """Optimizer stages chained by name (src/optimizer/optimizers.py:131-151).
 
 The reference's stage functions add graph nodes; one `sess.run` later executes the whole chain per variable.
-Here each stage appends itself to `ctx.plan`, and `lower_plan` maps the finished plan onto the fused multi-tensor
-kernels (obst_opt_norms / obst_opt_update / obst_opt_finalize): the plan
+Here each stage appends itself to `ctx.plan`, and `lower_plan` maps the finished plan onto kernels:
     [adaptive_clip:<c>] - sm3 - momentum:<beta>:1:<nesterov> - learning_rate
-is what those kernels realise in one HBM pass.  Other registered stages raise until they get a kernel
-(SURVEY.md 8(f) item 1)."""
+(the hot path's chain) becomes ONE fused HBM pass (obst_opt_norms / obst_opt_update / obst_opt_finalize); any other
+chain of registered stages runs stage by stage (obst_opt_stage / obst_opt_sm3_stage), one launch each."""
 import typing
 
 from .context import OptimizerCtx
 
+# name -> number of string arguments the reference's stage function takes (graft: the inner optimizer + its own)
+STAGE_ARGS = {"adam": 0, "sm3": 0, "novograd": 0, "adaptive_clip": 1, "l2norm_clip": 1, "value_clip": 1,
+              "gradient_centralisation": 0, "weight_centralisation": 0, "learning_rate": 0, "global_l2norm_clip": 1,
+              "momentum": 3}
+
+
+def _check_args(name: str, args: typing.Tuple[str, ...]):
+    if name == "graft":
+        if not args or args[0] not in STAGE_ARGS:
+            raise ValueError(f"graft needs a registered inner optimizer, got {args!r}")
+        _check_args(args[0], tuple(args[1:]))
+        return
+    if len(args) != STAGE_ARGS[name]:
+        raise TypeError(f"optimizer stage '{name}' takes {STAGE_ARGS[name]} argument(s), got {len(args)}: {args!r}")
+    for a in args:
+        float(a)
+
 
 def _stage(name: str):
     def fn(ctx: OptimizerCtx, *args: str):
+        _check_args(name, tuple(args))
         ctx.plan.append((name, tuple(args)))
         return ctx.grad
 
@@ -20,32 +37,11 @@ def _stage(name: str):
     return fn
 
 
-def _unsupported(name: str):
-    def fn(ctx: OptimizerCtx, *args: str):
-        raise NotImplementedError(f"optimizer stage '{name}' is registered by the reference but has no fused B200 "
-                                  f"kernel yet (SURVEY.md 8(f))")
-
-    fn.__name__ = name
-    return fn
-
-
-sm3 = _stage("sm3")
-adaptive_gradient_clipping = _stage("adaptive_clip")
-multiply_learning_rate = _stage("learning_rate")
-momentum = _stage("momentum")
-
-OPTIMIZERS = {"adam": _unsupported("adam"),
-              "sm3": sm3,
-              "novograd": _unsupported("novograd"),
-              "adaptive_clip": adaptive_gradient_clipping,
-              "l2norm_clip": _unsupported("l2norm_clip"),
-              "value_clip": _unsupported("value_clip"),
-              "gradient_centralisation": _unsupported("gradient_centralisation"),
-              "weight_centralisation": _unsupported("weight_centralisation"),
-              "learning_rate": multiply_learning_rate,
-              "global_l2norm_clip": _unsupported("global_l2norm_clip"),
-              "momentum": momentum,
-              "graft": _unsupported("graft")}
+OPTIMIZERS = {name: _stage(name) for name in
+              ("adam", "sm3", "novograd", "adaptive_clip", "l2norm_clip", "value_clip", "gradient_centralisation",
+               "weight_centralisation", "learning_rate", "global_l2norm_clip", "momentum", "graft")}
+sm3, momentum = OPTIMIZERS["sm3"], OPTIMIZERS["momentum"]
+adaptive_gradient_clipping, multiply_learning_rate = OPTIMIZERS["adaptive_clip"], OPTIMIZERS["learning_rate"]
 
 
 class FusedPlan(typing.NamedTuple):
@@ -54,17 +50,19 @@ class FusedPlan(typing.NamedTuple):
     nesterov: bool
 
 
-def lower_plan(plan: typing.List[typing.Tuple[str, tuple]]) -> FusedPlan:
+class GenericPlan(typing.NamedTuple):
+    stages: typing.Tuple[typing.Tuple[str, typing.Tuple[str, ...]], ...]
+
+
+def lower_plan(plan: typing.List[typing.Tuple[str, tuple]]) -> typing.Union[FusedPlan, GenericPlan]:
     names = [p[0] for p in plan]
     clip = 0.0
     rest = list(plan)
     if names and names[0] == "adaptive_clip":
         clip = float(rest[0][1][0])
         rest = rest[1:]
-    if [p[0] for p in rest] != ["sm3", "momentum", "learning_rate"]:
-        raise NotImplementedError(f"optimizer chain {'-'.join(names)!r}: the fused kernel implements "
-                                  f"'[adaptive_clip:c-]sm3-momentum:b:1:n-learning_rate'")
-    margs = rest[1][1]
-    if len(margs) != 3 or float(margs[1]) != 1.0:
-        raise NotImplementedError(f"momentum:{':'.join(margs)}: gradient_multiplier must be 1")
-    return FusedPlan(clip, float(margs[0]), bool(int(margs[2])))
+    if [p[0] for p in rest] == ["sm3", "momentum", "learning_rate"]:
+        margs = rest[1][1]
+        if float(margs[1]) == 1.0:
+            return FusedPlan(clip, float(margs[0]), bool(int(margs[2])))
+    return GenericPlan(tuple((n, tuple(a)) for n, a in plan))

@@ -210,6 +210,59 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
 int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dtype_state,
                       void* stream);
 
+/* ---- generic optimizer chains ---------------------------------------------------------------------
+ * Every stage the reference registers in OPTIMIZERS (src/optimizer/optimizers.py:131-151), one launch per
+ * stage over the same tensor table and work list, for optimizer strings other than the hot path's
+ * (which obst_opt_update runs fused).  A stage rewrites the working gradient `work` in place -- as the
+ * reference's stage functions return the new ctx.grad -- and keeps its slots in flat state buffers laid
+ * out like the flat gradient buffer (element i of tensor t lives at (table[t].g - grad_base) + i).
+ *   REDUCE             sums[t] += {sum g^2, sum g, sum cast_AT(p)^2, sum cast_AT(p)} (flags&2: clear first)
+ *   ROUND_BF16         g <- bf16(g): the gradient dtype the graph hands over (src/optimizer/__init__.py:180)
+ *   COPY               work2 <- work
+ *   ADAPTIVE_CLIP      f[0]=clip                                   optimizers.py:79-84    (reads sums)
+ *   L2NORM_CLIP        f[0]=clip                                   optimizers.py:87-90    (reads sums)
+ *   GLOBAL_L2NORM_CLIP f[0]=clip; sums = REDUCE of the RAW grads   optimizers.py:93-98
+ *   VALUE_CLIP         f[0]=clip                                   optimizers.py:101-103
+ *   GRAD_CENTRALISE / WEIGHT_CENTRALISE                            optimizers.py:106-111  (reads sums)
+ *   LEARNING_RATE      f[0]=lr                                     optimizers.py:114-115
+ *   MOMENTUM           f[0]=momentum mult, f[1]=grad mult, flags&1 nesterov; state_a   optimizers.py:118-128
+ *   ADAM               f={beta1, beta2, 1/(1-beta1^t), 1/(1-beta2^t)}; state_a=exp_avg_p1, state_b=exp_avg_p2
+ *                                                                  optimizers.py:32-43
+ *   NOVOGRAD           f={beta1, beta2, -, 1/(1-beta2^t)}; state_a=exp_avg_p1; scalars_in/out = exp_avg_p2
+ *                      (one state-dtype scalar per tensor, in != out)    optimizers.py:46-57 (reads sums)
+ *   GRAFT_COMBINE      g <- g * rsqrt(sum g^2) * sqrt(sum inner^2); sums of g, sums2 of the inner step
+ *                                                                  optimizers.py:147-151
+ *   APPLY              p <- p - (g + [decay] cast_AT(p) * f[0]); shadow refreshed;  f[0] = lr * weight_decay
+ *                                                                  src/optimizer/__init__.py:49-66
+ * SM3 as a stage of such a chain is obst_opt_sm3_stage (+ obst_opt_finalize). */
+enum {
+  OBST_STAGE_REDUCE = 0, OBST_STAGE_ROUND_BF16, OBST_STAGE_COPY, OBST_STAGE_ADAPTIVE_CLIP,
+  OBST_STAGE_L2NORM_CLIP, OBST_STAGE_GLOBAL_L2NORM_CLIP, OBST_STAGE_VALUE_CLIP,
+  OBST_STAGE_GRAD_CENTRALISE, OBST_STAGE_WEIGHT_CENTRALISE, OBST_STAGE_LEARNING_RATE,
+  OBST_STAGE_MOMENTUM, OBST_STAGE_ADAM, OBST_STAGE_NOVOGRAD, OBST_STAGE_GRAFT_COMBINE, OBST_STAGE_APPLY
+};
+typedef struct obst_opt_stage_args {
+  int32_t stage, dtype_act, dtype_state, flags;
+  float f[4];
+  const float* grad_base; /* start of the flat gradient buffer the table's g pointers point into */
+  float* work;            /* buffer the stage rewrites (normally == grad_base) */
+  float* work2;           /* COPY destination */
+  void* state_a;
+  void* state_b;
+  const void* scalars_in;
+  void* scalars_out;
+  double* sums;           /* [ntensors][4] */
+  const double* sums2;    /* [ntensors][4] */
+} obst_opt_stage_args;
+int obst_opt_stage(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
+                   const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
+                   const obst_opt_stage_args* args, void* stream);
+/* g <- g * opt_rsqrt(nu) for every tensor of the work list (src/optimizer/optimizers.py:60-76); the new
+ * accumulators are max-reduced into acc_new, obst_opt_finalize commits them.  Reads table[t].g in place. */
+int obst_opt_sm3_stage(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
+                       const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
+                       int32_t max_cols, int32_t vec4, int32_t dtype_state, void* stream);
+
 /* ---- the same update for ONE tensor, without any device allocation -----------------------------------
  * No counterpart in the reference (its update always runs inside the Mesh-TensorFlow graph).
  * obst_opt_norms/update/finalize need a tensor table, a work list, norm sums and SM3 staging in device

@@ -487,49 +487,115 @@ def init_opt_state(params) -> typing.Dict[str, typing.Dict[str, np.ndarray]]:
     return st
 
 
-def optimizer_step(sh: Shapes, params, grads, opt_state, lr: float):
+def _opt_rsqrt(x):
+    """opt_rsqrt, src/optimizer/optimizers.py:13-14: 1 / max(sqrt(x), 1e-5)."""
+    return np.float32(1) / np.maximum(np.sqrt(x), np.float32(1e-5))
+
+
+def _sum_f32(x) -> np.float32:
+    return np.float32(np.sum(x.astype(np.float64)))
+
+
+def _apply_stage(opt: str, args, g, w, st, hyper):
+    """One registered optimizer stage (src/optimizer/optimizers.py:32-151) on one variable.  g: fp32 gradient as
+    the previous stage left it; w: the weight as the graph sees it (activation-dtype cast); st: the variable's
+    slots (created on first use, zeros: src/optimizer/backend.py:23-25); hyper: lr, step_count, beta1, beta2,
+    global_sq (sum of squares of ALL raw gradients, for global_l2norm_clip), keep (slot rounding)."""
+    f32 = np.float32
+    keep = hyper["keep"]
+    b1, b2, t = f32(hyper["beta1"]), f32(hyper["beta2"]), f32(hyper["step_count"])
+
+    def slot(name, shape):
+        if name not in st:
+            st[name] = np.zeros(shape, f32)
+        return st[name]
+
+    def debias_momentum(beta):  # optimizers.py:17-18
+        return f32(1) / (f32(1) - np.power(beta, t))
+
+    def adam():  # optimizers.py:32-43
+        p2 = slot("exp_avg_p2", g.shape) * b2 + (g * g) * (f32(1) - b2)  # weighted_add, utils_mtf.py:332-333
+        p1 = slot("exp_avg_p1", g.shape) * b1 + g * (f32(1) - b1)
+        st["exp_avg_p2"], st["exp_avg_p1"] = keep(p2), keep(p1)
+        return _opt_rsqrt(p2 * debias_momentum(b2)) * p1 * debias_momentum(b1)
+
+    if opt == "adam":
+        return adam()
+    if opt == "novograd":  # optimizers.py:46-57
+        if g.ndim == 0:
+            return adam()
+        p1_old, p2_old = slot("exp_avg_p1", g.shape), slot("exp_avg_p2", ())
+        p1 = b1 * p1_old + g * _opt_rsqrt(p2_old)
+        p2 = p2_old * b2 + _sum_f32(g * g) * (f32(1) - b2)
+        st["exp_avg_p1"], st["exp_avg_p2"] = keep(p1), keep(np.asarray(p2, f32))
+        return b1 * p1 + g * _opt_rsqrt(p2 * debias_momentum(b2))
+    if opt == "sm3":  # optimizers.py:60-76
+        nd = g.ndim
+        if nd == 0:
+            return adam()
+        acc = slot("dim0", g.shape[:1]).reshape([-1] + [1] * (nd - 1))
+        for i in range(1, nd):
+            shape = [1] * nd
+            shape[i] = -1
+            acc = np.minimum(acc, slot(f"dim{i}", (g.shape[i],)).reshape(shape))
+        nu = acc + g * g
+        for i in range(nd):
+            red = tuple(j for j in range(nd) if j != i)
+            st[f"dim{i}"] = keep(nu.max(axis=red) if red else nu)
+        return g * _opt_rsqrt(nu)
+    if opt == "adaptive_clip":  # optimizers.py:79-84
+        clip = f32(float(args[0]))
+        with np.errstate(divide="ignore"):
+            gn = np.minimum(f32(1) / np.sqrt(_sum_f32(g * g)), f32(1e6))
+        wn = np.maximum(np.sqrt(_sum_f32(w * w)), f32(1e-3))
+        return g * np.minimum(wn * gn * clip, f32(1))
+    if opt == "l2norm_clip":  # optimizers.py:87-90
+        clip = f32(float(args[0]))
+        return g * clip * (f32(1) / np.sqrt(np.maximum(_sum_f32(g * g), clip ** f32(-2))))
+    if opt == "global_l2norm_clip":  # optimizers.py:93-98: the sum runs over the RAW gradients of all variables
+        clip = f32(float(args[0]))
+        return g * clip * (f32(1) / np.sqrt(np.maximum(f32(hyper["global_sq"]), clip ** f32(-2))))
+    if opt == "value_clip":  # optimizers.py:101-103
+        clip = f32(float(args[0]))
+        return np.maximum(np.minimum(g, clip), -clip)
+    if opt == "gradient_centralisation":  # optimizers.py:106-107
+        return g - f32(np.mean(g.astype(np.float64)))
+    if opt == "weight_centralisation":  # optimizers.py:110-111
+        return g + f32(np.mean(w.astype(np.float64)))
+    if opt == "learning_rate":  # optimizers.py:114-115
+        return g * f32(hyper["lr"])
+    if opt == "momentum":  # optimizers.py:118-128
+        mult, gmult, nesterov = f32(float(args[0])), f32(float(args[1])), bool(int(args[2]))
+        new_state = mult * slot("momentum", g.shape) + g * gmult
+        st["momentum"] = keep(new_state)
+        return g + mult * new_state if nesterov else new_state
+    if opt == "graft":  # optimizers.py:147-151: direction of g, magnitude of the inner optimizer's step
+        inner = _apply_stage(args[0], list(args[1:]), g, w, st, hyper)
+        with np.errstate(divide="ignore"):
+            return g * (f32(1) / np.sqrt(_sum_f32(g * g))) * np.sqrt(_sum_f32(inner * inner))
+    raise NotImplementedError(f"oracle: optimizer '{opt}'")
+
+
+def optimizer_step(sh: Shapes, params, grads, opt_state, lr: float, step_count: int = 1, optimizer: str = None):
     """In-place update of params (fp32 slices) and opt_state, all arithmetic in fp32
-    (optimizer_calculation_dtype).  `grads` already carry the dtype the graph would hand over."""
+    (optimizer_calculation_dtype).  `grads` already carry the dtype the graph would hand over.
+    update(), src/optimizer/__init__.py:31-66: the stages of the optimizer string in order, the weight-decay rule,
+    assign_sub.  step_count = global_step + 1 (`:96` with grad_accumulation 1); `optimizer` overrides sh.optimizer."""
     f32 = np.float32
     act_bf16 = sh.calculation_dtype == "bfloat16"
     st_bf16 = sh.optimizer_slice_dtype == "bfloat16"
     lr = f32(lr)
-    chain = [o.split(":") for o in sh.optimizer.split("-")]
+    chain = [o.split(":") for o in (optimizer or sh.optimizer).split("-")]
+    hyper = {"lr": lr, "step_count": step_count, "beta1": getattr(sh, "opt_beta1", 0.9),
+             "beta2": getattr(sh, "opt_beta2", 0.99),
+             "global_sq": sum(float(np.sum(g.astype(np.float64) ** 2)) for g in grads.values()),
+             "keep": (lambda v: round_bf16(np.asarray(v, f32))) if st_bf16 else (lambda v: np.asarray(v, f32))}
     for name, p in params.items():
         g = grads[name].astype(f32)
         w = round_bf16(p) if act_bf16 else p  # var.value: the slice cast to the activation dtype
         st = opt_state[name]
         for opt, *args in chain:
-            if opt == "adaptive_clip":  # optimizers.py:79-84
-                clip = f32(float(args[0]))
-                sg = f32(np.sum(g.astype(np.float64) ** 2))
-                sw = f32(np.sum(w.astype(np.float64) ** 2))
-                with np.errstate(divide="ignore"):
-                    gn = np.minimum(f32(1) / np.sqrt(sg), f32(1e6))
-                wn = np.maximum(np.sqrt(sw), f32(1e-3))
-                g = g * np.minimum(wn * gn * clip, f32(1))
-            elif opt == "sm3":  # optimizers.py:60-76
-                nd = p.ndim
-                acc = st["dim0"].reshape([-1] + [1] * (nd - 1))
-                for i in range(1, nd):
-                    shape = [1] * nd
-                    shape[i] = -1
-                    acc = np.minimum(acc, st[f"dim{i}"].reshape(shape))
-                nu = acc + g * g
-                for i in range(nd):
-                    red = tuple(j for j in range(nd) if j != i)
-                    new = nu.max(axis=red) if red else nu
-                    st[f"dim{i}"] = round_bf16(new) if st_bf16 else new.astype(f32)
-                g = g * (f32(1) / np.maximum(np.sqrt(nu), f32(1e-5)))  # opt_rsqrt, optimizers.py:13-14
-            elif opt == "momentum":  # optimizers.py:118-128
-                mult, gmult, nesterov = f32(float(args[0])), f32(float(args[1])), bool(int(args[2]))
-                new_state = mult * st["momentum"] + g * gmult
-                st["momentum"] = round_bf16(new_state) if st_bf16 else new_state.astype(f32)
-                g = g + mult * new_state if nesterov else new_state
-            elif opt == "learning_rate":  # optimizers.py:114-115
-                g = g * lr
-            else:
-                raise NotImplementedError(f"oracle: optimizer '{opt}'")
+            g = _apply_stage(opt, args, g, w, st, hyper)
         if is_large_tensor(name) and sh.weight_decay > 0:  # __init__.py:49-61
             g = g + w * lr * f32(sh.weight_decay)
         params[name] = (p - g).astype(f32)  # assign_sub on the fp32 slice, __init__.py:64
@@ -542,7 +608,7 @@ def train_step(sh: Shapes, params, opt_state, tok_x, tok_y, global_step: int, dt
     if sh.calculation_dtype == "bfloat16":
         grads = {k: round_bf16(v.astype(np.float32)) for k, v in grads.items()}
     lr = learning_rate(sh, global_step)
-    optimizer_step(sh, params, grads, opt_state, lr)
+    optimizer_step(sh, params, grads, opt_state, lr, step_count=global_step + 1)
     return loss, acc, grads, lr
 
 

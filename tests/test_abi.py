@@ -56,20 +56,34 @@ def test_argument_validation_needs_no_gpu(lib):
     assert b"vocab" in lib.obst_last_error()
     assert lib.obst_act_fwd(0, 7, None, None, 8, None) == -1
     assert lib.obst_gn_fwd(1, None, None, None, None, None, 8, 8, 100, 0, None) == -1  # width not a multiple of 8
+    from obst import native
+    a = native.OptStageArgs()
+    assert lib.obst_opt_stage(None, 1, None, None, None, 1, ctypes.byref(a), None) == -1
+    assert b"null argument" in lib.obst_last_error()
+    one = ctypes.c_int32(0)
+    ptr = ctypes.addressof(one)
+    a.stage = 99
+    assert lib.obst_opt_stage(ptr, 1, ptr, ptr, ptr, 1, ctypes.byref(a), None) == -1 and b"bad stage" in lib.obst_last_error()
+    a.stage = native.STAGE_ADAM
+    assert lib.obst_opt_stage(ptr, 1, ptr, ptr, ptr, 1, ctypes.byref(a), None) == -1   # no buffers
+    assert lib.obst_opt_sm3_stage(ptr, 1, ptr, ptr, ptr, 1, 20000, 1, 1, None) == -1
 
 
 def test_struct_layout_matches_the_c_compiler(tmp_path):
     from obst import native
     c = tmp_path / "sz.c"
     c.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "obst_b200.h"\nint main(){'
-                 'printf("%zu %zu %zu %zu %zu %zu\\n", sizeof(obst_operand), sizeof(obst_gemm_desc), '
+                 'printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(obst_operand), sizeof(obst_gemm_desc), '
                  'sizeof(obst_opt_tensor), offsetof(obst_gemm_desc, D), offsetof(obst_opt_tensor, numel), '
-                 'offsetof(obst_opt_tensor, tril_s)); return 0;}')
+                 'offsetof(obst_opt_tensor, tril_s), sizeof(obst_opt_stage_args), '
+                 'offsetof(obst_opt_stage_args, grad_base), offsetof(obst_opt_stage_args, sums2)); return 0;}')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(c), "-o", str(exe)], check=True)
     out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
     got = [ctypes.sizeof(native.Operand), ctypes.sizeof(native.GemmDesc), ctypes.sizeof(native.OptTensor),
-           native.GemmDesc.D.offset, native.OptTensor.numel.offset, native.OptTensor.tril_s.offset]
+           native.GemmDesc.D.offset, native.OptTensor.numel.offset, native.OptTensor.tril_s.offset,
+           ctypes.sizeof(native.OptStageArgs), native.OptStageArgs.grad_base.offset,
+           native.OptStageArgs.sums2.offset]
     assert [int(v) for v in out] == got
 
 

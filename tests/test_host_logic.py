@@ -125,12 +125,22 @@ def test_optimizer_string_lowers_to_the_fused_plan():
     assert (f.clip, f.beta, f.nesterov) == (0.003, 0.9, True)
     f = plan_of("sm3-momentum:0.5:1:0-learning_rate")
     assert (f.clip, f.beta, f.nesterov) == (0.0, 0.5, False)
-    with pytest.raises(NotImplementedError):
-        plan_of("learning_rate")
-    with pytest.raises(NotImplementedError):
-        plan_of("adam-learning_rate")
-    with pytest.raises(NotImplementedError):
-        plan_of("sm3-momentum:0.9:0.5:1-learning_rate")
+    # every other chain of registered stages lowers to the stage-by-stage plan, arguments checked up front
+    from obst.optimizer.optimizers import GenericPlan
+    g = plan_of("learning_rate")
+    assert isinstance(g, GenericPlan) and g.stages == (("learning_rate", ()),)
+    g = plan_of("adam-learning_rate")
+    assert g.stages == (("adam", ()), ("learning_rate", ()))
+    g = plan_of("sm3-momentum:0.9:0.5:1-learning_rate")   # gradient multiplier != 1: not the fused kernel's form
+    assert isinstance(g, GenericPlan) and g.stages[1] == ("momentum", ("0.9", "0.5", "1"))
+    g = plan_of("global_l2norm_clip:1.0-graft:adam-momentum:0.9:1:0-learning_rate")
+    assert g.stages[1] == ("graft", ("adam",))
+    with pytest.raises(TypeError):
+        plan_of("momentum:0.9-learning_rate")
+    with pytest.raises(ValueError):
+        plan_of("graft:nothing")
+    with pytest.raises(KeyError):
+        plan_of("sgd")
 
 
 @pytest.mark.parametrize("step", [0, 1, 100, 2048, 4095, 4096, 100000])

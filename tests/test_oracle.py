@@ -242,6 +242,75 @@ def test_optimizer_step_closed_form_first_step():
             assert np.allclose(st[k][f"dim{i}"], (gs * gs).max(axis=red), rtol=1e-5)
 
 
+def test_every_registered_optimizer_stage_against_closed_forms():
+    """The stages of src/optimizer/optimizers.py:32-151 outside the hot path's chain, each pinned by a property
+    that follows from its defining lines (the reference has no tests for them)."""
+    sh = orc.Shapes(small_cfg(depth=1))
+    rng = np.random.default_rng(3)
+    g = rng.standard_normal((6, 10)).astype(np.float32) * 0.01
+    w = rng.standard_normal((6, 10)).astype(np.float32)
+    keep = lambda v: np.asarray(v, np.float32)  # noqa: E731
+    hyper = {"lr": 0.01, "step_count": 1, "beta1": 0.9, "beta2": 0.99, "global_sq": 4.0, "keep": keep}
+    stage = lambda name, args=(), st=None, h=hyper: orc._apply_stage(name, list(args), g, w, {} if st is None else st, h)  # noqa: E731
+    # value_clip clamps, centralisations shift by a mean
+    out = stage("value_clip", ["0.005"])
+    assert out.max() <= 0.005 and out.min() >= -0.005 and np.array_equal(out[np.abs(g) < 0.005], g[np.abs(g) < 0.005])
+    assert abs(float(stage("gradient_centralisation").mean())) < 1e-9
+    assert np.allclose(stage("weight_centralisation") - g, w.mean(), atol=1e-7)
+    # l2norm_clip: norm becomes clip * |g| / max(|g|, 1/clip) -> exactly `clip` once |g| exceeds 1/clip ... here it
+    # does not, so the result is g * clip^2
+    gn = np.sqrt((g.astype(np.float64) ** 2).sum())
+    assert gn < 1 / 0.5
+    assert np.allclose(stage("l2norm_clip", ["0.5"]), g * 0.25, rtol=1e-6)
+    assert np.allclose(stage("l2norm_clip", ["100"]), g * 100 / gn, rtol=1e-5)          # |g| > 1/clip: norm == clip
+    assert np.allclose(stage("global_l2norm_clip", ["1"]), g / 2.0, rtol=1e-6)      # sqrt(global_sq) = 2 > 1/clip
+    assert np.allclose(stage("global_l2norm_clip", ["0.1"]), g * 0.01, rtol=1e-6)   # below 1/clip: g * clip^2
+    # adam, first step from zero slots: debiasing cancels the (1 - beta) factors -> g / max(|g|, 1e-5) = sign(g)
+    st = {}
+    out = stage("adam", st=st)
+    big = np.abs(g) > 1e-4
+    assert np.allclose(out[big], np.sign(g)[big], rtol=1e-4)
+    assert np.allclose(st["exp_avg_p1"], 0.1 * g, rtol=1e-6) and np.allclose(st["exp_avg_p2"], 0.01 * g * g, rtol=1e-5)
+    # second step with the same gradient: still sign(g) (both moments are multiples of g and g^2)
+    out2 = orc._apply_stage("adam", [], g, w, st, {**hyper, "step_count": 2})
+    assert np.allclose(out2[big], np.sign(g)[big], rtol=1e-4)
+    # novograd, first step: exp_avg_p2 (a scalar) is zero -> p1 = g * 1e5; p2 <- (1 - beta2) sum g^2, debiased = sum g^2
+    st = {}
+    out = stage("novograd", st=st)
+    assert st["exp_avg_p2"].shape == () and np.isclose(st["exp_avg_p2"], 0.01 * gn ** 2, rtol=1e-5)
+    assert np.allclose(st["exp_avg_p1"], g * 1e5, rtol=1e-6)
+    assert np.allclose(out, 0.9 * g * 1e5 + g / gn, rtol=1e-5)
+    # momentum without nesterov returns the new state; with nesterov g + mult * state
+    st = {}
+    out = stage("momentum", ["0.5", "2", "0"], st=st)
+    assert np.allclose(out, 2 * g) and np.allclose(st["momentum"], 2 * g)
+    out = orc._apply_stage("momentum", ["0.5", "2", "1"], g, w, st, hyper)
+    assert np.allclose(st["momentum"], 0.5 * 2 * g + 2 * g) and np.allclose(out, g + 0.5 * (3 * g), rtol=1e-6)
+    # graft: direction of g, norm of the inner step
+    inner = orc._apply_stage("adam", [], g, w, {}, hyper)
+    out = stage("graft", ["adam"])
+    assert np.isclose(np.linalg.norm(out), np.linalg.norm(inner), rtol=1e-5)
+    assert np.allclose(out / np.linalg.norm(out), g / np.linalg.norm(g), atol=1e-6)
+    # sm3 on a vector: one accumulator, nu = acc + g^2
+    st = {"dim0": np.full(6, 0.25, np.float32)}
+    v = g[:, 0]
+    out = orc._apply_stage("sm3", [], v, w[:, 0], st, hyper)
+    assert np.allclose(out, v / np.sqrt(0.25 + v * v), rtol=1e-6) and np.allclose(st["dim0"], 0.25 + v * v)
+    # the default chain through the generic interpreter is the golden step (test_golden_fixture) -- and an unknown
+    # stage is an error
+    import pytest
+    with pytest.raises(NotImplementedError):
+        stage("sgd")
+    # whole-model step with a non-default chain: every tensor moves, slots are created lazily under the reference names
+    p = orc.init_params(sh, 0)
+    grads = {k: rng.standard_normal(v.shape).astype(np.float32) * 1e-3 for k, v in p.items()}
+    st = {k: {} for k in p}
+    p2 = {k: v.copy() for k, v in p.items()}
+    orc.optimizer_step(sh, p2, grads, st, 0.01, step_count=5, optimizer="global_l2norm_clip:1-novograd-learning_rate")
+    for k in p:
+        assert set(st[k]) == {"exp_avg_p1", "exp_avg_p2"} and not np.array_equal(p2[k], p[k]), k
+
+
 def test_lr_zero_leaves_weights_bit_identical_but_moves_state():
     sh = orc.Shapes(small_cfg(depth=1))
     p = orc.init_params(sh, 0)

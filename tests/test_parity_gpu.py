@@ -307,10 +307,8 @@ def test_unsupported_layers_and_optimizers_fail_loudly(cuda):
     with pytest.raises(NotImplementedError, match="rezero"):
         get_train_model(params, None, None, None, x, x, None, None, None, 0)
     cfg = copy.deepcopy(orc.TINY_CONFIG)
-    cfg.update(depth=1, train_batch_size=2, sequence_length=64, optimizer="adam-learning_rate")
+    cfg.update(depth=1, train_batch_size=2, sequence_length=64)
     params = ModelParameter(gpt_mode(cfg))
-    with pytest.raises(NotImplementedError, match="adam"):
-        get_train_model(params, None, None, None, x, x, None, None, None, 0)
     with pytest.raises(NotImplementedError, match="video"):
         get_train_model(params, x, None, None, x, x, None, None, None, 0)
 
@@ -355,3 +353,62 @@ def test_transposed_shadows_follow_the_optimizer(cuda):
         assert torch.equal(v.value_t, v.value.view(v._t_view).transpose(1, 2).contiguous()), n
         moved += int(not torch.equal(v.value_t, before[n]))
     assert moved >= 4
+
+
+GENERIC_CHAINS = [
+    "adam-learning_rate",
+    "novograd-learning_rate",
+    "sm3-momentum:0.9:0.5:1-learning_rate",                      # gradient multiplier != 1: not the fused form
+    "l2norm_clip:0.5-momentum:0.8:1:0-learning_rate",
+    "global_l2norm_clip:0.1-gradient_centralisation-adam-learning_rate",
+    "value_clip:0.001-weight_centralisation-sm3-learning_rate",
+    "adaptive_clip:0.003-graft:adam-momentum:0.9:1:1-learning_rate",
+    "graft:sm3-learning_rate",
+    "learning_rate",
+]
+
+
+@pytest.mark.parametrize("state_dtype,tol", [("float32", 2e-5), ("bfloat16", 2e-2)])
+@pytest.mark.parametrize("chain", GENERIC_CHAINS)
+def test_generic_optimizer_chains_match_the_oracle(cuda, monkeypatch, chain, state_dtype, tol):
+    """every optimizer stage the reference registers (src/optimizer/optimizers.py:131-151), in
+    chains other than the hot path's, through obst_opt_stage / obst_opt_sm3_stage.  Two steps on the tiny model
+    (the second starts from non-zero slots); the oracle's optimizer arithmetic is applied to the PRODUCT's
+    gradients, so this isolates the update.  Updates at `tol` relative, slots at `tol`."""
+    from obst.optimizer import FusedOptimizer
+    from obst.optimizer.backend import slot_name
+    raw = {}
+    real_step = FusedOptimizer.step
+
+    def step_and_keep_the_raw_gradient(self, *a, **kw):  # the stages rewrite the gradient buffer in place
+        raw["flat"] = self.flat_grad.clone()
+        return real_step(self, *a, **kw)
+
+    monkeypatch.setattr(FusedOptimizer, "step", step_and_keep_the_raw_gradient)
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=64, optimizer=chain, optimizer_slice_dtype=state_dtype)
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=7)
+    tok_x, tok_y = orc.synthetic_tokens(sh)
+    params = make_params(cfg, op)
+    params.global_step = 3000
+    ost = {k: {} for k in op}      # slots are created by the stages on first use
+    oparams = {k: v.copy() for k, v in op.items()}
+    for step in range(2):
+        before = {k: v.copy() for k, v in oparams.items()}
+        run_product_step(params, tok_x, tok_y)
+        byname = variables_by_oracle_name(params, sh)
+        state = params.optimizer_state
+        offs = {id(v): o for v, o in zip(state.variables, state.offsets)}
+        gprod = {k: to_np(raw["flat"][offs[id(v)][0]:offs[id(v)][0] + offs[id(v)][1]]).reshape(v.data.shape)
+                 for k, v in byname.items()}
+        orc.optimizer_step(sh, oparams, gprod, ost, orc.learning_rate(sh, 3000 + step), step_count=3001 + step)
+        slots = params.optimizer_state.slots
+        for name, var in byname.items():
+            upd, upd_ref = to_np(var.data) - before[name], oparams[name] - before[name]
+            assert rel(upd, upd_ref) < tol, (chain, step, name, rel(upd, upd_ref))
+            for slot, ref in ost[name].items():
+                got = to_np(slots[slot_name(params, var.name, slot)])
+                assert rel(got, ref) < tol, (chain, step, name, slot)
+            # keep the two sides on the same weights: the comparison is per-step, not accumulated drift
+            oparams[name] = to_np(var.data).astype(np.float32)
