@@ -113,6 +113,9 @@ def _build(params: ModelParameter, txt_src: Tensor, txt_tgt: Tensor):
     src = scoped("input", _input, params, txt_src)
     out = scoped("body", _body, params, src)
     token_out = scoped("output", _output, params, out)
+    if getattr(params, "skip_loss", False):  # sampling (obst.run.inference): the logits themselves are the result
+        params.attention_idx = 0
+        return None, token_out
     token_loss = scoped("loss", _loss, params, token_out, txt_tgt)
     params.attention_idx = 0
     return token_loss, token_out

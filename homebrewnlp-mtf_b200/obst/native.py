@@ -77,6 +77,8 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_opt_update": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32, c_i32,
                                 c_i32, c_void_p, c_void_p, c_float, c_float, c_i32, c_float, c_float, c_void_p]),
     "obst_opt_finalize": (c_int, [c_void_p, c_i32, c_i32, c_void_p]),
+    "obst_sample_step": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32, c_float,
+                                 ctypes.c_uint64, c_void_p]),
     "obst_opt_stage": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, ctypes.POINTER(OptStageArgs),
                                c_void_p]),
     "obst_opt_sm3_stage": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32,
@@ -265,6 +267,21 @@ def cast_param(src, dst, tril_s: int = 0):
     _cuda(src, dst)
     check(load().obst_cast_param(dtype_code(dst.dtype), _p(src), _p(dst), src.numel(), tril_s, stream_ptr()),
           "obst_cast_param")
+
+
+def sample_step(logits, tokens, position: int, temperature: float = 0.0, seed: int = 0, uniform=None):
+    """tokens[b, position] <- Gumbel-argmax of logits[b, position - 1] (obst_sample_step)."""
+    _cuda(logits, tokens)
+    if tokens.dtype != torch.int32 or not tokens.is_contiguous() or not logits.is_contiguous():
+        raise NativeError("sample_step: tokens must be contiguous int32, logits contiguous")
+    vocab = logits.shape[-1]
+    batch = tokens.shape[0]
+    seq = tokens.numel() // max(batch, 1)
+    if logits.numel() != batch * seq * vocab:
+        raise NativeError(f"sample_step: logits {tuple(logits.shape)} do not match tokens {tuple(tokens.shape)}")
+    check(load().obst_sample_step(dtype_code(logits.dtype), _p(logits), _p(tokens), _p(uniform), batch, seq, vocab,
+                                  int(position), float(temperature), int(seed) & (2 ** 64 - 1), stream_ptr()),
+          "obst_sample_step")
 
 
 def transpose_param(src, dst):

@@ -210,6 +210,17 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
 int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dtype_state,
                       void* stream);
 
+/* ---- autoregressive sampling, one step -------------------------------------------------------------
+ * src/run/inference.py:76-95 (language branch of autoregressive_model's loop body), after the forward pass:
+ * tokens[b, position] = argmax_v(logits[b, position-1, v] + log(-log(U)) * (-temperature)),
+ * U ~ Uniform(1e-9, 1) -- the one entry of shift(argmax(...), +1, wrap=False) the loop keeps; position 0
+ * receives the shift's zero.  logits AT [batch, seq, vocab]; tokens int32 [batch, seq], updated in place.
+ * uniform: NULL (counter-based generator keyed by seed / position / row / entry) or fp32 [batch, vocab]
+ * samples to use instead (tests).  temperature 0 = greedy. */
+int obst_sample_step(int dtype, const void* logits, int32_t* tokens, const float* uniform, int32_t batch,
+                     int32_t seq, int32_t vocab, int32_t position, float temperature, uint64_t seed,
+                     void* stream);
+
 /* ---- generic optimizer chains ---------------------------------------------------------------------
  * Every stage the reference registers in OPTIMIZERS (src/optimizer/optimizers.py:131-151), one launch per
  * stage over the same tensor table and work list, for optimizer strings other than the hot path's

@@ -612,6 +612,29 @@ def train_step(sh: Shapes, params, opt_state, tok_x, tok_y, global_step: int, dt
     return loss, acc, grads, lr
 
 
+def sample_tokens(sh: Shapes, params, token_x, initial_pos: int, temperature: float = 0.0,
+                  end_iterations: typing.Optional[int] = None, uniform_fn=None, dtype=np.float64):
+    """autoregressive_model, language branch (src/run/inference.py:76-134): every iteration runs the whole forward
+    pass, adds log(-log(U)) * (-temperature) to the logits, takes the argmax over the vocabulary, shifts it one
+    position to the right (zero fill) and writes the entry at `position` into the token window.
+    uniform_fn(position) -> U of shape [batch, sequence, vocab] (the reference draws tf.random_uniform)."""
+    tok = np.array(token_x, dtype=np.int64).reshape(token_x.shape[0], sh.sequence_length)
+    end = sh.sequence_length if end_iterations is None else end_iterations
+    pos = initial_pos
+    while pos < end:
+        trace = {}
+        forward(sh, params, tok[:, :, None], tok[:, :, None], dtype=dtype, trace=trace)
+        logits = trace["logits"].reshape(tok.shape[0], sh.sequence_length, -1).astype(np.float32)
+        if temperature != 0:
+            u = np.clip(uniform_fn(pos).astype(np.float32), np.float32(1e-9), np.float32(0.99999994))
+            logits = logits + np.log(-np.log(u)) * np.float32(-temperature)
+        out = logits.argmax(-1)
+        shifted = np.concatenate([np.zeros_like(out[:, :1]), out[:, :-1]], 1)  # shift(+1, wrap=False)
+        tok[:, pos] = shifted[:, pos]
+        pos += 1
+    return tok
+
+
 def count_params(sh: Shapes) -> int:
     B, S, H, K, F, I, K2, I0, V, L = sh.dims
     per_depth = H * K * I + I * H * K2 + H * K2 * K + 2 * H * K2 + 6 * H * K

@@ -301,6 +301,43 @@ def test_transpose_param(nat, shape, dtype):
         nat.transpose_param(src, src)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("vocab", [256, 50, 1000])
+def test_sample_step(nat, dtype, vocab):
+    """obst_sample_step against the defining lines (src/run/inference.py:88-95) on random logits: greedy, with
+    supplied uniforms (bit-identical choice), position 0, and the built-in generator's statistics."""
+    B, S = 5, 12
+    logits = randn(B, S, vocab, dtype=dtype, seed=40, scale=2.0)
+    tok0 = torch.randint(0, vocab, (B, S), dtype=torch.int32, device=DEV)
+    lf = logits.float()
+    for pos in (1, 7, S - 1):
+        tok = tok0.clone()
+        nat.sample_step(logits, tok, pos, 0.0)
+        exp = tok0.clone()
+        exp[:, pos] = lf[:, pos - 1].argmax(-1).int()
+        assert torch.equal(tok, exp)
+        u = torch.rand(B, vocab, device=DEV)
+        tok = tok0.clone()
+        nat.sample_step(logits, tok, pos, 1.5, uniform=u)
+        uc = u.clamp(1e-9, 0.99999994)
+        exp[:, pos] = (lf[:, pos - 1] + torch.log(-torch.log(uc)) * -1.5).argmax(-1).int()
+        assert torch.equal(tok, exp)
+    tok = tok0.clone()
+    nat.sample_step(logits, tok, 0, 0.7)
+    assert torch.equal(tok[:, 1:], tok0[:, 1:]) and int(tok[:, 0].abs().max()) == 0
+    # built-in generator: at a huge temperature the choice is uniform over the vocabulary, and seeds differ
+    toks = torch.zeros(4096, 2, dtype=torch.int32, device=DEV)
+    big = torch.zeros(4096, 2, 8, dtype=dtype, device=DEV)
+    nat.sample_step(big, toks, 1, 1e3, seed=1)
+    counts = torch.bincount(toks[:, 1].long(), minlength=8).float()
+    assert float((counts - 512).abs().max()) < 120          # ~5.6 sigma of Binomial(4096, 1/8)
+    toks2 = torch.zeros(4096, 2, dtype=torch.int32, device=DEV)
+    nat.sample_step(big, toks2, 1, 1e3, seed=2)
+    assert not torch.equal(toks, toks2)
+    with pytest.raises(nat.NativeError):
+        nat.sample_step(logits, tok0.clone(), S, 0.0)
+
+
 # ---------------------------------------------------------------------------------------------------
 # edge cases: empty inputs, ragged sizes, the largest mixing map of the reference configs
 # ---------------------------------------------------------------------------------------------------

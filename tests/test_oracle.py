@@ -311,6 +311,32 @@ def test_every_registered_optimizer_stage_against_closed_forms():
         assert set(st[k]) == {"exp_avg_p1", "exp_avg_p2"} and not np.array_equal(p2[k], p[k]), k
 
 
+def test_autoregressive_sampling_semantics():
+    """src/run/inference.py:76-95: greedy at temperature 0, only positions >= initial_pos are rewritten, each with
+    the argmax of the logits one position earlier (shift +1), position 0 with the shift's zero fill."""
+    sh = orc.Shapes(small_cfg(depth=1))
+    p = orc.init_params(sh, 0)
+    rng = np.random.default_rng(5)
+    S = sh.sequence_length
+    tok = rng.integers(0, 256, (2, S))
+    out = orc.sample_tokens(sh, p, tok, initial_pos=S - 3)
+    assert np.array_equal(out[:, :S - 3], tok[:, :S - 3])
+    # replay the last iteration by hand
+    trace = {}
+    prev = out.copy()
+    orc.forward(sh, p, prev[:, :, None], prev[:, :, None], trace=trace)
+    logits = trace["logits"].reshape(2, S, -1)
+    assert np.array_equal(out[:, S - 1], logits[:, S - 2].argmax(-1))  # causal: rewriting S-1 does not change S-2's logits
+    # position 0 gets the zero the shift brings in
+    out0 = orc.sample_tokens(sh, p, tok, initial_pos=0, end_iterations=1)
+    assert np.array_equal(out0[:, 0], [0, 0]) and np.array_equal(out0[:, 1:], tok[:, 1:])
+    # temperature: the same uniforms give the same tokens; different uniforms (eventually) different ones
+    uni = {pos: rng.uniform(0, 1, (2, S, 256)) for pos in range(S - 3, S)}
+    a = orc.sample_tokens(sh, p, tok, S - 3, temperature=5.0, uniform_fn=lambda pos: uni[pos])
+    b = orc.sample_tokens(sh, p, tok, S - 3, temperature=5.0, uniform_fn=lambda pos: uni[pos])
+    assert np.array_equal(a, b) and not np.array_equal(a, out)
+
+
 def test_lr_zero_leaves_weights_bit_identical_but_moves_state():
     sh = orc.Shapes(small_cfg(depth=1))
     p = orc.init_params(sh, 0)

@@ -412,3 +412,30 @@ def test_generic_optimizer_chains_match_the_oracle(cuda, monkeypatch, chain, sta
                 assert rel(got, ref) < tol, (chain, step, name, slot)
             # keep the two sides on the same weights: the comparison is per-step, not accumulated drift
             oparams[name] = to_np(var.data).astype(np.float32)
+
+
+@pytest.mark.parametrize("temperature", [0.0, 0.8])
+def test_autoregressive_sampling_matches_the_oracle(cuda, temperature):
+    """autoregressive_model (src/run/inference.py:76-134) on the tiny fp32 model: 6 positions
+    generated, greedy and with shared uniform samples; the token windows must be identical."""
+    from obst.run.inference import autoregressive_model
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=2, train_batch_size=3, sequence_length=64)
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=9)
+    rng = np.random.default_rng(10)
+    # an untrained model's logits are ~1e-3 apart: spread the LM head so that fp32-vs-fp64 noise cannot flip an argmax
+    op["wo"] = (op["wo"] * 50).astype(np.float32)
+    S, V = sh.sequence_length, 256
+    tok = rng.integers(0, V, (3, S)).astype(np.int32)
+    start = S - 6
+    uni = {pos: rng.uniform(0, 1, (3, S, V)).astype(np.float32) for pos in range(start, S)}
+    ref = orc.sample_tokens(sh, op, tok, start, temperature=temperature, uniform_fn=lambda pos: uni[pos])
+    params = make_params(cfg, op)
+    params.sampling_temperature = temperature
+    got, frames = autoregressive_model(
+        params, token_x_input=torch.from_numpy(tok[:, :, None]).cuda(), initial_pos=start,
+        uniform_fn=lambda pos: torch.from_numpy(np.ascontiguousarray(uni[pos][:, pos - 1])).cuda())
+    assert frames is None
+    assert np.array_equal(got.cpu().numpy().reshape(3, S), ref)
+    assert not np.array_equal(ref[:, start:], tok[:, start:])
