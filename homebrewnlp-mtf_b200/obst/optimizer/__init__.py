@@ -180,8 +180,13 @@ class FusedOptimizer:
         if slot not in bufs:
             buf = torch.zeros_like(self.flat_momentum)
             bufs[slot] = buf
+            entries = getattr(self.params, "restore_entries", None) or {}  # resume (obst.run.checkpoint)
             for v, (off, sz) in zip(self.variables, self.offsets):
-                self.slots[slot_name(self.params, v.name, slot)] = buf[off:off + sz].view(v.data.shape)
+                name = slot_name(self.params, v.name, slot)
+                view = buf[off:off + sz].view(v.data.shape)
+                self.slots[name] = view
+                if name in entries:
+                    view.copy_(entries[name].to(view.device).reshape(view.shape).to(view.dtype))
         return bufs[slot]
 
     def _scratch(self, name: str, numel: int, dtype) -> torch.Tensor:
@@ -252,8 +257,15 @@ class FusedOptimizer:
                         state_a=self._flat_state("exp_avg_p1"), state_b=self._flat_state("exp_avg_p2"))
         elif name == "novograd":
             reduce_into(sums)
-            pair = self.__dict__.setdefault("_novograd_p2", [torch.zeros(nt, dtype=self.state_dtype,
-                                                                         device=work.device) for _ in range(2)])
+            if "_novograd_p2" not in self.__dict__:
+                pair = [torch.zeros(nt, dtype=self.state_dtype, device=work.device) for _ in range(2)]
+                entries = getattr(self.params, "restore_entries", None) or {}
+                for i, v in enumerate(self.variables):
+                    name = slot_name(self.params, v.name, "exp_avg_p2")
+                    if name in entries:
+                        pair[0][i] = entries[name].to(work.device).reshape(()).to(self.state_dtype)
+                self._novograd_p2 = pair
+            pair = self._novograd_p2
             self._stage(N.STAGE_NOVOGRAD, work, f=[b1, b2, 0.0, debias(b2)], state_a=self._flat_state("exp_avg_p1"),
                         scalars=pair, sums=sums)
             pair.reverse()  # [0] is always the current exp_avg_p2
@@ -370,6 +382,9 @@ def _ensure_state(params: ModelParameter) -> FusedOptimizer:
             OPTIMIZERS[opt](ctx, *args)
         state = FusedOptimizer(params, lower_plan(ctx.plan))
         params.optimizer_state = state
+        if getattr(params, "restore_entries", None) is not None:  # resume: slots come from the checkpoint
+            from ..run.checkpoint import restore_slots
+            restore_slots(params, state)
     return state
 
 

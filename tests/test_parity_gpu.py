@@ -404,12 +404,23 @@ def test_generic_optimizer_chains_match_the_oracle(cuda, monkeypatch, chain, sta
                  for k, v in byname.items()}
         orc.optimizer_step(sh, oparams, gprod, ost, orc.learning_rate(sh, 3000 + step), step_count=3001 + step)
         slots = params.optimizer_state.slots
+
+        def agree(got, ref):
+            """rel L2 below tol -- or all but a handful of elements within tol: adam-like stages turn g into
+            ~sign(g), so an element whose (centralised / clipped) gradient is within an ulp of zero may come out
+            with the other sign on the two sides, an O(1) difference in one entry."""
+            got, ref = np.asarray(got, np.float64), np.asarray(ref, np.float64)
+            if rel(got, ref) < tol:
+                return True
+            bad = np.abs(got - ref) > tol * max(float(np.abs(ref).max()), 1e-30)
+            return int(bad.sum()) <= max(2, int(1e-3 * ref.size))
+
         for name, var in byname.items():
             upd, upd_ref = to_np(var.data) - before[name], oparams[name] - before[name]
-            assert rel(upd, upd_ref) < tol, (chain, step, name, rel(upd, upd_ref))
+            assert agree(upd, upd_ref), (chain, step, name, rel(upd, upd_ref))
             for slot, ref in ost[name].items():
                 got = to_np(slots[slot_name(params, var.name, slot)])
-                assert rel(got, ref) < tol, (chain, step, name, slot)
+                assert agree(got, ref), (chain, step, name, slot, rel(got, ref))
             # keep the two sides on the same weights: the comparison is per-step, not accumulated drift
             oparams[name] = to_np(var.data).astype(np.float32)
 
@@ -439,3 +450,69 @@ def test_autoregressive_sampling_matches_the_oracle(cuda, temperature):
     assert frames is None
     assert np.array_equal(got.cpu().numpy().reshape(3, S), ref)
     assert not np.array_equal(ref[:, start:], tok[:, start:])
+
+
+@pytest.mark.parametrize("chain", [None, "adam-learning_rate", "novograd-momentum:0.9:1:0-learning_rate"])
+def test_checkpoint_resume(cuda, tmp_path, chain):
+    """Stop after two steps, save (exact fp32 slices), load into a fresh ModelParameter, take step three: weights
+    and slots equal those of an uninterrupted three-step run.  With the reference's dtypes
+    (storage_dtype) the file holds master-dtype values under the reference's variable / slot names."""
+    from obst.run.checkpoint import load_checkpoint, save_checkpoint
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=64)
+    if chain:
+        cfg["optimizer"] = chain
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=11)
+    tok_x, tok_y = orc.synthetic_tokens(sh)
+
+    def fresh():
+        p = make_params(cfg, op)
+        p.global_step = 1500
+        return p
+
+    straight = fresh()
+    for _ in range(3):
+        run_product_step(straight, tok_x, tok_y)
+    stopped = fresh()
+    for _ in range(2):
+        run_product_step(stopped, tok_x, tok_y)
+    path = str(tmp_path / "ckpt.npz")
+    save_checkpoint(stopped, path, exact=True)
+    resumed = make_params(cfg, {k: np.zeros_like(v) for k, v in op.items()})  # weights must come from the file
+    resumed.import_variables = None
+    load_checkpoint(resumed, path)
+    assert resumed.global_step == 1502 and resumed.manual_global_step == 2
+    run_product_step(resumed, tok_x, tok_y)
+    assert resumed.global_step == straight.global_step
+    # two runs of the same step differ in the last bits (fp32 atomics in the weight-gradient / embedding-gradient
+    # accumulation are unordered), so the third step is compared at 1e-6 ...
+    # (novograd's first step from a zero second moment multiplies the gradient by 1e5 -- src/optimizer/
+    # optimizers.py:13-14,52 -- so that run is chaotic and only has to agree to 1e-3; a slot that was NOT restored
+    # shows up as an O(1) difference)
+    wtol = 1e-3 if chain and "novograd" in chain else 1e-6
+    for (na, a), (nb, b) in zip(straight.variable_cache.items(), resumed.variable_cache.items()):
+        assert na == nb and rel(to_np(b.data), to_np(a.data)) < wtol, na
+    sa, sb = straight.optimizer_state.slots, resumed.optimizer_state.slots
+    assert sa.keys() == sb.keys()
+    for k in sa:
+        assert rel(to_np(sb[k]), to_np(sa[k])) < 10 * wtol, k
+    # ... and the restore itself bit for bit: loading into an already-built model overwrites everything in place
+    probe = fresh()
+    run_product_step(probe, tok_x, tok_y)
+    load_checkpoint(probe, path)
+    assert probe.global_step == 1502
+    for (na, a), (nb, b) in zip(stopped.variable_cache.items(), probe.variable_cache.items()):
+        assert na == nb and torch.equal(a.data, b.data) and torch.equal(a.value, b.value), na
+        if a.value_t is not None:
+            assert torch.equal(a.value_t, b.value_t), na
+    for k, v in stopped.optimizer_state.slots.items():
+        assert torch.equal(v, probe.optimizer_state.slots[k]), k
+    # the reference-dtype file: names are the reference's, weights in storage_dtype
+    save_checkpoint(stopped, str(tmp_path / "ref.npz"))
+    with np.load(str(tmp_path / "ref.npz")) as f:
+        names = set(f.files)
+    assert "global_step" in names
+    assert any(n.startswith("gpt0v/body0v/0_0v/") and "get_variable" in n for n in names), sorted(names)[:5]
+    opt = stopped.optimizer.replace(":", "_")
+    assert any(f"/{opt}/" in n for n in names)
