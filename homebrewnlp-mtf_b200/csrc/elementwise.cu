@@ -686,9 +686,10 @@ int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, con
 }
 
 int obst_act_fwd(int dtype, int32_t kind, const void* x, void* y, int64_t n, void* stream) {
-  OBST_REQUIRE(kind == 0 || kind == 1, "obst_act_fwd: bad kind %d", kind);
+  OBST_REQUIRE(kind >= 0 && kind <= OBST_ACT_EXP, "obst_act_fwd: bad kind %d", kind);
   if (n <= 0) return OBST_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (kind >= 2) return act_any_launch(dtype, kind, false, x, nullptr, y, n, st);
   if (dtype == OBST_BF16) {
     const unsigned b = ew_blocks(n / 8 + 1);
     if (kind == 0) act_kernel<bf16, 0, false><<<b, 256, 0, st>>>((const bf16*)x, nullptr, (bf16*)y, n);
@@ -705,9 +706,10 @@ int obst_act_fwd(int dtype, int32_t kind, const void* x, void* y, int64_t n, voi
 }
 
 int obst_act_bwd(int dtype, int32_t kind, const void* x, const void* dy, void* dx, int64_t n, void* stream) {
-  OBST_REQUIRE(kind == 0 || kind == 1, "obst_act_bwd: bad kind %d", kind);
+  OBST_REQUIRE(kind >= 0 && kind <= OBST_ACT_EXP, "obst_act_bwd: bad kind %d", kind);
   if (n <= 0) return OBST_OK;
   cudaStream_t st = (cudaStream_t)stream;
+  if (kind >= 2) return act_any_launch(dtype, kind, true, x, dy, dx, n, st);
   if (dtype == OBST_BF16) {
     const unsigned b = ew_blocks(n / 8 + 1);
     if (kind == 0) act_kernel<bf16, 0, true><<<b, 256, 0, st>>>((const bf16*)x, (const bf16*)dy, (bf16*)dx, n);

@@ -166,6 +166,9 @@ __device__ __forceinline__ float gelu_obst_grad(float x) {
   return s * fmaf(x * (1.0f - s), fmaf(x * x, 0.26829f, 1.5957691216057308f), 1.0f);
 }
 
+// pointwise.cu: activations other than relu / gelu (obst_act_fwd / obst_act_bwd route kinds >= 2 here)
+int act_any_launch(int dtype, int kind, bool bwd, const void* x, const void* dy, void* out, int64_t n, cudaStream_t st);
+
 static inline int num_sms() {
   static int sms = 0;
   if (sms == 0) {

@@ -1,6 +1,7 @@
 """Activations (src/model/activation.py:158-211): `activate` picks the first extra that names a known function and
-falls back to identity with the reference's message.  relu and the reference's non-standard gelu have kernels;
-the other registered names raise NotImplementedError (SURVEY.md 8(f) "next")."""
+falls back to identity with the reference's message.  relu and the reference's non-standard gelu are the hot
+path's (act_kernel, or fused into a GEMM epilogue / the norm kernel); the other registered names run through the
+generic pointwise kernel, with the reference's own (non-analytic) backward for silu and mish."""
 import torch
 
 from .. import native
@@ -27,26 +28,14 @@ def _pointwise(kind: int):
     return fn
 
 
-def _unsupported(name: str):
-    def fn(args: BlockArgs) -> Tensor:
-        raise NotImplementedError(f"activation '{name}' is registered by the reference but has no B200 kernel yet")
-
-    return fn
-
-
 relu = _pointwise(0)
 gelu = _pointwise(1)
 
-ACTIVATIONS = {'relu': relu,
-               'gelu': gelu,
-               'sigmoid': _unsupported('sigmoid'),
-               'tanh': _unsupported('tanh'),
-               'lecun_tanh': _unsupported('lecun_tanh'),
-               'silu': _unsupported('silu'),
-               'mish': _unsupported('mish'),
-               'mtf_mish': _unsupported('mtf_mish'),
-               'softsign': _unsupported('softsign'),
-               'exp': _unsupported('exp')}
+# name -> OBST_ACT_* kind of include/obst_b200.h (src/model/activation.py:190-200)
+ACTIVATION_KINDS = {'relu': 0, 'gelu': 1, 'sigmoid': 2, 'tanh': 3, 'lecun_tanh': 4, 'silu': 5, 'mish': 6,
+                    'mtf_mish': 7, 'softsign': 8, 'exp': 9}
+ACTIVATIONS = {name: _pointwise(kind) for name, kind in ACTIVATION_KINDS.items()}
+ACTIVATIONS['relu'], ACTIVATIONS['gelu'] = relu, gelu
 
 
 _WARNED = set()

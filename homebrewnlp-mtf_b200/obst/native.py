@@ -65,6 +65,8 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
                             c_i64, c_i32, c_i32, c_i32, c_i32, c_i32, c_void_p]),
     "obst_act_fwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_act_bwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
+    "obst_gate_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
+    "obst_gate_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_axpby": (c_int, [c_int, c_void_p, c_void_p, c_float, c_void_p, c_i64, c_void_p]),
     "obst_embed_gather": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
     "obst_embed_scatter_add": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
@@ -234,6 +236,17 @@ def act_bwd(kind: int, x, dy, dx):
     _cuda(x, dy, dx)
     check(load().obst_act_bwd(dtype_code(x.dtype), kind, _p(x), _p(dy), _p(dx), x.numel(), stream_ptr()),
           "obst_act_bwd")
+
+
+def gate_fwd(a, b, out):
+    _cuda(a, b, out)
+    check(load().obst_gate_fwd(dtype_code(a.dtype), _p(a), _p(b), _p(out), a.numel(), stream_ptr()), "obst_gate_fwd")
+
+
+def gate_bwd(a, b, dy, da, db):
+    _cuda(a, b, dy, da, db)
+    check(load().obst_gate_bwd(dtype_code(a.dtype), _p(a), _p(b), _p(dy), _p(da), _p(db), a.numel(), stream_ptr()),
+          "obst_gate_bwd")
 
 
 def axpby(a, b, sign: float, out):

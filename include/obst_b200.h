@@ -112,10 +112,22 @@ int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, con
                 void* stream);
 
 /* ---- activations, src/model/activation.py:158-169,201-211 ---------------------------------------
- * kind: 0 relu | 1 OBST gelu 0.5x(1+tanh(0.044715x^3+sqrt(2/pi)x)). */
+ * kind: 0 relu | 1 OBST gelu 0.5x(1+tanh(0.044715x^3+sqrt(2/pi)x)) | 2.. the other entries of ACTIVATIONS
+ * (activation.py:13-155,168-200).  silu and mish use the reference's own backward operations, which are not
+ * the analytic derivatives: silu' := (x-1)*sigmoid(x)+1, mish' := t + 1 - t^2*x*sigmoid(x), t = tanh(softplus x);
+ * mtf_mish is differentiated analytically (MTF autodiff). */
+enum {
+  OBST_ACT_RELU = 0, OBST_ACT_GELU, OBST_ACT_SIGMOID, OBST_ACT_TANH, OBST_ACT_LECUN_TANH, OBST_ACT_SILU,
+  OBST_ACT_MISH, OBST_ACT_MTF_MISH, OBST_ACT_SOFTSIGN, OBST_ACT_EXP
+};
 int obst_act_fwd(int dtype, int32_t kind, const void* x, void* y, int64_t n, void* stream);
 int obst_act_bwd(int dtype, int32_t kind, const void* x, const void* dy, void* dx, int64_t n,
                  void* stream);
+/* GLU gate of activated_linear (src/model/basic.py:51-54): out = a * sigmoid(b);
+ * backward: da = dy * sigmoid(b), db = dy * a * sigmoid(b) * (1 - sigmoid(b)). */
+int obst_gate_fwd(int dtype, const void* a, const void* b, void* out, int64_t n, void* stream);
+int obst_gate_bwd(int dtype, const void* a, const void* b, const void* dy, void* da, void* db,
+                  int64_t n, void* stream);
 
 /* ---- residual stream arithmetic, src/model/revnet.py:23,89,120; src/model/__init__.py:129 ------
  * out = a + sign*b (sign = +1 or -1), all AT, n elements; out may alias a or b. */

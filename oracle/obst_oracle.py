@@ -612,6 +612,87 @@ def train_step(sh: Shapes, params, opt_state, tok_x, tok_y, global_step: int, dt
     return loss, acc, grads, lr
 
 
+# ----------------------------------------------------------------------------------------------------------
+# the other registered activations and the feed_forward layer
+# ----------------------------------------------------------------------------------------------------------
+def _sigmoid(x):
+    return 1.0 / (1.0 + np.exp(-x))
+
+
+def _softplus(x):
+    return np.where(x > 20, x, np.log1p(np.exp(np.minimum(x, 20))))
+
+
+# forward, and the backward THE REFERENCE uses: its custom operations for lecun_tanh / silu / mish / softsign
+# (src/model/activation.py:13-155) -- silu's and mish's are not the analytic derivatives -- and autodiff for the rest
+ACT_FWD = {
+    "relu": lambda x: np.maximum(x, 0), "gelu": gelu_fwd,
+    "sigmoid": _sigmoid, "tanh": np.tanh, "lecun_tanh": lambda x: np.tanh(x) + x * 0.1,
+    "silu": lambda x: x * _sigmoid(x), "mish": lambda x: x * np.tanh(_softplus(x)),
+    "mtf_mish": lambda x: x * np.tanh(_softplus(x)), "softsign": lambda x: x / (1 + np.abs(x)), "exp": np.exp,
+}
+
+
+def _mish_ref_bwd(x):
+    gte = np.tanh(_softplus(x))
+    return gte + 1.0 - gte * gte * x * _sigmoid(x)     # activation.py:41-44
+
+
+ACT_BWD = {  # d/dx as the reference computes it, to be multiplied by dy
+    "relu": lambda x: (x > 0).astype(x.dtype), "gelu": gelu_grad,
+    "sigmoid": lambda x: _sigmoid(x) * (1 - _sigmoid(x)), "tanh": lambda x: 1 - np.tanh(x) ** 2,
+    "lecun_tanh": lambda x: 1.1 - np.tanh(x) ** 2,            # activation.py:112-113
+    "silu": lambda x: (x - 1) * _sigmoid(x) + 1,              # activation.py:77-79
+    "mish": _mish_ref_bwd,
+    "mtf_mish": lambda x: np.tanh(_softplus(x)) + x * (1 - np.tanh(_softplus(x)) ** 2) * _sigmoid(x),
+    "softsign": lambda x: 1 / (1 + np.abs(x)) ** 2,           # activation.py:147-148
+    "exp": np.exp,
+}
+
+
+def activated_linear_fwd(x, ws, act=None, glu=None):
+    """activated_linear without norm (src/model/basic.py:47-55): x [T, K]; ws = [W1 (, W2 (, W3))], each [K, N];
+    glu in (None, 'glu', 'glu_add').  Returns (out, cache)."""
+    f = ACT_FWD[act] if act else (lambda v: v)
+    z1 = x @ ws[0]
+    out = f(z1)
+    cache = {"x": x, "z1": z1}
+    if glu:
+        z2 = x @ ws[1]
+        cache.update(z2=z2, a=out)
+        out = out * _sigmoid(z2)
+    if glu == "glu_add":
+        z3 = x @ ws[2]
+        cache["z3"] = z3
+        out = out + f(z3)
+    return out, cache
+
+
+def activated_linear_bwd(dy, ws, cache, act=None, glu=None):
+    """Returns (dx, [dW...]) with the reference's activation backward formulas."""
+    d = ACT_BWD[act] if act else (lambda v: np.ones_like(v))
+    x = cache["x"]
+    grads = []
+    dx = 0
+    if glu:
+        s = _sigmoid(cache["z2"])
+        dz2 = dy * cache["a"] * s * (1 - s)
+        da = dy * s
+    else:
+        da = dy
+    dz1 = da * d(cache["z1"])
+    grads.append(x.T @ dz1)
+    dx = dx + dz1 @ ws[0].T
+    if glu:
+        grads.append(x.T @ dz2)
+        dx = dx + dz2 @ ws[1].T
+    if glu == "glu_add":
+        dz3 = dy * d(cache["z3"])
+        grads.append(x.T @ dz3)
+        dx = dx + dz3 @ ws[2].T
+    return dx, grads
+
+
 def sample_tokens(sh: Shapes, params, token_x, initial_pos: int, temperature: float = 0.0,
                   end_iterations: typing.Optional[int] = None, uniform_fn=None, dtype=np.float64):
     """autoregressive_model, language branch (src/run/inference.py:76-134): every iteration runs the whole forward

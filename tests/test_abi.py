@@ -54,7 +54,7 @@ def test_argument_validation_needs_no_gpu(lib):
     assert lib.obst_gemm(ctypes.byref(d), 0, None) == -1
     assert lib.obst_xent_fwd_bwd(0, None, None, None, None, 4, 4096, 1.0, 0.0, None) == -1
     assert b"vocab" in lib.obst_last_error()
-    assert lib.obst_act_fwd(0, 7, None, None, 8, None) == -1
+    assert lib.obst_act_fwd(0, 77, None, None, 8, None) == -1
     assert lib.obst_gn_fwd(1, None, None, None, None, None, 8, 8, 100, 0, None) == -1  # width not a multiple of 8
     from obst import native
     a = native.OptStageArgs()

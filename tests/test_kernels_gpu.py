@@ -232,6 +232,36 @@ def test_activations(nat, dtype, tol, kind):
     assert rel_err(dx, xr.grad) < tol
 
 
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
+@pytest.mark.parametrize("name", ["sigmoid", "tanh", "lecun_tanh", "silu", "mish", "mtf_mish", "softsign", "exp"])
+def test_other_registered_activations(nat, name, dtype, tol):
+    """Every other entry of ACTIVATIONS (src/model/activation.py:190-200) against the oracle, including the
+    reference's own non-analytic backward of silu and mish."""
+    from oracle import obst_oracle as orc
+    from obst.model.activation import ACTIVATION_KINDS
+    kind = ACTIVATION_KINDS[name]
+    x = randn(4099, dtype=dtype, seed=50, scale=2.0)
+    dy = randn(4099, dtype=dtype, seed=51)
+    y, dx = torch.empty_like(x), torch.empty_like(x)
+    nat.act_fwd(kind, x, y)
+    nat.act_bwd(kind, x, dy, dx)
+    xn, gn = x.double().cpu().numpy(), dy.double().cpu().numpy()
+    assert rel_err(y, torch.from_numpy(orc.ACT_FWD[name](xn)).to(DEV)) < tol
+    assert rel_err(dx, torch.from_numpy(orc.ACT_BWD[name](xn) * gn).to(DEV)) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 2e-2)])
+def test_glu_gate(nat, dtype, tol):
+    a, b, dy = (randn(3001, dtype=dtype, seed=s) for s in (52, 53, 54))
+    out, da, db = torch.empty_like(a), torch.empty_like(a), torch.empty_like(a)
+    nat.gate_fwd(a, b, out)
+    nat.gate_bwd(a, b, dy, da, db)
+    ad, bd = a.double().requires_grad_(True), b.double().requires_grad_(True)
+    ref = ad * torch.sigmoid(bd)
+    ref.backward(dy.double())
+    assert rel_err(out, ref.detach()) < tol and rel_err(da, ad.grad) < tol and rel_err(db, bd.grad) < tol
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_axpby(nat, dtype):
     a = randn(4099, dtype=dtype, seed=27)

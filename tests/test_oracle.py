@@ -311,6 +311,49 @@ def test_every_registered_optimizer_stage_against_closed_forms():
         assert set(st[k]) == {"exp_avg_p1", "exp_avg_p2"} and not np.array_equal(p2[k], p[k]), k
 
 
+def test_registered_activations_and_glu():
+    """Analytic derivatives (autodiff in the reference) against torch autograd; the reference's hand-written
+    backward operations for silu / mish pinned by their own formulas (they are NOT the analytic derivatives);
+    activated_linear with glu / glu_add against autograd for an analytic activation."""
+    import torch
+    x = np.linspace(-6, 6, 241)
+    xt = torch.tensor(x, dtype=torch.float64, requires_grad=True)
+    tf = {"sigmoid": torch.sigmoid, "tanh": torch.tanh, "lecun_tanh": lambda v: torch.tanh(v) + 0.1 * v,
+          "mtf_mish": lambda v: v * torch.tanh(torch.nn.functional.softplus(v)),
+          "softsign": torch.nn.functional.softsign, "exp": torch.exp, "relu": torch.relu}
+    for name, fn in tf.items():
+        y = fn(xt)
+        (g,) = torch.autograd.grad(y.sum(), xt)
+        assert np.allclose(orc.ACT_FWD[name](x), y.detach().numpy(), atol=1e-12), name
+        mask = np.abs(x) > 1e-9 if name == "relu" else slice(None)
+        assert np.allclose(orc.ACT_BWD[name](x)[mask], g.numpy()[mask], atol=1e-10), name
+    s = 1 / (1 + np.exp(-x))
+    assert np.allclose(orc.ACT_FWD["silu"](x), x * s) and np.allclose(orc.ACT_BWD["silu"](x), (x - 1) * s + 1)
+    assert not np.allclose(orc.ACT_BWD["silu"](x), s * (1 + x * (1 - s)))          # the analytic one differs
+    t = np.tanh(np.log1p(np.exp(x)))
+    assert np.allclose(orc.ACT_FWD["mish"](x), x * t) and np.allclose(orc.ACT_BWD["mish"](x), t + 1 - t * t * x * s)
+    assert set(orc.ACT_FWD) == {"relu", "gelu", "sigmoid", "tanh", "lecun_tanh", "silu", "mish", "mtf_mish",
+                                "softsign", "exp"}                                 # activation.py:190-200
+    rng = np.random.default_rng(8)
+    xs, dy = rng.standard_normal((7, 5)), rng.standard_normal((7, 4))
+    ws = [rng.standard_normal((5, 4)) * 0.5 for _ in range(3)]
+    for glu in (None, "glu", "glu_add"):
+        out, cache = orc.activated_linear_fwd(xs, ws, "tanh", glu)
+        dx, gw = orc.activated_linear_bwd(dy, ws, cache, "tanh", glu)
+        xt = torch.tensor(xs, requires_grad=True)
+        wt = [torch.tensor(w, requires_grad=True) for w in ws]
+        o = torch.tanh(xt @ wt[0])
+        if glu:
+            o = o * torch.sigmoid(xt @ wt[1])
+        if glu == "glu_add":
+            o = o + torch.tanh(xt @ wt[2])
+        assert np.allclose(out, o.detach().numpy(), atol=1e-12)
+        o.backward(torch.tensor(dy))
+        assert np.allclose(dx, xt.grad.numpy(), atol=1e-10)
+        for g_or, w in zip(gw, wt):
+            assert np.allclose(g_or, w.grad.numpy(), atol=1e-10)
+
+
 def test_autoregressive_sampling_semantics():
     """src/run/inference.py:76-95: greedy at temperature 0, only positions >= initial_pos are rewritten, each with
     the argmax of the logits one position earlier (shift +1), position 0 with the shift's zero fill."""
