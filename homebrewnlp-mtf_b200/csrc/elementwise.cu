@@ -664,7 +664,14 @@ int obst_gn_fwd(int dtype, const void* x, const void* gamma, const void* beta, v
   if (rows == 0) return OBST_OK;
   cudaStream_t st = (cudaStream_t)stream;
   float2* s2 = reinterpret_cast<float2*>(stats);
-  if (dtype == OBST_BF16) return gn_fwd_launch<bf16>(x, gamma, beta, y, s2, rows, heads, width, act, st);
+  if (dtype == OBST_BF16) {
+    static const bool ring_off = getenv("OBST_GN_FWD_RING") && atoi(getenv("OBST_GN_FWD_RING")) == 0;
+    if (!ring_off) {
+      const int rc = gn_fwd_ring_launch(x, gamma, beta, y, s2, rows, heads, width, act, st);
+      if (rc != 1) return rc;
+    }
+    return gn_fwd_launch<bf16>(x, gamma, beta, y, s2, rows, heads, width, act, st);
+  }
   if (dtype == OBST_F32) return gn_fwd_launch<float>(x, gamma, beta, y, s2, rows, heads, width, act, st);
   OBST_REQUIRE(false, "obst_gn_fwd: bad dtype %d", dtype);
 }

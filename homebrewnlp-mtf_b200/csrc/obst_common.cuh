@@ -169,6 +169,10 @@ __device__ __forceinline__ float gelu_obst_grad(float x) {
 // pointwise.cu: activations other than relu / gelu (obst_act_fwd / obst_act_bwd route kinds >= 2 here)
 int act_any_launch(int dtype, int kind, bool bwd, const void* x, const void* dy, void* out, int64_t n, cudaStream_t st);
 
+// gn_fwd_ring.cu: bf16 rows of 512 / 1024 elements; returns 1 when the shape is not covered
+int gn_fwd_ring_launch(const void* x, const void* gamma, const void* beta, void* y, float2* stats, int64_t rows,
+                       int heads, int width, int act, cudaStream_t st);
+
 static inline int num_sms() {
   static int sms = 0;
   if (sms == 0) {
