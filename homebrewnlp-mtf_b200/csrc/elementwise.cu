@@ -683,9 +683,16 @@ int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, con
   if (rows == 0) return OBST_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const float2* s2 = reinterpret_cast<const float2*>(stats);
-  if (dtype == OBST_BF16)
+  if (dtype == OBST_BF16) {
+    static const bool ring_off = getenv("OBST_GN_BWD_RING") && atoi(getenv("OBST_GN_BWD_RING")) == 0;
+    if (!ring_off) {
+      const int rc = gn_bwd_ring_launch(dy, x, gamma, beta, dx, dgamma, dbeta, s2, rows, heads, width, act, relu_mask,
+                                        dx_accumulate, st);
+      if (rc != 1) return rc;
+    }
     return gn_bwd_launch<bf16>(dy, x, gamma, beta, dx, dgamma, dbeta, s2, rows, heads, width, act, relu_mask,
                                dx_accumulate, st);
+  }
   if (dtype == OBST_F32)
     return gn_bwd_launch<float>(dy, x, gamma, beta, dx, dgamma, dbeta, s2, rows, heads, width, act, relu_mask,
                                 dx_accumulate, st);

@@ -173,6 +173,11 @@ int act_any_launch(int dtype, int kind, bool bwd, const void* x, const void* dy,
 int gn_fwd_ring_launch(const void* x, const void* gamma, const void* beta, void* y, float2* stats, int64_t rows,
                        int heads, int width, int act, cudaStream_t st);
 
+// gn_bwd_ring.cu: bf16 rows of 512 elements with saved statistics; returns 1 when the case is not covered
+int gn_bwd_ring_launch(const void* dy, const void* x, const void* gamma, const void* beta, void* dx, float* dgamma,
+                       float* dbeta, const float2* stats, int64_t rows, int heads, int width, int act, int relu_mask,
+                       int dx_acc, cudaStream_t st);
+
 static inline int num_sms() {
   static int sms = 0;
   if (sms == 0) {
