@@ -32,7 +32,10 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="32big_mixer", choices=["32big_mixer", "32ctx_mixer", "32mixer_group", "tiny"])
+    ap.add_argument("--workload", default="32big_mixer",
+                    choices=["32big_mixer", "32ctx_mixer", "32mixer_group", "tiny", "optimizer"],
+                    help="'optimizer' = BASELINE.json configs[4]: the fused optimizer update alone over the 32big_mixer "
+                         "parameter set (HBM roofline)")
     ap.add_argument("--micro-batch", type=int, default=0, help="rows per micro-batch (0 = auto)")
     ap.add_argument("--depth", type=int, default=0, help="override depth (debug only: makes the number INVALID)")
     ap.add_argument("--cpu-rows", type=int, default=1, help="sequences per step of the CPU baseline sample")
@@ -92,6 +95,24 @@ class ClockSampler(threading.Thread):
 # ------------------------------------------------------------------------------------------------------------
 # CPU baseline / reference arm: the oracle (a port: the reference needs TF 2.7 + mesh-tensorflow, not installable)
 # ------------------------------------------------------------------------------------------------------------
+def pin_host_threads() -> int:
+    """Use every host core for the CPU arm, and say how many.  torch.distributed.run exports OMP_NUM_THREADS=1 to its
+    workers, which silently halves-or-worse a NumPy/BLAS baseline launched under it (the round-1 records showed the
+    CPU arm dropping from 56 to 26 tokens/s at N >= 2); the limit is therefore set explicitly, before and after the
+    BLAS library is loaded."""
+    cores = os.cpu_count() or 1
+    for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[var] = str(cores)
+    try:
+        import threadpoolctl
+        import numpy  # noqa: F401  (loads the BLAS the limit applies to)
+        threadpoolctl.threadpool_limits(limits=cores)
+        used = max([cores] + [int(p.get("num_threads", 0)) for p in threadpoolctl.threadpool_info()])
+    except Exception:
+        used = cores
+    return min(used, cores) if used else cores
+
+
 def cpu_step_rate(workload: str, rows: int, steps: int, warmup: int, depth: int = 0):
     """The CPU restatement (oracle/, kind "port") on the host cores, bounded: forward + reversible backward are
     timed on `rows` sequences at FULL depth (per-token work), the optimizer update once over the FULL parameter
@@ -106,7 +127,7 @@ def cpu_step_rate(workload: str, rows: int, steps: int, warmup: int, depth: int 
     full_tokens = cfg["train_batch_size"] * cfg["sequence_length"]
     cfg["train_batch_size"] = rows
     sh = orc.Shapes(cfg)
-    cores = os.cpu_count() or 1
+    cores = pin_host_threads()
     params = orc.init_params_fast(sh, seed=0)
     state = orc.init_opt_state(params)
     tx, ty = orc.synthetic_tokens(sh)
@@ -136,6 +157,9 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    pin_host_threads()
+    if args.workload == "optimizer":
+        return run_reference_optimizer(args)
     value, cores, sample, sec = cpu_step_rate(args.workload, args.cpu_rows, args.steps, args.warmup, args.depth)
     line = {"impl": "reference", "metric": METRIC.replace("32big_mixer", args.workload), "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
@@ -150,10 +174,180 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+OPT_METRIC = "fused optimizer update, 32big_mixer parameter set: algorithmic GB/s (14 B/param)"
+
+
+def cpu_optimizer_rate(steps: int, warmup: int):
+    """The oracle's optimizer update over the full 32big_mixer parameter set on the host cores: GB/s on the same
+    14 B/param algorithmic basis (it is NumPy fp32, op by op: the reference's own formulation of the update)."""
+    import numpy as np
+    from oracle import obst_oracle as orc
+    from obst.configs import mixer_config
+    sh = orc.Shapes(mixer_config("32big_mixer"))
+    cores = pin_host_threads()
+    params = orc.init_params_fast(sh, seed=0)
+    state = orc.init_opt_state(params)
+    rng = np.random.default_rng(0)
+    grads = {k: orc.round_bf16((rng.standard_normal(v.shape) * 1e-3).astype(np.float32)) for k, v in params.items()}
+    n = sum(v.size for v in params.values())
+    times = []
+    for _ in range(warmup + steps):
+        t0 = time.perf_counter()
+        orc.optimizer_step(sh, params, grads, state, 0.005)
+        times.append(time.perf_counter() - t0)
+    sec = sum(times[warmup:]) / max(1, len(times[warmup:]))
+    return 14.0 * n / sec / 1e9, cores, sec, n
+
+
+def run_reference_optimizer(args):
+    steps, warmup = min(args.steps, 3), min(args.warmup, 1)
+    value, cores, sec, n = cpu_optimizer_rate(steps, warmup)
+    sample = (f"oracle optimizer_step (NumPy fp32, op by op) over all {n} parameters of 32big_mixer, mean of {steps} "
+              f"after {warmup} warm-up: {sec:.2f} s per update on {cores} host cores")
+    line = {"impl": "reference", "metric": OPT_METRIC, "value": value, "unit": "GB/s", "n_gpus": args.gpus,
+            "steps": steps, "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "optimizer update over the 32big_mixer parameter set (357 tensors)"},
+            "cpu_baseline": {"value": value, "unit": "GB/s", "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_b200_optimizer(args):
+    """BASELINE.json configs[4]: the fused update alone.  Gradients (bf16, ~N(0, 1e-3): SURVEY 8(d)) are resident in
+    the hand-over buffer; one step = what FusedOptimizer.step() runs in a training step after the hand-over: norms
+    (sum g^2 over the bf16 gradients, weight norms carried over), update, accumulator finalize, transposed-shadow
+    refresh.  L2 is flushed between timed iterations (the state is 4.8 GB, but the tail of one update would
+    otherwise serve the head of the next)."""
+    import torch
+    from obst import native
+    from obst.configs import mixer_config
+    from obst.dataclass import ModelParameter
+    from obst.optimizer import _ensure_state
+    from obst.run.train import get_train_model
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and int(os.environ.get("RANK", "0")) != 0:
+        return  # the update is replicated, not sharded: one rank measures it (DESIGN.md: "replicas only")
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+    native.load()
+    import contextlib
+    import io
+    cfg = mixer_config("32big_mixer", train_batch_size=1)
+    cfg["device"] = f"cuda:{torch.cuda.current_device()}"
+    with contextlib.redirect_stdout(io.StringIO()):
+        params = ModelParameter(cfg)
+    S = cfg["sequence_length"]
+    tok = torch.randint(0, 256, (1, S + 1), dtype=torch.int32, device="cuda")
+    # one real step on a single sequence creates every variable, shadow and the optimizer state
+    get_train_model(params, None, None, None, tok[:, :-1, None].contiguous(), tok[:, 1:, None].contiguous(), None,
+                    None, None, 0)
+    st = _ensure_state(params)
+    n = st.n_params
+    assert st.grad_lp, "the 32big_mixer dtypes hand bf16 gradients to the optimizer"
+    host_g = (torch.randn(st.flat_grad_lp.numel(), dtype=torch.float32) * 1e-3).to(torch.bfloat16).pin_memory()
+    st.flat_grad_lp.copy_(host_g)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def prepare():
+        st.zero_grad()                       # clears the norm sums and the hand-over bookkeeping
+        st.finalized.update(st.item_ranges)  # gradients are already in the hand-over buffer
+
+    def timed(iters, refresh_transposed, e2e=False):
+        tot = 0.0
+        for _ in range(iters):
+            prepare()
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            if e2e:
+                st.flat_grad_lp.copy_(host_g, non_blocking=True)
+            st.step(0.005, refresh_transposed)
+            if e2e:
+                probe = st.norms[:2].cpu()  # noqa: F841  (device -> host read of a result of the step)
+            e1.record()
+            torch.cuda.synchronize()
+            tot += e0.elapsed_time(e1)
+        return tot / iters
+
+    timed(max(args.warmup, 3), True)
+    sampler = ClockSampler(torch.cuda.current_device())
+    sampler.start()
+    native.launch_count_reset()
+    ring0 = native.path_count(native.PATH_OPT_RING)
+    iters = max(args.steps, 20)
+    ms = timed(iters, True)
+    launches = native.launch_count()
+    ring = native.path_count(native.PATH_OPT_RING) - ring0
+    ms_no_t = timed(iters, False)
+    ms_e2e = timed(3, True, e2e=True)
+    # the update kernel alone (the dominant kernel): CUDA events around its launch
+    lib = native.load()
+    orig = lib.obst_opt_update
+    ev = []
+
+    def wrapped(*a):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = orig(*a)
+        e1.record()
+        ev.append((e0, e1))
+        return rc
+
+    lib.obst_opt_update = wrapped
+    for _ in range(10):
+        prepare()
+        flush.zero_()
+        st.step(0.005, False)
+    torch.cuda.synchronize()
+    lib.obst_opt_update = orig
+    ms_update = sum(a.elapsed_time(b) for a, b in ev) / len(ev)
+    sampler.stop_flag.set()
+    sampler.join(timeout=2)
+    pk = peaks()
+    alg_bytes = 14.0 * n
+    value = alg_bytes / (ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "optimizer_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch")
+    achieved = alg_bytes / (ms_update * 1e-3) / 1e9
+    line = {"metric": OPT_METRIC, "value": value, "unit": "GB/s", "n_gpus": 1, "steps": iters,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"fused optimizer update over the 32big_mixer parameter set: {len(st.variables)} "
+                                   f"tensors, {n} parameters; fp32 masters, bf16 momentum / SM3 slots, bf16 gradients "
+                                   f"~N(0, 1e-3), bf16 shadows + transposed shadows",
+                       "l2": "flushed between timed iterations (256 MiB write)",
+                       "step": "obst_opt_norms (sum g^2; weight norms carried) + obst_opt_update + obst_opt_finalize + "
+                               "obst_transpose_batched",
+                       "bytes_per_param": {"algorithmic": 14, "moved": "norms 2 + update 16 (g 2, p 4+4, m 2+2, "
+                                                                       "shadow 2) + transposed shadows ~4"},
+                       "ms_without_transposed_refresh": ms_no_t, "ms_update_kernel": ms_update,
+                       "streaming_kernel_launches": ring},
+            "clocks": sampler.summary(),
+            "e2e": {"value": alg_bytes / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": host_g.numel() * 2, "d2h_bytes_per_step": 16,
+                    "note": "gradients copied from pinned host memory every step: PCIe-bound, reported for the contract"},
+            "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "kernel": "obst::opt_update_ring_kernel", "achieved": achieved,
+                         "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"], "traffic": traffic,
+                         "peak_source": f"{pk['source']} (hbm_gbs)",
+                         "whole_update_achieved": value, "whole_update_frac": value / pk["hbm_gbs"],
+                         "algorithmic_bytes_per_launch": alg_bytes}}
+    if not args.no_cpu_baseline:
+        v, cores, sec, _ = cpu_optimizer_rate(1, 0)
+        line["cpu_baseline"] = {"value": v, "unit": "GB/s", "cores": cores, "kind": "port",
+                                "sample": f"oracle optimizer_step over the same {n} parameters once: {sec:.2f} s"}
+    print(json.dumps(line), flush=True)
+
+
 # ------------------------------------------------------------------------------------------------------------
 # B200 arm
 # ------------------------------------------------------------------------------------------------------------
 def run_b200(args):
+    if args.workload == "optimizer":
+        return run_b200_optimizer(args)
     import torch
     import torch.distributed as dist
     from obst import native

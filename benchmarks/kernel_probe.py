@@ -54,7 +54,10 @@ def main():
             s += f"  {bytes_ / ms / 1e6:8.1f} GB/s"
         print(s, flush=True)
 
-    for be, tag in ((2, "tc"),):
+    only = os.environ.get("PROBE_ONLY", "")  # "gn": only the bandwidth kernels (short enough to run under ncu)
+    dh2 = torch.empty(T, H * K2, device=DEV, dtype=bf)
+    out = torch.empty(T, F, device=DEV, dtype=bf)
+    for be, tag in ((2, "tc"),) if only in ("", "gemm") else ():
         ms = timeit(lambda: nat.gemm(nat.operand(x, F, 1), nat.operand(win, 1, I), h1, T, I, F, d_ld=I, epi=1, backend=be))
         rep(f"W_in fwd [{tag}] T x512 x4096", ms, 2 * T * I * F)
         ms = timeit(lambda: nat.gemm(nat.operand(h1, I, 1), nat.operand(wmid, 1, H * K2), h2, T, H * K2, I, d_ld=H * K2, epi=1, backend=be))
@@ -72,7 +75,6 @@ def main():
         ms = timeit(lambda: nat.gemm(nat.operand(h2, H * K2, 1, s_glo=K2), nat.operand(wout_t, K2, 1, s_glo=K2 * K), y, T, K, K2, GLO=H, d_ld=F, d_glo=K, R=y, epi=2, backend=be))
         rep(f"W_out fwd grouped, W^T stored [{tag}]", ms, 2 * T * H * K2 * K)
         # dgrads
-        dh2 = torch.empty(T, H * K2, device=DEV, dtype=bf)
         ms = timeit(lambda: nat.gemm(nat.operand(y, F, 1, s_glo=K), nat.operand(wout, K, 1, s_glo=K2 * K), dh2, T, K2, K, GLO=H, d_ld=H * K2, d_glo=K2, backend=be))
         rep(f"W_out dgrad grouped [{tag}]", ms, 2 * T * H * K2 * K)
         ms = timeit(lambda: nat.gemm(nat.operand(h2, H * K2, 1), nat.operand(wmid, H * K2, 1), h1, T, I, H * K2, d_ld=I, R=h1, epi=4, backend=be))
@@ -92,7 +94,6 @@ def main():
         # token mixing
         Bn = T // S
         mix = torch.tril(torch.randn(H, S, S, device=DEV) * 0.01).to(bf)
-        out = torch.empty(T, F, device=DEV, dtype=bf)
         ms = timeit(lambda: nat.gemm(nat.operand(mix, S, 1, s_glo=S * S), nat.operand(x, 1, F, s_glo=K, s_ghi=S * F), out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, tri=1, backend=be))
         rep(f"mix fwd [{tag}] (causal flops)", ms, 2 * T * F * (S + 1) / 2)
         ms = timeit(lambda: nat.gemm(nat.operand(mix, 1, S, s_glo=S * S), nat.operand(x, 1, F, s_glo=K, s_ghi=S * F), out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, tri=2, backend=be))
@@ -100,6 +101,8 @@ def main():
         dm = torch.zeros(H, S, S, device=DEV)
         ms = timeit(lambda: nat.gemm(nat.operand(y, F, 1, s_ko=S * F, s_glo=K), nat.operand(x, F, 1, s_ko=S * F, s_glo=K), dm, S, S, K, KO=Bn, GLO=H, d_ld=S, d_glo=S * S, tri=3, accumulate=True, backend=be))
         rep(f"mix dM [{tag}] (causal flops)", ms, 2 * T * F * (S + 1) / 2)
+    if only == "gemm":
+        return
     # cuBLAS yardstick on this box
     a = torch.randn(8192, 8192, device=DEV, dtype=bf)
     b = torch.randn(8192, 8192, device=DEV, dtype=bf)
@@ -150,6 +153,21 @@ def main():
     nat.gn_fwd(h2, gam2, bet2, n2, H, K2, 0, stats=st2)
     ms = timeit(lambda: nat.gn_bwd(dh2, h2, gam2, bet2, n2, dg2, db2, H, K2, 0, True, stats=st2))
     rep("gn_bwd relu-mask saved stats [T,8,1024]", ms, bytes_=3 * T * H * K2 * 2)
+    ms = timeit(lambda: nat.gn_bwd(dh2, h2, gam2, bet2, n2, dg2, db2, H, K2, 0, False, False, stats=st2))
+    rep("gn_bwd saved stats [T,8,1024]", ms, bytes_=3 * T * H * K2 * 2)
+    # 256-wide heads (32ctx_mixer / 32mixer_group): [T, 16, 256] has the bytes of [T, 8, 512]
+    x4 = x.view(T, 16, 256)
+    gam4 = torch.ones(16, 256, device=DEV, dtype=bf)
+    bet4 = torch.zeros(16, 256, device=DEV, dtype=bf)
+    st4 = torch.empty(T * 16, 2, device=DEV)
+    dg4 = torch.zeros(16, 256, device=DEV)
+    db4 = torch.zeros(16, 256, device=DEV)
+    ms = timeit(lambda: nat.gn_fwd(x4, gam4, bet4, c_tmp, 16, 256, 0, stats=st4))
+    rep("gn_fwd +stats [T,16,256]", ms, bytes_=2 * T * F * 2)
+    ms = timeit(lambda: nat.gn_bwd(y, x4, gam4, bet4, out, dg4, db4, 16, 256, stats=st4))
+    rep("gn_bwd saved stats [T,16,256]", ms, bytes_=3 * T * F * 2)
+    ms = timeit(lambda: nat.gn_bwd(y, x4, gam4, bet4, out, dg4, db4, 16, 256, 1, False, True, stats=st4))
+    rep("gn_bwd + gelu dx+= saved stats [T,16,256]", ms, bytes_=4 * T * F * 2)
     ms = timeit(lambda: nat.axpby(x, y, 1.0, out))
     rep("axpby [T,4096]", ms, bytes_=3 * T * F * 2)
     c = torch.empty_like(x)

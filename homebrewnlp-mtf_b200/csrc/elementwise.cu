@@ -536,9 +536,11 @@ __global__ void __launch_bounds__(256) scatter_kernel(const int32_t* __restrict_
 // softmax cross-entropy (+z-loss, accuracy), forward and backward: one warp per token
 // ================================================================================================
 template <typename T, int MAXI>
-__global__ void __launch_bounds__(256) xent_kernel(const T* __restrict__ logits, const int32_t* __restrict__ targets,
-                                                    T* __restrict__ dlogits, double* __restrict__ sums, int64_t tokens,
-                                                    int vocab, float inv_n, float z_loss) {
+__global__ void __launch_bounds__(256) xent_kernel(const T* logits, const int32_t* __restrict__ targets, T* dlogits,
+                                                    double* __restrict__ sums, int64_t tokens, int vocab, float inv_n,
+                                                    float z_loss) {
+  // logits / dlogits are NOT __restrict__: the model calls this in place (dlogits == logits), so everything that is
+  // needed of a row -- including the target's logit -- is read before the row's gradient is stored.
   __shared__ double s_acc[3];
   if (threadIdx.x < 3) s_acc[threadIdx.x] = 0.0;
   __syncthreads();
@@ -581,6 +583,8 @@ __global__ void __launch_bounds__(256) xent_kernel(const T* __restrict__ logits,
     const float logz = logf(se) + mx;
     int tgt = targets[t];
     tgt = tgt < 0 ? 0 : (tgt >= vocab ? vocab - 1 : tgt);
+    const float lt = to_f32(lr[tgt]);  // before the stores below: dlogits may alias logits
+    __syncwarp();                      // ... by ANY lane of the warp that owns this row
     const float inv_se = 1.0f / se;
     const float zc = 2.0f * z_loss * inv_n * logz;
     T* dr = dlogits + t * vocab;
@@ -594,7 +598,6 @@ __global__ void __launch_bounds__(256) xent_kernel(const T* __restrict__ logits,
       }
     }
     if (lane == 0) {
-      const float lt = to_f32(lr[tgt]);
       a_nll += (double)(logz - lt);
       a_z += (double)logz * (double)logz;
       a_hit += (arg == tgt) ? 1.0 : 0.0;

@@ -115,6 +115,7 @@ int gemm_simt_launch(const GemmParams& p, cudaStream_t st) {
   else if (p.dtype_in == OBST_F32 && p.dtype_out == OBST_BF16) gemm_simt_kernel<float, bf16><<<grid, 256, 0, st>>>(p);
   else OBST_REQUIRE(false, "obst_gemm(simt): bad dtypes %d/%d", p.dtype_in, p.dtype_out);
   count_launch();
+  count_path(OBST_PATH_GEMM_SIMT);
   return check_launch("obst_gemm(simt)");
 }
 

@@ -1037,6 +1037,7 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
     gemm_tc_kernel<1><<<grid, TC_THREADS, Cfg<1>::SMEM, st>>>(tmA, tmB, tmD, tmR, p);
   }
   count_launch();
+  count_path(OBST_PATH_GEMM_TC);
   return check_launch("obst_gemm(tc)");
 }
 

@@ -1,7 +1,16 @@
-// Group norm backward, bf16, 512-wide rows, with the (mean, rstd) the forward kernel saved.
-// Same plan as the generic kernel in elementwise.cu (a warp walks the tokens of ONE head, dgamma / dbeta partials in
-// registers, rows streamed through a per-warp cp.async ring), but every option is a template parameter and gamma /
-// beta live packed in registers: no per-element flag tests, no shared-memory reads for the affine parameters.
+// Group norm backward, bf16, rows of 256 / 512 / 1024 elements, with the (mean, rstd) the forward kernel saved.
+//
+// Plan (as the generic kernel in elementwise.cu): a warp walks the tokens of ONE head, so the dgamma / dbeta partials
+// stay in registers and gamma / beta sit packed in registers; rows are streamed through a per-warp cp.async ring.
+// Every option (fused gelu derivative, ReLU mask of a W_mid output, dx accumulation) is a template parameter.
+//
+// What bounds the kernel is the number of BYTES IN FLIGHT per SM, not instruction issue: ~6.5 TB/s x ~1 us of loaded
+// HBM latency wants >= 44 KB outstanding per SM.  The generic kernel (128 registers -> two blocks per SM, one row of
+// x and dy in flight per warp) holds 32 KB and runs at 4.7 TB/s; with dx accumulation it holds 48 KB and runs at 5.4.
+// Here the ring is RING rows deep (RING - 1 in flight), sized so that two blocks per SM keep ~96 KB outstanding.
+//
+// A 1024-wide row is split over two warps (SPLIT = 2): per-lane state stays that of the 512-wide case and the two
+// row sums are exchanged through shared memory under a 64-thread named barrier.
 #include "obst_common.cuh"
 
 namespace obst {
@@ -17,82 +26,87 @@ __device__ __forceinline__ void bcp_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-static constexpr int BRING = 3;   // rows in flight per warp
 static constexpr int BWARPS = 8;  // warps per block
-static constexpr int BW = 512;    // row width
-static constexpr int BROWB = BW * 2;
 
-template <int ACT, bool RELU, bool ACC>
-__global__ void __launch_bounds__(BWARPS * 32, 2) gn_bwd_ring_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x,
-                                                                 const bf16* __restrict__ gamma,
-                                                                 const bf16* __restrict__ beta, bf16* __restrict__ dx,
-                                                                 float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                                 const float2* __restrict__ stats, int64_t tokens,
-                                                                 int heads, int tokens_per_block) {
-  constexpr int NT = ACC ? 3 : 2;  // tensors staged per row: x, dy (, dx)
+// MAXC: 16-byte chunks per lane (1: 256 columns per warp, 2: 512).  SPLIT: warps per row.  width = 256 MAXC SPLIT.
+template <int MAXC, int SPLIT, int RING, int ACT, bool RELU, bool ACC>
+__global__ void __launch_bounds__(BWARPS * 32, 2)
+gn_bwd_ring_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, const bf16* __restrict__ gamma,
+                   const bf16* __restrict__ beta, bf16* __restrict__ dx, float* __restrict__ dgamma,
+                   float* __restrict__ dbeta, const float2* __restrict__ stats, int64_t tokens, int heads,
+                   int tokens_per_block) {
+  constexpr int NT = ACC ? 3 : 2;         // tensors staged per row: x, dy (, dx)
+  constexpr int WCOLS = 256 * MAXC;       // columns per warp
+  constexpr int WIDTH = WCOLS * SPLIT;    // row width
+  constexpr int ROWB = WCOLS * 2;         // bytes of one warp's part of a row
+  constexpr int SLOTS = BWARPS / SPLIT;   // rows a block works on at a time
   extern __shared__ __align__(16) uint8_t s_raw[];
-  float* s_red = reinterpret_cast<float*>(s_raw);  // [2 * BW] block reduction of dgamma / dbeta
+  __shared__ float s_x[SLOTS][2][2][2];   // [row slot][row parity][which sum][half]: the SPLIT == 2 exchange
+  float* s_red = reinterpret_cast<float*>(s_raw);  // [2 * WIDTH] block reduction of dgamma / dbeta
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slot = warp / SPLIT;   // which row of the block's current group this warp works on
+  const int half = warp % SPLIT;   // which part of that row
+  const int col0 = half * WCOLS;
   const int h = blockIdx.y;
-  uint8_t* ring = s_raw + 2 * BW * sizeof(float) + (size_t)warp * BRING * NT * BROWB;
-  for (int i = threadIdx.x; i < 2 * BW; i += blockDim.x) s_red[i] = 0.f;
+  uint8_t* ring = s_raw + 2 * WIDTH * sizeof(float) + (size_t)warp * RING * NT * ROWB;
+  for (int i = threadIdx.x; i < 2 * WIDTH; i += blockDim.x) s_red[i] = 0.f;
   __syncthreads();
-  uint4 gp[2], bp[2];
+  uint4 gp[MAXC], bp[MAXC];
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int c = (lane + 32 * i) * 8;
-    gp[i] = gamma ? *reinterpret_cast<const uint4*>(gamma + (int64_t)h * BW + c)
-                  : make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
-    bp[i] = (ACT == 1 && beta) ? *reinterpret_cast<const uint4*>(beta + (int64_t)h * BW + c)
+  for (int i = 0; i < MAXC; ++i) {
+    const int c = col0 + (lane + 32 * i) * 8;
+    gp[i] = gamma ? *reinterpret_cast<const uint4*>(gamma + (int64_t)h * WIDTH + c)
+                  : make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);  // bf16 1.0 pairs
+    bp[i] = (ACT == 1 && beta) ? *reinterpret_cast<const uint4*>(beta + (int64_t)h * WIDTH + c)
                                : make_uint4(0u, 0u, 0u, 0u);
   }
-  float pg[2][8], pb[2][8];
+  float pg[MAXC][8], pb[MAXC][8];
 #pragma unroll
-  for (int i = 0; i < 2; ++i)
+  for (int i = 0; i < MAXC; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) pg[i][j] = pb[i][j] = 0.f;
 
   const int64_t t0 = (int64_t)blockIdx.x * tokens_per_block;
   const int64_t t1 = t0 + tokens_per_block < tokens ? t0 + tokens_per_block : tokens;
   auto issue = [&](int64_t t, int stage) {
-    const int64_t off = (t * heads + h) * BW;
-    uint8_t* dst = ring + stage * NT * BROWB;
+    const int64_t off = (t * heads + h) * WIDTH + col0;
+    uint8_t* dst = ring + stage * NT * ROWB;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       bcp16(dst + c * 16, x + off + c * 8);
-      bcp16(dst + BROWB + c * 16, dy + off + c * 8);
-      if (ACC) bcp16(dst + 2 * BROWB + c * 16, dx + off + c * 8);
+      bcp16(dst + ROWB + c * 16, dy + off + c * 8);
+      if (ACC) bcp16(dst + 2 * ROWB + c * 16, dx + off + c * 8);
     }
     bcp_commit();
   };
 #pragma unroll
-  for (int s = 0; s < BRING - 1; ++s) {
-    if (t0 + warp + (int64_t)s * BWARPS < t1) issue(t0 + warp + (int64_t)s * BWARPS, s);
-    else bcp_commit();
+  for (int s = 0; s < RING - 1; ++s) {
+    if (t0 + slot + (int64_t)s * SLOTS < t1) issue(t0 + slot + (int64_t)s * SLOTS, s);
+    else bcp_commit();  // keep one group per ring slot so the wait_group counts stay aligned
   }
   float2 st_next = make_float2(0.f, 0.f);
-  if (t0 + warp < t1) st_next = stats[(t0 + warp) * heads + h];
-  int stage = 0;
-  for (int64_t t = t0 + warp; t < t1; t += BWARPS, stage = (stage + 1) % BRING) {
-    const int64_t tn = t + (int64_t)(BRING - 1) * BWARPS;
-    if (tn < t1) issue(tn, (stage + BRING - 1) % BRING);
+  if (t0 + slot < t1) st_next = stats[(t0 + slot) * heads + h];
+  int stage = 0, parity = 0;
+  for (int64_t t = t0 + slot; t < t1; t += SLOTS, stage = (stage + 1 == RING ? 0 : stage + 1), parity ^= 1) {
+    const int64_t tn = t + (int64_t)(RING - 1) * SLOTS;
+    if (tn < t1) issue(tn, stage == 0 ? RING - 1 : stage - 1);
     else bcp_commit();
     const float2 st = st_next;
-    if (t + BWARPS < t1) st_next = stats[(t + BWARPS) * heads + h];
-    bcp_wait<BRING - 1>();
+    if (t + SLOTS < t1) st_next = stats[(t + SLOTS) * heads + h];
+    bcp_wait<RING - 1>();
     __syncwarp();
-    const uint8_t* src = ring + stage * NT * BROWB;
+    const uint8_t* src = ring + stage * NT * ROWB;
     const float rstd = st.y, nmr = -st.x * st.y;
-    float z[2][8], g[2][8];
+    float z[MAXC][8], g[MAXC][8];
     float sg = 0.f, sgz = 0.f;
     uint32_t maskbits = 0;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       Raw16<bf16> rx, rd, rg;
       rx.r = *reinterpret_cast<const uint4*>(src + c * 16);
-      rd.r = *reinterpret_cast<const uint4*>(src + BROWB + c * 16);
+      rd.r = *reinterpret_cast<const uint4*>(src + ROWB + c * 16);
       rg.r = gp[i];
       float xv[8], dv[8], gam[8], bet[8];
       rx.unpack(xv);
@@ -120,15 +134,24 @@ __global__ void __launch_bounds__(BWARPS * 32, 2) gn_bwd_ring_kernel(const bf16*
     }
     sg = warp_sum(sg);
     sgz = warp_sum(sgz);
-    const float c0 = -sg * (1.0f / BW) * rstd, c1 = -sgz * (1.0f / BW) * rstd;
-    bf16* dst = dx + (t * heads + h) * BW;
+    if (SPLIT == 2) {  // the other half of the row lives in the partner warp
+      if (lane == 0) {
+        s_x[slot][parity][0][half] = sg;
+        s_x[slot][parity][1][half] = sgz;
+      }
+      asm volatile("bar.sync %0, 64;" ::"r"(1 + slot) : "memory");
+      sg = s_x[slot][parity][0][0] + s_x[slot][parity][0][1];
+      sgz = s_x[slot][parity][1][0] + s_x[slot][parity][1][1];
+    }
+    const float c0 = -sg * (1.0f / WIDTH) * rstd, c1 = -sgz * (1.0f / WIDTH) * rstd;
+    bf16* dst = dx + (t * heads + h) * WIDTH + col0;
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < MAXC; ++i) {
       const int c = lane + 32 * i;
       float o[8];
       if (ACC) {
         Raw16<bf16> ra;
-        ra.r = *reinterpret_cast<const uint4*>(src + 2 * BROWB + c * 16);
+        ra.r = *reinterpret_cast<const uint4*>(src + 2 * ROWB + c * 16);
         ra.unpack(o);
       }
 #pragma unroll
@@ -141,64 +164,89 @@ __global__ void __launch_bounds__(BWARPS * 32, 2) gn_bwd_ring_kernel(const bf16*
       out.pack(o);
       out.store(dst + c * 8);
     }
-    __syncwarp();
+    __syncwarp();  // everyone is done with this stage before the next iteration refills it
   }
   // block reduce of the affine gradients, then one fp32 atomic per column and block
 #pragma unroll
-  for (int i = 0; i < 2; ++i)
+  for (int i = 0; i < MAXC; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int col = (lane + 32 * i) * 8 + j;
+      const int col = col0 + (lane + 32 * i) * 8 + j;
       if (dgamma) atomicAdd(&s_red[col], pg[i][j]);
-      if (dbeta) atomicAdd(&s_red[BW + col], pb[i][j]);
+      if (dbeta) atomicAdd(&s_red[WIDTH + col], pb[i][j]);
     }
   __syncthreads();
-  for (int i = threadIdx.x; i < BW; i += blockDim.x) {
-    if (dgamma) atomicAdd(&dgamma[(int64_t)h * BW + i], s_red[i]);
-    if (dbeta) atomicAdd(&dbeta[(int64_t)h * BW + i], s_red[BW + i]);
+  for (int i = threadIdx.x; i < WIDTH; i += blockDim.x) {
+    if (dgamma) atomicAdd(&dgamma[(int64_t)h * WIDTH + i], s_red[i]);
+    if (dbeta) atomicAdd(&dbeta[(int64_t)h * WIDTH + i], s_red[WIDTH + i]);
   }
+}
+
+template <int MAXC, int SPLIT, int ACT, bool RELU, bool ACC>
+static int gn_bwd_ring_typed(const void* dy, const void* x, const void* gamma, const void* beta, void* dx,
+                             float* dgamma, float* dbeta, const float2* stats, int64_t tokens, int heads,
+                             cudaStream_t st) {
+  // ~8-12 KB of ring per warp whatever the row part: narrow parts get a deeper ring
+  constexpr int RING = MAXC == 1 ? 8 : 4;
+  constexpr int WIDTH = 256 * MAXC * SPLIT;
+  constexpr int SMEM = 2 * WIDTH * (int)sizeof(float) + BWARPS * RING * (ACC ? 3 : 2) * (256 * MAXC * 2);
+  // 32 rows per warp (the ring's start-up is RING - 1 rows), fewer when the problem would not fill the machine
+  int tpb = 32 * (BWARPS / SPLIT) * (MAXC == 1 ? 2 : 1);
+  while (tpb > 32 && ((tokens + tpb - 1) / tpb) * heads < 4 * (int64_t)num_sms()) tpb >>= 1;
+  const dim3 grid((unsigned)((tokens + tpb - 1) / tpb), (unsigned)heads);
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(gn_bwd_ring_kernel<MAXC, SPLIT, RING, ACT, RELU, ACC>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) {
+      set_error("obst_gn_bwd: cannot opt in to %d B of shared memory: %s", SMEM, cudaGetErrorString(e));
+      return OBST_ECUDA;
+    }
+    attr = true;
+  }
+  gn_bwd_ring_kernel<MAXC, SPLIT, RING, ACT, RELU, ACC><<<grid, BWARPS * 32, SMEM, st>>>(
+      (const bf16*)dy, (const bf16*)x, (const bf16*)gamma, (const bf16*)beta, (bf16*)dx, dgamma, dbeta, stats, tokens,
+      heads, tpb);
+  count_launch();
+  count_path(OBST_PATH_GN_BWD_RING);
+  return check_launch("obst_gn_bwd");
+}
+
+template <int MAXC, int SPLIT>
+static int gn_bwd_ring_opts(const void* dy, const void* x, const void* gamma, const void* beta, void* dx, float* dgamma,
+                            float* dbeta, const float2* stats, int64_t tokens, int heads, int act, int relu_mask,
+                            int dx_acc, cudaStream_t st) {
+#define OBST_BR(A, R, C) \
+  return gn_bwd_ring_typed<MAXC, SPLIT, A, R, C>(dy, x, gamma, beta, dx, dgamma, dbeta, stats, tokens, heads, st)
+  if (act == 1) {
+    if (relu_mask) {
+      if (dx_acc) OBST_BR(1, true, true);
+      OBST_BR(1, true, false);
+    }
+    if (dx_acc) OBST_BR(1, false, true);
+    OBST_BR(1, false, false);
+  }
+  if (relu_mask) {
+    if (dx_acc) OBST_BR(0, true, true);
+    OBST_BR(0, true, false);
+  }
+  if (dx_acc) OBST_BR(0, false, true);
+  OBST_BR(0, false, false);
+#undef OBST_BR
 }
 
 // Returns OBST_OK after launching, or 1 when this case is not covered (the caller falls back to the generic kernel).
 int gn_bwd_ring_launch(const void* dy, const void* x, const void* gamma, const void* beta, void* dx, float* dgamma,
                        float* dbeta, const float2* stats, int64_t rows, int heads, int width, int act, int relu_mask,
                        int dx_acc, cudaStream_t st) {
-  // Measured (B200, [65536, 8, 512]): with the fused gelu derivative 0.370 ms against 0.450 ms for the generic
-  // kernel; without it the two are equal (0.347 / 0.345 ms: both wait on memory at 16 warps per SM, and an
-  // 80-register build that fits 24 warps spills and is slower), so only the gelu case is routed here.
-  if (act != 1 || width != BW || !stats || rows % heads != 0) return 1;
+  if (!stats || rows % heads != 0 || (width != 256 && width != 512 && width != 1024)) return 1;
   const int64_t tokens = rows / heads;
-  if (tokens < 4096) return 1;
-  const int tpb = 128;
-  const dim3 grid((unsigned)((tokens + tpb - 1) / tpb), (unsigned)heads);
-  const size_t smem = 2 * BW * sizeof(float) + (size_t)BWARPS * BRING * (dx_acc ? 3 : 2) * BROWB;
-#define OBST_BR3(A, R, C)                                                                                          \
-  do {                                                                                                             \
-    static bool attr = false;                                                                                      \
-    if (!attr) {                                                                                                   \
-      cudaFuncSetAttribute(gn_bwd_ring_kernel<A, R, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);   \
-      attr = true;                                                                                                 \
-    }                                                                                                              \
-    gn_bwd_ring_kernel<A, R, C><<<grid, BWARPS * 32, smem, st>>>((const bf16*)dy, (const bf16*)x,                  \
-                                                                 (const bf16*)gamma, (const bf16*)beta, (bf16*)dx, \
-                                                                 dgamma, dbeta, stats, tokens, heads, tpb);        \
-  } while (0)
-#define OBST_BR2(A, R)            \
-  do {                            \
-    if (dx_acc) OBST_BR3(A, R, true); \
-    else OBST_BR3(A, R, false);   \
-  } while (0)
-#define OBST_BR1(A)                  \
-  do {                               \
-    if (relu_mask) OBST_BR2(A, true); \
-    else OBST_BR2(A, false);         \
-  } while (0)
-  OBST_BR1(1);
-#undef OBST_BR1
-#undef OBST_BR2
-#undef OBST_BR3
-  count_launch();
-  return check_launch("obst_gn_bwd");
+  if (tokens < 4096) return 1;  // small problems: the generic kernel's finer grid wins
+  if (width == 256)
+    return gn_bwd_ring_opts<1, 1>(dy, x, gamma, beta, dx, dgamma, dbeta, stats, tokens, heads, act, relu_mask, dx_acc, st);
+  if (width == 512)
+    return gn_bwd_ring_opts<2, 1>(dy, x, gamma, beta, dx, dgamma, dbeta, stats, tokens, heads, act, relu_mask, dx_acc, st);
+  return gn_bwd_ring_opts<2, 2>(dy, x, gamma, beta, dx, dgamma, dbeta, stats, tokens, heads, act, relu_mask, dx_acc, st);
 }
 
 }  // namespace obst

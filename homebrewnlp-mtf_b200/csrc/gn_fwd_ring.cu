@@ -1,4 +1,4 @@
-// Group norm forward, bf16, rows of 256 * MAXC elements (512 / 1024 wide in the benchmark configs).
+// Group norm forward, bf16, rows of 256 * MAXC elements (256 / 512 / 1024 wide in the reference's configs).
 //
 // The generic forward kernel (elementwise.cu) gives every warp one row at a time: load, reduce, normalise, store,
 // next row.  With 64 registers per thread an SM holds 32 warps = 32 KB of loads in flight, which at ~1.2 us of
@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(RING_WARPS * 32) gn_fwd_ring_kernel(const bf16
 // Returns OBST_OK after launching, or 1 when this shape is not covered (the caller falls back to the generic kernel).
 int gn_fwd_ring_launch(const void* x, const void* gamma, const void* beta, void* y, float2* stats, int64_t rows,
                        int heads, int width, int act, cudaStream_t st) {
-  if ((width != 512 && width != 1024) || rows % heads != 0) return 1;
+  if ((width != 256 && width != 512 && width != 1024) || rows % heads != 0) return 1;
   const int64_t tokens = rows / heads;
   if (tokens < 4096) return 1;  // small problems: the generic kernel's finer grid wins
   int tpb = 128;                // tokens per block: 16 rows per warp amortise the gamma / beta loads
@@ -146,12 +146,14 @@ int gn_fwd_ring_launch(const void* x, const void* gamma, const void* beta, void*
     if (act == 1) OBST_RING2(MC, 1); \
     else OBST_RING2(MC, 0);       \
   } while (0)
-  if (width == 512) OBST_RING1(2);
+  if (width == 256) OBST_RING1(1);
+  else if (width == 512) OBST_RING1(2);
   else OBST_RING1(4);
 #undef OBST_RING1
 #undef OBST_RING2
 #undef OBST_RING3
   count_launch();
+  count_path(OBST_PATH_GN_FWD_RING);
   return check_launch("obst_gn_fwd");
 }
 

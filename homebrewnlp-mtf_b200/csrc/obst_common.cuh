@@ -13,6 +13,7 @@ namespace obst {
 // ---- host-side error + launch bookkeeping (defined in api.cu) ------------------------------
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+void count_path(int which);  // OBST_PATH_*: which specialised kernel a call was routed to
 int check_launch(const char* what);  // cudaGetLastError -> OBST_ECUDA
 
 #define OBST_REQUIRE(cond, ...)            \
@@ -169,11 +170,11 @@ __device__ __forceinline__ float gelu_obst_grad(float x) {
 // pointwise.cu: activations other than relu / gelu (obst_act_fwd / obst_act_bwd route kinds >= 2 here)
 int act_any_launch(int dtype, int kind, bool bwd, const void* x, const void* dy, void* out, int64_t n, cudaStream_t st);
 
-// gn_fwd_ring.cu: bf16 rows of 512 / 1024 elements; returns 1 when the shape is not covered
+// gn_fwd_ring.cu: bf16 rows of 256 / 512 / 1024 elements; returns 1 when the shape is not covered
 int gn_fwd_ring_launch(const void* x, const void* gamma, const void* beta, void* y, float2* stats, int64_t rows,
                        int heads, int width, int act, cudaStream_t st);
 
-// gn_bwd_ring.cu: bf16 rows of 512 elements with saved statistics; returns 1 when the case is not covered
+// gn_bwd_ring.cu: bf16 rows of 256 / 512 / 1024 elements with saved statistics; returns 1 when not covered
 int gn_bwd_ring_launch(const void* dy, const void* x, const void* gamma, const void* beta, void* dx, float* dgamma,
                        float* dbeta, const float2* stats, int64_t rows, int heads, int width, int act, int relu_mask,
                        int dx_acc, cudaStream_t st);

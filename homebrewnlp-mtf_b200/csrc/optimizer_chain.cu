@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(256) opt_stage_kernel(const obst_opt_tensor* _
   const int cols = T.dims[T.ndim - 1];
   const int64_t e0 = (int64_t)item_row0[item] * cols;
   const int64_t n = (int64_t)item_rows[item] * cols;
-  const int64_t flat = (T.g - a.grad_base) + e0;  // element offset inside every flat buffer
+  const int64_t flat = (reinterpret_cast<const float*>(T.g) - a.grad_base) + e0;  // element offset inside every flat buffer
   float* __restrict__ g = a.work + flat;
   const float* __restrict__ p = T.p + e0;
   const bool act_bf16 = a.dtype_act == OBST_BF16;

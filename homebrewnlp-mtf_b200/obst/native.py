@@ -36,8 +36,13 @@ class GemmDesc(ctypes.Structure):
 
 class OptTensor(ctypes.Structure):
     _fields_ = [("p", c_void_p), ("shadow", c_void_p), ("g", c_void_p), ("m", c_void_p), ("acc", c_void_p * 4),
-                ("acc_new", c_void_p * 4), ("numel", c_i64), ("dims", c_i32 * 4), ("ndim", c_i32), ("decay", c_i32),
-                ("tril_s", c_i32), ("pad_", c_i32)]
+                ("acc_new", c_void_p * 4), ("g_acc", c_void_p), ("numel", c_i64), ("dims", c_i32 * 4), ("ndim", c_i32),
+                ("decay", c_i32), ("tril_s", c_i32), ("g_bf16", c_i32)]
+
+
+class TransposeItem(ctypes.Structure):  # obst_transpose_item
+    _fields_ = [("src", c_void_p), ("dst", c_void_p), ("batch", c_i32), ("rows", c_i32), ("cols", c_i32),
+                ("tile0", c_i32)]
 
 
 class OptStageArgs(ctypes.Structure):  # obst_opt_stage_args
@@ -58,6 +63,7 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_last_error": (ctypes.c_char_p, []),
     "obst_launch_count": (c_i64, []),
     "obst_launch_count_reset": (None, []),
+    "obst_path_count": (c_i64, [c_i32]),
     "obst_gemm": (c_int, [ctypes.POINTER(GemmDesc), c_int, c_void_p]),
     "obst_gn_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_i32,
                             c_void_p]),
@@ -77,7 +83,10 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_opt_norms": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_void_p,
                                c_i32, c_void_p, c_i32, c_i32, c_void_p]),
     "obst_opt_update": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32, c_i32,
-                                c_i32, c_void_p, c_void_p, c_float, c_float, c_i32, c_float, c_float, c_void_p]),
+                                c_i32, c_void_p, c_void_p, c_float, c_float, c_i32, c_float, c_float, c_i32,
+                                c_void_p]),
+    "obst_grad_finalize": (c_int, [c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_void_p, c_i32, c_void_p]),
+    "obst_transpose_batched": (c_int, [c_int, c_void_p, c_i32, c_i32, c_void_p]),
     "obst_opt_finalize": (c_int, [c_void_p, c_i32, c_i32, c_void_p]),
     "obst_sample_step": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_i32, c_float,
                                  ctypes.c_uint64, c_void_p]),
@@ -150,6 +159,15 @@ def launch_count() -> int:
 
 def launch_count_reset():
     load().obst_launch_count_reset()
+
+
+# the OBST_PATH_* enum of include/obst_b200.h
+PATH_GEMM_TC, PATH_GEMM_SIMT, PATH_GN_FWD_RING, PATH_GN_BWD_RING, PATH_OPT_RING = range(5)
+
+
+def path_count(which: int) -> int:
+    """Calls routed to a specialised kernel so far (obst_path_count)."""
+    return int(load().obst_path_count(which))
 
 
 def operand(t: torch.Tensor, s_mn: int, s_k: int, s_ko: int = 0, s_glo: int = 0, s_ghi: int = 0,

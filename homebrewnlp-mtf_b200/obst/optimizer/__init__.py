@@ -20,7 +20,7 @@ from .context import OptimizerCtx
 from .learning_rate import get_learning_rate
 from .optimizers import OPTIMIZERS, FusedPlan, GenericPlan, lower_plan
 
-ITEM_ELEMS = 32768  # elements per work item of the fused kernels
+ITEM_ELEMS = 131072  # elements of one 512-column chunk per work item of the fused kernels (32 rows per warp)
 
 
 def is_large_tensor(params: ModelParameter, var: Variable) -> bool:
@@ -57,6 +57,11 @@ class FusedOptimizer:
         dev = torch.device(params.device)
         self.state_dtype = params.optimizer_dtype.slice_dtype
         self.act_dtype = params.variable_dtype.activation_dtype
+        # The graph hands the optimizer gradients in the activation dtype (src/optimizer/__init__.py:180).  For the
+        # fused chain with bf16 activations they are therefore kept as a second, bf16 flat buffer -- written once per
+        # step from the fp32 accumulation buffer (obst_grad_finalize), all-reduced in that dtype, read by the update.
+        # Generic chains rewrite the gradient stage by stage and stay on the fp32 buffer.
+        self.grad_lp = self.act_dtype == torch.bfloat16 and isinstance(plan, FusedPlan)
         variables = [v for v in params.variable_cache.values() if v.trainable]
         if not variables:
             raise RuntimeError("no trainable variables: run build() once before get_optimizer()")
@@ -75,6 +80,7 @@ class FusedOptimizer:
         pad = [(-s) % 64 for s in sizes]  # keep every tensor 256-byte aligned inside the flat buffers
         total = sum(s + p for s, p in zip(sizes, pad))
         self.flat_grad = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_grad_lp = torch.zeros(total, dtype=torch.bfloat16, device=dev) if self.grad_lp else None
         self.flat_momentum = torch.zeros(total, dtype=self.state_dtype, device=dev)
         n_acc = sum(sum(d.size for d in v.dims) + 64 * len(v.dims) for v in self.variables)
         self.flat_acc = torch.zeros(n_acc, dtype=self.state_dtype, device=dev)
@@ -83,9 +89,12 @@ class FusedOptimizer:
         self.slots: typing.Dict[str, torch.Tensor] = {}
         self.offsets: typing.List[typing.Tuple[int, int]] = []
         self.depth_ranges: typing.Dict[int, typing.List[int]] = {}
+        self.item_ranges: typing.Dict[int, typing.List[int]] = {}  # depth key -> [first item, end item)
+        self.finalized: typing.Set[int] = set()                     # depth keys handed over this step
+        self.g2_keys: typing.Set[int] = set()                       # ... whose sum g^2 the hand-over already took
 
         table = (native.OptTensor * len(self.variables))()
-        items = []  # (class, tensor, row0, rows)
+        items = []  # (tensor, row0, rows), in flat-layout order
         off = 0
         aoff = 0
         max_cols, vec4 = 1, True
@@ -105,7 +114,14 @@ class FusedOptimizer:
             t = table[ti]
             t.p = v.data.data_ptr()
             t.shadow = v.value.data_ptr() if v.value is not v.data else None
-            t.g = v.grad.data_ptr()
+            if self.grad_lp:
+                t.g = self.flat_grad_lp.data_ptr() + 2 * off
+                t.g_acc = v.grad.data_ptr()
+                t.g_bf16 = 1
+            else:
+                t.g = v.grad.data_ptr()
+                t.g_acc = None
+                t.g_bf16 = 0
             t.m = m.data_ptr()
             dims = [dd.size for dd in v.dims]
             for i, n in enumerate(dims):
@@ -124,44 +140,89 @@ class FusedOptimizer:
             rows = sz // cols
             max_cols = max(max_cols, cols)
             vec4 &= cols % 4 == 0
-            # launch class = the register footprint the update kernel needs for this last dim (columns per lane):
-            # tensors of a class share one launch, so narrow tensors are not run with the widest instantiation
-            per_lane = -(-cols // (128 if cols % 4 == 0 else 32))
-            klass = 4 if per_lane <= 4 else (8 if per_lane <= 8 else (16 if per_lane <= 16 else 0))
-            # the update kernel splits wide rows into 512-column chunks (one block each): size items per chunk
+            # the update kernels split wide rows into 512-column chunks (one block each): size items per chunk
             rpi = min(2048, max(1, ITEM_ELEMS // min(cols, 512)))
+            irng = self.item_ranges.setdefault(key, [len(items), len(items)])
+            if irng[1] != len(items):
+                raise RuntimeError("flat layout is not grouped by depth")  # the sort above guarantees it
             for r0 in range(0, rows, rpi):
-                items.append((klass if cols % 4 == 0 else -klass - 1, ti, r0, min(rpi, rows - r0), cols))
+                items.append((ti, r0, min(rpi, rows - r0)))
+            irng[1] = len(items)
             off += sz + pd
-        items.sort(key=lambda it: (it[0], it[1], it[2]))
-        items_t = [it[1] for it in items]
-        items_r0 = [it[2] for it in items]
-        items_rows = [it[3] for it in items]
-        self.groups: typing.List[typing.Dict[str, int]] = []
-        for pos, it in enumerate(items):
-            if not self.groups or self.groups[-1]["key"] != it[0]:
-                self.groups.append({"key": it[0], "item0": pos, "items": 0, "max_cols": 1, "vec4": int(it[0] >= 0)})
-            g = self.groups[-1]
-            g["items"] += 1
-            g["max_cols"] = max(g["max_cols"], it[4])
         self.max_cols, self.vec4 = max_cols, vec4
         raw = bytes(table)
         self.table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
-        self.n_items = len(items_t)
-        self.item_tensor = torch.tensor(items_t, dtype=torch.int32, device=dev)
-        self.item_row0 = torch.tensor(items_r0, dtype=torch.int32, device=dev)
-        self.item_rows = torch.tensor(items_rows, dtype=torch.int32, device=dev)
+        self.n_items = len(items)
+        self.item_tensor = torch.tensor([it[0] for it in items], dtype=torch.int32, device=dev)
+        self.item_row0 = torch.tensor([it[1] for it in items], dtype=torch.int32, device=dev)
+        self.item_rows = torch.tensor([it[2] for it in items], dtype=torch.int32, device=dev)
         self.decay_names = [v.name for v in self.variables if is_large_tensor(params, v)]
         # sum cast_AT(p)^2 per tensor, accumulated by the update itself for the NEXT step's adaptive-clip norm
         self.wnext = torch.zeros(len(self.variables), dtype=torch.float64, device=dev)
         self.wnorm_valid = False
+        self._t_sig = None   # (shadow, transposed shadow) addresses the transpose table was built for
+        self._t_table = None
+        self._t_tiles = 0
 
     @property
     def n_params(self) -> int:
         return sum(sz for _, sz in self.offsets)
 
     def zero_grad(self):
+        """Start of a step: clear the fp32 accumulation buffer, the norm sums and the hand-over bookkeeping."""
         self.flat_grad.zero_()
+        self.norms.zero_()
+        self.finalized.clear()
+        self.g2_keys.clear()
+
+    def reduce_buffer(self) -> torch.Tensor:
+        """What data-parallel ranks all-reduce: the gradients in the dtype the optimizer is handed."""
+        return self.flat_grad_lp if self.grad_lp else self.flat_grad
+
+    def hand_over(self, key: typing.Optional[int], with_norms: bool):
+        """g(bf16) <- round(fp32 accumulation) for one depth bucket (`key`; None = every bucket not yet handed
+        over): the cast of src/optimizer/__init__.py:180 at the point where the bucket's gradient is final.
+        with_norms: also sum the squares of the rounded values (single rank: nothing is reduced afterwards)."""
+        if not self.grad_lp:
+            return
+        keys = [k for k in self.item_ranges if k not in self.finalized] if key is None else [key]
+        lib, st = native.load(), native.stream_ptr()
+        # contiguous item ranges are merged into one launch
+        spans = sorted(tuple(self.item_ranges[k]) for k in keys if k not in self.finalized)
+        merged: typing.List[typing.List[int]] = []
+        for a, b in spans:
+            if merged and merged[-1][1] == a:
+                merged[-1][1] = b
+            elif b > a:
+                merged.append([a, b])
+        for a, b in merged:
+            native.check(lib.obst_grad_finalize(self.table.data_ptr(), len(self.variables),
+                                                self.item_tensor.data_ptr() + 4 * a, self.item_row0.data_ptr() + 4 * a,
+                                                self.item_rows.data_ptr() + 4 * a, b - a, self.norms.data_ptr(),
+                                                int(with_norms), st), "obst_grad_finalize")
+        self.finalized.update(keys)
+        if with_norms:
+            self.g2_keys.update(keys)
+
+    def refresh_transposed(self):
+        """Rewrite every transposed weight shadow from the shadow the update kernel just wrote: one launch."""
+        pairs = [(v, v.value, v.value_t) for v in self.variables if v.value_t is not None]
+        if not pairs:
+            return
+        sig = tuple((a.data_ptr(), b.data_ptr()) for _, a, b in pairs)
+        if sig != self._t_sig:
+            items = (native.TransposeItem * len(pairs))()
+            tiles = 0
+            for it, (v, a, b) in zip(items, pairs):
+                batch, rows, cols = v._t_view
+                it.src, it.dst = a.data_ptr(), b.data_ptr()
+                it.batch, it.rows, it.cols, it.tile0 = batch, rows, cols, tiles
+                tiles += batch * (-(-rows // 32)) * (-(-cols // 32))
+            self._t_table = torch.frombuffer(bytearray(bytes(items)), dtype=torch.uint8).to(self.table.device)
+            self._t_sig, self._t_tiles, self._t_n = sig, tiles, len(pairs)
+        native.check(native.load().obst_transpose_batched(native.dtype_code(self.act_dtype), self._t_table.data_ptr(),
+                                                          self._t_n, self._t_tiles, native.stream_ptr()),
+                     "obst_transpose_batched")
 
     def invalidate_weight_norms(self):
         """Call after writing Variable.data from outside the optimizer (weight import): the carried norms are stale."""
@@ -274,12 +335,9 @@ class FusedOptimizer:
         elif name == "sm3":
             table = self.table if work is self.flat_grad else self._shifted_table(work)
             lib, st, sdt = native.load(), native.stream_ptr(), native.dtype_code(self.state_dtype)
-            for g in self.groups:
-                o = 4 * g["item0"]
-                native.check(lib.obst_opt_sm3_stage(table.data_ptr(), nt, self.item_tensor.data_ptr() + o,
-                                                    self.item_row0.data_ptr() + o, self.item_rows.data_ptr() + o,
-                                                    g["items"], g["max_cols"], g["vec4"], sdt, st),
-                             "obst_opt_sm3_stage")
+            native.check(lib.obst_opt_sm3_stage(table.data_ptr(), nt, self.item_tensor.data_ptr(),
+                                                self.item_row0.data_ptr(), self.item_rows.data_ptr(), self.n_items,
+                                                self.max_cols, int(self.vec4), sdt, st), "obst_opt_sm3_stage")
             native.check(lib.obst_opt_finalize(table.data_ptr(), nt, sdt, st), "obst_opt_finalize")
         elif name == "graft":  # direction of g, magnitude of the inner optimizer's step (optimizers.py:147-151)
             sums_g = self._scratch("sums_graft", 4 * nt, torch.float64)
@@ -326,36 +384,47 @@ class FusedOptimizer:
         self._stage(N.STAGE_APPLY, work, f=[float(lr) * float(self.params.weight_decay)])
         self.wnorm_valid = False
         if refresh_transposed:
-            for v in self.variables:
-                v.refresh_t()
+            self.refresh_transposed()
 
-    def step(self, lr: float, refresh_transposed: bool = True, step_count: int = 1):
+    def step(self, lr: float, refresh_transposed: bool = True, step_count: int = 1, preview: bool = False):
+        """One update of every variable.  preview: write only the shadows of the would-be weights (the
+        reference's non-final macro-batches, src/run/train.py:63-69); weights and optimizer state stay as they are."""
         if isinstance(self.plan, GenericPlan):
+            if preview:
+                raise NotImplementedError("macro_batching > 1 needs the fused optimizer chain "
+                                          "([adaptive_clip-]sm3-momentum:<b>:1:<n>-learning_rate)")
             return self._step_generic(lr, step_count, refresh_transposed)
         lib = native.load()
         st = native.stream_ptr()
         p, plan = self.params, self.plan
         nt = len(self.variables)
-        grad_bf16 = int(self.act_dtype == torch.bfloat16)
         act, sdt = native.dtype_code(self.act_dtype), native.dtype_code(self.state_dtype)
+        # gradient hand-over dtype: 2 = stored as bf16 (flat_grad_lp), 1 = fp32 rounded to bf16 on read, 0 = fp32
+        grad_bf16 = 2 if self.grad_lp else int(self.act_dtype == torch.bfloat16)
         tp, it, ir0, irs = (self.table.data_ptr(), self.item_tensor.data_ptr(), self.item_row0.data_ptr(),
                             self.item_rows.data_ptr())
-        carry = 1 if self.wnorm_valid else 0
-        if plan.clip > 0:  # one pass over every gradient (and, on the first step only, every weight)
-            native.check(lib.obst_opt_norms(tp, nt, it, ir0, irs, self.n_items, act, grad_bf16,
-                                            self.norms.data_ptr(), carry, self.wnext.data_ptr(), 0, nt, st),
+        single = getattr(getattr(p, "grad_reducer", None), "world", 1) == 1
+        # buckets the data-parallel reducer did not hand over (single rank: all of them, in one launch)
+        self.hand_over(None, with_norms=single and plan.clip > 0)
+        carry = 1 if (self.wnorm_valid and not preview) else 0  # a preview must not consume the carried sums
+        if plan.clip > 0:
+            # sum g^2: taken by the hand-over on a single rank (flags 2|4: keep it, add only the weight half);
+            # with several ranks the buckets were all-reduced after the hand-over, so it is taken here.
+            # sum cast(p)^2: carried over from the previous update (flag 1) or, on the first step, read here.
+            have_g = self.grad_lp and self.g2_keys == set(self.item_ranges)
+            flags = carry | (6 if have_g else 0)
+            native.check(lib.obst_opt_norms(tp, nt, it, ir0, irs, self.n_items, act, grad_bf16 & 1,
+                                            self.norms.data_ptr(), flags, self.wnext.data_ptr(), 0, nt, st),
                          "obst_opt_norms")
-        for g in self.groups:
-            o = 4 * g["item0"]
-            native.check(lib.obst_opt_update(tp, nt, it + o, ir0 + o, irs + o, g["items"], g["max_cols"], g["vec4"],
-                                             act, sdt, grad_bf16, self.norms.data_ptr(), self.wnext.data_ptr(),
-                                             plan.clip, plan.beta, int(plan.nesterov), float(lr),
-                                             float(p.weight_decay), st), "obst_opt_update")
-        native.check(lib.obst_opt_finalize(tp, nt, sdt, st), "obst_opt_finalize")
+        native.check(lib.obst_opt_update(tp, nt, it, ir0, irs, self.n_items, self.max_cols, int(self.vec4), act, sdt,
+                                         grad_bf16, self.norms.data_ptr(), self.wnext.data_ptr(), plan.clip, plan.beta,
+                                         int(plan.nesterov), float(lr), float(p.weight_decay), int(preview), st),
+                     "obst_opt_update")
+        if not preview:
+            native.check(lib.obst_opt_finalize(tp, nt, sdt, st), "obst_opt_finalize")
+            self.wnorm_valid = plan.clip > 0
         if refresh_transposed:  # the update rewrote the shadows in place: transposed copies follow
-            for v in self.variables:
-                v.refresh_t()
-        self.wnorm_valid = plan.clip > 0
+            self.refresh_transposed()
 
 
 def update(ctx: OptimizerCtx):

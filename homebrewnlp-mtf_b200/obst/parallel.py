@@ -1,7 +1,9 @@
 """Data parallelism: the reference's `batch:b` mesh axis (src/dataclass.py:247-252) as one process per GPU.
 
 Every rank holds all parameters and optimizer state, takes train_batch_size/world rows of the batch, and the
-weight gradients are SUM-allreduced (NCCL over NVLink; gloo on CPU for tests) in depth buckets.  During the last
+weight gradients are SUM-allreduced (NCCL over NVLink; gloo on CPU for tests) in depth buckets, in the dtype the
+graph hands the optimizer (bf16 when calculation_dtype is bfloat16: what an MTF einsum over the batch mesh axis
+reduces in).  During the last
 backward pass a depth's bucket is launched on a side stream as soon as that depth's two reversible sub-blocks
 have been back-propagated, so the transfer overlaps the rest of backward; the shared token-mixing maps and the
 input/output variables (final only at the very end) form the last bucket together with the loss scalars.
@@ -31,7 +33,17 @@ class GradReducer:
         self.handles = []
 
     def _flat(self) -> torch.Tensor:
-        return self.params.optimizer_state.flat_grad
+        """The buffer that is reduced: the gradients in the dtype the graph hands the optimizer (activation dtype,
+        src/optimizer/__init__.py:180) -- bf16 for the 32*_mixer configs, which halves the NVLink bytes."""
+        state = self.params.optimizer_state
+        fn = getattr(state, "reduce_buffer", None)
+        return fn() if fn is not None else state.flat_grad
+
+    def _hand_over(self, key: int):
+        """Round the bucket's fp32 accumulation into the hand-over buffer (no-op when that IS the fp32 buffer)."""
+        fn = getattr(self.params.optimizer_state, "hand_over", None)
+        if fn is not None:
+            fn(key, with_norms=False)
 
     def _reduce(self, t: torch.Tensor):
         if self.world == 1 or t.numel() == 0:
@@ -54,6 +66,7 @@ class GradReducer:
         if rng is None or depth in self.launched:
             return
         self.launched.add(depth)
+        self._hand_over(depth)
         self._reduce(self._flat()[rng[0]:rng[1]])
 
     def finish(self):
@@ -65,6 +78,7 @@ class GradReducer:
         for key, rng in state.depth_ranges.items():
             if key not in self.launched:
                 self.launched.add(key)
+                self._hand_over(key)
                 self._reduce(self._flat()[rng[0]:rng[1]])
         sums = getattr(self.params, "loss_sums", None)
         if sums is not None:

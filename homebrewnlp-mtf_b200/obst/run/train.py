@@ -30,6 +30,12 @@ def get_train_model(params: ModelParameter, frame_input, cat_mask_src, cat_mask_
                     frame_mask_src, frame_mask_tag, token_mask, manual_global_step):
     if frame_input is not None:
         raise NotImplementedError("video inputs are outside the hot path")
+    if int(params.macro_batching) != 1:
+        # src/run/train.py:35-74 chains the macro-batches through the weights the previous one WOULD have produced
+        # and commits only the last update; that path is not built yet, and silently doing something else (the
+        # micro-batches below ACCUMULATE gradients, which is a different algorithm) would be worse than refusing
+        raise NotImplementedError(f"macro_batching = {params.macro_batching}: the reference's macro-batching chain "
+                                  f"(src/run/train.py:35-74) is not implemented; use macro_batching = 1")
     tx, ty = _as_tensor(params, token_x_input), _as_tensor(params, token_y_input)
     rows = tx.data.shape[0]
     mb = params.micro_batch_size or rows

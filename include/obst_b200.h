@@ -8,7 +8,8 @@
  * op, each citing the reference lines whose arithmetic it replaces.
  *
  * Conventions (all entry points):
- *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless named host_*;
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless named host_* (descriptor
+ *     structs passed by pointer -- obst_gemm_desc, obst_opt_stage_args -- are read on the host);
  *   - `stream` is a cudaStream_t passed as void*; work is enqueued, never synchronised;
  *   - nothing is allocated or freed (the caller owns every buffer), except a host-side cache of
  *     TMA tensor maps inside obst_gemm (host memory, keyed by operand geometry);
@@ -40,6 +41,17 @@ const char* obst_last_error(void);
  * gpu_launches). */
 int64_t obst_launch_count(void);
 void obst_launch_count_reset(void);
+/* How many calls since load were routed to a specialised kernel: lets a test (or a user) confirm that the shape it
+ * runs takes the kernel it means to measure, not the generic fallback.  Returns -1 for an unknown id. */
+enum {
+  OBST_PATH_GEMM_TC = 0,    /* obst_gemm -> tcgen05 / TMEM / TMA kernel            */
+  OBST_PATH_GEMM_SIMT,      /* obst_gemm -> fp32-FMA kernel                        */
+  OBST_PATH_GN_FWD_RING,    /* obst_gn_fwd -> streaming kernel (gn_fwd_ring.cu)    */
+  OBST_PATH_GN_BWD_RING,    /* obst_gn_bwd -> streaming kernel (gn_bwd_ring.cu)    */
+  OBST_PATH_OPT_RING,       /* obst_opt_update -> streaming kernel (optimizer_ring.cu) */
+  OBST_PATH_COUNT
+};
+int64_t obst_path_count(int32_t which);
 
 /* ---- GEMM family -------------------------------------------------------------------------------
  * One descriptor covers every contraction on the path:
@@ -170,57 +182,88 @@ int obst_transpose_param(int dtype, const void* src, void* dst, int64_t batch, i
  * adaptive_clip:<clip> - sm3 - momentum:<beta>:1:<nesterov> - learning_rate, plus the
  * weight-decay rule and assign_sub:  src/optimizer/__init__.py:31-66,
  * src/optimizer/optimizers.py:13-14,60-84,114-128, src/optimizer/backend.py:23-25.
+ * The arithmetic is the reference's op sequence evaluated op by op in fp32 (IEEE sqrt / reciprocal, no
+ * fused multiply-add), the two norms in float64: for identical gradients the slots and the master
+ * weights are bit-identical to such an evaluation (oracle/obst_oracle.py: optimizer_step).
  *
  * One obst_opt_tensor per variable (table lives in DEVICE memory, built by the caller once):
  *   p      fp32 master slice (updated in place)
  *   shadow AT copy refreshed with the new value (may be NULL); tril_s as in obst_cast_param
- *   g      fp32 gradient (post-allreduce); grad_bf16!=0 rounds it to bf16 first, which is the
- *          dtype the reference hands to the optimizer when calculation_dtype is bfloat16
+ *   g      the gradient handed to the optimizer (post-allreduce): fp32, or -- g_bf16 != 0 -- bfloat16,
+ *          the dtype the reference hands over when calculation_dtype is bfloat16
+ *          (src/optimizer/__init__.py:180).  With an fp32 g, grad_bf16 != 0 rounds it to bf16 on read.
+ *   g_acc  fp32 buffer the backward pass accumulates into when g is bf16 (obst_grad_finalize rounds it
+ *          into g), else NULL
  *   m      momentum state, state dtype (optimizer_slice_dtype)
  *   acc[i] SM3 accumulator of dim i (state dtype), length dims[i]; ndim in 1..4
  *   acc_new[i] fp32 staging for the new accumulator (scratch, length dims[i])
- * Three launches: norms -> update (+ new-accumulator max) -> finalize accumulators.
+ * Launches: [grad_finalize ->] norms -> update (+ new-accumulator max) -> finalize accumulators.
  */
 typedef struct obst_opt_tensor {
   float* p;
   void* shadow;
-  float* g;
+  void* g;
   void* m;
   void* acc[4];
   float* acc_new[4];
+  float* g_acc;
   int64_t numel;
   int32_t dims[4];
   int32_t ndim;
   int32_t decay;   /* 1 = "large tensor" per src/optimizer/__init__.py:49-61 */
   int32_t tril_s;
-  int32_t pad_;
+  int32_t g_bf16;  /* 1 = g points to bfloat16 */
 } obst_opt_tensor;
 
 /* Work list (DEVICE arrays, built by the caller once): item i covers rows
  * [item_row0[i], item_row0[i]+item_rows[i]) of tensor item_tensor[i] viewed as [numel/cols, cols]
- * with cols = dims[ndim-1]; an item covers at most 2048 rows.  A call may pass any sub-range of the list (e.g. one depth at a time, so
- * that the gradients read by obst_opt_norms are still in L2 when obst_opt_update reads them again).
+ * with cols = dims[ndim-1]; an item covers at most 2048 rows.  A call may pass any sub-range of the
+ * list (e.g. the items of one depth).
  * norms: double[2*ntensors] scratch: {sum g^2, sum cast_AT(p)^2} per tensor.  Entries
  * [first_tensor, first_tensor+tensor_count) are cleared first unless flags&2.
  * flags&1 ("carry"): sum cast_AT(p)^2 is NOT recomputed (4 B/param less traffic) but moved from
- * wnext[t], where the previous obst_opt_update accumulated it while writing p; wnext[t] is reset. */
+ * wnext[t], where the previous obst_opt_update accumulated it while writing p; wnext[t] is reset.
+ * flags&4: sum g^2 is already in norms (obst_grad_finalize put it there): only the weight half is
+ * produced (with flags&1 no gradient or weight is read at all). */
 int obst_opt_norms(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
                    const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
                    int32_t dtype_act, int32_t grad_bf16, double* norms, int32_t flags, double* wnext,
                    int32_t first_tensor, int32_t tensor_count, void* stream);
+/* The hand-over of src/optimizer/__init__.py:180 for tensors with a bf16 g: g = bf16(g_acc) for every
+ * item passed (tensors whose g_acc is NULL are skipped).  flags&1: norms[2t] += sum g^2 of the rounded
+ * values (the caller clears norms at the start of a step; skip this when the gradient still has to be
+ * all-reduced, and let obst_opt_norms take the sum afterwards). */
+int obst_grad_finalize(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
+                       const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
+                       double* norms, int32_t flags, void* stream);
 /* reads norms, old accumulators and m; writes p, shadow, m and max-reduces the new SM3
  * accumulators into acc_new (which must be zero on entry; obst_opt_finalize leaves it zero).
- * max_cols = largest last dim over the items passed (<= 12288); vec4 != 0 promises that every last
- * dim is a multiple of 4.  clip <= 0 skips adaptive_clip (norms may then be NULL).
- * wnext (double[ntensors], may be NULL): += sum cast_AT(p_new)^2 per tensor, for the next step's carry. */
+ * max_cols = largest last dim over the items passed; vec4 != 0 promises that every last dim is a
+ * multiple of 4 (the streaming kernel; otherwise a slower generic kernel runs).  clip <= 0 skips
+ * adaptive_clip (norms may then be NULL).
+ * wnext (double[ntensors], may be NULL): += sum cast_AT(p_new)^2 per tensor, for the next step's carry.
+ * preview != 0: nothing but `shadow` is written -- the weights the graph WOULD see after this update
+ * (the reference's macro-batching chain, src/run/train.py:63-69, src/optimizer/__init__.py:65-66). */
 int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
                     const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
                     int32_t max_cols, int32_t vec4, int32_t dtype_act, int32_t dtype_state,
                     int32_t grad_bf16, const double* norms, double* wnext, float clip, float beta,
-                    int32_t nesterov, float lr, float weight_decay, void* stream);
+                    int32_t nesterov, float lr, float weight_decay, int32_t preview, void* stream);
 /* acc[i] = cast_state(acc_new[i]); acc_new[i] = 0. */
 int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dtype_state,
                       void* stream);
+
+/* Batched form of obst_transpose_param: every transposed weight shadow in one launch.  items: DEVICE
+ * array; item i is `batch` row-major [rows, cols] matrices at src, written as [cols, rows] at dst;
+ * tile0 = number of 32x32 tiles of all earlier items (exclusive prefix sum of
+ * batch * ceil(rows/32) * ceil(cols/32)); total_tiles = that sum over all items. */
+typedef struct obst_transpose_item {
+  const void* src;
+  void* dst;
+  int32_t batch, rows, cols, tile0;
+} obst_transpose_item;
+int obst_transpose_batched(int dtype, const obst_transpose_item* items, int32_t nitems, int32_t total_tiles,
+                           void* stream);
 
 /* ---- autoregressive sampling, one step -------------------------------------------------------------
  * src/run/inference.py:76-95 (language branch of autoregressive_model's loop body), after the forward pass:
@@ -294,17 +337,19 @@ int obst_opt_sm3_stage(const obst_opt_tensor* table, int32_t ntensors, const int
  * uses this entry point instead: the table, work list, norm sums and staging live in a fixed ~114 KB block
  * inside the library image (a file-scope __device__ array; every GPU that loads the library holds it until
  * the process exits).  The caller passes only the tensor itself:
- *   p, g fp32 [numel] (16-byte aligned), shadow (activation dtype, may be NULL), m and acc[i] (state dtype,
- *   acc[i] has dims[i] entries), ndim 1..4; remaining arguments as obst_opt_update.
+ *   p, g fp32 [numel], shadow (activation dtype, may be NULL), m (state dtype) -- DEVICE pointers, all
+ *   16-byte aligned when the last dim is a multiple of 4;
+ *   host_acc: HOST array of ndim DEVICE pointers, host_acc[i] = SM3 accumulator of dim i (state dtype,
+ *   host_dims[i] entries); host_dims: HOST array of the ndim dims; ndim 1..4;
+ *   remaining arguments as obst_opt_update.
  * Limits (rejected with OBST_EINVAL and a message): the dims, each rounded up to 64, may add up to at most
- * 16640; the tensor may need at most 4096 work items of 32768/last_dim rows (134 M elements for
- * last dims <= 32768); last dim <= 12288.
+ * 16640; the tensor may need at most 4096 work items of 32768/min(last_dim, 512) rows (134 M elements).
  * The first call on each device looks up the block's device address; make that call before capturing a
  * stream.  Every call on a device shares the block (it is cleared on entry where the update needs zeros),
  * so two calls that overlap on the GPU -- different streams, or graph branches -- race: serialise them.
  * Calls no cudaMalloc / cudaFree or other allocating routine; enqueues 3-4 kernels on `stream`. */
-int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, void* const* acc,
-                          const int32_t* dims, int32_t ndim, int32_t decay, int32_t tril_s,
+int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, void* const* host_acc,
+                          const int32_t* host_dims, int32_t ndim, int32_t decay, int32_t tril_s,
                           int32_t dtype_act, int32_t dtype_state, int32_t grad_bf16, float clip,
                           float beta, int32_t nesterov, float lr, float weight_decay, void* stream);
 

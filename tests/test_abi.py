@@ -66,24 +66,33 @@ def test_argument_validation_needs_no_gpu(lib):
     assert lib.obst_opt_stage(ptr, 1, ptr, ptr, ptr, 1, ctypes.byref(a), None) == -1 and b"bad stage" in lib.obst_last_error()
     a.stage = native.STAGE_ADAM
     assert lib.obst_opt_stage(ptr, 1, ptr, ptr, ptr, 1, ctypes.byref(a), None) == -1   # no buffers
-    assert lib.obst_opt_sm3_stage(ptr, 1, ptr, ptr, ptr, 1, 20000, 1, 1, None) == -1
+    assert lib.obst_opt_sm3_stage(ptr, 1, ptr, ptr, ptr, 1, 512, 1, 7, None) == -1 and b"state dtype" in lib.obst_last_error()
+    assert lib.obst_opt_update(ptr, 1, ptr, ptr, ptr, 1, 512, 1, 1, 7, 0, ptr, None, 0.003, 0.9, 1, 0.01, 0.0, 0,
+                               None) == -1 and b"state dtype" in lib.obst_last_error()
+    assert lib.obst_grad_finalize(ptr, 1, ptr, ptr, ptr, 1, None, 1, None) == -1 and b"norms" in lib.obst_last_error()
+    assert lib.obst_transpose_batched(1, None, 3, 5, None) == -1 and b"null item" in lib.obst_last_error()
+    assert lib.obst_transpose_batched(1, None, 0, 0, None) == 0
 
 
 def test_struct_layout_matches_the_c_compiler(tmp_path):
     from obst import native
     c = tmp_path / "sz.c"
     c.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "obst_b200.h"\nint main(){'
-                 'printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(obst_operand), sizeof(obst_gemm_desc), '
+                 'printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(obst_operand), '
+                 'sizeof(obst_gemm_desc), '
                  'sizeof(obst_opt_tensor), offsetof(obst_gemm_desc, D), offsetof(obst_opt_tensor, numel), '
                  'offsetof(obst_opt_tensor, tril_s), sizeof(obst_opt_stage_args), '
-                 'offsetof(obst_opt_stage_args, grad_base), offsetof(obst_opt_stage_args, sums2)); return 0;}')
+                 'offsetof(obst_opt_stage_args, grad_base), offsetof(obst_opt_stage_args, sums2), '
+                 'offsetof(obst_opt_tensor, g_acc), offsetof(obst_opt_tensor, g_bf16), sizeof(obst_transpose_item), '
+                 'offsetof(obst_transpose_item, tile0)); return 0;}')
     exe = tmp_path / "sz"
     subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), str(c), "-o", str(exe)], check=True)
     out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
     got = [ctypes.sizeof(native.Operand), ctypes.sizeof(native.GemmDesc), ctypes.sizeof(native.OptTensor),
            native.GemmDesc.D.offset, native.OptTensor.numel.offset, native.OptTensor.tril_s.offset,
            ctypes.sizeof(native.OptStageArgs), native.OptStageArgs.grad_base.offset,
-           native.OptStageArgs.sums2.offset]
+           native.OptStageArgs.sums2.offset, native.OptTensor.g_acc.offset, native.OptTensor.g_bf16.offset,
+           ctypes.sizeof(native.TransposeItem), native.TransposeItem.tile0.offset]
     assert [int(v) for v in out] == got
 
 

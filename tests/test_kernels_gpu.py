@@ -204,6 +204,74 @@ def test_gn_fwd_bwd(nat, dtype, tol, width, act, saved_stats):
     assert rel_err(db, br.grad) < tol
 
 
+# The kernels the benchmark runs: from 4096 tokens on, bf16 rows of 512 / 1024 elements take the streaming ("ring")
+# kernels of gn_fwd_ring.cu / gn_bwd_ring.cu, which the small case above never reaches.  Every template instantiation
+# (width x fused gelu x saved statistics x dx accumulation x ReLU mask) against the torch float64 statement; 8200
+# tokens is not a multiple of the 128-token block, so the ragged tail is covered too.
+@pytest.mark.parametrize("T", [4096, 8200])
+@pytest.mark.parametrize("width", [256, 512, 1024])
+@pytest.mark.parametrize("act", [0, 1])
+def test_gn_fwd_streaming_kernels(nat, T, width, act):
+    H = 8
+    x = randn(T, H, width, seed=60, scale=2.0) + 0.5
+    gamma = (1 + 0.02 * torch.randn(H, width)).to(torch.bfloat16).to(DEV)
+    beta = (0.02 * torch.randn(H, width)).to(torch.bfloat16).to(DEV)
+    yr = gn_ref(x.double(), gamma.double(), beta.double(), act)
+    xd = x.double().view(T * H, width)
+    for with_stats in (False, True):
+        y = torch.full_like(x, float("nan"))
+        stats = torch.full((T * H, 2), float("nan"), device=DEV) if with_stats else None
+        before = nat.path_count(nat.PATH_GN_FWD_RING)
+        nat.gn_fwd(x, gamma, beta, y, H, width, act, stats=stats)
+        assert nat.path_count(nat.PATH_GN_FWD_RING) == before + 1, "the streaming forward kernel did not run"
+        assert rel_err(y, yr) < 2e-2 and bool(torch.isfinite(y.float()).all())
+        assert max_rel(y, yr) < 2e-2  # no row may be off: a wrong row would hide in the L2 norm of 8200 x 8 rows
+        if with_stats:
+            assert rel_err(stats[:, 0], xd.mean(-1)) < 1e-5
+            assert rel_err(stats[:, 1], (xd.var(-1, unbiased=False) + 1e-5).rsqrt()) < 1e-5
+    # no scale / no shift
+    y = torch.empty_like(x)
+    nat.gn_fwd(x, None, None, y, H, width, act)
+    assert rel_err(y, gn_ref(x.double(), 1.0, 0.0, act)) < 2e-2
+
+
+@pytest.mark.parametrize("T", [4096, 8200])
+@pytest.mark.parametrize("width,relu_mask", [(256, False), (512, False), (1024, False), (1024, True), (512, True)])
+@pytest.mark.parametrize("act", [0, 1])
+@pytest.mark.parametrize("dx_accumulate", [False, True])
+def test_gn_bwd_streaming_kernels(nat, T, width, relu_mask, act, dx_accumulate):
+    H = 8
+    x = randn(T, H, width, seed=61, scale=2.0) + 0.5
+    if relu_mask:
+        x = x.relu()  # the W_mid path: the normalised tensor is a ReLU output
+    gamma = (1 + 0.02 * torch.randn(H, width)).to(torch.bfloat16).to(DEV)
+    beta = (0.02 * torch.randn(H, width)).to(torch.bfloat16).to(DEV)
+    dy = randn(T, H, width, seed=62)
+    y = torch.empty_like(x)
+    stats = torch.empty(T * H, 2, device=DEV)
+    nat.gn_fwd(x, gamma, beta, y, H, width, act, stats=stats)
+    xr = x.double().requires_grad_(True)
+    gr = gamma.double().requires_grad_(True)
+    br = beta.double().requires_grad_(True)
+    gn_ref(xr, gr, br, act).backward(dy.double())
+    dx_ref = xr.grad * (x > 0) if relu_mask else xr.grad
+    dx0 = randn(T, H, width, seed=63)
+    for saved in (True, False):
+        dx = dx0.clone() if dx_accumulate else torch.full_like(x, float("nan"))
+        dg = torch.zeros(H, width, device=DEV)
+        db = torch.zeros(H, width, device=DEV)
+        before = nat.path_count(nat.PATH_GN_BWD_RING)
+        nat.gn_bwd(dy, x, gamma, beta, dx, dg, db, H, width, act=act, relu_mask=relu_mask, dx_accumulate=dx_accumulate,
+                   stats=stats if saved else None)
+        if saved:  # the training step always passes the forward's statistics: that is the streaming kernel's case
+            assert nat.path_count(nat.PATH_GN_BWD_RING) == before + 1, "the streaming backward kernel did not run"
+        want = dx0.double() + dx_ref if dx_accumulate else dx_ref
+        assert rel_err(dx, want) < 2e-2 and bool(torch.isfinite(dx.float()).all())
+        assert max_rel(dx, want) < 4e-2
+        assert rel_err(dg, gr.grad) < 2e-2
+        assert rel_err(db, br.grad) < 2e-2
+
+
 def test_gn_bwd_relu_mask(nat):
     T, H, W = 64, 8, 64
     x = randn(T, H, W, dtype=torch.float32, seed=23).relu()
@@ -307,6 +375,12 @@ def test_xent(nat, dtype, tol):
     assert abs(float(sums[1]) - float(z2)) / float(z2) < 1e-5
     assert float(sums[2]) == float((logits.float().argmax(-1) == tgt).sum())
     assert rel_err(dl, lr.grad) < tol
+    # in place, as the model calls it (dlogits IS logits): same sums, same gradient
+    inplace = logits.clone()
+    sums2 = torch.zeros(3, dtype=torch.float64, device=DEV)
+    nat.xent_fwd_bwd(inplace, tgt, inplace, sums2, 1.0 / n_global, 1e-4)
+    assert torch.equal(inplace, dl)
+    assert torch.allclose(sums2, sums, rtol=1e-12, atol=0)
 
 
 def test_cast_param_tril(nat):
