@@ -42,15 +42,12 @@ gn_bwd_ring_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, cons
   constexpr int SLOTS = BWARPS / SPLIT;   // rows a block works on at a time
   extern __shared__ __align__(16) uint8_t s_raw[];
   __shared__ float s_x[SLOTS][2][2][2];   // [row slot][row parity][which sum][half]: the SPLIT == 2 exchange
-  float* s_red = reinterpret_cast<float*>(s_raw);  // [2 * WIDTH] block reduction of dgamma / dbeta
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slot = warp / SPLIT;   // which row of the block's current group this warp works on
   const int half = warp % SPLIT;   // which part of that row
   const int col0 = half * WCOLS;
   const int h = blockIdx.y;
-  uint8_t* ring = s_raw + 2 * WIDTH * sizeof(float) + (size_t)warp * RING * NT * ROWB;
-  for (int i = threadIdx.x; i < 2 * WIDTH; i += blockDim.x) s_red[i] = 0.f;
-  __syncthreads();
+  uint8_t* ring = s_raw + (size_t)warp * RING * NT * ROWB;
   uint4 gp[MAXC], bp[MAXC];
 #pragma unroll
   for (int i = 0; i < MAXC; ++i) {
@@ -166,19 +163,35 @@ gn_bwd_ring_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, cons
     }
     __syncwarp();  // everyone is done with this stage before the next iteration refills it
   }
-  // block reduce of the affine gradients, then one fp32 atomic per column and block
+  // Block reduce of the affine gradients without shared-memory atomics (fp32 atomicAdd on shared memory is a
+  // compare-and-swap loop, 8-way contended here): every warp parks its partials in its own -- now idle -- ring,
+  // then each thread sums one column over the warps that hold it and issues ONE global atomic.
+  bcp_wait<0>();
+  __syncwarp();
+  static_assert(RING * NT * ROWB >= 2 * WCOLS * (int)sizeof(float), "ring too small to park the partials");
+  float* park = reinterpret_cast<float*>(ring);
 #pragma unroll
-  for (int i = 0; i < MAXC; ++i)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int col = col0 + (lane + 32 * i) * 8 + j;
-      if (dgamma) atomicAdd(&s_red[col], pg[i][j]);
-      if (dbeta) atomicAdd(&s_red[WIDTH + col], pb[i][j]);
-    }
+  for (int i = 0; i < MAXC; ++i) {
+    const int c = (lane + 32 * i) * 8;
+    *reinterpret_cast<float4*>(park + c) = make_float4(pg[i][0], pg[i][1], pg[i][2], pg[i][3]);
+    *reinterpret_cast<float4*>(park + c + 4) = make_float4(pg[i][4], pg[i][5], pg[i][6], pg[i][7]);
+    *reinterpret_cast<float4*>(park + WCOLS + c) = make_float4(pb[i][0], pb[i][1], pb[i][2], pb[i][3]);
+    *reinterpret_cast<float4*>(park + WCOLS + c + 4) = make_float4(pb[i][4], pb[i][5], pb[i][6], pb[i][7]);
+  }
   __syncthreads();
-  for (int i = threadIdx.x; i < WIDTH; i += blockDim.x) {
-    if (dgamma) atomicAdd(&dgamma[(int64_t)h * WIDTH + i], s_red[i]);
-    if (dbeta) atomicAdd(&dbeta[(int64_t)h * WIDTH + i], s_red[WIDTH + i]);
+  const float* rings = reinterpret_cast<const float*>(s_raw);
+  constexpr int RING_FLOATS = RING * NT * ROWB / (int)sizeof(float);
+  for (int col = threadIdx.x; col < WIDTH; col += blockDim.x) {
+    const int hf = col / WCOLS, cc = col - hf * WCOLS;
+    float a = 0.f, b = 0.f;
+#pragma unroll
+    for (int sl = 0; sl < SLOTS; ++sl) {
+      const float* pw = rings + (size_t)(sl * SPLIT + hf) * RING_FLOATS;
+      a += pw[cc];
+      b += pw[WCOLS + cc];
+    }
+    if (dgamma) atomicAdd(&dgamma[(int64_t)h * WIDTH + col], a);
+    if (dbeta) atomicAdd(&dbeta[(int64_t)h * WIDTH + col], b);
   }
 }
 
@@ -189,7 +202,7 @@ static int gn_bwd_ring_typed(const void* dy, const void* x, const void* gamma, c
   // ~8-12 KB of ring per warp whatever the row part: narrow parts get a deeper ring
   constexpr int RING = MAXC == 1 ? 8 : 4;
   constexpr int WIDTH = 256 * MAXC * SPLIT;
-  constexpr int SMEM = 2 * WIDTH * (int)sizeof(float) + BWARPS * RING * (ACC ? 3 : 2) * (256 * MAXC * 2);
+  constexpr int SMEM = BWARPS * RING * (ACC ? 3 : 2) * (256 * MAXC * 2);
   // 32 rows per warp (the ring's start-up is RING - 1 rows), fewer when the problem would not fill the machine
   int tpb = 32 * (BWARPS / SPLIT) * (MAXC == 1 ? 2 : 1);
   while (tpb > 32 && ((tokens + tpb - 1) / tpb) * heads < 4 * (int64_t)num_sms()) tpb >>= 1;

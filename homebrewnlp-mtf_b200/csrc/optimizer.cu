@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
         Tp[e] = o.p_new;
         reinterpret_cast<TS*>(Tm)[e] = from_f32<TS>(o.m_new);
         const float wv = hp.act_bf16 ? round_to<bf16>(o.p_new) : o.p_new;
-        w2 += square_as_double(wv, hp.act_bf16 != 0);
+        w2 = add_square(w2, wv, hp.act_bf16 != 0);
       }
     }
     rowmax = warp_max(rowmax);

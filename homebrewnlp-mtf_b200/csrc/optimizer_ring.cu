@@ -182,7 +182,7 @@ __global__ void __launch_bounds__(RWARPS * 32, 2) opt_update_ring_kernel(const o
         }
         if (!preview) {
           const float wv = hp.act_bf16 ? round_to<bf16>(o.p_new) : o.p_new;
-          w2 += square_as_double(wv, hp.act_bf16 != 0);
+          w2 = add_square(w2, wv, hp.act_bf16 != 0);
         }
       }
       if (Tshadow) {

@@ -15,7 +15,6 @@ Extensions (no counterpart in the reference, all optional):
                     reconstruction rounding).  Default false = the reference's algorithm.
 """
 import copy
-import random
 import typing
 
 import torch
@@ -92,109 +91,111 @@ class TensorStorage:
         self.text_input_embedding = None
 
 
-class ModelParameter(typing.Dict[str, typing.Any]):
+_DTYPE_KEYS = ("slice_dtype", "storage_dtype", "calculation_dtype", "optimizer_slice_dtype", "optimizer_calculation_dtype")
+_EMBEDDING_KEYS = ("position_embedding", "token_embedding", "output_embedding", "empty_frame_embedding")
+
+
+class ModelParameter:
+    """The reference's config object for the language ("gpt") path: every JSON key becomes an attribute, unknown keys
+    warn, then the sizes and named dimensions the layers use are derived (src/dataclass.py:184-342).  What the
+    reference derives only for its video / mixture-of-experts / TPU-mesh branches is left out: those branches are
+    outside the hot path and `build` refuses them."""
+
     def __init__(self, config: typing.Dict[str, typing.Any]):
-        super().__init__()
+        values = copy.deepcopy(DEFAULTS)
+        values.update(copy.deepcopy(EXTENSIONS))
+        source = config.dict() if hasattr(config, "dict") and not isinstance(config, dict) else config
+        for key, value in source.items():
+            if key not in values:
+                print(f"WARNING: Unknown ModelParameter {key}={value!r}")
+            values[key] = value
+        self.__dict__.update(values)
+        self._validate()
+        self._parse_strings()
+        self._derive_sizes()
+        self._name_dimensions()
+        # ---- execution state of this implementation ----
+        self.attention_idx = 0
+        self.variable_cache = {}
+        self.cached_parameters = {}
+        self.tape: typing.Optional[list] = None     # backward closures recorded while not None
+        self.residual = None                        # (buffer, sign, out) a final GEMM may fuse: revnet.py
+        self.n_global_targets: typing.Optional[int] = None  # loss normaliser across DP ranks and micro-batches
+        self.global_step = 0                        # tf.train global_step (int64 in the reference)
+        self.manual_global_step = 0
 
-        self.__dict__.update(copy.deepcopy(DEFAULTS))
-        self.__dict__.update(copy.deepcopy(EXTENSIONS))
-
-        if hasattr(config, 'dict'):
-            config = config.dict()
-
-        for k, v in config.items():
-            if k not in self.__dict__:
-                print(f"WARNING: Unknown ModelParameter {k}={v!r}")
-            self.__dict__[k] = v
-
+    def _validate(self):
+        """The ValueErrors of src/dataclass.py:189-241 that can fire on the language path."""
         if self.grad_accumulation > 1:
             raise ValueError("Gradient accumulation is not supported right now. The optimizer was split into two "
                              "different 'sections' where the 'accumulation' section still has to be integrated")
-
-        assert self.macro_batching > 0, "MacroBatching has to be >=1, where 1 means it's disabled"
-        if isinstance(self.position_embedding, str):
-            self.position_embedding = self.position_embedding.split('-')
-            self.token_embedding = self.token_embedding.split('-')
-            self.output_embedding = self.output_embedding.split('-')
-            self.empty_frame_embedding = self.empty_frame_embedding.split('-')
-
-            for key in ("slice_dtype", "storage_dtype", "calculation_dtype", "optimizer_slice_dtype",
-                        "optimizer_calculation_dtype"):
-                name = getattr(self, key)
-                if name not in DTYPES:
-                    raise ValueError(f"{key}={name!r}: supported dtypes on this path are {list(DTYPES)}")
-                setattr(self, key, DTYPES[name])
-
-            self.learning_rate_config = {key: LearningRateConfig(**cfg) for key, cfg in
-                                         self.learning_rate_config.items()}
-            self.tensor_storage = TensorStorage()
-
-        self.multi_loss_strategy = self.multi_loss_strategy.lower()
-        if self.multi_loss_strategy not in ["linear", "pcgrad", "mgda"]:
-            print(f'{self.multi_loss_strategy} is not in the support option list for multi loss strategies: '
-                  f'["linear", "pcgrad", "mgda"]. default to "linear".')
-            self.multi_loss_strategy = "linear"
+        if self.macro_batching < 1:
+            raise ValueError("MacroBatching has to be >=1, where 1 means it's disabled")
         if not self.use_language and not self.use_video:
             raise ValueError("Language and video mode are disabled. No model can be built.")
-        if self.weight_standardisation and not self.weight_centralisation:
-            print("Can't standardise weights without centralizing them first. Enabling it.")
-            self.weight_centralisation = True
         if self.features is None and self.features_per_head is None:
             raise ValueError("Either features or features_per_head has to be specified")
+
+    def _parse_strings(self):
+        for key in _EMBEDDING_KEYS:  # "absolute-orthogonal" -> ["absolute", "orthogonal"]
+            value = getattr(self, key)
+            if isinstance(value, str):
+                setattr(self, key, value.split('-'))
+        for key in _DTYPE_KEYS:
+            name = getattr(self, key)
+            if isinstance(name, torch.dtype):
+                continue
+            if name not in DTYPES:
+                raise ValueError(f"{key}={name!r}: supported dtypes on this path are {list(DTYPES)}")
+            setattr(self, key, DTYPES[name])
+        self.learning_rate_config = {key: cfg if isinstance(cfg, LearningRateConfig) else LearningRateConfig(**cfg)
+                                     for key, cfg in self.learning_rate_config.items()}
+        self.variable_dtype = VariableDType(self.storage_dtype, self.slice_dtype, self.calculation_dtype)
+        self.optimizer_dtype = VariableDType(self.storage_dtype, self.optimizer_slice_dtype,
+                                             self.optimizer_calculation_dtype)
+        self.tensor_storage = TensorStorage()
+        strategy = self.memory_reduction_strategy
+        self.block_config = [BlockConfig(c, memory_reduction_strategy=strategy) for c in self.block_config]
+        self.input_block_config = [BlockConfig(c, memory_reduction_strategy="checkpoint")
+                                   for c in self.input_block_config]
+        self.output_block_config = [BlockConfig(c, memory_reduction_strategy="checkpoint")
+                                    for c in self.output_block_config]
+
+    def _derive_sizes(self):
         if self.features is None:
             self.features = self.features_per_head * self.heads
         if self.features_per_head is None:
             self.features_per_head = self.features // self.heads
-        if self.use_video and (self.frame_width * self.frame_height // self.patch_size) % self.experts:
-            raise ValueError("Frame size has to be divisible by number of experts. Set \"experts\" to 1 if you're not "
-                             "using MoE")
-        if self.intermediate_feed_forward_multiplier_multiplier is not None:
-            self.intermediate_feed_forward_multiplier = \
-                self.group_linear_factor * self.intermediate_feed_forward_multiplier_multiplier / self.heads
-        if self.intermediate_feed_forward_multiplier is None:
+        # width of the bottleneck: features * group_linear_factor * mm / heads  (src/dataclass.py:230-235,283-285)
+        mm = self.intermediate_feed_forward_multiplier_multiplier
+        if mm is not None:
+            self.intermediate_feed_forward_multiplier = self.group_linear_factor * mm / self.heads
+        elif self.intermediate_feed_forward_multiplier is None:
             self.intermediate_feed_forward_multiplier = self.group_linear_factor / self.heads
         if not self.use_video and self.language_token_per_frame != self.sequence_length:
             print(f"language_token_per_frame is unused in language-only mode. Overwriting with "
                   f"sequence_length={self.sequence_length}")
             self.language_token_per_frame = self.sequence_length
-        if self.macro_batching > 1 and self.grad_accumulation > 1 and self.macro_batching % self.grad_accumulation != 0:
-            raise ValueError(f'"macro_batching" needs do be divisible by "grad_accumulation", '
-                             f'{self.macro_batching} is not divisible by {self.grad_accumulation}')
-
-        if self.use_random_dataloader:
-            print('WARNING: Use random dataset seed')
-            for _ in range(random.randint(0, 1000)):
-                self.data_seed = random.randint(0, 1000000)
-        # The reference derives an MTF mesh "b:<tpu_size//heads>,h:<heads>" (src/dataclass.py:247-252).  The
-        # strings are kept for inspection; execution maps `batch:b` to data parallelism over the GPUs of one box
-        # and keeps all heads on one GPU.
-        split_batch = self.heads < self.tpu_size
-        split_heads = self.heads > 1
-        self.mesh_shape = ','.join([f"b:{self.tpu_size // self.heads:.0f}"] * split_batch +
-                                   [f"h:{self.heads:.0f}"] * split_heads)
-        self.layout = ','.join(["batch:b"] * split_batch + ["heads:h"] * split_heads)
-        self.variable_dtype = VariableDType(self.storage_dtype, self.slice_dtype, self.calculation_dtype)
-        self.optimizer_dtype = VariableDType(self.storage_dtype, self.optimizer_slice_dtype,
-                                             self.optimizer_calculation_dtype)
-        self.block_config = [BlockConfig(conf, memory_reduction_strategy=self.memory_reduction_strategy) for conf in
-                             self.block_config]
-        self.input_block_config = [BlockConfig(conf, memory_reduction_strategy="checkpoint") for conf in
-                                   self.input_block_config]
-        self.output_block_config = [BlockConfig(conf, memory_reduction_strategy="checkpoint") for conf in
-                                    self.output_block_config]
         self.time_patch_size = self.sequence_length // self.time_patch
         self.language_token_patch = self.language_token_per_frame // self.token_patch_size
+        # The reference turns (tpu_size, heads) into an MTF mesh "b:<tpu_size//heads>,h:<heads>" with layout
+        # "batch:b,heads:h" (src/dataclass.py:247-252).  The strings are kept for inspection only: here `batch:b` is
+        # data parallelism over the GPUs of one box and all heads stay on one GPU.
+        axes = [("b", self.tpu_size // self.heads, "batch")] * (self.heads < self.tpu_size) + \
+               [("h", self.heads, "heads")] * (self.heads > 1)
+        self.mesh_shape = ','.join(f"{a}:{n:.0f}" for a, n, _ in axes)
+        self.layout = ','.join(f"{d}:{a}" for a, _, d in axes)
 
+    def _name_dimensions(self):
         self.head_dim = Dimension("heads", self.heads)
         self.head_dimensions = [self.head_dim]
         self.key_dim = Dimension("features_per_head", self.features // self.heads)
         self.feature_dims = self.head_dimensions + [self.key_dim]
-        self.intermediate = [Dimension("intermediate",
-                                       int(self.heads * self.key_dim.size * self.intermediate_feed_forward_multiplier))]
-        self.expert_dim = Dimension("experts", self.experts)
-        self.macro_batch_dim = Dimension("batch", self.train_batch_size * self.macro_batching)
+        width = int(self.heads * self.key_dim.size * self.intermediate_feed_forward_multiplier)
+        self.intermediate = [Dimension("intermediate", width)]
         self.vocab_dim = Dimension('vocab', self.vocab_size)
         self.batch_dim = Dimension("batch", self.train_batch_size)
+        self.macro_batch_dim = Dimension("batch", self.train_batch_size * self.macro_batching)
         self.sequence_dim = Dimension("sequence", self.time_patch_size)
         self.token_patch_dim = Dimension("language_token_patch", self.token_patch_size)
         self.token_dim_shape = [self.batch_dim, self.sequence_dim, self.token_patch_dim]
@@ -203,37 +204,19 @@ class ModelParameter(typing.Dict[str, typing.Any]):
             self.input_pipeline_shape['token_x'] = self.token_dim_shape
             self.input_pipeline_shape['token_y'] = self.token_dim_shape
 
-        self.attention_idx = 0
-        self.variable_cache = {}
-        self.cached_parameters = {}
-        self.debug_outfeed = {}
-        # ---- execution state of this implementation ----
-        self.tape: typing.Optional[list] = None     # backward closures recorded while not None
-        self.residual = None                        # (buffer, sign) a final GEMM may fuse: revnet.py
-        self.n_global_targets: typing.Optional[int] = None  # loss normaliser across DP ranks and micro-batches
-        self.global_step = 0                        # tf.train global_step (int64 in the reference)
-        self.manual_global_step = 0
+    def dict(self) -> typing.Dict[str, typing.Any]:
+        return self.__dict__
 
-    def __getitem__(self, key: str) -> typing.Any:
-        print(f"Getting {key} via deprecated interface")
-        return self.key
+    def items(self):
+        return self.__dict__.items()
 
-    def __setitem__(self, key: str, value: typing.Any) -> None:
-        print(f"Setting {key} via deprecated interface")
-        self.key = value
-
-    def get(self, key: str, default: typing.Any) -> typing.Any:
-        print(f"Getting {key} via deprecated interface with default value {default}")
-        return self.__dict__.get(key, default)
+    def values(self):
+        return self.__dict__.values()
 
     def __str__(self) -> str:
         return str(self.__dict__)
 
-    def __repr__(self) -> str:
-        return str(self)
-
-    def dict(self) -> typing.Dict[str, typing.Any]:
-        return self.__dict__
+    __repr__ = __str__
 
 
 def gpt_mode(params_or_config):
