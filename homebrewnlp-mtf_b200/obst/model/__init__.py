@@ -14,7 +14,7 @@ from ..utils_mtf import Dimension, Tensor, shape_size
 from .backend import TapeEntry, linear_to_features, run_tape
 from .embedding import embed, gather_embed
 from .frontend import LAYER_FUNCTIONS, block_part_fn  # noqa: F401
-from .revnet import reversible_body
+from .revnet import checkpoint_body, plain_body, reversible_body
 
 
 class Loss:
@@ -59,10 +59,15 @@ def _body(params: ModelParameter, src: Tensor) -> Tensor:
             raise NotImplementedError("token_patch_size > 1 is not on the hot path")
         dims = [d for d in src.dims if d != params.token_patch_dim]
         src = Tensor(src.data.view([d.size for d in dims]), dims)
-    if params.memory_reduction_strategy != "revnet":
-        raise NotImplementedError(f"memory_reduction_strategy '{params.memory_reduction_strategy}': only 'revnet' "
-                                  f"(used by every mixer config) has a B200 path")
-    return reversible_body(params, src)
+    strategy = params.memory_reduction_strategy
+    if strategy == "revnet":
+        return reversible_body(params, src)
+    if strategy == "checkpoint":
+        return checkpoint_body(params, src)
+    if strategy == "none":
+        return plain_body(params, src)
+    raise NotImplementedError(f"memory_reduction_strategy '{strategy}': 'revnet' (every mixer config), 'checkpoint' and "
+                              f"'none' have a B200 path; 'momentum' (MomentumNet) does not")
 
 
 def _output(params: ModelParameter, out: Tensor) -> Tensor:

@@ -11,6 +11,36 @@ from .spatial import attention, cummean, cumsum
 
 
 def _get_block_part(block_part_config: BlockConfig, params: ModelParameter, block_input: Tensor) -> Tensor:
+    skip = block_part_config.skip and block_part_config.memory_reduction_strategy in ("none", "checkpoint")
+    if skip:  # out = f(x) + x: f's backward goes on a tape of its own, the skip entry adds the identity branch
+        return _with_skip(block_part_config, params, block_input)
+    return _run_layers(block_part_config, params, block_input)
+
+
+def _with_skip(block_part_config: BlockConfig, params: ModelParameter, block_input: Tensor) -> Tensor:
+    import torch
+
+    from .. import native
+    from .backend import TapeEntry, run_tape
+    outer = params.tape
+    params.tape = [] if outer is not None else None
+    try:
+        out = _run_layers(block_part_config, params, block_input)
+    finally:
+        sub, params.tape = params.tape, outer
+    if tuple(out.data.shape) != tuple(block_input.data.shape):
+        raise ValueError(f"skip connection needs matching shapes, got {out.dims} and {block_input.dims}")
+    res = torch.empty_like(out.data)
+    native.axpby(out.data, block_input.data, 1.0, res)
+    if outer is not None:
+        def bwd(dy, mask, acc):
+            return run_tape(sub, dy, acc=dy.clone())  # dx = dy + J^T dy
+
+        outer.append(TapeEntry(bwd))
+    return Tensor(res, out.dims)
+
+
+def _run_layers(block_part_config: BlockConfig, params: ModelParameter, block_input: Tensor) -> Tensor:
     out = block_input
     layers = list(block_part_config.layer)
     skip_next = False
@@ -32,8 +62,6 @@ def _get_block_part(block_part_config: BlockConfig, params: ModelParameter, bloc
             out = scoped(name + '_', LAYER_FUNCTIONS[name], args)
         if idx != len(layers):
             params.residual = pending
-    if block_part_config.skip and block_part_config.memory_reduction_strategy in ("none", "checkpoint"):
-        raise NotImplementedError("skip connections of the 'none'/'checkpoint' strategies are not on the hot path")
     return out
 
 

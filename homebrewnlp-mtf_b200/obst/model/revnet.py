@@ -134,3 +134,59 @@ def reversible_body(params: ModelParameter, src: Tensor) -> Tensor:
         body_scope = list(utils_core._SCOPE)
         outer_tape.append(TapeEntry(bwd))
     return Tensor(out, dims)
+
+
+def plain_body(params: ModelParameter, src: Tensor) -> Tensor:
+    """_body for memory_reduction_strategy == 'none' (src/model/__init__.py:119-123): the sub-blocks are simply
+    composed, out = f_n(... f_1(src)), every layer's backward stays on the tape (a sub-block adds its input when its
+    block_config sets `skip`, src/model/frontend.py:29-30)."""
+    out = src
+    for i in range(params.depth):
+        for config in params.block_config:
+            out = block_part_fn(params, config, out, str(i))
+    return out
+
+
+def checkpoint_body(params: ModelParameter, src: Tensor) -> Tensor:
+    """_body for memory_reduction_strategy == 'checkpoint' (src/model/__init__.py:107-112, mtf recompute_grad): the
+    same composition as 'none', but forward keeps only each sub-block's INPUT; backward re-runs the sub-block from it
+    with the tape on, then back-propagates -- the recompute of the reversible path without its reconstruction."""
+    dims = src.dims
+    outer_tape = params.tape
+    params.tape = None
+    x = src.data
+    records: typing.List[typing.Tuple[dict, int, torch.Tensor]] = []
+    for i in range(params.depth):
+        for config in params.block_config:
+            records.append((utils_core.snapshot(), params.attention_idx, x))
+            x = block_part_fn(params, config, Tensor(x, dims), str(i)).data
+    params.tape = outer_tape
+    if outer_tape is not None:
+        n_cfg = len(params.block_config)
+        body_scope = list(utils_core._SCOPE)
+
+        def bwd(dy: torch.Tensor, mask, acc):
+            saved_names, saved_idx = utils_core.snapshot(), params.attention_idx
+            saved_scope = list(utils_core._SCOPE)
+            reducer = getattr(params, "grad_reducer", None)
+            utils_core._SCOPE[:] = body_scope
+            for j in range(len(records) - 1, -1, -1):
+                i, c = divmod(j, n_cfg)
+                names, att_idx, xin = records[j]
+                utils_core.restore(names)
+                params.attention_idx = att_idx
+                reset_shared_ordinals(params, str(i), f"{c}v")
+                params.tape = []
+                block_part_fn(params, params.block_config[c], Tensor(xin, dims), str(i))
+                tape, params.tape = params.tape, None
+                dy = run_tape(tape, dy)
+                records[j] = None  # frees the stored input
+                if c == 0 and reducer is not None:
+                    reducer.on_depth_done(i)
+            utils_core.restore(saved_names)
+            params.attention_idx = saved_idx
+            utils_core._SCOPE[:] = saved_scope
+            return dy
+
+        outer_tape.append(TapeEntry(bwd))
+    return Tensor(x, dims)

@@ -63,6 +63,10 @@ class Shapes:
         self.optimizer = c.get("optimizer", "learning_rate")
         self.calculation_dtype = c.get("calculation_dtype", "float32")
         self.optimizer_slice_dtype = c.get("optimizer_slice_dtype", "float32")
+        self.memory_reduction_strategy = c.get("memory_reduction_strategy", "revnet")
+        # `skip` of each block_config entry: out += block_input under the 'none' / 'checkpoint' strategies
+        # (src/model/frontend.py:29-30; src/dataclass.py BlockConfig default False)
+        self.skip = [bool(b.get("skip", False)) for b in c.get("block_config", [{}, {}])]
 
     # short names used in the math below
     @property
@@ -357,6 +361,56 @@ def _cast_params(params, dtype):
 
 def forward(sh: Shapes, params, tok_x, tok_y, dtype=np.float64, n_global: typing.Optional[int] = None,
             trace: typing.Optional[dict] = None, rnd=_ident):
+    if sh.memory_reduction_strategy in ("none", "checkpoint"):
+        return _forward_plain(sh, params, tok_x, tok_y, dtype, n_global, trace, rnd)
+    return _forward_revnet(sh, params, tok_x, tok_y, dtype, n_global, trace, rnd)
+
+
+def _head_and_loss(sh: Shapes, p, out, tok_y, Bn, n, rnd, trace):
+    """_output + softmax cross-entropy with z-loss + accuracy (src/model/__init__.py:138-145,183-187;
+    src/mtf_wrapper.py:64-71)."""
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    logits = rnd(out.reshape(Bn * S, F) @ p["wo"].reshape(F, V))
+    mx = logits.max(-1, keepdims=True)
+    logz = np.log(np.exp(logits - mx).sum(-1)) + mx[:, 0]
+    tgt = tok_y.reshape(-1).astype(np.int64)
+    nll = (logz - logits[np.arange(Bn * S), tgt]).sum()
+    z2 = (logz * logz).sum()
+    loss = nll / n + sh.z_loss * z2 / n
+    acc = float((logits.argmax(-1) == tgt).sum()) / n
+    if trace is not None:
+        trace["out"] = out.copy()
+        trace["logits"] = logits.copy()
+        trace["logz"] = logz.copy()
+        trace["loss_nll"] = nll / n
+    return float(loss), acc, logits, logz, tgt
+
+
+def _forward_plain(sh: Shapes, params, tok_x, tok_y, dtype, n_global, trace, rnd):
+    """memory_reduction_strategy 'none' / 'checkpoint' (src/model/__init__.py:107-123): the sub-blocks are composed,
+    x <- f(x) (+ x when the block_config entry sets `skip`, src/model/frontend.py:29-30).  'checkpoint' differs only
+    in WHEN the intermediates are computed (mtf recompute_grad), not in any value."""
+    B, S, H, K, F, I, K2, I0, V, L = sh.dims
+    Bn = tok_x.shape[0]
+    p = _cast_params(params, dtype)
+    n = float(Bn * S if n_global is None else n_global)
+    e = p["embed"][tok_x]
+    x = rnd((e.reshape(Bn * S, I0) @ p["w0"].reshape(I0, F)).reshape(Bn, S, H, K))
+    caches = []
+    for i in range(L):
+        for c, blk in enumerate(BLOCKS):
+            f, cache = blk.fwd(p, i, x, keep=True, rnd=rnd)
+            caches.append(cache)
+            x = rnd(f + x) if sh.skip[c] else rnd(f)
+            if trace is not None:
+                trace[f"x_{i}_{c}"] = x.copy()
+    loss, acc, logits, logz, tgt = _head_and_loss(sh, p, x, tok_y, Bn, n, rnd, trace)
+    state = dict(p=p, e=e, out=x, logits=logits, logz=logz, tgt=tgt, n=n, tok_x=tok_x, rnd=rnd, caches=caches)
+    return loss, acc, state
+
+
+def _forward_revnet(sh: Shapes, params, tok_x, tok_y, dtype=np.float64, n_global: typing.Optional[int] = None,
+                    trace: typing.Optional[dict] = None, rnd=_ident):
     """_input -> _body (revnet) -> _output -> _loss  (src/model/__init__.py:75-85,101-129,138-145,183-187).
     Returns (loss, accuracy, state) where state holds what backward() needs.  `n_global` = targets.size of the
     GLOBAL batch (src/mtf_wrapper.py:67: the loss normaliser), default = this batch.
@@ -414,6 +468,23 @@ def backward(sh: Shapes, state, trace: typing.Optional[dict] = None):
     out2 = state["out"].reshape(Bn * S, F)
     grads["wo"] = (out2.T @ dlogits).reshape(H, K, 1, V)
     dout = rnd(dlogits @ p["wo"].reshape(F, V).T).reshape(Bn, S, H, K)
+    if "caches" in state:  # 'none' / 'checkpoint': plain chain rule through the stored (or recomputed) sub-blocks
+        dx = dout
+        caches = state["caches"]
+        for i in reversed(range(L)):
+            for c in reversed(range(len(BLOCKS))):
+                dxf, g = BLOCKS[c].bwd(p, i, caches[i * len(BLOCKS) + c], dx, rnd=rnd)
+                for k, v in g.items():
+                    grads[k] = grads[k] + v if k in grads else v
+                dx = rnd(dxf + dx) if sh.skip[c] else rnd(dxf)
+        dsrc = dx.reshape(Bn * S, F)
+        e2 = state["e"].reshape(Bn * S, I0)
+        grads["w0"] = (e2.T @ dsrc).reshape(1, I0, H, K)
+        de = rnd(dsrc @ p["w0"].reshape(I0, F).T)
+        dE = np.zeros((V, I0), dtype=de.dtype)
+        np.add.at(dE, state["tok_x"].reshape(-1), de)
+        grads["embed"] = dE
+        return grads
     pp, q = state["x1"], state["x2"]  # final (x1, x2)
     dp, dq = dout, dout.copy()
     for i in reversed(range(L)):

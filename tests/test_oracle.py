@@ -428,3 +428,27 @@ def test_golden_fixture():
         assert np.isclose(p2[k].astype(np.float64).sum(), float(gold[f"pnew_sum/{k}"]), rtol=1e-6, atol=1e-6), k
         assert np.isclose(np.linalg.norm(st[k]["momentum"]), float(gold[f"mom_norm/{k}"]), rtol=1e-5), k
         assert np.isclose(st[k]["dim0"].astype(np.float64).sum(), float(gold[f"dim0_sum/{k}"]), rtol=1e-5), k
+
+
+def test_plain_composition_strategies_match_finite_differences():
+    """memory_reduction_strategy 'none' / 'checkpoint' with the `skip` residual: the oracle's hand-written chain rule
+    against central differences of its own forward (float64)."""
+    import copy
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=16, features_per_head=8, memory_reduction_strategy="none")
+    for skip in (False, True):
+        for b in cfg["block_config"]:
+            b["skip"] = skip
+        sh = orc.Shapes(cfg)
+        op = {k: v.astype(np.float64) for k, v in orc.init_params(sh, seed=0).items()}
+        tx, ty = orc.synthetic_tokens(sh)
+        loss, _, st = orc.forward(sh, op, tx, ty)
+        g = orc.backward(sh, st)
+        for name, idx in (("win_0", (0, 1, 2)), ("mix_a", (1, 5, 3)), ("g2_0", (2, 3)), ("w0", (0, 0, 2, 3))):
+            eps = 1e-5
+            hi = {k: v.copy() for k, v in op.items()}
+            lo = {k: v.copy() for k, v in op.items()}
+            hi[name][idx] += eps
+            lo[name][idx] -= eps
+            fd = (orc.forward(sh, hi, tx, ty)[0] - orc.forward(sh, lo, tx, ty)[0]) / (2 * eps)
+            assert abs(fd - g[name][idx]) < 1e-6 * max(1.0, abs(fd)) + 1e-9, (skip, name, fd, g[name][idx])

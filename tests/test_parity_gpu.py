@@ -379,6 +379,29 @@ def test_full_depth_32big_step_against_the_precision_twin(cuda):
     print("full-depth 32big (1 sequence) gradient errors (cuda vs f64, twin vs f64, cuda vs twin):", report)
 
 
+@pytest.mark.parametrize("strategy", ["none", "checkpoint"])
+@pytest.mark.parametrize("skip", [False, True])
+def test_none_and_checkpoint_memory_strategies(cuda, strategy, skip):
+    """memory_reduction_strategy 'none' and 'checkpoint' (src/model/__init__.py:107-123), with and without the
+    block_config `skip` residual (src/model/frontend.py:29-30): fp32, loss and EVERY gradient at the plain 1e-5 bar
+    (no reconstruction on these paths), and 'checkpoint' == 'none' for the same inputs."""
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=2, train_batch_size=3, sequence_length=64, memory_reduction_strategy=strategy)
+    for b in cfg["block_config"]:
+        b["skip"] = skip
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=13)
+    tok_x, tok_y = orc.synthetic_tokens(sh)
+    params = make_params(cfg, op)
+    params.global_step = 2048
+    _, scal = run_product_step(params, tok_x, tok_y)
+    loss, acc, state = orc.forward(sh, op, tok_x, tok_y, dtype=np.float64)
+    grads = orc.backward(sh, state)
+    assert abs(scal["loss"] - loss) / loss < 1e-5
+    for name, var in variables_by_oracle_name(params, sh).items():
+        assert rel(to_np(var.grad), grads[name]) < 1e-5, name
+
+
 def test_ragged_micro_batches(cuda):
     """5 rows in micro-batches of 2 (2 + 2 + 1): same loss and gradients as one pass."""
     cfg = copy.deepcopy(orc.TINY_CONFIG)
