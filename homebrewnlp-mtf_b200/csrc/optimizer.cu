@@ -49,21 +49,24 @@ __global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* _
   const int64_t e0 = (int64_t)item_row0[item] * cols;
   const int64_t n = (int64_t)item_rows[item] * cols;
   const float* __restrict__ p = T.p + e0;
-  double sg = 0.0, sw = 0.0;
+  double sg = 0.0, sg2 = 0.0, sw = 0.0;
   const bool g_is_bf16_value = T.g_bf16 || grad_bf16;
   if (!skip_g) {
     if (T.g_bf16) {
       const bf16* __restrict__ g = reinterpret_cast<const bf16*>(T.g) + e0;
       const bool vec_ok = ((e0 & 7) == 0);
       const int64_t nv = vec_ok ? n / 8 : 0;
+#pragma unroll 4
       for (int64_t i = threadIdx.x; i < nv; i += blockDim.x) {
         const uint4 q = reinterpret_cast<const uint4*>(g)[i];
         const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const double lo = bf16_bits_to_double(w[j] << 16), hi = bf16_bits_to_double(w[j] & 0xFFFF0000u);
-          sg = fma(lo, lo, sg);  // exact products of 8-bit significands
-          sg = fma(hi, hi, sg);
+          // the square of a bf16 value is exact in fp32; the squares are summed in float64 (two accumulators
+          // shorten the dependent chain)
+          const float lo = __uint_as_float(w[j] << 16), hi = __uint_as_float(w[j] & 0xFFFF0000u);
+          sg += (double)__fmul_rn(lo, lo);
+          sg2 += (double)__fmul_rn(hi, hi);
         }
       }
       for (int64_t i = nv * 8 + threadIdx.x; i < n; i += blockDim.x) sg += square_as_double(to_f32(g[i]), true);
@@ -81,7 +84,7 @@ __global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* _
       sw += square_as_double(ww, act_bf16 != 0);
     }
   }
-  const double dg = warp_sum_d(sg), dw = warp_sum_d(sw);
+  const double dg = warp_sum_d(sg + sg2), dw = warp_sum_d(sw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) {
     s_part[0][warp] = dg;

@@ -59,8 +59,9 @@ __device__ __forceinline__ void st4(bf16* d, const float (&v)[4]) {
   *reinterpret_cast<uint2*>(d) = t;
 }
 
-// TS = state dtype (momentum / accumulators), TG = gradient storage dtype, RING = rows in flight per warp + 1
-template <typename TS, typename TG, int RING>
+// TS = state dtype (momentum / accumulators), TG = gradient storage dtype, RING = rows in flight per warp + 1,
+// ACT_BF16 = the graph reads the weights through a bf16 cast (else fp32)
+template <typename TS, typename TG, int RING, bool ACT_BF16>
 __global__ void __launch_bounds__(RWARPS * 32, 2) opt_update_ring_kernel(const obst_opt_tensor* __restrict__ table,
                                                                        const int32_t* __restrict__ item_tensor,
                                                                        const int32_t* __restrict__ item_row0,
@@ -155,39 +156,90 @@ __global__ void __launch_bounds__(RWARPS * 32, 2) opt_update_ring_kernel(const o
 #pragma unroll
     for (int k = 0; k < RG; ++k) {
       if (!live[k]) continue;
-      float pv[4], gv[4], mv[4], pn[4], mn[4], sh[4];
+      float pv[4], g[4], mv[4], pn[4], mn[4], u[4];
       ld4(reinterpret_cast<const float*>(src + k * 512) + lane * 4, pv);
-      ld4(reinterpret_cast<const TG*>(src + P_BYTES) + k * 128 + lane * 4, gv);
+      ld4(reinterpret_cast<const TG*>(src + P_BYTES) + k * 128 + lane * 4, g);
       ld4(reinterpret_cast<const TS*>(src + P_BYTES + G_BYTES) + k * 128 + lane * 4, mv);
       const int64_t e = rbase + k * 128;
+      // Every per-launch / per-tensor option below is a warp-uniform branch around a 4-element loop, never a test
+      // inside one: the kernel is instruction-issue bound (about 40 instructions per element remain, half of them the
+      // two correctly rounded special functions).
+      if (sizeof(TG) == 4 && hp.grad_bf16) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g[j] = round_to<bf16>(g[j]);
+      }
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        float g = gv[j];
-        if (sizeof(TG) == 4 && hp.grad_bf16) g = round_to<bf16>(g);
-        g = __fmul_rn(g, scale);
-        const float w = hp.act_bf16 ? round_to<bf16>(pv[j]) : pv[j];
-        const OptElemOut o = opt_element(g, fminf(rowmin, al[k][j]), mv[j], pv[j], w, hp, wd_on);
-        cm[k][j] = fmaxf(cm[k][j], o.nu);
-        rowmax = fmaxf(rowmax, o.nu);
-        pn[j] = o.p_new;
-        mn[j] = o.m_new;
-        sh[j] = o.p_new;
-        if (tril_fast) {
-          if (cbase + k * 128 + lane * 4 + j > row_in) sh[j] = 0.f;
-        } else if (tril_s > 0) {
-          const int64_t ee = e + j;
-          const int col = (int)(ee % tril_s);
-          const int row = (int)((ee / tril_s) % tril_s);
-          if (col > row) sh[j] = 0.f;
-        }
-        if (!preview) {
-          const float wv = hp.act_bf16 ? round_to<bf16>(o.p_new) : o.p_new;
-          w2 = add_square(w2, wv, hp.act_bf16 != 0);
+        g[j] = __fmul_rn(g[j], scale);
+        const float nu = __fadd_rn(fminf(rowmin, al[k][j]), __fmul_rn(g[j], g[j]));  // optimizers.py:70
+        cm[k][j] = fmaxf(cm[k][j], nu);
+        rowmax = fmaxf(rowmax, nu);
+        u[j] = __fmul_rn(g[j], __frcp_rn(fmaxf(__fsqrt_rn(nu), 1e-5f)));             // g * opt_rsqrt(nu)
+        mn[j] = __fadd_rn(__fmul_rn(hp.beta, mv[j]), u[j]);                          // optimizers.py:124
+      }
+      if (hp.nesterov) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) u[j] = __fadd_rn(u[j], __fmul_rn(hp.beta, mn[j]));  // :126-128
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) u[j] = mn[j];
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) u[j] = __fmul_rn(u[j], hp.lr);                     // :114-115
+      if (wd_on) {                                                                   // __init__.py:59-61
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float w = ACT_BF16 ? round_to<bf16>(pv[j]) : pv[j];
+          u[j] = __fadd_rn(u[j], __fmul_rn(__fmul_rn(w, hp.lr), hp.weight_decay));
         }
       }
-      if (Tshadow) {
-        if (hp.act_bf16) st4(reinterpret_cast<bf16*>(Tshadow) + e, sh);
-        else st4(reinterpret_cast<float*>(Tshadow) + e, sh);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) pn[j] = __fsub_rn(pv[j], u[j]);                    // assign_sub, __init__.py:64
+      // the shadow: the new master in the activation dtype; its (unmasked) bf16 values also feed the weight norm
+      if (ACT_BF16) {
+        uint2 sb;
+        sb.x = pack_bf16x2(pn[0], pn[1]);
+        sb.y = pack_bf16x2(pn[2], pn[3]);
+        if (!preview) {
+          const float w0 = __uint_as_float(sb.x << 16), w1 = __uint_as_float(sb.x & 0xFFFF0000u);
+          const float w2a = __uint_as_float(sb.y << 16), w3 = __uint_as_float(sb.y & 0xFFFF0000u);
+          // squares of bf16 values are exact in fp32; they are summed in float64
+          w2 += (double)__fmul_rn(w0, w0);
+          w2 += (double)__fmul_rn(w1, w1);
+          w2 += (double)__fmul_rn(w2a, w2a);
+          w2 += (double)__fmul_rn(w3, w3);
+        }
+        if (tril_s > 0) {  // causal mask of a mixing map: entries above the diagonal read as zero
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            bool masked;
+            if (tril_fast) {
+              masked = cbase + k * 128 + lane * 4 + j > row_in;
+            } else {
+              const int64_t ee = e + j;
+              masked = (int)(ee % tril_s) > (int)((ee / tril_s) % tril_s);
+            }
+            if (masked) {
+              if (j == 0) sb.x &= 0xFFFF0000u;
+              if (j == 1) sb.x &= 0x0000FFFFu;
+              if (j == 2) sb.y &= 0xFFFF0000u;
+              if (j == 3) sb.y &= 0x0000FFFFu;
+            }
+          }
+        }
+        if (Tshadow) *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(Tshadow) + e) = sb;
+      } else {
+        float sh[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          sh[j] = pn[j];
+          if (!preview) w2 += (double)__fmul_rn(pn[j], pn[j]);
+          if (tril_s > 0) {
+            const int64_t ee = e + j;
+            if ((int)(ee % tril_s) > (int)((ee / tril_s) % tril_s)) sh[j] = 0.f;
+          }
+        }
+        if (Tshadow) st4(reinterpret_cast<float*>(Tshadow) + e, sh);
       }
       if (!preview) {
         st4(Tp + e, pn);
@@ -232,8 +284,11 @@ static int ring_launch_typed(const obst_opt_tensor* table, const int32_t* item_t
   constexpr int SMEM = STAGE * RING * RWARPS;
   static bool attr = false;
   if (!attr) {
-    cudaError_t e = cudaFuncSetAttribute(opt_update_ring_kernel<TS, TG, RING>,
+    cudaError_t e = cudaFuncSetAttribute(opt_update_ring_kernel<TS, TG, RING, true>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(opt_update_ring_kernel<TS, TG, RING, false>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
     if (e != cudaSuccess) {
       set_error("obst_opt_update: cannot opt in to %d B of shared memory: %s", SMEM, cudaGetErrorString(e));
       return OBST_ECUDA;
@@ -243,8 +298,12 @@ static int ring_launch_typed(const obst_opt_tensor* table, const int32_t* item_t
   const int64_t ychunks = ((int64_t)max_cols + RCHUNK - 1) / RCHUNK;
   OBST_REQUIRE(ychunks <= 65535, "obst_opt_update: last dim %d too large (max %d)", max_cols, 65535 * RCHUNK);
   const dim3 grid((unsigned)nitems, (unsigned)ychunks);
-  opt_update_ring_kernel<TS, TG, RING><<<grid, RWARPS * 32, SMEM, st>>>(table, item_tensor, item_row0, item_rows,
-                                                                         norms, hp, wnext);
+  if (hp.act_bf16)
+    opt_update_ring_kernel<TS, TG, RING, true><<<grid, RWARPS * 32, SMEM, st>>>(table, item_tensor, item_row0,
+                                                                                 item_rows, norms, hp, wnext);
+  else
+    opt_update_ring_kernel<TS, TG, RING, false><<<grid, RWARPS * 32, SMEM, st>>>(table, item_tensor, item_row0,
+                                                                                  item_rows, norms, hp, wnext);
   count_launch();
   count_path(OBST_PATH_OPT_RING);
   return check_launch("obst_opt_update");
@@ -267,12 +326,16 @@ int opt_update_ring_launch(const obst_opt_tensor* table, const int32_t* item_ten
 }
 
 // ------------------------------------------------------------------------------------------------
-// every transposed weight shadow in one launch: one block per 32 x 32 tile of any of the matrices
+// every transposed weight shadow in one launch: one block per 64 x 64 tile of any of the matrices
 // ------------------------------------------------------------------------------------------------
+// 16-bit elements move as 16-byte words on both sides (a 64-wide tile row is one full 128-byte line); other cases
+// (fp32, odd sizes, unaligned bases) take the element-wise path of the same kernel.
+static constexpr int TT = 64;
+
 template <typename T>
 __global__ void __launch_bounds__(256) transpose_batched_kernel(const obst_transpose_item* __restrict__ items,
                                                                  int nitems) {
-  __shared__ T tile[32][33];
+  __shared__ T tile[TT][TT + 2];
   // which item owns this tile: binary search in the exclusive prefix sums
   int lo = 0, hi = nitems - 1;
   const int tile_id = blockIdx.x;
@@ -282,7 +345,7 @@ __global__ void __launch_bounds__(256) transpose_batched_kernel(const obst_trans
     else hi = mid - 1;
   }
   const obst_transpose_item it = items[lo];
-  const int tiles_c = (it.cols + 31) / 32, tiles_r = (it.rows + 31) / 32;
+  const int tiles_c = (it.cols + TT - 1) / TT, tiles_r = (it.rows + TT - 1) / TT;
   int local = tile_id - it.tile0;
   const int tc = local % tiles_c;
   local /= tiles_c;
@@ -291,18 +354,50 @@ __global__ void __launch_bounds__(256) transpose_batched_kernel(const obst_trans
   if (b >= it.batch) return;
   const T* __restrict__ src = reinterpret_cast<const T*>(it.src) + (int64_t)b * it.rows * it.cols;
   T* __restrict__ dst = reinterpret_cast<T*>(it.dst) + (int64_t)b * it.rows * it.cols;
-  const int c0 = tc * 32, r0 = tr * 32;
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = tc * TT, r0 = tr * TT;
+  const bool fast = sizeof(T) == 2 && (it.rows % 8 == 0) && (it.cols % 8 == 0) &&
+                    ((reinterpret_cast<uintptr_t>(it.src) | reinterpret_cast<uintptr_t>(it.dst)) & 15) == 0;
+  if (fast) {
+    const int chunk = threadIdx.x & 7, rr = threadIdx.x >> 3;  // 8 chunks of 8 elements per tile row, 32 rows a pass
 #pragma unroll
-  for (int i = 0; i < 32; i += 8) {
-    const int r = r0 + ty + i, c = c0 + tx;
-    if (r < it.rows && c < it.cols) tile[ty + i][tx] = src[(int64_t)r * it.cols + c];
+    for (int pass = 0; pass < 2; ++pass) {
+      const int r = r0 + rr + 32 * pass, c = c0 + chunk * 8;
+      if (r < it.rows && c < it.cols) {
+        const uint4 v = *reinterpret_cast<const uint4*>(src + (int64_t)r * it.cols + c);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        uint16_t* trow = reinterpret_cast<uint16_t*>(&tile[rr + 32 * pass][chunk * 8]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          trow[2 * j] = (uint16_t)(w[j] & 0xFFFFu);
+          trow[2 * j + 1] = (uint16_t)(w[j] >> 16);
+        }
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int pass = 0; pass < 2; ++pass) {
+      const int c = c0 + rr + 32 * pass, r = r0 + chunk * 8;  // output row c, 8 consecutive source rows
+      if (c < it.cols && r < it.rows) {
+        uint32_t w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint16_t a = *reinterpret_cast<const uint16_t*>(&tile[chunk * 8 + 2 * j][rr + 32 * pass]);
+          const uint16_t bb = *reinterpret_cast<const uint16_t*>(&tile[chunk * 8 + 2 * j + 1][rr + 32 * pass]);
+          w[j] = (uint32_t)a | ((uint32_t)bb << 16);
+        }
+        *reinterpret_cast<uint4*>(dst + (int64_t)c * it.rows + r) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+    return;
+  }
+  for (int i = threadIdx.x; i < TT * TT; i += blockDim.x) {
+    const int r = r0 + i / TT, c = c0 + i % TT;
+    if (r < it.rows && c < it.cols) tile[i / TT][i % TT] = src[(int64_t)r * it.cols + c];
   }
   __syncthreads();
-#pragma unroll
-  for (int i = 0; i < 32; i += 8) {
-    const int c = c0 + ty + i, r = r0 + tx;
-    if (r < it.rows && c < it.cols) dst[(int64_t)c * it.rows + r] = tile[tx][ty + i];
+  for (int i = threadIdx.x; i < TT * TT; i += blockDim.x) {
+    const int c = c0 + i / TT, r = r0 + i % TT;
+    if (r < it.rows && c < it.cols) dst[(int64_t)c * it.rows + r] = tile[i % TT][i / TT];
   }
 }
 

@@ -69,12 +69,35 @@ def attention(args: BlockArgs) -> Tensor:
     return Tensor(out, x.dims)
 
 
-def _unsupported(name):
-    def fn(args: BlockArgs) -> Tensor:
-        raise NotImplementedError(f"layer '{name}' is registered by the reference but is outside the mixer hot path")
+def _running_sum(args: BlockArgs, mean: bool) -> Tensor:
+    """cumsum / cummean along the attention dim (src/model/spatial.py:26-39): out[s] = sum_{t<=s} x[t] (divided by
+    s + 1 for cummean); gradient = the reverse running sum of dy (of dy / (t + 1) for cummean)."""
+    x = args.tensor
+    dim = get_attention_dim(args).dim
+    idx = x.dims.index(dim)
+    outer = 1
+    for d in x.dims[:idx]:
+        outer *= d.size
+    inner = 1
+    for d in x.dims[idx + 1:]:
+        inner *= d.size
+    seq = dim.size
+    xin = x.data.contiguous()
+    out = torch.empty_like(xin)
+    native.cumsum(xin, out, outer, seq, inner, reverse=False, scale=1 if mean else 0)
+    if args.params.tape is not None:
+        def bwd(dy, mask, acc):
+            dx = torch.empty_like(xin)
+            native.cumsum(dy.contiguous(), dx, outer, seq, inner, reverse=True, scale=2 if mean else 0)
+            return dx
 
-    return fn
+        args.params.tape.append(TapeEntry(bwd))
+    return Tensor(out, x.dims)
 
 
-cumsum = _unsupported('cumsum')
-cummean = _unsupported('cummean')
+def cumsum(args: BlockArgs) -> Tensor:
+    return _running_sum(args, False)
+
+
+def cummean(args: BlockArgs) -> Tensor:
+    return _running_sum(args, True)

@@ -74,6 +74,14 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_gate_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_gate_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_axpby": (c_int, [c_int, c_void_p, c_void_p, c_float, c_void_p, c_i64, c_void_p]),
+    "obst_sum_heads": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
+    "obst_broadcast_heads": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
+    "obst_swap_axes": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_i32, c_void_p]),
+    "obst_mul": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
+    "obst_scale": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
+    "obst_dot_accumulate": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
+    "obst_dropout": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_float, ctypes.c_uint64, c_void_p]),
+    "obst_cumsum": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_i64, c_i32, c_i32, c_void_p]),
     "obst_embed_gather": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
     "obst_embed_scatter_add": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
     "obst_xent_fwd_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_float, c_float,
@@ -270,6 +278,56 @@ def gate_bwd(a, b, dy, da, db):
 def axpby(a, b, sign: float, out):
     _cuda(a, b, out)
     check(load().obst_axpby(dtype_code(a.dtype), _p(a), _p(b), sign, _p(out), a.numel(), stream_ptr()), "obst_axpby")
+
+
+def sum_heads(x, out, rows: int, heads: int, width: int):
+    _cuda(x, out)
+    check(load().obst_sum_heads(dtype_code(x.dtype), _p(x), _p(out), rows, heads, width, stream_ptr()), "obst_sum_heads")
+
+
+def broadcast_heads(dy, dx, rows: int, heads: int, width: int):
+    _cuda(dy, dx)
+    check(load().obst_broadcast_heads(dtype_code(dy.dtype), _p(dy), _p(dx), rows, heads, width, stream_ptr()),
+          "obst_broadcast_heads")
+
+
+def swap_axes(x, out, outer: int, a: int, mid: int, b: int):
+    _cuda(x, out)
+    check(load().obst_swap_axes(dtype_code(x.dtype), _p(x), _p(out), outer, a, mid, b, stream_ptr()), "obst_swap_axes")
+
+
+def mul(a, b, out):
+    _cuda(a, b, out)
+    check(load().obst_mul(dtype_code(a.dtype), _p(a), _p(b), _p(out), a.numel(), stream_ptr()), "obst_mul")
+
+
+def scale(x, scalar, out):
+    _cuda(x, scalar, out)
+    check(load().obst_scale(dtype_code(x.dtype), _p(x), _p(scalar), _p(out), x.numel(), stream_ptr()), "obst_scale")
+
+
+def dot_accumulate(a, b, out):
+    """out[0] (fp32) += sum(a * b)"""
+    _cuda(a, b, out)
+    if out.dtype != torch.float32:
+        raise NativeError("dot_accumulate: the accumulator must be fp32")
+    check(load().obst_dot_accumulate(dtype_code(a.dtype), _p(a), _p(b), _p(out), a.numel(), stream_ptr()),
+          "obst_dot_accumulate")
+
+
+def dropout(x, out, keep: float, seed: int):
+    _cuda(x, out)
+    check(load().obst_dropout(dtype_code(x.dtype), _p(x), _p(out), x.numel(), float(keep), int(seed) & (2 ** 64 - 1),
+                              stream_ptr()), "obst_dropout")
+
+
+def cumsum(x, out, outer: int, seq: int, inner: int, reverse: bool = False, scale: int = 0):
+    """Running sum along the middle axis of [outer, seq, inner] (obst_cumsum)."""
+    _cuda(x, out)
+    if x.data_ptr() == out.data_ptr():
+        raise NativeError("cumsum: in-place operation is not supported")
+    check(load().obst_cumsum(dtype_code(x.dtype), _p(x), _p(out), outer, seq, inner, int(reverse), scale, stream_ptr()),
+          "obst_cumsum")
 
 
 def embed_gather(idx, table, out):

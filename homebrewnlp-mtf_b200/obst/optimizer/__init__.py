@@ -217,7 +217,7 @@ class FusedOptimizer:
                 batch, rows, cols = v._t_view
                 it.src, it.dst = a.data_ptr(), b.data_ptr()
                 it.batch, it.rows, it.cols, it.tile0 = batch, rows, cols, tiles
-                tiles += batch * (-(-rows // 32)) * (-(-cols // 32))
+                tiles += batch * (-(-rows // 64)) * (-(-cols // 64))
             self._t_table = torch.frombuffer(bytearray(bytes(items)), dtype=torch.uint8).to(self.table.device)
             self._t_sig, self._t_tiles, self._t_n = sig, tiles, len(pairs)
         native.check(native.load().obst_transpose_batched(native.dtype_code(self.act_dtype), self._t_table.data_ptr(),

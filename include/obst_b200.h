@@ -141,6 +141,35 @@ int obst_gate_fwd(int dtype, const void* a, const void* b, void* out, int64_t n,
 int obst_gate_bwd(int dtype, const void* a, const void* b, const void* dy, void* da, void* db,
                   int64_t n, void* stream);
 
+/* ---- running sums along the sequence axis, src/model/spatial.py:26-39 ------------------------------
+ * x, out: AT [outer, seq, inner], inner contiguous (a multiple of 8 bf16 / 4 fp32), x != out.
+ *   reverse == 0: out[o,s,:] = sum_{t<=s} x[o,t,:]   (cumsum; tf.cumsum)
+ *   reverse != 0: out[o,s,:] = sum_{t>=s} x[o,t,:]   (its gradient, _cumsum_grad: tf.cumsum(reverse=True))
+ *   scale 1: the sum is divided by (s + 1) on the way out   (cummean = cumsum / (1 + range), spatial.py:37-39)
+ *   scale 2: x[o,t,:] is divided by (t + 1) on the way in    (cummean's gradient, with reverse != 0)
+ * The running sum is kept in fp32. */
+int obst_cumsum(int dtype, const void* x, void* out, int64_t outer, int32_t seq, int64_t inner,
+                int32_t reverse, int32_t scale, void* stream);
+
+/* ---- registered layers off the mixer hot path ---------------------------------
+ * sum_heads (src/model/basic.py:77-78): out[r,w] = sum_h x[r,h,w]; its gradient broadcasts back. */
+int obst_sum_heads(int dtype, const void* x, void* out, int64_t rows, int32_t heads, int32_t width, void* stream);
+int obst_broadcast_heads(int dtype, const void* dy, void* dx, int64_t rows, int32_t heads, int32_t width,
+                         void* stream);
+/* transpose_sequence_features (src/model/basic.py:81-86): x [outer, a, mid, b] -> out [outer, b, mid, a] with
+ * out[o,j,m,i] = x[o,i,m,j] (x != out).  The gradient is the same call with a and b exchanged. */
+int obst_swap_axes(int dtype, const void* x, void* out, int64_t outer, int32_t a, int32_t mid, int32_t b,
+                   void* stream);
+/* element-wise product (split_path's `multiply`, src/model/frontend.py:39-55); out may alias a or b. */
+int obst_mul(int dtype, const void* a, const void* b, void* out, int64_t n, void* stream);
+/* rezero (src/model/basic.py:21-22): out = x * scalar[0] (scalar: AT, one element in device memory); the scalar's
+ * gradient is obst_dot_accumulate(x, dy): out[0] += sum_i a[i] * b[i] in fp32. */
+int obst_scale(int dtype, const void* x, const void* scalar, void* out, int64_t n, void* stream);
+int obst_dot_accumulate(int dtype, const void* a, const void* b, float* out, int64_t n, void* stream);
+/* dropout (src/model/basic.py:25-30 -> mtf.dropout): out = x * [u_i < keep] / keep with u_i a counter-based
+ * uniform of (seed, i); calling it on dy with the same seed applies the same mask (the backward). */
+int obst_dropout(int dtype, const void* x, void* out, int64_t n, float keep, uint64_t seed, void* stream);
+
 /* ---- residual stream arithmetic, src/model/revnet.py:23,89,120; src/model/__init__.py:129 ------
  * out = a + sign*b (sign = +1 or -1), all AT, n elements; out may alias a or b. */
 int obst_axpby(int dtype, const void* a, const void* b, float sign, void* out, int64_t n,
@@ -255,8 +284,8 @@ int obst_opt_finalize(const obst_opt_tensor* table, int32_t ntensors, int32_t dt
 
 /* Batched form of obst_transpose_param: every transposed weight shadow in one launch.  items: DEVICE
  * array; item i is `batch` row-major [rows, cols] matrices at src, written as [cols, rows] at dst;
- * tile0 = number of 32x32 tiles of all earlier items (exclusive prefix sum of
- * batch * ceil(rows/32) * ceil(cols/32)); total_tiles = that sum over all items. */
+ * tile0 = number of 64x64 tiles of all earlier items (exclusive prefix sum of
+ * batch * ceil(rows/64) * ceil(cols/64)); total_tiles = that sum over all items. */
 typedef struct obst_transpose_item {
   const void* src;
   void* dst;

@@ -270,6 +270,27 @@ def mix_bwd(m_tril, x, do):
     return dx, np.tril(dm)
 
 
+def cumsum_fwd(x, axis: int = 1, mean: bool = False):
+    """cumsum / cummean (src/model/spatial.py:26-39): tf.cumsum along the attention dim; cummean divides by
+    1 + range(dim)."""
+    out = np.cumsum(x, axis=axis)
+    if mean:
+        shape = [1] * x.ndim
+        shape[axis] = -1
+        out = out / (1.0 + np.arange(x.shape[axis], dtype=x.dtype)).reshape(shape)
+    return out
+
+
+def cumsum_bwd(dy, axis: int = 1, mean: bool = False):
+    """_cumsum_grad (src/model/spatial.py:26-28): tf.cumsum(dy, reverse=True); for cummean the division is
+    differentiated first."""
+    if mean:
+        shape = [1] * dy.ndim
+        shape[axis] = -1
+        dy = dy / (1.0 + np.arange(dy.shape[axis], dtype=dy.dtype)).reshape(shape)
+    return np.flip(np.cumsum(np.flip(dy, axis), axis=axis), axis)
+
+
 def _ident(x):
     return x
 

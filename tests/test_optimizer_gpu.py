@@ -198,7 +198,7 @@ def test_transpose_batched(nat):
     tiles = 0
     for it, s, a, b in zip(items, shapes, src, dst):
         it.src, it.dst, it.batch, it.rows, it.cols, it.tile0 = a.data_ptr(), b.data_ptr(), s[0], s[1], s[2], tiles
-        tiles += s[0] * (-(-s[1] // 32)) * (-(-s[2] // 32))
+        tiles += s[0] * (-(-s[1] // 64)) * (-(-s[2] // 64))
     table = torch.frombuffer(bytearray(bytes(items)), dtype=torch.uint8).to(DEV)
     nat.check(nat.load().obst_transpose_batched(nat.BF16, table.data_ptr(), len(shapes), tiles, nat.stream_ptr()),
               "obst_transpose_batched")

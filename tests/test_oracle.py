@@ -452,3 +452,17 @@ def test_plain_composition_strategies_match_finite_differences():
             lo[name][idx] -= eps
             fd = (orc.forward(sh, hi, tx, ty)[0] - orc.forward(sh, lo, tx, ty)[0]) / (2 * eps)
             assert abs(fd - g[name][idx]) < 1e-6 * max(1.0, abs(fd)) + 1e-9, (skip, name, fd, g[name][idx])
+
+
+def test_cumsum_and_cummean_gradients_against_autograd():
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((2, 7, 3, 4))
+    dy = rng.standard_normal((2, 7, 3, 4))
+    for mean in (False, True):
+        xt = torch.from_numpy(x).requires_grad_(True)
+        yt = torch.cumsum(xt, 1)
+        if mean:
+            yt = yt / (1 + torch.arange(7, dtype=torch.float64)).view(1, 7, 1, 1)
+        yt.backward(torch.from_numpy(dy))
+        assert np.allclose(orc.cumsum_fwd(x, 1, mean), yt.detach().numpy(), atol=1e-12)
+        assert np.allclose(orc.cumsum_bwd(dy, 1, mean), xt.grad.numpy(), atol=1e-12)

@@ -693,3 +693,35 @@ def test_feed_forward_layer_with_glu_variants(cuda, layer, act, glu):
     assert rel(to_np(dx).reshape(-1, F), dx_ref) < 1e-5
     for v, g in zip(variables, g_in + g_out):
         assert rel(to_np(v.grad).reshape(g.shape), g) < 1e-5, v.name
+
+
+@pytest.mark.parametrize("layer", ["cumsum", "cummean"])
+@pytest.mark.parametrize("dtype,tol", [("float32", 1e-5), ("bfloat16", 2e-2)])
+def test_cumsum_and_cummean_layers(cuda, layer, dtype, tol):
+    """the reference's `cumsum` / `cummean` layers (src/model/spatial.py:26-39) through the layer
+    registry: output and input gradient against the oracle."""
+    from obst import utils_core
+    from obst.dataclass import BlockConfig, ModelParameter, gpt_mode
+    from obst.model.backend import run_tape
+    from obst.model.frontend import block_part_fn
+    from obst.utils_core import scoped
+    from obst.utils_mtf import Tensor
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=3, sequence_length=50, features_per_head=16, calculation_dtype=dtype)
+    params = ModelParameter(gpt_mode(cfg))
+    rng = np.random.default_rng(14)
+    B, S, H, K = 3, 50, params.heads, params.features_per_head
+    tdt = torch.float32 if dtype == "float32" else torch.bfloat16
+    x = torch.from_numpy(rng.standard_normal((B, S, H, K)).astype(np.float32)).to(tdt).cuda()
+    dy = torch.from_numpy(rng.standard_normal((B, S, H, K)).astype(np.float32)).to(tdt).cuda()
+    dims = [params.batch_dim._replace(size=B), params.sequence_dim] + params.feature_dims
+    utils_core.NAME_INDICES.clear()
+    params.cached_parameters.clear()
+    params.tape = []
+    block = BlockConfig({"layer": [layer]}, "revnet")
+    out = scoped("gpt", lambda: scoped("body", lambda: block_part_fn(params, block, Tensor(x, dims), "0")))
+    tape, params.tape = params.tape, None
+    dx = run_tape(tape, dy)
+    mean = layer == "cummean"
+    assert rel(to_np(out.data), orc.cumsum_fwd(x.double().cpu().numpy(), 1, mean)) < tol
+    assert rel(to_np(dx), orc.cumsum_bwd(dy.double().cpu().numpy(), 1, mean)) < tol
