@@ -168,14 +168,19 @@ __global__ void __launch_bounds__(RWARPS * 32, 2) opt_update_ring_kernel(const o
 #pragma unroll
         for (int j = 0; j < 4; ++j) g[j] = round_to<bf16>(g[j]);
       }
+      float nu[4], inv[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         g[j] = __fmul_rn(g[j], scale);
-        const float nu = __fadd_rn(fminf(rowmin, al[k][j]), __fmul_rn(g[j], g[j]));  // optimizers.py:70
-        cm[k][j] = fmaxf(cm[k][j], nu);
-        rowmax = fmaxf(rowmax, nu);
-        u[j] = __fmul_rn(g[j], __frcp_rn(fmaxf(__fsqrt_rn(nu), 1e-5f)));             // g * opt_rsqrt(nu)
-        mn[j] = __fadd_rn(__fmul_rn(hp.beta, mv[j]), u[j]);                          // optimizers.py:124
+        nu[j] = __fadd_rn(fminf(rowmin, al[k][j]), __fmul_rn(g[j], g[j]));           // optimizers.py:70
+        cm[k][j] = fmaxf(cm[k][j], nu[j]);
+        rowmax = fmaxf(rowmax, nu[j]);
+      }
+      opt_rsqrt4(nu, inv);                                                           // opt_rsqrt, :13-14
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        u[j] = __fmul_rn(g[j], inv[j]);                                              // :76
+        mn[j] = __fadd_rn(__fmul_rn(hp.beta, mv[j]), u[j]);                          // :124
       }
       if (hp.nesterov) {
 #pragma unroll

@@ -249,45 +249,59 @@ def linear(args: BlockArgs, old: DIM_LIST, new: DIM_LIST, relu: bool = False) ->
     old, new = list(old), list(new)
     var = orthogonal_var(args, old + new, old)
     group = [d for d in old if d in new]
-    contract = [d for d in old if d not in group]
+    # MTF's einsum only contracts dims the INPUT carries: an `old` dim missing from the tensor (reduced_half_linear:
+    # the head dim after sum_heads, src/model/basic.py:89-90) is simply a produced dim, and the same input feeds
+    # every group
+    absent = [d for d in group if d not in x.dims]
+    contract = [d for d in old if d not in group and d in x.dims]
     produce = [d for d in new if d not in group]
     if len(group) > 1:
         raise NotImplementedError(f"linear: more than one grouped dim ({group}) is not supported on this path")
+    present_group = [d for d in group if d not in absent]
     lead = shape_sub(x.shape, old)
-    if x.dims != lead + group + contract:
+    if x.dims != lead + present_group + contract:
         raise NotImplementedError(f"linear: contracted dims {old} must be the trailing dims of {x.dims}")
     out_dims = deduplicate(lead + new)
     if out_dims != lead + group + produce:
         raise NotImplementedError(f"linear: unsupported output layout {out_dims}")
     M, G, Kc, Np = shape_size(lead), shape_size(group), shape_size(contract), shape_size(produce)
-    if [d.size for d in var.dims] != [d.size for d in group + contract + produce]:
+    if [d.size for d in var.dims] != [d.size for d in group + [d for d in old if d not in group] + produce]:
         raise NotImplementedError(f"linear: weight layout {var.dims} is not [group, contract, produce]")
+    if shape_size([d for d in old if d not in group]) != Kc:
+        raise NotImplementedError(f"linear: contracted dims {old} are only partly present in {x.dims}")
     be = params.gemm_backend
     dt = x.data.dtype
     w = var.value
     wt = var.transposed(G, Kc, Np)  # [G, Np, Kc]: the forward B operand, K-major
     residual = params.residual
     xin = x.data
+    xg = 0 if absent else Kc      # stride of the input along the group (0: one input broadcast to every group)
+    xld = Kc if absent else G * Kc
     if residual is not None:
         params.residual = None
         buf, sign, out = residual  # out = buf +/- x@W; out is buf itself for the in-place (reversible) case
         if relu or tuple(buf.shape) != tuple(d.size for d in out_dims):
             raise NotImplementedError("linear: residual fusion needs a plain final linear of matching shape")
-        native.gemm(native.operand(xin, G * Kc, 1, s_glo=Kc), native.operand(wt, Kc, 1, s_glo=Kc * Np), out, M, Np, Kc,
+        native.gemm(native.operand(xin, xld, 1, s_glo=xg), native.operand(wt, Kc, 1, s_glo=Kc * Np), out, M, Np, Kc,
                     GLO=G, d_ld=G * Np, d_glo=Np, R=buf, epi=2 if sign > 0 else 3, dtype_in=dt, backend=be)
     else:
         out = torch.empty([d.size for d in out_dims], dtype=dt, device=xin.device)
-        native.gemm(native.operand(xin, G * Kc, 1, s_glo=Kc), native.operand(wt, Kc, 1, s_glo=Kc * Np), out, M, Np, Kc,
+        native.gemm(native.operand(xin, xld, 1, s_glo=xg), native.operand(wt, Kc, 1, s_glo=Kc * Np), out, M, Np, Kc,
                     GLO=G, d_ld=G * Np, d_glo=Np, epi=1 if relu else 0, dtype_in=dt, backend=be)
 
     if params.tape is not None:
         def bwd(dy: torch.Tensor, mask, acc):
             # wgrad: dW[g,kc,np] += sum_m x[m,g,kc] dy[m,g,np]   (both operands read MN-major, fp32 atomics)
-            native.gemm(native.operand(xin, 1, G * Kc, s_glo=Kc), native.operand(dy, 1, G * Np, s_glo=Np),
+            native.gemm(native.operand(xin, 1, xld, s_glo=xg), native.operand(dy, 1, G * Np, s_glo=Np),
                         var.ensure_grad(), Kc, Np, M, GLO=G, d_ld=Np, d_glo=Kc * Np, accumulate=True, dtype_in=dt,
                         backend=be)
-            # dgrad: dx[m,g,kc] = sum_np dy[m,g,np] W[g,kc,np]   (+ ReLU mask of the producer folded in)
             dx = torch.empty_like(xin)
+            if absent:
+                # dx[m,kc] = sum_g sum_np dy[m,g,np] W[g,kc,np]: the group is an outer reduction index
+                native.gemm(native.operand(dy, G * Np, 1, s_ko=Np), native.operand(w, Np, 1, s_ko=Kc * Np), dx, M, Kc,
+                            Np, KO=G, d_ld=Kc, R=mask, epi=4 if mask is not None else 0, dtype_in=dt, backend=be)
+                return dx
+            # dgrad: dx[m,g,kc] = sum_np dy[m,g,np] W[g,kc,np]   (+ ReLU mask of the producer folded in)
             native.gemm(native.operand(dy, G * Np, 1, s_glo=Np), native.operand(w, Np, 1, s_glo=Kc * Np), dx, M, Kc,
                         Np, GLO=G, d_ld=G * Kc, d_glo=Kc, R=mask, epi=4 if mask is not None else 0, dtype_in=dt,
                         backend=be)

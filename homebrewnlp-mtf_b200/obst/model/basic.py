@@ -18,13 +18,34 @@ def _unsupported(name: str):
 
 
 def dropout(args: BlockArgs) -> Tensor:
+    """src/model/basic.py:25-30 -> mtf.dropout: identity unless training with keep_prob < 1, else inverted dropout.
+    The mask comes from a counter-based generator keyed by (init_seed, step, call site), so the backward pass (and a
+    reversible recompute of the same call site within the step) sees the same mask."""
+    import torch
+
+    from .. import native
+    from ..utils_core import current_scope
+    from .backend import TapeEntry
     keep = 1
     for extra in args.name_extras:
         if isinstance(extra, str) and extra.startswith('dropout_rate'):
             keep = 1 - float(extra[len('dropout_rate'):])
-    if keep != 1:
-        raise NotImplementedError("dropout with keep_prob < 1 is not on the hot path (all configs use rate 0)")
-    return args.tensor
+    params = args.params
+    if keep == 1 or not params.train:
+        return args.tensor
+    import zlib
+    seed = (zlib.crc32(current_scope().encode()) << 32) ^ (int(params.global_step) * 2654435761 + int(params.init_seed))
+    x = args.tensor.data
+    out = torch.empty_like(x)
+    native.dropout(x, out, keep, seed)
+    if params.tape is not None:
+        def bwd(dy, mask, acc):
+            dx = torch.empty_like(dy)
+            native.dropout(dy, dx, keep, seed)
+            return dx
+
+        params.tape.append(TapeEntry(bwd))
+    return Tensor(out, args.tensor.dims)
 
 
 def wrapped_linear(args: BlockArgs, relu: bool = False) -> Tensor:
@@ -129,10 +150,94 @@ def bottleneck_group_linear(args: BlockArgs) -> Tensor:
     return activated_linear_out(args)
 
 
-rezero = _unsupported('rezero')
-group_linear = _unsupported('group_linear')
-sum_heads = _unsupported('sum_heads')
-transpose_sequence_features = _unsupported('transpose_sequence_features')
-reduced_half_linear = _unsupported('reduced_half_linear')
+def rezero(args: BlockArgs) -> Tensor:
+    """src/model/basic.py:21-22: x * s with s a rank-0 variable initialised to 0 (the optimizer gives rank-0 variables
+    adam instead of sm3 and rezero variables their own learning-rate multiplier, src/optimizer/optimizers.py:61-62,
+    src/optimizer/__init__.py:46-47)."""
+    import numpy as np
+    import torch
+
+    from .. import native
+    from .backend import TapeEntry, get_var
+    var = get_var(args, [], lambda seed: np.zeros((), np.float32))
+    x = args.tensor.data
+    out = torch.empty_like(x)
+    native.scale(x, var.value, out)
+    if args.params.tape is not None:
+        def bwd(dy, mask, acc):
+            native.dot_accumulate(x, dy, var.ensure_grad())
+            dx = torch.empty_like(dy)
+            native.scale(dy, var.value, dx)
+            return dx
+
+        args.params.tape.append(TapeEntry(bwd))
+    return Tensor(out, args.tensor.dims)
+
+
+def group_linear(args: BlockArgs) -> Tensor:
+    """src/model/basic.py:72-74: a per-head linear over the features of each head, reshaped back to the input's
+    dims.  (`args('group')` in the reference appends the TYPE `str`, not the string -- BlockArgs.__call__ quirk -- so
+    no `group` extra is actually added; nothing downstream of this call reads it.)"""
+    from ..utils_mtf import anonymize_dim
+    params = args.params
+    anonymous_key = [anonymize_dim(d) if d == params.key_dim else d for d in params.feature_dims]
+    out = linear(args('group'), params.feature_dims, anonymous_key)
+    dims = [params.key_dim if d == anonymize_dim(params.key_dim) else d for d in out.dims]
+    return Tensor(out.data, dims)
+
+
+def sum_heads(args: BlockArgs) -> Tensor:
+    """src/model/basic.py:77-78: reduce_sum over the head dim."""
+    import torch
+
+    from .. import native
+    from .backend import TapeEntry
+    params = args.params
+    x = args.tensor
+    if x.dims[-2:] != params.feature_dims:
+        raise NotImplementedError(f"sum_heads: expected [..., heads, features_per_head], got {x.dims}")
+    H, K = params.head_dim.size, params.key_dim.size
+    rows = x.data.numel() // (H * K)
+    out = torch.empty(list(x.data.shape[:-2]) + [K], dtype=x.data.dtype, device=x.data.device)
+    native.sum_heads(x.data, out, rows, H, K)
+    if params.tape is not None:
+        def bwd(dy, mask, acc):
+            dx = torch.empty_like(x.data)
+            native.broadcast_heads(dy, dx, rows, H, K)
+            return dx
+
+        params.tape.append(TapeEntry(bwd))
+    return Tensor(out, x.dims[:-2] + [params.key_dim])
+
+
+def transpose_sequence_features(args: BlockArgs) -> Tensor:
+    """src/model/basic.py:81-86: exchange the sequence and features_per_head axes (they must have equal sizes)."""
+    import torch
+
+    from .. import native
+    from .backend import TapeEntry
+    params = args.params
+    x = args.tensor
+    assert params.features_per_head == params.sequence_length, "ToDo: Support other shapes"
+    if len(x.dims) != 4 or x.dims[1] != params.sequence_dim or x.dims[2:] != params.feature_dims:
+        raise NotImplementedError(f"transpose_sequence_features: expected [batch, sequence, heads, features], got {x.dims}")
+    B, S, H, K = (d.size for d in x.dims)
+    out = torch.empty_like(x.data)
+    native.swap_axes(x.data, out, B, S, H, K)
+    if params.tape is not None:
+        def bwd(dy, mask, acc):
+            dx = torch.empty_like(dy)
+            native.swap_axes(dy, dx, B, K, H, S)
+            return dx
+
+        params.tape.append(TapeEntry(bwd))
+    return Tensor(out, x.dims)
+
+
+def reduced_half_linear(args: BlockArgs) -> Tensor:
+    """src/model/basic.py:89-90: group_linear of the head sum: every head's weight sees the same summed input."""
+    return group_linear(args(sum_heads(args)))
+
+
 product_key_memory = _unsupported('product_key_memory')
 feed_forward_product_key_memory = _unsupported('feed_forward_product_key_memory')

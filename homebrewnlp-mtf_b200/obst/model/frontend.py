@@ -70,6 +70,62 @@ def block_part_fn(params: ModelParameter, block_part_config: BlockConfig, block_
     return scoped(f"{name_prefix}_", _get_block_part, block_part_config, params, block_input)
 
 
+def split_path(args: BlockArgs) -> Tensor:
+    """src/model/frontend.py:39-55: "split_path-add;<layers>;<layers>..." (or multiply): every ';'-separated path is a
+    ','-separated list of layer strings applied to the SAME input; the path outputs are summed (or multiplied).
+    Each path records its own tape; one composite entry sends dy (times the other paths' outputs, for multiply)
+    down every path and sums the input gradients."""
+    import torch
+
+    from .. import native
+    from .backend import TapeEntry, run_tape
+    base, *paths = '-'.join(str(e) for e in args.name_extras).split(';')
+    base = base.split('-')
+    if 'add' in base:
+        multiply = False
+    elif 'multiply' in base:
+        multiply = True
+    else:
+        raise ValueError
+    params = args.params
+    outer = params.tape
+    pending, params.residual = params.residual, None  # a residual can only ride on a single final GEMM
+    outs, tapes = [], []
+    for conf in paths:
+        params.tape = [] if outer is not None else None
+        try:
+            outs.append(_run_layers(BlockConfig({'skip': False, 'layer': conf.split(',')}, ''), params, args.tensor))
+        finally:
+            tapes.append(params.tape)
+            params.tape = outer
+    params.residual = pending
+    if not outs:
+        raise ValueError("split_path needs at least one path")
+    total = outs[0].data.clone()
+    for o in outs[1:]:
+        if multiply:
+            native.mul(total, o.data, total)
+        else:
+            native.axpby(total, o.data, 1.0, total)
+    if outer is not None:
+        def bwd(dy, mask, acc):
+            dx = acc
+            for i, tape in enumerate(tapes):
+                g = dy
+                if multiply:  # d/d(path i) of the product = dy * product of the other paths
+                    g = dy.clone()
+                    for j, o in enumerate(outs):
+                        if j != i:
+                            native.mul(g, o.data, g)
+                if dx is None:
+                    dx = torch.zeros_like(args.tensor.data)
+                dx = run_tape(tape, g, acc=dx)
+            return dx
+
+        outer.append(TapeEntry(bwd, supports_acc=True))
+    return Tensor(total, outs[0].dims)
+
+
 def _unsupported(name):
     def fn(args: BlockArgs) -> Tensor:
         raise NotImplementedError(f"layer '{name}' is registered by the reference but is outside the mixer hot path")
@@ -87,7 +143,7 @@ LAYER_FUNCTIONS = {'feed_forward': feed_forward,
                    'convolution': _unsupported('convolution'),
                    'dropout': dropout,
                    'group_linear': group_linear,
-                   'split_path': _unsupported('split_path'),
+                   'split_path': split_path,
                    'feed_forward_product_key_memory': feed_forward_product_key_memory,
                    'product_key_memory': product_key_memory,
                    'reduced_half_linear': reduced_half_linear,

@@ -51,9 +51,10 @@ class FusedOptimizer:
     """State + launch plumbing of the fused update.  Owns the flat gradient buffer (so DP reduction is one or a few
     contiguous allreduces), the momentum / SM3 slots and the device-side tensor table."""
 
-    def __init__(self, params: ModelParameter, plan: FusedPlan):
+    def __init__(self, params: ModelParameter, plan: FusedPlan, variables: typing.Optional[list] = None):
         self.params = params
         self.plan = plan
+        self.scalar_opt: typing.Optional["FusedOptimizer"] = None
         dev = torch.device(params.device)
         self.state_dtype = params.optimizer_dtype.slice_dtype
         self.act_dtype = params.variable_dtype.activation_dtype
@@ -62,13 +63,19 @@ class FusedOptimizer:
         # step from the fp32 accumulation buffer (obst_grad_finalize), all-reduced in that dtype, read by the update.
         # Generic chains rewrite the gradient stage by stage and stay on the fp32 buffer.
         self.grad_lp = self.act_dtype == torch.bfloat16 and isinstance(plan, FusedPlan)
-        variables = [v for v in params.variable_cache.values() if v.trainable]
-        if not variables:
-            raise RuntimeError("no trainable variables: run build() once before get_optimizer()")
+        if variables is None:
+            variables = [v for v in params.variable_cache.values() if v.trainable]
+            if not variables:
+                raise RuntimeError("no trainable variables: run build() once before get_optimizer()")
+            scalars = [v for v in variables if len(v.dims) == 0]
+            variables = [v for v in variables if len(v.dims) > 0]
+            if scalars:
+                # rank-0 variables (rezero gates): sm3 / novograd fall back to adam for them
+                # (src/optimizer/optimizers.py:48-49,61-62) -- a second, stage-by-stage state holds them
+                self.scalar_opt = FusedOptimizer(params, _scalar_plan(plan), variables=scalars)
         for v in variables:
-            if not 1 <= len(v.dims) <= 4:
-                raise NotImplementedError(f"sm3 on rank-{len(v.dims)} variable {v.name}: ranks 1..4 are fused "
-                                          f"(rank 0 falls back to adam in the reference, unused by the mixer)")
+            if len(v.dims) > 4:
+                raise NotImplementedError(f"sm3 on rank-{len(v.dims)} variable {v.name}: ranks 0..4 are supported")
         # flat layout: per-depth variables first (their gradients are final first during the last backward pass),
         # shared mixing maps / input / output variables last
         shared = {id(v) for v in variables if _depth_of(v) == 0 and "embed" in v.name}
@@ -123,7 +130,7 @@ class FusedOptimizer:
                 t.g_acc = None
                 t.g_bf16 = 0
             t.m = m.data_ptr()
-            dims = [dd.size for dd in v.dims]
+            dims = [dd.size for dd in v.dims] or [1]  # a rank-0 variable is laid out as one element
             for i, n in enumerate(dims):
                 a = self.flat_acc[aoff:aoff + n]
                 an = self.flat_acc_new[aoff:aoff + n]
@@ -163,6 +170,8 @@ class FusedOptimizer:
         self._t_sig = None   # (shadow, transposed shadow) addresses the transpose table was built for
         self._t_table = None
         self._t_tiles = 0
+        if self.scalar_opt is not None:
+            self.slots.update(self.scalar_opt.slots)
 
     @property
     def n_params(self) -> int:
@@ -174,6 +183,12 @@ class FusedOptimizer:
         self.norms.zero_()
         self.finalized.clear()
         self.g2_keys.clear()
+        if self.scalar_opt is not None:
+            self.scalar_opt.zero_grad()
+
+    def extra_reduce_buffers(self) -> typing.List[torch.Tensor]:
+        """Gradient buffers outside the depth buckets that data-parallel ranks must also sum (rank-0 variables)."""
+        return [] if self.scalar_opt is None else [self.scalar_opt.flat_grad]
 
     def reduce_buffer(self) -> torch.Tensor:
         """What data-parallel ranks all-reduce: the gradients in the dtype the optimizer is handed."""
@@ -381,6 +396,10 @@ class FusedOptimizer:
                                                                           torch.float64))
         for name, args in plan.stages:
             self._run_stage(name, args, work, lr, step_count)
+        if any("rezero" in v.name for v in self.variables):  # src/optimizer/__init__.py:46-47
+            if not all("rezero" in v.name for v in self.variables):
+                raise NotImplementedError("rezero_lr_multiplier: rezero and other variables share one generic chain")
+            self._stage(N.STAGE_LEARNING_RATE, work, f=[float(self.params.rezero_lr_multiplier)])
         self._stage(N.STAGE_APPLY, work, f=[float(lr) * float(self.params.weight_decay)])
         self.wnorm_valid = False
         if refresh_transposed:
@@ -389,6 +408,8 @@ class FusedOptimizer:
     def step(self, lr: float, refresh_transposed: bool = True, step_count: int = 1, preview: bool = False):
         """One update of every variable.  preview: write only the shadows of the would-be weights (the
         reference's non-final macro-batches, src/run/train.py:63-69); weights and optimizer state stay as they are."""
+        if self.scalar_opt is not None:
+            self.scalar_opt.step(lr, False, step_count, preview)
         if isinstance(self.plan, GenericPlan):
             if preview:
                 raise NotImplementedError("macro_batching > 1 needs the fused optimizer chain "
@@ -425,6 +446,17 @@ class FusedOptimizer:
             self.wnorm_valid = plan.clip > 0
         if refresh_transposed:  # the update rewrote the shadows in place: transposed copies follow
             self.refresh_transposed()
+
+
+def _scalar_plan(plan) -> GenericPlan:
+    """The chain as it runs for a rank-0 variable: sm3 and novograd hand over to adam
+    (src/optimizer/optimizers.py:48-49,61-62)."""
+    if isinstance(plan, FusedPlan):
+        stages = ([("adaptive_clip", (repr(plan.clip),))] if plan.clip > 0 else []) + \
+                 [("adam", ()), ("momentum", (repr(plan.beta), "1", str(int(plan.nesterov)))), ("learning_rate", ())]
+    else:
+        stages = [("adam", ()) if n in ("sm3", "novograd") else (n, a) for n, a in plan.stages]
+    return GenericPlan(tuple(stages))
 
 
 def update(ctx: OptimizerCtx):

@@ -80,6 +80,9 @@ class GradReducer:
                 self.launched.add(key)
                 self._hand_over(key)
                 self._reduce(self._flat()[rng[0]:rng[1]])
+        extra = getattr(state, "extra_reduce_buffers", None)
+        for buf in (extra() if extra is not None else []):
+            self._reduce(buf)
         sums = getattr(self.params, "loss_sums", None)
         if sums is not None:
             self._reduce(sums)

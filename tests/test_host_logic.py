@@ -106,7 +106,7 @@ def test_registries_carry_the_reference_names():
                                "global_l2norm_clip", "momentum", "graft"}
     assert set(MODULES) == {"linear_warmup", "exponential_decay", "linear_decay", "lower_bound", "upper_bound"}
     with pytest.raises(NotImplementedError):
-        LAYER_FUNCTIONS["rezero"](None)
+        LAYER_FUNCTIONS["convolution"](None)  # registered by the reference, outside the scope of this path
 
 
 def test_optimizer_string_lowers_to_the_fused_plan():

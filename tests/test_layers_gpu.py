@@ -1,0 +1,146 @@
+"""The registered layers beside the mixer hot path, each through the layer registry exactly as a
+block_config string would reach it, against a float64 statement of the reference's lines written with torch autograd
+(these are small floating-point compositions; the statement cites the lines it follows).  fp32 at 1e-5."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import obst_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from obst import native
+    native.load()
+
+
+def rel(a, b):
+    a, b = a.double().cpu(), b.double().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+def run_layers(layers, seq=16, fph=16, batch=2, seed=20, **cfg_overrides):
+    """Runs one block made of `layers` on a random [batch, seq, heads, fph] input; returns everything a checker needs."""
+    from obst import utils_core
+    from obst.dataclass import BlockConfig, ModelParameter, gpt_mode
+    from obst.model.backend import run_tape
+    from obst.model.frontend import block_part_fn
+    from obst.utils_core import scoped
+    from obst.utils_mtf import Tensor
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=batch, sequence_length=seq, features_per_head=fph)
+    cfg.update(cfg_overrides)
+    params = ModelParameter(gpt_mode(cfg))
+    rng = np.random.default_rng(seed)
+    H = params.heads
+    x = torch.from_numpy(rng.standard_normal((batch, seq, H, fph)).astype(np.float32)).cuda()
+    dims = [params.batch_dim._replace(size=batch), params.sequence_dim] + params.feature_dims
+    utils_core.NAME_INDICES.clear()
+    params.cached_parameters.clear()
+    params.tape = []
+    block = BlockConfig({"layer": layers}, "revnet")
+    out = scoped("gpt", lambda: scoped("body", lambda: block_part_fn(params, block, Tensor(x, dims), "0")))
+    tape, params.tape = params.tape, None
+    dy = torch.from_numpy(rng.standard_normal(tuple(out.data.shape)).astype(np.float32)).cuda()
+    dx = run_tape(tape, dy)
+    return params, x, out, dy, dx, list(params.variable_cache.values())
+
+
+def test_group_linear_and_reduced_half_linear(cuda):
+    """group_linear (src/model/basic.py:72-74): out[b,s,h,j] = sum_k x[b,s,h,k] W[h,k,j];
+    reduced_half_linear (:89-90): the same weights applied to the head SUM, out[b,s,h,j] = sum_k (sum_h' x)[k] W[h,k,j]."""
+    params, x, out, dy, dx, variables = run_layers(["group_linear"])
+    (w,) = variables
+    xr = x.double().requires_grad_(True)
+    wr = w.data.double().requires_grad_(True)
+    ref = torch.einsum("bshk,hkj->bshj", xr, wr)
+    ref.backward(dy.double())
+    assert rel(out.data, ref.detach()) < 1e-5 and rel(dx, xr.grad) < 1e-5 and rel(w.grad, wr.grad) < 1e-5
+    params, x, out, dy, dx, variables = run_layers(["reduced_half_linear"])
+    (w,) = variables
+    xr = x.double().requires_grad_(True)
+    wr = w.data.double().requires_grad_(True)
+    ref = torch.einsum("bsk,hkj->bshj", xr.sum(2), wr)
+    ref.backward(dy.double())
+    assert tuple(out.data.shape) == tuple(ref.shape)
+    assert rel(out.data, ref.detach()) < 1e-5 and rel(dx, xr.grad) < 1e-5 and rel(w.grad, wr.grad) < 1e-5
+
+
+def test_sum_heads_and_transpose_sequence_features(cuda):
+    """sum_heads (src/model/basic.py:77-78) = reduce_sum over heads; transpose_sequence_features (:81-86) exchanges
+    the sequence and features_per_head axes (equal sizes)."""
+    params, x, out, dy, dx, _ = run_layers(["sum_heads"])
+    assert rel(out.data, x.double().sum(2)) < 1e-6
+    assert rel(dx, dy.double()[:, :, None, :].expand_as(x)) == 0.0
+    params, x, out, dy, dx, _ = run_layers(["transpose_sequence_features"], seq=16, fph=16)
+    assert torch.equal(out.data, x.permute(0, 3, 2, 1).contiguous())
+    assert torch.equal(dx, dy.permute(0, 3, 2, 1).contiguous())
+
+
+def test_rezero_layer_and_its_optimizer_rule(cuda):
+    """rezero (src/model/basic.py:21-22): x * s, s a rank-0 variable initialised to 0; ds = sum(x * dy).  The
+    optimizer gives rank-0 variables adam in place of sm3 (src/optimizer/optimizers.py:61-62) and rezero variables
+    the extra learning-rate multiplier (src/optimizer/__init__.py:46-47)."""
+    params, x, out, dy, dx, variables = run_layers(["group_linear", "rezero"])
+    w, s = variables
+    assert s.data.dim() == 0 and float(s.data) == 0.0
+    assert float(out.data.abs().max()) == 0.0 and float(dx.abs().max()) == 0.0
+    h = torch.einsum("bshk,hkj->bshj", x.double(), w.data.double())
+    assert abs(float(s.grad) - float((h * dy.double()).sum())) < 1e-5 * float((h * dy.double()).abs().sum())
+    # one optimizer step on this single scalar through the product's optimizer
+    from obst.optimizer import _ensure_state
+    state = _ensure_state(params)
+    assert state.scalar_opt is not None and len(state.variables) == 1
+    g = float(s.grad)
+    lr = 0.01
+    state.step(lr, refresh_transposed=False, step_count=1)
+    torch.cuda.synchronize()
+    # oracle: adaptive_clip -> adam (rank 0) -> momentum:0.9:1:1 -> learning_rate, then the rezero multiplier
+    st = {}
+    f32 = np.float32
+    hyper = {"lr": f32(lr), "step_count": 1, "beta1": 0.9, "beta2": 0.99, "global_sq": g * g,
+             "keep": lambda v: np.asarray(v, f32)}
+    gg = np.asarray(g, f32)
+    w = np.asarray(0.0, f32)
+    for opt, *a in (o.split(":") for o in orc.TINY_CONFIG["optimizer"].split("-")):
+        gg = orc._apply_stage(opt, a, gg, w, st, hyper)
+    expect = -float(gg) * params.rezero_lr_multiplier
+    assert abs(float(s.data) - expect) < 1e-5 * abs(expect), (float(s.data), expect)
+
+
+def test_split_path_add_and_multiply(cuda):
+    """split_path (src/model/frontend.py:39-55): every ';' path is applied to the same input, outputs summed or
+    multiplied."""
+    for mode in ("add", "multiply"):
+        params, x, out, dy, dx, variables = run_layers([f"split_path-{mode};cumsum;group_linear,activation-tanh;cummean"])
+        (w,) = variables
+        xr = x.double().requires_grad_(True)
+        wr = w.data.double().requires_grad_(True)
+        p1 = torch.cumsum(xr, 1)
+        p2 = torch.tanh(torch.einsum("bshk,hkj->bshj", xr, wr))
+        p3 = torch.cumsum(xr, 1) / (1 + torch.arange(x.shape[1], dtype=torch.float64, device=xr.device)).view(1, -1, 1, 1)
+        ref = p1 + p2 + p3 if mode == "add" else p1 * p2 * p3
+        ref.backward(dy.double())
+        assert rel(out.data, ref.detach()) < 1e-5, mode
+        assert rel(dx, xr.grad) < 1e-5 and rel(w.grad, wr.grad) < 1e-5, mode
+
+
+def test_dropout_keeps_the_stated_fraction_and_replays_its_mask(cuda):
+    """dropout-dropout_rate0.25 (src/model/basic.py:25-30 -> mtf.dropout): inverted dropout; the reference's own test
+    (tests/basic_pointwise_test.py) checks the kept fraction, so does this, plus: survivors are scaled by 1/keep and
+    the backward pass applies the same mask."""
+    params, x, out, dy, dx, _ = run_layers(["dropout-dropout_rate0.25"], seq=64, fph=64, batch=4)
+    kept = out.data != 0
+    frac = float(kept.float().mean())
+    assert abs(frac - 0.75) < 0.01, frac
+    assert torch.allclose(out.data[kept], x[kept] / 0.75, rtol=1e-6)
+    assert torch.equal(dx != 0, kept & (dy != 0)) and torch.allclose(dx[kept], dy[kept] / 0.75, rtol=1e-6)
+    # evaluation mode (params.train False) and rate 0: identity
+    params, x, out, dy, dx, _ = run_layers(["dropout-dropout_rate0.25"], train=False)
+    assert torch.equal(out.data, x)

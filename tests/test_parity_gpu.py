@@ -425,12 +425,12 @@ def test_unsupported_layers_and_optimizers_fail_loudly(cuda):
     from obst.run.train import get_train_model
     cfg = copy.deepcopy(orc.TINY_CONFIG)
     cfg.update(depth=1, train_batch_size=2, sequence_length=64)
-    cfg["block_config"] = [{"layer": ["norm-shift-scale-features-group", "rezero"]}]
+    cfg["block_config"] = [{"layer": ["norm-shift-scale-features-group", "convolution"]}]
     sh = orc.Shapes(orc.TINY_CONFIG)
     from obst.dataclass import ModelParameter, gpt_mode
     params = ModelParameter(gpt_mode(cfg))
     x = torch.zeros(2, 64, 1, dtype=torch.int32, device="cuda")
-    with pytest.raises(NotImplementedError, match="rezero"):
+    with pytest.raises(NotImplementedError, match="convolution"):
         get_train_model(params, None, None, None, x, x, None, None, None, 0)
     cfg = copy.deepcopy(orc.TINY_CONFIG)
     cfg.update(depth=1, train_batch_size=2, sequence_length=64)
