@@ -31,7 +31,7 @@ __global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* _
                                                          const int32_t* __restrict__ item_rows, int act_bf16,
                                                          int grad_bf16, double* __restrict__ norms, int carry,
                                                          int skip_g, double* __restrict__ wnext, int carry_first,
-                                                         int carry_count) {
+                                                         int carry_count, int w_from_shadow) {
   __shared__ double s_part[2][8];
   const int item = blockIdx.x;
   // carry mode: sum cast_AT(p)^2 was accumulated by the previous update (it wrote every p) -- move it into place
@@ -79,8 +79,15 @@ __global__ void __launch_bounds__(256) opt_norms_kernel(const obst_opt_tensor* _
     }
   }
   if (!carry) {
+    const bool from_shadow = w_from_shadow && T.shadow != nullptr;
     for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
-      const float ww = act_bf16 ? round_to<bf16>(p[i]) : p[i];
+      float ww = act_bf16 ? round_to<bf16>(p[i]) : p[i];
+      if (from_shadow) {  // macro-batching chain: see OptHyper::w_from_shadow
+        const int64_t e = e0 + i;
+        const bool masked = T.tril_s > 0 && (int)(e % T.tril_s) > (int)((e / T.tril_s) % T.tril_s);
+        if (!masked)
+          ww = act_bf16 ? to_f32(reinterpret_cast<const bf16*>(T.shadow)[e]) : reinterpret_cast<const float*>(T.shadow)[e];
+      }
       sw += square_as_double(ww, act_bf16 != 0);
     }
   }
@@ -226,7 +233,13 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
         const int64_t e = rbase + c;
         const float pv = Tp[e];
         const float g = __fmul_rn(ld_grad(T, e, hp.grad_bf16), scale);
-        const float w = hp.act_bf16 ? round_to<bf16>(pv) : pv;
+        float w = hp.act_bf16 ? round_to<bf16>(pv) : pv;
+        bool masked = false;
+        if (tril_s > 0) masked = (int)(e % tril_s) > (int)((e / tril_s) % tril_s);
+        // macro-batching chain: the graph reads the previous macro-batch's would-be weights, which live in the
+        // shadow (masked entries of a mixing map never move, so there the cast of p is still the value)
+        if (hp.w_from_shadow && Tshadow && !masked)
+          w = hp.act_bf16 ? to_f32(reinterpret_cast<const bf16*>(Tshadow)[e]) : reinterpret_cast<const float*>(Tshadow)[e];
         const float mv = hp.sm3_only ? 0.f : ld_state<TS>(Tm, e);
         const OptElemOut o = opt_element(g, fminf(rowmin, al[i * VEC + j]), mv, pv, w, hp, wd_on);
         cm[i * VEC + j] = fmaxf(cm[i * VEC + j], o.nu);
@@ -236,18 +249,19 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
           continue;
         }
         float sh = o.p_new;
-        if (tril_s > 0) {
-          const int col = (int)(e % tril_s);
-          const int row = (int)((e / tril_s) % tril_s);
-          if (col > row) sh = 0.f;
+        if (hp.preview) {  // subtract(var.value, cast(update)) in the activation dtype
+          const float w0 = hp.act_bf16 ? round_to<bf16>(pv) : pv;
+          const float us = hp.act_bf16 ? round_to<bf16>(o.step) : o.step;
+          sh = __fsub_rn(w0, us);
         }
+        if (masked) sh = 0.f;
         if (Tshadow) {
           if (hp.act_bf16) reinterpret_cast<bf16*>(Tshadow)[e] = __float2bfloat16_rn(sh);
           else reinterpret_cast<float*>(Tshadow)[e] = sh;
         }
+        reinterpret_cast<TS*>(Tm)[e] = from_f32<TS>(o.m_new);
         if (hp.preview) continue;
         Tp[e] = o.p_new;
-        reinterpret_cast<TS*>(Tm)[e] = from_f32<TS>(o.m_new);
         const float wv = hp.act_bf16 ? round_to<bf16>(o.p_new) : o.p_new;
         w2 = add_square(w2, wv, hp.act_bf16 != 0);
       }
@@ -256,7 +270,6 @@ __global__ void __launch_bounds__(256) opt_update_kernel(const obst_opt_tensor* 
     if (lane == 0) s_rowmax[r - row_begin] = rowmax;
   }
   __syncthreads();
-  if (hp.preview) return;
   opt_row_maxima_commit(T, item_row0[item], item_rows[item], s_rowmax);
 #pragma unroll
   for (int i = 0; i < NI; ++i) {
@@ -298,7 +311,7 @@ __global__ void __launch_bounds__(256) opt_finalize_kernel(const obst_opt_tensor
 static int launch_update(const obst_opt_tensor* table, const int32_t* item_tensor, const int32_t* item_row0,
                          const int32_t* item_rows, int nitems, int max_cols, int vec4, int dtype_state,
                          const double* norms, const OptHyper& hp, double* wnext, cudaStream_t st, const char* what) {
-  if (vec4 && !hp.sm3_only)
+  if (vec4 && !hp.sm3_only && !hp.preview && !hp.w_from_shadow)  // the macro-batching chain takes the generic kernel
     return opt_update_ring_launch(table, item_tensor, item_row0, item_rows, nitems, max_cols, dtype_state, norms, hp,
                                   wnext, st);
   const int vec = vec4 ? 4 : 1;
@@ -349,7 +362,8 @@ int obst_opt_norms(const obst_opt_tensor* table, int32_t ntensors, const int32_t
   // carry + skip_g: only the carried weight sums have to be moved into place -- one block
   const unsigned blocks = (carry && skip_g) ? 1u : (unsigned)nitems;
   opt_norms_kernel<<<blocks, 256, 0, st>>>(table, item_tensor, item_row0, item_rows, dtype_act == OBST_BF16,
-                                           grad_bf16, norms, carry, skip_g, wnext, first_tensor, tensor_count);
+                                           grad_bf16, norms, carry, skip_g, wnext, first_tensor, tensor_count,
+                                           (flags & 8) != 0);
   count_launch();
   return check_launch("obst_opt_norms");
 }
@@ -379,9 +393,10 @@ int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_
   hp.clip = clip; hp.beta = beta; hp.lr = lr; hp.weight_decay = weight_decay;
   hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
   hp.sm3_only = 0;
-  hp.preview = preview != 0;
+  hp.preview = (preview & 1) != 0;
+  hp.w_from_shadow = (preview & 2) != 0;
   return launch_update(table, item_tensor, item_row0, item_rows, nitems, max_cols, vec4, dtype_state, norms, hp,
-                       preview ? nullptr : wnext, (cudaStream_t)stream, "obst_opt_update");
+                       hp.preview ? nullptr : wnext, (cudaStream_t)stream, "obst_opt_update");
 }
 
 /* SM3 as a stand-alone stage of a generic chain: g <- g * opt_rsqrt(nu), accumulators max-reduced into acc_new
@@ -396,7 +411,7 @@ int obst_opt_sm3_stage(const obst_opt_tensor* table, int32_t ntensors, const int
   if (nitems <= 0) return OBST_OK;
   OptHyper hp;
   hp.clip = 0.f; hp.beta = 0.f; hp.lr = 1.f; hp.weight_decay = 0.f;
-  hp.nesterov = 0; hp.act_bf16 = 0; hp.grad_bf16 = 0; hp.sm3_only = 1; hp.preview = 0;
+  hp.nesterov = 0; hp.act_bf16 = 0; hp.grad_bf16 = 0; hp.sm3_only = 1; hp.preview = 0; hp.w_from_shadow = 0;
   return launch_update(table, item_tensor, item_row0, item_rows, nitems, max_cols, vec4, dtype_state, nullptr, hp,
                        nullptr, (cudaStream_t)stream, "obst_opt_sm3_stage");
 }
@@ -556,7 +571,7 @@ extern "C" int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, 
   count_launch();
   if (clip > 0.f) {
     opt_norms_kernel<<<(unsigned)f.nitems, 256, 0, st>>>(table, item_tensor, item_row0, item_rows,
-                                                         dtype_act == OBST_BF16, grad_bf16, norms, 0, 0, nullptr, 0, 0);
+                                                         dtype_act == OBST_BF16, grad_bf16, norms, 0, 0, nullptr, 0, 0, 0);
     count_launch();
   }
   OptHyper hp;
@@ -564,6 +579,7 @@ extern "C" int obst_opt_step_noalloc(float* p, void* shadow, float* g, void* m, 
   hp.nesterov = nesterov; hp.act_bf16 = dtype_act == OBST_BF16; hp.grad_bf16 = grad_bf16;
   hp.sm3_only = 0;
   hp.preview = 0;
+  hp.w_from_shadow = 0;
   const int rc = launch_update(table, item_tensor, item_row0, item_rows, f.nitems, cols, vec4, dtype_state, norms, hp,
                                nullptr, st, "obst_opt_step_noalloc");
   if (rc != OBST_OK) return rc;

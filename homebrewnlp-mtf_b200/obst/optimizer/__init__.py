@@ -405,13 +405,19 @@ class FusedOptimizer:
         if refresh_transposed:
             self.refresh_transposed()
 
-    def step(self, lr: float, refresh_transposed: bool = True, step_count: int = 1, preview: bool = False):
-        """One update of every variable.  preview: write only the shadows of the would-be weights (the
-        reference's non-final macro-batches, src/run/train.py:63-69); weights and optimizer state stay as they are."""
+    def step(self, lr: float, refresh_transposed: bool = True, step_count: int = 1, preview: bool = False,
+             chained: bool = False):
+        """One update of every variable.
+        preview / chained: the reference's macro-batching (src/run/train.py:35-74).  A non-final macro-batch
+        (preview) moves the optimizer state on but leaves the master weights alone; the shadows receive the weights
+        the next macro-batch's graph reads, var.value - update in the activation dtype.  `chained` says the graph of
+        THIS macro-batch read such chained weights, so the clip norm and the weight decay use the shadows' values."""
         if self.scalar_opt is not None:
-            self.scalar_opt.step(lr, False, step_count, preview)
+            if preview or chained:
+                raise NotImplementedError("macro_batching > 1 with rank-0 (rezero) variables")
+            self.scalar_opt.step(lr, False, step_count)
         if isinstance(self.plan, GenericPlan):
-            if preview:
+            if preview or chained:
                 raise NotImplementedError("macro_batching > 1 needs the fused optimizer chain "
                                           "([adaptive_clip-]sm3-momentum:<b>:1:<n>-learning_rate)")
             return self._step_generic(lr, step_count, refresh_transposed)
@@ -427,23 +433,25 @@ class FusedOptimizer:
         single = getattr(getattr(p, "grad_reducer", None), "world", 1) == 1
         # buckets the data-parallel reducer did not hand over (single rank: all of them, in one launch)
         self.hand_over(None, with_norms=single and plan.clip > 0)
-        carry = 1 if (self.wnorm_valid and not preview) else 0  # a preview must not consume the carried sums
+        macro = preview or chained
+        carry = 1 if (self.wnorm_valid and not macro) else 0  # the chain's weight norms are read from the shadows
         if plan.clip > 0:
             # sum g^2: taken by the hand-over on a single rank (flags 2|4: keep it, add only the weight half);
             # with several ranks the buckets were all-reduced after the hand-over, so it is taken here.
             # sum cast(p)^2: carried over from the previous update (flag 1) or, on the first step, read here.
             have_g = self.grad_lp and self.g2_keys == set(self.item_ranges)
-            flags = carry | (6 if have_g else 0)
+            flags = carry | (6 if have_g else 0) | (8 if macro else 0)
             native.check(lib.obst_opt_norms(tp, nt, it, ir0, irs, self.n_items, act, grad_bf16 & 1,
                                             self.norms.data_ptr(), flags, self.wnext.data_ptr(), 0, nt, st),
                          "obst_opt_norms")
         native.check(lib.obst_opt_update(tp, nt, it, ir0, irs, self.n_items, self.max_cols, int(self.vec4), act, sdt,
                                          grad_bf16, self.norms.data_ptr(), self.wnext.data_ptr(), plan.clip, plan.beta,
-                                         int(plan.nesterov), float(lr), float(p.weight_decay), int(preview), st),
-                     "obst_opt_update")
-        if not preview:
-            native.check(lib.obst_opt_finalize(tp, nt, sdt, st), "obst_opt_finalize")
-            self.wnorm_valid = plan.clip > 0
+                                         int(plan.nesterov), float(lr), float(p.weight_decay),
+                                         int(preview) | (2 if macro else 0), st), "obst_opt_update")
+        native.check(lib.obst_opt_finalize(tp, nt, sdt, st), "obst_opt_finalize")
+        self.wnorm_valid = plan.clip > 0 and not macro
+        if macro:
+            self.wnext.zero_()
         if refresh_transposed:  # the update rewrote the shadows in place: transposed copies follow
             self.refresh_transposed()
 
@@ -470,7 +478,8 @@ def update(ctx: OptimizerCtx):
     opt_state: FusedOptimizer = params.optimizer_state
     if opt_state.plan != plan:
         raise RuntimeError("optimizer string changed after the optimizer state was created")
-    opt_state.step(ctx.learning_rate, step_count=ctx.step_count)
+    opt_state.step(ctx.learning_rate, step_count=ctx.step_count, preview=not ctx.assign,
+                   chained=bool(getattr(params, "macro_chained", False)))
     ctx.update_ops.extend(v.name for v in opt_state.variables)
 
 
@@ -491,22 +500,25 @@ def _ensure_state(params: ModelParameter) -> FusedOptimizer:
 
 def get_optimizer(loss_list: typing.List[typing.Any], params: ModelParameter, manual_step: int, fn: str
                   ) -> typing.Tuple[typing.List[str], float]:
-    """Differentiate the recorded step and, when fn == "update", apply the parameter update.
-    Same contract as the reference (src/optimizer/__init__.py:69-186): returns (update_ops, learning_rate);
-    any fn other than "update" only accumulates gradients (the reference's "add"/"accumulate" arm, used for all
-    but the last micro-batch)."""
+    """Differentiate the recorded step and run the optimizer.  Same contract as the reference
+    (src/optimizer/__init__.py:69-186): returns (update_ops, learning_rate).
+      fn == "update"      the committed update (`ctx.assign`)
+      fn == "accumulate"  gradients are only accumulated (this implementation's micro-batches; the name is the one
+                          the reference's docstring reserves for gradient accumulation)
+      anything else       the reference's non-assign arm ("add" in src/run/train.py:54): the update is computed and
+                          chained into the next macro-batch, the master weights stay (FusedOptimizer.step)"""
     state = _ensure_state(params)
     update_ops: typing.List[str] = []
     learning_rate_ctx = get_learning_rate(params, loss_list, update_ops)
     learning_rate = float(learning_rate_ctx.learning_rate)
     reducer = getattr(params, "grad_reducer", None)
     if reducer is not None:
-        reducer.begin_backward(last=(fn == "update"))
+        reducer.begin_backward(last=(fn != "accumulate"))  # every optimizer call needs the reduced gradient
     _backward(params)
-    if fn != "update":
+    if fn == "accumulate":
         return update_ops, learning_rate
     if reducer is not None:
         reducer.finish()
-    ctx = OptimizerCtx(params, update_ops, learning_rate, int(params.global_step) + 1, True)
+    ctx = OptimizerCtx(params, update_ops, learning_rate, int(params.global_step) + 1, fn == "update")
     update(ctx)
     return ctx.update_ops, learning_rate

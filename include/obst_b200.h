@@ -253,7 +253,8 @@ typedef struct obst_opt_tensor {
  * flags&1 ("carry"): sum cast_AT(p)^2 is NOT recomputed (4 B/param less traffic) but moved from
  * wnext[t], where the previous obst_opt_update accumulated it while writing p; wnext[t] is reset.
  * flags&4: sum g^2 is already in norms (obst_grad_finalize put it there): only the weight half is
- * produced (with flags&1 no gradient or weight is read at all). */
+ * produced (with flags&1 no gradient or weight is read at all).
+ * flags&8: the weight half is taken from the shadows (macro-batching chain, see obst_opt_update's preview). */
 int obst_opt_norms(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
                    const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
                    int32_t dtype_act, int32_t grad_bf16, double* norms, int32_t flags, double* wnext,
@@ -271,8 +272,12 @@ int obst_grad_finalize(const obst_opt_tensor* table, int32_t ntensors, const int
  * multiple of 4 (the streaming kernel; otherwise a slower generic kernel runs).  clip <= 0 skips
  * adaptive_clip (norms may then be NULL).
  * wnext (double[ntensors], may be NULL): += sum cast_AT(p_new)^2 per tensor, for the next step's carry.
- * preview != 0: nothing but `shadow` is written -- the weights the graph WOULD see after this update
- * (the reference's macro-batching chain, src/run/train.py:63-69, src/optimizer/__init__.py:65-66). */
+ * preview: the reference's macro-batching chain (src/run/train.py:35-74).  bit 0: a NON-FINAL macro-batch -- the
+ * optimizer state (m, accumulators) is updated, the master p is not, and `shadow` receives what the next
+ * macro-batch's graph reads: subtract(var.value, cast(update)) evaluated in the activation dtype
+ * (src/optimizer/__init__.py:65-66, src/optimizer/optimizers.py:25-29).  bit 1: the weight the graph sees (weight
+ * decay here, the clip norm via obst_opt_norms flags&8) is the shadow's current value instead of cast_AT(p) --
+ * macro-batches after the first read the chained weights.  0 = the ordinary committed update. */
 int obst_opt_update(const obst_opt_tensor* table, int32_t ntensors, const int32_t* item_tensor,
                     const int32_t* item_row0, const int32_t* item_rows, int32_t nitems,
                     int32_t max_cols, int32_t vec4, int32_t dtype_act, int32_t dtype_state,

@@ -668,11 +668,18 @@ def _apply_stage(opt: str, args, g, w, st, hyper):
     raise NotImplementedError(f"oracle: optimizer '{opt}'")
 
 
-def optimizer_step(sh: Shapes, params, grads, opt_state, lr: float, step_count: int = 1, optimizer: str = None):
+def optimizer_step(sh: Shapes, params, grads, opt_state, lr: float, step_count: int = 1, optimizer: str = None,
+                   seen=None, assign: bool = True):
     """In-place update of params (fp32 slices) and opt_state, all arithmetic in fp32
     (optimizer_calculation_dtype).  `grads` already carry the dtype the graph would hand over.
     update(), src/optimizer/__init__.py:31-66: the stages of the optimizer string in order, the weight-decay rule,
-    assign_sub.  step_count = global_step + 1 (`:96` with grad_accumulation 1); `optimizer` overrides sh.optimizer."""
+    assign_sub.  step_count = global_step + 1 (`:96` with grad_accumulation 1); `optimizer` overrides sh.optimizer.
+
+    Macro-batching (src/run/train.py:35-74): `seen` = the weights this macro-batch's graph read (ctx.value: the
+    chained tensors of the previous macro-batch; default: the cast of the slices); assign=False is the "add" arm --
+    optimizer slots still move on (assign_ctx's tensors replace the slot variables in params.variable_cache, so the
+    next macro-batch reads them), the slices stay, and the function returns what the next macro-batch's graph reads
+    in place of each variable: subtract(var.value, cast(update)) in the activation dtype (`__init__.py:65-66`)."""
     f32 = np.float32
     act_bf16 = sh.calculation_dtype == "bfloat16"
     st_bf16 = sh.optimizer_slice_dtype == "bfloat16"
@@ -682,15 +689,45 @@ def optimizer_step(sh: Shapes, params, grads, opt_state, lr: float, step_count: 
              "beta2": getattr(sh, "opt_beta2", 0.99),
              "global_sq": sum(float(np.sum(g.astype(np.float64) ** 2)) for g in grads.values()),
              "keep": (lambda v: round_bf16(np.asarray(v, f32))) if st_bf16 else (lambda v: np.asarray(v, f32))}
+    act = round_bf16 if act_bf16 else (lambda v: np.asarray(v, f32))
+    chained = {}
     for name, p in params.items():
         g = grads[name].astype(f32)
-        w = round_bf16(p) if act_bf16 else p  # var.value: the slice cast to the activation dtype
+        w = act(p) if seen is None else np.asarray(seen[name], f32)  # var.value / the chained tensor
         st = opt_state[name]
         for opt, *args in chain:
             g = _apply_stage(opt, args, g, w, st, hyper)
+        if "rezero" in name:  # __init__.py:46-47
+            g = g * f32(getattr(sh, "rezero_lr_multiplier", 0.1))
         if is_large_tensor(name) and sh.weight_decay > 0:  # __init__.py:49-61
             g = g + w * lr * f32(sh.weight_decay)
-        params[name] = (p - g).astype(f32)  # assign_sub on the fp32 slice, __init__.py:64
+        if assign:
+            params[name] = (p - g).astype(f32)  # assign_sub on the fp32 slice, __init__.py:64
+        else:
+            chained[name] = act(act(p) - act(g))  # subtract(ctx.var, cast(grad, calculation_dtype)), __init__.py:66
+    return None if assign else chained
+
+
+def train_step_macro(sh: Shapes, params, opt_state, tok_x, tok_y, global_step: int, macro: int, dtype=np.float64):
+    """get_train_model with macro_batching = macro (src/run/train.py:19-77): row b * macro + s belongs to slice s;
+    every slice is differentiated against the weights chained from the previous slice's non-assign update; only the
+    last slice's update reaches the slices.  Returns (mean loss, first loss, last loss, lr)."""
+    act_bf16 = sh.calculation_dtype == "bfloat16"
+    lr = learning_rate(sh, global_step)
+    seen = None
+    losses = []
+    for s in range(macro):
+        sx, sy = tok_x[s::macro], tok_y[s::macro]
+        graph_params = seen if seen is not None else (
+            {k: round_bf16(v) for k, v in params.items()} if act_bf16 else params)
+        loss, acc, state = forward(sh, graph_params, sx, sy, dtype=dtype)
+        grads = backward(sh, state)
+        if act_bf16:
+            grads = {k: round_bf16(v.astype(np.float32)) for k, v in grads.items()}
+        losses.append(loss)
+        seen = optimizer_step(sh, params, grads, opt_state, lr, step_count=global_step + 1, seen=seen,
+                              assign=s == macro - 1)
+    return float(np.mean(losses)), losses[0], losses[-1], lr
 
 
 def train_step(sh: Shapes, params, opt_state, tok_x, tok_y, global_step: int, dtype=np.float64):

@@ -725,3 +725,48 @@ def test_cumsum_and_cummean_layers(cuda, layer, dtype, tol):
     mean = layer == "cummean"
     assert rel(to_np(out.data), orc.cumsum_fwd(x.double().cpu().numpy(), 1, mean)) < tol
     assert rel(to_np(dx), orc.cumsum_bwd(dy.double().cpu().numpy(), 1, mean)) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [("float32", 1e-5), ("bfloat16", 2e-2)])
+def test_macro_batching_chain_matches_the_oracle(cuda, dtype, tol):
+    """macro_batching = 3 (src/run/train.py:35-74): three slices of the input, each differentiated against the
+    weights the previous slice's non-assign update WOULD have produced; optimizer slots move on every slice, the
+    master weights only take the last update.  Losses per slice, final weights and slots against the oracle's
+    train_step_macro; the product's micro-batching runs inside every slice as well."""
+    from obst.optimizer.backend import slot_name
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=64, macro_batching=3, calculation_dtype=dtype,
+               optimizer_slice_dtype=dtype)
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=21)
+    tok_x, tok_y = orc.synthetic_tokens(sh, batch=6)  # train_batch_size * macro_batching rows
+    params = make_params(cfg, op, micro_batch_size=1)
+    params.global_step = 3000
+    out, scal = run_product_step(params, tok_x, tok_y)
+    from obst.run.train import read_scalars
+    first, last = read_scalars(params, out[4])["loss"], read_scalars(params, out[5])["loss"]
+    oparams = {k: v.copy() for k, v in op.items()}
+    ost = orc.init_opt_state(op)
+    mean_loss, first_ref, last_ref, lr = orc.train_step_macro(sh, oparams, ost, tok_x, tok_y, 3000, 3)
+    ltol = 1e-5 if dtype == "float32" else 2e-2
+    assert abs(first - first_ref) / first_ref < ltol
+    assert abs(last - last_ref) / last_ref < ltol
+    assert abs(scal["loss"] - mean_loss) / mean_loss < ltol
+    assert abs(out[2] - lr) < 1e-12
+    assert params.global_step == 3003 and params.manual_global_step == 3
+    byname = variables_by_oracle_name(params, sh)
+    slots = params.optimizer_state.slots
+    # the slices' gradients differ between the two sides by the reconstruction noise of the reversible backward
+    # (budgeted elsewhere); the update is ~lr * sign-like, so weights are compared by their MOVE
+    for name, var in byname.items():
+        move, move_ref = to_np(var.data) - op[name], oparams[name] - op[name]
+        assert rel(to_np(var.data), oparams[name]) < (1e-5 if dtype == "float32" else 1e-3), name
+        assert rel(move, move_ref) < (5e-2 if dtype == "float32" else 0.5), (name, rel(move, move_ref))
+        m = to_np(slots[slot_name(params, var.name, "momentum")])
+        assert rel(m, ost[name]["momentum"]) < (5e-2 if dtype == "float32" else 0.5), name
+    # the shadows hold the committed weights again (not a chained preview)
+    for name, var in byname.items():
+        seen = orc.round_bf16(to_np(var.data)) if dtype == "bfloat16" else to_np(var.data)
+        if var.tril_s:
+            seen = np.tril(seen)
+        assert np.array_equal(to_np(var.value), seen), name
