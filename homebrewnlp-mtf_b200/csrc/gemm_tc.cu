@@ -43,6 +43,9 @@ struct TcParams {
   int32_t a_mn, b_mn;                  // 1 = MN-major operand
   int32_t a_uglo, a_ughi, a_uko;       // does the operand depend on g_lo / g_hi / ko
   int32_t b_uglo, b_ughi, b_uko;
+  const void* aux0;                    // epilogues 5..8, see obst_gemm_desc
+  const void* aux1;
+  const void* aux2;
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -423,6 +426,68 @@ __device__ __forceinline__ void epi_chunk(uint8_t* buf, int lane, const uint32_t
   }
 }
 
+// Epilogues 5 / 6: the group norm of the A operand folded into this GEMM (include/obst_b200.h):
+//   D = R +/- ( rstd[m] * acc - rstd[m] * mean[m] * c[n] + d[n] )
+// rs = rstd, rm = rstd * mean of this thread's row; cvec / dvec point at the chunk's 64 columns (every lane reads
+// the same addresses: one transaction per load).
+template <int EPI>
+__device__ __forceinline__ void epi_chunk_affine(uint8_t* buf, int lane, const uint32_t (&r)[64], float rs, float rm,
+                                                 const float* __restrict__ cvec, const float* __restrict__ dvec) {
+  uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4));
+    const float4 c0 = __ldg(reinterpret_cast<const float4*>(cvec + j * 8));
+    const float4 c1 = __ldg(reinterpret_cast<const float4*>(cvec + j * 8 + 4));
+    const float4 d0 = __ldg(reinterpret_cast<const float4*>(dvec + j * 8));
+    const float4 d1 = __ldg(reinterpret_cast<const float4*>(dvec + j * 8 + 4));
+    const float cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    const float dd[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+    const uint4 ru = *slot;
+    const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z), f3 = unpack_bf16x2(ru.w);
+    const float rr[8] = {f0.x, f0.y, f1.x, f1.y, f2.x, f2.y, f3.x, f3.y};
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float f = fmaf(rs, __uint_as_float(r[j * 8 + e]), fmaf(-rm, cc[e], dd[e]));
+      v[e] = EPI == 5 ? rr[e] + f : rr[e] - f;
+    }
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]);
+    o.w = pack_bf16x2(v[6], v[7]);
+    *slot = o;
+  }
+}
+
+// Epilogue 7: D = relu(acc), and the row's sum and sum of squares of the values AS STORED (bf16-rounded) are added to
+// (s1, s2): the statistics of the group norm that follows (src/model/basic.py:55-56), taken where the data is made.
+__device__ __forceinline__ void epi_chunk_relu_stats(uint8_t* buf, int lane, const uint32_t (&r)[64], float& s1,
+                                                     float& s2) {
+  uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4));
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) v[e] = fmaxf(__uint_as_float(r[j * 8 + e]), 0.f);
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]);
+    o.w = pack_bf16x2(v[6], v[7]);
+    *slot = o;
+    const uint32_t w[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float lo = __uint_as_float(w[q] << 16), hi = __uint_as_float(w[q] & 0xFFFF0000u);
+      s1 += lo + hi;
+      s2 = fmaf(lo, lo, fmaf(hi, hi, s2));
+    }
+  }
+}
+
 template <int CG>
 struct Cfg {
   static constexpr int STAGES = CG == 2 ? 5 : 3;
@@ -598,12 +663,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool live1 = c1 < nchunks && row0 < p.M && col1 < p.N;
         bulk_wait_read0_elect();  // last tile's stores have read both slabs (they were issued a whole tile ago)
         __syncwarp();
-        if (p.epi >= 2) {
+        const bool has_r = p.epi >= 2 && p.epi <= 6;
+        if (has_r) {
           if (live0) tma_load_r_elect(smem_u32(buf0), &tmR, smem_u32(rb0), EPI_BUF_BYTES, col0, row0, t.glo, t.ghi);
           if (live1)
             tma_load_r_elect(smem_u32(buf0 + EPI_BUF_BYTES), &tmR, smem_u32(rb0 + 1), EPI_BUF_BYTES, col1, row0, t.glo,
                              t.ghi);
         }
+        // epilogues 5 / 6: this thread's row statistics (mean, rstd) of the folded group norm
+        float rs = 0.f, rm = 0.f;
+        if (p.epi == 5 || p.epi == 6) {
+          if (row0 + lane < p.M) {
+            const float2 st = __ldg(reinterpret_cast<const float2*>(p.aux0) + (int64_t)(row0 + lane) * p.GLO + t.glo);
+            rs = st.y;
+            rm = st.y * st.x;
+          }
+        }
+        float s1 = 0.f, s2 = 0.f;  // epilogue 7
         mbar_wait(&tfull_bar[acc], acc_phase, 3);
         tcgen05_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
@@ -625,20 +701,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (!live) continue;
           uint8_t* const buf = buf0 + sl * EPI_BUF_BYTES;
           const uint32_t (&r)[64] = sl == 0 ? ra : rc;
-          if (p.epi >= 2) {
+          if (has_r) {
             mbar_wait(rb0 + sl, (rphase >> sl) & 1u, 4);
             rphase ^= 1u << sl;
           }
+          const int colx = sl == 0 ? col0 : col1;
           switch (p.epi) {
             case 0: epi_chunk<0>(buf, lane, r); break;
             case 1: epi_chunk<1>(buf, lane, r); break;
             case 2: epi_chunk<2>(buf, lane, r); break;
             case 3: epi_chunk<3>(buf, lane, r); break;
-            default: epi_chunk<4>(buf, lane, r); break;
+            case 4: epi_chunk<4>(buf, lane, r); break;
+            case 5:
+              epi_chunk_affine<5>(buf, lane, r, rs, rm,
+                                  reinterpret_cast<const float*>(p.aux1) + (int64_t)t.glo * p.N + colx,
+                                  reinterpret_cast<const float*>(p.aux2) + (int64_t)t.glo * p.N + colx);
+              break;
+            case 6:
+              epi_chunk_affine<6>(buf, lane, r, rs, rm,
+                                  reinterpret_cast<const float*>(p.aux1) + (int64_t)t.glo * p.N + colx,
+                                  reinterpret_cast<const float*>(p.aux2) + (int64_t)t.glo * p.N + colx);
+              break;
+            default: epi_chunk_relu_stats(buf, lane, r, s1, s2); break;
           }
           fence_async_smem();
           __syncwarp();
           tma_store_commit_elect(&tmD, smem_u32(buf), sl == 0 ? col0 : col1, row0, t.glo, t.ghi, 0);
+        }
+        if (p.epi == 7 && row0 + lane < p.M) {
+          // one (sum, sum of squares) per row, tile and epilogue warp: [M][2 * tiles_n] float2, summed by the consumer
+          float2* part = reinterpret_cast<float2*>(const_cast<void*>(p.aux0));
+          part[(int64_t)(row0 + lane) * (2 * p.tiles_n) + 2 * (t.n0 / p.BN) + half] = make_float2(s1, s2);
         }
         if (++acc == 2) {
           acc = 0;
@@ -656,6 +749,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int m = t.m0 + cta_m + quarter * 32 + lane;
         const bool row_ok = m < p.M;
         const int64_t row_off = (int64_t)t.glo * p.d_glo + (int64_t)t.ghi * p.d_ghi + (int64_t)m * p.d_ld;
+        // epilogue 8: every output row is scaled by aux0[g_lo, m] before it is accumulated
+        const float row_scale =
+            (p.epi == 8 && row_ok) ? __ldg(reinterpret_cast<const float*>(p.aux0) + (int64_t)t.glo * p.M + m) : 1.f;
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
         for (int c = half; c < p.BN / 32; c += 2) {
           uint32_t r[32];
@@ -674,7 +770,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
               if (p.out_f32) {
                 float* dp = reinterpret_cast<float*>(p.D) + row_off + n;
-                if (p.epi >= 2) {
+                if (p.epi >= 2 && p.epi <= 4) {
                   const float4 r0 =
                       *reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.R) + row_off + n);
                   const float4 r1 =
@@ -683,6 +779,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   rr[4] = r1.x; rr[5] = r1.y; rr[6] = r1.z; rr[7] = r1.w;
                 }
                 epi_apply(v, rr, p.epi);
+                if (p.epi == 8) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) v[j] *= row_scale;
+                }
                 if (p.accumulate) {
                   if (p.tri == 3 && n + 7 > m) {
 #pragma unroll
@@ -698,7 +798,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
               } else {
                 bf16* dp = reinterpret_cast<bf16*>(p.D) + row_off + n;
-                if (p.epi >= 2) {
+                if (p.epi >= 2 && p.epi <= 4) {
                   const uint4 ru = *reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.R) + row_off + n);
                   const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z),
                                f3 = unpack_bf16x2(ru.w);
@@ -920,13 +1020,22 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
       (reinterpret_cast<uintptr_t>(g.D) & 15) != 0 || (g.R && (reinterpret_cast<uintptr_t>(g.R) & 15) != 0))
     TC_NOTSUP("obst_gemm(tc): output not 16-byte addressable (N=%d ld=%lld)", g.N, (long long)g.d_ld);
   if (g.accumulate && !out_f32) TC_NOTSUP("obst_gemm(tc): accumulate needs fp32 output");
-  if (g.epi >= 2 && !g.R) TC_NOTSUP("obst_gemm(tc): epilogue %d needs R", g.epi);
+  if (g.epi >= 2 && g.epi <= 6 && !g.R) TC_NOTSUP("obst_gemm(tc): epilogue %d needs R", g.epi);
+  if ((g.epi == 5 || g.epi == 6) && (!g.aux0 || !g.aux1 || !g.aux2 || g.GHI != 1 || out_f32 || g.N % 64 != 0))
+    TC_NOTSUP("obst_gemm(tc): epilogue %d needs aux0..2, GHI == 1, bf16 output and N %% 64 == 0", g.epi);
+  if (g.epi == 7 && (!g.aux0 || out_f32 || g.N % 256 != 0 || g.GLO * g.GHI != 1))
+    TC_NOTSUP("obst_gemm(tc): epilogue 7 needs aux0, bf16 output, one group and N %% 256 == 0");
+  if (g.epi == 8 && (!g.aux0 || !g.accumulate || g.GHI != 1))
+    TC_NOTSUP("obst_gemm(tc): epilogue 8 needs aux0, accumulate and GHI == 1");
 #undef TC_NOTSUP
 
   TcParams p;
   memset(&p, 0, sizeof(p));
   p.D = g.D;
   p.R = g.R;
+  p.aux0 = g.aux0;
+  p.aux1 = g.aux1;
+  p.aux2 = g.aux2;
   p.d_ld = g.d_ld;
   p.d_glo = g.d_glo;
   p.d_ghi = g.d_ghi;
@@ -992,10 +1101,14 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   if (!out_f32 && !g.accumulate) {
     int rd = make_out_map(g.D, g.N, g.M, g.GLO, g.GHI, g.d_ld, g.d_glo, g.d_ghi, &tmD, strict);
     int rr = OBST_OK;
-    if (rd == OBST_OK && g.epi >= 2)
+    if (rd == OBST_OK && g.epi >= 2 && g.epi <= 6)
       rr = make_out_map(g.R, g.N, g.M, g.GLO, g.GHI, g.d_ld, g.d_glo, g.d_ghi, &tmR, strict);
     if (rd == OBST_ECUDA || rr == OBST_ECUDA) return OBST_ECUDA;
     p.tma_store = (rd == OBST_OK && rr == OBST_OK) ? 1 : 0;
+  }
+  if (g.epi >= 5 && g.epi <= 7 && !p.tma_store) {
+    if (strict) set_error("obst_gemm(tc): epilogue %d needs a TMA-addressable output", g.epi);
+    return OBST_ENOTSUP;
   }
 
   static bool attr_set = false;
@@ -1050,10 +1163,12 @@ extern "C" int obst_gemm(const obst_gemm_desc* d, int backend, void* stream) {
   OBST_REQUIRE(d->M > 0 && d->N > 0 && d->KI > 0 && d->KO > 0 && d->GLO > 0 && d->GHI > 0,
                "obst_gemm: bad sizes M=%d N=%d KI=%d KO=%d GLO=%d GHI=%d", d->M, d->N, d->KI, d->KO, d->GLO, d->GHI);
   OBST_REQUIRE(d->A.ptr && d->B.ptr && d->D, "obst_gemm: null operand");
-  OBST_REQUIRE(d->tri >= 0 && d->tri <= 3 && d->epi >= 0 && d->epi <= 4, "obst_gemm: bad tri/epi %d/%d", d->tri, d->epi);
-  OBST_REQUIRE(!(d->epi >= 2 && d->R == nullptr), "obst_gemm: epilogue %d needs R", d->epi);
+  OBST_REQUIRE(d->tri >= 0 && d->tri <= 3 && d->epi >= 0 && d->epi <= 8, "obst_gemm: bad tri/epi %d/%d", d->tri, d->epi);
+  OBST_REQUIRE(!(d->epi >= 2 && d->epi <= 6 && d->R == nullptr), "obst_gemm: epilogue %d needs R", d->epi);
   OBST_REQUIRE(!(d->accumulate && d->dtype_out != OBST_F32), "obst_gemm: accumulate needs fp32 output");
-  OBST_REQUIRE(!(d->accumulate && d->epi >= 2), "obst_gemm: accumulate cannot be combined with an R epilogue");
+  OBST_REQUIRE(!(d->accumulate && d->epi >= 2 && d->epi <= 7),
+               "obst_gemm: accumulate cannot be combined with an R epilogue");
+  OBST_REQUIRE(!(d->epi >= 5 && d->aux0 == nullptr), "obst_gemm: epilogue %d needs aux0", d->epi);
   OBST_REQUIRE(!((d->tri == 1 || d->tri == 2) && d->KO != 1), "obst_gemm: tri 1/2 need KO == 1");
   OBST_REQUIRE(!(d->tri == 3 && !d->accumulate), "obst_gemm: tri 3 needs accumulate");
   GemmParams p;
@@ -1064,7 +1179,12 @@ extern "C" int obst_gemm(const obst_gemm_desc* d, int backend, void* stream) {
   p.M = d->M; p.N = d->N; p.KI = d->KI; p.KO = d->KO; p.GLO = d->GLO; p.GHI = d->GHI;
   p.dtype_in = d->dtype_in; p.dtype_out = d->dtype_out;
   p.tri = d->tri; p.epi = d->epi; p.accumulate = d->accumulate; p.splits = d->splits;
+  p.aux0 = d->aux0; p.aux1 = d->aux1; p.aux2 = d->aux2;
   cudaStream_t st = (cudaStream_t)stream;
+  if (d->epi >= 5) {  // the fused-norm epilogues exist in the tcgen05 kernel only
+    OBST_REQUIRE(backend != 1, "obst_gemm: epilogue %d is not available in the SIMT kernel", d->epi);
+    return gemm_tc_launch(p, st, true);
+  }
   if (backend == 1) return gemm_simt_launch(p, st);
   if (backend == 2) return gemm_tc_launch(p, st, true);
   OBST_REQUIRE(backend == 0, "obst_gemm: bad backend %d", backend);

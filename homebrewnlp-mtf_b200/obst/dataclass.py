@@ -10,6 +10,8 @@ Extensions (no counterpart in the reference, all optional):
                     accumulated in fp32), None = whole local batch
   gemm_backend      0 auto | 1 SIMT | 2 tcgen05   (include/obst_b200.h)
   device            torch device string
+  fold_mid_norm     fold the group norm between W_mid and W_out into those two GEMMs (bf16, tcgen05 path): same
+                    function, the normalised tensor is never written (model/basic.py).  Default true.
   revnet_store_activations  keep every sub-block's intermediates instead of recomputing / reconstructing them in
                     backward (memory for speed; numerics differ from the reversible path only by the reference's
                     reconstruction rounding).  Default false = the reference's algorithm.
@@ -59,7 +61,7 @@ DEFAULTS: typing.Dict[str, typing.Any] = dict(
 )
 # extensions of this implementation (see module docstring)
 EXTENSIONS: typing.Dict[str, typing.Any] = dict(micro_batch_size=None, gemm_backend=0, device="cuda", init_seed=0,
-                                                revnet_store_activations=False)
+                                                revnet_store_activations=False, fold_mid_norm=True)
 
 
 class BlockConfig:

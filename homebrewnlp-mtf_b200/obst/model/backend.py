@@ -28,17 +28,21 @@ class Variable:
         self.dims = list(dims)
         self.shape = self.dims
         self.trainable = trainable
-        self.data = torch.from_numpy(np.ascontiguousarray(init, dtype=np.float32)).to(dev)  # slice_dtype fp32
+        init = np.asarray(init, dtype=np.float32)  # (np.ascontiguousarray would turn a rank-0 array into rank 1)
+        self.data = torch.tensor(init, dtype=torch.float32).to(dev).contiguous()  # slice_dtype fp32
         self.tril_s = 0          # >0: causal mask folded into the shadow (token-mixing maps)
         self.value: typing.Optional[torch.Tensor] = None
         self.value_t: typing.Optional[torch.Tensor] = None  # transposed shadow, see transposed()
         self._t_view: typing.Optional[typing.Tuple[int, int, int]] = None
         self.grad: typing.Optional[torch.Tensor] = None  # bound by the optimizer to a view of its flat buffer
         self._act_dtype = params.variable_dtype.activation_dtype
+        # macro-batching chains would-be weights through the shadow while the master stays put
+        # (src/run/train.py:63-69), so the shadow needs a buffer of its own even when the dtypes agree
+        self._own_shadow = int(getattr(params, "macro_batching", 1)) > 1
 
     def refresh(self):
         """(Re)build the shadow: cast of the fp32 slice to the activation dtype (mtf.Variable.value)."""
-        if self._act_dtype == torch.float32 and self.tril_s == 0:
+        if self._act_dtype == torch.float32 and self.tril_s == 0 and not self._own_shadow:
             self.value = self.data
         else:
             if self.value is None or self.value is self.data:
@@ -51,6 +55,30 @@ class Variable:
         every update, since its kernels rewrite `value` in place."""
         if self.value_t is not None:
             native.transpose_param(self.value.view(self._t_view), self.value_t)
+        self.refresh_folded()
+
+    # -- a group norm folded into this weight (basic._mid_norm_out_folded): (gamma . W)^T, gamma^T W, beta^T W ----
+    folded = None  # (gamma variable, beta variable, heads, kin, kout, wg_t, cvec, dvec, gamma_f)
+
+    def fold_norm(self, gamma: typing.Optional["Variable"], beta: typing.Optional["Variable"], heads: int, kin: int,
+                  kout: int):
+        if self.folded is None or self.folded[0] is not gamma or self.folded[1] is not beta:
+            dev = self.value.device
+            self.folded = (gamma, beta, heads, kin, kout,
+                           torch.empty((heads, kout, kin), dtype=self.value.dtype, device=dev),
+                           torch.empty((heads, kout), dtype=torch.float32, device=dev),
+                           torch.empty((heads, kout), dtype=torch.float32, device=dev),
+                           torch.empty((heads, kin), dtype=torch.float32, device=dev))
+            self.refresh_folded()
+        return self.folded[5:]
+
+    def refresh_folded(self):
+        """Called whenever this weight or the norm's scale / shift moved (the optimizer does, once per update)."""
+        if self.folded is None:
+            return
+        gamma, beta, heads, kin, kout, wg_t, cvec, dvec, gamma_f = self.folded
+        native.fold_norm_weight(self.value, None if gamma is None else gamma.value,
+                                None if beta is None else beta.value, wg_t, cvec, dvec, gamma_f, heads, kin, kout)
 
     def transposed(self, batch: int, rows: int, cols: int) -> torch.Tensor:
         """The shadow, seen as [batch, rows, cols], stored as [batch, cols, rows].  Forward GEMMs read the weight
@@ -240,10 +268,13 @@ def run_tape(tape: typing.List[TapeEntry], dy: typing.Optional[torch.Tensor],
 # ----------------------------------------------------------------------------------------------------------
 # linear
 # ----------------------------------------------------------------------------------------------------------
-def linear(args: BlockArgs, old: DIM_LIST, new: DIM_LIST, relu: bool = False) -> Tensor:
+def linear(args: BlockArgs, old: DIM_LIST, new: DIM_LIST, relu: bool = False,
+           relu_stats: typing.Optional[torch.Tensor] = None) -> Tensor:
     """einsum([tensor, W[old + new]]) -> (tensor.shape - old) + new, optional fused ReLU.
     If `args.params.residual` is set (by the reversible driver) the result is combined with that buffer in the
-    GEMM epilogue: out = residual +/- x@W, in place."""
+    GEMM epilogue: out = residual +/- x@W, in place.
+    relu_stats: fp32 [rows, N / 128, 2] buffer; with it the ReLU epilogue also emits the per-row partial sums of a
+    group norm that follows (obst_gemm epilogue 7)."""
     params = args.params
     x = args.tensor
     old, new = list(old), list(new)
@@ -286,8 +317,14 @@ def linear(args: BlockArgs, old: DIM_LIST, new: DIM_LIST, relu: bool = False) ->
                     GLO=G, d_ld=G * Np, d_glo=Np, R=buf, epi=2 if sign > 0 else 3, dtype_in=dt, backend=be)
     else:
         out = torch.empty([d.size for d in out_dims], dtype=dt, device=xin.device)
-        native.gemm(native.operand(xin, xld, 1, s_glo=xg), native.operand(wt, Kc, 1, s_glo=Kc * Np), out, M, Np, Kc,
-                    GLO=G, d_ld=G * Np, d_glo=Np, epi=1 if relu else 0, dtype_in=dt, backend=be)
+        if relu_stats is not None:
+            if not relu or G != 1:
+                raise NotImplementedError("linear: the statistics epilogue rides on an ungrouped ReLU linear")
+            native.gemm(native.operand(xin, xld, 1), native.operand(wt, Kc, 1), out, M, Np, Kc, d_ld=Np, epi=7,
+                        dtype_in=dt, backend=2, aux=(relu_stats,))
+        else:
+            native.gemm(native.operand(xin, xld, 1, s_glo=xg), native.operand(wt, Kc, 1, s_glo=Kc * Np), out, M, Np,
+                        Kc, GLO=G, d_ld=G * Np, d_glo=Np, epi=1 if relu else 0, dtype_in=dt, backend=be)
 
     if params.tape is not None:
         def bwd(dy: torch.Tensor, mask, acc):

@@ -11,7 +11,9 @@ from ..utils_mtf import DIM_LIST, Tensor, linear_shapes, shape_size, shape_sub
 from .backend import TapeEntry, normal_var
 
 
-def norm(args: BlockArgs, feature_shape: typing.Optional[DIM_LIST] = None, fuse_gelu: bool = False) -> Tensor:
+def norm_layout(args: BlockArgs, feature_shape: typing.Optional[DIM_LIST] = None):
+    """What norm() normalises over, and its scale / shift variables (created here, in the reference's order):
+    returns (heads, width, gamma, beta)."""
     params = args.params
     x = args.tensor
     feature_shape = list(linear_shapes(args).old if feature_shape is None else feature_shape)
@@ -27,6 +29,13 @@ def norm(args: BlockArgs, feature_shape: typing.Optional[DIM_LIST] = None, fuse_
     heads = shape_size(outer)
     gamma = normal_var(args, feature_shape, mean=1) if 'scale' in args else None
     beta = normal_var(args, feature_shape, mean=0) if 'shift' in args else None
+    return heads, width, gamma, beta
+
+
+def norm(args: BlockArgs, feature_shape: typing.Optional[DIM_LIST] = None, fuse_gelu: bool = False) -> Tensor:
+    params = args.params
+    x = args.tensor
+    heads, width, gamma, beta = norm_layout(args, feature_shape)
     act = 1 if fuse_gelu else 0
     xin = x.data
     y = torch.empty_like(xin)

@@ -31,7 +31,7 @@ class GemmDesc(ctypes.Structure):
     _fields_ = [("dtype_in", c_i32), ("dtype_out", c_i32), ("M", c_i32), ("N", c_i32), ("KI", c_i32), ("KO", c_i32),
                 ("GLO", c_i32), ("GHI", c_i32), ("A", Operand), ("B", Operand), ("D", c_void_p), ("R", c_void_p),
                 ("d_ld", c_i64), ("d_glo", c_i64), ("d_ghi", c_i64), ("tri", c_i32), ("epi", c_i32),
-                ("accumulate", c_i32), ("splits", c_i32)]
+                ("accumulate", c_i32), ("splits", c_i32), ("aux0", c_void_p), ("aux1", c_void_p), ("aux2", c_void_p)]
 
 
 class OptTensor(ctypes.Structure):
@@ -69,6 +69,11 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
                             c_void_p]),
     "obst_gn_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_i64, c_i32, c_i32, c_i32, c_i32, c_i32, c_void_p]),
+    "obst_norm_stats_finalize": (c_int, [c_void_p, c_void_p, c_i64, c_i32, c_i32, c_i32, c_void_p]),
+    "obst_fold_norm_weight": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i32, c_i32,
+                                      c_i32, c_void_p]),
+    "obst_rowscale_colsum": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
+    "obst_norm_wgrad_rank1": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_void_p]),
     "obst_act_fwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_act_bwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_gate_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
@@ -205,7 +210,7 @@ def gemm_profile(on: bool):
 def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO: int = 1, GLO: int = 1, GHI: int = 1,
          d_ld: int, d_glo: int = 0, d_ghi: int = 0, d_offset: int = 0, R: typing.Optional[torch.Tensor] = None,
          r_offset: typing.Optional[int] = None, tri: int = 0, epi: int = 0, accumulate: bool = False, splits: int = 0,
-         dtype_in: torch.dtype = torch.bfloat16, backend: int = 0):
+         dtype_in: torch.dtype = torch.bfloat16, backend: int = 0, aux=()):
     """D[g,m,n] = epi(sum_k A[g,m,k] B[g,n,k]) -- see include/obst_b200.h for the full semantics."""
     _cuda(D, R)
     desc = GemmDesc()
@@ -221,6 +226,9 @@ def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO
         desc.R = None
     desc.d_ld, desc.d_glo, desc.d_ghi = d_ld, d_glo, d_ghi
     desc.tri, desc.epi, desc.accumulate, desc.splits = tri, epi, int(accumulate), splits
+    for i, a in enumerate(aux):  # epilogues 5..8: row statistics / folded-norm vectors / row scales
+        _cuda(a)
+        setattr(desc, f"aux{i}", a.data_ptr())
     if _PROFILE is not None:
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
@@ -319,6 +327,32 @@ def dropout(x, out, keep: float, seed: int):
     _cuda(x, out)
     check(load().obst_dropout(dtype_code(x.dtype), _p(x), _p(out), x.numel(), float(keep), int(seed) & (2 ** 64 - 1),
                               stream_ptr()), "obst_dropout")
+
+
+def norm_stats_finalize(partials, stats, rows: int, heads: int, per_head: int, width: int):
+    _cuda(partials, stats)
+    check(load().obst_norm_stats_finalize(_p(partials), _p(stats), rows, heads, per_head, width, stream_ptr()),
+          "obst_norm_stats_finalize")
+
+
+def fold_norm_weight(w, gamma, beta, wg_t, cvec, dvec, gamma_f, heads: int, kin: int, kout: int):
+    _cuda(w, wg_t, cvec, dvec, gamma_f)
+    if w.dtype != torch.bfloat16:
+        raise NativeError("fold_norm_weight: bf16 weights only")
+    check(load().obst_fold_norm_weight(_p(w), _p(gamma), _p(beta), _p(wg_t), _p(cvec), _p(dvec), _p(gamma_f), heads, kin,
+                                       kout, stream_ptr()), "obst_fold_norm_weight")
+
+
+def rowscale_colsum(dy, stats, dyr, v1, v2, tokens: int, heads: int, width: int):
+    _cuda(dy, stats, dyr, v1, v2)
+    check(load().obst_rowscale_colsum(_p(dy), _p(stats), _p(dyr), _p(v1), _p(v2), tokens, heads, width, stream_ptr()),
+          "obst_rowscale_colsum")
+
+
+def norm_wgrad_rank1(dw, gamma, beta, v1, v2, heads: int, kin: int, kout: int):
+    _cuda(dw, v1, v2)
+    check(load().obst_norm_wgrad_rank1(_p(dw), _p(gamma), _p(beta), _p(v1), _p(v2), heads, kin, kout, stream_ptr()),
+          "obst_norm_wgrad_rank1")
 
 
 def cumsum(x, out, outer: int, seq: int, inner: int, reverse: bool = False, scale: int = 0):

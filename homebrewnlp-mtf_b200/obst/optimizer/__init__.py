@@ -221,6 +221,8 @@ class FusedOptimizer:
 
     def refresh_transposed(self):
         """Rewrite every transposed weight shadow from the shadow the update kernel just wrote: one launch."""
+        for v in self.variables:  # weights with a group norm folded into them (basic._mid_norm_out_folded)
+            v.refresh_folded()
         pairs = [(v, v.value, v.value_t) for v in self.variables if v.value_t is not None]
         if not pairs:
             return

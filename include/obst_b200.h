@@ -70,6 +70,15 @@ int64_t obst_path_count(int32_t which);
  *        2 promise: A(g,m,k) == 0 for k < m, likewise
  *        3 only outputs with n <= m are accumulated (requires accumulate != 0)
  *   epi: 0 D=acc | 1 D=relu(acc) | 2 D=R+acc | 3 D=R-acc | 4 D=acc*[R>0]
+ *        5/6 (tcgen05 backend, bf16 out, GHI == 1): a group norm of the A operand folded into this GEMM --
+ *            D = R +/- ( rstd[m,g]*acc - rstd[m,g]*mean[m,g]*c[g,n] + d[g,n] )
+ *            aux0 = float2 (mean, rstd) per (m, g_lo) [M, GLO]; aux1 = c, aux2 = d: fp32 [GLO, N]
+ *            (norm -> linear, src/model/basic.py:55-56,122-126, evaluated as r*(h@(gamma.W)) - r*mu*(gamma^T W)
+ *            + beta^T W: B holds gamma.W, c = gamma^T W, d = beta^T W -- see obst_fold_norm_weight)
+ *        7 (tcgen05 backend, bf16 out, one group, N % 256 == 0): D = relu(acc), and aux0 (float2
+ *            [M, N/128]) receives per row and 128-column slice the (sum, sum of squares) of the stored values:
+ *            entry [m, 2*(n/256) + w] covers columns 256*(n/256) + 64*(w + 2i) .. +63, i = 0, 1
+ *        8 (tcgen05 backend, accumulate): D += aux0[g_lo, m] * acc, aux0 fp32 [GLO, M]
  *   accumulate!=0: D (fp32 only) += value with atomics (split-K allowed; tri==3 masks the store)
  *   D/R address: ptr[g_lo*d_glo + g_hi*d_ghi + m*d_ld + n]; R may alias D.
  * backend: 0 auto (tcgen05 when dtype_in is bf16 and the geometry is TMA-legal, else SIMT),
@@ -97,6 +106,9 @@ typedef struct obst_gemm_desc {
   int32_t epi;
   int32_t accumulate;
   int32_t splits; /* split-K factor for accumulate mode; 0 = choose */
+  const void* aux0; /* epilogues 5..8, else NULL */
+  const void* aux1;
+  const void* aux2;
 } obst_gemm_desc;
 
 int obst_gemm(const obst_gemm_desc* desc, int backend, void* stream);
@@ -122,6 +134,32 @@ int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, con
                 void* dx, float* dgamma, float* dbeta, const float* stats, int64_t rows,
                 int32_t heads, int32_t width, int32_t act, int32_t relu_mask, int32_t dx_accumulate,
                 void* stream);
+
+/* ---- group norm folded into the neighbouring GEMMs (bf16 activations) -------------------------------
+ * bottleneck_group_linear's mid/out pair (src/model/basic.py:47-57,122-126): out = norm(h) @ W per head with
+ * h = relu(h1 @ W_mid).  With n = (h - mu) r gamma + beta:
+ *   n @ W = r (h @ (gamma.W)) - r mu (gamma^T W) + beta^T W,
+ *   dW[j,k] = gamma_j ( sum_t h[t,j] r_t dy[t,k] - sum_t r_t mu_t dy[t,k] ) + beta_j sum_t dy[t,k],
+ * so the normalised tensor is never written: obst_gemm epilogue 7 emits the statistics with h, epilogues 5/6
+ * apply the norm to W_out's accumulator, epilogue 8 scales the weight gradient's rows, and:
+ *   obst_norm_stats_finalize  partials float2 [rows, heads, per_head] (epilogue 7's layout with rows of
+ *                             heads * per_head slices of 128 columns; width = 128 * per_head) -> stats float2
+ *                             (mean, rstd) [rows, heads], the array obst_gn_bwd accepts
+ *   obst_fold_norm_weight     w AT [heads, kin, kout], gamma / beta AT [heads, kin] (NULL = 1 / 0) ->
+ *                             wg_t AT [heads, kout, kin] = (gamma.W)^T, cvec = gamma^T W and dvec = beta^T W
+ *                             fp32 [heads, kout], gamma_f fp32 [heads, kin]; once per weight update
+ *   obst_rowscale_colsum      dyr = rstd . dy (AT [tokens, heads, width]), v1[h,:] += sum_t rstd mean dy,
+ *                             v2[h,:] += sum_t dy (fp32 [heads, width], atomics; width 256 or 512)
+ *   obst_norm_wgrad_rank1     dw[h,j,k] += -gamma[h,j] v1[h,k] + beta[h,j] v2[h,k]   (dw fp32 [heads, kin, kout])
+ * AT is bfloat16 here. */
+int obst_norm_stats_finalize(const float* partials, float* stats, int64_t rows, int32_t heads, int32_t per_head,
+                             int32_t width, void* stream);
+int obst_fold_norm_weight(const void* w, const void* gamma, const void* beta, void* wg_t, float* cvec, float* dvec,
+                          float* gamma_f, int32_t heads, int32_t kin, int32_t kout, void* stream);
+int obst_rowscale_colsum(const void* dy, const float* stats, void* dyr, float* v1, float* v2, int64_t tokens,
+                         int32_t heads, int32_t width, void* stream);
+int obst_norm_wgrad_rank1(float* dw, const void* gamma, const void* beta, const float* v1, const float* v2,
+                          int32_t heads, int32_t kin, int32_t kout, void* stream);
 
 /* ---- activations, src/model/activation.py:158-169,201-211 ---------------------------------------
  * kind: 0 relu | 1 OBST gelu 0.5x(1+tanh(0.044715x^3+sqrt(2/pi)x)) | 2.. the other entries of ACTIVATIONS

@@ -164,30 +164,38 @@ def test_fused_update_is_bit_identical_to_the_op_by_op_chain(nat, act_bf16, stat
                 assert torch.equal(bank.g_lp[ti].float().cpu(), torch.from_numpy(handed[n])), (step, n)
 
 
-def test_preview_writes_only_the_shadow(nat):
-    """preview != 0 (the reference's non-final macro-batches): the shadow shows the weights after the update, nothing
-    else changes -- a committed update from the same state then gives exactly that shadow."""
+def test_macro_batching_mode_moves_the_state_but_not_the_master(nat):
+    """preview bit 0 (the reference's non-final macro-batches, src/run/train.py:63-69): momentum and accumulators
+    are updated exactly as by a committed update, the master stays, and the shadow receives
+    cast(cast(p) - cast(update)) -- the value the next macro-batch's graph reads."""
     shapes = [(8, 96, 128), (4, 64, 64)]
     a = Bank(nat, shapes, torch.bfloat16, True, True, [0, 64], [1, 0])
     b = Bank(nat, shapes, torch.bfloat16, True, True, [0, 64], [1, 0])
     gen = torch.Generator().manual_seed(3)
     grads = [(torch.randn(s, generator=gen) * 1e-2).to(DEV) for s in shapes]
     hyper = (0.003, 0.9, 1, 0.01, 1e-4)
-    b.step(grads, hyper)
+    p0 = [t.clone() for t in b.p]
+    b.step(grads, hyper)  # the committed update: reference for the state and for the size of the update
     lib, st = nat.load(), nat.stream_ptr()
     for dst, g in zip(a.g_acc, grads):
         dst.copy_(g)
-    before = [t.clone() for t in a.p + a.m + [x for acc in a.acc for x in acc]]
     args = (a.table.data_ptr(), a.n, a.it.data_ptr(), a.ir0.data_ptr(), a.irs.data_ptr(), a.n_items)
     nat.check(lib.obst_grad_finalize(*args, a.norms.data_ptr(), 1, st), "obst_grad_finalize")
     nat.check(lib.obst_opt_norms(*args, nat.BF16, 0, a.norms.data_ptr(), 6, a.wnext.data_ptr(), 0, a.n, st), "norms")
     nat.check(lib.obst_opt_update(*args, a.max_cols, 1, nat.BF16, nat.BF16, 2, a.norms.data_ptr(), None, *hyper, 1, st),
               "obst_opt_update")
+    nat.check(lib.obst_opt_finalize(a.table.data_ptr(), a.n, nat.BF16, st), "obst_opt_finalize")
     torch.cuda.synchronize()
-    after = a.p + a.m + [x for acc in a.acc for x in acc]
-    assert all(torch.equal(x, y) for x, y in zip(before, after))
-    assert all(float(x.abs().max()) == 0.0 for acc in a.acc_new for x in acc)
-    assert all(torch.equal(x, y) for x, y in zip(a.shadow, b.shadow))
+    for i in range(len(shapes)):
+        assert torch.equal(a.p[i], p0[i])                       # master untouched
+        assert torch.equal(a.m[i], b.m[i])                      # state as after a committed update
+        assert all(torch.equal(x, y) for x, y in zip(a.acc[i], b.acc[i]))
+        step = (p0[i] - b.p[i])                                 # the update the committed path applied (fp32)
+        want = (p0[i].bfloat16().float() - step.bfloat16().float()).bfloat16()
+        if i == 1:
+            want = torch.tril(want)
+        # p0 - b.p re-derives the update with one extra rounding: allow the last bf16 bit
+        assert float((a.shadow[i].float() - want.float()).abs().max()) <= float(want.float().abs().max()) * 2 ** -7
 
 
 def test_transpose_batched(nat):

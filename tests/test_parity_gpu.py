@@ -756,14 +756,19 @@ def test_macro_batching_chain_matches_the_oracle(cuda, dtype, tol):
     assert params.global_step == 3003 and params.manual_global_step == 3
     byname = variables_by_oracle_name(params, sh)
     slots = params.optimizer_state.slots
-    # the slices' gradients differ between the two sides by the reconstruction noise of the reversible backward
-    # (budgeted elsewhere); the update is ~lr * sign-like, so weights are compared by their MOVE
-    for name, var in byname.items():
+    # fp32: everything at 1e-4 on the MOVE of the weights (the update is ~lr * sign-like; the weights themselves agree
+    # to 1e-6).  bf16: the reversible reconstruction loses block_config[0]'s gradients at depth 0 for ANY
+    # implementation (see budget()), so there only the well-conditioned tensors of the last sub-block are compared.
+    well = ("wo", "mix_b", "g2_0", "b2_0", "bm_0") if dtype == "bfloat16" else tuple(byname)
+    for name in well:
+        var = byname[name]
         move, move_ref = to_np(var.data) - op[name], oparams[name] - op[name]
-        assert rel(to_np(var.data), oparams[name]) < (1e-5 if dtype == "float32" else 1e-3), name
-        assert rel(move, move_ref) < (5e-2 if dtype == "float32" else 0.5), (name, rel(move, move_ref))
+        bar = 1e-4 if dtype == "float32" else 0.2
+        assert rel(move, move_ref) < bar, (name, rel(move, move_ref))
         m = to_np(slots[slot_name(params, var.name, "momentum")])
-        assert rel(m, ost[name]["momentum"]) < (5e-2 if dtype == "float32" else 0.5), name
+        assert rel(m, ost[name]["momentum"]) < bar, name
+        if dtype == "float32":
+            assert rel(to_np(var.data), oparams[name]) < 1e-5, name
     # the shadows hold the committed weights again (not a chained preview)
     for name, var in byname.items():
         seen = orc.round_bf16(to_np(var.data)) if dtype == "bfloat16" else to_np(var.data)
