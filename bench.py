@@ -40,6 +40,9 @@ def parse():
     ap.add_argument("--depth", type=int, default=0, help="override depth (debug only: makes the number INVALID)")
     ap.add_argument("--cpu-rows", type=int, default=1, help="sequences per step of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fold-norm", action="store_true",
+                    help="A/B switch: run the group norm between W_mid and W_out as its own kernel instead of folding "
+                         "it into the two GEMMs")
     ap.add_argument("--store-activations", action="store_true",
                     help="extension: keep activations instead of the reference's reversible recompute (reported "
                          "separately; the default run is the reference algorithm)")
@@ -377,6 +380,7 @@ def run_b200(args):
     rows = r1 - r0
     mb = args.micro_batch or max(1, min(rows, (32768 if args.store_activations else 131072) // seq))
     cfg["revnet_store_activations"] = bool(args.store_activations)
+    cfg["fold_mid_norm"] = not args.no_fold_norm
     cfg["micro_batch_size"] = mb
     cfg["device"] = f"cuda:{local_rank}"
     import contextlib
