@@ -1055,6 +1055,13 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   }();
   int cg = (p.BN >= 128 && g.M > BM) ? 2 : 1;
   if (force_cg == 1) cg = 1;
+  // causal (triangular) products: a 256-row pair tile straddling the diagonal executes MACs a 128-row tile skips;
+  // OBST_GEMM_TRI_CTA_GROUP=1 runs those GEMMs with 128-row tiles (A/B switch)
+  static const int tri_cg = [] {
+    const char* e = getenv("OBST_GEMM_TRI_CTA_GROUP");
+    return e ? atoi(e) : 0;
+  }();
+  if (tri_cg == 1 && (g.tri == 1 || g.tri == 2)) cg = 1;
   p.tiles_m = (g.M + BM * cg - 1) / (BM * cg);
   p.tiles_n = (g.N + p.BN - 1) / p.BN;
   p.tri = g.tri;
