@@ -35,11 +35,16 @@ __global__ void __launch_bounds__(256) norm_stats_kernel(const float2* __restric
 
 // gamma . W (transposed for the forward GEMM's K-major B operand), c = gamma^T W, d = beta^T W, and gamma as fp32.
 // One block per (32 output features, head): it walks the whole contraction axis, so the two vectors need no atomics.
-__global__ void __launch_bounds__(256) fold_norm_weight_kernel(const bf16* __restrict__ w, const bf16* __restrict__ gamma,
-                                                                const bf16* __restrict__ beta, bf16* __restrict__ wg_t,
-                                                                float* __restrict__ cvec, float* __restrict__ dvec,
-                                                                float* __restrict__ gamma_f, int heads, int kin,
-                                                                int kout) {
+__global__ void __launch_bounds__(256) fold_norm_weight_kernel(const obst_fold_item* __restrict__ items, int heads,
+                                                                int kin, int kout) {
+  const obst_fold_item it = items[blockIdx.z];  // blockIdx.z: which weight of a batched refresh
+  const bf16* __restrict__ w = reinterpret_cast<const bf16*>(it.w);
+  const bf16* __restrict__ gamma = reinterpret_cast<const bf16*>(it.gamma);
+  const bf16* __restrict__ beta = reinterpret_cast<const bf16*>(it.beta);
+  bf16* __restrict__ wg_t = reinterpret_cast<bf16*>(it.wg_t);
+  float* __restrict__ cvec = it.cvec;
+  float* __restrict__ dvec = it.dvec;
+  float* __restrict__ gamma_f = it.gamma_f;
   __shared__ bf16 tile[32][33];
   __shared__ float s_c[8][32], s_d[8][32];
   const int h = blockIdx.y;
@@ -182,13 +187,13 @@ int obst_norm_stats_finalize(const float* partials, float* stats, int64_t rows, 
   return check_launch("obst_norm_stats_finalize");
 }
 
-int obst_fold_norm_weight(const void* w, const void* gamma, const void* beta, void* wg_t, float* cvec, float* dvec,
-                          float* gamma_f, int32_t heads, int32_t kin, int32_t kout, void* stream) {
-  OBST_REQUIRE(w && wg_t && cvec && dvec && gamma_f && heads > 0 && kin > 0 && kout > 0,
-               "obst_fold_norm_weight: bad arguments");
-  const dim3 grid((unsigned)((kout + 31) / 32), (unsigned)heads);
-  fold_norm_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)w, (const bf16*)gamma, (const bf16*)beta,
-                                                                   (bf16*)wg_t, cvec, dvec, gamma_f, heads, kin, kout);
+int obst_fold_norm_weight(const obst_fold_item* items, int32_t nitems, int32_t heads, int32_t kin, int32_t kout,
+                          void* stream) {
+  OBST_REQUIRE(nitems >= 0 && nitems <= 65535 && heads > 0 && kin > 0 && kout > 0, "obst_fold_norm_weight: bad arguments");
+  if (nitems == 0) return OBST_OK;
+  OBST_REQUIRE(items != nullptr, "obst_fold_norm_weight: null item table");
+  const dim3 grid((unsigned)((kout + 31) / 32), (unsigned)heads, (unsigned)nitems);
+  fold_norm_weight_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(items, heads, kin, kout);
   count_launch();
   return check_launch("obst_fold_norm_weight");
 }

@@ -1,13 +1,21 @@
 // tcgen05 / TMEM / TMA implementation of the obst_gemm descriptor for bf16 operands (sm_100a).
 //
-// One persistent, warp-specialised kernel serves every contraction of the mixer step:
-//   warp 0      : TMA producer   (cp.async.bulk.tensor, 5-D maps, 128B swizzle, 4-stage mbarrier ring)
-//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (128 x BN x 16, fp32 accumulate in TMEM)
-//   warps 2..5  : epilogue       (tcgen05.ld 32x32b -> registers -> fused op -> 16-byte global stores / fp32 red)
-// Two 256-column TMEM accumulators let the epilogue of tile i overlap the MMAs of tile i+1.
-// Operands may be K-major or MN-major in global memory (the smem/instruction descriptors carry the
-// majorness), so forward, dgrad and wgrad all read the tensors where they lie: no transposes.
+// One persistent, warp-specialised kernel (352 threads, one CTA per SM) serves every contraction of the mixer step.
+// Default: CTA PAIRS (cta_group::2, cluster (2,1,1)): one 256-row x BN tile per pair, each CTA stages its 128 rows
+// of A and half of B, the leader's MMA thread issues 256 x BN x 16 UMMAs over both CTAs' shared memory.
+//   warp 0      : TMA producer for A (cp.async.bulk.tensor, 5-D maps, 128B swizzle, 5-stage mbarrier ring)
+//   warp 10     : TMA producer for B (an MN-major operand needs one box per 64 elements: its own warp)
+//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (fp32 accumulate in TMEM, two 256-column
+//                 accumulators: the epilogue of tile i overlaps the MMAs of tile i + 1)
+//   warps 2..9  : epilogue, two warps per TMEM lane quarter: tcgen05.ld 32x32b -> registers (accumulator released at
+//                 once) -> fused op -> 128B-swizzled shared-memory slab -> TMA store; the residual / ReLU-mask
+//                 operand R arrives by TMA load into the same slab; fp32 (wgrad) outputs use red.global.add.v4.f32
+// Producer and issuer loops are warp-uniform with one elected lane (elect.sync inside the asm statement).
+// Operands may be K-major or MN-major in global memory (the smem/instruction descriptors carry the majorness), so
+// forward, dgrad and wgrad all read the tensors where they lie: no activation is ever transposed.
 // Triangular modes skip whole k-blocks / output tiles of the causal token-mixing matrices.
+// Fused epilogues: ReLU, residual +/-, ReLU-backward mask, and the group norm around the bottleneck's W_mid / W_out
+// pair (5-8: row statistics out, norm applied to the accumulator, row-scaled weight gradient) -- include/obst_b200.h.
 #include <cuda.h>
 #include <stdlib.h>
 

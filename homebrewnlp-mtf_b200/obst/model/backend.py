@@ -72,13 +72,19 @@ class Variable:
             self.refresh_folded()
         return self.folded[5:]
 
+    def fold_entry(self):
+        """(w, gamma, beta, wg_t, cvec, dvec, gamma_f): one row of a native.fold_items table."""
+        gamma, beta, heads, kin, kout, wg_t, cvec, dvec, gamma_f = self.folded
+        return (self.value, None if gamma is None else gamma.value, None if beta is None else beta.value, wg_t, cvec,
+                dvec, gamma_f)
+
     def refresh_folded(self):
-        """Called whenever this weight or the norm's scale / shift moved (the optimizer does, once per update)."""
+        """Called whenever this weight or the norm's scale / shift moved outside the optimizer (creation, weight
+        import, checkpoint restore); the optimizer refreshes all folded weights of a shape in one launch."""
         if self.folded is None:
             return
-        gamma, beta, heads, kin, kout, wg_t, cvec, dvec, gamma_f = self.folded
-        native.fold_norm_weight(self.value, None if gamma is None else gamma.value,
-                                None if beta is None else beta.value, wg_t, cvec, dvec, gamma_f, heads, kin, kout)
+        heads, kin, kout = self.folded[2:5]
+        native.fold_norm_weight(native.fold_items([self.fold_entry()]), 1, heads, kin, kout)
 
     def transposed(self, batch: int, rows: int, cols: int) -> torch.Tensor:
         """The shadow, seen as [batch, rows, cols], stored as [batch, cols, rows].  Forward GEMMs read the weight

@@ -40,6 +40,11 @@ class OptTensor(ctypes.Structure):
                 ("decay", c_i32), ("tril_s", c_i32), ("g_bf16", c_i32)]
 
 
+class FoldItem(ctypes.Structure):  # obst_fold_item
+    _fields_ = [("w", c_void_p), ("gamma", c_void_p), ("beta", c_void_p), ("wg_t", c_void_p), ("cvec", c_void_p),
+                ("dvec", c_void_p), ("gamma_f", c_void_p)]
+
+
 class TransposeItem(ctypes.Structure):  # obst_transpose_item
     _fields_ = [("src", c_void_p), ("dst", c_void_p), ("batch", c_i32), ("rows", c_i32), ("cols", c_i32),
                 ("tile0", c_i32)]
@@ -70,8 +75,7 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_gn_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                             c_i64, c_i32, c_i32, c_i32, c_i32, c_i32, c_void_p]),
     "obst_norm_stats_finalize": (c_int, [c_void_p, c_void_p, c_i64, c_i32, c_i32, c_i32, c_void_p]),
-    "obst_fold_norm_weight": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i32, c_i32,
-                                      c_i32, c_void_p]),
+    "obst_fold_norm_weight": (c_int, [c_void_p, c_i32, c_i32, c_i32, c_i32, c_void_p]),
     "obst_rowscale_colsum": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
     "obst_norm_wgrad_rank1": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_void_p]),
     "obst_act_fwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_i64, c_void_p]),
@@ -335,12 +339,20 @@ def norm_stats_finalize(partials, stats, rows: int, heads: int, per_head: int, w
           "obst_norm_stats_finalize")
 
 
-def fold_norm_weight(w, gamma, beta, wg_t, cvec, dvec, gamma_f, heads: int, kin: int, kout: int):
-    _cuda(w, wg_t, cvec, dvec, gamma_f)
-    if w.dtype != torch.bfloat16:
-        raise NativeError("fold_norm_weight: bf16 weights only")
-    check(load().obst_fold_norm_weight(_p(w), _p(gamma), _p(beta), _p(wg_t), _p(cvec), _p(dvec), _p(gamma_f), heads, kin,
-                                       kout, stream_ptr()), "obst_fold_norm_weight")
+def fold_items(entries) -> torch.Tensor:
+    """Device table of obst_fold_item from (w, gamma, beta, wg_t, cvec, dvec, gamma_f) tensor tuples."""
+    items = (FoldItem * len(entries))()
+    for it, (w, gamma, beta, wg_t, cvec, dvec, gamma_f) in zip(items, entries):
+        _cuda(w, wg_t, cvec, dvec, gamma_f)
+        if w.dtype != torch.bfloat16:
+            raise NativeError("fold_norm_weight: bf16 weights only")
+        it.w, it.gamma, it.beta, it.wg_t = _p(w), _p(gamma), _p(beta), _p(wg_t)
+        it.cvec, it.dvec, it.gamma_f = _p(cvec), _p(dvec), _p(gamma_f)
+    return torch.frombuffer(bytearray(bytes(items)), dtype=torch.uint8).to(entries[0][0].device)
+
+
+def fold_norm_weight(table: torch.Tensor, nitems: int, heads: int, kin: int, kout: int):
+    check(load().obst_fold_norm_weight(_p(table), nitems, heads, kin, kout, stream_ptr()), "obst_fold_norm_weight")
 
 
 def rowscale_colsum(dy, stats, dyr, v1, v2, tokens: int, heads: int, width: int):

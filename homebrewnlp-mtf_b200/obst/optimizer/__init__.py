@@ -221,8 +221,19 @@ class FusedOptimizer:
 
     def refresh_transposed(self):
         """Rewrite every transposed weight shadow from the shadow the update kernel just wrote: one launch."""
-        for v in self.variables:  # weights with a group norm folded into them (basic._mid_norm_out_folded)
-            v.refresh_folded()
+        # weights with a group norm folded into them (basic._mid_norm_out_folded): one launch per shape
+        folded = [v for v in self.variables if v.folded is not None]
+        if folded:
+            sig = tuple((v.value.data_ptr(), v.folded[5].data_ptr()) for v in folded)
+            if sig != self.__dict__.get("_fold_sig"):
+                groups: typing.Dict[tuple, list] = {}
+                for v in folded:
+                    groups.setdefault(tuple(v.folded[2:5]), []).append(v.fold_entry())
+                self._fold_tables = [(native.fold_items(entries), len(entries), shape)
+                                     for shape, entries in groups.items()]
+                self._fold_sig = sig
+            for table, n, (heads, kin, kout) in self._fold_tables:
+                native.fold_norm_weight(table, n, heads, kin, kout)
         pairs = [(v, v.value, v.value_t) for v in self.variables if v.value_t is not None]
         if not pairs:
             return

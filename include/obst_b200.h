@@ -145,17 +145,27 @@ int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, con
  *   obst_norm_stats_finalize  partials float2 [rows, heads, per_head] (epilogue 7's layout with rows of
  *                             heads * per_head slices of 128 columns; width = 128 * per_head) -> stats float2
  *                             (mean, rstd) [rows, heads], the array obst_gn_bwd accepts
- *   obst_fold_norm_weight     w AT [heads, kin, kout], gamma / beta AT [heads, kin] (NULL = 1 / 0) ->
- *                             wg_t AT [heads, kout, kin] = (gamma.W)^T, cvec = gamma^T W and dvec = beta^T W
- *                             fp32 [heads, kout], gamma_f fp32 [heads, kin]; once per weight update
+ *   obst_fold_norm_weight     for each item of a DEVICE table (all weights of one shape in one launch, once per
+ *                             weight update): w AT [heads, kin, kout], gamma / beta AT [heads, kin] (NULL = 1 / 0)
+ *                             -> wg_t AT [heads, kout, kin] = (gamma.W)^T, cvec = gamma^T W and dvec = beta^T W
+ *                             fp32 [heads, kout], gamma_f fp32 [heads, kin]
  *   obst_rowscale_colsum      dyr = rstd . dy (AT [tokens, heads, width]), v1[h,:] += sum_t rstd mean dy,
  *                             v2[h,:] += sum_t dy (fp32 [heads, width], atomics; width 256 or 512)
  *   obst_norm_wgrad_rank1     dw[h,j,k] += -gamma[h,j] v1[h,k] + beta[h,j] v2[h,k]   (dw fp32 [heads, kin, kout])
  * AT is bfloat16 here. */
 int obst_norm_stats_finalize(const float* partials, float* stats, int64_t rows, int32_t heads, int32_t per_head,
                              int32_t width, void* stream);
-int obst_fold_norm_weight(const void* w, const void* gamma, const void* beta, void* wg_t, float* cvec, float* dvec,
-                          float* gamma_f, int32_t heads, int32_t kin, int32_t kout, void* stream);
+typedef struct obst_fold_item {
+  const void* w;
+  const void* gamma;
+  const void* beta;
+  void* wg_t;
+  float* cvec;
+  float* dvec;
+  float* gamma_f;
+} obst_fold_item;
+int obst_fold_norm_weight(const obst_fold_item* items, int32_t nitems, int32_t heads, int32_t kin, int32_t kout,
+                          void* stream);
 int obst_rowscale_colsum(const void* dy, const float* stats, void* dyr, float* v1, float* v2, int64_t tokens,
                          int32_t heads, int32_t width, void* stream);
 int obst_norm_wgrad_rank1(float* dw, const void* gamma, const void* beta, const float* v1, const float* v2,
