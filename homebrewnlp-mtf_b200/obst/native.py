@@ -90,6 +90,12 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_scale": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_dot_accumulate": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_dropout": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_float, ctypes.c_uint64, c_void_p]),
+    "obst_attn_softmax_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32,
+                                      c_i32, c_i32, c_float, c_i32, c_void_p]),
+    "obst_attn_softmax_bwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_i64, c_i32, c_i32, c_i32, c_float, c_i32, c_void_p]),
+    "obst_bias_add": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i64, c_void_p]),
+    "obst_colsum_accumulate": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i64, c_void_p]),
     "obst_cumsum": (c_int, [c_int, c_void_p, c_void_p, c_i64, c_i32, c_i64, c_i32, c_i32, c_void_p]),
     "obst_embed_gather": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
     "obst_embed_scatter_add": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
@@ -365,6 +371,35 @@ def norm_wgrad_rank1(dw, gamma, beta, v1, v2, heads: int, kin: int, kout: int):
     _cuda(dw, v1, v2)
     check(load().obst_norm_wgrad_rank1(_p(dw), _p(gamma), _p(beta), _p(v1), _p(v2), heads, kin, kout, stream_ptr()),
           "obst_norm_wgrad_rank1")
+
+
+def attn_softmax_fwd(logits, bias, add_map, mul_map, soft, probs, batch, seq, heads, keys, scale, masked):
+    _cuda(logits, soft)
+    check(load().obst_attn_softmax_fwd(dtype_code(logits.dtype), _p(logits), _p(bias), _p(add_map), _p(mul_map), _p(soft),
+                                       _p(probs), batch, seq, heads, keys, float(scale), int(masked), stream_ptr()),
+          "obst_attn_softmax_fwd")
+
+
+def attn_softmax_bwd(dprobs, soft, add_map, mul_map, dlogits, dbias, dadd, dmul, batch, seq, heads, keys, scale,
+                     masked):
+    _cuda(dprobs, soft, dlogits)
+    check(load().obst_attn_softmax_bwd(dtype_code(soft.dtype), _p(dprobs), _p(soft), _p(add_map), _p(mul_map),
+                                       _p(dlogits), _p(dbias), _p(dadd), _p(dmul), batch, seq, heads, keys, float(scale),
+                                       int(masked), stream_ptr()), "obst_attn_softmax_bwd")
+
+
+def bias_add(x, bias, out):
+    _cuda(x, bias, out)
+    n = bias.numel()
+    check(load().obst_bias_add(dtype_code(x.dtype), _p(x), _p(bias), _p(out), x.numel() // n, n, stream_ptr()),
+          "obst_bias_add")
+
+
+def colsum_accumulate(x, out):
+    _cuda(x, out)
+    n = out.numel()
+    check(load().obst_colsum_accumulate(dtype_code(x.dtype), _p(x), _p(out), x.numel() // n, n, stream_ptr()),
+          "obst_colsum_accumulate")
 
 
 def cumsum(x, out, outer: int, seq: int, inner: int, reverse: bool = False, scale: int = 0):

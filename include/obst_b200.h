@@ -218,6 +218,27 @@ int obst_dot_accumulate(int dtype, const void* a, const void* b, float* out, int
  * uniform of (seed, i); calling it on dy with the same seed applies the same mask (the backward). */
 int obst_dropout(int dtype, const void* x, void* out, int64_t n, float keep, uint64_t seed, void* stream);
 
+/* ---- dot-product attention's soft-max stage, src/model/spatial.py:42-81 ------------------------------
+ * logits, soft, probs: AT [batch, seq, heads, keys] (keys contiguous; the q.k^T, p.v contractions and their
+ * gradients are obst_gemm calls).  Per (batch, position s, head) row over key positions t:
+ *   z_t = scale * logit_t + bias[h,s,t];  z_t = -inf for t > s (the reference always adds the causal -2e38, :71);
+ *   soft = softmax(z);  p_t = (soft_t + add_map[h,s,t] * m) * (mul_map[h,s,t] * m),  m = [s >= t] if masked else 1
+ * bias / add_map / mul_map: AT [heads, seq, keys] or NULL ('biased_softmax', 'biased_attention_map',
+ * 'scale_attention_map': the learned maps of _masked_map, :19-23).  soft is always written (the backward needs
+ * it); probs only when a map follows the soft-max (otherwise p == soft; pass NULL).
+ * Backward: dprobs -> dlogits (= scale * dz; may alias dprobs), map gradients (fp32 [heads, seq, keys], atomics,
+ * NULL to skip). */
+int obst_attn_softmax_fwd(int dtype, const void* logits, const void* bias, const void* add_map, const void* mul_map,
+                          void* soft, void* probs, int64_t batch, int32_t seq, int32_t heads, int32_t keys, float scale,
+                          int32_t masked, void* stream);
+int obst_attn_softmax_bwd(int dtype, const void* dprobs, const void* soft, const void* add_map, const void* mul_map,
+                          void* dlogits, float* dbias, float* dadd, float* dmul, int64_t batch, int32_t seq,
+                          int32_t heads, int32_t keys, float scale, int32_t masked, void* stream);
+/* a position embedding added to every batch row (key += embed(...), :57-58): out[o,i] = x[o,i] + bias[i]; its
+ * gradient out[i] += sum_o x[o,i] (fp32). */
+int obst_bias_add(int dtype, const void* x, const void* bias, void* out, int64_t outer, int64_t n, void* stream);
+int obst_colsum_accumulate(int dtype, const void* x, float* out, int64_t outer, int64_t n, void* stream);
+
 /* ---- residual stream arithmetic, src/model/revnet.py:23,89,120; src/model/__init__.py:129 ------
  * out = a + sign*b (sign = +1 or -1), all AT, n elements; out may alias a or b. */
 int obst_axpby(int dtype, const void* a, const void* b, float sign, void* out, int64_t n,
