@@ -15,15 +15,24 @@ from .embedding import embed
 
 
 def attention(args: BlockArgs) -> Tensor:
+    """src/model/spatial.py:42-81.  The mixer configs reach it as `biased_attention_map-absolute-input_as_value-
+    shared` (a learned causal map applied to the input itself): that form runs as one causal GEMM (_map_mix).  Every
+    other combination -- dot-product logits, `biased_softmax`, `scale_attention_map`, projected values -- goes through
+    _general_attention."""
     params = args.params
     params.attention_idx += 1
-    if "dot_product" in args or "input_as_value" not in args or 'biased_softmax' in args \
-            or 'scale_attention_map' in args:
-        raise NotImplementedError("attention: only 'biased_attention_map' + 'input_as_value' (the mixer path) has a "
-                                  "B200 kernel; dot-product / softmax variants are SURVEY.md 8(f) 'next'")
-    if 'biased_attention_map' not in args:
-        raise UserWarning(f"WARNING: There is no spatial mixing happening with the following attention parameters: "
-                          f"{args.name_extras}.")
+    simple = ("dot_product" not in args and "input_as_value" in args and 'biased_softmax' not in args
+              and 'scale_attention_map' not in args)
+    if simple:
+        if 'biased_attention_map' not in args:
+            raise UserWarning(f"WARNING: There is no spatial mixing happening with the following attention parameters: "
+                              f"{args.name_extras}.")
+        return _map_mix(args)
+    return _general_attention(args)
+
+
+def _map_mix(args: BlockArgs) -> Tensor:
+    params = args.params
     x = args.tensor
     dim = get_attention_dim(args).dim
     tmp = anonymize_dim(dim)
@@ -66,6 +75,165 @@ def attention(args: BlockArgs) -> Tensor:
             return dx
 
         params.tape.append(TapeEntry(bwd))
+    return Tensor(out, x.dims)
+
+
+def _general_attention(args: BlockArgs) -> Tensor:
+    """The full form of src/model/spatial.py:42-81 (see include/obst_b200.h, obst_attn_softmax_fwd, for the soft-max
+    stage).  The contractions are obst_gemm calls on the [batch, seq, heads, *] layouts as they lie:
+        logits[b,s,h,t] = sum_k q[b,s,h,k] key[b,t,h,k]        out[b,s,h,k] = sum_t p[b,s,h,t] val[b,t,h,k]
+    The projections (activated_linear_in / _out, one weight each for key, query and value) record their own tapes;
+    one composite tape entry differentiates the whole layer."""
+    from .backend import run_tape
+    from .basic import activated_linear_in, activated_linear_out
+    params = args.params
+    x = args.tensor
+    dim = get_attention_dim(args).dim
+    tmp = anonymize_dim(dim)
+    if len(x.dims) != 4 or x.dims[1] != dim or x.dims[2:] != params.feature_dims:
+        raise NotImplementedError(f"attention: expected [batch, {dim.name}, heads, features_per_head], got {x.dims}")
+    Bn, S, H, K = (d.size for d in x.dims)
+    F = H * K
+    be = params.gemm_backend
+    dt = x.data.dtype
+    outer = params.tape
+    pending, params.residual = params.residual, None
+    masked = is_masked(args)
+
+    def branch(fn):
+        params.tape = [] if outer is not None else None
+        try:
+            y = fn()
+        finally:
+            tape, params.tape = params.tape, outer
+        return y, tape
+
+    def masked_map():
+        var = embed(args, [params.head_dim, dim, tmp])
+        var.set_masked(dim.size if masked else 0)
+        return var
+
+    base = tape_in = None
+    if "dot_product" in args or "input_as_value" not in args:
+        base, tape_in = branch(lambda: activated_linear_in(args))
+    bargs = args(base) if base is not None else None
+
+    qry = key = pos = None
+    tape_q = tape_k = None
+    val = tape_v = None
+    logits = None
+    scale = 1.0
+    if 'dot_product' in args:
+        if 'embedded' in args or 'context' in args:
+            key, tape_k = branch(lambda: activated_linear_out(bargs))
+        if 'embedded' in args or 'positional' in args:
+            pos = embed(args, [dim] + params.feature_dims)
+        qry, tape_q = branch(lambda: activated_linear_out(bargs))
+        scale = float(dim.size) ** -0.5  # qry *= dim.size ** -0.5 (:61), applied inside the soft-max kernel
+        if key is not None and pos is not None:
+            summed = torch.empty_like(key.data)
+            native.bias_add(key.data, pos.value, summed)
+            key_data = summed
+        elif key is not None:
+            key_data = key.data
+        elif pos is not None:
+            key_data = pos.value  # [seq, heads, features]: the same keys for every batch row
+        else:
+            raise ValueError("dot_product attention needs 'embedded', 'context' or 'positional' keys")
+        key_batched = key is not None
+        logits = torch.empty((Bn, S, H, S), dtype=dt, device=x.data.device)
+        native.gemm(native.operand(qry.data, F, 1, s_glo=K, s_ghi=S * F),
+                    native.operand(key_data, F, 1, s_glo=K, s_ghi=S * F if key_batched else 0), logits, S, S, K, GLO=H,
+                    GHI=Bn, d_ld=H * S, d_glo=S, d_ghi=S * H * S, dtype_in=dt, backend=be)
+        if "shared_key_value" in args:
+            if not key_batched:
+                raise NotImplementedError("shared_key_value with position-only keys")
+            val = key_data
+    bias_var = masked_map() if 'biased_softmax' in args else None
+    if logits is None and bias_var is not None:
+        logits = torch.zeros((Bn, S, H, S), dtype=dt, device=x.data.device)
+    if logits is None:
+        raise NotImplementedError(f"attention without soft-max logits and with {args.name_extras}: only the plain "
+                                  f"'biased_attention_map' + 'input_as_value' form is supported")
+    add_var = masked_map() if 'biased_attention_map' in args else None
+    mul_var = masked_map() if 'scale_attention_map' in args else None
+    soft = torch.empty_like(logits)
+    probs = torch.empty_like(logits) if (add_var is not None or mul_var is not None) else None
+    native.attn_softmax_fwd(logits, None if bias_var is None else bias_var.value,
+                            None if add_var is None else add_var.value, None if mul_var is None else mul_var.value,
+                            soft, probs, Bn, S, H, S, scale, masked)
+    del logits
+    p = probs if probs is not None else soft
+    if val is None:
+        if "input_as_value" in args:
+            val = x.data
+        else:
+            v, tape_v = branch(lambda: activated_linear_out(bargs))
+            val = v.data
+    p_op = native.operand(p, H * S, 1, s_glo=S, s_ghi=S * H * S)
+    v_op = native.operand(val, 1, F, s_glo=K, s_ghi=S * F)
+    params.residual = None
+    if pending is not None:
+        buf, sign, out = pending
+        native.gemm(p_op, v_op, out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, R=buf,
+                    epi=2 if sign > 0 else 3, dtype_in=dt, backend=be)
+    else:
+        out = torch.empty_like(x.data)
+        native.gemm(p_op, v_op, out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, dtype_in=dt, backend=be)
+
+    if outer is not None:
+        def into(tape, g):
+            # a branch that ends in a ReLU fused into its GEMM leaves the [y > 0] mask to whoever produces dy
+            if tape and tape[-1].out_relu is not None:
+                m = torch.empty_like(g)
+                native.act_bwd(0, tape[-1].out_relu, g, m)
+                return m
+            return g
+
+        def bwd(dy, mask, acc):
+            # through out = p @ val
+            dp = torch.empty_like(soft)
+            native.gemm(native.operand(dy, F, 1, s_glo=K, s_ghi=S * F), native.operand(val, F, 1, s_glo=K, s_ghi=S * F),
+                        dp, S, S, K, GLO=H, GHI=Bn, d_ld=H * S, d_glo=S, d_ghi=S * H * S, dtype_in=dt, backend=be)
+            dval = torch.empty_like(val)
+            native.gemm(native.operand(p, 1, H * S, s_glo=S, s_ghi=S * H * S),
+                        native.operand(dy, 1, F, s_glo=K, s_ghi=S * F), dval, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K,
+                        d_ghi=S * F, dtype_in=dt, backend=be)
+            # through the soft-max stage: dp -> dlogits (in place), map gradients
+            native.attn_softmax_bwd(dp, soft, None if add_var is None else add_var.value,
+                                    None if mul_var is None else mul_var.value, dp,
+                                    None if bias_var is None else bias_var.ensure_grad(),
+                                    None if add_var is None else add_var.ensure_grad(),
+                                    None if mul_var is None else mul_var.ensure_grad(), Bn, S, H, S, scale, masked)
+            dbase = None
+            dx = None
+            if qry is not None:
+                dq = torch.empty_like(qry.data)
+                native.gemm(native.operand(dp, H * S, 1, s_glo=S, s_ghi=S * H * S),
+                            native.operand(key_data, 1, F, s_glo=K, s_ghi=S * F if key_batched else 0), dq, S, K, S,
+                            GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, dtype_in=dt, backend=be)
+                dk = torch.empty_like(qry.data)
+                native.gemm(native.operand(dp, 1, H * S, s_glo=S, s_ghi=S * H * S),
+                            native.operand(qry.data, 1, F, s_glo=K, s_ghi=S * F), dk, S, K, S, GLO=H, GHI=Bn, d_ld=F,
+                            d_glo=K, d_ghi=S * F, dtype_in=dt, backend=be)
+                if "shared_key_value" in args:
+                    native.axpby(dk, dval, 1.0, dk)
+                if pos is not None and pos.ensure_grad() is not None:
+                    native.colsum_accumulate(dk, pos.ensure_grad())
+                dbase = run_tape(tape_q, into(tape_q, dq))
+                if tape_k is not None:
+                    dbase = run_tape(tape_k, into(tape_k, dk), acc=dbase)
+            if tape_v is not None:
+                g = into(tape_v, dval)
+                dbase = run_tape(tape_v, g, acc=dbase) if dbase is not None else run_tape(tape_v, g)
+            elif "input_as_value" in args and "shared_key_value" not in args:
+                dx = dval
+            if dbase is not None:
+                via_base = run_tape(tape_in, into(tape_in, dbase), acc=dx)
+                dx = via_base
+            return dx
+
+        outer.append(TapeEntry(bwd))
     return Tensor(out, x.dims)
 
 

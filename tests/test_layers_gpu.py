@@ -144,3 +144,86 @@ def test_dropout_keeps_the_stated_fraction_and_replays_its_mask(cuda):
     # evaluation mode (params.train False) and rate 0: identity
     params, x, out, dy, dx, _ = run_layers(["dropout-dropout_rate0.25"], train=False)
     assert torch.equal(out.data, x)
+
+
+def _attention_reference(layer, x, variables, params, dy):
+    """float64 torch statement of src/model/spatial.py:42-81 for the flag set in `layer`; returns (out, dx, grads)."""
+    flags = layer.split('-')[1:]
+    B, S, H, K = x.shape
+    it = iter(variables)
+    leaves = []
+
+    def nxt():
+        v = next(it)
+        t = (v.data if hasattr(v, "full_name") else v.value).double().clone().requires_grad_(hasattr(v, "full_name"))
+        leaves.append((v, t))
+        return t
+
+    xr = x.double().requires_grad_(True)
+    m = torch.tril(torch.ones(S, S, dtype=torch.float64, device=x.device))
+    masked = 0 in params.masked_attention_dimensions
+    mm = m if masked else torch.ones_like(m)
+    base = None
+    if "dot_product" in flags or "input_as_value" not in flags:
+        base = torch.einsum("bshk,hki->bsi", xr, nxt())
+        if "in:relu" in flags:
+            base = base.relu()
+    logit = None
+    val = None
+    if "dot_product" in flags:
+        key = 0
+        if "embedded" in flags or "context" in flags:
+            key = torch.einsum("bsi,ihk->bshk", base, nxt())
+        if "embedded" in flags or "positional" in flags:
+            key = key + nxt()[None]
+        qry = torch.einsum("bsi,ihk->bshk", base, nxt()) * S ** -0.5
+        if key.dim() == 3:
+            key = key[None].expand(B, -1, -1, -1)
+        logit = torch.einsum("bshk,bthk->bsht", qry, key)
+        if "shared_key_value" in flags:
+            val = key
+    if "biased_softmax" in flags:
+        bias = nxt() * mm[None]
+        logit = bias.permute(1, 0, 2)[None] + (logit if logit is not None else 0)
+    logit = logit.masked_fill(m[None, :, None, :] == 0, float("-inf"))
+    p = torch.softmax(logit, -1)
+    if "biased_attention_map" in flags:
+        p = p + (nxt() * mm[None]).permute(1, 0, 2)[None]
+    if "scale_attention_map" in flags:
+        p = p * (nxt() * mm[None]).permute(1, 0, 2)[None]
+    if val is None:
+        val = xr if "input_as_value" in flags else torch.einsum("bsi,ihk->bshk", base, nxt())
+    out = torch.einsum("bsht,bthk->bshk", p, val)
+    out.backward(dy.double())
+    return out.detach(), xr.grad, [(v, t.grad) for v, t in leaves if t.requires_grad]
+
+
+@pytest.mark.parametrize("layer", [
+    "attention-dot_product-embedded-absolute-in:relu",
+    "attention-dot_product-context-input_as_value-biased_softmax-absolute",
+    "attention-biased_softmax-scale_attention_map-biased_attention_map-input_as_value-absolute",
+    "attention-dot_product-positional-relative-input_as_value",
+    "attention-dot_product-embedded-shared_key_value-absolute",
+])
+def test_dot_product_attention_variants(cuda, layer):
+    """The general attention layer (src/model/spatial.py:42-81): dot-product logits from projected queries / keys
+    (+ absolute or sinusoidal relative position keys), `biased_softmax`, the causal soft-max, `biased_attention_map`,
+    `scale_attention_map`, projected / shared / input values -- output, input gradient and every weight gradient
+    against a float64 statement of those lines, fp32 at 1e-5."""
+    params, x, out, dy, dx, variables = run_layers([layer], seq=24, fph=16, batch=2, position_embedding="relative")
+    # constants (relative embeddings) are not in the variable cache: rebuild the creation-order list
+    from obst.model.embedding import Constant, relative_embedding  # noqa: F401
+    ordered = list(variables)
+    if "relative" in layer.split('-'):
+        from obst.dataclass import BlockArgs
+        from obst.utils_mtf import Tensor as T_
+        dims = [params.batch_dim._replace(size=2), params.sequence_dim] + params.feature_dims
+        const = Constant(relative_embedding(BlockArgs(params, T_(x, dims), layer.split('-')[1:]),
+                                            [params.sequence_dim] + params.feature_dims),
+                         [params.sequence_dim] + params.feature_dims)
+        ordered.insert(1, const)  # created after the input projection, before the query projection
+    ref, dx_ref, grads = _attention_reference(layer, x, ordered, params, dy)
+    assert rel(out.data, ref) < 1e-5
+    assert rel(dx, dx_ref) < 1e-5
+    for v, g in grads:
+        assert rel(v.grad, g.reshape(v.grad.shape)) < 1e-5, v.name
