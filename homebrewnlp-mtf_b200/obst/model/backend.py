@@ -165,11 +165,12 @@ def get_variable(params: ModelParameter, name: str, shape: DIM_LIST, initializer
     shape = deduplicate(list(shape))
     index = len(params.variable_cache)
     imported = getattr(params, "import_variables", None)
-    restoring = getattr(params, "restore_entries", None)  # obst.run.checkpoint.load_checkpoint
-    if restoring is not None:
-        if full_name not in restoring:
-            raise KeyError(f"checkpoint has no variable '{full_name}'")
-        init = restoring[full_name].float().numpy().reshape([d.size for d in shape])
+    restored = None
+    if getattr(params, "restore_entries", None) is not None:  # obst.run.checkpoint.load_checkpoint
+        from ..run.checkpoint import take_entry
+        restored = take_entry(params, full_name)
+    if restored is not None:
+        init = restored.float().numpy().reshape([d.size for d in shape])
     elif imported is not None:
         init = np.asarray(imported[index], dtype=np.float32).reshape([d.size for d in shape])
     else:

@@ -269,13 +269,12 @@ class FusedOptimizer:
         if slot not in bufs:
             buf = torch.zeros_like(self.flat_momentum)
             bufs[slot] = buf
-            entries = getattr(self.params, "restore_entries", None) or {}  # resume (obst.run.checkpoint)
+            from ..run.checkpoint import restore_slot  # resume: no-op unless load_checkpoint armed the parameters
             for v, (off, sz) in zip(self.variables, self.offsets):
                 name = slot_name(self.params, v.name, slot)
                 view = buf[off:off + sz].view(v.data.shape)
                 self.slots[name] = view
-                if name in entries:
-                    view.copy_(entries[name].to(view.device).reshape(view.shape).to(view.dtype))
+                restore_slot(self.params, name, view)
         return bufs[slot]
 
     def _scratch(self, name: str, numel: int, dtype) -> torch.Tensor:
@@ -315,6 +314,9 @@ class FusedOptimizer:
 
         def reduce_into(dst, src=work):
             self._stage(N.STAGE_REDUCE, src, flags=2, sums=dst)
+            reducer = getattr(self.params, "grad_reducer", None)
+            if reducer is not None:  # replicas agree on the sums (see GradReducer.agree)
+                reducer.agree(dst)
 
         def debias(beta):  # debias_momentum, optimizers.py:17-18, in fp32 like the graph
             return f32(1) / (f32(1) - np.power(beta, f32(step_count)))
@@ -348,11 +350,9 @@ class FusedOptimizer:
             reduce_into(sums)
             if "_novograd_p2" not in self.__dict__:
                 pair = [torch.zeros(nt, dtype=self.state_dtype, device=work.device) for _ in range(2)]
-                entries = getattr(self.params, "restore_entries", None) or {}
+                from ..run.checkpoint import restore_slot
                 for i, v in enumerate(self.variables):
-                    name = slot_name(self.params, v.name, "exp_avg_p2")
-                    if name in entries:
-                        pair[0][i] = entries[name].to(work.device).reshape(()).to(self.state_dtype)
+                    restore_slot(self.params, slot_name(self.params, v.name, "exp_avg_p2"), pair[0][i])
                 self._novograd_p2 = pair
             pair = self._novograd_p2
             self._stage(N.STAGE_NOVOGRAD, work, f=[b1, b2, 0.0, debias(b2)], state_a=self._flat_state("exp_avg_p1"),
@@ -405,8 +405,10 @@ class FusedOptimizer:
             return any(n == stage_name or (n == "graft" and a and a[0] == stage_name) for n, a in stages)
 
         if uses("global_l2norm_clip", plan.stages):
-            self._stage(N.STAGE_REDUCE, work, flags=2, sums=self._scratch("sums_raw", 4 * len(self.variables),
-                                                                          torch.float64))
+            raw = self._scratch("sums_raw", 4 * len(self.variables), torch.float64)
+            self._stage(N.STAGE_REDUCE, work, flags=2, sums=raw)
+            if getattr(self.params, "grad_reducer", None) is not None:
+                self.params.grad_reducer.agree(raw)
         for name, args in plan.stages:
             self._run_stage(name, args, work, lr, step_count)
         if any("rezero" in v.name for v in self.variables):  # src/optimizer/__init__.py:46-47
@@ -457,6 +459,8 @@ class FusedOptimizer:
             native.check(lib.obst_opt_norms(tp, nt, it, ir0, irs, self.n_items, act, grad_bf16 & 1,
                                             self.norms.data_ptr(), flags, self.wnext.data_ptr(), 0, nt, st),
                          "obst_opt_norms")
+            if not single:  # float64 atomics in a per-rank order: all replicas take rank 0's sums
+                p.grad_reducer.agree(self.norms)
         native.check(lib.obst_opt_update(tp, nt, it, ir0, irs, self.n_items, self.max_cols, int(self.vec4), act, sdt,
                                          grad_bf16, self.norms.data_ptr(), self.wnext.data_ptr(), plan.clip, plan.beta,
                                          int(plan.nesterov), float(lr), float(p.weight_decay),

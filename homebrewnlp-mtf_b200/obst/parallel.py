@@ -58,6 +58,15 @@ class GradReducer:
         else:
             dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
 
+    def agree(self, t: torch.Tensor):
+        """Make every rank use rank 0's copy of a few reduction results (per-tensor norm sums).  Each rank accumulates
+        them with float64 atomics in its own order; a last-bit difference in one rank's clip scale would let that
+        replica's weights drift for the rest of the run, and nothing downstream would notice."""
+        if self.world == 1 or t.numel() == 0:
+            return
+        src = dist.get_global_rank(self.group, 0) if self.group is not None else 0
+        dist.broadcast(t, src=src, group=self.group)
+
     def on_depth_done(self, depth: int):
         """Gradients of every variable owned by `depth` are final (both sub-blocks back-propagated)."""
         if not self.last or self.world == 1:

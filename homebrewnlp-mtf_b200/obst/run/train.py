@@ -84,6 +84,9 @@ def get_train_model(params: ModelParameter, frame_input, cat_mask_src, cat_mask_
     params.macro_chained = False
     params.global_step += params.macro_batching            # src/run/run.py:139-156
     params.manual_global_step += params.macro_batching
+    if getattr(params, "restore_entries", None) is not None:  # resumed: every variable and slot exists by now
+        from .checkpoint import finish_restore
+        finish_restore(params)
     n = params.n_global_targets
     z = float(params.z_loss or 0.0)
     if macro > 1:  # total_loss = mean over the slices (`:50,75`)

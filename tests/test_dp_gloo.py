@@ -51,7 +51,9 @@ def _worker(rank, world, port, early, out):
         red.on_depth_done(d)
     red.finish()
     ok = torch.equal(before, _State(rank).flat_grad)
-    torch.save({"grad": params.optimizer_state.flat_grad, "sums": params.loss_sums, "ok": ok,
+    norms = torch.tensor([1.0, 2.0 + rank * 2.0 ** -50], dtype=torch.float64)  # last-bit disagreement between ranks
+    red.agree(norms)
+    torch.save({"grad": params.optimizer_state.flat_grad, "sums": params.loss_sums, "ok": ok, "norms": norms,
                 "bytes": red.bytes_reduced}, os.path.join(out, f"r{rank}.pt"))
     dist.destroy_process_group()
 
@@ -66,4 +68,5 @@ def test_grad_reducer_world2_gloo(tmp_path, early):
     assert r0["ok"] and r1["ok"]
     assert torch.allclose(r0["grad"], expect) and torch.equal(r0["grad"], r1["grad"])  # summed once, identical
     assert r0["sums"].tolist() == [3.0, 4.0, 6.0]
+    assert r0["norms"].tolist() == [1.0, 2.0] and torch.equal(r0["norms"], r1["norms"])  # rank 0's copy everywhere
     assert r0["bytes"] == 1000 * 4 + 3 * 8

@@ -611,6 +611,15 @@ def test_checkpoint_resume(cuda, tmp_path, chain):
     assert resumed.global_step == 1502 and resumed.manual_global_step == 2
     run_product_step(resumed, tok_x, tok_y)
     assert resumed.global_step == straight.global_step
+    assert resumed.restore_entries is None  # everything consumed, host copy of the file released
+    # a changed optimizer string asks for slot names the file does not hold: that raises instead of silently
+    # restarting the optimizer state from zero
+    other = copy.deepcopy(cfg)
+    other["optimizer"] = "adam-learning_rate" if chain != "adam-learning_rate" else "momentum:0.9:1:0-learning_rate"
+    wrong = make_params(other, op)
+    load_checkpoint(wrong, path)
+    with pytest.raises(KeyError, match="slot"):
+        run_product_step(wrong, tok_x, tok_y)
     # two runs of the same step differ in the last bits (fp32 atomics in the weight-gradient / embedding-gradient
     # accumulation are unordered), so the third step is compared at 1e-6 ...
     # (novograd's first step from a zero second moment multiplies the gradient by 1e5 -- src/optimizer/
