@@ -10,7 +10,7 @@
 // copy rate.
 //
 // A tensor is viewed as [rows, cols] (cols = last dim); a block takes one work item (a run of rows) and one chunk
-// of 512 columns (blockIdx.y); a warp owns whole rows of that chunk; lane l owns columns 128 g + 4 l + {0..3} of
+// of 512 columns (block index = item * chunks + chunk); a warp owns whole rows of that chunk; lane l owns columns 128 g + 4 l + {0..3} of
 // the chunk for g = 0..3, so every global access of a warp is one fully used, contiguous 512-byte (fp32) or
 // 256-byte (bf16) run.  SM3 bookkeeping as in the generic kernel: the maxima over rows of the last dim's new
 // accumulator live in registers, the maxima over columns go through one warp reduction per row.
@@ -67,32 +67,32 @@ __global__ void __launch_bounds__(RWARPS * 32, 2) opt_update_ring_kernel(const o
                                                                        const int32_t* __restrict__ item_row0,
                                                                        const int32_t* __restrict__ item_rows,
                                                                        const double* __restrict__ norms,
-                                                                       const OptHyper hp, double* __restrict__ wnext) {
+                                                                       const OptHyper hp, double* __restrict__ wnext,
+                                                                       const unsigned ychunks) {
   constexpr int P_BYTES = RCHUNK * 4, G_BYTES = RCHUNK * (int)sizeof(TG), M_BYTES = RCHUNK * (int)sizeof(TS);
   constexpr int STAGE = P_BYTES + G_BYTES + M_BYTES;
   extern __shared__ __align__(16) uint8_t s_ring_raw[];
   __shared__ float s_col[RCHUNK];  // block-level column maxima of this chunk
-  __shared__ obst_opt_tensor sT;   // the table entry (dynamically indexed: keep it out of local memory)
   __shared__ double s_w2[RWARPS];
   __shared__ float s_rowmax[OPT_MAX_ITEM_ROWS];
-  const int item = blockIdx.x;
+  // item-major block order (the two 512-column chunks of a wide row run are neighbours): blocks are dispatched in
+  // work-list order, so a list that ends in small items drains evenly
+  const int item = (int)(blockIdx.x / ychunks);
   const int ti = item_tensor[item];
   const int nrows = item_rows[item];
   const int row_begin = item_row0[item];
   if (nrows > OPT_MAX_ITEM_ROWS) __trap();  // contract of the work list (include/obst_b200.h)
-  if (threadIdx.x == 0) sT = table[ti];
-  __syncthreads();
-  const obst_opt_tensor& T = sT;
+  // the table entry is read where it lies (read-only, L1/L2-resident after the first blocks): its fields arrive with one
+  // memory latency for all threads, where a staged copy in shared memory would cost a latency plus a barrier
+  const obst_opt_tensor& T = table[ti];
   if ((sizeof(TG) == 2) != (T.g_bf16 != 0)) __trap();  // the launch's gradient dtype must be the table's
   const int nd = T.ndim;
   const int cols = T.dims[nd - 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int cbase = (int)blockIdx.y * RCHUNK;
+  const int cbase = (int)(blockIdx.x % ychunks) * RCHUNK;
   if (cbase >= cols) return;  // whole block: this tensor is narrower than the widest one of the launch
   for (int i = threadIdx.x; i < RCHUNK; i += blockDim.x) s_col[i] = 0.f;
-  opt_row_minima<TS>(T, row_begin, nrows, s_rowmax);
-  __syncthreads();
-  // the table entry's hot fields in registers (sT is shared memory: every use would be a reload)
+  // the table entry's hot fields in registers
   float* const Tp = T.p;
   const TG* const Tg = reinterpret_cast<const TG*>(T.g);
   TS* const Tm = reinterpret_cast<TS*>(T.m);
@@ -141,6 +141,10 @@ __global__ void __launch_bounds__(RWARPS * 32, 2) opt_update_ring_kernel(const o
     if (row_begin + warp + s * RWARPS < row_end) issue(row_begin + warp + s * RWARPS, s);
     else cp_commit_group();  // keep one group per slot so the wait_group counts stay aligned
   }
+  // the rows are on their way: only now the per-row minima of the other dims' accumulators (their loads overlap the
+  // ring's first fill instead of preceding it)
+  opt_row_minima<TS>(T, row_begin, nrows, s_rowmax);
+  __syncthreads();
   int stage = 0;
   for (int r = row_begin + warp; r < row_end; r += RWARPS, stage = (stage + 1 == RING ? 0 : stage + 1)) {
     const int rn = r + (RING - 1) * RWARPS;
@@ -301,14 +305,17 @@ static int ring_launch_typed(const obst_opt_tensor* table, const int32_t* item_t
     attr = true;
   }
   const int64_t ychunks = ((int64_t)max_cols + RCHUNK - 1) / RCHUNK;
-  OBST_REQUIRE(ychunks <= 65535, "obst_opt_update: last dim %d too large (max %d)", max_cols, 65535 * RCHUNK);
-  const dim3 grid((unsigned)nitems, (unsigned)ychunks);
+  OBST_REQUIRE(ychunks * (int64_t)nitems < (int64_t)1 << 31, "obst_opt_update: %d work items x %lld column chunks "
+               "exceed the grid", nitems, (long long)ychunks);
+  const dim3 grid((unsigned)(nitems * ychunks));
   if (hp.act_bf16)
     opt_update_ring_kernel<TS, TG, RING, true><<<grid, RWARPS * 32, SMEM, st>>>(table, item_tensor, item_row0,
-                                                                                 item_rows, norms, hp, wnext);
+                                                                                 item_rows, norms, hp, wnext,
+                                                                                 (unsigned)ychunks);
   else
     opt_update_ring_kernel<TS, TG, RING, false><<<grid, RWARPS * 32, SMEM, st>>>(table, item_tensor, item_row0,
-                                                                                  item_rows, norms, hp, wnext);
+                                                                                  item_rows, norms, hp, wnext,
+                                                                                  (unsigned)ychunks);
   count_launch();
   count_path(OBST_PATH_OPT_RING);
   return check_launch("obst_opt_update");
