@@ -553,6 +553,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+  // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor prefetch, the cluster
+  // barrier) touches no global data and may run while the previous kernel of the stream drains its last tiles; from
+  // here on its results are needed.  A no-op when the launch did not ask for the overlap.  The trigger right after
+  // lets the NEXT tensor-core GEMM do the same as this grid's CTAs retire (one wave: nobody is kept off an SM).
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
   const int bn_cta = p.BN / CG;  // B rows (N) this CTA stages
   const uint32_t stage_bytes = (uint32_t)(A_STAGE_BYTES + bn_cta * BK * 2) * CG;  // what the (leader's) barrier sees
@@ -1089,12 +1095,35 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   if (g.accumulate) {
     splits = g.splits;
     if (splits <= 0) {
-      // enough work items to fill the machine ~2x, but keep >= 8 k-blocks per split
-      const int sms = num_sms();
-      splits = (int)((2 * sms + base_tiles - 1) / base_tiles);
+      // The work items (tiles x splits) are dealt round-robin to the resident CTAs (CTA pairs), all of the same length:
+      // the kernel takes ceil(items / slots) rounds, and a last round that is mostly empty costs a whole round
+      // (the weight gradients of the step have 32 or 64 tiles: 10 / 5 splits = 320 items on 74 CTA pairs ran 5 rounds
+      // for 4.3 rounds of work).  Pick the split count whose last round is fullest, preferring fewer splits (each one
+      // adds a tile of fp32 reduction traffic) and keeping >= 8 k-blocks per split.
+      const int slots = num_sms() / cg;
       const int max_by_k = p.nkb / 8 > 0 ? p.nkb / 8 : 1;
-      if (splits > max_by_k) splits = max_by_k;
-      if (splits < 1) splits = 1;
+      int64_t hi = (8 * (int64_t)slots + base_tiles - 1) / base_tiles;
+      if (hi > max_by_k) hi = max_by_k;
+      if (hi < 1 || base_tiles >= 4 * (int64_t)slots) hi = 1;  // plenty of tiles already: no split
+      static const bool legacy = [] {  // OBST_GEMM_SPLIT_LEGACY=1: round 1's rule (2 x SMs / tiles), for A/B runs
+        const char* e = getenv("OBST_GEMM_SPLIT_LEGACY");
+        return e && e[0] == '1';
+      }();
+      if (legacy) {
+        splits = (int)((2 * num_sms() + base_tiles - 1) / base_tiles);
+        if (splits > max_by_k) splits = max_by_k;
+        hi = 0;
+      }
+      double best = -1.0;
+      for (int s = 1; s <= (int)hi; ++s) {
+        const int64_t items = base_tiles * s;
+        const int64_t rounds = (items + slots - 1) / slots;
+        const double score = (double)items / (double)(rounds * slots) - 0.002 * s;
+        if (score > best) {
+          best = score;
+          splits = s;
+        }
+      }
     }
     if (splits > p.nkb) splits = p.nkb;
   }
@@ -1147,13 +1176,21 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
     cfg.blockDim = dim3(TC_THREADS);
     cfg.dynamicSmemBytes = Cfg<2>::SMEM;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    // the kernel waits (griddepcontrol.wait) before its first global access: its prologue may overlap the tail of
+    // the kernel before it.  OBST_GEMM_PDL=0 launches fully serialised (A/B switch).
+    static const bool pdl = [] {
+      const char* e = getenv("OBST_GEMM_PDL");
+      return !(e && e[0] == '0');
+    }();
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2>, tmA, tmB, tmD, tmR, p);
     if (e != cudaSuccess) {
       set_error("obst_gemm(tc): cluster launch failed: %s", cudaGetErrorString(e));
