@@ -48,6 +48,7 @@ struct TcParams {
   int32_t BN, tiles_m, tiles_n, total_tiles;
   int32_t splits, tri, epi, accumulate, out_f32;
   int32_t tma_store;                   // bf16 output through smem staging + TMA store (and TMA load of R)
+  int32_t tri_live;                    // tri == 3 with square tiles: tiles per group on or below the diagonal (else 0)
   int32_t a_mn, b_mn;                  // 1 = MN-major operand
   int32_t a_uglo, a_ughi, a_uko;       // does the operand depend on g_lo / g_hi / ko
   int32_t b_uglo, b_ughi, b_uko;
@@ -358,10 +359,24 @@ struct Tile {
 template <int CG>
 __device__ __forceinline__ bool get_tile(const TcParams& p, int tile, Tile& t) {
   constexpr int TM = BM * CG;
-  const int nt = tile % p.tiles_n;
-  int r = tile / p.tiles_n;
-  const int mt = r % p.tiles_m;
-  r /= p.tiles_m;
+  int nt, mt, r;
+  if (p.tri_live) {
+    // only the tiles on or below the diagonal are numbered (row by row: (0,0) (1,0) (1,1) (2,0) ...): with all tiles
+    // numbered and the dead ones skipped, the CTA pairs that drew them idled while the others set the kernel's time
+    int idx = tile % p.tri_live;
+    r = tile / p.tri_live;
+    mt = 0;
+    while (idx > mt) {
+      idx -= mt + 1;
+      ++mt;
+    }
+    nt = idx;
+  } else {
+    nt = tile % p.tiles_n;
+    r = tile / p.tiles_n;
+    mt = r % p.tiles_m;
+    r /= p.tiles_m;
+  }
   const int g = r % p.G;
   const int sp = r / p.G;
   t.m0 = mt * TM;
@@ -1090,7 +1105,9 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   p.b_uglo = g.b_glo != 0;
   p.b_ughi = g.b_ghi != 0;
   p.b_uko = (g.b_ko != 0 && g.KO > 1);
-  const int64_t base_tiles = (int64_t)p.tiles_m * p.tiles_n * p.G;
+  // lower-triangular output (gradient of a causal mixing map) with square tiles: number the live tiles only
+  p.tri_live = (g.tri == 3 && p.tiles_m == p.tiles_n && p.BN == BM * cg) ? p.tiles_m * (p.tiles_m + 1) / 2 : 0;
+  const int64_t base_tiles = (p.tri_live ? (int64_t)p.tri_live : (int64_t)p.tiles_m * p.tiles_n) * p.G;
   int splits = 1;
   if (g.accumulate) {
     splits = g.splits;
