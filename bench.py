@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--no-fold-norm", action="store_true",
                     help="A/B switch: run the group norm between W_mid and W_out as its own kernel instead of folding "
                          "it into the two GEMMs")
+    ap.add_argument("--no-fold-norm-bwd", action="store_true",
+                    help="A/B switch: keep the mid norm's backward as a separate kernel (dn written and re-read)")
     ap.add_argument("--store-activations", action="store_true",
                     help="extension: keep activations instead of the reference's reversible recompute (reported "
                          "separately; the default run is the reference algorithm)")
@@ -381,6 +383,7 @@ def run_b200(args):
     mb = args.micro_batch or max(1, min(rows, (32768 if args.store_activations else 131072) // seq))
     cfg["revnet_store_activations"] = bool(args.store_activations)
     cfg["fold_mid_norm"] = not args.no_fold_norm
+    cfg["fold_mid_norm_backward"] = not args.no_fold_norm_bwd
     cfg["micro_batch_size"] = mb
     cfg["device"] = f"cuda:{local_rank}"
     import contextlib

@@ -33,7 +33,8 @@ __global__ void __launch_bounds__(256) norm_stats_kernel(const float2* __restric
   }
 }
 
-// gamma . W (transposed for the forward GEMM's K-major B operand), c = gamma^T W, d = beta^T W, and gamma as fp32.
+// gamma . W (transposed for the forward GEMM's K-major B operand, and untransposed for the backward's), c = gamma^T W,
+// d = beta^T W, and gamma as fp32.
 // One block per (32 output features, head): it walks the whole contraction axis, so the two vectors need no atomics.
 __global__ void __launch_bounds__(256) fold_norm_weight_kernel(const obst_fold_item* __restrict__ items, int heads,
                                                                 int kin, int kout) {
@@ -42,6 +43,7 @@ __global__ void __launch_bounds__(256) fold_norm_weight_kernel(const obst_fold_i
   const bf16* __restrict__ gamma = reinterpret_cast<const bf16*>(it.gamma);
   const bf16* __restrict__ beta = reinterpret_cast<const bf16*>(it.beta);
   bf16* __restrict__ wg_t = reinterpret_cast<bf16*>(it.wg_t);
+  bf16* __restrict__ wg_n = reinterpret_cast<bf16*>(it.wg);  // gamma . W in W's own layout (may be NULL)
   float* __restrict__ cvec = it.cvec;
   float* __restrict__ dvec = it.dvec;
   float* __restrict__ gamma_f = it.gamma_f;
@@ -64,6 +66,7 @@ __global__ void __launch_bounds__(256) fold_norm_weight_kernel(const obst_fold_i
         wg = to_f32(wgb);                 // c is the column sum of what the GEMM really multiplies with
         d_acc = fmaf(b, wv, d_acc);
         tile[ty + i][tx] = wgb;
+        if (wg_n) wg_n[((int64_t)h * kin + j) * kout + k] = wgb;
       }
       c_acc += wg;
     }
@@ -167,6 +170,61 @@ __global__ void __launch_bounds__(256) norm_wgrad_rank1_kernel(float* __restrict
   }
 }
 
+// The folded norm's backward, per (row, head): the two reductions over the head's features arrive as partial
+// dot products from W_out's recompute epilogue (obst_gemm epilogues 9 / 10):
+//   s1 = sum_j gamma_j dn_j        = sum_k dy_k (gamma^T W)_k
+//   s2 = sum_j gamma_j h_j dn_j    = sum_k dy_k (h @ (gamma.W))_k
+// and dh_j = r (gamma_j dn_j - s1/K - xhat_j * r (s2 - mu s1)/K), xhat_j = (h_j - mu) r, which the dgrad epilogue (11)
+// evaluates as a * gamma_j * dn_j + b * h_j + c with  a = r,  b = -r^2 m2,  c = r^2 mu m2 - r m1,
+// m1 = s1 / K,  m2 = r (s2 - mu s1) / K.
+__global__ void __launch_bounds__(256) norm_bwd_coeffs_kernel(const float2* __restrict__ part,
+                                                              const float2* __restrict__ stats,
+                                                              float4* __restrict__ coeffs, int64_t total, int nparts,
+                                                              float inv_width) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    float s1 = 0.f, s2 = 0.f;
+    for (int k = 0; k < nparts; ++k) {
+      const float2 v = part[i * nparts + k];
+      s1 += v.x;
+      s2 += v.y;
+    }
+    const float2 st = stats[i];
+    const float mu = st.x, r = st.y;
+    const float m1 = s1 * inv_width;
+    const float m2 = r * (s2 - mu * s1) * inv_width;
+    coeffs[i] = make_float4(r, -r * r * m2, r * r * mu * m2 - r * m1, 0.f);
+  }
+}
+
+// dgamma[h,j] -= sum_k W[h,j,k] v1[h,k];  dbeta[h,j] += sum_k W[h,j,k] v2[h,k]   (one warp per (h, j))
+// -- the parts of the norm's scale / shift gradients that do not need the weight gradient's accumulator:
+//   dbeta_j  = sum_t dn_tj           = sum_k W_jk sum_t dy_tk
+//   dgamma_j = sum_t dn_tj xhat_tj   = sum_k W_jk (G_jk - sum_t r_t mu_t dy_tk),  G = h^T (r . dy): epilogue 8's part
+__global__ void __launch_bounds__(256) norm_affine_grad_kernel(const bf16* __restrict__ w, const float* __restrict__ v1,
+                                                               const float* __restrict__ v2,
+                                                               float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                               int heads, int kin, int kout) {
+  const int lane = threadIdx.x & 31;
+  const int64_t rows = (int64_t)heads * kin;
+  for (int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows;
+       row += (int64_t)gridDim.x * (blockDim.x >> 5)) {
+    const int h = (int)(row / kin);
+    const bf16* wr = w + row * kout;
+    float a1 = 0.f, a2 = 0.f;
+    for (int k = lane; k < kout; k += 32) {
+      const float wv = to_f32(wr[k]);
+      a1 = fmaf(wv, v1[(int64_t)h * kout + k], a1);
+      a2 = fmaf(wv, v2[(int64_t)h * kout + k], a2);
+    }
+    a1 = warp_sum(a1);
+    a2 = warp_sum(a2);
+    if (lane == 0) {
+      if (dgamma) dgamma[row] -= a1;
+      if (dbeta) dbeta[row] += a2;
+    }
+  }
+}
+
 }  // namespace obst
 
 using namespace obst;
@@ -227,6 +285,34 @@ int obst_norm_wgrad_rank1(float* dw, const void* gamma, const void* beta, const 
                                                                                v1, v2, heads, kin, kout);
   count_launch();
   return check_launch("obst_norm_wgrad_rank1");
+}
+
+int obst_norm_bwd_coeffs(const float* partials, const float* stats, float* coeffs, int64_t rows, int32_t heads,
+                         int32_t nparts, int32_t width, void* stream) {
+  OBST_REQUIRE(partials && stats && coeffs && heads > 0 && nparts > 0 && width > 0, "obst_norm_bwd_coeffs: bad arguments");
+  OBST_REQUIRE((reinterpret_cast<uintptr_t>(coeffs) & 15) == 0, "obst_norm_bwd_coeffs: coeffs must be 16-byte aligned");
+  if (rows <= 0) return OBST_OK;
+  const int64_t total = rows * heads;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > (int64_t)num_sms() * 16) blocks = (int64_t)num_sms() * 16;
+  norm_bwd_coeffs_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const float2*>(partials), reinterpret_cast<const float2*>(stats),
+      reinterpret_cast<float4*>(coeffs), total, nparts, 1.0f / (float)width);
+  count_launch();
+  return check_launch("obst_norm_bwd_coeffs");
+}
+
+int obst_norm_affine_grad(const void* w, const float* v1, const float* v2, float* dgamma, float* dbeta, int32_t heads,
+                          int32_t kin, int32_t kout, void* stream) {
+  OBST_REQUIRE(w && v1 && v2 && heads > 0 && kin > 0 && kout > 0, "obst_norm_affine_grad: bad arguments");
+  if (!dgamma && !dbeta) return OBST_OK;
+  const int64_t rows = (int64_t)heads * kin;
+  int64_t blocks = (rows + 7) / 8;
+  if (blocks > (int64_t)num_sms() * 16) blocks = (int64_t)num_sms() * 16;
+  norm_affine_grad_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const bf16*)w, v1, v2, dgamma, dbeta,
+                                                                               heads, kin, kout);
+  count_launch();
+  return check_launch("obst_norm_affine_grad");
 }
 
 }  // extern "C"

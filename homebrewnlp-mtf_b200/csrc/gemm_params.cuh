@@ -12,6 +12,8 @@ struct GemmParams {
   const void* aux0;
   const void* aux1;
   const void* aux2;
+  const void* aux3;
+  void* aux4;
   int64_t a_mn, a_k, a_ko, a_glo, a_ghi;
   int64_t b_mn, b_k, b_ko, b_glo, b_ghi;
   int64_t d_ld, d_glo, d_ghi;

@@ -55,6 +55,8 @@ struct TcParams {
   const void* aux0;                    // epilogues 5..8, see obst_gemm_desc
   const void* aux1;
   const void* aux2;
+  const void* aux3;
+  void* aux4;
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -484,6 +486,67 @@ __device__ __forceinline__ void epi_chunk_affine(uint8_t* buf, int lane, const u
   }
 }
 
+// Epilogues 9 / 10 = 5 / 6, and on the way the two reductions the folded norm's BACKWARD needs, taken over this
+// chunk's 64 columns of the thread's row: p1 += sum dy * c, p2 += sum dy * acc.  gy = the row's 64 dy values (the
+// gradient that will reach this output) as 32 packed bf16 pairs, fetched into registers BEFORE the accumulator was
+// waited for: a load issued here, between the uses, would expose an L2 round trip per 8 columns.
+template <int EPI>
+__device__ __forceinline__ void epi_chunk_affine_dots(uint8_t* buf, int lane, const uint32_t (&r)[64], float rs,
+                                                      float rm, float2 cv, float2 dv, const uint32_t (&gy)[32],
+                                                      float& p1, float& p2) {
+  // cv / dv: c and d of the chunk's 64 columns, two columns per lane (as gamma in epilogue 11), read through shuffles:
+  // with the 32 registers of dy next to the accumulator there is no room for vectors of them
+  uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4));
+    const uint4 ru = *slot;
+    const uint32_t rw[4] = {ru.x, ru.y, ru.z, ru.w};
+    uint32_t ow[4];
+#pragma unroll
+    for (int h = 0; h < 4; ++h) {
+      const float2 rr = unpack_bf16x2(rw[h]);
+      const float2 gg = unpack_bf16x2(gy[j * 4 + h]);
+      const int src = j * 4 + h;  // the lane that holds columns 2 src and 2 src + 1
+      const float c0 = __shfl_sync(0xffffffffu, cv.x, src), c1 = __shfl_sync(0xffffffffu, cv.y, src);
+      const float d0 = __shfl_sync(0xffffffffu, dv.x, src), d1 = __shfl_sync(0xffffffffu, dv.y, src);
+      const float a0 = __uint_as_float(r[j * 8 + 2 * h]), a1 = __uint_as_float(r[j * 8 + 2 * h + 1]);
+      p1 = fmaf(gg.x, c0, fmaf(gg.y, c1, p1));
+      p2 = fmaf(gg.x, a0, fmaf(gg.y, a1, p2));
+      const float f0 = fmaf(rs, a0, fmaf(-rm, c0, d0)), f1 = fmaf(rs, a1, fmaf(-rm, c1, d1));
+      ow[h] = EPI == 9 ? pack_bf16x2(rr.x + f0, rr.y + f1) : pack_bf16x2(rr.x - f0, rr.y - f1);
+    }
+    *slot = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+  }
+}
+
+// Epilogue 11: the folded norm's backward: D = [h > 0] * (a * acc + b * h + c), h from the slab, acc = gamma * dn
+// (the GEMM's B operand is gamma . W: a scale per column applied here cost a shuffle per element, and this epilogue
+// belongs to a K = 512 GEMM whose main loop is shorter than its epilogue).
+__device__ __forceinline__ void epi_chunk_norm_bwd(uint8_t* buf, int lane, const uint32_t (&r)[64], float ca, float cb,
+                                                   float cc) {
+  uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4));
+    const uint4 ru = *slot;
+    const float2 f0 = unpack_bf16x2(ru.x), f1 = unpack_bf16x2(ru.y), f2 = unpack_bf16x2(ru.z), f3 = unpack_bf16x2(ru.w);
+    const float hh[8] = {f0.x, f0.y, f1.x, f1.y, f2.x, f2.y, f3.x, f3.y};
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float t = fmaf(ca, __uint_as_float(r[j * 8 + e]), fmaf(cb, hh[e], cc));
+      v[e] = hh[e] > 0.f ? t : 0.f;
+    }
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]);
+    o.w = pack_bf16x2(v[6], v[7]);
+    *slot = o;
+  }
+}
+
 // Epilogue 7: D = relu(acc), and the row's sum and sum of squares of the values AS STORED (bf16-rounded) are added to
 // (s1, s2): the statistics of the group norm that follows (src/model/basic.py:55-56), taken where the data is made.
 __device__ __forceinline__ void epi_chunk_relu_stats(uint8_t* buf, int lane, const uint32_t (&r)[64], float& s1,
@@ -520,12 +583,17 @@ struct Cfg {
   static constexpr int SMEM = BAR_OFF + 512 + 1024;
 };
 
-template <int CG>
+// SEQ: the instantiation for epilogues 9 / 10 (the row dots with a second tile): its epilogue warps hold that tile's
+// rows in registers and take the two column chunks one after the other.  A kernel of its own so that the register
+// allocation of every other epilogue stays what it was.
+// MODE 2: the instantiation for epilogue 11 (the folded norm's backward), split off for the same reason.
+template <int CG, int MODE = 0>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR, const TcParams p) {
   constexpr int STAGES = Cfg<CG>::STAGES;
   constexpr int B_STAGE = Cfg<CG>::B_STAGE;
+  constexpr bool SEQ = MODE == 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* smem_a = smem;
@@ -692,7 +760,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool live1 = c1 < nchunks && row0 < p.M && col1 < p.N;
         bulk_wait_read0_elect();  // last tile's stores have read both slabs (they were issued a whole tile ago)
         __syncwarp();
-        const bool has_r = p.epi >= 2 && p.epi <= 6;
+        const bool has_r = (p.epi >= 2 && p.epi <= 6) || (p.epi >= 9 && p.epi <= 11);
         if (has_r) {
           if (live0) tma_load_r_elect(smem_u32(buf0), &tmR, smem_u32(rb0), EPI_BUF_BYTES, col0, row0, t.glo, t.ghi);
           if (live1)
@@ -701,14 +769,55 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         // epilogues 5 / 6: this thread's row statistics (mean, rstd) of the folded group norm
         float rs = 0.f, rm = 0.f;
-        if (p.epi == 5 || p.epi == 6) {
-          if (row0 + lane < p.M) {
+        [[maybe_unused]] float rk = 0.f;
+        const bool row_live = row0 + lane < p.M;
+        if constexpr (MODE == 2) {  // (a, b, c) of the folded norm's backward for this thread's row
+          if (row_live) {
+            const float4 st = __ldg(reinterpret_cast<const float4*>(p.aux0) + (int64_t)(row0 + lane) * p.GLO + t.glo);
+            rs = st.x;
+            rm = st.y;
+            rk = st.z;
+          }
+        } else if (SEQ || p.epi == 5 || p.epi == 6) {
+          if (row_live) {
             const float2 st = __ldg(reinterpret_cast<const float2*>(p.aux0) + (int64_t)(row0 + lane) * p.GLO + t.glo);
             rs = st.y;
             rm = st.y * st.x;
           }
         }
-        float s1 = 0.f, s2 = 0.f;  // epilogue 7
+        // epilogues 9 / 10: this thread's row of the second tile (the upstream gradient, D's layout): the first chunk's
+        // 64 values into registers now -- the loads fly while the MMAs finish -- and the second chunk's line asked into
+        // L2; it is fetched when the first chunk is done.  The two chunks are taken one after the other (`seq`): both
+        // chunks' accumulators next to both rows of dy would not fit the register file.
+        constexpr bool seq = SEQ;
+        uint32_t gy[SEQ ? 32 : 1];
+        const bf16* dy_row = nullptr;
+        // epilogues 9 / 10: c (gv) and d (dv) of the two chunks, two columns per lane
+        float2 cdv[SEQ ? 4 : 1];  // c of chunk 0 / 1, d of chunk 0 / 1
+        if constexpr (SEQ) {
+          dy_row = reinterpret_cast<const bf16*>(p.aux3) + (int64_t)t.glo * p.d_glo + (int64_t)t.ghi * p.d_ghi +
+                   (int64_t)(row0 + lane) * p.d_ld;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            uint4 a = make_uint4(0u, 0u, 0u, 0u);
+            if (row_live && live0) a = __ldg(reinterpret_cast<const uint4*>(dy_row + col0) + q);
+            gy[q * 4] = a.x; gy[q * 4 + 1] = a.y; gy[q * 4 + 2] = a.z; gy[q * 4 + 3] = a.w;
+          }
+          if (row_live && live1) asm volatile("prefetch.global.L2 [%0];" ::"l"(dy_row + col1));
+          // c (in gv0 / gv1) and d (dv0 / dv1) of the two chunks, two columns per lane
+          const float* const cvec = reinterpret_cast<const float*>(p.aux1) + (int64_t)t.glo * p.N;
+          const float* const dvec = reinterpret_cast<const float*>(p.aux2) + (int64_t)t.glo * p.N;
+          cdv[0] = cdv[1] = cdv[2] = cdv[3] = make_float2(0.f, 0.f);
+          if (live0) {
+            cdv[0] = __ldg(reinterpret_cast<const float2*>(cvec + col0) + lane);
+            cdv[2] = __ldg(reinterpret_cast<const float2*>(dvec + col0) + lane);
+          }
+          if (live1) {
+            cdv[1] = __ldg(reinterpret_cast<const float2*>(cvec + col1) + lane);
+            cdv[3] = __ldg(reinterpret_cast<const float2*>(dvec + col1) + lane);
+          }
+        }
+        float s1 = 0.f, s2 = 0.f;  // epilogue 7 (sum, sum of squares); 9 / 10 (the two dot products)
         mbar_wait(&tfull_bar[acc], acc_phase, 3);
         tcgen05_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
@@ -717,24 +826,49 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tmem_ld32(taddr0 + (uint32_t)(c0 * EPI_BOX_COLS), *reinterpret_cast<uint32_t (*)[32]>(&ra[0]));
           tmem_ld32(taddr0 + (uint32_t)(c0 * EPI_BOX_COLS + 32), *reinterpret_cast<uint32_t (*)[32]>(&ra[32]));
         }
-        if (c1 < nchunks) {
+        if (!seq && c1 < nchunks) {
           tmem_ld32(taddr0 + (uint32_t)(c1 * EPI_BOX_COLS), *reinterpret_cast<uint32_t (*)[32]>(&rc[0]));
           tmem_ld32(taddr0 + (uint32_t)(c1 * EPI_BOX_COLS + 32), *reinterpret_cast<uint32_t (*)[32]>(&rc[32]));
         }
         tmem_ld_wait();
-        tcgen05_fence_before();
-        mbar_arrive_cta<CG>(&tempty_bar[acc], 0);  // accumulator is in registers: release it
+        if (!seq) {
+          tcgen05_fence_before();
+          mbar_arrive_cta<CG>(&tempty_bar[acc], 0);  // accumulator is in registers: release it
+        }
 #pragma unroll
         for (int sl = 0; sl < 2; ++sl) {
+          if (seq && sl == 1) {  // the second chunk's dy row and accumulator only now (see above), then release
+            if constexpr (SEQ) {
+#pragma unroll
+              for (int q = 0; q < 8; ++q) {
+                uint4 a = make_uint4(0u, 0u, 0u, 0u);
+                if (row_live && live1) a = __ldg(reinterpret_cast<const uint4*>(dy_row + col1) + q);
+                gy[q * 4] = a.x; gy[q * 4 + 1] = a.y; gy[q * 4 + 2] = a.z; gy[q * 4 + 3] = a.w;
+              }
+            }
+            if (c1 < nchunks) {  // into the first chunk's registers: they are free now
+              tmem_ld32(taddr0 + (uint32_t)(c1 * EPI_BOX_COLS), *reinterpret_cast<uint32_t (*)[32]>(&ra[0]));
+              tmem_ld32(taddr0 + (uint32_t)(c1 * EPI_BOX_COLS + 32), *reinterpret_cast<uint32_t (*)[32]>(&ra[32]));
+            }
+            tmem_ld_wait();
+            tcgen05_fence_before();
+            mbar_arrive_cta<CG>(&tempty_bar[acc], 0);
+          }
           const bool live = sl == 0 ? live0 : live1;
           if (!live) continue;
           uint8_t* const buf = buf0 + sl * EPI_BUF_BYTES;
-          const uint32_t (&r)[64] = sl == 0 ? ra : rc;
+          const uint32_t (&r)[64] = (seq || sl == 0) ? ra : rc;
           if (has_r) {
             mbar_wait(rb0 + sl, (rphase >> sl) & 1u, 4);
             rphase ^= 1u << sl;
           }
           const int colx = sl == 0 ? col0 : col1;
+          if constexpr (SEQ) {
+            if (p.epi == 9) epi_chunk_affine_dots<9>(buf, lane, r, rs, rm, cdv[sl], cdv[2 + sl], gy, s1, s2);
+            else epi_chunk_affine_dots<10>(buf, lane, r, rs, rm, cdv[sl], cdv[2 + sl], gy, s1, s2);
+          } else if constexpr (MODE == 2) {
+            epi_chunk_norm_bwd(buf, lane, r, rs, rm, rk);
+          } else
           switch (p.epi) {
             case 0: epi_chunk<0>(buf, lane, r); break;
             case 1: epi_chunk<1>(buf, lane, r); break;
@@ -757,7 +891,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           __syncwarp();
           tma_store_commit_elect(&tmD, smem_u32(buf), sl == 0 ? col0 : col1, row0, t.glo, t.ghi, 0);
         }
-        if (p.epi == 7 && row0 + lane < p.M) {
+        if (SEQ && row_live) {
+          // one pair per row, group, 256-column tile and epilogue warp: [M][GLO][2 * tiles_n] float2
+          float2* part = reinterpret_cast<float2*>(p.aux4);
+          part[((int64_t)(row0 + lane) * p.GLO + t.glo) * (2 * p.tiles_n) + 2 * (t.n0 / p.BN) + half] =
+              make_float2(s1, s2);
+        }
+        if (MODE == 0 && p.epi == 7 && row0 + lane < p.M) {
           // one (sum, sum of squares) per row, tile and epilogue warp: [M][2 * tiles_n] float2, summed by the consumer
           float2* part = reinterpret_cast<float2*>(const_cast<void*>(p.aux0));
           part[(int64_t)(row0 + lane) * (2 * p.tiles_n) + 2 * (t.n0 / p.BN) + half] = make_float2(s1, s2);
@@ -782,6 +922,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const float row_scale =
             (p.epi == 8 && row_ok) ? __ldg(reinterpret_cast<const float*>(p.aux0) + (int64_t)t.glo * p.M + m) : 1.f;
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
+        // epilogue 8 with aux1 / aux2: this row's dot product of the raw accumulator with a bf16 tile in D's layout
+        const bool row_dot = p.epi == 8 && p.aux1 != nullptr && row_ok;
+        float wdot = 0.f;
         for (int c = half; c < p.BN / 32; c += 2) {
           uint32_t r[32];
           tmem_ld32(taddr0 + (uint32_t)(c * 32), r);
@@ -809,6 +952,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
                 epi_apply(v, rr, p.epi);
                 if (p.epi == 8) {
+                  if (row_dot) {
+                    const uint4 wu = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<const bf16*>(p.aux1) + row_off + n));
+                    const float2 w0 = unpack_bf16x2(wu.x), w1 = unpack_bf16x2(wu.y), w2 = unpack_bf16x2(wu.z),
+                                 w3 = unpack_bf16x2(wu.w);
+                    wdot = fmaf(w0.x, v[0], fmaf(w0.y, v[1], fmaf(w1.x, v[2], fmaf(w1.y, v[3], wdot))));
+                    wdot = fmaf(w2.x, v[4], fmaf(w2.y, v[5], fmaf(w3.x, v[6], fmaf(w3.y, v[7], wdot))));
+                  }
 #pragma unroll
                   for (int j = 0; j < 8; ++j) v[j] *= row_scale;
                 }
@@ -845,6 +995,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
           }
         }
+        if (row_dot) atomicAdd(reinterpret_cast<float*>(const_cast<void*>(p.aux2)) + (int64_t)t.glo * p.M + m, wdot);
         tcgen05_fence_before();
         mbar_arrive_cta<CG>(&tempty_bar[acc], 0);  // 256*CG arrivals release the accumulator to the MMA warp
         if (++acc == 2) {
@@ -1049,9 +1200,19 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
       (reinterpret_cast<uintptr_t>(g.D) & 15) != 0 || (g.R && (reinterpret_cast<uintptr_t>(g.R) & 15) != 0))
     TC_NOTSUP("obst_gemm(tc): output not 16-byte addressable (N=%d ld=%lld)", g.N, (long long)g.d_ld);
   if (g.accumulate && !out_f32) TC_NOTSUP("obst_gemm(tc): accumulate needs fp32 output");
-  if (g.epi >= 2 && g.epi <= 6 && !g.R) TC_NOTSUP("obst_gemm(tc): epilogue %d needs R", g.epi);
-  if ((g.epi == 5 || g.epi == 6) && (!g.aux0 || !g.aux1 || !g.aux2 || g.GHI != 1 || out_f32 || g.N % 64 != 0))
+  const bool affine = g.epi == 5 || g.epi == 6 || g.epi == 9 || g.epi == 10;
+  if (((g.epi >= 2 && g.epi <= 6) || (g.epi >= 9 && g.epi <= 11)) && !g.R)
+    TC_NOTSUP("obst_gemm(tc): epilogue %d needs R", g.epi);
+  if (affine && (!g.aux0 || !g.aux1 || !g.aux2 || g.GHI != 1 || out_f32 || g.N % 64 != 0))
     TC_NOTSUP("obst_gemm(tc): epilogue %d needs aux0..2, GHI == 1, bf16 output and N %% 64 == 0", g.epi);
+  if ((g.epi == 9 || g.epi == 10) && (!g.aux3 || !g.aux4 || (reinterpret_cast<uintptr_t>(g.aux3) & 15) != 0))
+    TC_NOTSUP("obst_gemm(tc): epilogue %d needs aux3 (16-byte aligned, D's layout) and aux4", g.epi);
+  if (g.epi == 11 && (!g.aux0 || g.GHI != 1 || out_f32 || g.N % 64 != 0 ||
+                      (reinterpret_cast<uintptr_t>(g.aux0) & 15) != 0))
+    TC_NOTSUP("obst_gemm(tc): epilogue 11 needs aux0 (float4 rows), GHI == 1, bf16 output and N %% 64 == 0");
+  if (g.epi == 8 && g.aux1 && (!g.aux2 || (reinterpret_cast<uintptr_t>(g.aux1) & 15) != 0))
+    TC_NOTSUP("obst_gemm(tc): epilogue 8 with aux1 needs aux2 and a 16-byte aligned aux1");
+  if (g.epi > 11 || g.epi < 0) TC_NOTSUP("obst_gemm(tc): unknown epilogue %d", g.epi);
   if (g.epi == 7 && (!g.aux0 || out_f32 || g.N % 256 != 0 || g.GLO * g.GHI != 1))
     TC_NOTSUP("obst_gemm(tc): epilogue 7 needs aux0, bf16 output, one group and N %% 256 == 0");
   if (g.epi == 8 && (!g.aux0 || !g.accumulate || g.GHI != 1))
@@ -1065,6 +1226,8 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   p.aux0 = g.aux0;
   p.aux1 = g.aux1;
   p.aux2 = g.aux2;
+  p.aux3 = g.aux3;
+  p.aux4 = g.aux4;
   p.d_ld = g.d_ld;
   p.d_glo = g.d_glo;
   p.d_ghi = g.d_ghi;
@@ -1091,6 +1254,10 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
     return e ? atoi(e) : 0;
   }();
   if (tri_cg == 1 && (g.tri == 1 || g.tri == 2)) cg = 1;
+  if (g.epi >= 9 && g.epi <= 11 && cg != 2) {
+    if (strict) set_error("obst_gemm(tc): epilogue %d exists in the CTA-pair kernel only (M > 128, N > 64)", g.epi);
+    return OBST_ENOTSUP;
+  }
   p.tiles_m = (g.M + BM * cg - 1) / (BM * cg);
   p.tiles_n = (g.N + p.BN - 1) / p.BN;
   p.tri = g.tri;
@@ -1162,12 +1329,12 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   if (!out_f32 && !g.accumulate) {
     int rd = make_out_map(g.D, g.N, g.M, g.GLO, g.GHI, g.d_ld, g.d_glo, g.d_ghi, &tmD, strict);
     int rr = OBST_OK;
-    if (rd == OBST_OK && g.epi >= 2 && g.epi <= 6)
+    if (rd == OBST_OK && ((g.epi >= 2 && g.epi <= 6) || (g.epi >= 9 && g.epi <= 11)))
       rr = make_out_map(g.R, g.N, g.M, g.GLO, g.GHI, g.d_ld, g.d_glo, g.d_ghi, &tmR, strict);
     if (rd == OBST_ECUDA || rr == OBST_ECUDA) return OBST_ECUDA;
     p.tma_store = (rd == OBST_OK && rr == OBST_OK) ? 1 : 0;
   }
-  if (g.epi >= 5 && g.epi <= 7 && !p.tma_store) {
+  if (((g.epi >= 5 && g.epi <= 7) || (g.epi >= 9 && g.epi <= 11)) && !p.tma_store) {
     if (strict) set_error("obst_gemm(tc): epilogue %d needs a TMA-addressable output", g.epi);
     return OBST_ENOTSUP;
   }
@@ -1178,6 +1345,10 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
                                          Cfg<1>::SMEM);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(gemm_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_tc_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_tc_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM);
     if (e != cudaSuccess) {
       set_error("obst_gemm(tc): cannot opt in to %d B of shared memory: %s", Cfg<2>::SMEM, cudaGetErrorString(e));
       return OBST_ECUDA;
@@ -1208,7 +1379,9 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 2 : 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2>, tmA, tmB, tmD, tmR, p);
+    cudaError_t e = (g.epi == 9 || g.epi == 10) ? cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2, 1>, tmA, tmB, tmD, tmR, p)
+                    : g.epi == 11               ? cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2, 2>, tmA, tmB, tmD, tmR, p)
+                                                : cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2>, tmA, tmB, tmD, tmR, p);
     if (e != cudaSuccess) {
       set_error("obst_gemm(tc): cluster launch failed: %s", cudaGetErrorString(e));
       return OBST_ECUDA;
@@ -1232,10 +1405,11 @@ extern "C" int obst_gemm(const obst_gemm_desc* d, int backend, void* stream) {
   OBST_REQUIRE(d->M > 0 && d->N > 0 && d->KI > 0 && d->KO > 0 && d->GLO > 0 && d->GHI > 0,
                "obst_gemm: bad sizes M=%d N=%d KI=%d KO=%d GLO=%d GHI=%d", d->M, d->N, d->KI, d->KO, d->GLO, d->GHI);
   OBST_REQUIRE(d->A.ptr && d->B.ptr && d->D, "obst_gemm: null operand");
-  OBST_REQUIRE(d->tri >= 0 && d->tri <= 3 && d->epi >= 0 && d->epi <= 8, "obst_gemm: bad tri/epi %d/%d", d->tri, d->epi);
-  OBST_REQUIRE(!(d->epi >= 2 && d->epi <= 6 && d->R == nullptr), "obst_gemm: epilogue %d needs R", d->epi);
+  OBST_REQUIRE(d->tri >= 0 && d->tri <= 3 && d->epi >= 0 && d->epi <= 11, "obst_gemm: bad tri/epi %d/%d", d->tri, d->epi);
+  OBST_REQUIRE(!(((d->epi >= 2 && d->epi <= 6) || d->epi >= 9) && d->R == nullptr), "obst_gemm: epilogue %d needs R",
+               d->epi);
   OBST_REQUIRE(!(d->accumulate && d->dtype_out != OBST_F32), "obst_gemm: accumulate needs fp32 output");
-  OBST_REQUIRE(!(d->accumulate && d->epi >= 2 && d->epi <= 7),
+  OBST_REQUIRE(!(d->accumulate && d->epi >= 2 && d->epi != 8),
                "obst_gemm: accumulate cannot be combined with an R epilogue");
   OBST_REQUIRE(!(d->epi >= 5 && d->aux0 == nullptr), "obst_gemm: epilogue %d needs aux0", d->epi);
   OBST_REQUIRE(!((d->tri == 1 || d->tri == 2) && d->KO != 1), "obst_gemm: tri 1/2 need KO == 1");
@@ -1248,7 +1422,7 @@ extern "C" int obst_gemm(const obst_gemm_desc* d, int backend, void* stream) {
   p.M = d->M; p.N = d->N; p.KI = d->KI; p.KO = d->KO; p.GLO = d->GLO; p.GHI = d->GHI;
   p.dtype_in = d->dtype_in; p.dtype_out = d->dtype_out;
   p.tri = d->tri; p.epi = d->epi; p.accumulate = d->accumulate; p.splits = d->splits;
-  p.aux0 = d->aux0; p.aux1 = d->aux1; p.aux2 = d->aux2;
+  p.aux0 = d->aux0; p.aux1 = d->aux1; p.aux2 = d->aux2; p.aux3 = d->aux3; p.aux4 = d->aux4;
   cudaStream_t st = (cudaStream_t)stream;
   if (d->epi >= 5) {  // the fused-norm epilogues exist in the tcgen05 kernel only
     OBST_REQUIRE(backend != 1, "obst_gemm: epilogue %d is not available in the SIMT kernel", d->epi);

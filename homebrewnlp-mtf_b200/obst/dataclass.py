@@ -12,6 +12,8 @@ Extensions (no counterpart in the reference, all optional):
   device            torch device string
   fold_mid_norm     fold the group norm between W_mid and W_out into those two GEMMs (bf16, tcgen05 path): same
                     function, the normalised tensor is never written (model/basic.py).  Default true.
+  fold_mid_norm_backward  in the reversible backward also fold that norm's own backward into the GEMMs (the
+                    gradient of W_out's input is never written either).  Default true.
   revnet_store_activations  keep every sub-block's intermediates instead of recomputing / reconstructing them in
                     backward (memory for speed; numerics differ from the reversible path only by the reference's
                     reconstruction rounding).  Default false = the reference's algorithm.
@@ -61,7 +63,8 @@ DEFAULTS: typing.Dict[str, typing.Any] = dict(
 )
 # extensions of this implementation (see module docstring)
 EXTENSIONS: typing.Dict[str, typing.Any] = dict(micro_batch_size=None, gemm_backend=0, device="cuda", init_seed=0,
-                                                revnet_store_activations=False, fold_mid_norm=True)
+                                                revnet_store_activations=False, fold_mid_norm=True,
+                                                fold_mid_norm_backward=True)
 
 
 class BlockConfig:

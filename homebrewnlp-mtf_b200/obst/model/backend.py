@@ -58,7 +58,7 @@ class Variable:
         self.refresh_folded()
 
     # -- a group norm folded into this weight (basic._mid_norm_out_folded): (gamma . W)^T, gamma^T W, beta^T W ----
-    folded = None  # (gamma variable, beta variable, heads, kin, kout, wg_t, cvec, dvec, gamma_f)
+    folded = None  # (gamma variable, beta variable, heads, kin, kout, wg_t, cvec, dvec, gamma_f, wg)
 
     def fold_norm(self, gamma: typing.Optional["Variable"], beta: typing.Optional["Variable"], heads: int, kin: int,
                   kout: int):
@@ -68,15 +68,16 @@ class Variable:
                            torch.empty((heads, kout, kin), dtype=self.value.dtype, device=dev),
                            torch.empty((heads, kout), dtype=torch.float32, device=dev),
                            torch.empty((heads, kout), dtype=torch.float32, device=dev),
-                           torch.empty((heads, kin), dtype=torch.float32, device=dev))
+                           torch.empty((heads, kin), dtype=torch.float32, device=dev),
+                           torch.empty((heads, kin, kout), dtype=self.value.dtype, device=dev))
             self.refresh_folded()
         return self.folded[5:]
 
     def fold_entry(self):
-        """(w, gamma, beta, wg_t, cvec, dvec, gamma_f): one row of a native.fold_items table."""
-        gamma, beta, heads, kin, kout, wg_t, cvec, dvec, gamma_f = self.folded
+        """(w, gamma, beta, wg_t, cvec, dvec, gamma_f, wg): one row of a native.fold_items table."""
+        gamma, beta, heads, kin, kout, wg_t, cvec, dvec, gamma_f, wg = self.folded
         return (self.value, None if gamma is None else gamma.value, None if beta is None else beta.value, wg_t, cvec,
-                dvec, gamma_f)
+                dvec, gamma_f, wg)
 
     def refresh_folded(self):
         """Called whenever this weight or the norm's scale / shift moved outside the optimizer (creation, weight

@@ -223,7 +223,7 @@ def _mid_norm_out_folded(args: BlockArgs) -> Tensor:
     if group != [params.head_dim] or h.dims != lead + group + contract or shape_size(contract) != width:
         raise NotImplementedError(f"folded norm: unexpected layout {h.dims} / {old} -> {new}")
     G, Kc, Np = heads, width, shape_size(produce)
-    wg_t, cvec, dvec, gamma_f = var.fold_norm(gamma, beta, G, Kc, Np)
+    wg_t, cvec, dvec, gamma_f, wg = var.fold_norm(gamma, beta, G, Kc, Np)
     out_dims = lead + group + produce
     if pending is not None:
         buf, sign, dst = pending
@@ -233,8 +233,22 @@ def _mid_norm_out_folded(args: BlockArgs) -> Tensor:
         buf = dst = torch.zeros([d.size for d in out_dims], dtype=h.data.dtype, device=h.data.device)
         sign = 1.0
     hd = h.data
-    native.gemm(native.operand(hd, G * Kc, 1, s_glo=Kc), native.operand(wg_t, Kc, 1, s_glo=Kc * Np), dst, T, Np, Kc,
-                GLO=G, d_ld=G * Np, d_glo=Np, R=buf, epi=5 if sign > 0 else 6, backend=2, aux=(stats, cvec, dvec))
+    # The reversible backward knows the gradient dy of this block's output while it recomputes the block
+    # (params.upstream_grad, src/model/revnet.py:91-120): W_out's epilogue then also takes the two per-row reductions
+    # of the norm's backward -- sum_j gamma_j dn_j = dy . (gamma^T W) and sum_j gamma_j h_j dn_j = dy . (h @ (gamma.W)),
+    # the latter being a dot product with this very accumulator -- and dn = dy @ W^T never has to be written.
+    up = getattr(params, "upstream_grad", None)
+    fold_bwd = (getattr(params, "fold_mid_norm_backward", True) and up is not None and pending is not None and params.tape is not None and gamma is not None
+                and up.dtype == hd.dtype and tuple(up.shape) == tuple(dst.shape) and up.is_contiguous())
+    dots = None
+    if fold_bwd:
+        dots = torch.empty((T, G, 2 * ((Np + 255) // 256), 2), dtype=torch.float32, device=hd.device)
+        native.gemm(native.operand(hd, G * Kc, 1, s_glo=Kc), native.operand(wg_t, Kc, 1, s_glo=Kc * Np), dst, T, Np, Kc,
+                    GLO=G, d_ld=G * Np, d_glo=Np, R=buf, epi=9 if sign > 0 else 10, backend=2,
+                    aux=(stats, cvec, dvec, up, dots))
+    else:
+        native.gemm(native.operand(hd, G * Kc, 1, s_glo=Kc), native.operand(wg_t, Kc, 1, s_glo=Kc * Np), dst, T, Np, Kc,
+                    GLO=G, d_ld=G * Np, d_glo=Np, R=buf, epi=5 if sign > 0 else 6, backend=2, aux=(stats, cvec, dvec))
     if params.tape is not None:
         w = var.value
         g_val = None if gamma is None else gamma.value
@@ -246,6 +260,24 @@ def _mid_norm_out_folded(args: BlockArgs) -> Tensor:
             v = torch.zeros((2, G, Np), dtype=torch.float32, device=dy.device)
             native.rowscale_colsum(dy, stats, dyr, v[0], v[1], T, G, Np)
             grad = var.ensure_grad()
+            folded = dots is not None and mask is not None and dy.data_ptr() == up.data_ptr()
+            if folded:
+                # ... the same GEMM also leaves sum_k W_jk G_jk in gamma's gradient (G = its raw accumulator), which
+                # with the two column sums is the norm's scale / shift gradient
+                dgamma = gamma.ensure_grad()
+                dbeta = None if beta is None else beta.ensure_grad()
+                native.gemm(native.operand(hd, 1, G * Kc, s_glo=Kc), native.operand(dyr, 1, G * Np, s_glo=Np), grad, Kc,
+                            Np, T, GLO=G, d_ld=Np, d_glo=Kc * Np, accumulate=True, epi=8, backend=2,
+                            aux=(gamma_f, w, dgamma))
+                native.norm_affine_grad(w, v[0], v[1], dgamma, dbeta, G, Kc, Np)
+                native.norm_wgrad_rank1(grad, g_val, b_val, v[0], v[1], G, Kc, Np)
+                coeffs = torch.empty((T, G, 4), dtype=torch.float32, device=dy.device)
+                native.norm_bwd_coeffs(dots, stats, coeffs, T, G, dots.shape[2], Kc)
+                # dh = [h > 0] (a (dy @ (gamma.W)^T) + b h + c): the norm's and the ReLU's backward in the dgrad epilogue
+                dh = torch.empty_like(hd)
+                native.gemm(native.operand(dy, G * Np, 1, s_glo=Np), native.operand(wg, Np, 1, s_glo=Kc * Np), dh, T, Kc,
+                            Np, GLO=G, d_ld=G * Kc, d_glo=Kc, R=hd, epi=11, backend=2, aux=(coeffs,))
+                return dh
             native.gemm(native.operand(hd, 1, G * Kc, s_glo=Kc), native.operand(dyr, 1, G * Np, s_glo=Np), grad, Kc, Np,
                         T, GLO=G, d_ld=Np, d_glo=Kc * Np, accumulate=True, epi=8, backend=2, aux=(gamma_f,))
             native.norm_wgrad_rank1(grad, g_val, b_val, v[0], v[1], G, Kc, Np)

@@ -115,7 +115,11 @@ def reversible_body(params: ModelParameter, src: Tensor) -> Tensor:
                 reset_shared_ordinals(params, str(i), f"{c}v")
                 # state after block j is (p, q) = (x2_in, x1_in + f(x2_in))
                 params.tape = []
-                _apply(params, config, i, Tensor(p, dims), q, -1.0)   # q <- x1_in = y1 - f(x2_in)
+                params.upstream_grad = dq  # the gradient f's output will receive: layers may fold reductions with it
+                try:
+                    _apply(params, config, i, Tensor(p, dims), q, -1.0)   # q <- x1_in = y1 - f(x2_in)
+                finally:
+                    params.upstream_grad = None
                 tape, params.tape = params.tape, None
                 run_tape(tape, dq, acc=dp)                              # dp <- dy2 + J^T dy1
                 del tape

@@ -31,7 +31,8 @@ class GemmDesc(ctypes.Structure):
     _fields_ = [("dtype_in", c_i32), ("dtype_out", c_i32), ("M", c_i32), ("N", c_i32), ("KI", c_i32), ("KO", c_i32),
                 ("GLO", c_i32), ("GHI", c_i32), ("A", Operand), ("B", Operand), ("D", c_void_p), ("R", c_void_p),
                 ("d_ld", c_i64), ("d_glo", c_i64), ("d_ghi", c_i64), ("tri", c_i32), ("epi", c_i32),
-                ("accumulate", c_i32), ("splits", c_i32), ("aux0", c_void_p), ("aux1", c_void_p), ("aux2", c_void_p)]
+                ("accumulate", c_i32), ("splits", c_i32), ("aux0", c_void_p), ("aux1", c_void_p), ("aux2", c_void_p),
+                ("aux3", c_void_p), ("aux4", c_void_p)]
 
 
 class OptTensor(ctypes.Structure):
@@ -42,7 +43,7 @@ class OptTensor(ctypes.Structure):
 
 class FoldItem(ctypes.Structure):  # obst_fold_item
     _fields_ = [("w", c_void_p), ("gamma", c_void_p), ("beta", c_void_p), ("wg_t", c_void_p), ("cvec", c_void_p),
-                ("dvec", c_void_p), ("gamma_f", c_void_p)]
+                ("dvec", c_void_p), ("gamma_f", c_void_p), ("wg", c_void_p)]
 
 
 class TransposeItem(ctypes.Structure):  # obst_transpose_item
@@ -78,6 +79,8 @@ SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] 
     "obst_fold_norm_weight": (c_int, [c_void_p, c_i32, c_i32, c_i32, c_i32, c_void_p]),
     "obst_rowscale_colsum": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_void_p]),
     "obst_norm_wgrad_rank1": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_void_p]),
+    "obst_norm_bwd_coeffs": (c_int, [c_void_p, c_void_p, c_void_p, c_i64, c_i32, c_i32, c_i32, c_void_p]),
+    "obst_norm_affine_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_i32, c_i32, c_i32, c_void_p]),
     "obst_act_fwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_act_bwd": (c_int, [c_int, c_i32, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
     "obst_gate_fwd": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_i64, c_void_p]),
@@ -236,7 +239,9 @@ def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO
         desc.R = None
     desc.d_ld, desc.d_glo, desc.d_ghi = d_ld, d_glo, d_ghi
     desc.tri, desc.epi, desc.accumulate, desc.splits = tri, epi, int(accumulate), splits
-    for i, a in enumerate(aux):  # epilogues 5..8: row statistics / folded-norm vectors / row scales
+    for i, a in enumerate(aux):  # epilogues 5..11: row statistics / folded-norm vectors / row scales / second tiles
+        if a is None:
+            continue
         _cuda(a)
         setattr(desc, f"aux{i}", a.data_ptr())
     if _PROFILE is not None:
@@ -346,9 +351,11 @@ def norm_stats_finalize(partials, stats, rows: int, heads: int, per_head: int, w
 
 
 def fold_items(entries) -> torch.Tensor:
-    """Device table of obst_fold_item from (w, gamma, beta, wg_t, cvec, dvec, gamma_f) tensor tuples."""
+    """Device table of obst_fold_item from (w, gamma, beta, wg_t, cvec, dvec, gamma_f[, wg]) tensor tuples."""
     items = (FoldItem * len(entries))()
-    for it, (w, gamma, beta, wg_t, cvec, dvec, gamma_f) in zip(items, entries):
+    for it, entry in zip(items, entries):
+        w, gamma, beta, wg_t, cvec, dvec, gamma_f = entry[:7]
+        it.wg = _p(entry[7]) if len(entry) > 7 else None
         _cuda(w, wg_t, cvec, dvec, gamma_f)
         if w.dtype != torch.bfloat16:
             raise NativeError("fold_norm_weight: bf16 weights only")
@@ -365,6 +372,20 @@ def rowscale_colsum(dy, stats, dyr, v1, v2, tokens: int, heads: int, width: int)
     _cuda(dy, stats, dyr, v1, v2)
     check(load().obst_rowscale_colsum(_p(dy), _p(stats), _p(dyr), _p(v1), _p(v2), tokens, heads, width, stream_ptr()),
           "obst_rowscale_colsum")
+
+
+def norm_bwd_coeffs(partials, stats, coeffs, rows: int, heads: int, nparts: int, width: int):
+    """(a, b, c) per (row, head) of the folded norm's backward from epilogue 9 / 10's partial dot products."""
+    _cuda(partials, stats, coeffs)
+    check(load().obst_norm_bwd_coeffs(_p(partials), _p(stats), _p(coeffs), rows, heads, nparts, width, stream_ptr()),
+          "obst_norm_bwd_coeffs")
+
+
+def norm_affine_grad(w, v1, v2, dgamma, dbeta, heads: int, kin: int, kout: int):
+    """dgamma -= W v1, dbeta += W v2 per head (the halves of the norm's scale / shift gradients that need no dn)."""
+    _cuda(w, v1, v2)
+    check(load().obst_norm_affine_grad(_p(w), _p(v1), _p(v2), _p(dgamma), _p(dbeta), heads, kin, kout, stream_ptr()),
+          "obst_norm_affine_grad")
 
 
 def norm_wgrad_rank1(dw, gamma, beta, v1, v2, heads: int, kin: int, kout: int):

@@ -78,7 +78,18 @@ int64_t obst_path_count(int32_t which);
  *        7 (tcgen05 backend, bf16 out, one group, N % 256 == 0): D = relu(acc), and aux0 (float2
  *            [M, N/128]) receives per row and 128-column slice the (sum, sum of squares) of the stored values:
  *            entry [m, 2*(n/256) + w] covers columns 256*(n/256) + 64*(w + 2i) .. +63, i = 0, 1
- *        8 (tcgen05 backend, accumulate): D += aux0[g_lo, m] * acc, aux0 fp32 [GLO, M]
+ *        8 (tcgen05 backend, accumulate): D += aux0[g_lo, m] * acc, aux0 fp32 [GLO, M].  With aux1 (bf16, D's
+ *            layout) and aux2 (fp32 [GLO, M]) set, also aux2[g_lo, m] += sum_n aux1[g_lo, m, n] * acc[m, n]
+ *            (atomics): the gamma gradient of a folded group norm, d gamma_j = sum_k W_jk (G_jk - ...), taken
+ *            where the weight gradient's accumulator G is (src/model/normalization.py:22-34 differentiated)
+ *        9/10 = 5/6, plus two row dot products of the accumulator's tile with a second tile aux3 (bf16, D's
+ *            layout: the gradient that will reach this output): aux4 (float2 [M, GLO, 2 * ceil(N/256)]) receives
+ *            ( sum_n aux3*c , sum_n aux3*acc ) per row, group, 256-column tile and epilogue warp pair; their
+ *            sums are the two reductions of the folded norm's backward (obst_norm_bwd_coeffs)
+ *        11 (tcgen05 backend, bf16 out, GHI == 1): the folded norm's backward applied to this GEMM's output:
+ *            D = [R > 0] * ( a[m,g] * acc + b[m,g] * R + c[m,g] ) with acc = dy @ (gamma . W)^T = gamma * dn (B is
+ *            obst_fold_item.wg), R = the norm's input h (a ReLU output: the mask is its own derivative),
+ *            aux0 = float4 (a, b, c, -) [M, GLO] from obst_norm_bwd_coeffs
  *   accumulate!=0: D (fp32 only) += value with atomics (split-K allowed; tri==3 masks the store)
  *   D/R address: ptr[g_lo*d_glo + g_hi*d_ghi + m*d_ld + n]; R may alias D.
  * backend: 0 auto (tcgen05 when dtype_in is bf16 and the geometry is TMA-legal, else SIMT),
@@ -106,9 +117,11 @@ typedef struct obst_gemm_desc {
   int32_t epi;
   int32_t accumulate;
   int32_t splits; /* split-K factor for accumulate mode; 0 = choose */
-  const void* aux0; /* epilogues 5..8, else NULL */
+  const void* aux0; /* epilogues 5..11, else NULL */
   const void* aux1;
   const void* aux2;
+  const void* aux3;
+  void* aux4;
 } obst_gemm_desc;
 
 int obst_gemm(const obst_gemm_desc* desc, int backend, void* stream);
@@ -148,7 +161,7 @@ int obst_gn_bwd(int dtype, const void* dy, const void* x, const void* gamma, con
  *   obst_fold_norm_weight     for each item of a DEVICE table (all weights of one shape in one launch, once per
  *                             weight update): w AT [heads, kin, kout], gamma / beta AT [heads, kin] (NULL = 1 / 0)
  *                             -> wg_t AT [heads, kout, kin] = (gamma.W)^T, cvec = gamma^T W and dvec = beta^T W
- *                             fp32 [heads, kout], gamma_f fp32 [heads, kin]
+ *                             fp32 [heads, kout], gamma_f fp32 [heads, kin], wg AT [heads, kin, kout] = gamma.W
  *   obst_rowscale_colsum      dyr = rstd . dy (AT [tokens, heads, width]), v1[h,:] += sum_t rstd mean dy,
  *                             v2[h,:] += sum_t dy (fp32 [heads, width], atomics; width 256 or 512)
  *   obst_norm_wgrad_rank1     dw[h,j,k] += -gamma[h,j] v1[h,k] + beta[h,j] v2[h,k]   (dw fp32 [heads, kin, kout])
@@ -163,6 +176,7 @@ typedef struct obst_fold_item {
   float* cvec;
   float* dvec;
   float* gamma_f;
+  void* wg; /* AT [heads, kin, kout] = gamma . W in W's own layout (the dgrad's B operand for epilogue 11), or NULL */
 } obst_fold_item;
 int obst_fold_norm_weight(const obst_fold_item* items, int32_t nitems, int32_t heads, int32_t kin, int32_t kout,
                           void* stream);
@@ -170,6 +184,19 @@ int obst_rowscale_colsum(const void* dy, const float* stats, void* dyr, float* v
                          int32_t heads, int32_t width, void* stream);
 int obst_norm_wgrad_rank1(float* dw, const void* gamma, const void* beta, const float* v1, const float* v2,
                           int32_t heads, int32_t kin, int32_t kout, void* stream);
+/* The norm's own backward folded into the GEMMs as well (src/model/normalization.py:22-34 differentiated; used by
+ * the reversible backward, where the gradient dy of the block's output is known while W_out is recomputed):
+ *   obst_norm_bwd_coeffs    partials float2 [rows, heads, nparts] from obst_gemm epilogues 9 / 10 + stats float2
+ *                           (mean, rstd) [rows, heads] -> coeffs float4 (a, b, c, 0) [rows, heads] for epilogue 11:
+ *                           dh = [h > 0] (a gamma dn + b h + c), gamma dn = dy @ (gamma . W)^T the dgrad accumulator
+ *   obst_norm_affine_grad   dgamma[h,j] -= sum_k W[h,j,k] v1[h,k]; dbeta[h,j] += sum_k W[h,j,k] v2[h,k]
+ *                           (w AT [heads, kin, kout]; v1, v2 as obst_rowscale_colsum leaves them; dgamma / dbeta fp32
+ *                           [heads, kin], either may be NULL) -- together with epilogue 8's row dots (aux1 = W,
+ *                           aux2 = dgamma) this is sum_t dn xhat and sum_t dn without dn ever being stored */
+int obst_norm_bwd_coeffs(const float* partials, const float* stats, float* coeffs, int64_t rows, int32_t heads,
+                         int32_t nparts, int32_t width, void* stream);
+int obst_norm_affine_grad(const void* w, const float* v1, const float* v2, float* dgamma, float* dbeta, int32_t heads,
+                          int32_t kin, int32_t kout, void* stream);
 
 /* ---- activations, src/model/activation.py:158-169,201-211 ---------------------------------------
  * kind: 0 relu | 1 OBST gelu 0.5x(1+tanh(0.044715x^3+sqrt(2/pi)x)) | 2.. the other entries of ACTIVATIONS

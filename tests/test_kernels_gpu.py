@@ -497,3 +497,80 @@ def test_token_mix_at_the_longest_context_of_the_reference_configs(nat):
              KO=Bn, GLO=H, d_ld=S, d_glo=S * S, tri=3, accumulate=True)
     ref = torch.tril(torch.einsum("bshk,bthk->hst", out.float(), x.float()))
     assert max_rel(dm, ref) < 1e-4
+
+
+# ---------------------------------------------------------------------------------------------------
+# The group norm between W_mid and W_out folded into the GEMMs around it, forward AND backward
+# (obst_gemm epilogues 5..11 + the small kernels of csrc/fused_norm.cu), against float64 autograd of
+#   h = relu(h1 @ W_mid);  n = group_norm(h) * gamma + beta;  y = R +/- n @ W_out (per head)
+# (src/model/basic.py:47-57,122-126; src/model/normalization.py:22-34).
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("T,G,Kc,Np,sign", [(512, 8, 1024, 512, -1.0), (384, 4, 512, 256, 1.0), (300, 2, 256, 256, -1.0)])
+def test_folded_group_norm_forward_and_backward_chain(nat, T, G, Kc, Np, sign):
+    bf = torch.bfloat16
+    K1 = 256
+    h1 = randn(T, K1, seed=1)
+    w_mid = randn(K1, G * Kc, scale=K1 ** -0.5, seed=2)
+    gamma = (1.0 + 0.3 * randn(G, Kc, dtype=torch.float32, seed=3)).to(bf)
+    beta = (0.2 * randn(G, Kc, dtype=torch.float32, seed=4)).to(bf)
+    w_out = randn(G, Kc, Np, scale=Kc ** -0.5, seed=5)
+    res = randn(T, G, Np, seed=6)
+    dy = randn(T, G, Np, seed=7)
+    # ---- device chain -------------------------------------------------------------------------------
+    part = torch.empty((T, G * Kc // 128, 2), dtype=torch.float32, device=DEV)
+    h = torch.empty((T, G * Kc), dtype=bf, device=DEV)
+    nat.gemm(nat.operand(h1, K1, 1), nat.operand(w_mid, 1, G * Kc), h, T, G * Kc, K1, d_ld=G * Kc, epi=7, backend=2,
+             aux=(part,))
+    stats = torch.empty((T * G, 2), dtype=torch.float32, device=DEV)
+    nat.norm_stats_finalize(part, stats, T, G, Kc // 128, Kc)
+    wg_t = torch.empty((G, Np, Kc), dtype=bf, device=DEV)
+    cvec = torch.empty((G, Np), dtype=torch.float32, device=DEV)
+    dvec = torch.empty((G, Np), dtype=torch.float32, device=DEV)
+    gamma_f = torch.empty((G, Kc), dtype=torch.float32, device=DEV)
+    wg = torch.empty((G, Kc, Np), dtype=bf, device=DEV)
+    nat.fold_norm_weight(nat.fold_items([(w_out, gamma, beta, wg_t, cvec, dvec, gamma_f, wg)]), 1, G, Kc, Np)
+    assert torch.equal(wg, wg_t.transpose(1, 2))
+    y_plain = torch.empty((T, G, Np), dtype=bf, device=DEV)
+    nat.gemm(nat.operand(h, G * Kc, 1, s_glo=Kc), nat.operand(wg_t, Kc, 1, s_glo=Kc * Np), y_plain, T, Np, Kc, GLO=G,
+             d_ld=G * Np, d_glo=Np, R=res, epi=5 if sign > 0 else 6, backend=2, aux=(stats, cvec, dvec))
+    y = torch.empty((T, G, Np), dtype=bf, device=DEV)
+    nparts = 2 * ((Np + 255) // 256)
+    dots = torch.full((T, G, nparts, 2), float("nan"), dtype=torch.float32, device=DEV)
+    nat.gemm(nat.operand(h, G * Kc, 1, s_glo=Kc), nat.operand(wg_t, Kc, 1, s_glo=Kc * Np), y, T, Np, Kc, GLO=G,
+             d_ld=G * Np, d_glo=Np, R=res, epi=9 if sign > 0 else 10, backend=2, aux=(stats, cvec, dvec, dy, dots))
+    assert torch.equal(y, y_plain)  # the dot products ride along: the output itself is that of epilogue 5 / 6
+    dyr = torch.empty_like(dy)
+    v = torch.zeros((2, G, Np), dtype=torch.float32, device=DEV)
+    nat.rowscale_colsum(dy, stats, dyr, v[0], v[1], T, G, Np)
+    dw = torch.zeros((G, Kc, Np), dtype=torch.float32, device=DEV)
+    dgamma = torch.zeros((G, Kc), dtype=torch.float32, device=DEV)
+    dbeta = torch.zeros((G, Kc), dtype=torch.float32, device=DEV)
+    nat.gemm(nat.operand(h, 1, G * Kc, s_glo=Kc), nat.operand(dyr, 1, G * Np, s_glo=Np), dw, Kc, Np, T, GLO=G,
+             d_ld=Np, d_glo=Kc * Np, accumulate=True, epi=8, backend=2, aux=(gamma_f, w_out, dgamma))
+    nat.norm_affine_grad(w_out, v[0], v[1], dgamma, dbeta, G, Kc, Np)
+    nat.norm_wgrad_rank1(dw, gamma, beta, v[0], v[1], G, Kc, Np)
+    coeffs = torch.empty((T, G, 4), dtype=torch.float32, device=DEV)
+    nat.norm_bwd_coeffs(dots, stats, coeffs, T, G, nparts, Kc)
+    dh = torch.empty_like(h)
+    nat.gemm(nat.operand(dy, G * Np, 1, s_glo=Np), nat.operand(wg, Np, 1, s_glo=Kc * Np), dh, T, Kc, Np, GLO=G,
+             d_ld=G * Kc, d_glo=Kc, R=h, epi=11, backend=2, aux=(coeffs,))
+    torch.cuda.synchronize()
+    assert torch.isfinite(dots).all()  # every partial slot was written
+    # ---- float64 autograd on the same (bf16-valued) inputs; the ReLU output is taken as stored -----------------
+    pre = (h1.double() @ w_mid.double()).requires_grad_(True)
+    g64 = gamma.double().requires_grad_(True)
+    b64 = beta.double().requires_grad_(True)
+    w64 = w_out.double().requires_grad_(True)
+    hr = torch.relu(pre).view(T, G, Kc)
+    mu = hr.mean(-1, keepdim=True)
+    var = hr.var(-1, unbiased=False, keepdim=True)
+    n = (hr - mu) * torch.rsqrt(var + 1e-5) * g64 + b64
+    f = torch.einsum("tgk,gkn->tgn", n, w64)
+    y_ref = res.double() + sign * f
+    f.backward(dy.double())
+    assert rel_err(h.view(T, G, Kc), hr.detach()) < 1e-2
+    assert rel_err(y, y_ref.detach()) < 2e-2                      # bf16 tier (north_star): 2e-2
+    assert rel_err(dh.view(T, G * Kc), pre.grad) < 2e-2
+    assert rel_err(dw, w64.grad) < 2e-2
+    assert rel_err(dgamma, g64.grad) < 2e-2
+    assert rel_err(dbeta, b64.grad) < 2e-2

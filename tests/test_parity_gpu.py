@@ -202,7 +202,24 @@ def test_sub_block_parity_at_the_shapes_of_the_reference_configs(cuda, c, name, 
     _sub_block_parity(0, c, "bfloat16", 2e-2, batch=2, seq=seq, fph=fph)
 
 
-def _sub_block_parity(backend, c, dtype, tol, batch, seq, fph):
+@pytest.mark.parametrize("name,seq,fph", [("32big_mixer", 512, 512), ("32ctx_mixer", 2048, 256)])
+def test_sub_block_parity_inside_the_reversible_backward(cuda, name, seq, fph):
+    """block_config[0] as the reversible backward runs it: the residual rides on W_out's epilogue (x1 = y1 - f) and
+    the gradient of the block's output is known while the block is recomputed, so the group norm between W_mid and
+    W_out is folded into the GEMMs in BOTH directions (obst_gemm epilogues 7, 10, 8 + row dots, 11): neither the
+    normalised tensor nor dn = dy @ W_out^T is ever written.  Same float64 / twin checks as the plain sub-block."""
+    from obst import native
+    calls = []
+    orig = native.norm_bwd_coeffs
+    native.norm_bwd_coeffs = lambda *a, **k: (calls.append(1), orig(*a, **k))[1]
+    try:
+        _sub_block_parity(0, 0, "bfloat16", 2e-2, batch=2, seq=seq, fph=fph, reversible=True)
+    finally:
+        native.norm_bwd_coeffs = orig
+    assert calls, "the folded norm backward did not run"
+
+
+def _sub_block_parity(backend, c, dtype, tol, batch, seq, fph, reversible=False):
     from obst import utils_core
     from obst.model.backend import run_tape
     from obst.model.frontend import block_part_fn
@@ -231,7 +248,16 @@ def _sub_block_parity(backend, c, dtype, tol, batch, seq, fph):
             utils_core.random_name("0_")  # block scopes are "<depth>_<config>": make this one config 1
         return block_part_fn(params, params.block_config[c], Tensor(x, dims), "0")
 
+    if reversible:  # what obst.model.revnet's backward sets up around the recompute: x1 <- y1 - f(x2), dy known
+        y1 = torch.zeros((B, S, H, K), dtype=tdt, device="cuda")  # x1 = -f: f is read back as exactly as it is stored
+        x1 = y1.clone()
+        params.residual = (x1, -1.0, x1)
+        params.upstream_grad = dy
     f = scoped("gpt", lambda: scoped("body", body))
+    if reversible:
+        assert params.residual is None, "the last GEMM did not take the residual"
+        params.upstream_grad = None
+        f = Tensor((y1.float() - x1.float()).to(tdt), f.dims)  # f as the stream saw it (rounded where y1 - f is)
     tape, params.tape = params.tape, None
     dx = run_tape(tape, dy)
     blk = orc.BLOCKS[c]
