@@ -49,16 +49,36 @@ def _input(params: ModelParameter, txt_src: Tensor) -> Tensor:
     return txt
 
 
+def _initial_position_embedding(params: ModelParameter, src: Tensor) -> Tensor:
+    """src += embed(position_embedding, [dim] + feature_dims) for every position dim after the batch
+    (src/model/__init__.py:97-99); text has one, the sequence."""
+    position_dims = [d for d in src.dims if d not in params.feature_dims][1:]
+    if position_dims != [src.dims[1]] or src.dims[2:] != params.feature_dims:
+        raise NotImplementedError(f"initial position embedding over {position_dims} of {src.dims}")
+    pos = embed(BlockArgs(params, src, [''])(params.position_embedding), position_dims + params.feature_dims)
+    out = torch.empty_like(src.data)
+    native.bias_add(src.data, pos.value, out)
+    if params.tape is not None:
+        def bwd(dy, mask, acc):
+            grad = pos.ensure_grad()  # None for the sinusoidal constant
+            if grad is not None:
+                native.colsum_accumulate(dy, grad)
+            return dy
+
+        params.tape.append(TapeEntry(bwd))
+    return Tensor(out, src.dims)
+
+
 def _body(params: ModelParameter, src: Tensor) -> Tensor:
     """src/model/__init__.py:94-130"""
-    if params.use_initial_position_embedding:
-        raise NotImplementedError("use_initial_position_embedding is not on the hot path (all configs: false)")
     # [batch, sequence, language_token_patch(=1), heads, features] -> [batch, sequence, heads, features]
     if params.token_patch_dim in src.dims:
         if params.token_patch_dim.size != 1:
             raise NotImplementedError("token_patch_size > 1 is not on the hot path")
         dims = [d for d in src.dims if d != params.token_patch_dim]
         src = Tensor(src.data.view([d.size for d in dims]), dims)
+    if params.use_initial_position_embedding:  # src/model/__init__.py:97-99
+        src = _initial_position_embedding(params, src)
     strategy = params.memory_reduction_strategy
     if strategy == "revnet":
         return reversible_body(params, src)

@@ -146,7 +146,7 @@ def test_dropout_keeps_the_stated_fraction_and_replays_its_mask(cuda):
     assert torch.equal(out.data, x)
 
 
-def _attention_reference(layer, x, variables, params, dy):
+def _attention_reference(layer, x, variables, params, dy, pos_builder=None):
     """float64 torch statement of src/model/spatial.py:42-81 for the flag set in `layer`; returns (out, dx, grads)."""
     flags = layer.split('-')[1:]
     B, S, H, K = x.shape
@@ -175,7 +175,7 @@ def _attention_reference(layer, x, variables, params, dy):
         if "embedded" in flags or "context" in flags:
             key = torch.einsum("bsi,ihk->bshk", base, nxt())
         if "embedded" in flags or "positional" in flags:
-            key = key + nxt()[None]
+            key = key + (pos_builder(nxt) if pos_builder is not None else nxt())[None]
         qry = torch.einsum("bsi,ihk->bshk", base, nxt()) * S ** -0.5
         if key.dim() == 3:
             key = key[None].expand(B, -1, -1, -1)
@@ -230,3 +230,93 @@ def test_dot_product_attention_variants(cuda, layer):
     assert rel(dx, dx_ref) < 1e-5
     for v, g in grads:
         assert rel(v.grad, g.reshape(v.grad.shape)) < 1e-5, v.name
+
+
+def _sinusoid(params, x, flags):
+    """The sinusoidal relative embedding (src/model/embedding.py:128-172) as the product builds it, in float64.  It is
+    taken from the product: the schedule is exp(feature index), whose sine is rounding noise in fp32 beyond the first
+    few features -- in the reference as here -- so a float64 restatement would not be the same constant."""
+    from obst.dataclass import BlockArgs
+    from obst.model.embedding import relative_embedding
+    from obst.utils_mtf import Tensor as T_
+    dims = [params.batch_dim._replace(size=x.shape[0]), params.sequence_dim] + params.feature_dims
+    return relative_embedding(BlockArgs(params, T_(x, dims), flags), [params.sequence_dim] + params.feature_dims).double()
+
+
+@pytest.mark.parametrize("kind", ["axial", "axial-3", "relative-learned"])
+def test_composed_position_embeddings_in_attention(cuda, kind):
+    """`axial` (the outer product of per-factor embeddings, src/model/embedding.py:192-212) and `relative-learned` (the
+    sinusoid times a learned feature scale, :214-217) as the position keys of dot-product attention: output, input
+    gradient and the gradients of the factor / scale variables against float64 autograd, fp32 at 1e-5."""
+    layer = f"attention-dot_product-positional-{kind}-input_as_value"
+    S, fph = 24, 8 if "relative" in kind else 16
+    params, x, out, dy, dx, variables = run_layers([layer], seq=S, fph=fph, batch=2)
+    H = params.heads
+
+    def pos_builder(nxt):
+        if kind == "relative-learned":
+            return _sinusoid(params, x, layer.split('-')[1:]) * nxt()[None]
+        splits = 3 if kind.endswith("3") else 2
+        parts = [nxt() for _ in range(splits)]
+        sizes = [p.shape[0] for p in parts]
+        assert int(np.prod(sizes)) == S, sizes
+        full = None
+        for i, p in enumerate(parts):
+            v = p.view([sizes[j] if j == i else 1 for j in range(splits)] + [H, fph])
+            full = v if full is None else full * v
+        return full.reshape(S, H, fph)
+
+    ref, dx_ref, grads = _attention_reference(layer, x, list(variables), params, dy, pos_builder)
+    assert rel(out.data, ref) < 1e-5
+    assert rel(dx, dx_ref) < 1e-5
+    assert len(grads) == len(variables)
+    for v, g in grads:
+        assert rel(v.grad, g.reshape(v.grad.shape)) < 1e-5, v.name
+
+
+@pytest.mark.parametrize("kind", ["absolute", "axial", "relative", "relative-learned"])
+def test_initial_position_embedding(cuda, kind):
+    """use_initial_position_embedding (src/model/__init__.py:97-99): src + embed(position_embedding, [sequence] +
+    feature_dims) in front of the body, with the gradient reaching the embedding's variables."""
+    from obst import utils_core
+    from obst.dataclass import ModelParameter, gpt_mode
+    from obst.model import _initial_position_embedding
+    from obst.model.backend import run_tape
+    from obst.utils_core import scoped
+    from obst.utils_mtf import Tensor
+    S, fph, B = 24, 8, 3
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=B, sequence_length=S, features_per_head=fph, position_embedding=kind,
+               use_initial_position_embedding=True)
+    params = ModelParameter(gpt_mode(cfg))
+    H = params.heads
+    rng = np.random.default_rng(3)
+    x = torch.from_numpy(rng.standard_normal((B, S, H, fph)).astype(np.float32)).cuda()
+    dy = torch.from_numpy(rng.standard_normal((B, S, H, fph)).astype(np.float32)).cuda()
+    dims = [params.batch_dim._replace(size=B), params.sequence_dim] + params.feature_dims
+    utils_core.NAME_INDICES.clear()
+    params.cached_parameters.clear()
+    params.tape = []
+    out = scoped("gpt", lambda: _initial_position_embedding(params, Tensor(x, dims)))
+    tape, params.tape = params.tape, None
+    dx = run_tape(tape, dy)
+    variables = list(params.variable_cache.values())
+    leaves = [v.data.double().clone().requires_grad_(True) for v in variables]
+    if kind == "absolute":
+        pos = leaves[0]
+    elif kind == "relative":
+        pos = _sinusoid(params, x, kind.split('-'))
+    elif kind == "relative-learned":
+        pos = _sinusoid(params, x, kind.split('-')) * leaves[0][None]
+    else:
+        a, b = leaves
+        pos = (a[:, None] * b[None]).reshape(S, H, fph)
+    ref = x.double() + pos[None]
+    assert rel(out.data, ref.detach()) < 1e-6
+    assert torch.equal(dx, dy)
+    if leaves:
+        ref.backward(dy.double())
+        for v, leaf in zip(variables, leaves):
+            assert rel(v.grad, leaf.grad.reshape(v.grad.shape)) < 1e-5, v.name
+    else:
+        assert not variables
