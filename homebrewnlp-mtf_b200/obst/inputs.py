@@ -37,12 +37,18 @@ def _crc_table():
     return _CRC_TABLE
 
 
-def crc32c(data: bytes) -> int:
+def crc32c_py(data: bytes) -> int:
+    """Bytewise table form: the statement the native routine (obst_crc32c) is tested against."""
     table = _crc_table()
     c = 0xFFFFFFFF
     for b in data:
         c = table[(c ^ b) & 0xFF] ^ (c >> 8)
     return c ^ 0xFFFFFFFF
+
+
+def crc32c(data: bytes) -> int:
+    from . import native
+    return native.crc32c(data)
 
 
 def masked_crc32c(data: bytes) -> int:

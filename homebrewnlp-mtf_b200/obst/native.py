@@ -66,6 +66,8 @@ class OptStageArgs(ctypes.Structure):  # obst_opt_stage_args
 # name -> (restype, argtypes); must list every symbol include/obst_b200.h declares (tests check this)
 SIGNATURES: typing.Dict[str, typing.Tuple[typing.Any, typing.List[typing.Any]]] = {
     "obst_version": (c_int, []),
+    "obst_crc32c": (ctypes.c_uint32, [c_void_p, c_i64, ctypes.c_uint32]),
+    "obst_crc32c_portable": (ctypes.c_uint32, [c_void_p, c_i64, ctypes.c_uint32]),
     "obst_last_error": (ctypes.c_char_p, []),
     "obst_launch_count": (c_i64, []),
     "obst_launch_count_reset": (None, []),
@@ -147,6 +149,20 @@ def load() -> ctypes.CDLL:
         fn.argtypes = args
     _lib = lib
     return lib
+
+
+def crc32c(data, crc: int = 0) -> int:
+    """CRC-32C of a bytes-like object or a C-contiguous numpy array / CPU tensor (host memory), continuing from `crc`."""
+    if isinstance(data, torch.Tensor):
+        if data.is_cuda or not data.is_contiguous():
+            raise NativeError("crc32c: a contiguous CPU tensor is expected")
+        return load().obst_crc32c(data.data_ptr(), data.numel() * data.element_size(), crc)
+    if hasattr(data, "ctypes"):  # numpy
+        if not data.flags["C_CONTIGUOUS"]:
+            raise NativeError("crc32c: a C-contiguous array is expected")
+        return load().obst_crc32c(data.ctypes.data, data.nbytes, crc)
+    data = bytes(data) if not isinstance(data, bytes) else data
+    return load().obst_crc32c(data, len(data), crc)
 
 
 def check(rc: int, what: str = ""):

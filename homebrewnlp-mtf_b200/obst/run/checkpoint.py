@@ -4,14 +4,15 @@ The reference relies on TF's Saver over the MTF master variables: every variable
 (`.../get_variableN`, src/utils_mtf.py:271-280), every optimizer slot under
 `<variable>/<optimizer string with ':' -> '_'>/<slot>` (src/optimizer/backend.py:23-25), in the MASTER dtype --
 `storage_dtype` for weights (bfloat16 in the 32*_mixer configs, so a restart there resumes from bf16-rounded
-weights) and the optimizer's master dtype for slots -- next to the global step.  The TensorBundle file format itself
-needs TensorFlow; this bridge keeps the names, dtypes and contents in a single .npz so that a run can be stopped
-and resumed (and so that a converter that has TensorFlow only has to rename nothing).
+weights) and the optimizer's master dtype for slots -- next to the global step.  Two containers hold the same names,
+dtypes and contents: the TensorBundle pair + `checkpoint` state file that tf.train.Saver writes (tf_checkpoint.py,
+restated without TensorFlow; `fmt="tf"`), and a single .npz (`fmt="npz"`).
 
     save_checkpoint(params, path)            after any number of steps
     load_checkpoint(params, path)            on a fresh ModelParameter, BEFORE the first step
 
 `exact=True` stores the fp32 slices instead of the storage dtype: resuming is then bit-identical to not stopping."""
+import os
 import typing
 import warnings
 
@@ -36,21 +37,66 @@ def _unpack(name: str, arr: np.ndarray) -> typing.Tuple[str, torch.Tensor]:
     return name, torch.from_numpy(np.array(arr))
 
 
-def save_checkpoint(params: ModelParameter, path: str, exact: bool = False):
+def _collect(params: ModelParameter, exact: bool) -> typing.Dict[str, torch.Tensor]:
+    """name -> tensor in the dtype it is stored in (reference names, master dtypes; fp32 slices when `exact`)."""
     if not params.variable_cache:
         raise RuntimeError("nothing to save: the model has not been built yet")
-    out = {"global_step": np.int64(params.global_step), "manual_global_step": np.int64(params.manual_global_step)}
+    out = {"global_step": torch.tensor(params.global_step, dtype=torch.int64),
+           "manual_global_step": torch.tensor(params.manual_global_step, dtype=torch.int64)}
     wdt = torch.float32 if exact else params.variable_dtype.master_dtype
     for name, var in params.variable_cache.items():
-        tag, arr = _pack(var.data, wdt)
-        out[name + tag] = arr
+        out[name] = var.data.detach().to(wdt)
     state = getattr(params, "optimizer_state", None)
     if state is not None:
-        sdt = torch.float32 if exact else params.optimizer_dtype.master_dtype
+        sdt = params.optimizer_dtype.master_dtype
         for name, slot in state.slots.items():
-            tag, arr = _pack(slot, slot.dtype if exact else sdt)
-            out[name + tag] = arr
+            out[name] = slot.detach().to(slot.dtype if exact else sdt)
+    return out
+
+
+def save_checkpoint(params: ModelParameter, path: str, exact: bool = False, fmt: typing.Optional[str] = None) -> str:
+    """fmt "npz": one .npz at `path`.  fmt "tf": `path` is the model directory; writes the TensorBundle pair
+    `model.ckpt-<global_step>.index` / `.data-00000-of-00001` and the `checkpoint` state file, as tf.train.Saver does
+    for the reference (src/run/run.py:158-175) -- see tf_checkpoint.py.  Default: "tf" for a directory (or a path
+    without extension that is not an .npz), else "npz".  Returns the checkpoint's path / prefix."""
+    tensors = _collect(params, exact)
+    if fmt is None:
+        fmt = "npz" if path.endswith(".npz") else ("tf" if os.path.isdir(path) else "npz")
+    if fmt == "tf":
+        from . import tf_checkpoint
+        os.makedirs(path, exist_ok=True)
+        name = f"model.ckpt-{params.global_step}"
+        tf_checkpoint.write_bundle(os.path.join(path, name), tensors)
+        older = []
+        state_file = os.path.join(path, "checkpoint")
+        if os.path.exists(state_file):
+            with open(state_file) as f:
+                older = [ln.split(":", 1)[1].strip().strip('"') for ln in f if ln.startswith("all_model_checkpoint_paths:")]
+        tf_checkpoint.write_checkpoint_state(path, name, [o for o in older if o != name])
+        return os.path.join(path, name)
+    if fmt != "npz":
+        raise ValueError(f"unknown checkpoint format '{fmt}'")
+    out = {}
+    for name, t in tensors.items():
+        tag, arr = _pack(t, t.dtype)
+        out[name + tag] = arr
     np.savez(path, **out)
+    return path
+
+
+def _read_entries(path: str) -> typing.Dict[str, torch.Tensor]:
+    """An .npz, a TensorBundle prefix, or a model directory with a `checkpoint` state file."""
+    from . import tf_checkpoint
+    if os.path.isdir(path):
+        latest = tf_checkpoint.latest_checkpoint(path)
+        if latest is None:
+            raise FileNotFoundError(f"{path} holds no `checkpoint` state file")
+        path = latest
+    if os.path.exists(path + ".index"):
+        entries = tf_checkpoint.read_bundle(path)
+        return {k: (v.float() if v.dtype == torch.bfloat16 else v) for k, v in entries.items()}
+    with np.load(path if path.endswith(".npz") else path + ".npz") as f:
+        return dict(_unpack(k, f[k]) for k in f.files)
 
 
 def load_checkpoint(params: ModelParameter, path: str):
@@ -59,8 +105,7 @@ def load_checkpoint(params: ModelParameter, path: str):
     file lacks raises KeyError at that point (a file saved before the first update holds no slots at all: those
     start from zero, as in the reference); entries nobody asked for are reported by `finish_restore`, which the
     training step calls once everything exists, and which releases the host copy of the file."""
-    with np.load(path if path.endswith(".npz") else path + ".npz") as f:
-        entries = dict(_unpack(k, f[k]) for k in f.files)
+    entries = _read_entries(path)
     params.global_step = int(entries.pop("global_step"))
     params.manual_global_step = int(entries.pop("manual_global_step"))
     params.restore_entries = entries

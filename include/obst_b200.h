@@ -53,6 +53,14 @@ enum {
 };
 int64_t obst_path_count(int32_t which);
 
+/* ---- host-side checksum --------------------------------------------------------------------------
+ * CRC-32C (Castagnoli) of HOST memory, continuing from `crc` (0 to start): the checksum of TFRecord frames
+ * (tf.data.TFRecordDataset behind src/inputs.py:231-268) and of TensorBundle checkpoint tensors and table blocks
+ * (tf.train.Saver, src/run/run.py:158-175).  SSE4.2 crc32 instruction where the host has it, slicing-by-8 tables
+ * otherwise (obst_crc32c_portable: always the tables).  No device work, no stream. */
+uint32_t obst_crc32c(const void* host_data, int64_t nbytes, uint32_t crc);
+uint32_t obst_crc32c_portable(const void* host_data, int64_t nbytes, uint32_t crc);
+
 /* ---- GEMM family -------------------------------------------------------------------------------
  * One descriptor covers every contraction on the path:
  *   dense  W_in / W_mid (+ReLU)            src/model/basic.py:33-34,47-57; src/model/backend.py:108-110

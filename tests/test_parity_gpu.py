@@ -4,6 +4,7 @@ Tolerances are north_star's: fp32 <= 1e-5 relative on per-sub-block activations,
 loss; bf16 <= 2e-2.  Optimizer state layout / step counters are compared exactly where exactness is defined
 (lr == 0 leaves every weight bit-unchanged)."""
 import copy
+import os
 
 import numpy as np
 import pytest
@@ -670,6 +671,19 @@ def test_checkpoint_resume(cuda, tmp_path, chain):
             assert torch.equal(a.value_t, b.value_t), na
     for k, v in stopped.optimizer_state.slots.items():
         assert torch.equal(v, probe.optimizer_state.slots[k]), k
+    # the same state through the TensorBundle bridge (tf.train.Saver's on-disk format, obst/run/tf_checkpoint.py)
+    tfdir = str(tmp_path / "tf")
+    prefix = save_checkpoint(stopped, tfdir, exact=True, fmt="tf")
+    assert prefix.endswith("model.ckpt-1502") and os.path.exists(prefix + ".index")
+    assert os.path.exists(prefix + ".data-00000-of-00001") and os.path.exists(os.path.join(tfdir, "checkpoint"))
+    probe2 = fresh()
+    run_product_step(probe2, tok_x, tok_y)
+    load_checkpoint(probe2, tfdir)  # the directory: resolved through the `checkpoint` state file
+    assert probe2.global_step == 1502 and probe2.manual_global_step == 2
+    for (na, a), (nb, b) in zip(stopped.variable_cache.items(), probe2.variable_cache.items()):
+        assert na == nb and torch.equal(a.data, b.data) and torch.equal(a.value, b.value), na
+    for k, v in stopped.optimizer_state.slots.items():
+        assert torch.equal(v, probe2.optimizer_state.slots[k]), k
     # the reference-dtype file: names are the reference's, weights in storage_dtype
     save_checkpoint(stopped, str(tmp_path / "ref.npz"))
     with np.load(str(tmp_path / "ref.npz")) as f:
