@@ -207,3 +207,42 @@ def test_analysis_matches_oracle_counts():
         sh = orc.Shapes(mixer_config(name))
         assert count_params(p) == orc.count_params(sh)
         assert flops_per_token_fwd(p) == orc.flops_per_token_fwd(sh)
+
+
+def test_update_work_list_covers_every_row_once():
+    """The optimizer update's own work list (graded in size towards the end so that the resident blocks run dry
+    together, obst/optimizer/__init__.py:_drain_list): whatever the grading, every row of every tensor is covered
+    exactly once, in the order of the list it was cut from, with at least 8 rows (one per warp) per item."""
+    import os
+    from obst.optimizer import _drain_list
+    cols_of = [512, 1024, 512, 8, 256]
+    rows_of = [4096, 4096, 8192, 8, 333]
+    items = []
+    for ti, rows in enumerate(rows_of):
+        rpi = max(1, 131072 // min(cols_of[ti], 512))
+        items += [(ti, r0, min(rpi, rows - r0)) for r0 in range(0, rows, rpi)]
+    old = os.environ.get("OBST_OPT_DRAIN")
+    try:
+        for setting in ("0:1:1", "0.05:3:6", "0.3:2:8", "1.0:4:16"):
+            os.environ["OBST_OPT_DRAIN"] = setting
+            out = _drain_list(items, cols_of)
+            covered = {ti: [] for ti in range(len(rows_of))}
+            for ti, r0, rows in out:
+                assert rows >= 1
+                covered[ti].append((r0, rows))
+            for ti, rows in enumerate(rows_of):
+                pos = 0
+                for r0, n in covered[ti]:
+                    assert r0 == pos, (setting, ti, r0, pos)
+                    pos += n
+                assert pos == rows
+            assert [t for t, _, _ in out] == sorted(t for t, _, _ in out)   # order of the tensors is kept
+            if setting == "0:1:1":
+                assert out == items
+            else:
+                assert len(out) > len(items)
+    finally:
+        if old is None:
+            os.environ.pop("OBST_OPT_DRAIN", None)
+        else:
+            os.environ["OBST_OPT_DRAIN"] = old
