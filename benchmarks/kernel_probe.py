@@ -101,6 +101,19 @@ def main():
         dm = torch.zeros(H, S, S, device=DEV)
         ms = timeit(lambda: nat.gemm(nat.operand(y, F, 1, s_ko=S * F, s_glo=K), nat.operand(x, F, 1, s_ko=S * F, s_glo=K), dm, S, S, K, KO=Bn, GLO=H, d_ld=S, d_glo=S * S, tri=3, accumulate=True, backend=be))
         rep(f"mix dM [{tag}] (causal flops)", ms, 2 * T * F * (S + 1) / 2)
+        # layout experiment: the same products with the operands head-major, [batch, heads, seq, features]
+        # (every (batch, head) slab contiguous) instead of the stream's [batch, seq, heads, features]
+        HM = dict(s_glo=S * K, s_ghi=H * S * K)
+        ms = timeit(lambda: nat.gemm(nat.operand(mix, S, 1, s_glo=S * S), nat.operand(x, 1, K, **HM), out, S, K, S, GLO=H, GHI=Bn, d_ld=K, d_glo=S * K, d_ghi=H * S * K, tri=1, backend=be))
+        rep(f"mix fwd, head-major in+out [{tag}]", ms, 2 * T * F * (S + 1) / 2)
+        ms = timeit(lambda: nat.gemm(nat.operand(mix, S, 1, s_glo=S * S), nat.operand(x, 1, K, **HM), out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, tri=1, backend=be))
+        rep(f"mix fwd, head-major in [{tag}]", ms, 2 * T * F * (S + 1) / 2)
+        ms = timeit(lambda: nat.gemm(nat.operand(mix, S, 1, s_glo=S * S), nat.operand(x, 1, F, s_glo=K, s_ghi=S * F), out, S, K, S, GLO=H, GHI=Bn, d_ld=K, d_glo=S * K, d_ghi=H * S * K, tri=1, backend=be))
+        rep(f"mix fwd, head-major out [{tag}]", ms, 2 * T * F * (S + 1) / 2)
+        ms = timeit(lambda: nat.gemm(nat.operand(mix, 1, S, s_glo=S * S), nat.operand(x, 1, K, **HM), out, S, K, S, GLO=H, GHI=Bn, d_ld=K, d_glo=S * K, d_ghi=H * S * K, tri=2, backend=be))
+        rep(f"mix dx, head-major in+out [{tag}]", ms, 2 * T * F * (S + 1) / 2)
+        ms = timeit(lambda: nat.gemm(nat.operand(y, K, 1, s_ko=H * S * K, s_glo=S * K), nat.operand(x, K, 1, s_ko=H * S * K, s_glo=S * K), dm, S, S, K, KO=Bn, GLO=H, d_ld=S, d_glo=S * S, tri=3, accumulate=True, backend=be))
+        rep(f"mix dM, head-major operands [{tag}]", ms, 2 * T * F * (S + 1) / 2)
     if only == "gemm":
         return
     # cuBLAS yardstick on this box
