@@ -15,7 +15,12 @@
 // forward, dgrad and wgrad all read the tensors where they lie: no activation is ever transposed.
 // Triangular modes skip whole k-blocks / output tiles of the causal token-mixing matrices.
 // Fused epilogues: ReLU, residual +/-, ReLU-backward mask, and the group norm around the bottleneck's W_mid / W_out
-// pair (5-8: row statistics out, norm applied to the accumulator, row-scaled weight gradient) -- include/obst_b200.h.
+// pair (5-8: row statistics out, norm applied to the accumulator, row-scaled weight gradient; 9-11: the same norm's
+// backward -- row dots of the accumulator with the upstream gradient, norm + ReLU backward on the dgrad accumulator --
+// in two instantiations of their own, gemm_tc_kernel<2, 1> / <2, 2>) -- include/obst_b200.h.
+// Work items (tiles x split-K) are dealt round-robin to the CTA pairs: the split count is chosen for full rounds, and
+// triangular outputs number only their live tiles.  The set-up precedes a griddepcontrol.wait (programmatic dependent
+// launch): it overlaps the previous kernel's tail.
 #include <cuda.h>
 #include <stdlib.h>
 

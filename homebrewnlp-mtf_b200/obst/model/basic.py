@@ -191,7 +191,12 @@ def _mid_norm_out_folded(args: BlockArgs) -> Tensor:
     The statistics come out of W_mid's epilogue (obst_gemm epilogue 7), W_out's epilogue applies the norm to its
     accumulator together with the reversible add (5 / 6), the weight gradient's rows are scaled by gamma in its
     epilogue (8).  Per token and depth this saves the norm kernel's read of h and write of n, and W_out's read of n
-    is replaced by the read of h: 32 KiB less HBM traffic per pass at 32big_mixer's shape."""
+    is replaced by the read of h: 32 KiB less HBM traffic per pass at 32big_mixer's shape.
+
+    Inside the reversible backward the norm's own backward is folded as well: with
+    s1 = dy . (gamma^T W) and s2 = dy . (h @ (gamma.W)) -- row dots with the accumulator of the recomputed W_out GEMM,
+    epilogues 9 / 10 -- the dgrad epilogue (11) writes dh = [h > 0] (r gamma dn - r m1 - r xhat m2) directly, and
+    dgamma / dbeta come out of the weight gradient's accumulator and two column sums; dn is never written."""
     import torch
 
     from .. import native
