@@ -1,0 +1,195 @@
+"""NumPy stand-in for the slice of TensorFlow the reference's Python touches (see ../README.md).  Tensors are NumPy
+arrays; float32 arithmetic stays float32 (NumPy >= 2 treats Python scalars as weak)."""
+import contextlib
+import types
+
+import numpy as np
+
+
+class DType:
+    def __init__(self, name, np_dtype, floating, bf16=False):
+        self.name = name
+        self.as_numpy_dtype = np_dtype
+        self.is_floating = floating
+        self.is_bf16 = bf16
+        self.size = 2 if bf16 else np.dtype(np_dtype).itemsize
+
+    def __repr__(self):
+        return f"tf.{self.name}"
+
+    @property
+    def is_integer(self):
+        return not self.is_floating and self.name != "bool"
+
+
+float32 = DType("float32", np.float32, True)
+float64 = DType("float64", np.float64, True)
+float16 = DType("float16", np.float16, True)
+bfloat16 = DType("bfloat16", np.float32, True, bf16=True)  # held as float32 values rounded to 8 significand bits
+int32 = DType("int32", np.int32, False)
+int64 = DType("int64", np.int64, False)
+uint8 = DType("uint8", np.uint8, False)
+bool = DType("bool", np.bool_, False)  # noqa: A001
+dtypes = types.SimpleNamespace(DType=DType, float32=float32, bfloat16=bfloat16, int32=int32, int64=int64)
+
+
+class Tensor:  # annotations only: values are numpy arrays
+    pass
+
+
+class Variable:
+    pass
+
+
+class Operation:
+    pass
+
+
+def round_bf16(x):
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    bits = x.view(np.uint32)
+    rounded = ((bits + 0x7FFF + ((bits >> 16) & 1)) & 0xFFFF0000).astype(np.uint32)
+    out = rounded.view(np.float32).copy()
+    out[np.isnan(x)] = np.nan
+    return out.reshape(x.shape)
+
+
+def cast(x, dtype, name=None):
+    x = np.asarray(x)
+    if dtype.is_bf16:
+        return round_bf16(x.astype(np.float32))
+    return x.astype(dtype.as_numpy_dtype)
+
+
+def constant(value, dtype=None, shape=None, name=None):
+    dtype = dtype or float32
+    arr = cast(np.asarray(value), dtype)
+    if shape is not None:
+        arr = np.broadcast_to(arr, tuple(shape)).copy()
+    return arr
+
+
+def _f(fn):
+    return lambda x, *a, name=None, **k: fn(np.asarray(x), *a, **k)
+
+
+maximum = lambda a, b, name=None: np.maximum(a, b)  # noqa: E731
+minimum = lambda a, b, name=None: np.minimum(a, b)  # noqa: E731
+equal = lambda a, b, name=None: np.equal(a, b)  # noqa: E731
+greater = lambda a, b, name=None: np.greater(a, b)  # noqa: E731
+greater_equal = lambda a, b, name=None: np.greater_equal(a, b)  # noqa: E731
+less = lambda a, b, name=None: np.less(a, b)  # noqa: E731
+less_equal = lambda a, b, name=None: np.less_equal(a, b)  # noqa: E731
+identity = lambda x, name=None: np.asarray(x)  # noqa: E731
+stop_gradient = identity
+reshape = lambda x, shape, name=None: np.reshape(x, shape)  # noqa: E731
+transpose = lambda x, perm=None, name=None: np.transpose(x, perm)  # noqa: E731
+zeros = lambda shape, dtype=float32, name=None: np.zeros(shape, dtype.as_numpy_dtype)  # noqa: E731
+ones = lambda shape, dtype=float32, name=None: np.ones(shape, dtype.as_numpy_dtype)  # noqa: E731
+zeros_like = lambda x, name=None: np.zeros_like(x)  # noqa: E731
+reduce_sum = lambda x, axis=None, keepdims=False, name=None: np.sum(x, axis=axis, keepdims=keepdims)  # noqa: E731
+reduce_mean = lambda x, axis=None, keepdims=False, name=None: np.mean(x, axis=axis, keepdims=keepdims)  # noqa: E731
+reduce_max = lambda x, axis=None, keepdims=False, name=None: np.max(x, axis=axis, keepdims=keepdims)  # noqa: E731
+einsum = lambda eq, *xs, name=None: np.einsum(eq, *xs)  # noqa: E731
+gather = lambda params, indices, axis=0, name=None: np.take(params, indices, axis=axis)  # noqa: E731
+squeeze = lambda x, axis=None, name=None: np.squeeze(x, axis=tuple(axis) if isinstance(axis, (list, tuple)) else axis)  # noqa: E731
+expand_dims = lambda x, axis, name=None: np.expand_dims(x, axis)  # noqa: E731
+square = _f(np.square)
+sqrt = _f(np.sqrt)
+exp = _f(np.exp)
+sin = _f(np.sin)
+tanh = _f(np.tanh)
+sign = _f(np.sign)
+abs = _f(np.abs)  # noqa: A001
+rsqrt = lambda x, name=None: (1 / np.sqrt(np.asarray(x))).astype(np.asarray(x).dtype)  # noqa: E731
+sigmoid = lambda x, name=None: (1 / (1 + np.exp(-np.asarray(x)))).astype(np.asarray(x).dtype)  # noqa: E731
+softplus = lambda x, name=None: np.logaddexp(np.asarray(x), 0).astype(np.asarray(x).dtype)  # noqa: E731
+
+
+def range(start, limit=None, delta=1, dtype=None, name=None):  # noqa: A001
+    if limit is None:
+        start, limit = 0, start
+    out = np.arange(start, limit, delta)
+    return out.astype(dtype.as_numpy_dtype) if dtype is not None else out.astype(np.int32)
+
+
+def mod(x, y, name=None):
+    return np.mod(x, y)
+
+
+def group(ops, name=None):
+    return list(ops)
+
+
+@contextlib.contextmanager
+def control_dependencies(ops):
+    yield
+
+
+@contextlib.contextmanager
+def name_scope(name):
+    yield
+
+
+math = types.SimpleNamespace(softplus=softplus, tanh=tanh, square=square, sigmoid=sigmoid, abs=abs, exp=exp, sin=sin,
+                             sqrt=sqrt, rsqrt=rsqrt, log=_f(np.log), maximum=maximum, minimum=minimum)
+
+
+# ---- compat.v1: variable scopes (names only), initializers, the global step -----------------------------
+class _Scope:
+    def __init__(self):
+        self.stack = []
+
+    @property
+    def name(self):
+        return "/".join(self.stack)
+
+
+_SCOPE = _Scope()
+
+
+@contextlib.contextmanager
+def _variable_scope(name, *a, **k):
+    if isinstance(name, _Scope):  # re-entering a captured scope object: the stand-in has one scope stack
+        yield _SCOPE
+        return
+    _SCOPE.stack.append(name)
+    try:
+        yield _SCOPE
+    finally:
+        _SCOPE.stack.pop()
+
+
+class _ZerosInitializer:
+    def __call__(self, shape, dtype=None, partition_info=None):
+        return np.zeros(shape, np.float32)
+
+
+GLOBAL_STEP = [np.asarray(0, np.int64)]
+_train = types.SimpleNamespace(get_or_create_global_step=lambda: GLOBAL_STEP[0])
+
+
+class _V1:
+    """tf.compat.v1: its own few names, everything else falls through to the top-level stand-ins."""
+    variable_scope = staticmethod(_variable_scope)
+    get_variable_scope = staticmethod(lambda: _SCOPE)
+    zeros_initializer = _ZerosInitializer
+    train = _train
+    logging = types.SimpleNamespace(info=lambda *a, **k: None)
+
+    def __getattr__(self, name):
+        try:
+            return globals()[name]
+        except KeyError:
+            raise AttributeError(f"tf.compat.v1.{name} is not part of the stand-in") from None
+
+
+compat = types.SimpleNamespace(v1=_V1())
+
+
+def __getattr__(name):
+    if name[:1].isupper():
+        cls = type(name, (), {})
+        globals()[name] = cls
+        return cls
+    raise AttributeError(f"tensorflow.{name} is not part of the stand-in (oracle/ref_shim/README.md)")

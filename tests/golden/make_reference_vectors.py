@@ -1,0 +1,204 @@
+"""Golden vectors from the REFERENCE'S OWN PYTHON, run in the build container (where /root/reference exists).
+
+    python tests/golden/make_reference_vectors.py        ->  tests/golden/reference_*.npz
+
+`src.*` of /root/reference is imported unmodified; its two third-party tensor libraries (tensorflow 2.7,
+mesh-tensorflow: not installable here) are replaced by the eager NumPy stand-ins of oracle/ref_shim (see its
+README).  Recorded:
+
+  reference_optimizer.npz      src/optimizer/__init__.py:get_optimizer itself -- learning-rate context, step / beta /
+                               step_count arithmetic, every stage of the optimizer string, the weight-decay rule and
+                               the assignment -- driven by a loss whose gradient is a given array per variable (a
+                               test-side mtf.Operation: <var, G>; the reference's reverse sweep calls its gradient()),
+                               for several optimizer strings, three consecutive steps each, and the macro-batching
+                               ("add" then "update") call pair of src/run/train.py:35-74
+  reference_learning_rate.npz  src/optimizer/learning_rate.py:get_learning_rate over steps and module combinations
+  reference_layers.npz         forward values of src/model/normalization.py:norm, the activations of
+                               src/model/activation.py, src/mtf_wrapper.py:softmax_cross_entropy_with_logits
+  reference_dataclass.json     derived sizes of src/dataclass.py:ModelParameter for the shipped configs
+
+tests/test_oracle_pins.py compares oracle/obst_oracle.py (and the host mirror's ModelParameter) with these files.
+"""
+import copy
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+REFERENCE = "/root/reference"
+sys.path.insert(0, os.path.join(ROOT, "oracle", "ref_shim"))
+sys.path.insert(0, REFERENCE)
+sys.path.insert(1, ROOT)
+
+import mesh_tensorflow as mtf  # noqa: E402  (the stand-in)
+import tensorflow as tf  # noqa: E402  (the stand-in)
+
+from src import utils_core  # noqa: E402
+from src.dataclass import BlockArgs, ModelParameter  # noqa: E402
+from src.optimizer import get_optimizer  # noqa: E402
+from src.optimizer.learning_rate import get_learning_rate  # noqa: E402
+from src.utils_mtf import get_variable  # noqa: E402
+
+from oracle import obst_oracle as orc  # noqa: E402  (only for the shared tiny config and seeded arrays)
+
+
+class LinearLoss(mtf.Operation):
+    """loss = sum_v <v, G_v>: its gradient hands every variable the array G_v (times the incoming gradient)."""
+
+    def __init__(self, values, grads):
+        super().__init__(values, name="linear_loss")
+        self.grads = grads
+        total = sum(float((v.np.astype(np.float64) * g).sum()) for v, g in zip(values, grads))
+        self._outputs = [mtf.Tensor(self, [], tf.float32, value=np.float32(total))]
+
+    def gradient(self, grad_ys):
+        dy = grad_ys[0]
+        return [mtf.import_fully_replicated(v.mesh, g.astype(np.float32), v.shape, "given_gradient") * dy
+                for v, g in zip(self.inputs, self.grads)]
+
+
+def fresh_params(config):
+    utils_core.NAME_INDICES.clear()
+    tf.compat.v1.get_variable_scope().stack.clear()
+    params = ModelParameter(copy.deepcopy(config))
+    params.mesh = mtf.Mesh(mtf.Graph(), "mesh")
+    return params
+
+
+class Given:
+    """Initializer returning a fixed array."""
+
+    def __init__(self, array):
+        self.array = array
+
+    def __call__(self, shape, dtype=None):
+        return self.array.reshape(shape)
+
+
+def make_variables(params, specs):
+    """specs: [(scope, dims, array)]; created through the reference's get_variable under that variable scope."""
+    out = []
+    for scope, dims, array in specs:
+        with tf.compat.v1.variable_scope(scope):
+            t = get_variable(params, "get_variable0", dims, Given(array), True, params.variable_dtype)
+        out.append(t)
+    return out
+
+
+def variable_specs(params, rng):
+    """A cross-section of the mixer's variables: scope names decide the weight-decay rule
+    (src/optimizer/__init__.py:49-57), ranks decide sm3 / adam."""
+    H, K = params.head_dim, params.key_dim
+    inter = params.intermediate[0]
+    seq = params.sequence_dim
+    aseq = mtf.Dimension("_" + seq.name, seq.size)
+
+    def arr(dims, scale=1.0):
+        return (rng.standard_normal([d.size for d in dims]) * scale).astype(np.float32)
+
+    specs = [
+        ("gpt0v/body0v/0_0v/bottleneck_group_linear_0v/activated_linear_in_0v/linear_0v/orthogonal_var_0v", [H, K, inter], 0.05),
+        ("gpt0v/body0v/0_0v/bottleneck_group_linear_0v/activated_linear_out_0v/linear_0v/orthogonal_var_0v", [H, inter, K], 0.05),
+        ("gpt0v/body0v/0_0v/norm_0v/normal_var_0v", [H, K], 1.0),
+        ("gpt0v/body0v/0_1v/attention_0v/embed_0v/normal_var_0v", [H, seq, aseq], 0.02),
+        ("gpt0v/input0v/linear_to_features_0v/orthogonal_var_0v", [inter, H, K], 0.05),
+        ("gpt0v/body0v/0_0v/rezero_0v/get_var_0v", [], 0.3),
+    ]
+    return [(scope, dims, arr(dims, s)) for scope, dims, s in specs]
+
+
+def run_optimizer_case(config, optimizer, steps, macro=1, seed=0):
+    cfg = copy.deepcopy(config)
+    cfg["optimizer"] = optimizer
+    cfg["macro_batching"] = macro
+    params = fresh_params(cfg)
+    rng = np.random.default_rng(seed)
+    specs = variable_specs(params, rng)
+    values = make_variables(params, specs)
+    names = list(params.variable_cache.keys())
+    record = {"names": names, "steps": []}
+    record["init"] = {n: params.variable_cache[n].master.copy() for n in names}
+    for step in range(steps):
+        tf.GLOBAL_STEP[0] = np.asarray(cfg.get("_first_step", 1500) + step * macro, np.int64)
+        grads_per_slice = []
+        idx = mtf.constant(params.mesh, 0, [], params.optimizer_calculation_dtype)
+        update_ops = []
+        for i in range(1, macro + 1):
+            utils_core.NAME_INDICES.clear()
+            grads = [(rng.standard_normal(v.shape.to_integer_list) * 10 ** rng.uniform(-3, -1)).astype(np.float32)
+                     for v in values]
+            grads_per_slice.append(grads)
+            # what the graph of this slice reads: the cache entry (a Variable, or the chained tensor's op)
+            seen = [params.variable_cache[n].outputs[0] for n in names]
+            loss = LinearLoss(seen, grads).outputs[0]
+            last = i == macro
+            update_ops, lr = get_optimizer([loss], params, idx, "update" if last else "add")
+            if not last:  # src/run/train.py:63-69
+                idx += 1
+                for tensor in update_ops:
+                    from src.mtf_wrapper import get_variable_for_tensor
+                    op = get_variable_for_tensor(tensor)
+                    chained = mtf.stop_gradient(mtf.cast(tensor, op.activation_dtype))
+                    params.variable_cache[op.full_name] = chained.operation
+        for op in update_ops:
+            op.apply()
+        # Within one get_train_model graph the cache entries of variables AND slots are replaced by the chained
+        # tensors' ops (src/run/train.py:63-69).  The reference builds that graph once and re-runs it every step, so
+        # the next step's first slice reads the variables again: put them back.
+        for var in [v for v in params.mesh.graph.operations if isinstance(v, mtf.Variable)]:
+            if hasattr(var, "full_name"):
+                params.variable_cache[var.full_name] = var
+        state = {v.full_name: v.master.copy() for v in params.mesh.graph.operations
+                 if isinstance(v, mtf.Variable) and hasattr(v, "full_name")}
+        record["steps"].append({"grads": grads_per_slice, "lr": float(lr.np), "state": state})
+        params.mesh.graph.operations[:] = [op for op in params.mesh.graph.operations if isinstance(op, mtf.Variable)]
+    return record
+
+
+def flatten(prefix, obj, out):
+    if isinstance(obj, dict):
+        for k, v in obj.items():
+            flatten(f"{prefix}|{k}", v, out)
+    elif isinstance(obj, (list, tuple)) and obj and not isinstance(obj[0], str):
+        for i, v in enumerate(obj):
+            flatten(f"{prefix}|{i}", v, out)
+    elif isinstance(obj, (list, tuple)):
+        out[prefix] = np.asarray(obj)
+    else:
+        out[prefix] = np.asarray(obj)
+
+
+def small_config():
+    """The oracle's tiny mixer config, shrunk so that the committed vectors stay small."""
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(sequence_length=16, features_per_head=8, heads=4, train_batch_size=2, vocab_size=32)
+    return cfg
+
+
+def main():
+    base = small_config()
+    out = {}
+    cases = {
+        "hot_path": ("adaptive_clip:0.003-sm3-momentum:0.9:1:1-learning_rate", 3, 1),
+        "no_clip_heavyball": ("sm3-momentum:0.9:1:0-learning_rate", 2, 1),
+        "adam": ("adam-learning_rate", 3, 1),
+        "novograd": ("novograd-momentum:0.9:1:0-learning_rate", 2, 1),
+        "clips": ("l2norm_clip:0.5-value_clip:0.01-gradient_centralisation-weight_centralisation-sm3-learning_rate", 2, 1),
+        "global_clip": ("global_l2norm_clip:0.2-momentum:0.95:0.5:1-learning_rate", 2, 1),
+        "graft": ("graft:adam-learning_rate", 2, 1),
+        "macro2": ("adaptive_clip:0.003-sm3-momentum:0.9:1:1-learning_rate", 2, 2),
+    }
+    for name, (optimizer, steps, macro) in cases.items():
+        rec = run_optimizer_case(base, optimizer, steps, macro, seed=100 + list(cases).index(name))
+        rec["optimizer"] = optimizer
+        rec["macro"] = macro
+        flatten(name, rec, out)
+        print("optimizer case", name, "ok:", len(rec["steps"]), "steps")
+    np.savez_compressed(os.path.join(HERE, "reference_optimizer.npz"), **out)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,95 @@
+"""Pins oracle/obst_oracle.py against vectors recorded from the REFERENCE'S OWN PYTHON (tests/golden/reference_*.npz,
+made by tests/golden/make_reference_vectors.py in the build container: /root/reference's src.* imported unmodified,
+its two third-party tensor libraries replaced by the eager NumPy stand-ins of oracle/ref_shim).  What is pinned is
+the reference's op order, constants and rules -- its code, executed -- not XLA's kernels.  CPU only; nothing here
+reads /root/reference."""
+import copy
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import obst_oracle as orc  # noqa: E402
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / (np.linalg.norm(b) + 1e-30))
+
+
+def small_config():
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(sequence_length=16, features_per_head=8, heads=4, train_batch_size=2, vocab_size=32)
+    return cfg
+
+
+def _nested(npz, prefix):
+    out = {}
+    for k in npz.files:
+        if k.startswith(prefix + "|"):
+            node = out
+            parts = k[len(prefix) + 1:].split("|")
+            for p in parts[:-1]:
+                node = node.setdefault(p, {})
+            node[parts[-1]] = npz[k]
+    return out
+
+
+# the recorded variables (make_reference_vectors.variable_specs), in order, under the oracle's names: the name decides
+# the oracle's weight-decay predicate and its rezero rule exactly as the scope name does in the reference
+ORACLE_NAMES = ["win_0", "wout_0", "g0_0", "mix_a", "w0", "rezero_0"]
+FIRST_STEP = 1500
+
+OPT_CASES = ["hot_path", "no_clip_heavyball", "adam", "novograd", "clips", "global_clip", "graft", "macro2"]
+
+
+@pytest.mark.parametrize("case", OPT_CASES)
+def test_optimizer_matches_the_reference_get_optimizer(case):
+    """src/optimizer/__init__.py:get_optimizer (learning-rate context, step / beta / step_count arithmetic, every
+    stage of src/optimizer/optimizers.py, the rezero multiplier, the weight-decay rule, assign_sub -- and for
+    `macro2` the "add" / "update" call pair of src/run/train.py:35-74) against orc.optimizer_step on the same
+    variables and gradients: weights and every optimizer slot after each of the recorded steps."""
+    with np.load(os.path.join(GOLDEN, "reference_optimizer.npz")) as f:
+        rec = _nested(f, case)
+    optimizer, macro = str(rec["optimizer"]), int(rec["macro"])
+    names = [str(n) for n in rec["names"]]
+    assert len(names) == len(ORACLE_NAMES)
+    cfg = small_config()
+    cfg["optimizer"] = optimizer
+    sh = orc.Shapes(cfg)
+    params = {o: rec["init"][n].astype(np.float32) for o, n in zip(ORACLE_NAMES, names)}
+    state = {o: {} for o in ORACLE_NAMES}  # slots appear on first use, zero (src/optimizer/backend.py:23-25)
+    opt_key = optimizer.replace(":", "_")
+    for s in sorted(rec["steps"], key=int):
+        step = rec["steps"][s]
+        global_step = FIRST_STEP + int(s) * macro
+        lr = orc.learning_rate(sh, global_step)
+        assert abs(lr - float(step["lr"])) <= 1e-7 * abs(lr), (lr, float(step["lr"]))
+        seen = None
+        for i in range(macro):
+            grads = {o: step["grads"][str(i)][str(j)].astype(np.float32) for j, o in enumerate(ORACLE_NAMES)}
+            last = i == macro - 1
+            seen = orc.optimizer_step(sh, params, grads, state, lr, step_count=global_step + 1, seen=seen, assign=last)
+        want = step["state"]
+        for o, n in zip(ORACLE_NAMES, names):
+            assert rel(params[o], want[n]) < 2e-6, (case, s, o)
+        # every slot the reference created: "<stage><k>v/<variable>/<optimizer string>/<slot>"
+        slots = {k: v for k, v in want.items() if k not in names}
+        assert slots, "no optimizer slots recorded"
+        seen_slots = 0
+        for key, value in slots.items():
+            scope, _, tail = key.partition("/")
+            var_name, _, slot = tail.rpartition(f"/{opt_key}/")
+            o = ORACLE_NAMES[names.index(var_name)]
+            assert slot in state[o], (case, key, sorted(state[o]))
+            got = np.asarray(state[o][slot], np.float32).reshape(value.shape)
+            scale = max(float(np.abs(value).max()), 1e-30)
+            assert float(np.abs(got - value).max()) <= 3e-6 * scale, (case, s, key)
+            seen_slots += 1
+        assert seen_slots == sum(len(v) for v in state.values()), "the oracle holds slots the reference does not"
