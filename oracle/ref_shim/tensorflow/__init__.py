@@ -1,5 +1,6 @@
 """NumPy stand-in for the slice of TensorFlow the reference's Python touches (see ../README.md).  Tensors are NumPy
 arrays; float32 arithmetic stays float32 (NumPy >= 2 treats Python scalars as weak)."""
+import builtins
 import contextlib
 import types
 
@@ -54,11 +55,37 @@ def round_bf16(x):
     return out.reshape(x.shape)
 
 
+class _StaticShape(tuple):
+    def as_list(self):
+        return list(self)
+
+
+class TFArray(np.ndarray):
+    """ndarray whose `.shape` also answers `.as_list()`, as a tf.Tensor's static shape does."""
+
+    @property
+    def shape(self):
+        return _StaticShape(np.ndarray.shape.__get__(self))
+
+
+def _w(x):
+    return np.asarray(x).view(TFArray)
+
+
 def cast(x, dtype, name=None):
     x = np.asarray(x)
+    if not isinstance(dtype, DType):  # a NumPy dtype taken from another stand-in tensor
+        return _w(x.astype(dtype))
     if dtype.is_bf16:
-        return round_bf16(x.astype(np.float32))
-    return x.astype(dtype.as_numpy_dtype)
+        return _w(round_bf16(x.astype(np.float32)))
+    return _w(x.astype(dtype.as_numpy_dtype))
+
+
+def tensor_scatter_nd_add(tensor, indices, updates, name=None):
+    out = np.array(tensor, copy=True)
+    idx = np.asarray(indices)
+    np.add.at(out, tuple(idx[..., k] for k in builtins.range(idx.shape[-1])), np.asarray(updates))
+    return _w(out)
 
 
 def constant(value, dtype=None, shape=None, name=None):
@@ -82,7 +109,7 @@ less = lambda a, b, name=None: np.less(a, b)  # noqa: E731
 less_equal = lambda a, b, name=None: np.less_equal(a, b)  # noqa: E731
 identity = lambda x, name=None: np.asarray(x)  # noqa: E731
 stop_gradient = identity
-reshape = lambda x, shape, name=None: np.reshape(x, shape)  # noqa: E731
+reshape = lambda x, shape, name=None: _w(np.reshape(np.asarray(x), shape))  # noqa: E731
 transpose = lambda x, perm=None, name=None: np.transpose(x, perm)  # noqa: E731
 zeros = lambda shape, dtype=float32, name=None: np.zeros(shape, dtype.as_numpy_dtype)  # noqa: E731
 ones = lambda shape, dtype=float32, name=None: np.ones(shape, dtype.as_numpy_dtype)  # noqa: E731
@@ -90,8 +117,8 @@ zeros_like = lambda x, name=None: np.zeros_like(x)  # noqa: E731
 reduce_sum = lambda x, axis=None, keepdims=False, name=None: np.sum(x, axis=axis, keepdims=keepdims)  # noqa: E731
 reduce_mean = lambda x, axis=None, keepdims=False, name=None: np.mean(x, axis=axis, keepdims=keepdims)  # noqa: E731
 reduce_max = lambda x, axis=None, keepdims=False, name=None: np.max(x, axis=axis, keepdims=keepdims)  # noqa: E731
-einsum = lambda eq, *xs, name=None: np.einsum(eq, *xs)  # noqa: E731
-gather = lambda params, indices, axis=0, name=None: np.take(params, indices, axis=axis)  # noqa: E731
+einsum = lambda eq, *xs, name=None: _w(np.einsum(eq, *[np.asarray(x) for x in xs]))  # noqa: E731
+gather = lambda params, indices, axis=0, name=None: _w(np.take(np.asarray(params), np.asarray(indices), axis=axis))  # noqa: E731
 squeeze = lambda x, axis=None, name=None: np.squeeze(x, axis=tuple(axis) if isinstance(axis, (list, tuple)) else axis)  # noqa: E731
 expand_dims = lambda x, axis, name=None: np.expand_dims(x, axis)  # noqa: E731
 square = _f(np.square)
@@ -104,6 +131,25 @@ abs = _f(np.abs)  # noqa: A001
 rsqrt = lambda x, name=None: (1 / np.sqrt(np.asarray(x))).astype(np.asarray(x).dtype)  # noqa: E731
 sigmoid = lambda x, name=None: (1 / (1 + np.exp(-np.asarray(x)))).astype(np.asarray(x).dtype)  # noqa: E731
 softplus = lambda x, name=None: np.logaddexp(np.asarray(x), 0).astype(np.asarray(x).dtype)  # noqa: E731
+
+
+class random_normal_initializer:  # noqa: N801
+    """Draws from NumPy's generator, not TensorFlow's: same distribution, different numbers (the drivers overwrite
+    trained variables with given arrays anyway)."""
+
+    def __init__(self, mean=0.0, stddev=0.05, seed=None):
+        self.mean, self.stddev, self.seed = mean, stddev, seed
+
+    def __call__(self, shape, dtype=None, partition_info=None):
+        return (np.random.default_rng(self.seed).standard_normal(tuple(shape)) * self.stddev + self.mean).astype(np.float32)
+
+
+class constant_initializer:  # noqa: N801
+    def __init__(self, value=0.0):
+        self.value = value
+
+    def __call__(self, shape, dtype=None, partition_info=None):
+        return np.full(tuple(shape), self.value, np.float32)
 
 
 def range(start, limit=None, delta=1, dtype=None, name=None):  # noqa: A001

@@ -143,6 +143,8 @@ def run_optimizer_case(config, optimizer, steps, macro=1, seed=0):
                     op = get_variable_for_tensor(tensor)
                     chained = mtf.stop_gradient(mtf.cast(tensor, op.activation_dtype))
                     params.variable_cache[op.full_name] = chained.operation
+        for op in update_ops:  # every new value from the OLD variable values, then the assignments
+            op.stage()
         for op in update_ops:
             op.apply()
         # Within one get_train_model graph the cache entries of variables AND slots are replaced by the chained
@@ -155,6 +157,65 @@ def run_optimizer_case(config, optimizer, steps, macro=1, seed=0):
                  if isinstance(v, mtf.Variable) and hasattr(v, "full_name")}
         record["steps"].append({"grads": grads_per_slice, "lr": float(lr.np), "state": state})
         params.mesh.graph.operations[:] = [op for op in params.mesh.graph.operations if isinstance(op, mtf.Variable)]
+    return record
+
+
+def run_training_step(config, steps=2, seed=3, first_step=1500):
+    """src/run/train.py:get_train_model itself -- build() (input embedding, the reversible body of RevGradOps, LM
+    head, softmax cross-entropy + z-loss, accuracy) and get_optimizer (the reverse sweep through every op's
+    gradient(), RevGradOp.gradient's recompute / reconstruction, the optimizer chain) -- on the oracle's seeded
+    weights and tokens.  Weights are imposed in creation order (that order is part of what is pinned)."""
+    import src.optimizer as ref_optimizer
+    from src.run.train import get_train_model
+    params = fresh_params(config)
+    params.train = True
+    sh = orc.Shapes(config)
+    weights = orc.init_params(sh, seed=seed)
+    names = orc.param_names(sh)
+    tok_x, tok_y = orc.synthetic_tokens(sh)
+    record = {"oracle_names": names, "tok_x": tok_x, "tok_y": tok_y, "steps": []}
+    record["init"] = {n: weights[n] for n in names}
+    grads = {}
+    original_update = ref_optimizer.update
+
+    def recording_update(ctx):
+        grads[ctx.var.full_name] = ctx.grad.np.copy()
+        return original_update(ctx)
+
+    ref_optimizer.update = recording_update
+    try:
+        for step in range(steps):
+            utils_core.NAME_INDICES.clear()
+            tf.GLOBAL_STEP[0] = np.asarray(first_step + step, np.int64)
+            if step == 0:
+                mtf.VARIABLE_VALUES[:] = [weights[n] for n in names]
+            shape = params.token_dim_shape
+            tx = mtf.import_fully_replicated(params.mesh, tok_x.reshape(shape.to_integer_list).astype(np.int32), shape, "x")
+            ty = mtf.import_fully_replicated(params.mesh, tok_y.reshape(shape.to_integer_list).astype(np.int32), shape, "y")
+            grads.clear()
+            out = get_train_model(params, None, None, None, tx, ty, None, None, None, None)
+            _, token_out, lr, total_loss, _, _, _, token_loss, accuracy, update_ops, _ = out
+            assert not mtf.VARIABLE_VALUES, "fewer trainable variables were created than the oracle names"
+            created = [n for n, v in params.variable_cache.items() if isinstance(v, mtf.Variable) and v.trainable]
+            rec = {"logits": token_out.np.copy(), "loss": float(total_loss.np), "token_loss": float(token_loss.np),
+                   "accuracy": float(accuracy.np), "lr": float(lr.np),
+                   "grads": {n: grads[n] for n in created}}
+            for op in update_ops:
+                op.stage()
+            for op in update_ops:
+                op.apply()
+            rec["state"] = {v.full_name: v.master.copy() for v in params.mesh.graph.operations
+                            if isinstance(v, mtf.Variable) and hasattr(v, "full_name")}
+            record["created"] = created
+            record["steps"].append(rec)
+            # the reference builds the graph once and re-runs it; here the step is rebuilt on the same variables
+            params.mesh.graph.operations[:] = [op for op in params.mesh.graph.operations if isinstance(op, mtf.Variable)]
+            for var in params.mesh.graph.operations:
+                if hasattr(var, "full_name"):
+                    params.variable_cache[var.full_name] = var
+            params.cached_parameters.clear()
+    finally:
+        ref_optimizer.update = original_update
     return record
 
 
@@ -175,6 +236,7 @@ def small_config():
     """The oracle's tiny mixer config, shrunk so that the committed vectors stay small."""
     cfg = copy.deepcopy(orc.TINY_CONFIG)
     cfg.update(sequence_length=16, features_per_head=8, heads=4, train_batch_size=2, vocab_size=32)
+    cfg.update(use_video=False, use_language=True)  # the model_mode == 'gpt' override of src/main.py:87-93
     return cfg
 
 
@@ -198,6 +260,12 @@ def main():
         flatten(name, rec, out)
         print("optimizer case", name, "ok:", len(rec["steps"]), "steps")
     np.savez_compressed(os.path.join(HERE, "reference_optimizer.npz"), **out)
+
+    out = {}
+    rec = run_training_step(small_config())
+    flatten("tiny", rec, out)
+    print("training step ok: loss", [s["loss"] for s in rec["steps"]])
+    np.savez_compressed(os.path.join(HERE, "reference_training_step.npz"), **out)
 
 
 if __name__ == "__main__":

@@ -93,3 +93,59 @@ def test_optimizer_matches_the_reference_get_optimizer(case):
             assert float(np.abs(got - value).max()) <= 3e-6 * scale, (case, s, key)
             seen_slots += 1
         assert seen_slots == sum(len(v) for v in state.values()), "the oracle holds slots the reference does not"
+
+
+def test_full_training_step_matches_the_reference_get_train_model():
+    """src/run/train.py:get_train_model itself, executed (tests/golden/make_reference_vectors.py:run_training_step):
+    build() -- token gather-embed, input linear, the reversible body as RevGradOps, LM head, softmax cross-entropy +
+    z-loss, accuracy -- and get_optimizer -- the reverse sweep through every op's gradient(), RevGradOp.gradient's
+    recompute and reconstruction, the optimizer chain -- on the oracle's seeded weights and tokens, two consecutive
+    steps.  The oracle (float64 forward / backward, fp32 optimizer) must reproduce logits, loss, accuracy, every
+    gradient, every updated weight and every optimizer slot; variables are matched BY CREATION ORDER, which pins that
+    order too."""
+    with np.load(os.path.join(GOLDEN, "reference_training_step.npz")) as f:
+        rec = _nested(f, "tiny")
+    cfg = small_config()
+    sh = orc.Shapes(cfg)
+    names = [str(n) for n in rec["oracle_names"]]
+    created = [str(n) for n in rec["created"]]
+    assert names == orc.param_names(sh) and len(created) == len(names)
+    params = {n: rec["init"][n].astype(np.float32).copy() for n in names}
+    state = orc.init_opt_state(params)
+    tok_x, tok_y = rec["tok_x"], rec["tok_y"]
+    opt_key = sh.optimizer.replace(":", "_")
+    for s in sorted(rec["steps"], key=int):
+        step = rec["steps"][s]
+        gs = FIRST_STEP + int(s)
+        trace = {}
+        seen = {k: v.astype(np.float64) for k, v in params.items()}
+        loss, acc, fwd_state = orc.forward(sh, seen, tok_x, tok_y, dtype=np.float64, trace=trace)
+        assert abs(loss - float(step["loss"])) < 1e-5 * abs(loss), (loss, float(step["loss"]))
+        assert abs(acc - float(step["accuracy"])) < 1e-7
+        logits = trace["logits"] if "logits" in trace else fwd_state.get("logits")
+        if logits is not None:
+            assert rel(np.asarray(logits).reshape(step["logits"].shape), step["logits"]) < 1e-4
+        grads = orc.backward(sh, fwd_state)
+        for o, n in zip(names, created):
+            want = step["grads"][n]
+            # the recorded run computes in float32 (calculation_dtype of the config) and the reversible backward
+            # differentiates at RECONSTRUCTED activations: fp32 rounding of that against the float64 oracle
+            assert rel(grads[o].reshape(want.shape), want) < 2e-4, (s, o, n)
+        lr = orc.learning_rate(sh, gs)
+        assert abs(lr - float(step["lr"])) <= 1e-7 * lr
+        orc.optimizer_step(sh, params, {k: v.astype(np.float32) for k, v in grads.items()}, state, lr, step_count=gs + 1)
+        for o, n in zip(names, created):
+            want = step["state"][n]
+            assert rel(params[o].reshape(want.shape), want) < 1e-4, (s, o)  # fp32 run vs float64 oracle, through sm3
+        n_slots = 0
+        for key, value in step["state"].items():
+            if key in created:
+                continue
+            _, _, tail = key.partition("/")
+            var_name, _, slot = tail.rpartition(f"/{opt_key}/")
+            o = names[created.index(var_name)]
+            got = np.asarray(state[o][slot], np.float32).reshape(value.shape)
+            scale = max(float(np.abs(value).max()), 1e-30)
+            assert float(np.abs(got - value).max()) <= 1e-3 * scale, (s, key)
+            n_slots += 1
+        assert n_slots >= 2 * len(names)
