@@ -196,6 +196,11 @@ def get_var(args: BlockArgs, shape: DIM_LIST, initializer) -> Variable:
 
     scope = scope_list()
     body_idx = scope.index("body0v") + 1
+    if scope[body_idx].startswith("recompute_grad"):
+        # 'checkpoint' strategy: recompute_grad's own scope sits between body and block.  The reference parses THAT as
+        # the block name and then divides by zero (src/model/backend.py:59-75): shared variables under 'checkpoint'
+        # do not run there; here the block name is simply read one level deeper.
+        body_idx += 1
     block, full_fn_name = scope[body_idx:body_idx + 2]
     block, config = block.split('_')
     first_block = block == '0'

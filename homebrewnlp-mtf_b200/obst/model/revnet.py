@@ -163,7 +163,9 @@ def checkpoint_body(params: ModelParameter, src: Tensor) -> Tensor:
     for i in range(params.depth):
         for config in params.block_config:
             records.append((utils_core.snapshot(), params.attention_idx, x))
-            x = block_part_fn(params, config, Tensor(x, dims), str(i)).data
+            # mtf_wrapper.recompute_grad is itself `scoped`: every block sits one scope level deeper than under the
+            # other strategies ("body0v/recompute_grad<n>v/<depth>_<config>v/..."), and that is part of the names
+            x = utils_core.scoped("recompute_grad", block_part_fn, params, config, Tensor(x, dims), str(i)).data
     params.tape = outer_tape
     if outer_tape is not None:
         n_cfg = len(params.block_config)
@@ -181,7 +183,7 @@ def checkpoint_body(params: ModelParameter, src: Tensor) -> Tensor:
                 params.attention_idx = att_idx
                 reset_shared_ordinals(params, str(i), f"{c}v")
                 params.tape = []
-                block_part_fn(params, params.block_config[c], Tensor(xin, dims), str(i))
+                utils_core.scoped("recompute_grad", block_part_fn, params, params.block_config[c], Tensor(xin, dims), str(i))
                 tape, params.tape = params.tape, None
                 dy = run_tape(tape, dy)
                 records[j] = None  # frees the stored input

@@ -146,8 +146,6 @@ def _general_attention(args: BlockArgs) -> Tensor:
                     native.operand(key_data, F, 1, s_glo=K, s_ghi=S * F if key_batched else 0), logits, S, S, K, GLO=H,
                     GHI=Bn, d_ld=H * S, d_glo=S, d_ghi=S * H * S, dtype_in=dt, backend=be)
         if "shared_key_value" in args:
-            if not key_batched:
-                raise NotImplementedError("shared_key_value with position-only keys")
             val = key_data
     bias_var = masked_map() if 'biased_softmax' in args else None
     if logits is None and bias_var is not None:
@@ -170,16 +168,39 @@ def _general_attention(args: BlockArgs) -> Tensor:
         else:
             v, tape_v = branch(lambda: activated_linear_out(bargs))
             val = v.data
-    p_op = native.operand(p, H * S, 1, s_glo=S, s_ghi=S * H * S)
-    v_op = native.operand(val, 1, F, s_glo=K, s_ghi=S * F)
     params.residual = None
-    if pending is not None:
-        buf, sign, out = pending
-        native.gemm(p_op, v_op, out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, R=buf,
-                    epi=2 if sign > 0 else 3, dtype_in=dt, backend=be)
+    # `shared_key_value` (src/model/spatial.py:63-64,76-81): `val = key` is set BEFORE the `if val == 0` that would
+    # rename its sequence dim, so the final einsum([map, val], shape) finds `sequence` in both operands and in the
+    # output -- it only contracts the map's own `_sequence`: out[b,s,h,:] = (sum_t map[b,s,h,t]) * key[b,s,h,:].
+    # No token is mixed (a pure soft-max map sums to 1: out = key).  That is what the reference computes, so that is
+    # what runs here.
+    degenerate = "shared_key_value" in args and 'dot_product' in args
+    rowsum_b = None
+    if degenerate:
+        rows = Bn * S * H
+        rowsum = torch.empty((rows,), dtype=dt, device=x.data.device)
+        native.sum_heads(p, rowsum, rows, S, 1)                       # sum over t
+        rowsum_b = torch.empty((Bn, S, H, K), dtype=dt, device=x.data.device)
+        native.broadcast_heads(rowsum, rowsum_b, rows, K, 1)          # ... spread over the features
+        if not key_batched:
+            val = val.unsqueeze(0).expand(Bn, S, H, K).contiguous()
+        f = torch.empty_like(x.data)
+        native.mul(rowsum_b, val, f)
+        if pending is not None:
+            buf, sign, out = pending
+            native.axpby(buf, f, sign, out)
+        else:
+            out = f
     else:
-        out = torch.empty_like(x.data)
-        native.gemm(p_op, v_op, out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, dtype_in=dt, backend=be)
+        p_op = native.operand(p, H * S, 1, s_glo=S, s_ghi=S * H * S)
+        v_op = native.operand(val, 1, F, s_glo=K, s_ghi=S * F)
+        if pending is not None:
+            buf, sign, out = pending
+            native.gemm(p_op, v_op, out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, R=buf,
+                        epi=2 if sign > 0 else 3, dtype_in=dt, backend=be)
+        else:
+            out = torch.empty_like(x.data)
+            native.gemm(p_op, v_op, out, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K, d_ghi=S * F, dtype_in=dt, backend=be)
 
     if outer is not None:
         def into(tape, g):
@@ -191,14 +212,21 @@ def _general_attention(args: BlockArgs) -> Tensor:
             return g
 
         def bwd(dy, mask, acc):
-            # through out = p @ val
             dp = torch.empty_like(soft)
-            native.gemm(native.operand(dy, F, 1, s_glo=K, s_ghi=S * F), native.operand(val, F, 1, s_glo=K, s_ghi=S * F),
-                        dp, S, S, K, GLO=H, GHI=Bn, d_ld=H * S, d_glo=S, d_ghi=S * H * S, dtype_in=dt, backend=be)
             dval = torch.empty_like(val)
-            native.gemm(native.operand(p, 1, H * S, s_glo=S, s_ghi=S * H * S),
-                        native.operand(dy, 1, F, s_glo=K, s_ghi=S * F), dval, S, K, S, GLO=H, GHI=Bn, d_ld=F, d_glo=K,
-                        d_ghi=S * F, dtype_in=dt, backend=be)
+            if degenerate:  # out = rowsum(map) * key
+                native.mul(rowsum_b, dy, dval)
+                tmp = torch.empty_like(val)
+                native.mul(dy, val, tmp)
+                d_rowsum = torch.empty((Bn * S * H,), dtype=dt, device=dy.device)
+                native.sum_heads(tmp, d_rowsum, Bn * S * H, K, 1)
+                native.broadcast_heads(d_rowsum, dp, Bn * S * H, S, 1)
+            else:  # through out = p @ val
+                native.gemm(native.operand(dy, F, 1, s_glo=K, s_ghi=S * F), native.operand(val, F, 1, s_glo=K, s_ghi=S * F),
+                            dp, S, S, K, GLO=H, GHI=Bn, d_ld=H * S, d_glo=S, d_ghi=S * H * S, dtype_in=dt, backend=be)
+                native.gemm(native.operand(p, 1, H * S, s_glo=S, s_ghi=S * H * S),
+                            native.operand(dy, 1, F, s_glo=K, s_ghi=S * F), dval, S, K, S, GLO=H, GHI=Bn, d_ld=F,
+                            d_glo=K, d_ghi=S * F, dtype_in=dt, backend=be)
             # through the soft-max stage: dp -> dlogits (in place), map gradients
             native.attn_softmax_bwd(dp, soft, None if add_var is None else add_var.value,
                                     None if mul_var is None else mul_var.value, dp,

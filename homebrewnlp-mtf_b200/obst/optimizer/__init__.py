@@ -63,10 +63,16 @@ def _drain_list(items, cols_of, slots: int = 296):
 
 def _depth_of(var: Variable) -> int:
     """Depth index from the scope name `.../body0v/<depth>_<cfg>v/...`; -1 for input/output variables."""
+    import re
     parts = var.name.split('/')
     if "body0v" in parts:
-        blk = parts[parts.index("body0v") + 1]
-        return int(blk.split('_')[0])
+        # the block scope follows body0v directly, or one level deeper under the 'checkpoint' strategy
+        # (body0v/recompute_grad<n>v/<depth>_<cfg>v); body-level variables that belong to no block (the initial
+        # position embedding) go with the input / output bucket
+        for blk in parts[parts.index("body0v") + 1:][:2]:
+            m = re.fullmatch(r"(\d+)_\d+v", blk)
+            if m:
+                return int(m.group(1))
     return -1
 
 

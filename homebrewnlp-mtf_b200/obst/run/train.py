@@ -96,8 +96,9 @@ def get_train_model(params: ModelParameter, frame_input, cat_mask_src, cat_mask_
     total = Loss(params.loss_sums, n, z)
     if macro == 1:
         first = last = total
-    accuracy = total if params.calc_accuracy else None
-    return None, token_out, learning_rate, total, first, last, None, total, accuracy, update_ops, {}
+    # token_loss and accuracy are what the LAST macro-batch's build returned (src/run/train.py:40,76-77)
+    accuracy = last if params.calc_accuracy else None
+    return None, token_out, learning_rate, total, first, last, None, last, accuracy, update_ops, {}
 
 
 def read_scalars(params: ModelParameter, loss: Loss) -> typing.Dict[str, float]:

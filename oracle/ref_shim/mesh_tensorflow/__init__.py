@@ -417,7 +417,11 @@ def _broadcast_shape(s1, s2):
 
 
 def _f32(arr, dtype):
-    return arr.astype(np.float32) if dtype.is_floating else arr
+    """Operand in the precision the op computes in: float32 for float32 / bfloat16 tensors (bf16 results are rounded
+    afterwards), float64 for float64 tensors."""
+    if not dtype.is_floating:
+        return arr
+    return arr.astype(np.float64 if dtype.name == "float64" else np.float32)
 
 
 def _sum_to(dy, shape):

@@ -67,6 +67,12 @@ class TFArray(np.ndarray):
     def shape(self):
         return _StaticShape(np.ndarray.shape.__get__(self))
 
+    # a tf.Tensor is immutable: `x += y` rebinds x to a new (broadcast) tensor
+    def __iadd__(self, other): return self + other  # noqa: E704
+    def __isub__(self, other): return self - other  # noqa: E704
+    def __imul__(self, other): return self * other  # noqa: E704
+    def __itruediv__(self, other): return self / other  # noqa: E704
+
 
 def _w(x):
     return np.asarray(x).view(TFArray)
@@ -133,6 +139,9 @@ sigmoid = lambda x, name=None: (1 / (1 + np.exp(-np.asarray(x)))).astype(np.asar
 softplus = lambda x, name=None: np.logaddexp(np.asarray(x), 0).astype(np.asarray(x).dtype)  # noqa: E731
 
 
+_SEEDS = [1000]
+
+
 class random_normal_initializer:  # noqa: N801
     """Draws from NumPy's generator, not TensorFlow's: same distribution, different numbers (the drivers overwrite
     trained variables with given arrays anyway)."""
@@ -141,7 +150,11 @@ class random_normal_initializer:  # noqa: N801
         self.mean, self.stddev, self.seed = mean, stddev, seed
 
     def __call__(self, shape, dtype=None, partition_info=None):
-        return (np.random.default_rng(self.seed).standard_normal(tuple(shape)) * self.stddev + self.mean).astype(np.float32)
+        seed = self.seed
+        if seed is None:  # deterministic across runs of the generator
+            _SEEDS[0] += 1
+            seed = _SEEDS[0]
+        return (np.random.default_rng(seed).standard_normal(tuple(shape)) * self.stddev + self.mean).astype(np.float32)
 
 
 class constant_initializer:  # noqa: N801
@@ -157,6 +170,16 @@ def range(start, limit=None, delta=1, dtype=None, name=None):  # noqa: A001
         start, limit = 0, start
     out = np.arange(start, limit, delta)
     return out.astype(dtype.as_numpy_dtype) if dtype is not None else out.astype(np.int32)
+
+
+def cumsum(x, axis=0, exclusive=False, reverse=False, name=None):
+    x = np.asarray(x)
+    if reverse:
+        x = np.flip(x, axis)
+    out = np.cumsum(x, axis=axis, dtype=x.dtype)
+    if exclusive:
+        out = out - x
+    return _w(np.flip(out, axis) if reverse else out)
 
 
 def mod(x, y, name=None):

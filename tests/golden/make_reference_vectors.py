@@ -219,6 +219,142 @@ def run_training_step(config, steps=2, seed=3, first_step=1500):
     return record
 
 
+def run_model_case(config, steps=1, first_step=1500, seed=11):
+    """get_train_model on an arbitrary config with the reference's OWN initialisers (orthogonal / normal / zeros --
+    drawn from NumPy's generator, see oracle/ref_shim).  Records the created trainable variables in creation order,
+    the tokens, and per step: logits, loss, accuracy, lr, every gradient, every updated variable.  Consumed by the
+    product's GPU tests, which import the weights in creation order."""
+    import random
+
+    import src.optimizer as ref_optimizer
+    from src.run.train import get_train_model
+    random.seed(seed)  # OrthogonalInit draws its seed from `random` (src/model/backend.py:23)
+    tf._SEEDS[0] = 1000 * seed
+    params = fresh_params(config)
+    params.train = True
+    rng = np.random.default_rng(seed)
+    macro = params.macro_batching
+    shape = mtf.Shape(params.token_dim_shape.dims)
+    ints = shape.to_integer_list
+    ints[0] *= macro
+    full = mtf.Shape([mtf.Dimension(shape.dims[0].name, ints[0])] + shape.dims[1:])
+    window = rng.integers(0, params.vocab_size, [ints[0], params.sequence_length + 1])
+    tok_x, tok_y = window[:, :-1].astype(np.int32), window[:, 1:].astype(np.int32)
+    record = {"config": json.dumps(config), "tok_x": tok_x, "tok_y": tok_y, "steps": []}
+    grads = {}
+    original_update = ref_optimizer.update
+
+    def recording_update(ctx):
+        grads.setdefault(ctx.var.full_name, []).append(ctx.grad.np.copy())
+        return original_update(ctx)
+
+    ref_optimizer.update = recording_update
+    try:
+        for step in range(steps):
+            utils_core.NAME_INDICES.clear()
+            tf.GLOBAL_STEP[0] = np.asarray(first_step + step * macro, np.int64)
+            tx = mtf.import_fully_replicated(params.mesh, tok_x.reshape(ints), full, "x")
+            ty = mtf.import_fully_replicated(params.mesh, tok_y.reshape(ints), full, "y")
+            grads.clear()
+            out = get_train_model(params, None, None, None, tx, ty, None, None, None, None)
+            _, token_out, lr, total_loss, first_loss, last_loss, _, token_loss, accuracy, update_ops, _ = out
+            # (with macro-batching src/run/train.py:57-60 lists the variables twice; it deduplicates a private copy)
+            variables = list(dict.fromkeys(v for v in params.mesh.graph.operations
+                                           if isinstance(v, mtf.Variable) and hasattr(v, "full_name")))
+            created = [v.full_name for v in variables if v.trainable]
+            if step == 0:
+                record["created"] = created
+                record["shapes"] = {v.full_name: np.asarray(v.shape.to_integer_list, np.int64) for v in variables if v.trainable}
+                record["init"] = {v.full_name: v.master.copy() for v in variables if v.trainable}
+            rec = {"logits": token_out.np.copy(), "loss": float(total_loss.np), "first_loss": float(first_loss.np),
+                   "last_loss": float(last_loss.np), "accuracy": float(accuracy.np), "lr": float(lr.np),
+                   "grads": {n: grads[n][-1] for n in created if n in grads}}
+            for op in update_ops:
+                op.stage()
+            for op in update_ops:
+                op.apply()
+            rec["state"] = {v.full_name: v.master.copy() for v in variables if v.trainable}
+            record["steps"].append(rec)
+            params.mesh.graph.operations[:] = variables
+            for var in variables:
+                params.variable_cache[var.full_name] = var
+            params.cached_parameters.clear()
+    finally:
+        ref_optimizer.update = original_update
+    return record
+
+
+def model_cases():
+    """Configs of the layer zoo: every registered layer / strategy the product implements, at toy sizes."""
+    base = small_config()
+    base.update(depth=1)
+
+    def cfg(**kw):
+        c = copy.deepcopy(base)
+        c.update(kw)
+        return c
+
+    norm = "norm-shift-scale-features-group"
+    mix = "attention-biased_attention_map-absolute-input_as_value-shared"
+
+    def blocks(*layer_lists, **extra):
+        return [dict({"layer": list(ls)}, **extra) for ls in layer_lists]
+
+    def one(layers, **kw):  # a single non-reversible block: every gradient is first-hand, no reconstruction noise
+        return cfg(memory_reduction_strategy="none", block_config=blocks([norm] + list(layers)), **kw)
+
+    cases = {
+        "mixer_depth2": cfg(depth=2),
+        "strategy_none": cfg(memory_reduction_strategy="none"),
+        # (`shared` variables cannot be combined with 'checkpoint' in the reference: recompute_grad's scope shifts the
+        # block name src/model/backend.py:59-62 parses, and the shared-variable counter divides by zero)
+        "strategy_checkpoint_skip": cfg(memory_reduction_strategy="checkpoint",
+                                        block_config=blocks([norm, "feed_forward-in:relu-in:norm-in:shift-in:scale-in:features"],
+                                                            [norm, mix.replace("-shared", "")], skip=True)),
+        "strategy_none_skip": cfg(memory_reduction_strategy="none",
+                                  block_config=blocks([norm, "feed_forward-in:relu"], [norm, mix], skip=True)),
+        "feed_forward_glu": cfg(block_config=blocks([norm, "feed_forward-in:mish-in:glu-in:norm-in:shift-in:scale-in:features"],
+                                                    [norm, "feed_forward-in:silu-in:glu_add"])),
+        "activations": cfg(memory_reduction_strategy="none",
+                           block_config=blocks([norm, "feed_forward-in:lecun_tanh"], [norm, "feed_forward-in:softsign"],
+                                               [norm, "feed_forward-in:mtf_mish"], [norm, "feed_forward-in:sigmoid-in:tanh"],
+                                               [norm, "feed_forward-in:gelu"])),
+        # ('exp' is registered as ACTIVATIONS['exp'] = mtf.exp and called with the BlockArgs, not its tensor,
+        # src/model/activation.py:201,211: it cannot run in the reference)
+        "cumsum_cummean": cfg(block_config=blocks([norm, "cumsum"], [norm, "cummean", "rezero"])),
+        # (reduced_half_linear reshapes a [.., heads, _features] product back to the head-reduced input's shape,
+        # src/model/basic.py:72-74,89-90: with more than one head mtf.reshape refuses the size change, so the layer has
+        # no reference behaviour here; sum_heads alone leaves a head-less tensor for the residual add)
+        "group_linear": cfg(block_config=blocks([norm, "group_linear"], [norm, mix])),
+        "transpose_sequence_features": cfg(sequence_length=8, block_config=blocks(
+            [norm, "transpose_sequence_features", "group_linear", "transpose_sequence_features"], [norm, mix])),
+        "attention_embedded": one(["attention-dot_product-embedded-absolute-in:relu"]),
+        "attention_context_biased_softmax": one(["attention-dot_product-context-input_as_value-biased_softmax-absolute"]),
+        "attention_maps": one(["attention-biased_softmax-scale_attention_map-biased_attention_map-input_as_value-absolute"]),
+        "attention_shared_key_value": one(["attention-dot_product-embedded-shared_key_value-absolute"]),
+        "attention_shared_key_value_maps": one(
+            ["attention-dot_product-context-shared_key_value-biased_attention_map-scale_attention_map-absolute"]),
+        # the sinusoid's schedule is exp(feature index): beyond a few features its sine is rounding noise in fp32
+        # (src/model/embedding.py:167-169), so these run with 2 heads x 4 features
+        "attention_relative": one(["attention-dot_product-positional-relative-input_as_value"],
+                                  position_embedding="relative", heads=2, features_per_head=4, vocab_weight_factorization=0.5),
+        "attention_relative_learned": one(["attention-dot_product-positional-relative-learned-input_as_value"],
+                                          position_embedding="relative", heads=2, features_per_head=4,
+                                          vocab_weight_factorization=0.5),
+        "attention_axial": one(["attention-dot_product-positional-axial-input_as_value"]),
+        "attention_stack_revnet": cfg(block_config=blocks(
+            [norm, "attention-dot_product-embedded-absolute-in:relu"],
+            [norm, "attention-dot_product-context-input_as_value-biased_softmax-absolute"],
+            [norm, "attention-dot_product-embedded-shared_key_value-absolute"])),
+        "split_path": cfg(block_config=blocks([norm, f"split_path-add;feed_forward-in:relu;{mix}"],
+                                              [norm, f"split_path-multiply;feed_forward-in:tanh;{mix}"])),
+        "initial_position_embedding": cfg(use_initial_position_embedding=True, position_embedding="axial"),
+        "macro_batching": cfg(macro_batching=2, depth=2),
+        "adam_chain": cfg(optimizer="adam-learning_rate", depth=2),
+    }
+    return cases
+
+
 def flatten(prefix, obj, out):
     if isinstance(obj, dict):
         for k, v in obj.items():
@@ -266,6 +402,21 @@ def main():
     flatten("tiny", rec, out)
     print("training step ok: loss", [s["loss"] for s in rec["steps"]])
     np.savez_compressed(os.path.join(HERE, "reference_training_step.npz"), **out)
+
+    out = {}
+    failed = {}
+    for name, config in model_cases().items():
+        try:
+            rec = run_model_case(config, steps=2 if name in ("mixer_depth2", "macro_batching", "adam_chain") else 1)
+        except Exception as exc:  # noqa: BLE001 -- reported, the other cases are still recorded
+            failed[name] = f"{type(exc).__name__}: {exc}"
+            print("model case", name, "FAILED:", failed[name])
+            continue
+        flatten(name, rec, out)
+        print("model case", name, "ok: loss", [round(s["loss"], 5) for s in rec["steps"]], len(rec["created"]), "variables")
+    np.savez_compressed(os.path.join(HERE, "reference_models.npz"), **out)
+    if failed:
+        print("FAILED CASES:", json.dumps(failed, indent=1))
 
 
 if __name__ == "__main__":
