@@ -13,6 +13,7 @@ restated without TensorFlow; `fmt="tf"`), and a single .npz (`fmt="npz"`).
 
 `exact=True` stores the fp32 slices instead of the storage dtype: resuming is then bit-identical to not stopping."""
 import os
+import re
 import typing
 import warnings
 
@@ -64,6 +65,7 @@ def save_checkpoint(params: ModelParameter, path: str, exact: bool = False, fmt:
         fmt = "npz" if path.endswith(".npz") else ("tf" if os.path.isdir(path) else "npz")
     if fmt == "tf":
         from . import tf_checkpoint
+        tensors = _to_graph_names(params, tensors)
         os.makedirs(path, exist_ok=True)
         name = f"model.ckpt-{params.global_step}"
         tf_checkpoint.write_bundle(os.path.join(path, name), tensors)
@@ -84,6 +86,57 @@ def save_checkpoint(params: ModelParameter, path: str, exact: bool = False, fmt:
     return path
 
 
+def _to_graph_names(params: ModelParameter, tensors: typing.Dict[str, torch.Tensor]) -> typing.Dict[str, torch.Tensor]:
+    """Slots under the names they have in the reference's graph (`<stage><k>v/...`, optimizer/backend.py:
+    graph_slot_name) -- the keys a TF checkpoint of the reference holds; variables keep their names."""
+    from ..optimizer.backend import graph_slot_name
+    opt = f"/{params.optimizer.replace(':', '_')}/"
+    order = {name: (k, len(var.data.shape)) for k, (name, var) in enumerate(params.variable_cache.items())}
+    out = {}
+    for name, t in tensors.items():
+        base, sep, slot = name.rpartition(opt)
+        if sep and base in order:
+            k, rank = order[base]
+            try:
+                name = graph_slot_name(params, base, slot, k, rank)
+            except KeyError:
+                continue  # a buffer of this implementation that no stage of the optimizer string owns (all zeros)
+        out[name] = t
+    return out
+
+
+def _slot_defined(params: ModelParameter, name: str) -> bool:
+    """Does any stage of the optimizer string create a slot of this name (for some rank)?"""
+    from ..optimizer.backend import slot_stage
+    slot = name.rsplit("/", 1)[-1]
+    for rank in (0, 4):
+        try:
+            slot_stage(params.optimizer, rank, slot)
+            return True
+        except KeyError:
+            pass
+    return False
+
+
+_GRAPH_PREFIX = re.compile(r"^[a-z_]+\d+v/(.+)$")
+
+
+def _from_graph_names(entries: typing.Dict[str, torch.Tensor]) -> typing.Dict[str, torch.Tensor]:
+    """Inverse of _to_graph_names on read: `<stage><k>v/<variable>/<optimizer string>/<slot>` -> the internal slot
+    name, recognised by its remainder starting with a variable that is itself in the file."""
+    out = {}
+    for name, t in entries.items():
+        m = _GRAPH_PREFIX.match(name)
+        if m:
+            rest = m.group(1)
+            parts = rest.split("/")
+            # <variable>/<optimizer string>/<slot>: the variable is everything but the last two components
+            if len(parts) > 2 and "/".join(parts[:-2]) in entries:
+                name = rest
+        out[name] = t
+    return out
+
+
 def _read_entries(path: str) -> typing.Dict[str, torch.Tensor]:
     """An .npz, a TensorBundle prefix, or a model directory with a `checkpoint` state file."""
     from . import tf_checkpoint
@@ -93,7 +146,7 @@ def _read_entries(path: str) -> typing.Dict[str, torch.Tensor]:
             raise FileNotFoundError(f"{path} holds no `checkpoint` state file")
         path = latest
     if os.path.exists(path + ".index"):
-        entries = tf_checkpoint.read_bundle(path)
+        entries = _from_graph_names(tf_checkpoint.read_bundle(path))
         return {k: (v.float() if v.dtype == torch.bfloat16 else v) for k, v in entries.items()}
     with np.load(path if path.endswith(".npz") else path + ".npz") as f:
         return dict(_unpack(k, f[k]) for k in f.files)
@@ -127,7 +180,7 @@ def take_entry(params: ModelParameter, name: str, kind: str = "variable") -> typ
     if entries is None:
         return None
     if name not in entries:
-        if kind == "slot" and not (set(entries) - set(params.variable_cache)):
+        if kind == "slot" and (not (set(entries) - set(params.variable_cache)) or not _slot_defined(params, name)):
             return None
         hint = " (optimizer string changed since the file was written?)" if kind == "slot" else ""
         raise KeyError(f"checkpoint has no {kind} '{name}'{hint}")

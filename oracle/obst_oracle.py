@@ -3,12 +3,19 @@
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this
 module, and only as the checker / reported CPU baseline.  The product (homebrewnlp-mtf_b200/) never does.
 
-PARITY UNPINNED: the reference holds no golden vectors, known-answer tests or fixtures for this path
-(its tests assert statistics of initialisers only) and it cannot be executed here
-(tensorflow==2.7.0 + mesh-tensorflow are not installable: requirements.txt:2-3, Python 3.12, no network).
-What pins this file is (a) line-by-line citation of the reference below, (b) the reference-authored
-statistical invariants re-asserted in tests/test_oracle.py, (c) an independent torch-autograd cross-check
-of every hand-written backward formula, (d) the committed fixtures under tests/golden/ made by this file.
+PARITY: pinned against THE REFERENCE'S OWN PYTHON, EXECUTED.  The reference holds no golden vectors for this path
+(its tests assert statistics of initialisers only) and its two tensor libraries cannot be
+installed here (tensorflow==2.7.0 + mesh-tensorflow: requirements.txt:2-3, Python 3.12, no network), but the
+reference itself is pure Python: tests/golden/make_reference_vectors.py imports /root/reference's src.* UNMODIFIED
+on top of eager NumPy stand-ins for those two libraries (oracle/ref_shim: named-dimension arithmetic, einsum,
+reductions and every op's gradient rule as mesh-tensorflow defines them; TensorFlow functions as their NumPy
+namesakes) and records what src/run/train.py:get_train_model -- build(), the RevGradOp reverse sweep with its
+reconstruction, get_optimizer with every stage -- returns.  tests/test_oracle_pins.py holds this file to those records
+(tests/golden/reference_*.npz): logits, loss, accuracy, every gradient, every updated weight and optimizer slot over
+consecutive steps, eight optimizer strings, the macro-batching chain.  What the stand-ins cannot pin is XLA's
+arithmetic itself (summation order, bf16 rounding points): those stay with (a) the line-by-line citations below,
+(b) the reference-authored statistical invariants of tests/test_oracle.py, (c) the torch-autograd cross-check of
+every hand-written backward formula.
 
 Citations are paths under /root/reference.
 """

@@ -149,3 +149,30 @@ def test_full_training_step_matches_the_reference_get_train_model():
             assert float(np.abs(got - value).max()) <= 1e-3 * scale, (s, key)
             n_slots += 1
         assert n_slots >= 2 * len(names)
+
+
+def test_graph_slot_names_match_what_the_reference_creates():
+    """The names of the optimizer slots in the reference's graph -- what a TF checkpoint of the reference holds --
+    against obst.optimizer.backend.graph_slot_name, for every recorded optimizer string: `<stage><k>v/<variable>/
+    <optimizer string>/<slot>`."""
+    sys.path.insert(0, os.path.join(ROOT, "homebrewnlp-mtf_b200"))
+    from obst.optimizer.backend import graph_slot_name
+
+    class P:
+        pass
+
+    with np.load(os.path.join(GOLDEN, "reference_optimizer.npz")) as f:
+        for case in OPT_CASES:
+            rec = _nested(f, case)
+            names = [str(n) for n in rec["names"]]
+            p = P()
+            p.optimizer = str(rec["optimizer"])
+            recorded = sorted(k for k in rec["steps"]["0"]["state"] if k not in names)
+            ranks = {n: rec["init"][n].ndim for n in names}
+            opt_key = p.optimizer.replace(":", "_")
+            made = []
+            for key in recorded:
+                _, _, tail = key.partition("/")
+                var_name, _, slot = tail.rpartition(f"/{opt_key}/")
+                made.append(graph_slot_name(p, var_name, slot, names.index(var_name), ranks[var_name]))
+            assert sorted(made) == recorded, (case, [m for m in made if m not in recorded][:3])

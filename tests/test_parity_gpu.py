@@ -676,6 +676,14 @@ def test_checkpoint_resume(cuda, tmp_path, chain):
     prefix = save_checkpoint(stopped, tfdir, exact=True, fmt="tf")
     assert prefix.endswith("model.ckpt-1502") and os.path.exists(prefix + ".index")
     assert os.path.exists(prefix + ".data-00000-of-00001") and os.path.exists(os.path.join(tfdir, "checkpoint"))
+    from obst.run import tf_checkpoint
+    keys = set(tf_checkpoint.read_bundle(prefix))
+    first_var = next(iter(stopped.variable_cache))
+    opt_key = stopped.optimizer.replace(":", "_")
+    slot_keys = [k for k in keys if f"/{opt_key}/" in k]
+    # slots are stored under the names they have in the reference's graph: "<stage><k>v/<variable>/<opt>/<slot>"
+    assert slot_keys and all(k.split("/")[0][-1] == "v" and k.split("/")[0][:-1][-1].isdigit() for k in slot_keys)
+    assert first_var in keys and "global_step" in keys
     probe2 = fresh()
     run_product_step(probe2, tok_x, tok_y)
     load_checkpoint(probe2, tfdir)  # the directory: resolved through the `checkpoint` state file
