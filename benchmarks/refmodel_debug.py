@@ -26,6 +26,10 @@ def main():
         x = torch.from_numpy(rec["tok_x"]).to(params.device)
         y = torch.from_numpy(rec["tok_y"]).to(params.device)
         step = rec["steps"]["0"]
+        twin = None
+        if "bf16" in case:
+            with np.load(GOLDEN) as f:
+                twin = _nested(f, case.replace("bf16", "f32") + "_twin")["steps"]["0"]["grads"]
         out = get_train_model(params, None, None, None, x, y, None, None, None, params.manual_global_step)
         print(case, "loss", read_scalars(params, out[3])["loss"], float(step["loss"]))
         for n in created:
@@ -35,7 +39,11 @@ def main():
             if g is None or mine is None:
                 print(f"  {n}: ref {None if g is None else np.linalg.norm(g):} mine {None if mine is None else np.linalg.norm(mine)}")
                 continue
-            print(f"  {n.replace('gpt0v/body0v/', '')[-70:]:70s} |ref| {np.linalg.norm(g):.3e} |mine| {np.linalg.norm(mine):.3e} rel {rel(mine.reshape(g.shape), g):.2e}")
+            extra = ""
+            if twin is not None:
+                t = twin[n]
+                extra = f" | f32 truth {np.linalg.norm(t):.3e}: ref-bf16 off {rel(g, t):.2e}, mine off {rel(mine.reshape(t.shape), t):.2e}"
+            print(f"  {n.replace('gpt0v/body0v/', '')[-70:]:70s} |ref| {np.linalg.norm(g):.3e} |mine| {np.linalg.norm(mine):.3e} rel {rel(mine.reshape(g.shape), g):.2e}{extra}")
 
 
 if __name__ == "__main__":

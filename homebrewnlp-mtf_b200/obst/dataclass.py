@@ -12,6 +12,8 @@ Extensions (no counterpart in the reference, all optional):
   device            torch device string
   fold_mid_norm     fold the group norm between W_mid and W_out into those two GEMMs (bf16, tcgen05 path): same
                     function, the normalised tensor is never written (model/basic.py).  Default true.
+  keep_logits       a training step's `token_out` holds the logits (a copy: the loss kernel writes the logit gradient
+                    over them in place); default false: `token_out` of a training step is that gradient buffer
   fold_mid_norm_backward  in the reversible backward also fold that norm's own backward into the GEMMs (the
                     gradient of W_out's input is never written either).  Default true.
   revnet_store_activations  keep every sub-block's intermediates instead of recomputing / reconstructing them in
@@ -64,7 +66,7 @@ DEFAULTS: typing.Dict[str, typing.Any] = dict(
 # extensions of this implementation (see module docstring)
 EXTENSIONS: typing.Dict[str, typing.Any] = dict(micro_batch_size=None, gemm_backend=0, device="cuda", init_seed=0,
                                                 revnet_store_activations=False, fold_mid_norm=True,
-                                                fold_mid_norm_backward=True)
+                                                fold_mid_norm_backward=True, keep_logits=False)
 
 
 class BlockConfig:

@@ -127,6 +127,10 @@ def _loss(params: ModelParameter, token_out: Tensor, txt_tgt: Tensor) -> Loss:
     sums = getattr(params, "loss_sums", None)  # one accumulator per step when driven by get_train_model
     if sums is None:
         sums = torch.zeros(3, dtype=torch.float64, device=logits.device)
+    if params.tape is not None and getattr(params, "keep_logits", False):
+        # the gradient overwrites the logits in place below; a caller that wants `token_out` back from a training step
+        # (the reference returns it, src/model/__init__.py:229) asks for this copy -- training loops do not
+        token_out.data = logits.clone()
     dlogits = logits  # gradient overwrites the logits in place
     native.xent_fwd_bwd(logits, txt_tgt.data, dlogits, sums, 1.0 / n_global, float(params.z_loss or 0.0))
     if params.tape is not None:

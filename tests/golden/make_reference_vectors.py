@@ -350,9 +350,46 @@ def model_cases():
                                               [norm, f"split_path-multiply;feed_forward-in:tanh;{mix}"])),
         "initial_position_embedding": cfg(use_initial_position_embedding=True, position_embedding="axial"),
         "macro_batching": cfg(macro_batching=2, depth=2),
+        # bf16 activations over fp32 slices, as the 32*_mixer configs run: the stand-ins round every op's output to
+        # bfloat16 -- a model of WHERE the graph rounds (each MTF op), not of XLA's internal accumulation
+        "mixer_bf16_none": cfg(calculation_dtype="bfloat16", memory_reduction_strategy="none", embedding_stddev=0.04, vocab_weight_factorization=1.0,
+                               train_batch_size=4),
+        "mixer_bf16_revnet": cfg(calculation_dtype="bfloat16", embedding_stddev=0.04, vocab_weight_factorization=1.0,
+                               train_batch_size=4),
+        # the same two models (same seeds, hence the same weights and tokens) in float32: the yardstick for how far
+        # bf16 takes ANY implementation from the truth
+        "mixer_f32_none_twin": cfg(memory_reduction_strategy="none", embedding_stddev=0.04, vocab_weight_factorization=1.0,
+                               train_batch_size=4),
+        "mixer_f32_revnet_twin": cfg(embedding_stddev=0.04, vocab_weight_factorization=1.0,
+                               train_batch_size=4),
         "adam_chain": cfg(optimizer="adam-learning_rate", depth=2),
     }
     return cases
+
+
+def describe_parameters(params):
+    """The derived attributes of a ModelParameter as plain JSON."""
+    def dims(ds):
+        return [[d.name, int(d.size)] for d in ds]
+
+    out = {k: getattr(params, k) for k in (
+        "features", "features_per_head", "heads", "depth", "sequence_length", "train_batch_size", "vocab_size",
+        "group_linear_factor", "intermediate_feed_forward_multiplier", "mesh_shape", "layout", "macro_batching",
+        "language_token_per_frame", "time_patch_size", "token_patch_size", "language_token_patch", "weight_decay",
+        "learning_rate", "optimizer", "memory_reduction_strategy", "use_video", "use_language", "z_loss",
+        "embedding_stddev", "scale_by_depth", "weight_centralisation", "weight_standardisation",
+        "position_embedding", "token_embedding", "output_embedding", "masked_attention_dimensions", "rezero_lr_multiplier",
+        "vocab_weight_factorization", "opt_beta1", "opt_beta2", "grad_accumulation", "input_dropout")}
+    out["feature_dims"] = dims(params.feature_dims)
+    out["intermediate"] = dims(params.intermediate)
+    out["named_dims"] = dims([params.head_dim, params.key_dim, params.vocab_dim, params.batch_dim, params.sequence_dim,
+                              params.token_patch_dim, params.macro_batch_dim])
+    out["token_dim_shape"] = dims(params.token_dim_shape.dims)
+    out["dtypes"] = {k: getattr(params, k).name for k in ("slice_dtype", "storage_dtype", "calculation_dtype",
+                                                          "optimizer_slice_dtype", "optimizer_calculation_dtype")}
+    out["learning_rate_config"] = {k: [v.start_step, v.final_step, v.factor] for k, v in params.learning_rate_config.items()}
+    out["block_config"] = [{"layer": list(b.layer), "skip": bool(b.skip)} for b in params.block_config]
+    return out
 
 
 def flatten(prefix, obj, out):
@@ -417,6 +454,23 @@ def main():
     np.savez_compressed(os.path.join(HERE, "reference_models.npz"), **out)
     if failed:
         print("FAILED CASES:", json.dumps(failed, indent=1))
+
+    # ---- src/dataclass.py:ModelParameter on the shipped configs: everything it derives ---------------------------
+    derived = {}
+    configs = {name[:-5]: json.load(open(os.path.join(REFERENCE, "configs", name)))
+               for name in sorted(os.listdir(os.path.join(REFERENCE, "configs"))) if name.endswith(".json")}
+    configs["small"] = small_config()
+    for name, config in configs.items():
+        config = dict(config)
+        if config.get("model_mode") == "gpt":  # src/main.py:87-93
+            config.update(use_video=False, use_language=True)
+        try:
+            derived[name] = describe_parameters(fresh_params(config))
+        except Exception as exc:  # noqa: BLE001
+            print("dataclass", name, "FAILED:", type(exc).__name__, exc)
+    with open(os.path.join(HERE, "reference_dataclass.json"), "w") as f:
+        json.dump(derived, f, indent=1, sort_keys=True)
+    print("dataclass ok:", sorted(derived))
 
 
 if __name__ == "__main__":

@@ -176,3 +176,45 @@ def test_graph_slot_names_match_what_the_reference_creates():
                 var_name, _, slot = tail.rpartition(f"/{opt_key}/")
                 made.append(graph_slot_name(p, var_name, slot, names.index(var_name), ranks[var_name]))
             assert sorted(made) == recorded, (case, [m for m in made if m not in recorded][:3])
+
+
+@pytest.mark.parametrize("name", ["32big_mixer", "32ctx_mixer", "32mixer_group", "small"])
+def test_model_parameter_derivations_match_the_reference_dataclass(name):
+    """src/dataclass.py:ModelParameter run on the shipped configs (tests/golden/reference_dataclass.json) against the
+    host mirror obst/dataclass.py: every derived size, dimension, dtype, embedding / optimizer string the step uses."""
+    sys.path.insert(0, os.path.join(ROOT, "homebrewnlp-mtf_b200"))
+    from obst.dataclass import ModelParameter, gpt_mode
+    with open(os.path.join(GOLDEN, "reference_dataclass.json")) as f:
+        want = json.load(f)[name]
+    if name == "small":
+        cfg = small_config()
+    else:  # the package's own copy of the shipped config: checked here against the reference's JSON, as parsed there
+        from obst.configs import mixer_config
+        cfg = mixer_config(name)
+    p = ModelParameter(gpt_mode(cfg))
+
+    def dims(ds):
+        return [[d.name, int(d.size)] for d in ds]
+
+    got = {"feature_dims": dims(p.feature_dims), "intermediate": dims(p.intermediate),
+           "named_dims": dims([p.head_dim, p.key_dim, p.vocab_dim, p.batch_dim, p.sequence_dim, p.token_patch_dim,
+                               p.macro_batch_dim]),
+           "token_dim_shape": dims(p.token_dim_shape),
+           "learning_rate_config": {k: [v.start_step, v.final_step, v.factor] for k, v in p.learning_rate_config.items()},
+           "block_config": [{"layer": list(b.layer), "skip": bool(b.skip)} for b in p.block_config]}
+    for key, value in got.items():
+        assert value == want[key], (key, value, want[key])
+    dtypes = {"float32": "float32", "bfloat16": "bfloat16"}
+    for key, value in want["dtypes"].items():
+        mine = getattr(p, key)
+        assert dtypes[value] in str(mine), (key, mine, value)
+    skip = {"feature_dims", "intermediate", "named_dims", "token_dim_shape", "learning_rate_config", "block_config",
+            "dtypes"}
+    for key, value in want.items():
+        if key in skip:
+            continue
+        mine = getattr(p, key)
+        if isinstance(value, float):
+            assert abs(mine - value) <= 1e-12 * max(1.0, abs(value)), (key, mine, value)
+        else:
+            assert (list(mine) if isinstance(value, list) else mine) == value, (key, mine, value)
