@@ -826,6 +826,40 @@ def slicewise(tf_fn, xs, output_shape=None, output_dtype=None, splittable_dims=N
                lambda op: tf_fn(*[t.np for t in op.inputs]), grad, name or "slicewise")
 
 
+UNIFORM_SOURCE = [None]  # the driver may supply (shape, minval, maxval) -> array, to share the draws with a checker
+
+
+def random_uniform(mesh, shape, **kwargs):
+    shape = convert_to_shape(shape)
+    dtype = kwargs.get("dtype", tf.float32)
+    lo, hi = kwargs.get("minval", 0), kwargs.get("maxval", 1)
+
+    def compute(op):
+        if UNIFORM_SOURCE[0] is not None:
+            return UNIFORM_SOURCE[0](shape.to_integer_list, lo, hi)
+        return np.random.default_rng(0).uniform(lo, hi, shape.to_integer_list)
+
+    return _op([], shape, dtype, compute, None, "random_uniform", mesh=mesh)
+
+
+BEFORE_LOOP_BODY = [None]  # the library traces a loop body ONCE; here it is re-run per iteration, and the driver uses
+#                             this hook to rewind the reference's name counters so that every re-run finds the same names
+
+
+def while_loop(cond_fn, body_fn, inputs, num_loop_vars=None, has_accumulators=False, **kwargs):
+    """Evaluated on the spot: the loop runs while cond_fn's (scalar) value is true."""
+    state = list(inputs)
+    while bool(np.asarray(cond_fn(*state).np).reshape(-1)[0]):
+        if BEFORE_LOOP_BODY[0] is not None:
+            BEFORE_LOOP_BODY[0]()
+        out = body_fn(*state)
+        for t in out:
+            if isinstance(t, Tensor):
+                t.np  # noqa: B018 -- evaluate now: the next iteration must not re-run this one lazily
+        state = list(out) + state[len(out):]
+    return state
+
+
 def recompute_grad(fn, explicit_inputs):
     return fn(*explicit_inputs)
 

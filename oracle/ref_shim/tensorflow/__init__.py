@@ -245,6 +245,7 @@ class _V1:
     zeros_initializer = _ZerosInitializer
     train = _train
     logging = types.SimpleNamespace(info=lambda *a, **k: None)
+    data = types.SimpleNamespace(Dataset=type("Dataset", (), {}))  # named in annotations only
 
     def __getattr__(self, name):
         try:

@@ -367,6 +367,58 @@ def model_cases():
     return cases
 
 
+def run_sampling(config, seed=5, initial_pos=4, temperatures=(0.0, 0.7)):
+    """src/run/inference.py:autoregressive_model (language branch) on the oracle's seeded weights: the whole sampling
+    loop -- forward pass per position, Gumbel-temperature argmax, shift, write-back.  The uniform draws are recorded so
+    that a checker can feed the same ones."""
+    from src.run.inference import autoregressive_model
+    sh = orc.Shapes(config)
+    weights = orc.init_params(sh, seed=seed)
+    names = orc.param_names(sh)
+    rng = np.random.default_rng(seed)
+    prompt = rng.integers(0, sh.vocab_size, [sh.train_batch_size, sh.sequence_length]).astype(np.int32)
+    record = {"oracle_names": names, "init": {n: weights[n] for n in names}, "prompt": prompt,
+              "initial_pos": initial_pos, "runs": []}
+    for temperature in temperatures:
+        cfg = dict(config, sampling_temperature=temperature, initial_autoregressive_position=initial_pos,
+                   use_autoregressive_sampling=True)
+        params = fresh_params(cfg)
+        params.train = False
+        mtf.VARIABLE_VALUES[:] = [weights[n] for n in names]
+        draws = []
+
+        def uniform(shape, lo, hi, draws=draws, rng=np.random.default_rng(100 + int(temperature * 10))):
+            u = rng.uniform(lo, hi, shape).astype(np.float32)
+            draws.append(u)
+            return u
+
+        mtf.UNIFORM_SOURCE[0] = uniform
+        names_at_loop = {}
+
+        def rewind(params=params):  # the loop body is traced once in the library: same names on every re-run
+            if not names_at_loop:
+                names_at_loop.update(utils_core.NAME_INDICES)
+            utils_core.NAME_INDICES.clear()
+            utils_core.NAME_INDICES.update(names_at_loop)
+            params.cached_parameters.clear()
+            params.attention_idx = 0
+
+        mtf.BEFORE_LOOP_BODY[0] = rewind
+        shape = params.token_dim_shape
+        tx = mtf.import_fully_replicated(params.mesh, prompt.reshape(shape.to_integer_list), shape, "x")
+        ty = mtf.import_fully_replicated(params.mesh, prompt.reshape(shape.to_integer_list), shape, "y")
+        try:
+            token_out, _ = autoregressive_model(params, token_x_input=tx, token_y_input=ty)
+            tokens = token_out.np.copy()
+        finally:
+            mtf.UNIFORM_SOURCE[0] = None
+            mtf.BEFORE_LOOP_BODY[0] = None
+            # only the first build creates variables; later iterations must not consume imposed values
+            mtf.VARIABLE_VALUES[:] = []
+        record["runs"].append({"temperature": temperature, "tokens": tokens, "uniform": np.stack(draws)})
+    return record
+
+
 def describe_parameters(params):
     """The derived attributes of a ModelParameter as plain JSON."""
     def dims(ds):
@@ -454,6 +506,34 @@ def main():
     np.savez_compressed(os.path.join(HERE, "reference_models.npz"), **out)
     if failed:
         print("FAILED CASES:", json.dumps(failed, indent=1))
+
+    out = {}
+    rec = run_sampling(small_config())
+    flatten("tiny", rec, out)
+    np.savez_compressed(os.path.join(HERE, "reference_sampling.npz"), **out)
+    print("sampling ok:", [r["tokens"].reshape(rec["prompt"].shape)[0, :10].tolist() for r in rec["runs"]])
+
+    # ---- src/optimizer/learning_rate.py:get_learning_rate over steps and module combinations ------------------------
+    schedules = {
+        "warmup": {"linear_warmup": {"final_step": 4096}},
+        "warmup_exp": {"linear_warmup": {"final_step": 100}, "exponential_decay": {"start_step": 50, "factor": 0.999}},
+        "warmup_linear_bounds": {"linear_warmup": {"final_step": 10}, "linear_decay": {"start_step": 20, "final_step": 400},
+                                 "lower_bound": {"factor": 1e-4}, "upper_bound": {"factor": 5e-3}},
+    }
+    steps = [0, 1, 5, 10, 49, 50, 51, 99, 100, 101, 399, 400, 1000, 4095, 4096, 100000]
+    lr_out = {}
+    for name, schedule in schedules.items():
+        cfg = small_config()
+        cfg["learning_rate_config"] = schedule
+        values = []
+        for step in steps:
+            params = fresh_params(cfg)
+            tf.GLOBAL_STEP[0] = np.asarray(step, np.int64)
+            values.append(float(np.asarray(get_learning_rate(params, [], []).learning_rate)))
+        lr_out[name] = {"schedule": schedule, "steps": steps, "values": values}
+    with open(os.path.join(HERE, "reference_learning_rate.json"), "w") as f:
+        json.dump(lr_out, f, indent=1)
+    print("learning rate ok:", {k: v["values"][:3] for k, v in lr_out.items()})
 
     # ---- src/dataclass.py:ModelParameter on the shipped configs: everything it derives ---------------------------
     derived = {}

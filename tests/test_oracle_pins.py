@@ -218,3 +218,50 @@ def test_model_parameter_derivations_match_the_reference_dataclass(name):
             assert abs(mine - value) <= 1e-12 * max(1.0, abs(value)), (key, mine, value)
         else:
             assert (list(mine) if isinstance(value, list) else mine) == value, (key, mine, value)
+
+
+def test_sampling_loop_matches_the_reference_autoregressive_model():
+    """src/run/inference.py:autoregressive_model, executed: the forward pass per position, log(-log U) * (-temperature)
+    added to the logits, argmax, shift by one, write-back at `position` -- greedy and at temperature 0.7, fed the
+    recorded uniform draws."""
+    with np.load(os.path.join(GOLDEN, "reference_sampling.npz")) as f:
+        rec = _nested(f, "tiny")
+    cfg = small_config()
+    sh = orc.Shapes(cfg)
+    names = [str(n) for n in rec["oracle_names"]]
+    params = {n: rec["init"][n].astype(np.float64) for n in names}
+    prompt = rec["prompt"]
+    first = int(rec["initial_pos"])
+    for r in sorted(rec["runs"], key=int):
+        run = rec["runs"][r]
+        uniform = run["uniform"]
+
+        def uniform_fn(pos, uniform=uniform):
+            return uniform[pos - first].reshape(prompt.shape[0], sh.sequence_length, -1)
+
+        got = orc.sample_tokens(sh, params, prompt, first, temperature=float(run["temperature"]), uniform_fn=uniform_fn)
+        want = run["tokens"].reshape(prompt.shape)
+        assert np.array_equal(got[:, :first], prompt[:, :first])
+        assert np.array_equal(got, want), (float(run["temperature"]), np.argwhere(got != want)[:5])
+
+
+def test_learning_rate_modules_match_the_reference():
+    """src/optimizer/learning_rate.py:get_learning_rate, executed, over 16 steps of three module combinations
+    (linear_warmup, exponential_decay, linear_decay, lower_bound, upper_bound) against orc.learning_rate and the host
+    mirror obst/optimizer/learning_rate.py."""
+    sys.path.insert(0, os.path.join(ROOT, "homebrewnlp-mtf_b200"))
+    from obst.dataclass import ModelParameter, gpt_mode
+    from obst.optimizer.learning_rate import get_learning_rate
+    with open(os.path.join(GOLDEN, "reference_learning_rate.json")) as f:
+        recs = json.load(f)
+    for name, rec in recs.items():
+        cfg = small_config()
+        cfg["learning_rate_config"] = rec["schedule"]
+        sh = orc.Shapes(cfg)
+        params = ModelParameter(gpt_mode(cfg))
+        for step, want in zip(rec["steps"], rec["values"]):
+            got = orc.learning_rate(sh, step)
+            assert abs(got - want) <= 2e-7 * abs(want) + 1e-12, (name, step, got, want)
+            params.global_step = step
+            mine = float(get_learning_rate(params, [], []).learning_rate)
+            assert abs(mine - want) <= 2e-7 * abs(want) + 1e-12, (name, step, mine, want)
