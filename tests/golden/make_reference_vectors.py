@@ -56,8 +56,9 @@ class LinearLoss(mtf.Operation):
 
     def gradient(self, grad_ys):
         dy = grad_ys[0]
-        return [mtf.import_fully_replicated(v.mesh, g.astype(np.float32), v.shape, "given_gradient") * dy
-                for v, g in zip(self.inputs, self.grads)]
+        # a gradient reaches get_optimizer in the dtype of the tensor it belongs to (the activation dtype)
+        return [mtf.cast(mtf.import_fully_replicated(v.mesh, g.astype(np.float32), v.shape, "given_gradient"), v.dtype)
+                * mtf.cast(dy, v.dtype) for v, g in zip(self.inputs, self.grads)]
 
 
 def fresh_params(config):
@@ -477,9 +478,17 @@ def main():
         "global_clip": ("global_l2norm_clip:0.2-momentum:0.95:0.5:1-learning_rate", 2, 1),
         "graft": ("graft:adam-learning_rate", 2, 1),
         "macro2": ("adaptive_clip:0.003-sm3-momentum:0.9:1:1-learning_rate", 2, 2),
+        # the dtype set of the 32*_mixer configs: bf16 activations and storage, bf16 optimizer slots, fp32 slices
+        "hot_path_bf16": ("adaptive_clip:0.003-sm3-momentum:0.9:1:1-learning_rate", 3, 1),
+        "adam_bf16": ("adam-learning_rate", 2, 1),
     }
     for name, (optimizer, steps, macro) in cases.items():
-        rec = run_optimizer_case(base, optimizer, steps, macro, seed=100 + list(cases).index(name))
+        cfg_case = dict(base)
+        if name.endswith("_bf16"):
+            cfg_case.update(calculation_dtype="bfloat16", storage_dtype="bfloat16", optimizer_slice_dtype="bfloat16")
+        rec = run_optimizer_case(cfg_case, optimizer, steps, macro, seed=100 + list(cases).index(name))
+        rec["dtypes"] = json.dumps({k: cfg_case[k] for k in ("calculation_dtype", "storage_dtype",
+                                                              "optimizer_slice_dtype", "slice_dtype")})
         rec["optimizer"] = optimizer
         rec["macro"] = macro
         flatten(name, rec, out)

@@ -46,7 +46,8 @@ def _nested(npz, prefix):
 ORACLE_NAMES = ["win_0", "wout_0", "g0_0", "mix_a", "w0", "rezero_0"]
 FIRST_STEP = 1500
 
-OPT_CASES = ["hot_path", "no_clip_heavyball", "adam", "novograd", "clips", "global_clip", "graft", "macro2"]
+OPT_CASES = ["hot_path", "no_clip_heavyball", "adam", "novograd", "clips", "global_clip", "graft", "macro2",
+             "hot_path_bf16", "adam_bf16"]
 
 
 @pytest.mark.parametrize("case", OPT_CASES)
@@ -62,6 +63,8 @@ def test_optimizer_matches_the_reference_get_optimizer(case):
     assert len(names) == len(ORACLE_NAMES)
     cfg = small_config()
     cfg["optimizer"] = optimizer
+    cfg.update(json.loads(str(rec["dtypes"])))
+    bf16 = cfg["calculation_dtype"] == "bfloat16"
     sh = orc.Shapes(cfg)
     params = {o: rec["init"][n].astype(np.float32) for o, n in zip(ORACLE_NAMES, names)}
     state = {o: {} for o in ORACLE_NAMES}  # slots appear on first use, zero (src/optimizer/backend.py:23-25)
@@ -74,6 +77,8 @@ def test_optimizer_matches_the_reference_get_optimizer(case):
         seen = None
         for i in range(macro):
             grads = {o: step["grads"][str(i)][str(j)].astype(np.float32) for j, o in enumerate(ORACLE_NAMES)}
+            if bf16:  # the graph hands the optimizer activation-dtype gradients (src/optimizer/__init__.py:180)
+                grads = {o: orc.round_bf16(g).reshape(g.shape) for o, g in grads.items()}
             last = i == macro - 1
             seen = orc.optimizer_step(sh, params, grads, state, lr, step_count=global_step + 1, seen=seen, assign=last)
         want = step["state"]
