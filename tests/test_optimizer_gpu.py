@@ -9,6 +9,7 @@ Bar: the kernels evaluate the same fp32 op sequence with correctly rounded opera
 and master weights must be BIT-IDENTICAL to the oracle (torch.equal on the raw values), shadows must be the bf16
 rounding of the new master with the causal mask applied, over three consecutive steps."""
 import ctypes
+import os
 import types
 
 import numpy as np
@@ -212,3 +213,48 @@ def test_transpose_batched(nat):
               "obst_transpose_batched")
     for a, b in zip(src, dst):
         assert torch.equal(b, a.transpose(1, 2).contiguous())
+
+
+@pytest.mark.parametrize("case,act_bf16,state_dtype,g_store_bf16", [
+    ("hot_path", False, torch.float32, False),
+    ("hot_path_bf16", True, torch.bfloat16, True),
+    ("hot_path_bf16", True, torch.bfloat16, False),
+])
+def test_fused_update_against_the_reference_run(nat, case, act_bf16, state_dtype, g_store_bf16):
+    """The CUDA update against what the REFERENCE'S OWN get_optimizer produced (tests/golden/reference_optimizer.npz:
+    /root/reference's src/optimizer run on NumPy stand-ins, see tests/golden/make_reference_vectors.py), three
+    consecutive steps on the recorded gradients: master weights to 2e-6, momentum and SM3 accumulators BIT FOR BIT in
+    the state dtype (fp32 slots: 1e-6, the two sides sum the clip norms in different orders)."""
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_optimizer.npz")
+    with np.load(path) as f:
+        keys = [k for k in f.files if k.startswith(case + "|")]
+        rec = {k[len(case) + 1:]: f[k] for k in keys}
+    names = [str(n) for n in rec["names"]]
+    use = [i for i, n in enumerate(names) if rec[f"init|{n}"].ndim >= 1]          # the rank-0 variable takes adam
+    shapes = [tuple(rec[f"init|{names[i]}"].shape) for i in use]
+    decay = [1 if "bottleneck" in names[i] else 0 for i in use]                     # src/optimizer/__init__.py:49-57
+    bank = Bank(nat, shapes, state_dtype, act_bf16, g_store_bf16, [0] * len(use), decay)
+    for p, i in zip(bank.p, use):
+        p.copy_(torch.from_numpy(rec[f"init|{names[i]}"]))
+    opt_key = "adaptive_clip_0.003-sm3-momentum_0.9_1_1-learning_rate"
+    for step in range(3):
+        grads = [torch.from_numpy(rec[f"steps|{step}|grads|0|{i}"]).to(DEV) for i in use]
+        if act_bf16:
+            grads = [g.to(torch.bfloat16).float() for g in grads]
+        bank.step(grads, (0.003, 0.9, 1, float(rec[f"steps|{step}|lr"]), 1e-4))
+        for k, i in enumerate(use):
+            n = names[i]
+            want = torch.from_numpy(rec[f"steps|{step}|state|{n}"]).to(DEV)
+            err = float((bank.p[k] - want).norm() / want.norm())
+            assert err < 2e-6, (step, n, err)
+            m_want = torch.from_numpy(rec[f"steps|{step}|state|momentum{i}v/{n}/{opt_key}/momentum"]).to(DEV)
+            if state_dtype == torch.bfloat16:
+                assert torch.equal(bank.m[k], m_want.to(torch.bfloat16)), (step, n, "momentum")
+            else:
+                assert float((bank.m[k] - m_want).abs().max() / m_want.abs().max()) < 1e-6, (step, n)
+            for d in range(len(shapes[k])):
+                a_want = torch.from_numpy(rec[f"steps|{step}|state|sm3{i}v/{n}/{opt_key}/dim{d}"]).to(DEV)
+                if state_dtype == torch.bfloat16:
+                    assert torch.equal(bank.acc[k][d], a_want.to(torch.bfloat16)), (step, n, d)
+                else:
+                    assert float((bank.acc[k][d] - a_want).abs().max() / a_want.abs().max()) < 1e-6, (step, n, d)
