@@ -243,7 +243,8 @@ def _mid_norm_out_folded(args: BlockArgs) -> Tensor:
     # of the norm's backward -- sum_j gamma_j dn_j = dy . (gamma^T W) and sum_j gamma_j h_j dn_j = dy . (h @ (gamma.W)),
     # the latter being a dot product with this very accumulator -- and dn = dy @ W^T never has to be written.
     up = getattr(params, "upstream_grad", None)
-    fold_bwd = (getattr(params, "fold_mid_norm_backward", True) and up is not None and pending is not None and params.tape is not None and gamma is not None
+    # (the row-dot epilogues exist in the CTA-pair kernel only: more than one 128-row tile)
+    fold_bwd = (T > 128 and getattr(params, "fold_mid_norm_backward", True) and up is not None and pending is not None and params.tape is not None and gamma is not None
                 and up.dtype == hd.dtype and tuple(up.shape) == tuple(dst.shape) and up.is_contiguous())
     dots = None
     if fold_bwd:
