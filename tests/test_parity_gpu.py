@@ -220,6 +220,21 @@ def test_sub_block_parity_inside_the_reversible_backward(cuda, name, seq, fph):
     assert calls, "the folded norm backward did not run"
 
 
+def test_sub_block_parity_in_the_reversible_backward_with_few_rows(cuda):
+    """64 rows at a foldable width: the forward fold still runs (its epilogues exist in the 128-row kernel), the
+    backward's row-dot epilogues do not (CTA-pair kernel only), so the norm's backward stays a kernel of its own --
+    same checks, no failure."""
+    from obst import native
+    calls = []
+    orig = native.norm_bwd_coeffs
+    native.norm_bwd_coeffs = lambda *a, **k: (calls.append(1), orig(*a, **k))[1]
+    try:
+        _sub_block_parity(0, 0, "bfloat16", 2e-2, batch=2, seq=32, fph=256, reversible=True)
+    finally:
+        native.norm_bwd_coeffs = orig
+    assert not calls
+
+
 def _sub_block_parity(backend, c, dtype, tol, batch, seq, fph, reversible=False):
     from obst import utils_core
     from obst.model.backend import run_tape
