@@ -850,3 +850,29 @@ def test_macro_batching_chain_matches_the_oracle(cuda, dtype, tol):
         if var.tril_s:
             seen = np.tril(seen)
         assert np.array_equal(to_np(var.value), seen), name
+
+
+def test_macro_batching_with_the_folded_norm(cuda):
+    """macro_batching over a foldable bottleneck (features_per_head 256, bf16, tcgen05): the weights a slice reads
+    are the chained previews, so gamma.W, gamma^T W, beta^T W must follow every preview -- the per-slice losses with
+    the norm folded (forward and backward) equal those of the separate norm kernels within the bf16 tier."""
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=128, features_per_head=256, macro_batching=2,
+               calculation_dtype="bfloat16", optimizer_slice_dtype="bfloat16", learning_rate=0.002)
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=23)
+    tok_x, tok_y = orc.synthetic_tokens(sh, batch=4)
+    from obst.run.train import read_scalars
+    results = []
+    for fold in (True, False):
+        params = make_params(cfg, op, fold_mid_norm=fold, fold_mid_norm_backward=fold)
+        params.global_step = 3000
+        losses = []
+        for _ in range(2):
+            out, scal = run_product_step(params, tok_x, tok_y)
+            losses += [read_scalars(params, out[4])["loss"], read_scalars(params, out[5])["loss"]]
+        results.append(losses)
+    for a, b in zip(*results):
+        assert abs(a - b) / b < 2e-2, results
+    # the second slice of a step really read other weights than the first (lr is large enough to show)
+    assert abs(results[0][0] - results[0][1]) > 1e-5, results
