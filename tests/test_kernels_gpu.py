@@ -574,3 +574,34 @@ def test_folded_group_norm_forward_and_backward_chain(nat, T, G, Kc, Np, sign):
     assert rel_err(dw, w64.grad) < 2e-2
     assert rel_err(dgamma, g64.grad) < 2e-2
     assert rel_err(dbeta, b64.grad) < 2e-2
+
+
+def test_folded_norm_epilogues_reject_what_they_cannot_run(nat):
+    """Epilogues 9 / 10 / 11 exist in the CTA-pair tensor-core kernel only and need their auxiliary tensors: anything
+    else is refused with an error, never run wrongly."""
+    bf = torch.bfloat16
+    G, Kc, Np = 2, 256, 256
+    stats = torch.zeros(128 * G, 2, device=DEV)
+    cvec = torch.zeros(G, Np, device=DEV)
+    wg_t = torch.zeros(G, Np, Kc, dtype=bf, device=DEV)
+
+    def fwd(T, epi, aux, backend=2):
+        h = torch.zeros(T, G * Kc, dtype=bf, device=DEV)
+        res = torch.zeros(T, G, Np, dtype=bf, device=DEV)
+        y = torch.empty(T, G, Np, dtype=bf, device=DEV)
+        nat.gemm(nat.operand(h, G * Kc, 1, s_glo=Kc), nat.operand(wg_t, Kc, 1, s_glo=Kc * Np), y, T, Np, Kc, GLO=G,
+                 d_ld=G * Np, d_glo=Np, R=res, epi=epi, backend=backend, aux=aux)
+
+    dy = torch.zeros(128, G, Np, dtype=bf, device=DEV)
+    dots = torch.zeros(128, G, 2, 2, device=DEV)
+    with pytest.raises(nat.NativeError, match="CTA-pair"):      # one 128-row tile: the 1-CTA kernel would run
+        fwd(128, 10, (stats, cvec, cvec, dy, dots))
+    with pytest.raises(nat.NativeError, match="aux3"):          # the second tile is missing
+        fwd(512, 10, (torch.zeros(512 * G, 2, device=DEV), cvec, cvec))
+    with pytest.raises(nat.NativeError, match="SIMT"):          # no fused-norm epilogue in the fp32-FMA kernel
+        fwd(512, 10, (torch.zeros(512 * G, 2, device=DEV), cvec, cvec, torch.zeros(512, G, Np, dtype=bf, device=DEV),
+                      torch.zeros(512, G, 2, 2, device=DEV)), backend=1)
+    with pytest.raises(nat.NativeError, match="aux0"):
+        fwd(512, 11, ())
+    with pytest.raises(nat.NativeError):
+        nat.norm_bwd_coeffs(torch.zeros(8, device=DEV), torch.zeros(8, device=DEV), torch.zeros(9, device=DEV)[1:], 1, 1, 4, 256)
