@@ -322,6 +322,15 @@ def model_cases():
                                                [norm, "feed_forward-in:gelu"])),
         # ('exp' is registered as ACTIVATIONS['exp'] = mtf.exp and called with the BlockArgs, not its tensor,
         # src/model/activation.py:201,211: it cannot run in the reference)
+        "norm_variants": cfg(memory_reduction_strategy="none", block_config=blocks(
+            ["norm", "feed_forward-in:relu"], ["norm-scale", mix], ["norm-shift-group", "feed_forward-in:relu"],
+            ["norm-scale-shift-features", mix])),
+        "bottleneck_variants": cfg(memory_reduction_strategy="none", block_config=blocks(
+            [norm, "bottleneck_group_linear-in:gelu-in:norm-in:scale-mid:silu-mid:glu"],
+            [norm, "bottleneck_group_linear-in:relu-mid:relu-mid:norm-mid:shift-mid:scale-mid:features-out:tanh"])),
+        "standalone_activations": cfg(memory_reduction_strategy="none", block_config=blocks(
+            [norm, "activation-silu", "feed_forward-in:relu"], [norm, "activation-mish", mix],
+            [norm, "activation-lecun_tanh", "activation-softsign", mix])),
         "cumsum_cummean": cfg(block_config=blocks([norm, "cumsum"], [norm, "cummean", "rezero"])),
         # (reduced_half_linear reshapes a [.., heads, _features] product back to the head-reduced input's shape,
         # src/model/basic.py:72-74,89-90: with more than one head mtf.reshape refuses the size change, so the layer has

@@ -24,7 +24,7 @@ pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(ROOT, "tests", "golden", "reference_models.npz")
 
 CASES = ["mixer_depth2", "strategy_none", "strategy_checkpoint_skip", "strategy_none_skip", "feed_forward_glu",
-         "activations", "cumsum_cummean", "group_linear", "transpose_sequence_features", "attention_embedded",
+         "activations", "norm_variants", "bottleneck_variants", "standalone_activations", "cumsum_cummean", "group_linear", "transpose_sequence_features", "attention_embedded",
          "attention_context_biased_softmax", "attention_maps", "attention_shared_key_value",
          "attention_shared_key_value_maps", "attention_relative", "attention_relative_learned", "attention_axial",
          "attention_stack_revnet", "split_path", "initial_position_embedding", "macro_batching", "adam_chain"]
