@@ -205,6 +205,27 @@ math = types.SimpleNamespace(softplus=softplus, tanh=tanh, square=square, sigmoi
 
 
 # ---- compat.v1: variable scopes (names only), initializers, the global step -----------------------------
+from . import _data  # noqa: E402
+
+data = types.SimpleNamespace(Dataset=_data.Dataset, TFRecordDataset=_data.TFRecordDataset,
+                             experimental=types.SimpleNamespace())
+io = types.SimpleNamespace(gfile=types.SimpleNamespace(glob=_data.glob), FixedLenFeature=_data.FixedLenFeature,
+                           VarLenFeature=_data.VarLenFeature, parse_single_example=_data.parse_single_example)
+strings = types.SimpleNamespace(unicode_decode=_data.unicode_decode)
+sparse = types.SimpleNamespace(to_dense=lambda x, **k: x)
+FixedLenFeature, VarLenFeature, parse_single_example = _data.FixedLenFeature, _data.VarLenFeature, _data.parse_single_example
+string = DType("string", np.object_, False)
+
+
+def function(fn=None, **kwargs):
+    """tf.function: the stand-in runs Python eagerly."""
+    return fn if fn is not None else (lambda f: f)
+
+
+def convert_to_tensor(x, dtype=None, name=None):
+    return np.asarray(x) if dtype is None else cast(np.asarray(x), dtype)
+
+
 class _Scope:
     def __init__(self):
         self.stack = []
@@ -245,7 +266,7 @@ class _V1:
     zeros_initializer = _ZerosInitializer
     train = _train
     logging = types.SimpleNamespace(info=lambda *a, **k: None)
-    data = types.SimpleNamespace(Dataset=type("Dataset", (), {}))  # named in annotations only
+    data = data
 
     def __getattr__(self, name):
         try:

@@ -429,6 +429,71 @@ def run_sampling(config, seed=5, initial_pos=4, temperatures=(0.0, 0.7)):
     return record
 
 
+def input_documents(kind, n_files=3, seed=9):
+    """Deterministic toy corpora: per file a few documents of 40-100 tokens (ints < 200, or ASCII text)."""
+    rng = np.random.default_rng(seed)
+    files = []
+    for _ in range(n_files):
+        docs = []
+        for _ in range(int(rng.integers(2, 4))):
+            tokens = rng.integers(32, 127, int(rng.integers(40, 100))).tolist()
+            docs.append(tokens if kind == "int64" else bytes(tokens).decode("ascii"))
+        files.append(docs)
+    return files
+
+
+def write_input_files(directory, kind):
+    """TFRecord files named as the reference expects (`int64` in the name selects decode_intstring; the trailing
+    number is the file's element count, src/inputs.py:34), written with the package's writer."""
+    sys.path.insert(0, os.path.join(ROOT, "homebrewnlp-mtf_b200"))
+    from obst.inputs import write_text_tfrecord
+    paths = []
+    for i, docs in enumerate(input_documents(kind)):
+        count = sum(len(d) for d in docs)
+        path = os.path.join(directory, f"toy_{kind}_{i}_{count}.tfrecord")
+        write_text_tfrecord(path, docs)
+        paths.append(path)
+    return paths
+
+
+def run_input_pipeline():
+    """src/inputs.py:gpt_neo_input on toy TFRecord files, through stand-ins for tf.data / TFRecordDataset /
+    parse_single_example: which windows come out, in which order, for which slice."""
+    import tempfile
+
+    from src.inputs import gpt_neo_input
+    out = {}
+    for kind in ("int64", "bytes"):
+        with tempfile.TemporaryDirectory() as directory:
+            write_input_files(directory, kind)
+            for shuffle in (0, 1):
+                for slice_index, slice_count in ((0, 1), (1, 2)):
+                    for interleaved in (1, 2):
+                        cfg = small_config()
+                        cfg.update(dataset_configs=[{"path": os.path.join(directory, "*.tfrecord"), "type": "text",
+                                                     "weight": 1}],
+                                   interleaved_datasets=interleaved, shuffle_input_filenames=shuffle, data_seed=7,
+                                   use_random_dataloader=False, token_patch_size=1)
+                        params = fresh_params(cfg)
+                        batches, partial = [], 0
+                        it = iter(gpt_neo_input(params, 2, slice_index, slice_count))
+                        while True:
+                            try:
+                                batches.append(next(it))
+                            except StopIteration:
+                                break
+                            except ValueError:
+                                # dset.batch(sub_batch_size) keeps a final partial batch, which _memory_func's
+                                # fixed-shape reshape rejects (src/inputs.py:543-545): the reference run ends there
+                                partial = 1
+                                break
+                        key = f"{kind}|shuffle{shuffle}|slice{slice_index}of{slice_count}|interleave{interleaved}"
+                        out[key + "|ended_on_partial_batch"] = np.asarray(partial)
+                        out[key + "|token_x"] = np.stack([np.asarray(b[0]) for b in batches])
+                        out[key + "|token_y"] = np.stack([np.asarray(b[1]) for b in batches])
+    return out
+
+
 def describe_parameters(params):
     """The derived attributes of a ModelParameter as plain JSON."""
     def dims(ds):
@@ -530,6 +595,10 @@ def main():
     flatten("tiny", rec, out)
     np.savez_compressed(os.path.join(HERE, "reference_sampling.npz"), **out)
     print("sampling ok:", [r["tokens"].reshape(rec["prompt"].shape)[0, :10].tolist() for r in rec["runs"]])
+
+    pipeline = run_input_pipeline()
+    np.savez_compressed(os.path.join(HERE, "reference_input_pipeline.npz"), **pipeline)
+    print("input pipeline ok:", {k: v.shape for k, v in list(pipeline.items())[:4]})
 
     # ---- src/optimizer/learning_rate.py:get_learning_rate over steps and module combinations ------------------------
     schedules = {
