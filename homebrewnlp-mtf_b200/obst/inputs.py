@@ -10,7 +10,8 @@ int32 torch tensors in the layout get_train_model takes ([batch, sequence, token
 parsed by hand (TFRecord framing with masked CRC-32C, protobuf wire format of Example), so no TensorFlow and no
 generated protobuf classes are needed.  `write_text_tfrecord` produces files the reference's pipeline reads.
 
-Deterministic path only: `use_random_dataloader` (shuffle buffer, repeat) and `runs_log` resume simulation raise."""
+Deterministic path only: `use_random_dataloader` (shuffle buffer, repeat) raises; a `runs_log` resumes where the
+logged runs stopped (`simulate_data_pipeline`)."""
 import glob
 import random
 import struct
@@ -241,17 +242,85 @@ def interleave(sources: typing.Iterable[typing.Iterator], cycle_length: int) -> 
         i = (i + 1) % len(slots)
 
 
+def _record_tokens(path) -> int:
+    """The element count a file name carries (`..._<count>.tfrecord`), read the way src/inputs.py:34 reads it: the last
+    `_` field with the CHARACTERS of '.tfrecord' stripped from both ends."""
+    return int(str(path).split("_")[-1].strip(".tfrecord"))
+
+
+def simulate_data_pipeline(runs_log: typing.Sequence[dict], file_list: typing.Sequence) -> typing.Tuple[list, list]:
+    """src/inputs.py:33-128: replays earlier runs over the (already ordered) file list to find where a resumed run
+    starts.  Returns (drop, consumed): per file, whether it is left out altogether and how many leading tokens of
+    each of its records are skipped.
+
+    One earlier run = {steps, grad_accumulation, batch_size, slice_count, ctx, interleave_size, token_patch_size}.
+    Every slice of that run read `steps * grad_accumulation * (batch_size // slice_count)` windows of `ctx` tokens,
+    round-robin over groups of `interleave_size` of its files.  The replay keeps the reference's arithmetic as it is,
+    including: a group the budget does not reach is still visited (it takes nothing, :106 tests the run's budget, not
+    what is left of it); a group the budget covers whole has its count SET to the usable length (:115), a group it
+    covers in part has the taken tokens ADDED (:103); files are dropped only by whole groups, and those groups are
+    formed over ALL files of the slice, dropped ones included (:118-126), while reading groups the live ones."""
+    size = [_record_tokens(f) for f in file_list]
+    n = len(size)
+    drop = [False] * n
+    consumed = [0] * n
+    for run in runs_log:
+        live = [i for i in range(n) if not drop[i]]
+        left = {i: size[i] - consumed[i] for i in live}
+        slices, ctx, patch = run["slice_count"], run["ctx"], run["token_patch_size"]
+        group = run["interleave_size"]
+        quota = run["steps"] * run["grad_accumulation"] * (run["batch_size"] // slices)
+        for s in range(slices):
+            mine = live[s::slices]
+            budget = quota
+            for start in range(0, len(mine), group):
+                members = mine[start:start + group]
+                usable = [left[i] - ((left[i] - patch) % ctx) - patch for i in members]
+                windows = sum(usable) // ctx
+                if windows <= budget:  # the whole group was read
+                    budget -= windows
+                    for i, u in zip(members, usable):
+                        drop[i] = True
+                        consumed[i] = u
+                    continue
+                rest = list(usable)
+                turn = 0
+                while budget > 0 and sum(rest) > 0:
+                    while rest[turn] <= 0:
+                        turn = (turn + 1) % len(rest)
+                    rest[turn] -= ctx
+                    budget -= 1
+                    turn = (turn + 1) % len(rest)
+                for i, u, r in zip(members, usable, rest):
+                    if r <= 0:
+                        drop[i] = True
+                    consumed[i] += u - r
+                if quota <= 0:
+                    break
+        for s in range(slices):
+            mine = list(range(n))[s::slices]
+            for start in range(0, len(mine), group):
+                members = mine[start:start + group]
+                gone = sum(drop[i] for i in members) == group
+                for i in members:
+                    drop[i] = gone
+    return drop, consumed
+
+
 def split_files(filenames: typing.Sequence[str], slice_index: int, slice_count: int, seed: int, runs_log=None):
     """src/inputs.py:15-30."""
     if not filenames:
         raise ValueError
-    if runs_log is not None:
-        raise NotImplementedError("runs_log resume simulation (simulate_data_pipeline) is outside the hot path")
     files = sorted(filenames)
     if seed != 0:
         random.seed(seed)
         random.shuffle(files)
-    return files[slice_index::slice_count], [0] * len(files[slice_index::slice_count])
+    skips = [0] * len(files)
+    if runs_log is not None:
+        drop, skips = simulate_data_pipeline(runs_log, files)
+        files = [f for f, d in zip(files, drop) if not d]
+        skips = [k for k, d in zip(skips, drop) if not d]
+    return files[slice_index::slice_count], skips[slice_index::slice_count]
 
 
 def gpt_neo_input(params: ModelParameter, sub_batch_size: int, slice_index: int, slice_count: int, runs_log=None,

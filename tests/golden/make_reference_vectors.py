@@ -494,6 +494,61 @@ def run_input_pipeline():
     return out
 
 
+def run_resume_simulation(n_cases=60, seed=21):
+    """src/inputs.py:simulate_data_pipeline / split_files on random file lists and run logs (pure integer host logic;
+    the file names carry the token counts), plus gpt_neo_input resumed from a log on the toy files."""
+    import tempfile
+
+    from src.inputs import gpt_neo_input, simulate_data_pipeline, split_files
+    rng = np.random.default_rng(seed)
+    cases = []
+    for _ in range(n_cases):
+        n_files = int(rng.integers(1, 13))
+        ctx = int(rng.choice([8, 16, 32]))
+        files = [f"data/set_{i:03d}_{int(rng.integers(0, 12 * ctx))}.tfrecord" for i in range(n_files)]
+        runs = []
+        for _ in range(int(rng.integers(1, 4))):
+            slice_count = int(rng.choice([1, 2, 4]))
+            runs.append({"steps": int(rng.integers(0, 9)), "grad_accumulation": int(rng.integers(1, 3)),
+                         "batch_size": slice_count * int(rng.integers(1, 4)), "slice_count": slice_count, "ctx": ctx,
+                         "interleave_size": int(rng.integers(1, 4)), "token_patch_size": int(rng.choice([1, 1, 2]))})
+        drop, consumed = simulate_data_pipeline(runs, sorted(files))
+        shuffle_seed = int(rng.choice([0, 5]))
+        slice_count = int(rng.choice([1, 2]))
+        split = [split_files(list(files), i, slice_count, shuffle_seed, runs) for i in range(slice_count)]
+        cases.append({"files": files, "runs_log": runs, "drop": [bool(d) for d in drop],
+                      "consumed": [int(c) for c in consumed], "seed": shuffle_seed, "slice_count": slice_count,
+                      "split": [[list(f), [int(k) for k in sk]] for f, sk in split]})
+    resumed = {}
+    with tempfile.TemporaryDirectory() as directory:
+        write_input_files(directory, "int64")
+        for interleaved, steps in ((1, 1), (2, 2), (2, 3)):
+            cfg = small_config()
+            cfg.update(dataset_configs=[{"path": os.path.join(directory, "*.tfrecord"), "type": "text", "weight": 1}],
+                       interleaved_datasets=interleaved, shuffle_input_filenames=0, data_seed=7,
+                       use_random_dataloader=False, token_patch_size=1)
+            params = fresh_params(cfg)
+            log = [{"steps": steps, "grad_accumulation": 1, "batch_size": 2, "slice_count": 1,
+                    "ctx": params.sequence_length, "interleave_size": interleaved, "token_patch_size": 1}]
+            batches = []
+            it = iter(gpt_neo_input(params, 2, 0, 1, log))
+            while True:
+                try:
+                    batches.append(next(it))
+                except (StopIteration, ValueError):  # ValueError: the final partial batch, as in run_input_pipeline
+                    break
+            resumed[f"interleave{interleaved}|steps{steps}"] = {
+                "runs_log": log, "token_x": [np.asarray(b[0]).tolist() for b in batches]}
+    return {"cases": cases, "resumed": resumed}
+
+
+def write_resume_simulation():
+    rec = run_resume_simulation()
+    with open(os.path.join(HERE, "reference_runs_log.json"), "w") as f:
+        json.dump(rec, f)
+    print("runs_log ok:", len(rec["cases"]), "cases;", {k: len(v["token_x"]) for k, v in rec["resumed"].items()})
+
+
 def describe_parameters(params):
     """The derived attributes of a ModelParameter as plain JSON."""
     def dims(ds):
@@ -541,6 +596,10 @@ def small_config():
 
 
 def main():
+    if sys.argv[1:] == ["runs_log"]:  # that file alone
+        write_resume_simulation()
+        return
+    write_resume_simulation()
     base = small_config()
     out = {}
     cases = {

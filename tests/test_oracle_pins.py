@@ -316,3 +316,38 @@ def test_text_input_pipeline_matches_the_reference_gpt_neo_input(tmp_path, kind)
                     assert np.array_equal(b["token_y"].numpy(), wy), key
                 checked += len(batches)
     assert checked > 40
+
+
+def test_resume_simulation_matches_the_reference_simulate_data_pipeline(tmp_path):
+    """src/inputs.py:simulate_data_pipeline and split_files(runs_log=...), executed on 60 random file lists / run logs,
+    and gpt_neo_input resumed from a log on the toy files: which files a resumed run leaves out, how many tokens of
+    each record it skips, and the windows it then reads -- against obst.inputs."""
+    sys.path.insert(0, os.path.join(ROOT, "homebrewnlp-mtf_b200"))
+    from obst.dataclass import ModelParameter, gpt_mode
+    from obst.inputs import gpt_neo_input, simulate_data_pipeline, split_files, write_text_tfrecord
+    with open(os.path.join(GOLDEN, "reference_runs_log.json")) as f:
+        golden = json.load(f)
+    dropped = partial = 0
+    for case in golden["cases"]:
+        drop, consumed = simulate_data_pipeline(case["runs_log"], sorted(case["files"]))
+        assert drop == case["drop"], case
+        assert consumed == case["consumed"], case
+        for i, (want_files, want_skips) in enumerate(case["split"]):
+            files, skips = split_files(list(case["files"]), i, case["slice_count"], case["seed"], case["runs_log"])
+            assert list(files) == want_files and list(skips) == want_skips, case
+        dropped += sum(drop)
+        partial += sum(1 for d, c in zip(drop, consumed) if c and not d)
+    assert dropped > 50 and partial > 20  # the vectors exercise both outcomes
+
+    for i, docs in enumerate(_toy_documents("int64")):
+        write_text_tfrecord(str(tmp_path / f"toy_int64_{i}_{sum(len(d) for d in docs)}.tfrecord"), docs)
+    for key, rec in golden["resumed"].items():
+        interleaved = int(key.split("|")[0][len("interleave"):])
+        cfg = small_config()
+        cfg.update(dataset_configs=[{"path": str(tmp_path / "*.tfrecord"), "type": "text", "weight": 1}],
+                   interleaved_datasets=interleaved, shuffle_input_filenames=0, data_seed=7,
+                   use_random_dataloader=False, token_patch_size=1)
+        batches = list(gpt_neo_input(ModelParameter(gpt_mode(cfg)), 2, 0, 1, rec["runs_log"]))
+        assert len(batches) == len(rec["token_x"]) > 0, key
+        for b, want in zip(batches, rec["token_x"]):
+            assert np.array_equal(b["token_x"].numpy(), np.asarray(want)), key
