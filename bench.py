@@ -45,6 +45,8 @@ def parse():
                          "it into the two GEMMs")
     ap.add_argument("--no-fold-norm-bwd", action="store_true",
                     help="A/B switch: keep the mid norm's backward as a separate kernel (dn written and re-read)")
+    ap.add_argument("--no-fuse-loss", action="store_true",
+                    help="A/B switch: LM head and softmax cross-entropy as two kernels (logits written and re-read)")
     ap.add_argument("--store-activations", action="store_true",
                     help="extension: keep activations instead of the reference's reversible recompute (reported "
                          "separately; the default run is the reference algorithm)")
@@ -384,6 +386,7 @@ def run_b200(args):
     cfg["revnet_store_activations"] = bool(args.store_activations)
     cfg["fold_mid_norm"] = not args.no_fold_norm
     cfg["fold_mid_norm_backward"] = not args.no_fold_norm_bwd
+    cfg["fuse_lm_head_loss"] = not args.no_fuse_loss
     cfg["micro_batch_size"] = mb
     cfg["device"] = f"cuda:{local_rank}"
     import contextlib

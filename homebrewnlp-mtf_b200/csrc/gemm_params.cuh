@@ -20,6 +20,7 @@ struct GemmParams {
   int32_t M, N, KI, KO, GLO, GHI;
   int32_t dtype_in, dtype_out;
   int32_t tri, epi, accumulate, splits;
+  float scalar0, scalar1;
 };
 
 int gemm_simt_launch(const GemmParams& p, cudaStream_t st);

@@ -17,7 +17,8 @@
 // Fused epilogues: ReLU, residual +/-, ReLU-backward mask, and the group norm around the bottleneck's W_mid / W_out
 // pair (5-8: row statistics out, norm applied to the accumulator, row-scaled weight gradient; 9-11: the same norm's
 // backward -- row dots of the accumulator with the upstream gradient, norm + ReLU backward on the dgrad accumulator --
-// in two instantiations of their own, gemm_tc_kernel<2, 1> / <2, 2>) -- include/obst_b200.h.
+// in two instantiations of their own, gemm_tc_kernel<2, 1> / <2, 2>), and the LM head's softmax cross-entropy (12,
+// gemm_tc_kernel<2, 3>: a 256-wide vocabulary is one tile, the logits never leave the SM) -- include/obst_b200.h.
 // Work items (tiles x split-K) are dealt round-robin to the CTA pairs: the split count is chosen for full rounds, and
 // triangular outputs number only their live tiles.  The set-up precedes a griddepcontrol.wait (programmatic dependent
 // launch): it overlaps the previous kernel's tail.
@@ -62,6 +63,7 @@ struct TcParams {
   const void* aux2;
   const void* aux3;
   void* aux4;
+  float scalar0, scalar1;              // epilogue 12: 1 / n, z_loss
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -579,6 +581,32 @@ __device__ __forceinline__ void epi_chunk_relu_stats(uint8_t* buf, int lane, con
   }
 }
 
+// Epilogue 12: the softmax cross-entropy's gradient for 64 columns of one row (columns col .. col + 63 of the
+// vocabulary), from the logits AS THEY WOULD HAVE BEEN STORED (bf16-rounded accumulator):
+//   d = (p - [n == tgt]) / n_tokens + (2 z logZ / n_tokens) p,   p = exp(l - max) / sum
+__device__ __forceinline__ float bf16_round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+
+__device__ __forceinline__ void epi_chunk_xent(uint8_t* buf, int lane, const uint32_t (&r)[64], int col, int tgt,
+                                               float mx, float inv_se, float inv_n, float zc) {
+  uint8_t* rowp = buf + lane * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4* slot = reinterpret_cast<uint4*>(rowp + ((j ^ (lane & 7)) << 4));
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float pr = expf(bf16_round(__uint_as_float(r[j * 8 + e])) - mx) * inv_se;
+      v[e] = (pr - (col + j * 8 + e == tgt ? 1.f : 0.f)) * inv_n + zc * pr;
+    }
+    uint4 o;
+    o.x = pack_bf16x2(v[0], v[1]);
+    o.y = pack_bf16x2(v[2], v[3]);
+    o.z = pack_bf16x2(v[4], v[5]);
+    o.w = pack_bf16x2(v[6], v[7]);
+    *slot = o;
+  }
+}
+
 template <int CG>
 struct Cfg {
   static constexpr int STAGES = CG == 2 ? 5 : 3;
@@ -592,6 +620,8 @@ struct Cfg {
 // rows in registers and take the two column chunks one after the other.  A kernel of its own so that the register
 // allocation of every other epilogue stays what it was.
 // MODE 2: the instantiation for epilogue 11 (the folded norm's backward), split off for the same reason.
+// MODE 3: the instantiation for epilogue 12 (LM head with the softmax cross-entropy): three passes over the row's
+// accumulator in TMEM (max / arg-max, sum of exponentials, gradient) -- the logits never leave the SM.
 template <int CG, int MODE = 0>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -755,6 +785,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint8_t* const buf0 = smem_epi + ew * 2 * EPI_BUF_BYTES;
       uint64_t* const rb0 = &rbar[ew * 2];
       uint32_t rphase = 0;  // bit s = phase of slab s's R barrier
+      [[maybe_unused]] double x_nll = 0.0, x_z = 0.0, x_hit = 0.0;  // epilogue 12: this thread's rows, all its tiles
       const int nchunks = (p.BN + EPI_BOX_COLS - 1) / EPI_BOX_COLS;
       for (int tile = cluster_id; tile < p.total_tiles; tile += num_clusters) {
         if (!get_tile<CG>(p, tile, t)) continue;
@@ -794,7 +825,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // 64 values into registers now -- the loads fly while the MMAs finish -- and the second chunk's line asked into
         // L2; it is fetched when the first chunk is done.  The two chunks are taken one after the other (`seq`): both
         // chunks' accumulators next to both rows of dy would not fit the register file.
-        constexpr bool seq = SEQ;
+        constexpr bool seq = SEQ || MODE == 3;  // (epilogue 12 keeps the row state of its loss next to the accumulator)
         uint32_t gy[SEQ ? 32 : 1];
         const bf16* dy_row = nullptr;
         // epilogues 9 / 10: c (gv) and d (dv) of the two chunks, two columns per lane
@@ -823,9 +854,57 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
         float s1 = 0.f, s2 = 0.f;  // epilogue 7 (sum, sum of squares); 9 / 10 (the two dot products)
+        [[maybe_unused]] int tgt = 0;
+        if constexpr (MODE == 3) {
+          if (row_live) {
+            tgt = __ldg(reinterpret_cast<const int32_t*>(p.aux0) + row0 + lane);
+            tgt = tgt < 0 ? 0 : (tgt >= p.N ? p.N - 1 : tgt);
+          }
+        }
         mbar_wait(&tfull_bar[acc], acc_phase, 3);
         tcgen05_fence_after();
         const uint32_t taddr0 = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * ACC_STRIDE);
+        [[maybe_unused]] float x_mx = 0.f, x_inv = 0.f, x_zc = 0.f;
+        if constexpr (MODE == 3) {
+          // the whole row (N == BN == 256) is read by BOTH warps of the quarter -- TMEM reads are cheap, an exchange
+          // between the warps is not -- each then writes its own two chunks; the `half == 0` warp counts the loss
+          float mx = -INFINITY;
+          int arg = 0;
+          for (int c = 0; c < 8; ++c) {
+            uint32_t r[32];
+            tmem_ld32(taddr0 + (uint32_t)(c * 32), r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float v = bf16_round(__uint_as_float(r[j]));
+              if (v > mx) {  // strict: the first index on ties (tf.argmax)
+                mx = v;
+                arg = c * 32 + j;
+              }
+            }
+          }
+          float se = 0.f, lt = 0.f;
+          for (int c = 0; c < 8; ++c) {
+            uint32_t r[32];
+            tmem_ld32(taddr0 + (uint32_t)(c * 32), r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const float v = bf16_round(__uint_as_float(r[j]));
+              se += expf(v - mx);
+              if (c * 32 + j == tgt) lt = v;
+            }
+          }
+          const float logz = logf(se) + mx;
+          x_mx = mx;
+          x_inv = 1.0f / se;
+          x_zc = 2.0f * p.scalar1 * p.scalar0 * logz;
+          if (half == 0 && row_live) {
+            x_nll += (double)(logz - lt);
+            x_z += (double)logz * (double)logz;
+            x_hit += (arg == tgt) ? 1.0 : 0.0;
+          }
+        }
         uint32_t ra[64], rc[64];
         if (c0 < nchunks) {
           tmem_ld32(taddr0 + (uint32_t)(c0 * EPI_BOX_COLS), *reinterpret_cast<uint32_t (*)[32]>(&ra[0]));
@@ -873,6 +952,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             else epi_chunk_affine_dots<10>(buf, lane, r, rs, rm, cdv[sl], cdv[2 + sl], gy, s1, s2);
           } else if constexpr (MODE == 2) {
             epi_chunk_norm_bwd(buf, lane, r, rs, rm, rk);
+          } else if constexpr (MODE == 3) {
+            epi_chunk_xent(buf, lane, r, colx, tgt, x_mx, x_inv, p.scalar0, x_zc);
           } else
           switch (p.epi) {
             case 0: epi_chunk<0>(buf, lane, r); break;
@@ -910,6 +991,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
+        }
+      }
+      if constexpr (MODE == 3) {
+        if (half == 0) {  // warp-uniform
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) {
+            x_nll += __shfl_xor_sync(0xffffffffu, x_nll, o);
+            x_z += __shfl_xor_sync(0xffffffffu, x_z, o);
+            x_hit += __shfl_xor_sync(0xffffffffu, x_hit, o);
+          }
+          if (lane == 0) {
+            double* sums = reinterpret_cast<double*>(p.aux4);
+            atomicAdd(sums, x_nll);
+            atomicAdd(sums + 1, x_z);
+            atomicAdd(sums + 2, x_hit);
+          }
         }
       }
       bulk_wait_all_elect();
@@ -1217,7 +1314,10 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
     TC_NOTSUP("obst_gemm(tc): epilogue 11 needs aux0 (float4 rows), GHI == 1, bf16 output and N %% 64 == 0");
   if (g.epi == 8 && g.aux1 && (!g.aux2 || (reinterpret_cast<uintptr_t>(g.aux1) & 15) != 0))
     TC_NOTSUP("obst_gemm(tc): epilogue 8 with aux1 needs aux2 and a 16-byte aligned aux1");
-  if (g.epi > 11 || g.epi < 0) TC_NOTSUP("obst_gemm(tc): unknown epilogue %d", g.epi);
+  if (g.epi > 12 || g.epi < 0) TC_NOTSUP("obst_gemm(tc): unknown epilogue %d", g.epi);
+  if (g.epi == 12 && (!g.aux0 || !g.aux4 || out_f32 || g.N != 256 || g.GLO * g.GHI != 1 || g.accumulate ||
+                      (reinterpret_cast<uintptr_t>(g.aux4) & 7) != 0))
+    TC_NOTSUP("obst_gemm(tc): epilogue 12 needs aux0 (targets), aux4 (double[3]), bf16 output, one group and N == 256");
   if (g.epi == 7 && (!g.aux0 || out_f32 || g.N % 256 != 0 || g.GLO * g.GHI != 1))
     TC_NOTSUP("obst_gemm(tc): epilogue 7 needs aux0, bf16 output, one group and N %% 256 == 0");
   if (g.epi == 8 && (!g.aux0 || !g.accumulate || g.GHI != 1))
@@ -1233,6 +1333,8 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   p.aux2 = g.aux2;
   p.aux3 = g.aux3;
   p.aux4 = g.aux4;
+  p.scalar0 = g.scalar0;
+  p.scalar1 = g.scalar1;
   p.d_ld = g.d_ld;
   p.d_glo = g.d_glo;
   p.d_ghi = g.d_ghi;
@@ -1259,7 +1361,7 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
     return e ? atoi(e) : 0;
   }();
   if (tri_cg == 1 && (g.tri == 1 || g.tri == 2)) cg = 1;
-  if (g.epi >= 9 && g.epi <= 11 && cg != 2) {
+  if (g.epi >= 9 && g.epi <= 12 && cg != 2) {
     if (strict) set_error("obst_gemm(tc): epilogue %d exists in the CTA-pair kernel only (M > 128, N > 64)", g.epi);
     return OBST_ENOTSUP;
   }
@@ -1339,7 +1441,7 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
     if (rd == OBST_ECUDA || rr == OBST_ECUDA) return OBST_ECUDA;
     p.tma_store = (rd == OBST_OK && rr == OBST_OK) ? 1 : 0;
   }
-  if (((g.epi >= 5 && g.epi <= 7) || (g.epi >= 9 && g.epi <= 11)) && !p.tma_store) {
+  if (((g.epi >= 5 && g.epi <= 7) || (g.epi >= 9 && g.epi <= 12)) && !p.tma_store) {
     if (strict) set_error("obst_gemm(tc): epilogue %d needs a TMA-addressable output", g.epi);
     return OBST_ENOTSUP;
   }
@@ -1354,6 +1456,8 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
       e = cudaFuncSetAttribute(gemm_tc_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(gemm_tc_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(gemm_tc_kernel<2, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<2>::SMEM);
     if (e != cudaSuccess) {
       set_error("obst_gemm(tc): cannot opt in to %d B of shared memory: %s", Cfg<2>::SMEM, cudaGetErrorString(e));
       return OBST_ECUDA;
@@ -1386,6 +1490,7 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
     cfg.numAttrs = pdl ? 2 : 1;
     cudaError_t e = (g.epi == 9 || g.epi == 10) ? cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2, 1>, tmA, tmB, tmD, tmR, p)
                     : g.epi == 11               ? cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2, 2>, tmA, tmB, tmD, tmR, p)
+                    : g.epi == 12               ? cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2, 3>, tmA, tmB, tmD, tmR, p)
                                                 : cudaLaunchKernelEx(&cfg, gemm_tc_kernel<2>, tmA, tmB, tmD, tmR, p);
     if (e != cudaSuccess) {
       set_error("obst_gemm(tc): cluster launch failed: %s", cudaGetErrorString(e));
@@ -1410,8 +1515,9 @@ extern "C" int obst_gemm(const obst_gemm_desc* d, int backend, void* stream) {
   OBST_REQUIRE(d->M > 0 && d->N > 0 && d->KI > 0 && d->KO > 0 && d->GLO > 0 && d->GHI > 0,
                "obst_gemm: bad sizes M=%d N=%d KI=%d KO=%d GLO=%d GHI=%d", d->M, d->N, d->KI, d->KO, d->GLO, d->GHI);
   OBST_REQUIRE(d->A.ptr && d->B.ptr && d->D, "obst_gemm: null operand");
-  OBST_REQUIRE(d->tri >= 0 && d->tri <= 3 && d->epi >= 0 && d->epi <= 11, "obst_gemm: bad tri/epi %d/%d", d->tri, d->epi);
-  OBST_REQUIRE(!(((d->epi >= 2 && d->epi <= 6) || d->epi >= 9) && d->R == nullptr), "obst_gemm: epilogue %d needs R",
+  OBST_REQUIRE(d->tri >= 0 && d->tri <= 3 && d->epi >= 0 && d->epi <= 12, "obst_gemm: bad tri/epi %d/%d", d->tri, d->epi);
+  OBST_REQUIRE(!(((d->epi >= 2 && d->epi <= 6) || (d->epi >= 9 && d->epi <= 11)) && d->R == nullptr),
+               "obst_gemm: epilogue %d needs R",
                d->epi);
   OBST_REQUIRE(!(d->accumulate && d->dtype_out != OBST_F32), "obst_gemm: accumulate needs fp32 output");
   OBST_REQUIRE(!(d->accumulate && d->epi >= 2 && d->epi != 8),
@@ -1428,6 +1534,7 @@ extern "C" int obst_gemm(const obst_gemm_desc* d, int backend, void* stream) {
   p.dtype_in = d->dtype_in; p.dtype_out = d->dtype_out;
   p.tri = d->tri; p.epi = d->epi; p.accumulate = d->accumulate; p.splits = d->splits;
   p.aux0 = d->aux0; p.aux1 = d->aux1; p.aux2 = d->aux2; p.aux3 = d->aux3; p.aux4 = d->aux4;
+  p.scalar0 = d->scalar0; p.scalar1 = d->scalar1;
   cudaStream_t st = (cudaStream_t)stream;
   if (d->epi >= 5) {  // the fused-norm epilogues exist in the tcgen05 kernel only
     OBST_REQUIRE(backend != 1, "obst_gemm: epilogue %d is not available in the SIMT kernel", d->epi);

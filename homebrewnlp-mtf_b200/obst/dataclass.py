@@ -16,6 +16,8 @@ Extensions (no counterpart in the reference, all optional):
                     over them in place); default false: `token_out` of a training step is that gradient buffer
   fold_mid_norm_backward  in the reversible backward also fold that norm's own backward into the GEMMs (the
                     gradient of W_out's input is never written either).  Default true.
+  fuse_lm_head_loss  softmax cross-entropy, z-loss and accuracy taken in the LM head GEMM's epilogue when the
+                    vocabulary is 256 wide (bf16, tcgen05 path, training): the logits are never written.  Default true.
   revnet_store_activations  keep every sub-block's intermediates instead of recomputing / reconstructing them in
                     backward (memory for speed; numerics differ from the reversible path only by the reference's
                     reconstruction rounding).  Default false = the reference's algorithm.
@@ -66,7 +68,8 @@ DEFAULTS: typing.Dict[str, typing.Any] = dict(
 # extensions of this implementation (see module docstring)
 EXTENSIONS: typing.Dict[str, typing.Any] = dict(micro_batch_size=None, gemm_backend=0, device="cuda", init_seed=0,
                                                 revnet_store_activations=False, fold_mid_norm=True,
-                                                fold_mid_norm_backward=True, keep_logits=False)
+                                                fold_mid_norm_backward=True, keep_logits=False,
+                                                fuse_lm_head_loss=True)
 
 
 class BlockConfig:

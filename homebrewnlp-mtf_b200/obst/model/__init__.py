@@ -90,8 +90,37 @@ def _body(params: ModelParameter, src: Tensor) -> Tensor:
                               f"'none' have a B200 path; 'momentum' (MomentumNet) does not")
 
 
-def _output(params: ModelParameter, out: Tensor) -> Tensor:
-    """src/model/__init__.py:138-145: logits = einsum(out[b,s,h,k], W_o[h,k,p,v])."""
+class FusedLoss:
+    """The loss taken in the LM head's own epilogue (obst_gemm epilogue 12): what `_output` needs to know of it."""
+
+    def __init__(self, targets: torch.Tensor, sums: torch.Tensor, n_global: int, z_loss: float):
+        self.targets, self.sums, self.n_global, self.z_loss = targets, sums, n_global, z_loss
+
+
+def _loss_sums(params: ModelParameter, device) -> torch.Tensor:
+    sums = getattr(params, "loss_sums", None)  # one accumulator per step when driven by get_train_model
+    if sums is None:
+        sums = torch.zeros(3, dtype=torch.float64, device=device)
+    return sums
+
+
+def _fused_loss(params: ModelParameter, out: Tensor, txt_tgt: Tensor) -> typing.Optional[FusedLoss]:
+    """LM head -> softmax cross-entropy as ONE kernel (src/model/__init__.py:144-145 -> src/mtf_wrapper.py:64-71) when
+    the vocabulary is one 256-column tile of the tcgen05 GEMM and the step wants the gradient, not the logits."""
+    vocab = params.token_patch_dim.size * params.vocab_dim.size
+    tokens = out.data.numel() // shape_size(params.feature_dims)
+    if (not getattr(params, "fuse_lm_head_loss", True) or params.tape is None or getattr(params, "keep_logits", False)
+            or out.data.dtype != torch.bfloat16 or params.gemm_backend == 1 or vocab != 256 or tokens <= 128
+            or txt_tgt.data.numel() != tokens or params.contrastive_across_samples
+            or params.contrastive_across_token_embeddings):
+        return None
+    return FusedLoss(txt_tgt.data, _loss_sums(params, out.data.device), params.n_global_targets or txt_tgt.size,
+                     float(params.z_loss or 0.0))
+
+
+def _output(params: ModelParameter, out: Tensor, fused: typing.Optional[FusedLoss] = None) -> Tensor:
+    """src/model/__init__.py:138-145: logits = einsum(out[b,s,h,k], W_o[h,k,p,v]).  With `fused`, the tensor returned
+    holds the loss's gradient with respect to the logits instead (they are never written)."""
     base_args = BlockArgs(params, out, [''])
     for config_idx, config in enumerate(params.output_block_config):
         out = block_part_fn(params, config, out, f'lang_out{config_idx}')
@@ -103,7 +132,12 @@ def _output(params: ModelParameter, out: Tensor) -> Tensor:
     T = x.numel() // F
     logits = torch.empty(list(x.shape[:-2]) + [d.size for d in new], dtype=x.dtype, device=x.device)
     be, dt, w = params.gemm_backend, x.dtype, var.value
-    native.gemm(native.operand(x, F, 1), native.operand(w, 1, V), logits, T, V, F, d_ld=V, dtype_in=dt, backend=be)
+    if fused is not None:
+        native.gemm(native.operand(x, F, 1), native.operand(w, 1, V), logits, T, V, F, d_ld=V, dtype_in=dt, backend=be,
+                    epi=12, aux=(fused.targets, None, None, None, fused.sums),
+                    scalars=(1.0 / fused.n_global, fused.z_loss))
+    else:
+        native.gemm(native.operand(x, F, 1), native.operand(w, 1, V), logits, T, V, F, d_ld=V, dtype_in=dt, backend=be)
     if params.tape is not None:
         def bwd(dy, mask, acc):
             native.gemm(native.operand(x, 1, F), native.operand(dy, 1, V), var.ensure_grad(), F, V, T, d_ld=V,
@@ -117,16 +151,18 @@ def _output(params: ModelParameter, out: Tensor) -> Tensor:
     return Tensor(logits, [d for d in out.dims if d not in old] + new)
 
 
-def _loss(params: ModelParameter, token_out: Tensor, txt_tgt: Tensor) -> Loss:
+def _loss(params: ModelParameter, token_out: Tensor, txt_tgt: Tensor, fused: typing.Optional[FusedLoss] = None) -> Loss:
     """softmax cross-entropy + z-loss + accuracy (src/mtf_wrapper.py:64-71, src/model/__init__.py:183-187).
     The normaliser is targets.size of the GLOBAL batch (all ranks, all micro-batches)."""
     if params.contrastive_across_samples or params.contrastive_across_token_embeddings:
         raise NotImplementedError("contrastive losses are outside the hot path")
+    if fused is not None:  # the LM head's epilogue has done it: token_out IS the gradient
+        dlogits = token_out.data
+        params.tape.append(TapeEntry(lambda dy, mask, acc: dlogits))
+        return Loss(fused.sums, fused.n_global, fused.z_loss)
     n_global = params.n_global_targets or txt_tgt.size
     logits = token_out.data
-    sums = getattr(params, "loss_sums", None)  # one accumulator per step when driven by get_train_model
-    if sums is None:
-        sums = torch.zeros(3, dtype=torch.float64, device=logits.device)
+    sums = _loss_sums(params, logits.device)
     if params.tape is not None and getattr(params, "keep_logits", False):
         # the gradient overwrites the logits in place below; a caller that wants `token_out` back from a training step
         # (the reference returns it, src/model/__init__.py:229) asks for this copy -- training loops do not
@@ -141,11 +177,13 @@ def _loss(params: ModelParameter, token_out: Tensor, txt_tgt: Tensor) -> Loss:
 def _build(params: ModelParameter, txt_src: Tensor, txt_tgt: Tensor):
     src = scoped("input", _input, params, txt_src)
     out = scoped("body", _body, params, src)
-    token_out = scoped("output", _output, params, out)
     if getattr(params, "skip_loss", False):  # sampling (obst.run.inference): the logits themselves are the result
+        token_out = scoped("output", _output, params, out)
         params.attention_idx = 0
         return None, token_out
-    token_loss = scoped("loss", _loss, params, token_out, txt_tgt)
+    fused = _fused_loss(params, out, txt_tgt)
+    token_out = scoped("output", _output, params, out, fused)
+    token_loss = scoped("loss", _loss, params, token_out, txt_tgt, fused)
     params.attention_idx = 0
     return token_loss, token_out
 

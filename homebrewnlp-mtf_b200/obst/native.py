@@ -32,7 +32,7 @@ class GemmDesc(ctypes.Structure):
                 ("GLO", c_i32), ("GHI", c_i32), ("A", Operand), ("B", Operand), ("D", c_void_p), ("R", c_void_p),
                 ("d_ld", c_i64), ("d_glo", c_i64), ("d_ghi", c_i64), ("tri", c_i32), ("epi", c_i32),
                 ("accumulate", c_i32), ("splits", c_i32), ("aux0", c_void_p), ("aux1", c_void_p), ("aux2", c_void_p),
-                ("aux3", c_void_p), ("aux4", c_void_p)]
+                ("aux3", c_void_p), ("aux4", c_void_p), ("scalar0", c_float), ("scalar1", c_float)]
 
 
 class OptTensor(ctypes.Structure):
@@ -239,7 +239,7 @@ def gemm_profile(on: bool):
 def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO: int = 1, GLO: int = 1, GHI: int = 1,
          d_ld: int, d_glo: int = 0, d_ghi: int = 0, d_offset: int = 0, R: typing.Optional[torch.Tensor] = None,
          r_offset: typing.Optional[int] = None, tri: int = 0, epi: int = 0, accumulate: bool = False, splits: int = 0,
-         dtype_in: torch.dtype = torch.bfloat16, backend: int = 0, aux=()):
+         dtype_in: torch.dtype = torch.bfloat16, backend: int = 0, aux=(), scalars=(0.0, 0.0)):
     """D[g,m,n] = epi(sum_k A[g,m,k] B[g,n,k]) -- see include/obst_b200.h for the full semantics."""
     _cuda(D, R)
     desc = GemmDesc()
@@ -255,6 +255,7 @@ def gemm(A: Operand, B: Operand, D: torch.Tensor, M: int, N: int, KI: int, *, KO
         desc.R = None
     desc.d_ld, desc.d_glo, desc.d_ghi = d_ld, d_glo, d_ghi
     desc.tri, desc.epi, desc.accumulate, desc.splits = tri, epi, int(accumulate), splits
+    desc.scalar0, desc.scalar1 = scalars
     for i, a in enumerate(aux):  # epilogues 5..11: row statistics / folded-norm vectors / row scales / second tiles
         if a is None:
             continue

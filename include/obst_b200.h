@@ -98,6 +98,14 @@ uint32_t obst_crc32c_portable(const void* host_data, int64_t nbytes, uint32_t cr
  *            D = [R > 0] * ( a[m,g] * acc + b[m,g] * R + c[m,g] ) with acc = dy @ (gamma . W)^T = gamma * dn (B is
  *            obst_fold_item.wg), R = the norm's input h (a ReLU output: the mask is its own derivative),
  *            aux0 = float4 (a, b, c, -) [M, GLO] from obst_norm_bwd_coeffs
+ *        12 (tcgen05 backend, bf16 out, one group, N == 256 = the whole vocabulary in one tile, M > 128): the LM head
+ *            with the softmax cross-entropy in its epilogue (src/model/__init__.py:144-145 -> src/mtf_wrapper.py:64-71,
+ *            accuracy src/model/__init__.py:185-187): the logits are never written.  Per row m, on the accumulator
+ *            rounded to bf16 (what obst_xent_fwd_bwd would have read back): logZ = log sum_n exp(l_n),
+ *            D[m, n] = (softmax_n - [n == t_m]) * scalar0 + 2 * scalar1 * scalar0 * logZ * softmax_n  (the gradient of
+ *            scalar0 * sum_m (logZ_m - l_{m,t_m} + scalar1 * logZ_m^2), as obst_xent_fwd_bwd with inv_n = scalar0,
+ *            z_loss = scalar1), aux0 = int32 targets [M] (clamped to the vocabulary),
+ *            aux4 = double[3] that receives += (sum nll, sum logZ^2, number of rows whose first arg-max is t_m)
  *   accumulate!=0: D (fp32 only) += value with atomics (split-K allowed; tri==3 masks the store)
  *   D/R address: ptr[g_lo*d_glo + g_hi*d_ghi + m*d_ld + n]; R may alias D.
  * backend: 0 auto (tcgen05 when dtype_in is bf16 and the geometry is TMA-legal, else SIMT),
@@ -125,11 +133,13 @@ typedef struct obst_gemm_desc {
   int32_t epi;
   int32_t accumulate;
   int32_t splits; /* split-K factor for accumulate mode; 0 = choose */
-  const void* aux0; /* epilogues 5..11, else NULL */
+  const void* aux0; /* epilogues 5..12, else NULL */
   const void* aux1;
   const void* aux2;
   const void* aux3;
   void* aux4;
+  float scalar0; /* epilogue 12 */
+  float scalar1;
 } obst_gemm_desc;
 
 int obst_gemm(const obst_gemm_desc* desc, int backend, void* stream);

@@ -605,3 +605,64 @@ def test_folded_norm_epilogues_reject_what_they_cannot_run(nat):
         fwd(512, 11, ())
     with pytest.raises(nat.NativeError):
         nat.norm_bwd_coeffs(torch.zeros(8, device=DEV), torch.zeros(8, device=DEV), torch.zeros(9, device=DEV)[1:], 1, 1, 4, 256)
+
+
+@pytest.mark.parametrize("T,F,z", [(1000, 512, 1e-4), (4096, 4096, 1e-4), (300, 256, 0.0)])
+def test_lm_head_with_the_cross_entropy_in_its_epilogue(nat, T, F, z):
+    """obst_gemm epilogue 12: LM head -> softmax cross-entropy + z-loss + accuracy as one kernel
+    (src/model/__init__.py:144-145 -> src/mtf_wrapper.py:64-71, accuracy :185-187).  Against the two-kernel path
+    (same bf16-rounded logits: the sums agree to float rounding, the hit count exactly, the gradient to an ulp of
+    bf16) and against float64 autograd; row tails, out-of-range targets (clamped like the separate kernel does)."""
+    bf, V = torch.bfloat16, 256
+    x = randn(T, F, seed=71, scale=1.0)
+    w = randn(F, V, seed=72, scale=3.0 / F ** 0.5)
+    tgt = torch.randint(0, V, (T,), dtype=torch.int32, device=DEV, generator=torch.Generator(DEV).manual_seed(5))
+    tgt[3], tgt[T - 1] = -7, V + 40
+    n_global = 3 * T
+    # two kernels
+    logits = torch.empty(T, V, dtype=bf, device=DEV)
+    nat.gemm(nat.operand(x, F, 1), nat.operand(w, 1, V), logits, T, V, F, d_ld=V, backend=2)
+    dl = torch.empty_like(logits)
+    sums = torch.zeros(3, dtype=torch.float64, device=DEV)
+    nat.xent_fwd_bwd(logits, tgt, dl, sums, 1.0 / n_global, z)
+    # one kernel, twice into the same accumulator (it adds)
+    fused = torch.full((T, V), float("nan"), dtype=bf, device=DEV)
+    fsums = torch.zeros(3, dtype=torch.float64, device=DEV)
+    for _ in range(2):
+        nat.gemm(nat.operand(x, F, 1), nat.operand(w, 1, V), fused, T, V, F, d_ld=V, backend=2, epi=12,
+                 aux=(tgt, None, None, None, fsums), scalars=(1.0 / n_global, z))
+    assert torch.allclose(fsums[:2] / 2, sums[:2], rtol=2e-6, atol=0), (fsums, sums)
+    assert float(fsums[2]) == 2 * float(sums[2])
+    assert torch.isfinite(fused.float()).all()
+    same = (fused == dl).float().mean().item()
+    assert same > 0.98, same
+    assert torch.allclose(fused.float(), dl.float(), rtol=8e-3, atol=1e-12)
+    # float64 autograd on the stored logits
+    lr = logits.double().requires_grad_(True)
+    logz = torch.logsumexp(lr, -1)
+    clamped = tgt.long().clamp(0, V - 1)
+    nll = (logz - lr.gather(1, clamped[:, None])[:, 0]).sum()
+    ((nll + z * (logz ** 2).sum()) / n_global).backward()
+    assert abs(float(fsums[0]) / 2 - float(nll)) / float(nll) < 1e-5
+    assert rel_err(fused, lr.grad) < 2e-2
+
+
+def test_lm_head_loss_epilogue_rejects_what_it_cannot_run(nat):
+    bf = torch.bfloat16
+    sums = torch.zeros(3, dtype=torch.float64, device=DEV)
+
+    def run(T, V, aux, backend=2):
+        x = torch.zeros(T, 64, dtype=bf, device=DEV)
+        w = torch.zeros(64, V, dtype=bf, device=DEV)
+        nat.gemm(nat.operand(x, 64, 1), nat.operand(w, 1, V), torch.empty(T, V, dtype=bf, device=DEV), T, V, 64,
+                 d_ld=V, backend=backend, epi=12, aux=aux, scalars=(1.0, 0.0))
+
+    tgt = torch.zeros(512, dtype=torch.int32, device=DEV)
+    with pytest.raises(nat.NativeError, match="N == 256"):
+        run(512, 128, (tgt, None, None, None, sums))
+    with pytest.raises(nat.NativeError, match="aux4|aux0"):
+        run(512, 256, (tgt,))
+    with pytest.raises(nat.NativeError, match="CTA-pair"):
+        run(128, 256, (tgt, None, None, None, sums))
+    with pytest.raises(nat.NativeError, match="SIMT"):
+        run(512, 256, (tgt, None, None, None, sums), backend=1)

@@ -876,3 +876,40 @@ def test_macro_batching_with_the_folded_norm(cuda):
         assert abs(a - b) / b < 2e-2, results
     # the second slice of a step really read other weights than the first (lr is large enough to show)
     assert abs(results[0][0] - results[0][1]) > 1e-5, results
+
+
+def test_lm_head_loss_fusion_matches_the_two_kernel_path(cuda):
+    """`fuse_lm_head_loss` (obst_gemm epilogue 12: softmax cross-entropy, z-loss and accuracy in the LM head's epilogue,
+    logits never written) against LM head + obst_xent_fwd_bwd: the same bf16-rounded logits enter both, so the first
+    step's loss and accuracy agree to float rounding and the weights move the same way within the bf16 tier; the fused
+    path is the one fewer launch per step."""
+    from obst import native
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=128, calculation_dtype="bfloat16",
+               optimizer_slice_dtype="bfloat16")
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=29)
+    tok_x, tok_y = orc.synthetic_tokens(sh, batch=2)
+    runs = []
+    for fuse in (True, False):
+        params = make_params(cfg, op, fuse_lm_head_loss=fuse)
+        params.global_step = 3000
+        scalars, launches, weights = [], [], None
+        for _ in range(2):
+            native.launch_count_reset()
+            out, scal = run_product_step(params, tok_x, tok_y)
+            launches.append(native.launch_count())
+            scalars.append(scal)
+            if weights is None:  # after the FIRST step: both runs read identical weights there, the second step's
+                # gradients also carry the bf16 reconstruction noise of slightly different weights (see budget())
+                weights = {n: to_np(v.data) for n, v in variables_by_oracle_name(params, sh).items()}
+        runs.append((scalars, launches, weights))
+    (fs, fl, fw), (us, ul, uw) = runs
+    assert fl[1] == ul[1] - 1, (fl, ul)
+    assert abs(fs[0]["loss"] - us[0]["loss"]) <= 2e-6 * abs(us[0]["loss"]), (fs, us)
+    assert fs[0].get("accuracy") == us[0].get("accuracy"), (fs, us)
+    assert abs(fs[1]["loss"] - us[1]["loss"]) <= 2e-3 * abs(us[1]["loss"]), (fs, us)
+    for name in fw:
+        move_f, move_u = fw[name] - op[name], uw[name] - op[name]
+        if np.linalg.norm(move_u) > 0:
+            assert rel(move_f, move_u) < 2e-2, (name, rel(move_f, move_u))
