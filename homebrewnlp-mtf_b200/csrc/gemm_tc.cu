@@ -55,6 +55,7 @@ struct TcParams {
   int32_t splits, tri, epi, accumulate, out_f32;
   int32_t tma_store;                   // bf16 output through smem staging + TMA store (and TMA load of R)
   int32_t tri_live;                    // tri == 3 with square tiles: tiles per group on or below the diagonal (else 0)
+  int32_t m_first;                     // number the M tiles of one N tile first (the tiles that share B become neighbours)
   int32_t a_mn, b_mn;                  // 1 = MN-major operand
   int32_t a_uglo, a_ughi, a_uko;       // does the operand depend on g_lo / g_hi / ko
   int32_t b_uglo, b_ughi, b_uko;
@@ -380,6 +381,11 @@ __device__ __forceinline__ bool get_tile(const TcParams& p, int tile, Tile& t) {
       ++mt;
     }
     nt = idx;
+  } else if (p.m_first) {
+    mt = tile % p.tiles_m;
+    r = tile / p.tiles_m;
+    nt = r % p.tiles_n;
+    r /= p.tiles_n;
   } else {
     nt = tile % p.tiles_n;
     r = tile / p.tiles_n;
@@ -1422,6 +1428,14 @@ int gemm_tc_launch(const GemmParams& g, cudaStream_t st, bool strict) {
   const int64_t total = base_tiles * splits;
   OBST_REQUIRE(total < (1ll << 31), "obst_gemm(tc): too many tiles");
   p.total_tiles = (int)total;
+  // A weight gradient whose big operand is B (W_mid: 2 M tiles x 32 N tiles, each slab of dh serves the 2 M tiles):
+  // with the M tiles numbered first the two tiles that read the same slab run on neighbouring CTA pairs; numbered
+  // N-first they ran 32 pairs apart and half of the slab was fetched from DRAM twice (ncu).  OBST_GEMM_M_FIRST=0: off.
+  static const bool m_first_off = [] {
+    const char* e = getenv("OBST_GEMM_M_FIRST");
+    return e && e[0] == '0';
+  }();
+  p.m_first = (!m_first_off && g.accumulate && g.tri == 0 && p.tiles_m > 1 && p.tiles_m < p.tiles_n) ? 1 : 0;
 
   CUtensorMap tmA, tmB;
   int rc = make_operand_map(g.A, g.a_mn, g.a_k, g.a_ko, g.a_glo, g.a_ghi, g.M, g.KI, g.KO, g.GLO, g.GHI, a_mn, BM, &tmA,
