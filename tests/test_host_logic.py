@@ -246,3 +246,35 @@ def test_update_work_list_covers_every_row_once():
             os.environ.pop("OBST_OPT_DRAIN", None)
         else:
             os.environ["OBST_OPT_DRAIN"] = old
+
+
+def test_the_loss_rides_on_the_lm_head_only_where_its_epilogue_exists():
+    """`_fused_loss` (obst/model/__init__.py): obst_gemm epilogue 12 needs bf16, the tcgen05 kernel, a 256-wide
+    vocabulary in one tile, more than one 128-row tile of tokens, and a step that wants the gradient -- anything
+    else keeps LM head and obst_xent_fwd_bwd apart."""
+    import torch
+
+    from obst.model import _fused_loss
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(calculation_dtype="bfloat16", train_batch_size=2, sequence_length=128)
+
+    def decide(dtype=torch.bfloat16, tokens=256, tape=True, **overrides):
+        c = copy.deepcopy(cfg)
+        c.update(overrides)
+        params = ModelParameter(gpt_mode(c))
+        params.tape = [] if tape else None
+        feat = [d.size for d in params.feature_dims]
+        out = Tensor(torch.zeros([tokens] + feat, dtype=dtype), [Dimension("tokens", tokens)] + params.feature_dims)
+        tgt = Tensor(torch.zeros(tokens, 1, dtype=torch.int32), [Dimension("tokens", tokens), params.token_patch_dim])
+        return _fused_loss(params, out, tgt)
+
+    fused = decide()
+    assert fused is not None and fused.n_global == 256 and fused.sums.dtype == torch.float64
+    assert abs(fused.z_loss - cfg.get("z_loss", 1e-4)) < 1e-12
+    assert decide(dtype=torch.float32) is None            # fp32 runs the SIMT GEMM
+    assert decide(tokens=128) is None                     # one 128-row tile: the 1-CTA kernel has no such epilogue
+    assert decide(tape=False) is None                     # evaluation wants the logits, not their gradient
+    assert decide(vocab_size=128) is None and decide(vocab_size=512) is None
+    assert decide(keep_logits=True) is None
+    assert decide(gemm_backend=1) is None
+    assert decide(fuse_lm_head_loss=False) is None
