@@ -1,7 +1,6 @@
 """Times the individual kernels at 32big_mixer shapes (CUDA events, L2-cold inputs) -- a development probe."""
 import os
 import sys
-import time
 
 import torch
 

@@ -50,7 +50,6 @@ def main():
     ms = timed(False)
     ms_with_transposes = timed(True)
     # per-kernel split (CUDA events around each launch of one extra step)
-    import ctypes  # noqa: F401
     lib = native.load()
     evs = []
     for name in ("obst_opt_norms", "obst_opt_update", "obst_opt_finalize"):

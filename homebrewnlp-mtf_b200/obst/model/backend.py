@@ -15,7 +15,7 @@ import torch
 from .. import native
 from ..dataclass import BlockArgs, ModelParameter
 from ..utils_core import current_scope, random_name, scope_list, scoped
-from ..utils_mtf import DIM_LIST, Dimension, Tensor, deduplicate, shape_size, shape_sub
+from ..utils_mtf import DIM_LIST, Tensor, deduplicate, shape_size, shape_sub
 
 
 class Variable:
