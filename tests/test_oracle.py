@@ -161,7 +161,7 @@ def test_hand_written_backward_matches_autograd():
     tp = {k: torch.from_numpy(v.astype(np.float64)).requires_grad_(True) for k, v in p.items()}
     tloss = _torch_forward(sh, tp, tx, ty)
     tloss.backward()
-    assert abs(float(tloss) - loss) < 1e-10
+    assert abs(float(tloss.detach()) - loss) < 1e-10
     for k, v in tp.items():
         ref = v.grad.numpy()
         err = np.linalg.norm(grads[k] - ref) / (np.linalg.norm(ref) + 1e-30)
