@@ -28,6 +28,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
+OUT = os.environ.get("OBST_GOLDEN_OUT", HERE)  # where the vectors go (tests/test_golden_regeneration.py: a scratch directory)
 REFERENCE = "/root/reference"
 sys.path.insert(0, os.path.join(ROOT, "oracle", "ref_shim"))
 sys.path.insert(0, REFERENCE)
@@ -544,7 +545,7 @@ def run_resume_simulation(n_cases=60, seed=21):
 
 def write_resume_simulation():
     rec = run_resume_simulation()
-    with open(os.path.join(HERE, "reference_runs_log.json"), "w") as f:
+    with open(os.path.join(OUT, "reference_runs_log.json"), "w") as f:
         json.dump(rec, f)
     print("runs_log ok:", len(rec["cases"]), "cases;", {k: len(v["token_x"]) for k, v in rec["resumed"].items()})
 
@@ -626,13 +627,13 @@ def main():
         rec["macro"] = macro
         flatten(name, rec, out)
         print("optimizer case", name, "ok:", len(rec["steps"]), "steps")
-    np.savez_compressed(os.path.join(HERE, "reference_optimizer.npz"), **out)
+    np.savez_compressed(os.path.join(OUT, "reference_optimizer.npz"), **out)
 
     out = {}
     rec = run_training_step(small_config())
     flatten("tiny", rec, out)
     print("training step ok: loss", [s["loss"] for s in rec["steps"]])
-    np.savez_compressed(os.path.join(HERE, "reference_training_step.npz"), **out)
+    np.savez_compressed(os.path.join(OUT, "reference_training_step.npz"), **out)
 
     out = {}
     failed = {}
@@ -645,18 +646,18 @@ def main():
             continue
         flatten(name, rec, out)
         print("model case", name, "ok: loss", [round(s["loss"], 5) for s in rec["steps"]], len(rec["created"]), "variables")
-    np.savez_compressed(os.path.join(HERE, "reference_models.npz"), **out)
+    np.savez_compressed(os.path.join(OUT, "reference_models.npz"), **out)
     if failed:
         print("FAILED CASES:", json.dumps(failed, indent=1))
 
     out = {}
     rec = run_sampling(small_config())
     flatten("tiny", rec, out)
-    np.savez_compressed(os.path.join(HERE, "reference_sampling.npz"), **out)
+    np.savez_compressed(os.path.join(OUT, "reference_sampling.npz"), **out)
     print("sampling ok:", [r["tokens"].reshape(rec["prompt"].shape)[0, :10].tolist() for r in rec["runs"]])
 
     pipeline = run_input_pipeline()
-    np.savez_compressed(os.path.join(HERE, "reference_input_pipeline.npz"), **pipeline)
+    np.savez_compressed(os.path.join(OUT, "reference_input_pipeline.npz"), **pipeline)
     print("input pipeline ok:", {k: v.shape for k, v in list(pipeline.items())[:4]})
 
     # ---- src/optimizer/learning_rate.py:get_learning_rate over steps and module combinations ------------------------
@@ -677,7 +678,7 @@ def main():
             tf.GLOBAL_STEP[0] = np.asarray(step, np.int64)
             values.append(float(np.asarray(get_learning_rate(params, [], []).learning_rate)))
         lr_out[name] = {"schedule": schedule, "steps": steps, "values": values}
-    with open(os.path.join(HERE, "reference_learning_rate.json"), "w") as f:
+    with open(os.path.join(OUT, "reference_learning_rate.json"), "w") as f:
         json.dump(lr_out, f, indent=1)
     print("learning rate ok:", {k: v["values"][:3] for k, v in lr_out.items()})
 
@@ -694,7 +695,7 @@ def main():
             derived[name] = describe_parameters(fresh_params(config))
         except Exception as exc:  # noqa: BLE001
             print("dataclass", name, "FAILED:", type(exc).__name__, exc)
-    with open(os.path.join(HERE, "reference_dataclass.json"), "w") as f:
+    with open(os.path.join(OUT, "reference_dataclass.json"), "w") as f:
         json.dump(derived, f, indent=1, sort_keys=True)
     print("dataclass ok:", sorted(derived))
 
