@@ -913,3 +913,26 @@ def test_lm_head_loss_fusion_matches_the_two_kernel_path(cuda):
         move_f, move_u = fw[name] - op[name], uw[name] - op[name]
         if np.linalg.norm(move_u) > 0:
             assert rel(move_f, move_u) < 2e-2, (name, rel(move_f, move_u))
+
+
+def test_log_dict_of_a_training_step(cuda):
+    """obst/run/summary.py:log_dict on what get_train_model returned: the reference's six scalar names
+    (src/run/run.py:123-132) with the values read_scalars gives, macro-batching included (first / last slice)."""
+    from obst.run.summary import log_dict
+    from obst.run.train import read_scalars
+    cfg = copy.deepcopy(orc.TINY_CONFIG)
+    cfg.update(depth=1, train_batch_size=2, sequence_length=64, macro_batching=2)
+    sh = orc.Shapes(cfg)
+    op = orc.init_params(sh, seed=31)
+    tok_x, tok_y = orc.synthetic_tokens(sh, batch=4)
+    params = make_params(cfg, op)
+    params.global_step = 2048
+    out, scal = run_product_step(params, tok_x, tok_y)
+    d = log_dict(params, out)
+    assert list(d) == ["learning_rate", "first_loss", "last_loss", "mean_loss", "token_loss", "accuracy"]
+    assert abs(d["learning_rate"] - float(out[2])) < 1e-12 and d["learning_rate"] > 0
+    assert d["mean_loss"] == scal["loss"]
+    assert d["first_loss"] == read_scalars(params, out[4])["loss"]
+    assert d["last_loss"] == read_scalars(params, out[5])["loss"] == d["token_loss"]
+    assert d["accuracy"] == read_scalars(params, out[5])["accuracy"]
+    assert abs(0.5 * (d["first_loss"] + d["last_loss"]) - d["mean_loss"]) < 1e-6 * d["mean_loss"]
